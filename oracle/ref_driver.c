@@ -1,0 +1,244 @@
+/* oracle/ref_driver.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * Picture-level driver around the UNMODIFIED reference sources, compiled where they lie
+ * under /root/reference (see oracle/Makefile). It fills the minimum of
+ * PictureParentControlSet_t / SequenceControlSet_t / MeContext_t that
+ * MotionEstimateLcu (EbMotionEstimation.c:6152) reads, stages each SB exactly like
+ * MotionEstimationKernel does (EbMotionEstimationProcess.c:481-555) and converts
+ * me_results[][] into the flat MeoPuResult image declared in me_oracle.h.
+ *
+ * EbMotionEstimation.c is #included (unity build) so its static functions are reachable;
+ * no reference source is copied into this repository.
+ */
+#include "EbMotionEstimation.c"          /* resolved through -I$(REF)/Lib/Codec */
+#include "EbMotionEstimationProcess.h"
+#include "EbPictureAnalysisProcess.h"
+#include "EbMcp.h"
+#include "me_oracle.h"
+#include <stdlib.h>
+#include <string.h>
+
+extern EbMemoryMapEntry *memoryMap;
+extern uint32_t         *memoryMapIndex;
+extern uint64_t         *totalLibMemory;
+
+extern void *set_me_hme_params_oq(MeContext_t *, PictureParentControlSet_t *, SequenceControlSet_t *, EbInputResolution);
+extern void Decimation2D(uint8_t *, uint32_t, uint32_t, uint32_t, uint8_t *, uint32_t, uint32_t);
+
+static void ensure_memory_map(void) {
+    static EbMemoryMapEntry *map; static uint32_t idx; static uint64_t total;
+    if (!map) map = (EbMemoryMapEntry *)calloc(4096, sizeof(EbMemoryMapEntry));
+    idx = 0;                    /* we never free through the map; just keep it from overflowing */
+    memoryMap = map; memoryMapIndex = &idx; totalLibMemory = &total;
+}
+
+static void plane_to_desc(const MeoPlane *p, EbPictureBufferDesc_t *d) {
+    memset(d, 0, sizeof(*d));
+    d->bufferY = p->buf; d->strideY = (uint16_t)p->stride;
+    d->origin_x = (uint16_t)p->origin_x; d->origin_y = (uint16_t)p->origin_y;
+    d->width = (uint16_t)p->width; d->height = (uint16_t)p->height;
+    d->maxWidth = d->width; d->maxHeight = d->height;
+}
+
+typedef struct RefPa {
+    EbObjectWrapper_t wrapper;
+    EbPaReferenceObject_t *obj;
+    EbPictureBufferDesc_t full, quarter, sixteenth;
+} RefPa;
+
+static void pa_init(RefPa *pa, const MeoPyramid *pyr) {
+    pa->obj = (EbPaReferenceObject_t *)calloc(1, sizeof(EbPaReferenceObject_t));
+    plane_to_desc(&pyr->full, &pa->full);
+    plane_to_desc(&pyr->quarter, &pa->quarter);
+    plane_to_desc(&pyr->sixteenth, &pa->sixteenth);
+    pa->obj->inputPaddedPicturePtr = &pa->full;
+    pa->obj->quarterDecimatedPicturePtr = &pa->quarter;
+    pa->obj->sixteenthDecimatedPicturePtr = &pa->sixteenth;
+    memset(&pa->wrapper, 0, sizeof(pa->wrapper));
+    pa->wrapper.objectPtr = pa->obj;
+}
+
+/* EbPictureAnalysisProcess.c:4866-4937 driven with the reference's own leaf functions. */
+void ref_build_pyramid(const uint8_t *luma, int32_t src_stride, MeoPyramid *pyr) {
+    MeoPlane *f = &pyr->full, *q = &pyr->quarter, *s = &pyr->sixteenth;
+    for (int y = 0; y < f->height; y++)
+        memcpy(f->buf + (size_t)(f->origin_y + y) * f->stride + f->origin_x, luma + (size_t)y * src_stride, f->width);
+    generate_padding(f->buf, f->stride, f->width, f->height, f->origin_x, f->origin_y);
+    Decimation2D(f->buf + f->origin_x + f->origin_y * f->stride, f->stride, f->width, f->height,
+                 q->buf + q->origin_x + q->origin_x * q->stride, q->stride, 2);
+    generate_padding(q->buf, q->stride, q->width, q->height, q->origin_x, q->origin_y);
+    Decimation2D(f->buf + f->origin_x + f->origin_y * f->stride, f->stride, f->width, f->height,
+                 s->buf + s->origin_x + s->origin_x * s->stride, s->stride, 4);
+    generate_padding(s->buf, s->stride, s->width, s->height, s->origin_x, s->origin_y);
+}
+
+int ref_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
+                                const MeoPyramid *ref0, const MeoPyramid *ref1,
+                                MeoPuResult *results, MeoSbDebug *debug) {
+    ensure_memory_map();
+
+    SequenceControlSet_t *scs = (SequenceControlSet_t *)calloc(1, sizeof(SequenceControlSet_t));
+    EncodeContext_t *enc = (EncodeContext_t *)calloc(1, sizeof(EncodeContext_t));
+    PictureParentControlSet_t *pcs = (PictureParentControlSet_t *)calloc(1, sizeof(PictureParentControlSet_t));
+    EbObjectWrapper_t scs_wrapper; memset(&scs_wrapper, 0, sizeof(scs_wrapper));
+    enc->asm_type = ASM_AVX2;                     /* the only runnable path, EbEncHandle.c:2535-2539 */
+    scs->encode_context_ptr = enc;
+    scs->luma_width = (uint16_t)prm->width; scs->luma_height = (uint16_t)prm->height;
+    scs->sb_sz = 64;
+    scs->static_config.rate_control_mode = 0;
+    scs->static_config.use_default_me_hme = 1;
+    derive_input_resolution(scs, (uint32_t)prm->width * (uint32_t)prm->height);
+    scs_wrapper.objectPtr = scs;
+
+    RefPa pa_cur, pa_ref[2];
+    pa_init(&pa_cur, cur);
+    pa_init(&pa_ref[0], ref0);
+    pa_init(&pa_ref[1], ref1 ? ref1 : ref0);
+
+    const uint32_t w_sb = (prm->width + 63) / 64, h_sb = (prm->height + 63) / 64, n_sb = w_sb * h_sb;
+    pcs->sequence_control_set_wrapper_ptr = &scs_wrapper;
+    pcs->max_number_of_pus_per_sb = (uint8_t)prm->num_pus;
+    pcs->pic_depth_mode = (prm->num_pus == MEO_MAX_PU_COUNT) ? PIC_ALL_DEPTH_MODE : PIC_SQ_DEPTH_MODE;
+    pcs->enable_hme_flag = (EbBool)prm->enable_hme_flag;
+    pcs->enable_hme_level0_flag = (EbBool)prm->enable_hme_level0;
+    pcs->enable_hme_level1_flag = (EbBool)prm->enable_hme_level1;
+    pcs->enable_hme_level2_flag = (EbBool)prm->enable_hme_level2;
+    pcs->slice_type = (prm->num_lists == 1) ? P_SLICE : B_SLICE;
+    pcs->temporal_layer_index = (uint8_t)prm->temporal_layer_index;
+    pcs->hierarchical_levels = (uint8_t)prm->hierarchical_levels;
+    pcs->is_used_as_reference_flag = (EbBool)prm->is_used_as_reference;
+    pcs->use_subpel_flag = (uint8_t)prm->use_subpel;
+    pcs->cu8x8_mode = (uint8_t)prm->cu8x8_mode;
+    pcs->enc_mode = ENC_M3;
+    pcs->ref_pa_pic_ptr_array[0] = &pa_ref[0].wrapper;
+    pcs->ref_pa_pic_ptr_array[1] = &pa_ref[1].wrapper;
+    pcs->ref_pic_poc_array[0] = 100;
+    pcs->ref_pic_poc_array[1] = prm->same_ref_poc ? 100 : 200;
+    pcs->enhanced_picture_ptr = &pa_cur.full;
+    pcs->me_results = (MeCuResults_t **)calloc(n_sb, sizeof(MeCuResults_t *));
+    for (uint32_t i = 0; i < n_sb; i++)
+        pcs->me_results[i] = (MeCuResults_t *)calloc(MEO_MAX_PU_COUNT, sizeof(MeCuResults_t));
+
+    static MeContext_t *ctx = NULL;              /* built once; reference allocations are never freed */
+    if (!ctx && MeContextCtor(&ctx) != EB_ErrorNone) return -1;
+    /* search-area parameters: take them from MeoParams (they default to the same tables) */
+    set_me_hme_params_oq(ctx, pcs, scs, scs->input_resolution);
+    ctx->number_hme_search_region_in_width = (uint16_t)prm->num_hme_regions_w;
+    ctx->number_hme_search_region_in_height = (uint16_t)prm->num_hme_regions_h;
+    ctx->hme_level0_total_search_area_width = (uint16_t)prm->hme_l0_total_w;
+    ctx->hme_level0_total_search_area_height = (uint16_t)prm->hme_l0_total_h;
+    for (int i = 0; i < 2; i++) {
+        ctx->hme_level0_search_area_in_width_array[i] = (uint16_t)prm->hme_l0_w[i];
+        ctx->hme_level0_search_area_in_height_array[i] = (uint16_t)prm->hme_l0_h[i];
+        ctx->hme_level1_search_area_in_width_array[i] = (uint16_t)prm->hme_l1_w[i];
+        ctx->hme_level1_search_area_in_height_array[i] = (uint16_t)prm->hme_l1_h[i];
+        ctx->hme_level2_search_area_in_width_array[i] = (uint16_t)prm->hme_l2_w[i];
+        ctx->hme_level2_search_area_in_height_array[i] = (uint16_t)prm->hme_l2_h[i];
+    }
+    ctx->search_area_width = (uint8_t)prm->search_area_w;
+    ctx->search_area_height = (uint8_t)prm->search_area_h;
+    ctx->lambda = 0;
+
+    EbPictureBufferDesc_t *in = &pa_cur.full, *qd = &pa_cur.quarter, *sd = &pa_cur.sixteenth;
+    for (uint32_t ys = 0; ys < h_sb; ys++) {
+        for (uint32_t xs = 0; xs < w_sb; xs++) {
+            uint32_t sb_index = xs + ys * w_sb, ox = xs * 64, oy = ys * 64;
+            uint32_t sb_w = (prm->width - ox) < 64 ? prm->width - ox : 64;
+            uint32_t sb_h = (prm->height - oy) < 64 ? prm->height - oy : 64;
+            uint32_t bi = (in->origin_y + oy) * in->strideY + in->origin_x + ox, r;
+            ctx->hme_search_type = HME_RECTANGULAR;
+            for (r = 0; r < 64; r++)
+                memcpy(&ctx->sb_buffer[r * 64], &in->bufferY[bi + r * in->strideY], 64);
+            ctx->sb_src_ptr = &in->bufferY[bi];
+            ctx->sb_src_stride = in->strideY;
+            if (pcs->enable_hme_level1_flag) {
+                bi = (qd->origin_y + (oy >> 1)) * qd->strideY + qd->origin_x + (ox >> 1);
+                for (r = 0; r < (sb_h >> 1); r++)
+                    memcpy(&ctx->quarter_sb_buffer[r * ctx->quarter_sb_buffer_stride], &qd->bufferY[bi + r * qd->strideY], sb_w >> 1);
+            }
+            if (pcs->enable_hme_level0_flag) {
+                bi = (sd->origin_y + (oy >> 2)) * sd->strideY + sd->origin_x + (ox >> 2);
+                uint8_t *fp = &sd->bufferY[bi], *lp = ctx->sixteenth_sb_buffer;
+                for (r = 0; r < (sb_h >> 2); r += 2) {
+                    memcpy(lp, fp, sb_w >> 2);
+                    lp += 16; fp += sd->strideY << 1;
+                }
+            }
+            MotionEstimateLcu(pcs, sb_index, ox, oy, ctx, in);
+
+            for (int pu = 0; pu < prm->num_pus; pu++) {
+                const MeCuResults_t *m = &pcs->me_results[sb_index][pu];
+                MeoPuResult *o = &results[(size_t)sb_index * prm->num_pus + pu];
+                memset(o, 0, sizeof(*o));
+                o->xMvL0 = m->xMvL0; o->yMvL0 = m->yMvL0; o->xMvL1 = m->xMvL1; o->yMvL1 = m->yMvL1;
+                o->total_cand = m->totalMeCandidateIndex;
+                for (int c = 0; c < m->totalMeCandidateIndex && c < 3; c++) {
+                    o->cand[c].distortion = m->distortionDirection[c].distortion;
+                    o->cand[c].direction = m->distortionDirection[c].direction;
+                }
+            }
+            if (debug) {
+                MeoSbDebug *d = &debug[sb_index];
+                memset(d, 0, sizeof(*d));
+                for (int l = 0; l < prm->num_lists; l++) {
+                    d->sa_origin_x[l] = ctx->x_search_area_origin[l][0];
+                    d->sa_origin_y[l] = ctx->y_search_area_origin[l][0];
+                    for (int i = 0; i < MEO_SQUARE_PU_COUNT; i++) {
+                        d->best_sad[l][i] = ctx->p_sb_best_sad[l][0][i];
+                        d->best_mv[l][i] = ctx->p_sb_best_mv[l][0][i];
+                    }
+                }
+            }
+        }
+    }
+    for (uint32_t i = 0; i < n_sb; i++) free(pcs->me_results[i]);
+    free(pcs->me_results);
+    /* MeContext buffers are owned by the (leaky by design) EB_MALLOC map of the reference */
+    free(pa_cur.obj); free(pa_ref[0].obj); free(pa_ref[1].obj);
+    free(pcs); free(enc); free(scs);
+    return 0;
+}
+
+/* Reference values of the search-area parameters (set_me_hme_params_oq + the L0 multiplier tables),
+ * used to pin meo_default_params(). */
+void ref_default_params(MeoParams *p, int32_t width, int32_t height, int32_t num_lists,
+                        int32_t temporal_layer_index, int32_t hierarchical_levels, int32_t is_ref) {
+    ensure_memory_map();
+    SequenceControlSet_t *scs = (SequenceControlSet_t *)calloc(1, sizeof(SequenceControlSet_t));
+    PictureParentControlSet_t *pcs = (PictureParentControlSet_t *)calloc(1, sizeof(PictureParentControlSet_t));
+    MeContext_t *ctx = (MeContext_t *)calloc(1, sizeof(MeContext_t));
+    scs->luma_width = (uint16_t)width; scs->luma_height = (uint16_t)height;
+    derive_input_resolution(scs, (uint32_t)width * (uint32_t)height);
+    pcs->enc_mode = ENC_M3;
+    set_me_hme_params_oq(ctx, pcs, scs, scs->input_resolution);
+    memset(p, 0, sizeof(*p));
+    p->width = width; p->height = height; p->num_lists = num_lists;
+    p->temporal_layer_index = temporal_layer_index; p->hierarchical_levels = hierarchical_levels;
+    p->is_used_as_reference = is_ref;
+    p->enable_hme_flag = 1; p->enable_hme_level0 = 1; p->enable_hme_level1 = 1;
+    {   /* signal_derivation_pre_analysis_oq, EbResourceCoordinationProcess.c:366-380 (hme_me_level = enc_mode = 3) */
+        uint32_t ratio = scs->luma_width / scs->luma_height; uint8_t ir = scs->input_resolution;
+        uint8_t ri = ir <= INPUT_SIZE_576p_RANGE_OR_LOWER ? 0 : (ir <= INPUT_SIZE_1080i_RANGE && ratio < 2) ? 1 :
+                     (ir <= INPUT_SIZE_1080i_RANGE && ratio > 3) ? 2 : (ir <= INPUT_SIZE_1080p_RANGE) ? 3 : 4;
+        p->enable_hme_level0 = EnableHmeLevel0Flag[ri][ENC_M3];
+        p->enable_hme_level1 = EnableHmeLevel1Flag[ri][ENC_M3];
+        p->enable_hme_level2 = EnableHmeLevel2Flag[ri][ENC_M3];
+    }
+    p->use_subpel = 1; p->num_pus = MEO_SQUARE_PU_COUNT; p->cu8x8_mode = 0;
+    p->num_hme_regions_w = ctx->number_hme_search_region_in_width;
+    p->num_hme_regions_h = ctx->number_hme_search_region_in_height;
+    p->hme_l0_total_w = ctx->hme_level0_total_search_area_width;
+    p->hme_l0_total_h = ctx->hme_level0_total_search_area_height;
+    for (int i = 0; i < 2; i++) {
+        p->hme_l0_w[i] = ctx->hme_level0_search_area_in_width_array[i];
+        p->hme_l0_h[i] = ctx->hme_level0_search_area_in_height_array[i];
+        p->hme_l1_w[i] = ctx->hme_level1_search_area_in_width_array[i];
+        p->hme_l1_h[i] = ctx->hme_level1_search_area_in_height_array[i];
+        p->hme_l2_w[i] = ctx->hme_level2_search_area_in_width_array[i];
+        p->hme_l2_h[i] = ctx->hme_level2_search_area_in_height_array[i];
+    }
+    p->search_area_w = ctx->search_area_width; p->search_area_h = ctx->search_area_height;
+    p->hme_l0_mult_x = HME_LEVEL_0_SEARCH_AREA_MULTIPLIER_X[hierarchical_levels][temporal_layer_index];
+    p->hme_l0_mult_y = HME_LEVEL_0_SEARCH_AREA_MULTIPLIER_Y[hierarchical_levels][temporal_layer_index];
+    free(ctx); free(pcs); free(scs);
+}
