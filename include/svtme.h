@@ -1,0 +1,127 @@
+/* include/svtme.h -- C-ABI of libsvtme_cuda.so: SVT-AV1 open-loop motion estimation on B200.
+ *
+ * Drop-in boundary. Each entry point replaces a piece of the reference's CPU path; the host
+ * encoder (plain C) keeps its own structures and calls these with plain pointers and sizes:
+ *
+ *   svtme_picture_upload        replaces PadPictureToMultipleOfLcuDimensions + DecimateInputPicture
+ *                               Source/Lib/Codec/EbPictureAnalysisProcess.c:4866-4937 (generate_padding
+ *                               EbMcp.c:173-216, Decimation2D :100-125): the padded full / quarter /
+ *                               sixteenth planes of EbPaReferenceObject_t live in HBM instead of host RAM.
+ *   svtme_motion_estimate       replaces the SB loop of MotionEstimationKernel,
+ *                               Source/Lib/Codec/EbMotionEstimationProcess.c:478-556, i.e. one
+ *                               MotionEstimateLcu (Source/Lib/Codec/EbMotionEstimation.c:6152) per SB,
+ *                               for whole pictures (all ME segments at once) and for a batch of pictures.
+ *   SvtMePuResult               is the byte image of MeCuResults_t
+ *                               (Source/Lib/Codec/EbMotionEstimationLcuResults.h:62-75); the host copies
+ *                               rows straight into PictureParentControlSet_t::me_results[sb][pu].
+ *   SvtMeParams                 carries what MotionEstimateLcu reads from PCS/SCS/MeContext
+ *                               (slice type, temporal layer, HME enables, search-area tables set by
+ *                               set_me_hme_params_oq, EbMotionEstimationProcess.c:94-156).
+ *
+ * Error behaviour mirrors EbErrorType (Source/API/EbErrorCodes.h): 0 = EB_ErrorNone,
+ * SVTME_ERR_INSUFFICIENT_RESOURCES = 0x80001000, SVTME_ERR_BAD_PARAMETER = 0x80001005,
+ * SVTME_ERR_UNDEFINED = 0x80001001 (any CUDA failure). There is no CPU fallback.
+ */
+#ifndef SVTME_H
+#define SVTME_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVTME_OK                          0
+#define SVTME_ERR_INSUFFICIENT_RESOURCES  ((int32_t)0x80001000)
+#define SVTME_ERR_UNDEFINED               ((int32_t)0x80001001)
+#define SVTME_ERR_BAD_PARAMETER           ((int32_t)0x80001005)
+
+#define SVTME_SQUARE_PU_COUNT 85
+#define SVTME_MAX_BATCH       64
+
+typedef struct SvtMeContext SvtMeContext;          /* opaque: one per GPU / encoder instance */
+
+/* == MeoParams of the test oracle; field meaning documented there and in DESIGN.md */
+typedef struct SvtMeParams {
+    int32_t width, height;
+    int32_t num_lists;
+    int32_t temporal_layer_index;
+    int32_t hierarchical_levels;
+    int32_t is_used_as_reference;
+    int32_t same_ref_poc;
+    int32_t enable_hme_flag, enable_hme_level0, enable_hme_level1, enable_hme_level2;
+    int32_t use_subpel;
+    int32_t num_pus;
+    int32_t cu8x8_mode;
+    int32_t num_hme_regions_w, num_hme_regions_h;
+    int32_t hme_l0_total_w, hme_l0_total_h;
+    int32_t hme_l0_w[2], hme_l0_h[2];
+    int32_t hme_l1_w[2], hme_l1_h[2];
+    int32_t hme_l2_w[2], hme_l2_h[2];
+    int32_t search_area_w, search_area_h;
+    int32_t hme_l0_mult_x, hme_l0_mult_y;
+} SvtMeParams;
+
+/* byte image of MeCuResults_t (40 bytes) */
+typedef struct SvtMePuResult {
+    int16_t  xMvL0, yMvL0, xMvL1, yMvL1;
+    struct { uint32_t distortion; uint32_t direction; } cand[3];
+    uint8_t  total_cand;
+    uint8_t  pad[7];
+} SvtMePuResult;
+
+/* per-SB intermediate state (optional output, for stage-level parity tests) */
+typedef struct SvtMeSbDebug {
+    int16_t  search_center_x[2], search_center_y[2];
+    int16_t  sa_origin_x[2], sa_origin_y[2];
+    int16_t  sa_width[2], sa_height[2];
+    uint32_t best_sad[2][SVTME_SQUARE_PU_COUNT];
+    uint32_t best_mv[2][SVTME_SQUARE_PU_COUNT];
+} SvtMeSbDebug;
+
+/* One picture to motion-estimate: slots name pictures previously uploaded into the context. */
+typedef struct SvtMeJob {
+    int32_t        cur_slot, ref0_slot, ref1_slot;   /* ref1_slot ignored when params.num_lists == 1 */
+    SvtMeParams    params;
+    SvtMePuResult *results;                          /* HOST memory, [num_sb][params.num_pus]; may be NULL */
+    SvtMeSbDebug  *debug;                            /* HOST memory, [num_sb]; may be NULL */
+} SvtMeJob;
+
+/* Default search parameters for a resolution: the M0 column every legal preset uses. */
+void    svtme_default_params(SvtMeParams *p, int32_t width, int32_t height, int32_t num_lists,
+                             int32_t temporal_layer_index, int32_t hierarchical_levels,
+                             int32_t is_used_as_reference);
+
+/* Context: owns the stream, the picture slots (pyramids in HBM) and all scratch. */
+int32_t svtme_create(SvtMeContext **ctx, int32_t device, int32_t width, int32_t height, int32_t num_slots);
+void    svtme_destroy(SvtMeContext *ctx);
+const char *svtme_last_error(const SvtMeContext *ctx);
+
+/* Upload one 8-bit luma plane (host memory, 'stride' bytes per row) into a slot and build its padded
+ * full / quarter / sixteenth planes on the device. Asynchronous on the context stream. */
+int32_t svtme_picture_upload(SvtMeContext *ctx, int32_t slot, const uint8_t *luma, int32_t stride);
+/* Same, from a luma plane that already lives in device memory (no H2D copy). */
+int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8_t *d_luma, int32_t stride);
+/* Read one padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) as tightly packed rows of
+ * (width>>level + 2*pad) bytes; *out_stride / *out_rows receive its geometry. Synchronous. */
+int32_t svtme_picture_download(SvtMeContext *ctx, int32_t slot, int32_t level, uint8_t *dst, size_t dst_bytes,
+                               int32_t *out_stride, int32_t *out_rows, int32_t *out_pad);
+
+/* Motion-estimate a batch of pictures (n_jobs <= SVTME_MAX_BATCH). Kernels are enqueued on the
+ * context stream; results/debug are copied to the host buffers of each job and the call returns
+ * when they are there. */
+int32_t svtme_motion_estimate(SvtMeContext *ctx, const SvtMeJob *jobs, int32_t n_jobs);
+/* Enqueue only (results stay in HBM); svtme_fetch_results copies them out later. */
+int32_t svtme_motion_estimate_async(SvtMeContext *ctx, const SvtMeJob *jobs, int32_t n_jobs);
+int32_t svtme_fetch_results(SvtMeContext *ctx, const SvtMeJob *jobs, int32_t n_jobs);
+int32_t svtme_synchronize(SvtMeContext *ctx);
+
+/* Introspection for benchmarks: the CUDA stream (cudaStream_t as void*) and the number of kernel
+ * launches issued so far. */
+void   *svtme_stream(SvtMeContext *ctx);
+int64_t svtme_kernel_launches(const SvtMeContext *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVTME_H */

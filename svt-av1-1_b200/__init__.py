@@ -1,0 +1,9 @@
+"""svt-av1-1_b200 -- B200-native (sm_100a CUDA) open-loop motion estimation of SVT-AV1 behind a C-ABI.
+
+The product is ``libsvtme_cuda.so`` (sources in ``csrc/``, interface in ``include/svtme.h``); this
+package only carries a thin ctypes binding used by the tests and by ``bench.py``. There is no CPU
+fallback: loading fails loudly when the library has not been built, and ``MeContext`` raises when no
+CUDA device is present.
+"""
+from .binding import (MeContext, SvtMeError, SvtMeParams, SvtMeJob, PU_RESULT_DTYPE, SB_DEBUG_DTYPE,  # noqa: F401
+                      default_params, load_library, library_path, EXPORTED_SYMBOLS)

@@ -1,0 +1,186 @@
+"""ctypes binding of include/svtme.h (no torch types, no oracle imports)."""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SQUARE_PU_COUNT = 85
+MAX_BATCH = 64
+
+EXPORTED_SYMBOLS = (
+    "svtme_default_params", "svtme_create", "svtme_destroy", "svtme_last_error", "svtme_picture_upload",
+    "svtme_picture_upload_device", "svtme_picture_download", "svtme_motion_estimate",
+    "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
+    "svtme_kernel_launches",
+)
+
+
+class SvtMeError(RuntimeError):
+    pass
+
+
+class SvtMeParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "width", "height", "num_lists", "temporal_layer_index", "hierarchical_levels", "is_used_as_reference",
+        "same_ref_poc", "enable_hme_flag", "enable_hme_level0", "enable_hme_level1", "enable_hme_level2",
+        "use_subpel", "num_pus", "cu8x8_mode", "num_hme_regions_w", "num_hme_regions_h",
+        "hme_l0_total_w", "hme_l0_total_h")] + [
+        ("hme_l0_w", C.c_int32 * 2), ("hme_l0_h", C.c_int32 * 2), ("hme_l1_w", C.c_int32 * 2),
+        ("hme_l1_h", C.c_int32 * 2), ("hme_l2_w", C.c_int32 * 2), ("hme_l2_h", C.c_int32 * 2),
+        ("search_area_w", C.c_int32), ("search_area_h", C.c_int32),
+        ("hme_l0_mult_x", C.c_int32), ("hme_l0_mult_y", C.c_int32)]
+
+
+class SvtMeJob(C.Structure):
+    _fields_ = [("cur_slot", C.c_int32), ("ref0_slot", C.c_int32), ("ref1_slot", C.c_int32),
+                ("params", SvtMeParams), ("results", C.c_void_p), ("debug", C.c_void_p)]
+
+
+PU_RESULT_DTYPE = np.dtype([("xMvL0", "<i2"), ("yMvL0", "<i2"), ("xMvL1", "<i2"), ("yMvL1", "<i2"),
+                            ("dist0", "<u4"), ("dir0", "<u4"), ("dist1", "<u4"), ("dir1", "<u4"),
+                            ("dist2", "<u4"), ("dir2", "<u4"), ("total", "u1"), ("pad", "u1", (7,))])
+SB_DEBUG_DTYPE = np.dtype([("search_center_x", "<i2", (2,)), ("search_center_y", "<i2", (2,)),
+                           ("sa_origin_x", "<i2", (2,)), ("sa_origin_y", "<i2", (2,)),
+                           ("sa_width", "<i2", (2,)), ("sa_height", "<i2", (2,)),
+                           ("best_sad", "<u4", (2, 85)), ("best_mv", "<u4", (2, 85))])
+
+_lib = None
+
+
+def library_path():
+    return os.path.join(_HERE, "libsvtme_cuda.so")
+
+
+def load_library():
+    """Load libsvtme_cuda.so; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = library_path()
+    if not os.path.exists(path):
+        raise SvtMeError(f"{path} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                         "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    lib.svtme_default_params.restype = None
+    lib.svtme_default_params.argtypes = [C.POINTER(SvtMeParams)] + [C.c_int32] * 6
+    lib.svtme_create.restype = C.c_int32
+    lib.svtme_create.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    lib.svtme_destroy.restype = None
+    lib.svtme_destroy.argtypes = [C.c_void_p]
+    lib.svtme_last_error.restype = C.c_char_p
+    lib.svtme_last_error.argtypes = [C.c_void_p]
+    lib.svtme_picture_upload.restype = C.c_int32
+    lib.svtme_picture_upload.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+    lib.svtme_picture_upload_device.restype = C.c_int32
+    lib.svtme_picture_upload_device.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+    lib.svtme_picture_download.restype = C.c_int32
+    lib.svtme_picture_download.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_size_t,
+                                           C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    for name in ("svtme_motion_estimate", "svtme_motion_estimate_async", "svtme_fetch_results"):
+        f = getattr(lib, name)
+        f.restype = C.c_int32
+        f.argtypes = [C.c_void_p, C.POINTER(SvtMeJob), C.c_int32]
+    lib.svtme_synchronize.restype = C.c_int32
+    lib.svtme_synchronize.argtypes = [C.c_void_p]
+    lib.svtme_stream.restype = C.c_void_p
+    lib.svtme_stream.argtypes = [C.c_void_p]
+    lib.svtme_kernel_launches.restype = C.c_int64
+    lib.svtme_kernel_launches.argtypes = [C.c_void_p]
+    _lib = lib
+    return lib
+
+
+def default_params(width, height, num_lists=2, temporal_layer_index=1, hierarchical_levels=3, is_ref=1):
+    p = SvtMeParams()
+    load_library().svtme_default_params(C.byref(p), width, height, num_lists, temporal_layer_index,
+                                        hierarchical_levels, is_ref)
+    return p
+
+
+class MeContext:
+    """One GPU context: picture slots in HBM + batched motion estimation (mirrors the reference's
+    per-picture ME stage: PA reference pictures in, me_results[sb][pu] out)."""
+
+    def __init__(self, width, height, num_slots, device=0):
+        self.lib = load_library()
+        self.width, self.height, self.num_slots = width, height, num_slots
+        self.n_sb = ((width + 63) // 64) * ((height + 63) // 64)
+        self._h = C.c_void_p()
+        rc = self.lib.svtme_create(C.byref(self._h), device, width, height, num_slots)
+        if rc != 0:
+            msg = self.lib.svtme_last_error(self._h).decode() if self._h else "no CUDA device / bad geometry"
+            if self._h:
+                self.lib.svtme_destroy(self._h)
+                self._h = C.c_void_p()
+            raise SvtMeError(f"svtme_create failed (0x{rc & 0xffffffff:08x}): {msg}")
+
+    def close(self):
+        if self._h:
+            self.lib.svtme_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise SvtMeError(f"{what} failed (0x{rc & 0xffffffff:08x}): {self.lib.svtme_last_error(self._h).decode()}")
+
+    def upload(self, slot, luma):
+        """luma: C-contiguous uint8 numpy array (height, width) in host memory (pinned or pageable)."""
+        assert luma.dtype == np.uint8 and luma.shape == (self.height, self.width)
+        self._check(self.lib.svtme_picture_upload(self._h, slot, luma.ctypes.data, luma.strides[0]), "svtme_picture_upload")
+
+    def upload_ptr(self, slot, host_ptr, stride):
+        self._check(self.lib.svtme_picture_upload(self._h, slot, host_ptr, stride), "svtme_picture_upload")
+
+    def upload_device(self, slot, dev_ptr, stride):
+        self._check(self.lib.svtme_picture_upload_device(self._h, slot, dev_ptr, stride), "svtme_picture_upload_device")
+
+    def download_plane(self, slot, level):
+        pad = (68, 32, 16)[level]
+        w, h = (self.width >> level) + 2 * pad, (self.height >> level) + 2 * pad
+        out = np.empty((h, w), dtype=np.uint8)
+        s, r, p = C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.lib.svtme_picture_download(self._h, slot, level, out.ctypes.data, out.nbytes,
+                                                    C.byref(s), C.byref(r), C.byref(p)), "svtme_picture_download")
+        assert (s.value, r.value, p.value) == (w, h, pad)
+        return out
+
+    def make_jobs(self, specs, want_debug=False, out_ptrs=None):
+        """specs: list of (cur_slot, ref0_slot, ref1_slot, SvtMeParams). Returns (jobs array, results, debug)."""
+        n = len(specs)
+        jobs = (SvtMeJob * n)()
+        results = np.zeros((n, self.n_sb, SQUARE_PU_COUNT), dtype=PU_RESULT_DTYPE) if out_ptrs is None else None
+        debug = np.zeros((n, self.n_sb), dtype=SB_DEBUG_DTYPE) if want_debug else None
+        for i, (cur, r0, r1, prm) in enumerate(specs):
+            jobs[i].cur_slot, jobs[i].ref0_slot, jobs[i].ref1_slot = cur, r0, (r1 if r1 is not None else r0)
+            jobs[i].params = prm
+            jobs[i].results = results[i].ctypes.data if out_ptrs is None else out_ptrs[i]
+            jobs[i].debug = debug[i].ctypes.data if want_debug else None
+        return jobs, results, debug
+
+    def motion_estimate(self, specs, want_debug=False):
+        jobs, results, debug = self.make_jobs(specs, want_debug)
+        self._check(self.lib.svtme_motion_estimate(self._h, jobs, len(specs)), "svtme_motion_estimate")
+        return results, debug
+
+    def motion_estimate_async(self, jobs):
+        self._check(self.lib.svtme_motion_estimate_async(self._h, jobs, len(jobs)), "svtme_motion_estimate_async")
+
+    def fetch(self, jobs):
+        self._check(self.lib.svtme_fetch_results(self._h, jobs, len(jobs)), "svtme_fetch_results")
+
+    def synchronize(self):
+        self._check(self.lib.svtme_synchronize(self._h), "svtme_synchronize")
+
+    @property
+    def stream(self):
+        return self.lib.svtme_stream(self._h)
+
+    @property
+    def kernel_launches(self):
+        return self.lib.svtme_kernel_launches(self._h)

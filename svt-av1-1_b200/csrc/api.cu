@@ -1,0 +1,284 @@
+// api.cu -- the C-ABI of libsvtme_cuda.so (include/svtme.h): context, picture slots, batched ME.
+// Host side only; every kernel lives in its own translation unit and is reached through launch_*().
+#include "me_common.cuh"
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace svtme;
+
+namespace svtme {
+cudaError_t configure_fullpel();
+cudaError_t configure_subpel();
+}
+
+struct Slot {
+    uint8_t* base = nullptr;      // one allocation: luma staging + three padded planes
+    uint8_t* luma = nullptr;      // unpadded luma as uploaded (pitch = width)
+    DPyramid pyr;
+    size_t plane_bytes[3] = { 0, 0, 0 };
+};
+
+struct SvtMeContext {
+    int device = 0, width = 0, height = 0, sb_cols = 0, sb_rows = 0, n_sb = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<Slot> slots;
+    // batch state
+    int batch_cap = 0;
+    SbScratch* d_scratch = nullptr;       // [batch_cap][n_sb]
+    SvtMePuResult* d_results = nullptr;   // [batch_cap][n_sb][85]
+    SvtMeSbDebug* d_debug = nullptr;      // [batch_cap][n_sb]
+    DJob* d_jobs = nullptr;               // [batch_cap]
+    DJob* h_jobs = nullptr;               // pinned
+    int64_t launches = 0;
+    std::string err;
+};
+
+static int32_t fail(SvtMeContext* c, int32_t code, const std::string& msg) {
+    if (c) c->err = msg;
+    return code;
+}
+#define CU(call)                                                                                   \
+    do { cudaError_t e_ = (call);                                                                  \
+         if (e_ != cudaSuccess)                                                                    \
+             return fail(ctx, e_ == cudaErrorMemoryAllocation ? SVTME_ERR_INSUFFICIENT_RESOURCES   \
+                                                                : SVTME_ERR_UNDEFINED,              \
+                         std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static void describe_plane(DPlane& pl, uint8_t* mem, int w, int h, int pad) {
+    pl.buf = mem; pl.stride = (int)align_up((size_t)w + 2 * pad, 64);
+    pl.ox = pad; pl.oy = pad; pl.w = w; pl.h = h;
+}
+static size_t plane_alloc_bytes(int w, int h, int pad) {
+    return align_up(align_up((size_t)w + 2 * pad, 64) * (size_t)(h + 2 * pad) + 256, 256);   // +256: tail slack for word reads
+}
+
+extern "C" {
+
+/* EbDefinitions.h:3320-3469 column M0, EbResourceCoordinationProcess.c:366-380, EbDefinitions.h:2980-2996 */
+void svtme_default_params(SvtMeParams* p, int32_t width, int32_t height, int32_t num_lists,
+                          int32_t temporal_layer_index, int32_t hierarchical_levels, int32_t is_ref) {
+    static const int16_t l0_total_w[5] = { 48, 64, 96, 96, 128 }, l0_w[5] = { 24, 32, 48, 48, 64 };
+    static const int16_t l0_total_h[5] = { 40, 48, 48, 48, 80 }, l0_h[5] = { 20, 24, 24, 24, 40 };
+    static const int8_t en_l2[5] = { 1, 1, 1, 1, 0 };
+    static const int16_t mult[6][6] = { { 100 }, { 100, 100 }, { 100, 100, 100 }, { 200, 140, 100, 70 },
+                                        { 350, 200, 100, 100, 100 }, { 525, 350, 200, 100, 100, 100 } };
+    const uint32_t size = (uint32_t)width * (uint32_t)height;
+    const int ir = size < 0xB71B0 ? 0 : size < 0x1AB3F0 ? 1 : size < 0x29F630 ? 2 : 3;
+    const uint32_t ratio = (uint32_t)width / (uint32_t)height;
+    const int ri = ir <= 0 ? 0 : (ir <= 1 && ratio < 2) ? 1 : (ir <= 1 && ratio > 3) ? 2 : (ir <= 2) ? 3 : 4;
+    memset(p, 0, sizeof(*p));
+    p->width = width; p->height = height; p->num_lists = num_lists;
+    p->temporal_layer_index = temporal_layer_index; p->hierarchical_levels = hierarchical_levels;
+    p->is_used_as_reference = is_ref;
+    p->enable_hme_flag = 1; p->enable_hme_level0 = 1; p->enable_hme_level1 = 1; p->enable_hme_level2 = en_l2[ri];
+    p->use_subpel = 1; p->num_pus = SVTME_SQUARE_PU_COUNT; p->cu8x8_mode = 0;
+    p->num_hme_regions_w = 2; p->num_hme_regions_h = 2;
+    p->hme_l0_total_w = l0_total_w[ri]; p->hme_l0_total_h = l0_total_h[ri];
+    for (int i = 0; i < 2; i++) {
+        p->hme_l0_w[i] = l0_w[ri]; p->hme_l0_h[i] = l0_h[ri];
+        p->hme_l1_w[i] = 16; p->hme_l1_h[i] = 16; p->hme_l2_w[i] = 8; p->hme_l2_h[i] = 8;
+    }
+    p->search_area_w = 64; p->search_area_h = 64;
+    p->hme_l0_mult_x = p->hme_l0_mult_y = mult[hierarchical_levels][temporal_layer_index];
+}
+
+int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t height, int32_t num_slots) {
+    if (!out) return SVTME_ERR_BAD_PARAMETER;
+    *out = nullptr;
+    if (width <= 0 || height <= 0 || (width & 7) || (height & 7) || num_slots <= 0 ||
+        ((width & 63) != 0 && (width & 63) != 32) || width > 8192 || height > 8192)
+        return SVTME_ERR_BAD_PARAMETER;
+    SvtMeContext* ctx = new (std::nothrow) SvtMeContext();
+    if (!ctx) return SVTME_ERR_INSUFFICIENT_RESOURCES;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        delete ctx; return SVTME_ERR_UNDEFINED;             // no GPU: fail loudly, there is no CPU path
+    }
+    ctx->device = device; ctx->width = width; ctx->height = height;
+    ctx->sb_cols = (width + 63) / 64; ctx->sb_rows = (height + 63) / 64; ctx->n_sb = ctx->sb_cols * ctx->sb_rows;
+    *out = ctx;                                              // handed out even on failure so the error text is readable
+    CU(cudaSetDevice(device));
+    CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CU(configure_fullpel());
+    CU(configure_subpel());
+    ctx->slots.resize(num_slots);
+    for (auto& s : ctx->slots) {
+        const size_t luma_bytes = align_up((size_t)width * height, 256);
+        s.plane_bytes[0] = plane_alloc_bytes(width, height, kPadFull);
+        s.plane_bytes[1] = plane_alloc_bytes(width >> 1, height >> 1, kPadQuarter);
+        s.plane_bytes[2] = plane_alloc_bytes(width >> 2, height >> 2, kPadSixteenth);
+        CU(cudaMalloc(&s.base, luma_bytes + s.plane_bytes[0] + s.plane_bytes[1] + s.plane_bytes[2]));
+        s.luma = s.base;
+        uint8_t* m = s.base + luma_bytes;
+        describe_plane(s.pyr.full, m, width, height, kPadFull); m += s.plane_bytes[0];
+        describe_plane(s.pyr.quarter, m, width >> 1, height >> 1, kPadQuarter); m += s.plane_bytes[1];
+        describe_plane(s.pyr.sixteenth, m, width >> 2, height >> 2, kPadSixteenth);
+        CU(cudaMemsetAsync(s.base, 0, luma_bytes + s.plane_bytes[0] + s.plane_bytes[1] + s.plane_bytes[2], ctx->stream));
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SVTME_OK;
+}
+
+void svtme_destroy(SvtMeContext* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (auto& s : ctx->slots) cudaFree(s.base);
+    cudaFree(ctx->d_scratch); cudaFree(ctx->d_results); cudaFree(ctx->d_debug); cudaFree(ctx->d_jobs);
+    if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* svtme_last_error(const SvtMeContext* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+void* svtme_stream(SvtMeContext* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+int64_t svtme_kernel_launches(const SvtMeContext* ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t svtme_picture_upload_device(SvtMeContext* ctx, int32_t slot, const uint8_t* d_luma, int32_t stride) {
+    if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || !d_luma || stride < ctx->width)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_device: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    launch_pyramid(d_luma, stride, ctx->slots[slot].pyr, ctx->stream);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_upload(SvtMeContext* ctx, int32_t slot, const uint8_t* luma, int32_t stride) {
+    if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || !luma || stride < ctx->width)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    Slot& s = ctx->slots[slot];
+    CU(cudaMemcpy2DAsync(s.luma, ctx->width, luma, stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->stream));
+    return svtme_picture_upload_device(ctx, slot, s.luma, ctx->width);
+}
+
+int32_t svtme_picture_download(SvtMeContext* ctx, int32_t slot, int32_t level, uint8_t* dst, size_t dst_bytes,
+                               int32_t* out_stride, int32_t* out_rows, int32_t* out_pad) {
+    if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || level < 0 || level > 2 || !dst)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_download: bad argument");
+    const DPlane& pl = level == 0 ? ctx->slots[slot].pyr.full : level == 1 ? ctx->slots[slot].pyr.quarter : ctx->slots[slot].pyr.sixteenth;
+    const int w = pl.w + 2 * pl.ox, rows = pl.h + 2 * pl.oy;
+    if (dst_bytes < (size_t)w * rows) return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_download: buffer too small");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMemcpy2DAsync(dst, w, pl.buf, pl.stride, w, rows, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (out_stride) *out_stride = w;
+    if (out_rows) *out_rows = rows;
+    if (out_pad) *out_pad = pl.ox;
+    return SVTME_OK;
+}
+
+static int32_t ensure_batch(SvtMeContext* ctx, int n) {
+    if (n <= ctx->batch_cap) return SVTME_OK;
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_scratch); cudaFree(ctx->d_results); cudaFree(ctx->d_debug); cudaFree(ctx->d_jobs);
+    if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
+    ctx->d_scratch = nullptr; ctx->d_results = nullptr; ctx->d_debug = nullptr; ctx->d_jobs = nullptr; ctx->h_jobs = nullptr;
+    ctx->batch_cap = 0;
+    CU(cudaMalloc(&ctx->d_scratch, sizeof(SbScratch) * (size_t)n * ctx->n_sb));
+    CU(cudaMalloc(&ctx->d_results, sizeof(SvtMePuResult) * (size_t)n * ctx->n_sb * kNumPu));
+    CU(cudaMalloc(&ctx->d_debug, sizeof(SvtMeSbDebug) * (size_t)n * ctx->n_sb));
+    CU(cudaMalloc(&ctx->d_jobs, sizeof(DJob) * (size_t)n));
+    CU(cudaMallocHost(&ctx->h_jobs, sizeof(DJob) * (size_t)n));
+    ctx->batch_cap = n;
+    return SVTME_OK;
+}
+
+static bool params_ok(const SvtMeContext* ctx, const SvtMeParams& p, std::string& why) {
+#define REQ(c) if (!(c)) { why = "unsupported SvtMeParams: " #c; return false; }
+    REQ(p.width == ctx->width && p.height == ctx->height);
+    REQ(p.num_lists == 1 || p.num_lists == 2);
+    REQ(p.num_pus == SVTME_SQUARE_PU_COUNT);
+    REQ(p.hierarchical_levels >= 0 && p.hierarchical_levels <= 5);
+    REQ(p.temporal_layer_index >= 0 && p.temporal_layer_index <= p.hierarchical_levels);
+    REQ(p.num_hme_regions_w >= 1 && p.num_hme_regions_w <= 2 && p.num_hme_regions_h >= 1 && p.num_hme_regions_h <= 2);
+    REQ(p.search_area_w >= 1 && p.search_area_w <= 64 && p.search_area_h >= 1 && p.search_area_h <= 64);
+    REQ(p.hme_l0_mult_x > 0 && p.hme_l0_mult_y > 0);
+    for (int i = 0; i < 2; i++) {
+        REQ(p.hme_l0_w[i] >= 1 && p.hme_l0_h[i] >= 1 && p.hme_l1_w[i] >= 1 && p.hme_l1_h[i] >= 1 && p.hme_l2_w[i] >= 0 && p.hme_l2_h[i] >= 0);
+        REQ(p.hme_l1_w[i] <= 64 && p.hme_l1_h[i] <= 64 && p.hme_l2_w[i] <= 64 && p.hme_l2_h[i] <= 64);
+        REQ(p.hme_l0_w[i] * p.hme_l0_mult_x / 100 <= 1024 && p.hme_l0_h[i] * p.hme_l0_mult_y / 100 <= 1024);
+    }
+    REQ(p.use_subpel == 0 || p.use_subpel == 1);
+#undef REQ
+    return true;
+}
+
+int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int32_t n_jobs) {
+    if (!ctx || !jobs || n_jobs <= 0 || n_jobs > SVTME_MAX_BATCH)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: bad batch");
+    CU(cudaSetDevice(ctx->device));
+    const int nslots = (int)ctx->slots.size();
+    int max_lists = 1;
+    for (int i = 0; i < n_jobs; i++) {
+        const SvtMeJob& j = jobs[i];
+        std::string why;
+        if (!params_ok(ctx, j.params, why)) return fail(ctx, SVTME_ERR_BAD_PARAMETER, why);
+        if (j.cur_slot < 0 || j.cur_slot >= nslots || j.ref0_slot < 0 || j.ref0_slot >= nslots ||
+            (j.params.num_lists == 2 && (j.ref1_slot < 0 || j.ref1_slot >= nslots)))
+            return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: slot out of range");
+        max_lists = j.params.num_lists > max_lists ? j.params.num_lists : max_lists;
+    }
+    int32_t rc = ensure_batch(ctx, n_jobs);
+    if (rc != SVTME_OK) return rc;
+    CU(cudaStreamSynchronize(ctx->stream));        // h_jobs is reused: the previous batch must have consumed it
+    for (int i = 0; i < n_jobs; i++) {
+        const SvtMeJob& j = jobs[i];
+        DJob& d = ctx->h_jobs[i];
+        d.cur = ctx->slots[j.cur_slot].pyr;
+        d.ref[0] = ctx->slots[j.ref0_slot].pyr;
+        d.ref[1] = ctx->slots[j.params.num_lists == 2 ? j.ref1_slot : j.ref0_slot].pyr;
+        d.prm = j.params;
+        d.scratch = ctx->d_scratch + (size_t)i * ctx->n_sb;
+        d.results = ctx->d_results + (size_t)i * ctx->n_sb * kNumPu;
+        d.debug = j.debug ? ctx->d_debug + (size_t)i * ctx->n_sb : nullptr;
+        d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
+    }
+    CU(cudaMemcpyAsync(ctx->d_jobs, ctx->h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
+    for (int list = 0; list < max_lists; list++) {
+        launch_hme(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream);
+        launch_fullpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream);
+        launch_subpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream);
+        ctx->launches += 3;
+    }
+    launch_bipred_pack(ctx->d_jobs, n_jobs, ctx->n_sb, ctx->stream);
+    ctx->launches += 1;
+    CU(cudaGetLastError());
+    return SVTME_OK;
+}
+
+int32_t svtme_fetch_results(SvtMeContext* ctx, const SvtMeJob* jobs, int32_t n_jobs) {
+    if (!ctx || !jobs || n_jobs <= 0 || n_jobs > ctx->batch_cap)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_fetch_results: bad batch");
+    CU(cudaSetDevice(ctx->device));
+    for (int i = 0; i < n_jobs; i++) {
+        if (jobs[i].results)
+            CU(cudaMemcpyAsync(jobs[i].results, ctx->d_results + (size_t)i * ctx->n_sb * kNumPu,
+                               sizeof(SvtMePuResult) * (size_t)ctx->n_sb * kNumPu, cudaMemcpyDeviceToHost, ctx->stream));
+        if (jobs[i].debug)
+            CU(cudaMemcpyAsync(jobs[i].debug, ctx->d_debug + (size_t)i * ctx->n_sb,
+                               sizeof(SvtMeSbDebug) * (size_t)ctx->n_sb, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SVTME_OK;
+}
+
+int32_t svtme_motion_estimate(SvtMeContext* ctx, const SvtMeJob* jobs, int32_t n_jobs) {
+    const int32_t rc = svtme_motion_estimate_async(ctx, jobs, n_jobs);
+    if (rc != SVTME_OK) return rc;
+    return svtme_fetch_results(ctx, jobs, n_jobs);
+}
+
+int32_t svtme_synchronize(SvtMeContext* ctx) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return SVTME_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,223 @@
+// fullpel.cu -- integer full-pel search of one 64x64 SB against one reference list: SADs of all 85
+// square PUs (64x64, 4x 32x32, 16x 16x16, 64x 8x8) at every position of the (<= 64x64) search area and
+// the per-PU argmin, bit-exact with FullPelSearch_LCU and its AVX2/SSE2 leaves
+// (reference Source/Lib/Codec/EbMotionEstimation.c:1237-1551,
+//  Source/Lib/ASM_AVX2/EbComputeSAD_Intrinsic_AVX2.c:3414-3932,
+//  Source/Lib/ASM_SSE2/EbMeSadCalculation_Intrinsic_SSE2.c:10-127).
+//
+// B200 mapping (INT-pipe bound: VABSDIFF4.U8.ACC issues at 64 lanes/clk/SM on the ALU pipe, shared
+// with SHF/LOP3/VIMNMX, so the hot loop must contain nothing but SADs):
+//   * the reference window (<= 126 rows x 128 bytes) is staged once into shared memory as FOUR copies,
+//     copy s shifted left by s bytes, so that every search position reads word-aligned data and the
+//     inner loop needs no funnel shifts;
+//   * one thread = one "tile" of 4 positions x, x+4, x+8, x+12 on one row: they share the same copy,
+//     19 reference words feed 64 SADs per source row, source words are broadcast LDS.128;
+//   * the reference kernels look at 8 rows of every 8x8 block sub-sampled by two (rows 0,2,4,6) and
+//     double the sum; per band of four such rows a tile owns 8 column blocks x 4 positions = 32
+//     accumulators; 16x16 / 32x32 / 64x64 SADs are sums of those;
+//   * argmin: 32-bit key = (sad << 12) | (row << 6) | col, reduced with one CREDUX.MIN per warp and one
+//     shared-memory atomicMin, which is exactly "smallest SAD, first in raster order"; the 32x32 PUs
+//     use (sad << 13) | (row << 7) | (group << 3) | idx to carry the reference's gcc-only MV quirk (Q4).
+#include "me_common.cuh"
+
+namespace svtme {
+
+constexpr int kFpThreads = 256;
+constexpr int kWinRows = 126;          // 64 search rows + 62
+constexpr int kWinPitch = 36;          // words; = 4 (mod 32) keeps the 8 row-distinct LDS.128 of a warp conflict-free
+constexpr int kFpSmemBytes = (4 * kWinRows * kWinPitch + 32 * 16 + 96) * 4;
+
+__device__ __forceinline__ void key_min(uint32_t* slot, uint32_t key) {
+    const uint32_t m = __reduce_min_sync(0xffffffffu, key);
+    if ((threadIdx.x & 31) == 0 && m != 0xFFFFFFFFu) atomicMin(slot, m);
+}
+
+__global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __restrict__ jobs, int list) {
+    extern __shared__ __align__(16) uint32_t smem[];
+    uint32_t* win = smem;
+    uint32_t* src = smem + 4 * kWinRows * kWinPitch;
+    uint32_t* keys = src + 32 * 16;
+    const DJob& job = jobs[blockIdx.y];
+    const int sb = blockIdx.x;
+    if (sb >= job.sb_cols * job.sb_rows) return;
+    const SvtMeParams& p = job.prm;
+    if (list >= p.num_lists) return;
+    const int tid = threadIdx.x;
+    const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
+    SbScratch& scr = job.scratch[sb];
+    const DPlane& rp = job.ref[list].full;
+    const int sax = scr.sa_x[list], say = scr.sa_y[list], saw = scr.sa_w[list], sah = scr.sa_h[list];
+
+    // ---- stage source (even rows) and the four byte-shifted window copies
+    for (int t = tid; t < 32 * 16; t += kFpThreads)
+        src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
+    if (tid < 96) keys[tid] = 0xFFFFFFFFu;
+    {
+        const int wrows = sah + 62;
+        const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
+        const int per_copy = wrows * nfill;
+        for (int t = tid; t < 4 * per_copy; t += kFpThreads) {
+            const int s = t / per_copy, q = t - s * per_copy;
+            const int r = q / nfill, c = q - r * nfill;
+            win[(s * kWinRows + r) * kWinPitch + c] = ldg_u32_unaligned(rp.at(ox + sax + s + 4 * c, oy + say + r));
+        }
+    }
+    __syncthreads();
+
+    const int ngroups = saw >> 3, mult8 = ngroups << 3, leftover = saw - mult8;
+    const int ngpairs = (ngroups + 1) >> 1;
+    const int tiles_g = sah * ngpairs * 4;                         // 8-position-group tiles
+    const int tiles_s = leftover ? sah * 4 : 0;                    // single-position tiles (width & 7 leftovers)
+    const int total = tiles_g + tiles_s;
+    const int s = tid & 3;
+
+    for (int u0 = 0; u0 < total; u0 += kFpThreads) {
+        const int u = u0 + tid;
+        const bool live = u < total;
+        const bool single = live && u >= tiles_g;
+        int y = 0, x0 = 0, G = 0;
+        bool val[4] = { false, false, false, false };
+        if (live) {
+            if (!single) {
+                const int q = u >> 2;
+                G = q % ngpairs; y = q / ngpairs; x0 = 16 * G + s;
+                val[0] = val[1] = (2 * G < ngroups); val[2] = val[3] = (2 * G + 1 < ngroups);
+            } else {
+                // keep the tile 16-byte aligned: with an odd number of groups the leftovers are positions 2,3
+                y = (u - tiles_g) >> 2; x0 = ((ngroups & 1) ? mult8 - 8 : mult8) + s;
+#pragma unroll
+                for (int k = 0; k < 4; k++) val[k] = (x0 + 4 * k >= mult8) && (x0 + 4 * k < saw);
+            }
+        }
+        uint32_t h16[4][4], s32[4][2], s64[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { s64[k] = 0; s32[k][0] = s32[k][1] = 0; }
+#pragma unroll 1
+        for (int b = 0; b < 8; b++) {
+            uint32_t acc[4][8];
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) acc[k][j] = 0;
+            if (live) {
+#pragma unroll
+                for (int rr = 0; rr < 4; rr++) {
+                    const int r = 4 * b + rr;
+                    const uint4* wp = reinterpret_cast<const uint4*>(win + (s * kWinRows + y + 2 * r) * kWinPitch + (x0 >> 2));
+                    uint32_t ref[20];
+#pragma unroll
+                    for (int i = 0; i < 5; i++) {
+                        const uint4 v = wp[i];
+                        ref[4 * i] = v.x; ref[4 * i + 1] = v.y; ref[4 * i + 2] = v.z; ref[4 * i + 3] = v.w;
+                    }
+                    const uint4* sp = reinterpret_cast<const uint4*>(src + r * 16);
+#pragma unroll
+                    for (int cc = 0; cc < 4; cc++) {
+                        const uint4 sv = sp[cc];
+                        const uint32_t sw[4] = { sv.x, sv.y, sv.z, sv.w };
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const int c = 4 * cc + j;
+#pragma unroll
+                            for (int k = 0; k < 4; k++) acc[k][c >> 1] = sad4(sw[j], ref[c + k], acc[k][c >> 1]);
+                        }
+                    }
+                }
+            }
+            const uint32_t pos = (uint32_t)(y << 6);
+            // ---- 8x8 PUs of block-row b
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                uint32_t key = 0xFFFFFFFFu;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (val[k]) key = min(key, (acc[k][j] << 12) | pos | (uint32_t)(x0 + 4 * k));
+                key_min(&keys[21 + kTab8[b * 8 + j]], key);
+            }
+            // ---- 16x16: sum of two block-rows
+            if ((b & 1) == 0) {
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+#pragma unroll
+                    for (int q = 0; q < 4; q++) h16[k][q] = acc[k][2 * q] + acc[k][2 * q + 1];
+                continue;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    h16[k][q] += acc[k][2 * q] + acc[k][2 * q + 1];
+                    s32[k][q >> 1] += h16[k][q];
+                }
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                uint32_t key = 0xFFFFFFFFu;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (val[k]) key = min(key, (h16[k][q] << 12) | pos | (uint32_t)(x0 + 4 * k));
+                key_min(&keys[5 + kTab16[(b >> 1) * 4 + q]], key);
+            }
+            if ((b & 3) != 3) continue;
+            // ---- 32x32: two PUs of this half of the SB
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+                uint32_t key = 0xFFFFFFFFu;
+                // quirk Q4: per 8-position group, first-min of positions 0..3 ("lo") and of 4..7 ("hi");
+                // lo wins only if strictly smaller and is then reported 4 to the right, hi 4 to the left.
+                // (shuffles are executed by every lane; single-position tiles ignore the outcome)
+#pragma unroll
+                for (int g2 = 0; g2 < 2; g2++) {
+                    uint32_t lo = (s32[2 * g2][q] << 2) | (uint32_t)s, hi = (s32[2 * g2 + 1][q] << 2) | (uint32_t)s;
+                    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 1)); lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 2));
+                    hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 1)); hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 2));
+                    const uint32_t lv = lo >> 2, hv = hi >> 2;
+                    const uint32_t v = (hv > lv) ? lv : hv;
+                    const uint32_t idx = (hv > lv) ? (lo & 3u) + 4u : (hi & 3u);
+                    if (!single && val[2 * g2]) key = min(key, (v << 13) | ((uint32_t)y << 7) | ((uint32_t)(2 * G + g2) << 3) | idx);
+                }
+                if (single) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        if (val[k]) key = min(key, (s32[k][q] << 13) | ((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3));
+                }
+                key_min(&keys[1 + (b >> 2) * 2 + q], key);
+#pragma unroll
+                for (int k = 0; k < 4; k++) { s64[k] += s32[k][q]; s32[k][q] = 0; }
+            }
+            if (b != 7) continue;
+            {
+                uint32_t key = 0xFFFFFFFFu;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (val[k]) key = min(key, (s64[k] << 12) | pos | (uint32_t)(x0 + 4 * k));
+                key_min(&keys[0], key);
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- decode the winning keys into p_sb_best_sad / p_sb_best_mv form
+    if (tid < kNumPu) {
+        const uint32_t key = keys[tid];
+        uint32_t v; int x, y;
+        if (tid >= 1 && tid <= 4) {
+            v = key >> 13; y = (key >> 7) & 63;
+            const int slot = (key >> 3) & 15, idx = key & 7;
+            x = slot < 8 ? slot * 8 + idx : mult8 + slot - 8;
+        } else {
+            v = key >> 12; y = (key >> 6) & 63; x = key & 63;
+        }
+        scr.best_sad[list][tid] = v << 1;
+        scr.best_mv[list][tid] = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
+    }
+}
+
+cudaError_t configure_fullpel() {
+    return cudaFuncSetAttribute(fullpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpSmemBytes);
+}
+
+void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
+    fullpel_kernel<<<dim3(max_sb, n_jobs), kFpThreads, kFpSmemBytes, st>>>(d_jobs, list);
+}
+
+}  // namespace svtme
