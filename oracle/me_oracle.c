@@ -15,6 +15,9 @@
  *   Q5  half-pel candidates are ranked with an 8-bit *wrapping* "SSD"
  *                                                     ASM_SSE4_1/EbPictureOperators_Intrinsic_SSE4_1.c:534-630
  *   Q6  64x64 quarter-pel refinement looks at the top-left 32x32 only        ME.c:3395-3409
+ *   Q7  the per-region HME centre arrays are initialised for list 0 only (the region counters are
+ *       not reset before the initialisation loop of list 1), so a disabled HME level hands list 1
+ *       the list-0 values                                                    ME.c:6323-6345
  * PARITY PIN: checked bit-exactly against oracle/_ref/libsvtref.so (the reference's own objects)
  * by tests/test_oracle_vs_ref.py and against tests/golden/ vectors generated from it.
  *
@@ -193,6 +196,8 @@ typedef struct SbCtx {
     uint32_t best_ssd[2][MEO_SQUARE_PU_COUNT];
     uint8_t  sub_dir[MEO_SQUARE_PU_COUNT];  /* psub_pel_direction*, shared by both lists like the reference */
     uint32_t bipred_sad[MEO_SQUARE_PU_COUNT];
+    int      hx[3][2][2], hy[3][2][2];      /* per-region HME centres of level 0/1/2 (live across lists: Q7) */
+    uint64_t hs[3][2][2];
 } SbCtx;
 
 static inline int16_t mvx(uint32_t mv) { return (int16_t)(mv & 0xFFFF); }
@@ -294,12 +299,13 @@ static void find_search_center(SbCtx *c, int list, int *xsc, int *ysc) {
     if (!(p->enable_hme_flag && c->sb_h == 64)) return;
 
     const int nw = p->num_hme_regions_w, nh = p->num_hme_regions_h;
-    int x0[2][2], y0[2][2], x1[2][2], y1[2][2], x2[2][2], y2[2][2];
-    uint64_t s0[2][2], s1[2][2], s2[2][2];
-    for (int h = 0; h < nh; h++) for (int w = 0; w < nw; w++) {
-        x0[w][h] = x1[w][h] = x2[w][h] = *xsc; y0[w][h] = y1[w][h] = y2[w][h] = *ysc;
-        s0[w][h] = s1[w][h] = s2[w][h] = 0;
-    }
+    int (*x0)[2] = c->hx[0], (*y0)[2] = c->hy[0], (*x1)[2] = c->hx[1], (*y1)[2] = c->hy[1], (*x2)[2] = c->hx[2], (*y2)[2] = c->hy[2];
+    uint64_t (*s0)[2] = c->hs[0], (*s1)[2] = c->hs[1], (*s2)[2] = c->hs[2];
+    if (list == 0)                                                  /* Q7 */
+        for (int h = 0; h < nh; h++) for (int w = 0; w < nw; w++) {
+            x0[w][h] = x1[w][h] = x2[w][h] = *xsc; y0[w][h] = y1[w][h] = y2[w][h] = *ysc;
+            s0[w][h] = s1[w][h] = s2[w][h] = 0;
+        }
     if (p->enable_hme_level0)
         for (int h = 0; h < nh; h++) for (int w = 0; w < nw; w++)
             hme_level0(c, list, w, h, (int16_t)*xsc >> 2, (int16_t)*ysc >> 2, &s0[w][h], &x0[w][h], &y0[w][h]);

@@ -167,9 +167,13 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
         // ---- HME, ME.c:6323-6637
         if (p.enable_hme_flag && sb_h == 64) {
             const int nw = p.num_hme_regions_w, nh = p.num_hme_regions_h;
+            // quirk Q7 (ME.c:6323-6345): the reference initialises the per-region centres for list 0 only;
+            // list 1 inherits whatever list 0 left there (visible when an HME level is disabled).
             if (tid < 12) {
                 const int l = tid >> 2, w = (tid >> 1) & 1, h = tid & 1;
-                s_x[l][w][h] = xsc; s_y[l][w][h] = ysc; s_sad[l][w][h] = 0;
+                s_x[l][w][h] = list == 0 ? xsc : scr.hme_x[l][w][h];
+                s_y[l][w][h] = list == 0 ? ysc : scr.hme_y[l][w][h];
+                s_sad[l][w][h] = 0;
             }
             __syncthreads();
             if (p.enable_hme_level0) {
@@ -228,6 +232,10 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
                     }
                     __syncthreads();
                 }
+            }
+            if (list == 0 && p.num_lists == 2 && tid < 12) {
+                const int l = tid >> 2, w = (tid >> 1) & 1, h = tid & 1;
+                scr.hme_x[l][w][h] = s_x[l][w][h]; scr.hme_y[l][w][h] = s_y[l][w][h];
             }
             if (tid == 0) {
                 int xh = 0, yh = 0;

@@ -32,6 +32,7 @@ struct DPyramid { DPlane full, quarter, sixteenth; };
 struct SbScratch {
     int32_t  sa_x[2], sa_y[2], sa_w[2], sa_h[2];     // clipped search area per list
     int32_t  center_x[2], center_y[2];
+    int32_t  hme_x[3][2][2], hme_y[3][2][2];         // per-region HME centres of list 0, inherited by list 1 (quirk Q7)
     uint32_t best_sad[2][kNumPu];                    // internal (z-order) PU index, like p_sb_best_sad
     uint32_t best_mv[2][kNumPu];
     uint8_t  pred[2][4][64 * 64];                    // final uni-pred blocks per list and PU size level

@@ -1,0 +1,213 @@
+"""Parity tests proper: the CUDA path, called through the C-ABI (include/svtme.h), against the oracle
+and the committed golden vectors, bit-exact (all of this is integer work). Needs a B200."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import me_common as M
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def meo():
+    M.build_oracle(ref=False)
+    return M.load_oracle()
+
+
+def _set(p, over):
+    for k, v in (over or {}).items():
+        if isinstance(v, tuple):
+            for i, x in enumerate(v):
+                getattr(p, k)[i] = x
+        else:
+            setattr(p, k, v)
+
+
+def _check_against_oracle(pkg, meo, frames, prm_list, triples):
+    """frames: list of luma arrays; prm_list[i] / triples[i] = SvtMeParams and (cur, ref0, ref1) per job."""
+    h, w = frames[0].shape
+    ctx = pkg.MeContext(w, h, len(frames))
+    try:
+        for i, f in enumerate(frames):
+            ctx.upload(i, f)
+        res, dbg = ctx.motion_estimate([(c, r0, r1, p) for (c, r0, r1), p in zip(triples, prm_list)], want_debug=True)
+    finally:
+        ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in frames]
+    for j, ((c, r0, r1), p) in enumerate(zip(triples, prm_list)):
+        want, wdbg = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p), pyr[c], pyr[r0],
+                                       pyr[r1] if p.num_lists == 2 else None)
+        nl = p.num_lists
+        for f in ("sa_origin_x", "sa_origin_y", "sa_width", "sa_height", "search_center_x", "search_center_y"):
+            assert np.array_equal(dbg[j][f][:, :nl], wdbg[f][:, :nl]), (j, f)
+        assert np.array_equal(dbg[j]["best_mv"][:, :nl], wdbg["best_mv"][:, :nl]), j
+        assert np.array_equal(dbg[j]["best_sad"][:, :nl], wdbg["best_sad"][:, :nl]), j
+        assert M.results_diff(res[j], want, nl) == [], j
+        if nl == 1:
+            assert not res[j]["xMvL1"].any() and not res[j]["yMvL1"].any()
+
+
+@pytest.mark.parametrize("w,h", [(416, 240), (64, 64), (160, 72), (1280, 720)])
+def test_pyramid_parity(pkg, meo, w, h):
+    f = M.synth_video(w, h, 1, seed=w)[0]
+    ctx = pkg.MeContext(w, h, 1)
+    ctx.upload(0, f)
+    got = [ctx.download_plane(0, l) for l in range(3)]
+    ctx.close()
+    want = M.build_pyramid(meo, "meo", f)
+    for g, x in zip(got, want.planes):
+        assert np.array_equal(g, x)
+
+
+def test_pyramid_strided_and_device_upload(pkg, meo):
+    import torch
+    w, h = 320, 136
+    f = M.synth_video(w, h, 1, seed=9)[0]
+    wide = np.zeros((h, w + 40), dtype=np.uint8)
+    wide[:, :w] = f
+    ctx = pkg.MeContext(w, h, 2)
+    ctx.upload_ptr(0, wide.ctypes.data, wide.strides[0])
+    d = torch.from_numpy(wide).cuda()
+    torch.cuda.synchronize()
+    ctx.upload_device(1, d.data_ptr(), d.stride(0))
+    a = [ctx.download_plane(0, l) for l in range(3)]
+    b = [ctx.download_plane(1, l) for l in range(3)]
+    ctx.close()
+    want = M.build_pyramid(meo, "meo", f)
+    for x, y, z in zip(a, b, want.planes):
+        assert np.array_equal(x, z) and np.array_equal(y, z)
+
+
+@pytest.mark.parametrize("name", M.golden_cases())
+def test_cuda_matches_reference_golden(pkg, name):
+    """CUDA path against vectors produced by the unmodified reference objects."""
+    g = M.load_golden(name)
+    prm = M.params_from_list(pkg.SvtMeParams, g["params"])
+    frames = g["frames"]
+    ctx = pkg.MeContext(prm.width, prm.height, 3)
+    for i in range(3):
+        ctx.upload(i, np.ascontiguousarray(frames[i]))
+        assert [M.plane_crc(ctx.download_plane(i, l)) for l in range(3)] == [int(v) for v in g["pyr_crc"][i]]
+    res, dbg = ctx.motion_estimate([(1, 0, 2, prm)], want_debug=True)
+    ctx.close()
+    nl = prm.num_lists
+    assert np.array_equal(dbg[0]["best_sad"][:, :nl], g["best_sad"][:, :nl])
+    assert np.array_equal(dbg[0]["best_mv"][:, :nl], g["best_mv"][:, :nl])
+    assert M.results_diff(res[0], g["results"], nl) == []
+
+
+@pytest.mark.parametrize("w,h", [(416, 240), (256, 192), (64, 64), (160, 72), (320, 136)])
+@pytest.mark.parametrize("nl,tl", [(2, 1), (1, 0), (2, 3), (2, 0)])
+def test_sizes_and_layers(pkg, meo, w, h, nl, tl):
+    fr = M.synth_video(w, h, 3, seed=w + h + nl + tl)
+    _check_against_oracle(pkg, meo, fr, [pkg.default_params(w, h, nl, tl, 3, 1)], [(1, 0, 2)])
+
+
+SWEEP = [
+    {"search_area_w": 24, "search_area_h": 17}, {"search_area_w": 7, "search_area_h": 5},
+    {"search_area_w": 43, "search_area_h": 64}, {"search_area_w": 1, "search_area_h": 1},
+    {"search_area_w": 9, "search_area_h": 3}, {"search_area_w": 16, "search_area_h": 16},
+    {"enable_hme_flag": 0}, {"enable_hme_level2": 0}, {"enable_hme_level1": 0, "enable_hme_level2": 0},
+    {"enable_hme_level0": 0}, {"enable_hme_level1": 0}, {"num_hme_regions_w": 1, "num_hme_regions_h": 1},
+    {"num_hme_regions_w": 2, "num_hme_regions_h": 1}, {"same_ref_poc": 1}, {"use_subpel": 0},
+    {"cu8x8_mode": 1}, {"hme_l1_w": (12, 20), "hme_l1_h": (9, 16)}, {"hme_l2_w": (5, 11), "hme_l2_h": (3, 8)},
+    {"is_used_as_reference": 0},
+]
+
+
+@pytest.mark.parametrize("over", SWEEP)
+def test_parameter_sweep(pkg, meo, over):
+    w, h = 320, 192
+    fr = M.synth_video(w, h, 3, seed=len(str(over)), max_shift=40)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    _set(p, over)
+    _check_against_oracle(pkg, meo, fr, [p], [(1, 0, 2)])
+
+
+@pytest.mark.parametrize("hl,tl", [(3, 0), (4, 0), (4, 1), (5, 0), (5, 1), (0, 0), (2, 2)])
+def test_hme_level0_multipliers(pkg, meo, hl, tl):
+    w, h = 448, 256
+    fr = M.synth_video(w, h, 3, seed=hl * 7 + tl, max_shift=70)
+    _check_against_oracle(pkg, meo, fr, [pkg.default_params(w, h, 2, tl, hl, 1)], [(1, 0, 2)])
+
+
+@pytest.mark.parametrize("synth", [
+    dict(noise=0.0, contrast=0.0), dict(noise=0.0, contrast=0.05, max_shift=4),
+    dict(noise=12.0, contrast=4.0, max_shift=60), dict(noise=1.0, contrast=1.0, max_shift=90),
+])
+def test_content_extremes(pkg, meo, synth):
+    w, h = 256, 192
+    fr = M.synth_video(w, h, 3, seed=7, **synth)
+    _check_against_oracle(pkg, meo, fr, [pkg.default_params(w, h, 2, 1, 3, 1), pkg.default_params(w, h, 2, 2, 3, 0)],
+                          [(1, 0, 2), (1, 2, 0)])
+
+
+def test_black_white_checker(pkg, meo):
+    w, h = 256, 128
+    yy, xx = np.mgrid[0:h, 0:w]
+    a = (((xx // 3 + yy // 5) & 1) * 255).astype(np.uint8)
+    b = (((xx // 3 + yy // 5 + 1) & 1) * 255).astype(np.uint8)
+    c = np.roll(a, (3, 5), (0, 1))
+    _check_against_oracle(pkg, meo, [b, a, c], [pkg.default_params(w, h, 2, 1, 3, 1)], [(1, 0, 2)])
+
+
+def test_mixed_batch(pkg, meo):
+    """One call, several pictures with different slice types / layers / references (a mini-GOP)."""
+    w, h = 320, 192
+    fr = M.synth_video(w, h, 9, seed=21, max_shift=16)
+    jobs, prms = [], []
+    # hierarchical mini-GOP 8: (poc, temporal layer, ref0, ref1), EbPredictionStructure.c:183-240
+    for poc, tl, r0, r1 in [(8, 0, 0, 0), (4, 1, 0, 8), (2, 2, 0, 4), (6, 2, 4, 8), (1, 3, 0, 2), (3, 3, 2, 4), (5, 3, 4, 6), (7, 3, 6, 8)]:
+        p = pkg.default_params(w, h, 2, tl, 3, 1 if tl < 3 else 0)
+        p.same_ref_poc = 1 if r0 == r1 else 0
+        jobs.append((poc, r0, r1)); prms.append(p)
+    p = pkg.default_params(w, h, 1, 0, 3, 1)
+    jobs.append((8, 0, 0)); prms.append(p)
+    _check_against_oracle(pkg, meo, fr, prms, jobs)
+
+
+def test_1080p_full_size_parity(pkg, meo):
+    """BASELINE config 2 geometry (1920x1080: 30x17 SBs, last SB row 56 high -> no HME there)."""
+    w, h = 1920, 1080
+    fr = M.synth_video(w, h, 3, seed=1080, max_shift=40)
+    _check_against_oracle(pkg, meo, fr, [pkg.default_params(w, h, 2, 1, 3, 1)], [(1, 0, 2)])
+
+
+def test_1080p_properties(pkg):
+    """Size-independent properties at full size: (1) a picture predicted from itself has zero SAD and zero
+    MVs for every PU; (2) a pure translation inside the search range is recovered by every interior SB's
+    64x64 PU with zero distortion; (3) results do not depend on batch position (idempotence)."""
+    w, h = 1920, 1080
+    rng = np.random.default_rng(4)
+    big = rng.integers(0, 256, size=(h + 64, w + 64), dtype=np.uint8)
+    cur = np.ascontiguousarray(big[32:32 + h, 32:32 + w])
+    dx, dy = 12, -8            # multiples of 4: the point-sampled HME levels see the same translation
+    ref = np.ascontiguousarray(big[32 + dy:32 + dy + h, 32 + dx:32 + dx + w])       # ref(x,y) = cur(x+dx, y+dy)
+    ctx = pkg.MeContext(w, h, 2)
+    ctx.upload(0, cur); ctx.upload(1, ref)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    res, _ = ctx.motion_estimate([(0, 0, 0, p), (0, 1, 1, p), (0, 0, 0, p)])
+    ctx.close()
+    assert np.array_equal(res[0], res[2])
+    assert not res[0]["dist0"].any() and not res[0]["xMvL0"].any() and not res[0]["yMvL0"].any()
+    r = res[1].reshape(17, 30, 85)[1:-1, 1:-1, 0]                                      # interior SBs, 64x64 PU
+    assert not r["dist0"].any()
+    assert (r["xMvL0"] == -dx * 4).all() and (r["yMvL0"] == -dy * 4).all()
+
+
+def test_error_codes(pkg):
+    w, h = 128, 128
+    ctx = pkg.MeContext(w, h, 2)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    p.num_pus = 209
+    with pytest.raises(pkg.SvtMeError, match="0x80001005"):
+        ctx.motion_estimate([(0, 1, 1, p)])
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    with pytest.raises(pkg.SvtMeError, match="0x80001005"):
+        ctx.motion_estimate([(0, 5, 1, p)])
+    p.search_area_w = 200
+    with pytest.raises(pkg.SvtMeError, match="0x80001005"):
+        ctx.motion_estimate([(0, 1, 1, p)])
+    ctx.close()
