@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py -- 1080p open-loop motion-estimation throughput (BASELINE.json configs[1]).
+
+Workload (one "step"): the ME stage of a 121-picture 1920x1080 8-bit sequence coded with the
+reference's hierarchical mini-GOP 8 / 4 temporal layers prediction structure
+(EbPredictionStructure.c:183-240): picture 0 is intra (pyramid only), pictures 1..120 are B pictures
+-> 121 pyramid builds (PictureAnalysis decimation + padding) and 120 x MotionEstimateLcu-per-SB
+(510 SBs x 2 lists x 85 PUs each). Synthetic, seeded luma.
+
+  value  frames/s with all luma planes already resident in HBM (results stay in HBM)
+  e2e    frames/s through the C-ABI with HOST buffers: H2D of every luma plane from pinned memory and
+         D2H of every picture's me_results image inside the timed region
+  roofline  of the dominant kernel (integer full-pel search): INT-pipe bound, see DESIGN.md
+  cpu_baseline  the reference's own AVX2 ME (oracle/_ref, compiled from /root/reference) timed on the
+         host cores of this box on a bounded sample of the same workload
+
+N GPUs: every rank runs the same workload on its own stream of pictures (one stream per GPU,
+BASELINE configs[4]); no data-path collective; value = N x 120 frames / max-over-ranks time.
+
+`--impl reference` times only the CPU reference (all host cores) on the same metric.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 1920, 1080
+N_PICS = 121                      # POC 0 (intra) + 15 mini-GOPs of 8
+MINIGOP = [(8, 0, 0, 8), (4, 1, -4, 4), (2, 2, -2, 2), (6, 2, -2, 2), (1, 3, -1, 1), (3, 3, -1, 1), (5, 3, -1, 1), (7, 3, -1, 1)]
+SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
+# algorithmic work of the full-pel kernel per SB and list: 64x64 positions x (64 x 32 sub-sampled pixels)
+FULLPEL_BYTE_SADS_PER_SB_LIST = 64 * 64 * 64 * 32
+
+
+def gop_jobs():
+    """[(poc, temporal_layer, ref0_poc, ref1_poc)] for pictures 1..120 in decode order."""
+    jobs = []
+    for g in range((N_PICS - 1) // 8):
+        base = g * 8
+        for off, tl, d0, d1 in MINIGOP:
+            poc = base + off
+            if tl == 0:
+                jobs.append((poc, 0, poc - 8, poc - 8))          # base layer: both lists point at the previous base picture
+            else:
+                jobs.append((poc, tl, poc + d0, poc + d1))
+    return jobs
+
+
+def synth_sequence(n, seed):
+    """n luma planes of a panning, noisy synthetic scene (uint8, HxW)."""
+    rng = np.random.default_rng(seed)
+    big = rng.integers(0, 256, size=((H + 512) // 8, (W + 768) // 8), dtype=np.uint8).astype(np.float32)
+    big = np.kron(big, np.ones((8, 8), dtype=np.float32))
+    k = np.array([1, 4, 6, 4, 1], dtype=np.float32) / 16.0
+    for _ in range(2):
+        big = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 1, big)
+        big = np.apply_along_axis(lambda r: np.convolve(r, k, mode="same"), 0, big)
+    big = big + rng.normal(0, 10.0, size=big.shape).astype(np.float32)
+    out = np.empty((n, H, W), dtype=np.uint8)
+    for t in range(n):
+        ox, oy = 64 + (3 * t) % 512, 64 + (2 * t) % 256
+        f = big[oy:oy + H, ox:ox + W] + rng.normal(0, 2.0, size=(H, W)).astype(np.float32)
+        out[t] = np.clip(np.rint(f), 0, 255).astype(np.uint8)
+    return out
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks and throttle reasons while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) == 6:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU reference arm: the reference's own ME (oracle/_ref) or, where it is absent, the oracle port.
+_CPU = {}
+
+
+def _cpu_init(frames, kind):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import me_common as M
+    _CPU["M"] = M
+    _CPU["kind"] = kind
+    _CPU["lib"] = M.load_ref() if kind == "reference" else M.load_oracle()
+    _CPU["prefix"] = "ref" if kind == "reference" else "meo"
+    _CPU["frames"] = frames
+    _CPU["pyr"] = {}
+
+
+def _cpu_task(job):
+    """One picture of the hot path on one core: pyramids of the pictures not seen yet by this worker
+    (PictureAnalysis decimation + padding) + MotionEstimateLcu for every SB."""
+    M, lib, pre = _CPU["M"], _CPU["lib"], _CPU["prefix"]
+    poc, tl, r0, r1 = job
+    for i in (poc, r0, r1):
+        if i not in _CPU["pyr"]:
+            _CPU["pyr"][i] = M.build_pyramid(lib, pre, _CPU["frames"][i])
+    prm = M.default_params(M.load_oracle(), "meo", W, H, 2, tl, 3, 1 if tl < 3 else 0)
+    prm.same_ref_poc = 1 if r0 == r1 else 0
+    res, _ = M.motion_estimate(lib, pre, prm, _CPU["pyr"][poc], _CPU["pyr"][r0], _CPU["pyr"][r1], want_debug=False)
+    return int(res["dist0"].sum() & 0xFFFFFFFF)
+
+
+def cpu_reference_available():
+    return os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libsvtref.so"))
+
+
+class CpuArm:
+    """Pool of worker processes (one per host core) running the CPU ME on a bounded sample."""
+
+    def __init__(self, frames17):
+        import multiprocessing as mp
+        self.kind = "reference" if cpu_reference_available() else "port"
+        if self.kind == "port":
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import me_common as M
+            M.build_oracle(ref=False)
+        self.cores = len(os.sched_getaffinity(0))
+        self.jobs16 = [j for j in gop_jobs() if j[0] <= 16]
+        ctx = mp.get_context("fork")                       # forked before any CUDA context exists in this process
+        self.pool = ctx.Pool(self.cores, initializer=_cpu_init, initargs=(frames17, self.kind))
+
+    def run(self, n_tasks):
+        tasks = [self.jobs16[i % 16] for i in range(n_tasks)]
+        t0 = time.perf_counter()
+        self.pool.map(_cpu_task, tasks, chunksize=1)
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def run_reference_impl(args, rank):
+    """`--impl reference`: the reference's own CPU implementation of the path, all host threads."""
+    if rank != 0:
+        return
+    frames = synth_sequence(17, seed=1)
+    arm = CpuArm(frames)
+    n_tasks = max(16, 4 * arm.cores)
+    for _ in range(args.warmup):
+        arm.run(arm.cores)                                 # warm-up also fills each worker's pyramid cache
+    times = [arm.run(n_tasks) for _ in range(args.steps)]
+    arm.close()
+    total = sum(times)
+    fps = n_tasks * args.steps / total
+    sample = f"{n_tasks} pictures per step drawn from the first two mini-GOPs of the 1080p sequence, one picture per task over {arm.cores} worker processes"
+    line = {
+        "impl": "reference", "metric": "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": arm.cores, "kind": arm.kind, "sample": sample},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "sb_per_sec": fps * SB_PER_FRAME, "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus):
+    return {"workload": "1920x1080 8-bit luma, 121 pictures (1 intra + 120 B), hierarchical mini-GOP 8 / 4 temporal layers, "
+                        "full open-loop ME per picture: pyramid + HME L0/L1/L2 + 64x64 full-pel (85 PUs) + half/quarter-pel + bi-pred",
+            "frames_per_step_per_gpu": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": 85,
+            "streams": n_gpus, "parallelism": f"one picture stream per GPU x{n_gpus}, no collective",
+            "l2_policy": "inputs larger than L2 (121 luma planes = 251 MB + 306 MB of padded pyramids per step)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+def int_pipe_peak(sm_mhz):
+    """Peak of the binding unit for the full-pel kernel: VABSDIFF4.U8.ACC issues at 64 lanes/clk/SM on
+    sm_100a (measured: profiles/microbench/int_pipe_bench_r01.jsonl, 122.5 lane-ops/ns/SM at 1.965 GHz
+    = 62.3 lanes/clk), 4 byte-SADs per lane-op, 148 SMs. Returned in tera byte-SADs per second at the
+    given clock (the clock observed under load, else the maximum)."""
+    return 148 * 64 * 4 * sm_mhz * 1e6 / 1e12
+
+
+def run_gpu_impl(args, rank, world, local_rank):
+    import torch
+    pkg = importlib.import_module("svt-av1-1_b200")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    # ---- CPU baseline first (rank 0, N=1 only), while this process has no CUDA context yet
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        frames17 = synth_sequence(17, seed=1)
+        arm = CpuArm(frames17)
+        n_tasks = max(32, 8 * arm.cores)                   # ~20-30 CPU-seconds of the reference's ME
+        arm.run(arm.cores)
+        t = arm.run(n_tasks)
+        arm.close()
+        cpu = {"value": n_tasks / t, "unit": "frames/s", "cores": arm.cores, "kind": arm.kind,
+               "sample": f"{n_tasks} pictures of the first two mini-GOPs, {arm.cores} worker processes, {t:.1f} s wall"}
+
+    torch.cuda.set_device(local_rank)
+    frames = synth_sequence(N_PICS, seed=1 + rank)
+    host = torch.from_numpy(frames).pin_memory()                       # pinned host planes (e2e source)
+    dev = host.cuda(non_blocking=False)                                 # HBM-resident planes (value source)
+    jobs = gop_jobs()
+    ctx = pkg.MeContext(W, H, N_PICS, device=local_rank)
+    specs = []
+    for poc, tl, r0, r1 in jobs:
+        p = pkg.default_params(W, H, 2, tl, 3, 1 if tl < 3 else 0)
+        p.same_ref_poc = 1 if r0 == r1 else 0
+        specs.append((poc, r0, r1, p))
+    n_sb = ctx.n_sb
+    out = torch.empty((len(jobs), n_sb, 85, 40), dtype=torch.uint8).pin_memory()     # host me_results images
+    ptrs = [out[i].data_ptr() for i in range(len(jobs))]
+    job_arr, _, _ = ctx.make_jobs(specs, out_ptrs=ptrs)
+    stride = W
+
+    def step_resident():
+        for i in range(N_PICS):
+            ctx.upload_device(i, dev[i].data_ptr(), stride)
+        ctx.motion_estimate_async(job_arr)
+
+    def step_e2e():
+        for i in range(N_PICS):
+            ctx.upload_ptr(i, host[i].data_ptr(), stride)
+        ctx.motion_estimate_async(job_arr)
+        ctx.fetch(job_arr)
+
+    def barrier():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    def timed(fn, steps):
+        """Device time of `steps` calls: CUDA events on the context stream (the stream the kernels run on)."""
+        st = torch.cuda.ExternalStream(ctx.stream)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(st)
+        for _ in range(steps):
+            fn()
+        e1.record(st)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ctx.set_profiling(True)
+    ctx.kernel_times(reset=True)
+    l0 = ctx.kernel_launches
+    ms = timed(step_resident, args.steps)
+    launches = ctx.kernel_launches - l0
+    kt = ctx.kernel_times(reset=True)
+    ctx.set_profiling(False)
+    clocks = sampler.stop() if sampler else None
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    checksum = int(out.view(torch.int32).sum(dtype=torch.int64).item()) if rank == 0 else 0
+    ctx.close()
+
+    if rank == 0:
+        frames_total = world * (N_PICS - 1) * args.steps
+        fps = frames_total / (ms / 1e3)
+        fps_e2e = frames_total / (ms_e2e / 1e3)
+        fp_ms, fp_n = kt["fullpel"]
+        total_kernel_ms = sum(v[0] for v in kt.values())
+        # algorithmic work of one full-pel launch: every SB of every picture of the batch, one list
+        sads_per_launch = FULLPEL_BYTE_SADS_PER_SB_LIST * SB_PER_FRAME * len(jobs)
+        achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n else None
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965
+        peak = int_pipe_peak(sm_mhz)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        py_ms, py_n = kt["pyramid"]
+        pyr_bytes = W * H + sum(((W >> s) + 2 * p) * ((H >> s) + 2 * p) for s, p in ((0, 68), (1, 32), (2, 16)))
+        line = {
+            "metric": "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(world),
+            "sb_per_sec": fps * SB_PER_FRAME,
+            "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": N_PICS * W * H,
+                    "d2h_bytes_per_step": len(jobs) * n_sb * 85 * 40, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
+                         "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "peak_source": f"148 SM x 64 lanes/clk x 4 bytes x {sm_mhz} MHz (VABSDIFF4 issue rate, profiles/microbench)",
+                         "launch_ms": fp_ms / fp_n if fp_n else None, "share_of_kernel_time": fp_ms / total_kernel_ms if total_kernel_ms else None},
+            "roofline_hbm": {"kernel": "pyramid_kernel", "bound": "hbm", "achieved": (pyr_bytes / (py_ms / py_n / 1e3) / 1e9) if py_n else None,
+                             "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes / (py_ms / py_n / 1e3) / 1e9 / hbm_peak) if py_n else None,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
+            "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
+            "kernel_launches_per_step": {k: v[1] / args.steps for k, v in kt.items()},
+            "clocks": clocks, "result_checksum": checksum,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_impl(args, rank)
+        return
+    run_gpu_impl(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

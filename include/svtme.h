@@ -37,7 +37,15 @@ extern "C" {
 #define SVTME_ERR_BAD_PARAMETER           ((int32_t)0x80001005)
 
 #define SVTME_SQUARE_PU_COUNT 85
-#define SVTME_MAX_BATCH       64
+#define SVTME_MAX_BATCH       128
+
+/* kernel kinds, for svtme_kernel_times */
+#define SVTME_KERNEL_PYRAMID     0
+#define SVTME_KERNEL_HME         1
+#define SVTME_KERNEL_FULLPEL     2
+#define SVTME_KERNEL_SUBPEL      3
+#define SVTME_KERNEL_BIPRED_PACK 4
+#define SVTME_KERNEL_KINDS       5
 
 typedef struct SvtMeContext SvtMeContext;          /* opaque: one per GPU / encoder instance */
 
@@ -120,6 +128,11 @@ int32_t svtme_synchronize(SvtMeContext *ctx);
  * launches issued so far. */
 void   *svtme_stream(SvtMeContext *ctx);
 int64_t svtme_kernel_launches(const SvtMeContext *ctx);
+/* Per-kernel device time: when enabled every launch is bracketed by CUDA events on the context stream.
+ * svtme_kernel_times synchronises, then returns accumulated milliseconds and launch counts per kernel
+ * kind (arrays of SVTME_KERNEL_KINDS; either may be NULL) and optionally resets the accumulators. */
+int32_t svtme_set_profiling(SvtMeContext *ctx, int32_t enable);
+int32_t svtme_kernel_times(SvtMeContext *ctx, double *ms, int64_t *launches, int32_t reset);
 
 #ifdef __cplusplus
 }

@@ -5,14 +5,15 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SQUARE_PU_COUNT = 85
-MAX_BATCH = 64
+MAX_BATCH = 128
 
 EXPORTED_SYMBOLS = (
     "svtme_default_params", "svtme_create", "svtme_destroy", "svtme_last_error", "svtme_picture_upload",
     "svtme_picture_upload_device", "svtme_picture_download", "svtme_motion_estimate",
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
-    "svtme_kernel_launches",
+    "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times",
 )
+KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
 
 
 class SvtMeError(RuntimeError):
@@ -86,6 +87,10 @@ def load_library():
     lib.svtme_stream.argtypes = [C.c_void_p]
     lib.svtme_kernel_launches.restype = C.c_int64
     lib.svtme_kernel_launches.argtypes = [C.c_void_p]
+    lib.svtme_set_profiling.restype = C.c_int32
+    lib.svtme_set_profiling.argtypes = [C.c_void_p, C.c_int32]
+    lib.svtme_kernel_times.restype = C.c_int32
+    lib.svtme_kernel_times.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]
     _lib = lib
     return lib
 
@@ -184,3 +189,13 @@ class MeContext:
     @property
     def kernel_launches(self):
         return self.lib.svtme_kernel_launches(self._h)
+
+    def set_profiling(self, enable):
+        self._check(self.lib.svtme_set_profiling(self._h, 1 if enable else 0), "svtme_set_profiling")
+
+    def kernel_times(self, reset=False):
+        """{kind: (milliseconds, launches)} accumulated since the last reset (synchronises the stream)."""
+        ms = (C.c_double * len(KERNEL_KINDS))()
+        n = (C.c_int64 * len(KERNEL_KINDS))()
+        self._check(self.lib.svtme_kernel_times(self._h, ms, n, 1 if reset else 0), "svtme_kernel_times")
+        return {k: (ms[i], n[i]) for i, k in enumerate(KERNEL_KINDS)}

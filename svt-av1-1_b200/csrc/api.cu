@@ -33,6 +33,31 @@ struct SvtMeContext {
     DJob* h_jobs = nullptr;               // pinned
     int64_t launches = 0;
     std::string err;
+    // optional per-kernel timing (CUDA events on the context stream)
+    bool profiling = false;
+    struct Timed { int kind; cudaEvent_t a, b; };
+    std::vector<Timed> timed;
+    std::vector<cudaEvent_t> event_pool;
+    double kind_ms[SVTME_KERNEL_KINDS] = { 0, 0, 0, 0, 0 };
+    int64_t kind_launches[SVTME_KERNEL_KINDS] = { 0, 0, 0, 0, 0 };
+};
+
+// Brackets one kernel launch with events when profiling is on.
+struct LaunchTimer {
+    SvtMeContext* c; int kind; cudaEvent_t a = nullptr, b = nullptr;
+    static cudaEvent_t get(SvtMeContext* c) {
+        cudaEvent_t e = nullptr;
+        if (!c->event_pool.empty()) { e = c->event_pool.back(); c->event_pool.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    }
+    LaunchTimer(SvtMeContext* ctx, int k) : c(ctx), kind(k) {
+        c->launches++; c->kind_launches[k]++;
+        if (c->profiling) { a = get(c); b = get(c); cudaEventRecord(a, c->stream); }
+    }
+    ~LaunchTimer() {
+        if (a) { cudaEventRecord(b, c->stream); c->timed.push_back({ kind, a, b }); }
+    }
 };
 
 static int32_t fail(SvtMeContext* c, int32_t code, const std::string& msg) {
@@ -127,6 +152,8 @@ void svtme_destroy(SvtMeContext* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (auto& t : ctx->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    for (auto e : ctx->event_pool) cudaEventDestroy(e);
     for (auto& s : ctx->slots) cudaFree(s.base);
     cudaFree(ctx->d_scratch); cudaFree(ctx->d_results); cudaFree(ctx->d_debug); cudaFree(ctx->d_jobs);
     if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
@@ -142,8 +169,7 @@ int32_t svtme_picture_upload_device(SvtMeContext* ctx, int32_t slot, const uint8
     if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || !d_luma || stride < ctx->width)
         return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_device: bad argument");
     CU(cudaSetDevice(ctx->device));
-    launch_pyramid(d_luma, stride, ctx->slots[slot].pyr, ctx->stream);
-    ctx->launches++;
+    { LaunchTimer t(ctx, SVTME_KERNEL_PYRAMID); launch_pyramid(d_luma, stride, ctx->slots[slot].pyr, ctx->stream); }
     CU(cudaGetLastError());
     return SVTME_OK;
 }
@@ -241,13 +267,11 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     }
     CU(cudaMemcpyAsync(ctx->d_jobs, ctx->h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
     for (int list = 0; list < max_lists; list++) {
-        launch_hme(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream);
-        launch_fullpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream);
-        launch_subpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream);
-        ctx->launches += 3;
+        { LaunchTimer t(ctx, SVTME_KERNEL_HME); launch_hme(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL); launch_fullpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL); launch_subpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
     }
-    launch_bipred_pack(ctx->d_jobs, n_jobs, ctx->n_sb, ctx->stream);
-    ctx->launches += 1;
+    { LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK); launch_bipred_pack(ctx->d_jobs, n_jobs, ctx->n_sb, ctx->stream); }
     CU(cudaGetLastError());
     return SVTME_OK;
 }
@@ -272,6 +296,31 @@ int32_t svtme_motion_estimate(SvtMeContext* ctx, const SvtMeJob* jobs, int32_t n
     const int32_t rc = svtme_motion_estimate_async(ctx, jobs, n_jobs);
     if (rc != SVTME_OK) return rc;
     return svtme_fetch_results(ctx, jobs, n_jobs);
+}
+
+int32_t svtme_set_profiling(SvtMeContext* ctx, int32_t enable) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    ctx->profiling = enable != 0;
+    return SVTME_OK;
+}
+
+int32_t svtme_kernel_times(SvtMeContext* ctx, double* ms, int64_t* launches, int32_t reset) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (auto& t : ctx->timed) {
+        float e = 0.f;
+        CU(cudaEventElapsedTime(&e, t.a, t.b));
+        ctx->kind_ms[t.kind] += e;
+        ctx->event_pool.push_back(t.a); ctx->event_pool.push_back(t.b);
+    }
+    ctx->timed.clear();
+    for (int k = 0; k < SVTME_KERNEL_KINDS; k++) {
+        if (ms) ms[k] = ctx->kind_ms[k];
+        if (launches) launches[k] = ctx->kind_launches[k];
+        if (reset) { ctx->kind_ms[k] = 0; ctx->kind_launches[k] = 0; }
+    }
+    return SVTME_OK;
 }
 
 int32_t svtme_synchronize(SvtMeContext* ctx) {
