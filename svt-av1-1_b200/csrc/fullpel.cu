@@ -27,9 +27,11 @@ constexpr int kWinRows = 126;          // 64 search rows + 62
 constexpr int kWinPitch = 36;          // words; = 4 (mod 32) keeps the 8 row-distinct LDS.128 of a warp conflict-free
 constexpr int kFpSmemBytes = (4 * kWinRows * kWinPitch + 32 * 16 + 96) * 4;
 
-__device__ __forceinline__ void key_min(uint32_t* slot, uint32_t key) {
+// Warp-wide min of a key, then one shared-memory RED.MIN from lane 0 (predicated, no branch).
+__device__ __forceinline__ void key_min(uint32_t slot_addr, uint32_t key, uint32_t is_lane0) {
     const uint32_t m = __reduce_min_sync(0xffffffffu, key);
-    if ((threadIdx.x & 31) == 0 && m != 0xFFFFFFFFu) atomicMin(slot, m);
+    asm volatile("{ .reg .pred p; setp.ne.u32 p, %2, 0; @p red.shared.min.u32 [%0], %1; }"
+                 :: "r"(slot_addr), "r"(m), "r"(is_lane0) : "memory");
 }
 
 __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __restrict__ jobs, int list) {
@@ -70,6 +72,8 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const int tiles_s = leftover ? sah * 4 : 0;                    // single-position tiles (width & 7 leftovers)
     const int total = tiles_g + tiles_s;
     const int s = tid & 3;
+    const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
+    const uint32_t is_lane0 = (tid & 31) == 0 ? 1u : 0u;
 
     for (int u0 = 0; u0 < total; u0 += kFpThreads) {
         const int u = u0 + tid;
@@ -89,6 +93,10 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                 for (int k = 0; k < 4; k++) val[k] = (x0 + 4 * k >= mult8) && (x0 + 4 * k < saw);
             }
         }
+        // key = sad * 4096 + (row << 6 | col) as ONE IMAD (FMA pipe); a dead position gets 0 * sad + ~0
+        uint32_t kmul[4], kadd[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { kmul[k] = val[k] ? 4096u : 0u; kadd[k] = val[k] ? (uint32_t)((y << 6) | (x0 + 4 * k)) : 0xFFFFFFFFu; }
         uint32_t h16[4][4], s32[4][2], s64[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) { s64[k] = 0; s32[k][0] = s32[k][1] = 0; }
@@ -124,15 +132,12 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                     }
                 }
             }
-            const uint32_t pos = (uint32_t)(y << 6);
             // ---- 8x8 PUs of block-row b
 #pragma unroll
             for (int j = 0; j < 8; j++) {
-                uint32_t key = 0xFFFFFFFFu;
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    if (val[k]) key = min(key, (acc[k][j] << 12) | pos | (uint32_t)(x0 + 4 * k));
-                key_min(&keys[21 + kTab8[b * 8 + j]], key);
+                const uint32_t key = min(min(acc[0][j] * kmul[0] + kadd[0], acc[1][j] * kmul[1] + kadd[1]),
+                                         min(acc[2][j] * kmul[2] + kadd[2], acc[3][j] * kmul[3] + kadd[3]));
+                key_min(keys_addr + 4u * (21 + kTab8[b * 8 + j]), key, is_lane0);
             }
             // ---- 16x16: sum of two block-rows
             if ((b & 1) == 0) {
@@ -151,11 +156,9 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                 }
 #pragma unroll
             for (int q = 0; q < 4; q++) {
-                uint32_t key = 0xFFFFFFFFu;
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    if (val[k]) key = min(key, (h16[k][q] << 12) | pos | (uint32_t)(x0 + 4 * k));
-                key_min(&keys[5 + kTab16[(b >> 1) * 4 + q]], key);
+                const uint32_t key = min(min(h16[0][q] * kmul[0] + kadd[0], h16[1][q] * kmul[1] + kadd[1]),
+                                         min(h16[2][q] * kmul[2] + kadd[2], h16[3][q] * kmul[3] + kadd[3]));
+                key_min(keys_addr + 4u * (5 + kTab16[(b >> 1) * 4 + q]), key, is_lane0);
             }
             if ((b & 3) != 3) continue;
             // ---- 32x32: two PUs of this half of the SB
@@ -180,17 +183,15 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                     for (int k = 0; k < 4; k++)
                         if (val[k]) key = min(key, (s32[k][q] << 13) | ((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3));
                 }
-                key_min(&keys[1 + (b >> 2) * 2 + q], key);
+                key_min(keys_addr + 4u * (1 + (b >> 2) * 2 + q), key, is_lane0);
 #pragma unroll
                 for (int k = 0; k < 4; k++) { s64[k] += s32[k][q]; s32[k][q] = 0; }
             }
             if (b != 7) continue;
             {
-                uint32_t key = 0xFFFFFFFFu;
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    if (val[k]) key = min(key, (s64[k] << 12) | pos | (uint32_t)(x0 + 4 * k));
-                key_min(&keys[0], key);
+                const uint32_t key = min(min(s64[0] * kmul[0] + kadd[0], s64[1] * kmul[1] + kadd[1]),
+                                         min(s64[2] * kmul[2] + kadd[2], s64[3] * kmul[3] + kadd[3]));
+                key_min(keys_addr, key, is_lane0);
             }
         }
     }

@@ -58,7 +58,12 @@ __device__ __forceinline__ int mv_y(uint32_t mv) { return (int16_t)(mv >> 16); }
 __device__ __forceinline__ uint32_t make_mv(int x, int y) { return ((uint32_t)(uint16_t)y << 16) | (uint16_t)x; }
 
 // SAD of four packed bytes accumulated into c: one VABSDIFF4.U8.ACC on sm_100a.
-__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c) { return __vsadu4(a, b) + c; }
+// (inline PTX: nvcc lowers `__vsadu4(a, b) + c` to VABSDIFF4 with a zero addend plus a separate IADD3.)
+__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 // 32-bit word at an arbitrary byte address of global memory (two aligned loads + funnel shift).
 __device__ __forceinline__ uint32_t ldg_u32_unaligned(const uint8_t* p) {
