@@ -228,7 +228,7 @@ static bool params_ok(const SvtMeContext* ctx, const SvtMeParams& p, std::string
     for (int i = 0; i < 2; i++) {
         REQ(p.hme_l0_w[i] >= 1 && p.hme_l0_h[i] >= 1 && p.hme_l1_w[i] >= 1 && p.hme_l1_h[i] >= 1 && p.hme_l2_w[i] >= 0 && p.hme_l2_h[i] >= 0);
         REQ(p.hme_l1_w[i] <= 64 && p.hme_l1_h[i] <= 64 && p.hme_l2_w[i] <= 64 && p.hme_l2_h[i] <= 64);
-        REQ(p.hme_l0_w[i] * p.hme_l0_mult_x / 100 <= 1024 && p.hme_l0_h[i] * p.hme_l0_mult_y / 100 <= 1024);
+        REQ(p.hme_l0_w[i] * p.hme_l0_mult_x / 100 <= 504 && p.hme_l0_h[i] * p.hme_l0_mult_y / 100 <= 248);   /* argmin key: 9-bit col, 8-bit row */
     }
     REQ(p.use_subpel == 0 || p.use_subpel == 1);
 #undef REQ

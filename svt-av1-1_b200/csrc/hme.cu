@@ -2,27 +2,44 @@
 // region selection, CheckZeroZeroCenter and the search-area clipping of MotionEstimateLcu
 // (reference Source/Lib/Codec/EbMotionEstimation.c:5882-6145, 4306-4758, 6300-6733, 5466-5552).
 //
-// One CTA (256 threads) per SB. Each search level stages its reference window in shared memory
-// (word aligned, chunked by rows when large) and gives every thread one search position at a time;
-// an 8-lane group is one of the reference's 8-position SIMD groups, which is what quirk Q3
-// (HME level 1: min(lo+hi, 65535 + min_group(lo))) needs. The argmin is a 64-bit key
-// (value << 32 | row << 16 | col): smallest value, first in raster order.
+// One CTA (256 threads) per SB. The 2x2 HME regions are independent chains (level 0 -> 1 -> 2 of the
+// same region), so each region is owned by a GROUP of 64 threads (two warps) that synchronises on its
+// own named barrier and stages its own reference window in shared memory; the four chains run
+// concurrently without CTA-wide barriers. Inside a group one thread evaluates 4 consecutive search
+// positions of one row: the window is staged word-aligned, so the four byte offsets are constant funnel
+// shifts of the same two words (3 SHF + 4 VABSDIFF4.ACC per source word). Two neighbouring lanes form one
+// of the reference's 8-position SIMD groups, which is what quirk Q3 (HME level 1:
+// min(lo+hi, 65535 + min_group(lo))) needs. argmin: 32-bit key (value, row, col) -> smallest value,
+// first in raster order; thread-local min, CREDUX.MIN per warp, one shared atomicMin per warp.
 #include "me_common.cuh"
 
 namespace svtme {
 
 constexpr int kHmeThreads = 256;
-constexpr int kWinBytes = 24 * 1024;
+constexpr int kGroupThreads = 64;
+constexpr int kRegionWinWords = 2560;          // 10 KB window buffer per region group
 
 struct HmeShared {
     uint32_t src_even[32 * 16];     // even rows of the 64x64 source SB
     uint32_t q_even[16 * 8];        // even rows of the 32x32 quarter SB
     uint32_t s_even[8 * 4];         // even rows of the 16x16 sixteenth SB
-    uint32_t win[kWinBytes / 4];
-    unsigned long long red[kHmeThreads / 32];
-    unsigned long long result;
+    uint32_t win[4][kRegionWinWords];
+    uint32_t best[12];              // [level][region] winning keys
     uint32_t cand_sad[8];
+    int x[3][2][2], y[3][2][2];
+    uint32_t sad[3][2][2];
+    int center[2];
 };
+
+// Named barrier of one 64-thread region group (ids 1..4; constant ids so ptxas reserves 5 barriers, not 16).
+__device__ __forceinline__ void group_bar(int id) {
+    switch (id) {
+    case 1: asm volatile("bar.sync 1, %0;" :: "n"(kGroupThreads) : "memory"); break;
+    case 2: asm volatile("bar.sync 2, %0;" :: "n"(kGroupThreads) : "memory"); break;
+    case 3: asm volatile("bar.sync 3, %0;" :: "n"(kGroupThreads) : "memory"); break;
+    default: asm volatile("bar.sync 4, %0;" :: "n"(kGroupThreads) : "memory"); break;
+    }
+}
 
 // SAD of the (sub-sampled) SB against the reference picture at displacement (dx,dy): one warp.
 // NxMSadKernel with doubled strides, ME.c:5918-5926.
@@ -36,84 +53,79 @@ __device__ uint32_t warp_sb_sad(const uint32_t* src_even, const DPlane& rp, int 
     return __reduce_add_sync(0xffffffffu, acc);
 }
 
-// Exhaustive search of one region. All threads of the CTA call this; returns the winning key in sh.result.
-//   src: even rows of the block, 'src_pitch' words per row;  w_words x rows block
+// Exhaustive search of one region by one 64-thread group. Returns the winning key
+// (value << VS | row << RS | col) to every thread of the group.
+//   src: even rows of the block, SP words per row;  W words x `rows` rows
 //   (rx, ry): top-left search position in level coordinates; saw x sah positions
-__device__ void search_region(HmeShared& sh, const uint32_t* src, int src_pitch, int w_words, int rows,
-                              const DPlane& rp, int rx, int ry, int saw, int sah, bool l1_quirk) {
-    const int tid = threadIdx.x;
-    const int sawp = (saw + 7) & ~7;
-    const int bx0 = rp.ox + rx;                       // byte column of position 0 inside the allocation
-    const int m = bx0 & 3;
-    const int pitch = ((m + saw + 4 * w_words - 1 + 3) >> 2) + 1;   // words per window row
-    const int max_rows = (kWinBytes / 4) / pitch;
+template <int W, int SP, bool QUIRK, int VS, int RS>
+__device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id, int gtid, const uint32_t* src, int rows,
+                                 const DPlane& rp, int rx, int ry, int saw, int sah) {
+    const int tpr = ((saw + 7) & ~7) >> 2;             // 4-position tiles per search row (whole 8-groups)
+    const int pitch = tpr + W;                          // window words per row
     const int extra = 2 * (rows - 1);
-    const int chunk = max(1, max_rows - extra);
-    unsigned long long best = ~0ull;
+    const int chunk = max(1, kRegionWinWords / pitch - extra);
+    uint32_t best = 0xFFFFFFFFu;
+    if (gtid == 0) *best_slot = 0xFFFFFFFFu;
     for (int i0 = 0; i0 < sah; i0 += chunk) {
         const int i1 = min(sah, i0 + chunk);
         const int wrows = i1 - i0 + extra;
-        __syncthreads();                              // previous users of sh.win are done
-        for (int t = tid; t < wrows * pitch; t += kHmeThreads) {
+        group_bar(bar_id);                              // previous users of the window are done
+        for (int t = gtid; t < wrows * pitch; t += kGroupThreads) {
             const int r = t / pitch, c = t - r * pitch;
-            const uint8_t* g = rp.buf + (size_t)(rp.oy + ry + i0 + r) * rp.stride + (bx0 - m) + 4 * c;
-            sh.win[t] = __ldg(reinterpret_cast<const uint32_t*>(g));
+            win[t] = ldg_u32_unaligned(rp.at(rx + 4 * c, ry + i0 + r));
         }
-        __syncthreads();
-        const int npos = (i1 - i0) * sawp;
-        for (int t = tid; t < ((npos + kHmeThreads - 1) / kHmeThreads) * kHmeThreads; t += kHmeThreads) {
-            const int i = t / sawp, j = t - i * sawp;
-            const bool valid = t < npos && j < saw;
-            uint32_t lo = 0, hi = 0;
-            if (valid) {
-                const int off = m + j, idx = off >> 2;
-                const uint32_t shb = (off & 3) * 8;
-                for (int r = 0; r < rows; r++) {
-                    const uint32_t* wr = sh.win + (i + 2 * r) * pitch + idx;
-                    const uint32_t* sr = src + r * src_pitch;
+        group_bar(bar_id);
+        const int ntiles = (i1 - i0) * tpr;
+        for (int t0 = 0; t0 < ntiles; t0 += kGroupThreads) {
+            const int t = t0 + gtid;
+            const bool live = t < ntiles;
+            const int i = live ? t / tpr : 0, jt = live ? t - i * tpr : 0;
+            uint32_t lo[4] = { 0, 0, 0, 0 }, hi[4] = { 0, 0, 0, 0 };
+            if (live) {
+                const uint32_t* wr = win + i * pitch + jt;
+                const uint32_t* sr = src;
+                for (int r = 0; r < rows; r++, wr += 2 * pitch, sr += SP) {
                     uint32_t a = wr[0];
-                    for (int c = 0; c < w_words; c++) {
-                        const uint32_t b = wr[c + 1];
-                        const uint32_t v = __funnelshift_r(a, b, shb);
-                        if (c < 4) lo = sad4(sr[c], v, lo); else hi = sad4(sr[c], v, hi);
+#pragma unroll
+                    for (int c = 0; c < W; c++) {
+                        const uint32_t b = wr[c + 1], s = sr[c];
+                        const uint32_t v1 = __funnelshift_r(a, b, 8), v2 = __funnelshift_r(a, b, 16), v3 = __funnelshift_r(a, b, 24);
+                        if (QUIRK && c >= 4) {
+                            hi[0] = sad4(s, a, hi[0]); hi[1] = sad4(s, v1, hi[1]); hi[2] = sad4(s, v2, hi[2]); hi[3] = sad4(s, v3, hi[3]);
+                        } else {
+                            lo[0] = sad4(s, a, lo[0]); lo[1] = sad4(s, v1, lo[1]); lo[2] = sad4(s, v2, lo[2]); lo[3] = sad4(s, v3, lo[3]);
+                        }
                         a = b;
                     }
                 }
             }
-            uint32_t val;
-            if (l1_quirk) {                            // quirk Q3: 16-bit halves + min-subtraction
-                uint32_t l = valid ? lo : 65535u, mlo = l;
+            uint32_t mlo = 0;
+            if (QUIRK) {                               // quirk Q3: min of the low halves over the 8-position group
+                mlo = 65535u;
+#pragma unroll
+                for (int k = 0; k < 4; k++) mlo = min(mlo, (live && 4 * jt + k < saw) ? lo[k] : 65535u);
                 mlo = min(mlo, __shfl_xor_sync(0xffffffffu, mlo, 1));
-                mlo = min(mlo, __shfl_xor_sync(0xffffffffu, mlo, 2));
-                mlo = min(mlo, __shfl_xor_sync(0xffffffffu, mlo, 4));
-                val = min(lo + hi, 65535u + mlo);
-            } else {
-                val = lo + hi;
             }
-            if (valid) {
-                const unsigned long long key = ((unsigned long long)val << 32) | ((uint32_t)(i0 + i) << 16) | (uint32_t)j;
-                best = key < best ? key : best;
+            if (live) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t val = QUIRK ? min(lo[k] + hi[k], 65535u + mlo) : lo[k];
+                    const uint32_t key = (val << VS) | ((uint32_t)(i0 + i) << RS) | (uint32_t)(4 * jt + k);
+                    if (4 * jt + k < saw) best = min(best, key);
+                }
             }
         }
     }
-    best = warp_min_u64(best);
-    if ((tid & 31) == 0) sh.red[tid >> 5] = best;
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long b = sh.red[0];
-        for (int w = 1; w < kHmeThreads / 32; w++) b = sh.red[w] < b ? sh.red[w] : b;
-        sh.result = b;
-    }
-    __syncthreads();
+    best = __reduce_min_sync(0xffffffffu, best);
+    if ((gtid & 31) == 0) atomicMin(best_slot, best);
+    group_bar(bar_id);
+    return *best_slot;
 }
 
 __device__ __forceinline__ int round_sa_width(int w) { return (w < 8) ? 8 : (w & 7) ? w + (w - ((w >> 3) << 3)) : w; }
 
 __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict__ jobs, int list) {
     __shared__ HmeShared sh;
-    __shared__ int s_x[3][2][2], s_y[3][2][2];
-    __shared__ unsigned long long s_sad[3][2][2];
-    __shared__ int s_center[2];
     const DJob& job = jobs[blockIdx.y];
     const int sb = blockIdx.x;
     if (sb >= job.sb_cols * job.sb_rows) return;
@@ -171,14 +183,18 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
             // list 1 inherits whatever list 0 left there (visible when an HME level is disabled).
             if (tid < 12) {
                 const int l = tid >> 2, w = (tid >> 1) & 1, h = tid & 1;
-                s_x[l][w][h] = list == 0 ? xsc : scr.hme_x[l][w][h];
-                s_y[l][w][h] = list == 0 ? ysc : scr.hme_y[l][w][h];
-                s_sad[l][w][h] = 0;
+                sh.x[l][w][h] = list == 0 ? xsc : scr.hme_x[l][w][h];
+                sh.y[l][w][h] = list == 0 ? ysc : scr.hme_y[l][w][h];
+                sh.sad[l][w][h] = 0;
             }
             __syncthreads();
-            if (p.enable_hme_level0) {
-                const DPlane& rp = ref.sixteenth;
-                for (int h = 0; h < nh; h++) for (int w = 0; w < nw; w++) {
+            const int g = tid >> 6, gtid = tid & 63;             // region group
+            if (g < nw * nh) {
+                const int w = g % nw, h = g / nw, bar = 1 + g;
+                uint32_t* win = sh.win[g];
+                const bool half = sb_w == 32;                     // right-edge SB of a width % 64 == 32 picture
+                if (p.enable_hme_level0) {                        // HmeLevel0, ME.c:4306-4503 (sixteenth picture)
+                    const DPlane& rp = ref.sixteenth;
                     int saw = (int16_t)((p.hme_l0_w[w] * p.hme_l0_mult_x) / 100);
                     int sah = (int16_t)((p.hme_l0_h[h] * p.hme_l0_mult_y) / 100);
                     int xd = xsc >> 2, yd = ysc >> 2;
@@ -188,80 +204,78 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
                     int say = -(int16_t)(((p.hme_l0_total_h * p.hme_l0_mult_y) / 100) >> 1) + yd;
                     clip_search_area(ox >> 2, sax, saw, rp.ox - 1, rp.w);
                     clip_search_area(oy >> 2, say, sah, rp.oy - 1, rp.h);
-                    search_region(sh, sh.s_even, 4, sb_w >> 4, sb_h >> 3, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah, false);
-                    if (tid == 0) {
-                        const unsigned long long k = sh.result;
-                        s_sad[0][w][h] = (k >> 32) * 2;
-                        s_x[0][w][h] = (int16_t)((((int)(k & 0xFFFF)) + sax) * 4);
-                        s_y[0][w][h] = (int16_t)((((int)((k >> 16) & 0xFFFF)) + say) * 4);
+                    const uint32_t k = half
+                        ? group_search<2, 4, false, 17, 9>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah)
+                        : group_search<4, 4, false, 17, 9>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah);
+                    if (gtid == 0) {
+                        sh.sad[0][w][h] = (k >> 17) * 2;
+                        sh.x[0][w][h] = (int16_t)(((int)(k & 511) + sax) * 4);
+                        sh.y[0][w][h] = (int16_t)(((int)((k >> 9) & 255) + say) * 4);
                     }
-                    __syncthreads();
+                    group_bar(bar);
                 }
-            }
-            if (p.enable_hme_level1) {
-                const DPlane& rp = ref.quarter;
-                for (int h = 0; h < nh; h++) for (int w = 0; w < nw; w++) {
+                if (p.enable_hme_level1) {                        // HmeLevel1, ME.c:4505-4625 (quarter picture)
+                    const DPlane& rp = ref.quarter;
                     int saw = round_sa_width(p.hme_l1_w[w]), sah = p.hme_l1_h[h];
-                    int sax = -(saw >> 1) + (s_x[0][w][h] >> 1), say = -(sah >> 1) + (s_y[0][w][h] >> 1);
+                    int sax = -(saw >> 1) + (sh.x[0][w][h] >> 1), say = -(sah >> 1) + (sh.y[0][w][h] >> 1);
                     clip_search_area(ox >> 1, sax, saw, rp.ox - 1, rp.w);
                     clip_search_area(oy >> 1, say, sah, rp.oy - 1, rp.h);
-                    const int ww = sb_w >> 3, rr = sb_h >> 2;
-                    search_region(sh, sh.q_even, 8, ww, rr, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah, ww == 8 && rr <= 16);
-                    if (tid == 0) {
-                        const unsigned long long k = sh.result;
-                        s_sad[1][w][h] = (k >> 32) * 2;
-                        s_x[1][w][h] = (int16_t)((((int)(k & 0xFFFF)) + sax) * 2);
-                        s_y[1][w][h] = (int16_t)((((int)((k >> 16) & 0xFFFF)) + say) * 2);
+                    const uint32_t k = half
+                        ? group_search<4, 8, false, 13, 7>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah)
+                        : group_search<8, 8, true, 13, 7>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah);
+                    if (gtid == 0) {
+                        sh.sad[1][w][h] = (k >> 13) * 2;
+                        sh.x[1][w][h] = (int16_t)(((int)(k & 127) + sax) * 2);
+                        sh.y[1][w][h] = (int16_t)(((int)((k >> 7) & 63) + say) * 2);
                     }
-                    __syncthreads();
+                    group_bar(bar);
                 }
-            }
-            if (p.enable_hme_level2) {
-                const DPlane& rp = ref.full;
-                for (int h = 0; h < nh; h++) for (int w = 0; w < nw; w++) {
+                if (p.enable_hme_level2) {                        // HmeLevel2, ME.c:4627-4758 (full picture)
+                    const DPlane& rp = ref.full;
                     int saw = round_sa_width(p.hme_l2_w[w]), sah = p.hme_l2_h[h];
-                    int sax = -(saw >> 1) + s_x[1][w][h], say = -(sah >> 1) + s_y[1][w][h];
+                    int sax = -(saw >> 1) + sh.x[1][w][h], say = -(sah >> 1) + sh.y[1][w][h];
                     clip_search_area(ox, sax, saw, 63, rp.w);
                     clip_search_area(oy, say, sah, 63, rp.h);
-                    search_region(sh, sh.src_even, 16, sb_w >> 2, sb_h >> 1, rp, ox + sax, oy + say, saw, sah, false);
-                    if (tid == 0) {
-                        const unsigned long long k = sh.result;
-                        s_sad[2][w][h] = (k >> 32) * 2;
-                        s_x[2][w][h] = (int16_t)(((int)(k & 0xFFFF)) + sax);
-                        s_y[2][w][h] = (int16_t)(((int)((k >> 16) & 0xFFFF)) + say);
+                    const uint32_t k = half
+                        ? group_search<8, 16, false, 13, 7>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah)
+                        : group_search<16, 16, false, 13, 7>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah);
+                    if (gtid == 0) {
+                        sh.sad[2][w][h] = (k >> 13) * 2;
+                        sh.x[2][w][h] = (int16_t)((int)(k & 127) + sax);
+                        sh.y[2][w][h] = (int16_t)((int)((k >> 7) & 63) + say);
                     }
-                    __syncthreads();
                 }
             }
+            __syncthreads();
             if (list == 0 && p.num_lists == 2 && tid < 12) {
                 const int l = tid >> 2, w = (tid >> 1) & 1, h = tid & 1;
-                scr.hme_x[l][w][h] = s_x[l][w][h]; scr.hme_y[l][w][h] = s_y[l][w][h];
+                scr.hme_x[l][w][h] = sh.x[l][w][h]; scr.hme_y[l][w][h] = sh.y[l][w][h];
             }
             if (tid == 0) {
                 int xh = 0, yh = 0;
                 const int lvl = p.enable_hme_level2 ? 2 : p.enable_hme_level1 ? 1 : p.enable_hme_level0 ? 0 : -1;
                 if (lvl >= 0) {
-                    xh = s_x[lvl][0][0]; yh = s_y[lvl][0][0];
-                    unsigned long long sh_ = s_sad[lvl][0][0];
+                    xh = sh.x[lvl][0][0]; yh = sh.y[lvl][0][0];
+                    uint32_t sh_ = sh.sad[lvl][0][0];
                     for (int h = 0; h < nh; h++) for (int w = (h == 0 ? 1 : 0); w < nw; w++)
-                        if (s_sad[lvl][w][h] < sh_) { xh = s_x[lvl][w][h]; yh = s_y[lvl][w][h]; sh_ = s_sad[lvl][w][h]; }
+                        if (sh.sad[lvl][w][h] < sh_) { xh = sh.x[lvl][w][h]; yh = sh.y[lvl][w][h]; sh_ = sh.sad[lvl][w][h]; }
                     const int tot = nw * nh;
                     if (lvl == 2 && p.same_ref_poc && list == 1 && tot > 1) {           // ME.c:6606-6631
                         for (int q = 0; q < tot - 1; q++) for (int n = q + 1; n < tot; n++) {
                             const int qa = q / nw, qb = q % nw, na = n / nw, nb = n % nw;
-                            if (s_sad[2][qa][qb] > s_sad[2][na][nb]) {
-                                const int tx = s_x[2][qa][qb], ty = s_y[2][qa][qb]; const unsigned long long ts = s_sad[2][qa][qb];
-                                s_x[2][qa][qb] = s_x[2][na][nb]; s_y[2][qa][qb] = s_y[2][na][nb]; s_sad[2][qa][qb] = s_sad[2][na][nb];
-                                s_x[2][na][nb] = tx; s_y[2][na][nb] = ty; s_sad[2][na][nb] = ts;
+                            if (sh.sad[2][qa][qb] > sh.sad[2][na][nb]) {
+                                const int tx = sh.x[2][qa][qb], ty = sh.y[2][qa][qb]; const uint32_t ts = sh.sad[2][qa][qb];
+                                sh.x[2][qa][qb] = sh.x[2][na][nb]; sh.y[2][qa][qb] = sh.y[2][na][nb]; sh.sad[2][qa][qb] = sh.sad[2][na][nb];
+                                sh.x[2][na][nb] = tx; sh.y[2][na][nb] = ty; sh.sad[2][na][nb] = ts;
                             }
                         }
-                        xh = s_x[2][0][1]; yh = s_y[2][0][1];
+                        xh = sh.x[2][0][1]; yh = sh.y[2][0][1];
                     }
                 }
-                s_center[0] = xh; s_center[1] = yh;
+                sh.center[0] = xh; sh.center[1] = yh;
             }
             __syncthreads();
-            xsc = s_center[0]; ysc = s_center[1];
+            xsc = sh.center[0]; ysc = sh.center[1];
         }
     }
 
