@@ -27,8 +27,8 @@ constexpr int kMargin = 3;              // window starts 3 pixels left/above the
 struct SpShared {
     uint32_t plane[4][kPlWords];        // A, B, H, J
     uint32_t src[64 * 16];
-    uint32_t ssd_part[4][9][64];
-    uint32_t sad_part[4][9][64];
+    uint32_t sum_ssd[9][kNumPu];        // per (candidate, PU) distortion sums, accumulated with shared atomics
+    uint32_t sum_sad[9][kNumPu];
     uint32_t pu_sad[kNumPu], pu_mv[kNumPu], pu_ssd[kNumPu];
     int32_t  pu_dir[kNumPu];
     uint32_t pu_imv[kNumPu];            // MV at entry of the current stage
@@ -97,17 +97,30 @@ __device__ __forceinline__ uint32_t true_ssd4(uint32_t a, uint32_t b, uint32_t a
     const uint32_t d = __vabsdiffu4(a, b);
     return __dp4a(d, d, acc);
 }
-// 4-tap {-2,18,18,-2} on four packed pixels given the four tap words
+// 4-tap {-2,18,18,-2}, +16 >> 5, clip to u8 on four packed pixels given the four tap words.
+// SIMD-in-word on two 16-bit lanes (even bytes / odd bytes): lane = 18*(b+c) - 2*(a+d) + 16 + 256*32 stays in
+// [7188, 17388], so nothing crosses a lane; after >> 5 the lane is 256 + (v >> 5), VIMNMX.U16x2 clamps it to
+// [256, 511] and the low byte of each lane is the clipped pixel.
+__device__ __forceinline__ uint32_t filt4_lanes(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    uint32_t v = b * 18u + 0x20102010u;
+    v = c * 18u + v;
+    v = v - 2u * (a + d);
+    v = (v >> 5) & 0x03FF03FFu;
+    v = __vmaxu2(v, 0x01000100u);
+    return __vminu2(v, 0x01FF01FFu);
+}
 __device__ __forceinline__ uint32_t filt4(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3) {
-    uint32_t out = 0;
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const int a = (t0 >> (8 * i)) & 255, b = (t1 >> (8 * i)) & 255, c = (t2 >> (8 * i)) & 255, d = (t3 >> (8 * i)) & 255;
-        int v = (18 * (b + c) - 2 * (a + d) + 16) >> 5;
-        v = min(max(v, 0), 255);
-        out |= (uint32_t)v << (8 * i);
-    }
-    return out;
+    const uint32_t e = filt4_lanes(__byte_perm(t0, 0, 0x4240), __byte_perm(t1, 0, 0x4240), __byte_perm(t2, 0, 0x4240), __byte_perm(t3, 0, 0x4240));
+    const uint32_t o = filt4_lanes(__byte_perm(t0, 0, 0x4341), __byte_perm(t1, 0, 0x4341), __byte_perm(t2, 0, 0x4341), __byte_perm(t3, 0, 0x4341));
+    return __byte_perm(e, o, 0x6240);
+}
+// validity of quarter-pel candidate k (order L R T B TL TR BR BL) given the best half-pel direction (ME.c:2859-2881):
+// the candidate itself or one of its two neighbours in the 8-cycle TL,T,TR,R,BR,B,BL,L; mirrored when the
+// half-pel MV has a fractional part (method != 0)
+__device__ __forceinline__ bool quarter_valid(int method, int dir, int k) {
+    const int q8 = k == 0 ? D_L : k == 1 ? D_R : k == 2 ? D_T : k == 3 ? D_B : k == 4 ? D_TL : k == 5 ? D_TR : k == 6 ? D_BR : D_BL;
+    const int centre = method ? ((q8 + 4) & 7) : q8;
+    return dir == centre || dir == ((centre + 1) & 7) || dir == ((centre + 7) & 7);
 }
 
 __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
@@ -159,11 +172,14 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         }
         __syncthreads();
 
-        // ---- half-pel: (level, block, candidate) tasks -> partial wrapping-SSD and SAD
+        for (int t = tid; t < 9 * kNumPu; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
+        __syncthreads();
+        // ---- half-pel: (level, block, candidate) tasks -> wrapping-SSD and SAD summed per (candidate, PU)
         for (int t = tid; t < 4 * 64 * 9; t += kSpThreads) {
             const int k = t % 9, blk = (t / 9) & 63, L = t / (9 * 64);
             const int bx = blk & 7, by = blk >> 3;
-            const uint32_t mv = sh.pu_imv[pu_of_block(L, bx, by)];
+            const int pu = pu_of_block(L, bx, by);
+            const uint32_t mv = sh.pu_imv[pu];
             const int X = kMargin + (mv_x(mv) >> 2) - sax + bx * 8 + kHalf[k][1];
             const int Y = kMargin + (mv_y(mv) >> 2) - say + by * 8 + kHalf[k][2];
             const uint32_t* pl = sh.plane[kHalf[k][0]];
@@ -175,20 +191,14 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                 ssd = wrap_ssd4(s0, c.x, ssd); ssd = wrap_ssd4(s1, c.y, ssd);
                 sad = sad4(s0, c.x, sad); sad = sad4(s1, c.y, sad);
             }
-            sh.ssd_part[L][k][blk] = ssd; sh.sad_part[L][k][blk] = sad;
+            atomicAdd(&sh.sum_ssd[k][pu], ssd); atomicAdd(&sh.sum_sad[k][pu], sad);
         }
         __syncthreads();
         // ---- per PU: nine candidates in the reference's order, strict '<' on the SSD  (ME.c:1909-2239)
         if (tid < kNumPu && (tid < 21 || p.cu8x8_mode != 1)) {
-            int L, bx, by, nb; pu_blocks(tid, L, bx, by, nb);
             uint32_t dist[9], sadv[9];
-            for (int k = 0; k < 9; k++) {
-                uint32_t a = 0, b = 0;
-                for (int yy = 0; yy < nb; yy++) for (int xx = 0; xx < nb; xx++) {
-                    a += sh.ssd_part[L][k][(by + yy) * 8 + bx + xx]; b += sh.sad_part[L][k][(by + yy) * 8 + bx + xx];
-                }
-                dist[k] = a; sadv[k] = b;
-            }
+#pragma unroll
+            for (int k = 0; k < 9; k++) { dist[k] = sh.sum_ssd[k][tid]; sadv[k] = sh.sum_sad[k][tid]; }
             const uint32_t imv = sh.pu_imv[tid];
             uint32_t bssd = dist[0], bsad = sh.pu_sad[tid], bmv = imv;
             for (int k = 1; k < 9; k++)
@@ -202,11 +212,13 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         }
         __syncthreads();
         if (tid < kNumPu) sh.pu_imv[tid] = sh.pu_mv[tid];
+        for (int t = tid; t < 9 * kNumPu; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
 
         // ---- quarter-pel: (level, block, candidate) tasks -> partial true-SSD and SAD of the averaged pair
-        for (int t = tid; t < 4 * 64 * 8; t += kSpThreads) {
-            const int k = t & 7, blk = (t >> 3) & 63, L = t >> 9;
+        // (exactly three of the eight positions are valid for a given half-pel direction: task index j picks one)
+        for (int t = tid; t < 4 * 64 * 3; t += kSpThreads) {
+            const int j = t % 3, blk = (t / 3) & 63, L = t / 192;
             const int bx = blk & 7, by = blk >> 3;
             uint32_t ssd = 0, sad = 0;
             const int pu = pu_of_block(L, bx, by);
@@ -215,15 +227,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                 const uint32_t mv = sh.pu_imv[pu];
                 const int xm = mv_x(mv), ym = mv_y(mv), dir = sh.pu_dir[pu];
                 const int method = (ym & 2) + ((xm & 2) >> 1);
-                // validity of L R T B TL TR BR BL given the best half-pel direction (ME.c:2859-2881)
-                bool valid;
+                int k = 0, cnt = 0;
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++)
+                    if (quarter_valid(method, dir, kk)) { if (cnt == j) k = kk; cnt++; }
                 {
-                    // neighbours (in the 8-cycle TL,T,TR,R,BR,B,BL,L) of each quarter position
-                    const int q8 = k == 0 ? D_L : k == 1 ? D_R : k == 2 ? D_T : k == 3 ? D_B : k == 4 ? D_TL : k == 5 ? D_TR : k == 6 ? D_BR : D_BL;
-                    const int centre = method ? ((q8 + 4) & 7) : q8;
-                    valid = dir == centre || dir == ((centre + 1) & 7) || dir == ((centre + 7) & 7);
-                }
-                if (valid) {
                     const int8_t* q = kQuarter[method][k];
                     const int X = kMargin + ((xm + 2) >> 2) - sax + bx * 8, Y = kMargin + ((ym + 2) >> 2) - say + by * 8;
                     const uint32_t* p1 = sh.plane[q[0]]; const uint32_t* p2 = sh.plane[q[3]];
@@ -235,22 +243,19 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                         ssd = true_ssd4(s0, a0, ssd); ssd = true_ssd4(s1, a1, ssd);
                         sad = sad4(s0, a0, sad); sad = sad4(s1, a1, sad);
                     }
-                } else ssd = 0xFFFFFFFFu;                                   // marks "not evaluated"
+                    atomicAdd(&sh.sum_ssd[k][pu], ssd); atomicAdd(&sh.sum_sad[k][pu], sad);
+                }
             }
-            sh.ssd_part[L][k][blk] = ssd; sh.sad_part[L][k][blk] = sad;
         }
         __syncthreads();
         if (tid < kNumPu && (tid < 21 || p.cu8x8_mode != 1)) {
-            int L, bx, by, nb; pu_blocks(tid, L, bx, by, nb);
-            if (L == 0) nb = 4;
             const uint32_t imv = sh.pu_imv[tid];
+            const int method = (mv_y(imv) & 2) + ((mv_x(imv) & 2) >> 1), dir = sh.pu_dir[tid];
             uint32_t bssd = sh.pu_ssd[tid], bsad = sh.pu_sad[tid], bmv = imv;
+#pragma unroll
             for (int k = 0; k < 8; k++) {
-                if (sh.ssd_part[L][k][by * 8 + bx] == 0xFFFFFFFFu) continue;
-                uint32_t a = 0, b = 0;
-                for (int yy = 0; yy < nb; yy++) for (int xx = 0; xx < nb; xx++) {
-                    a += sh.ssd_part[L][k][(by + yy) * 8 + bx + xx]; b += sh.sad_part[L][k][(by + yy) * 8 + bx + xx];
-                }
+                if (!quarter_valid(method, dir, k)) continue;
+                const uint32_t a = sh.sum_ssd[k][tid], b = sh.sum_sad[k][tid];
                 if (a < bssd) { bssd = a; bsad = b; bmv = make_mv((int16_t)(mv_x(imv) + kQmv[k][0]), (int16_t)(mv_y(imv) + kQmv[k][1])); }
             }
             sh.pu_sad[tid] = bsad; sh.pu_mv[tid] = bmv;
