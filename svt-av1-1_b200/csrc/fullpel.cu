@@ -27,11 +27,17 @@ constexpr int kWinRows = 126;          // 64 search rows + 62
 constexpr int kWinPitch = 36;          // words; = 4 (mod 32) keeps the 8 row-distinct LDS.128 of a warp conflict-free
 constexpr int kFpSmemBytes = (4 * kWinRows * kWinPitch + 32 * 16 + 96) * 4;
 
-// Warp-wide min of a key, then one shared-memory RED.MIN from lane 0 (predicated, no branch).
-__device__ __forceinline__ void key_min(uint32_t slot_addr, uint32_t key, uint32_t is_lane0) {
-    const uint32_t m = __reduce_min_sync(0xffffffffu, key);
-    asm volatile("{ .reg .pred p; setp.ne.u32 p, %2, 0; @p red.shared.min.u32 [%0], %1; }"
-                 :: "r"(slot_addr), "r"(m), "r"(is_lane0) : "memory");
+// One step of a streaming transpose-reduction: two keys a, b live in every lane; afterwards lanes whose `bit` is
+// clear hold min(a) over {lane, lane ^ bit} and lanes whose bit is set hold the same for b. Five such steps
+// (bits 16, 8, 4, 2, 1) turn 32 keys x 32 lanes into one fully reduced key per lane at 4 instructions per key
+// (2 SEL + SHFL + VIMNMX), after which every lane issues one RED.MIN to its own PU slot: no per-key CREDUX,
+// leader election or branch.
+__device__ __forceinline__ uint32_t pair_min(uint32_t a, uint32_t b, int bit, bool hi) {
+    const uint32_t keep = hi ? b : a, send = hi ? a : b;
+    return min(keep, __shfl_xor_sync(0xffffffffu, send, bit));
+}
+__device__ __forceinline__ void red_min(uint32_t slot_addr, uint32_t key) {
+    asm volatile("red.shared.min.u32 [%0], %1;" :: "r"(slot_addr), "r"(key) : "memory");
 }
 
 __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __restrict__ jobs, int list) {
@@ -73,7 +79,14 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const int total = tiles_g + tiles_s;
     const int s = tid & 3;
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
-    const uint32_t is_lane0 = (tid & 31) == 0 ? 1u : 0u;
+    const int lane = tid & 31;
+    const bool l16 = lane & 16, l8 = lane & 8, l4 = lane & 4, l2 = lane & 2, l1 = lane & 1;
+    // PU slot owned by this lane after the transpose-reductions (key index = bit-reversed lane):
+    //   8x8  : column block j = (l16, l8, l4), block row within the half = (l2, l1); internal index = Morton(j, row)
+    //   16x16: q = (l16, l8), row = (l4, l2);   32x32: q = l16, half = l8
+    const uint32_t addr8 = keys_addr + 4u * (21u + (l16 ? 1u : 0u) + (l8 ? 4u : 0u) + (l4 ? 16u : 0u) + (l2 ? 2u : 0u) + (l1 ? 8u : 0u));
+    const uint32_t addr16 = keys_addr + 4u * (5u + (l16 ? 1u : 0u) + (l8 ? 4u : 0u) + (l4 ? 2u : 0u) + (l2 ? 8u : 0u));
+    const uint32_t addr32 = keys_addr + 4u * (1u + (l16 ? 1u : 0u) + (l8 ? 2u : 0u));
 
     for (int u0 = 0; u0 < total; u0 += kFpThreads) {
         const int u = u0 + tid;
@@ -100,7 +113,9 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
         uint32_t h16[4][4], s32[4][2], s64[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) { s64[k] = 0; s32[k][0] = s32[k][1] = 0; }
-#pragma unroll 1
+        // carries of the streaming transpose-reductions (see pair_min)
+        uint32_t t3e = 0, t4a = 0, u2a = 0, u3a = 0, v32a = 0;
+#pragma unroll
         for (int b = 0; b < 8; b++) {
             uint32_t acc[4][8];
 #pragma unroll
@@ -132,12 +147,22 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                     }
                 }
             }
-            // ---- 8x8 PUs of block-row b
+            // ---- 8x8 PUs of block-row b: per-thread min over its 4 positions, then the transpose-reduction
+            {
+                uint32_t k8[8];
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const uint32_t key = min(min(acc[0][j] * kmul[0] + kadd[0], acc[1][j] * kmul[1] + kadd[1]),
-                                         min(acc[2][j] * kmul[2] + kadd[2], acc[3][j] * kmul[3] + kadd[3]));
-                key_min(keys_addr + 4u * (21 + kTab8[b * 8 + j]), key, is_lane0);
+                for (int j = 0; j < 8; j++)
+                    k8[j] = min(min(acc[0][j] * kmul[0] + kadd[0], acc[1][j] * kmul[1] + kadd[1]),
+                                min(acc[2][j] * kmul[2] + kadd[2], acc[3][j] * kmul[3] + kadd[3]));
+                const uint32_t a0 = pair_min(k8[0], k8[1], 16, l16), a1 = pair_min(k8[2], k8[3], 16, l16);
+                const uint32_t a2 = pair_min(k8[4], k8[5], 16, l16), a3 = pair_min(k8[6], k8[7], 16, l16);
+                const uint32_t t3 = pair_min(pair_min(a0, a1, 8, l8), pair_min(a2, a3, 8, l8), 4, l4);
+                if ((b & 1) == 0) t3e = t3;
+                else {
+                    const uint32_t t4 = pair_min(t3e, t3, 2, l2);
+                    if ((b & 3) == 1) t4a = t4;
+                    else red_min(addr8 + (b >> 2) * (4u * 32u), pair_min(t4a, t4, 1, l1));    // lane holds one (band, column) PU
+                }
             }
             // ---- 16x16: sum of two block-rows
             if ((b & 1) == 0) {
@@ -154,44 +179,69 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                     h16[k][q] += acc[k][2 * q] + acc[k][2 * q + 1];
                     s32[k][q >> 1] += h16[k][q];
                 }
+            {
+                uint32_t c16[4];
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const uint32_t key = min(min(h16[0][q] * kmul[0] + kadd[0], h16[1][q] * kmul[1] + kadd[1]),
-                                         min(h16[2][q] * kmul[2] + kadd[2], h16[3][q] * kmul[3] + kadd[3]));
-                key_min(keys_addr + 4u * (5 + kTab16[(b >> 1) * 4 + q]), key, is_lane0);
+                for (int q = 0; q < 4; q++)
+                    c16[q] = min(min(h16[0][q] * kmul[0] + kadd[0], h16[1][q] * kmul[1] + kadd[1]),
+                                 min(h16[2][q] * kmul[2] + kadd[2], h16[3][q] * kmul[3] + kadd[3]));
+                const uint32_t u2 = pair_min(pair_min(c16[0], c16[1], 16, l16), pair_min(c16[2], c16[3], 16, l16), 8, l8);
+                if ((b & 3) == 1) u2a = u2;
+                else {
+                    const uint32_t u3 = pair_min(u2a, u2, 4, l4);
+                    if (b == 3) u3a = u3;
+                    else {
+                        uint32_t u4 = pair_min(u3a, u3, 2, l2);
+                        u4 = min(u4, __shfl_xor_sync(0xffffffffu, u4, 1));
+                        if (!l1) red_min(addr16, u4);
+                    }
+                }
             }
             if ((b & 3) != 3) continue;
             // ---- 32x32: two PUs of this half of the SB
+            {
+                uint32_t k32[2];
 #pragma unroll
-            for (int q = 0; q < 2; q++) {
-                uint32_t key = 0xFFFFFFFFu;
-                // quirk Q4: per 8-position group, first-min of positions 0..3 ("lo") and of 4..7 ("hi");
-                // lo wins only if strictly smaller and is then reported 4 to the right, hi 4 to the left.
-                // (shuffles are executed by every lane; single-position tiles ignore the outcome)
+                for (int q = 0; q < 2; q++) {
+                    uint32_t key = 0xFFFFFFFFu;
+                    // quirk Q4: per 8-position group, first-min of positions 0..3 ("lo") and of 4..7 ("hi");
+                    // lo wins only if strictly smaller and is then reported 4 to the right, hi 4 to the left.
+                    // (shuffles are executed by every lane; single-position tiles ignore the outcome)
 #pragma unroll
-                for (int g2 = 0; g2 < 2; g2++) {
-                    uint32_t lo = (s32[2 * g2][q] << 2) | (uint32_t)s, hi = (s32[2 * g2 + 1][q] << 2) | (uint32_t)s;
-                    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 1)); lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 2));
-                    hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 1)); hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 2));
-                    const uint32_t lv = lo >> 2, hv = hi >> 2;
-                    const uint32_t v = (hv > lv) ? lv : hv;
-                    const uint32_t idx = (hv > lv) ? (lo & 3u) + 4u : (hi & 3u);
-                    if (!single && val[2 * g2]) key = min(key, (v << 13) | ((uint32_t)y << 7) | ((uint32_t)(2 * G + g2) << 3) | idx);
+                    for (int g2 = 0; g2 < 2; g2++) {
+                        uint32_t lo = (s32[2 * g2][q] << 2) | (uint32_t)s, hi = (s32[2 * g2 + 1][q] << 2) | (uint32_t)s;
+                        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 1)); lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 2));
+                        hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 1)); hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 2));
+                        const uint32_t lv = lo >> 2, hv = hi >> 2;
+                        const uint32_t v = (hv > lv) ? lv : hv;
+                        const uint32_t idx = (hv > lv) ? (lo & 3u) + 4u : (hi & 3u);
+                        if (!single && val[2 * g2]) key = min(key, (v << 13) | ((uint32_t)y << 7) | ((uint32_t)(2 * G + g2) << 3) | idx);
+                    }
+                    if (single) {
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            if (val[k]) key = min(key, (s32[k][q] << 13) | ((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3));
+                    }
+                    k32[q] = key;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) { s64[k] += s32[k][q]; s32[k][q] = 0; }
                 }
-                if (single) {
-#pragma unroll
-                    for (int k = 0; k < 4; k++)
-                        if (val[k]) key = min(key, (s32[k][q] << 13) | ((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3));
+                const uint32_t v32 = pair_min(k32[0], k32[1], 16, l16);
+                if (b == 3) v32a = v32;
+                else {
+                    uint32_t w = pair_min(v32a, v32, 8, l8);
+                    w = min(w, __shfl_xor_sync(0xffffffffu, w, 4));
+                    w = min(w, __shfl_xor_sync(0xffffffffu, w, 2));
+                    w = min(w, __shfl_xor_sync(0xffffffffu, w, 1));
+                    if ((lane & 7) == 0) red_min(addr32, w);
                 }
-                key_min(keys_addr + 4u * (1 + (b >> 2) * 2 + q), key, is_lane0);
-#pragma unroll
-                for (int k = 0; k < 4; k++) { s64[k] += s32[k][q]; s32[k][q] = 0; }
             }
             if (b != 7) continue;
             {
                 const uint32_t key = min(min(s64[0] * kmul[0] + kadd[0], s64[1] * kmul[1] + kadd[1]),
                                          min(s64[2] * kmul[2] + kadd[2], s64[3] * kmul[3] + kadd[3]));
-                key_min(keys_addr, key, is_lane0);
+                const uint32_t m = __reduce_min_sync(0xffffffffu, key);
+                if (lane == 0) red_min(keys_addr, m);
             }
         }
     }
