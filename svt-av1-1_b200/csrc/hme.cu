@@ -17,11 +17,12 @@ namespace svtme {
 
 constexpr int kHmeThreads = 256;
 constexpr int kGroupThreads = 64;
-constexpr int kRegionWinWords = 2560;          // 10 KB window buffer per region group
+constexpr int kRegionWinWords = 2560;
+constexpr int kSrcPitch = 17, kQPitch = 9;      // padded so that lanes on different block rows hit different banks          // 10 KB window buffer per region group
 
 struct HmeShared {
-    uint32_t src_even[32 * 16];     // even rows of the 64x64 source SB
-    uint32_t q_even[16 * 8];        // even rows of the 32x32 quarter SB
+    uint32_t src_even[32 * kSrcPitch];   // even rows of the 64x64 source SB
+    uint32_t q_even[16 * kQPitch];       // even rows of the 32x32 quarter SB
     uint32_t s_even[8 * 4];         // even rows of the 16x16 sixteenth SB
     uint32_t win[4][kRegionWinWords];
     uint32_t best[12];              // [level][region] winning keys
@@ -47,72 +48,123 @@ __device__ uint32_t warp_sb_sad(const uint32_t* src_even, const DPlane& rp, int 
     const int lane = threadIdx.x & 31;
     uint32_t acc = 0;
     if (lane < rows) {
+        // 17 independent aligned loads in flight, then one funnel shift per word (the path is L2-latency bound)
         const uint8_t* r = rp.at(x, y + 2 * lane);
-        for (int c = 0; c < w_words; c++) acc = sad4(src_even[lane * 16 + c], ldg_u32_unaligned(r + 4 * c), acc);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>((uintptr_t)r & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)(uintptr_t)r & 3u) * 8u;
+        uint32_t v[17];
+#pragma unroll
+        for (int c = 0; c < 17; c++) v[c] = (c <= w_words) ? __ldg(w + c) : 0u;
+#pragma unroll
+        for (int c = 0; c < 16; c++)
+            if (c < w_words) acc = sad4(src_even[lane * kSrcPitch + c], __funnelshift_r(v[c], v[c + 1], sh), acc);
     }
     return __reduce_add_sync(0xffffffffu, acc);
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
 // Exhaustive search of one region by one 64-thread group. Returns the winning key
 // (value << VS | row << RS | col) to every thread of the group.
 //   src: even rows of the block, SP words per row;  W words x `rows` rows
 //   (rx, ry): top-left search position in level coordinates; saw x sah positions
-template <int W, int SP, bool QUIRK, int VS, int RS>
+// Thread tile = one of the reference's 8-position SIMD groups (8 consecutive x on one search row): every
+// window word is funnel-shifted to its three other byte phases once (3 SHF) and feeds 8 VABSDIFF4 (4 phases x
+// 2 word offsets), and every lane reads DIFFERENT window words, so a shared-memory wavefront carries 32 useful
+// words (sharing words between lanes made the search wavefront-bound). RSPLIT lanes split the block rows of a
+// tile (interleaved rows, odd window pitch -> conflict-free banks) and add their partial sums with shuffles:
+// level 2 has only 64 positions but 2048 pixels each.
+template <int W, int SP, bool QUIRK, int VS, int RS, int RSPLIT>
 __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id, int gtid, const uint32_t* src, int rows,
                                  const DPlane& rp, int rx, int ry, int saw, int sah) {
-    const int tpr = ((saw + 7) & ~7) >> 2;             // 4-position tiles per search row (whole 8-groups)
-    const int pitch = tpr + W;                          // window words per row
+    const int tpr = (saw + 7) >> 3;                     // 8-position tiles per search row
+    const int pitch = (2 * tpr + W) | 1;                // window words per row (odd)
     const int extra = 2 * (rows - 1);
     const int chunk = max(1, kRegionWinWords / pitch - extra);
+    const int rs = gtid & (RSPLIT - 1);
+    constexpr int kTilesPerPass = kGroupThreads / RSPLIT;
     uint32_t best = 0xFFFFFFFFu;
     if (gtid == 0) *best_slot = 0xFFFFFFFFu;
     for (int i0 = 0; i0 < sah; i0 += chunk) {
         const int i1 = min(sah, i0 + chunk);
         const int wrows = i1 - i0 + extra;
+        const int wcols = 2 * tpr + W;
         group_bar(bar_id);                              // previous users of the window are done
-        for (int t = gtid; t < wrows * pitch; t += kGroupThreads) {
-            const int r = t / pitch, c = t - r * pitch;
-            win[t] = ldg_u32_unaligned(rp.at(rx + 4 * c, ry + i0 + r));
+#pragma unroll 4
+        for (int t = gtid; t < wrows * wcols; t += kGroupThreads) {
+            const int r = t / wcols, c = t - r * wcols;
+            win[r * pitch + c] = ldg_u32_unaligned(rp.at(rx + 4 * c, ry + i0 + r));
         }
         group_bar(bar_id);
         const int ntiles = (i1 - i0) * tpr;
-        for (int t0 = 0; t0 < ntiles; t0 += kGroupThreads) {
-            const int t = t0 + gtid;
+        for (int t0 = 0; t0 < ntiles; t0 += kTilesPerPass) {
+            const int t = t0 + gtid / RSPLIT;
             const bool live = t < ntiles;
             const int i = live ? t / tpr : 0, jt = live ? t - i * tpr : 0;
-            uint32_t lo[4] = { 0, 0, 0, 0 }, hi[4] = { 0, 0, 0, 0 };
-            if (live) {
-                const uint32_t* wr = win + i * pitch + jt;
-                const uint32_t* sr = src;
-                for (int r = 0; r < rows; r++, wr += 2 * pitch, sr += SP) {
-                    uint32_t a = wr[0];
+            uint32_t lo[2][4], hi[2][4];
 #pragma unroll
-                    for (int c = 0; c < W; c++) {
-                        const uint32_t b = wr[c + 1], s = sr[c];
+            for (int k = 0; k < 2; k++)
+#pragma unroll
+                for (int ph = 0; ph < 4; ph++) { lo[k][ph] = 0; hi[k][ph] = 0; }
+            if (live) {
+                const uint32_t* wr = win + (i + 2 * rs) * pitch + 2 * jt;
+                const uint32_t* sr = src + rs * SP;
+                for (int r = rs; r < rows; r += RSPLIT, wr += 2 * RSPLIT * pitch, sr += RSPLIT * SP) {
+                    uint32_t a = wr[0], sprev = 0;
+#pragma unroll
+                    for (int c = 0; c <= W; c++) {
+                        const uint32_t b = wr[c + 1];
                         const uint32_t v1 = __funnelshift_r(a, b, 8), v2 = __funnelshift_r(a, b, 16), v3 = __funnelshift_r(a, b, 24);
-                        if (QUIRK && c >= 4) {
-                            hi[0] = sad4(s, a, hi[0]); hi[1] = sad4(s, v1, hi[1]); hi[2] = sad4(s, v2, hi[2]); hi[3] = sad4(s, v3, hi[3]);
+                        if (c < W) {                    // positions 8jt + phase: source word c
+                            const uint32_t sw = sr[c];
+                            if (QUIRK && c >= 4) { hi[0][0] = sad4(sw, a, hi[0][0]); hi[0][1] = sad4(sw, v1, hi[0][1]); hi[0][2] = sad4(sw, v2, hi[0][2]); hi[0][3] = sad4(sw, v3, hi[0][3]); }
+                            else                 { lo[0][0] = sad4(sw, a, lo[0][0]); lo[0][1] = sad4(sw, v1, lo[0][1]); lo[0][2] = sad4(sw, v2, lo[0][2]); lo[0][3] = sad4(sw, v3, lo[0][3]); }
+                            if (c >= 1) {               // positions 8jt + 4 + phase: source word c - 1
+                                if (QUIRK && c - 1 >= 4) { hi[1][0] = sad4(sprev, a, hi[1][0]); hi[1][1] = sad4(sprev, v1, hi[1][1]); hi[1][2] = sad4(sprev, v2, hi[1][2]); hi[1][3] = sad4(sprev, v3, hi[1][3]); }
+                                else                     { lo[1][0] = sad4(sprev, a, lo[1][0]); lo[1][1] = sad4(sprev, v1, lo[1][1]); lo[1][2] = sad4(sprev, v2, lo[1][2]); lo[1][3] = sad4(sprev, v3, lo[1][3]); }
+                            }
+                            sprev = sw;
                         } else {
-                            lo[0] = sad4(s, a, lo[0]); lo[1] = sad4(s, v1, lo[1]); lo[2] = sad4(s, v2, lo[2]); lo[3] = sad4(s, v3, lo[3]);
+                            if (QUIRK && W - 1 >= 4) { hi[1][0] = sad4(sprev, a, hi[1][0]); hi[1][1] = sad4(sprev, v1, hi[1][1]); hi[1][2] = sad4(sprev, v2, hi[1][2]); hi[1][3] = sad4(sprev, v3, hi[1][3]); }
+                            else                     { lo[1][0] = sad4(sprev, a, lo[1][0]); lo[1][1] = sad4(sprev, v1, lo[1][1]); lo[1][2] = sad4(sprev, v2, lo[1][2]); lo[1][3] = sad4(sprev, v3, lo[1][3]); }
                         }
                         a = b;
                     }
                 }
             }
-            uint32_t mlo = 0;
-            if (QUIRK) {                               // quirk Q3: min of the low halves over the 8-position group
-                mlo = 65535u;
+            if (RSPLIT > 1) {
 #pragma unroll
-                for (int k = 0; k < 4; k++) mlo = min(mlo, (live && 4 * jt + k < saw) ? lo[k] : 65535u);
-                mlo = min(mlo, __shfl_xor_sync(0xffffffffu, mlo, 1));
+                for (int o = 1; o < RSPLIT; o <<= 1)
+#pragma unroll
+                    for (int k = 0; k < 2; k++)
+#pragma unroll
+                        for (int ph = 0; ph < 4; ph++) {
+                            lo[k][ph] += __shfl_xor_sync(0xffffffffu, lo[k][ph], o);
+                            if (QUIRK) hi[k][ph] += __shfl_xor_sync(0xffffffffu, hi[k][ph], o);
+                        }
             }
             if (live) {
+                uint32_t mlo = 65535u;                   // quirk Q3: min of the low halves over the 8-position group
+                if (QUIRK) {
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    const uint32_t val = QUIRK ? min(lo[k] + hi[k], 65535u + mlo) : lo[k];
-                    const uint32_t key = (val << VS) | ((uint32_t)(i0 + i) << RS) | (uint32_t)(4 * jt + k);
-                    if (4 * jt + k < saw) best = min(best, key);
+                    for (int k = 0; k < 2; k++)
+#pragma unroll
+                        for (int ph = 0; ph < 4; ph++) mlo = min(mlo, (8 * jt + 4 * k + ph < saw) ? lo[k][ph] : 65535u);
                 }
+#pragma unroll
+                for (int k = 0; k < 2; k++)
+#pragma unroll
+                    for (int ph = 0; ph < 4; ph++) {
+                        const int x = 8 * jt + 4 * k + ph;
+                        const uint32_t val = QUIRK ? min(lo[k][ph] + hi[k][ph], 65535u + mlo) : lo[k][ph];
+                        const uint32_t key = (val << VS) | ((uint32_t)(i0 + i) << RS) | (uint32_t)x;
+                        if (x < saw) best = min(best, key);
+                    }
             }
         }
     }
@@ -124,7 +176,7 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
 
 __device__ __forceinline__ int round_sa_width(int w) { return (w < 8) ? 8 : (w & 7) ? w + (w - ((w >> 3) << 3)) : w; }
 
-__global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict__ jobs, int list) {
+__global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restrict__ jobs, int list) {
     __shared__ HmeShared sh;
     const DJob& job = jobs[blockIdx.y];
     const int sb = blockIdx.x;
@@ -139,9 +191,9 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
 
     // ---- stage the source SB (even rows only: every SAD on this path is row-subsampled)
     for (int t = tid; t < 32 * 16; t += kHmeThreads)
-        sh.src_even[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
+        sh.src_even[(t >> 4) * kSrcPitch + (t & 15)] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
     if (tid < 16 * 8)
-        sh.q_even[tid] = *reinterpret_cast<const uint32_t*>(job.cur.quarter.at((ox >> 1) + 4 * (tid & 7), (oy >> 1) + 2 * (tid >> 3)));
+        sh.q_even[(tid >> 3) * kQPitch + (tid & 7)] = *reinterpret_cast<const uint32_t*>(job.cur.quarter.at((ox >> 1) + 4 * (tid & 7), (oy >> 1) + 2 * (tid >> 3)));
     if (tid < 8 * 4)
         sh.s_even[tid] = *reinterpret_cast<const uint32_t*>(job.cur.sixteenth.at((ox >> 2) + 4 * (tid & 3), (oy >> 2) + 2 * (tid >> 2)));
     __syncthreads();
@@ -205,8 +257,8 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
                     clip_search_area(ox >> 2, sax, saw, rp.ox - 1, rp.w);
                     clip_search_area(oy >> 2, say, sah, rp.oy - 1, rp.h);
                     const uint32_t k = half
-                        ? group_search<2, 4, false, 17, 9>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah)
-                        : group_search<4, 4, false, 17, 9>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah);
+                        ? group_search<2, 4, false, 17, 9, 1>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah)
+                        : group_search<4, 4, false, 17, 9, 1>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah);
                     if (gtid == 0) {
                         sh.sad[0][w][h] = (k >> 17) * 2;
                         sh.x[0][w][h] = (int16_t)(((int)(k & 511) + sax) * 4);
@@ -221,8 +273,8 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
                     clip_search_area(ox >> 1, sax, saw, rp.ox - 1, rp.w);
                     clip_search_area(oy >> 1, say, sah, rp.oy - 1, rp.h);
                     const uint32_t k = half
-                        ? group_search<4, 8, false, 13, 7>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah)
-                        : group_search<8, 8, true, 13, 7>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah);
+                        ? group_search<4, kQPitch, false, 13, 7, 2>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah)
+                        : group_search<8, kQPitch, true, 13, 7, 2>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah);
                     if (gtid == 0) {
                         sh.sad[1][w][h] = (k >> 13) * 2;
                         sh.x[1][w][h] = (int16_t)(((int)(k & 127) + sax) * 2);
@@ -237,8 +289,8 @@ __global__ void __launch_bounds__(kHmeThreads) hme_kernel(const DJob* __restrict
                     clip_search_area(ox, sax, saw, 63, rp.w);
                     clip_search_area(oy, say, sah, 63, rp.h);
                     const uint32_t k = half
-                        ? group_search<8, 16, false, 13, 7>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah)
-                        : group_search<16, 16, false, 13, 7>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah);
+                        ? group_search<8, kSrcPitch, false, 13, 7, 8>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah)
+                        : group_search<16, kSrcPitch, false, 13, 7, 8>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah);
                     if (gtid == 0) {
                         sh.sad[2][w][h] = (k >> 13) * 2;
                         sh.x[2][w][h] = (int16_t)((int)(k & 127) + sax);
