@@ -106,7 +106,8 @@ void    svtme_destroy(SvtMeContext *ctx);
 const char *svtme_last_error(const SvtMeContext *ctx);
 
 /* Upload one 8-bit luma plane (host memory, 'stride' bytes per row) into a slot and build its padded
- * full / quarter / sixteenth planes on the device. Asynchronous on the context stream. */
+ * full / quarter / sixteenth planes on the device. Asynchronous, on the context's upload stream; a slot is
+ * rewritten only after the batches that read its previous picture have finished. */
 int32_t svtme_picture_upload(SvtMeContext *ctx, int32_t slot, const uint8_t *luma, int32_t stride);
 /* Same, from a luma plane that already lives in device memory (no H2D copy). */
 int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8_t *d_luma, int32_t stride);
@@ -115,14 +116,20 @@ int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8
 int32_t svtme_picture_download(SvtMeContext *ctx, int32_t slot, int32_t level, uint8_t *dst, size_t dst_bytes,
                                int32_t *out_stride, int32_t *out_rows, int32_t *out_pad);
 
-/* Motion-estimate a batch of pictures (n_jobs <= SVTME_MAX_BATCH). Kernels are enqueued on the
- * context stream; results/debug are copied to the host buffers of each job and the call returns
- * when they are there. */
+/* Motion-estimate a batch of pictures (n_jobs <= SVTME_MAX_BATCH): kernels run on the compute stream
+ * once the pictures they read are uploaded; results/debug are copied to the host buffers of each job
+ * and the call returns when they are there. */
 int32_t svtme_motion_estimate(SvtMeContext *ctx, const SvtMeJob *jobs, int32_t n_jobs);
-/* Enqueue only (results stay in HBM); svtme_fetch_results copies them out later. */
+/* Enqueue only: searches on the compute stream, then the copies into job.results / job.debug (when not
+ * NULL; with NULL the results stay in HBM) on the result stream. Up to three batches are in flight, so
+ * uploads, searches and result copies of consecutive batches overlap. svtme_fetch_results waits until the
+ * results of every batch submitted so far are in the callers' buffers; svtme_synchronize waits for
+ * everything, uploads included. */
 int32_t svtme_motion_estimate_async(SvtMeContext *ctx, const SvtMeJob *jobs, int32_t n_jobs);
 int32_t svtme_fetch_results(SvtMeContext *ctx, const SvtMeJob *jobs, int32_t n_jobs);
 int32_t svtme_synchronize(SvtMeContext *ctx);
+/* Make the compute stream wait for all transfers enqueued so far (for timing with events on svtme_stream). */
+int32_t svtme_join(SvtMeContext *ctx);
 
 /* Introspection for benchmarks: the CUDA stream (cudaStream_t as void*) and the number of kernel
  * launches issued so far. */

@@ -11,7 +11,7 @@ EXPORTED_SYMBOLS = (
     "svtme_default_params", "svtme_create", "svtme_destroy", "svtme_last_error", "svtme_picture_upload",
     "svtme_picture_upload_device", "svtme_picture_download", "svtme_motion_estimate",
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
-    "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times",
+    "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join",
 )
 KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
 
@@ -83,6 +83,8 @@ def load_library():
         f.argtypes = [C.c_void_p, C.POINTER(SvtMeJob), C.c_int32]
     lib.svtme_synchronize.restype = C.c_int32
     lib.svtme_synchronize.argtypes = [C.c_void_p]
+    lib.svtme_join.restype = C.c_int32
+    lib.svtme_join.argtypes = [C.c_void_p]
     lib.svtme_stream.restype = C.c_void_p
     lib.svtme_stream.argtypes = [C.c_void_p]
     lib.svtme_kernel_launches.restype = C.c_int64
@@ -181,6 +183,9 @@ class MeContext:
 
     def synchronize(self):
         self._check(self.lib.svtme_synchronize(self._h), "svtme_synchronize")
+
+    def join(self):
+        self._check(self.lib.svtme_join(self._h), "svtme_join")
 
     @property
     def stream(self):

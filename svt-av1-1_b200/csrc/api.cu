@@ -1,5 +1,12 @@
 // api.cu -- the C-ABI of libsvtme_cuda.so (include/svtme.h): context, picture slots, batched ME.
 // Host side only; every kernel lives in its own translation unit and is reached through launch_*().
+//
+// Three streams per context so that transfers overlap the searches:
+//   copy_in  : H2D of uploaded luma planes + pyramid_kernel; records Slot::ready
+//   stream   : the ME kernels of each batch (waits on the ready events of the pictures it reads)
+//   copy_out : D2H of a batch's results into the caller's buffers (waits on Batch::computed)
+// Batches rotate through a small ring of job tables / scratch / result buffers, so a new batch can be
+// enqueued while the previous one computes and the one before that drains.
 #include "me_common.cuh"
 #include <cstdio>
 #include <cstring>
@@ -13,27 +20,41 @@ cudaError_t configure_fullpel();
 cudaError_t configure_subpel();
 }
 
+constexpr int kRing = 3;
+
+struct Batch {
+    int cap = 0;                          // pictures this entry can hold
+    SbScratch* d_scratch = nullptr;       // [cap][n_sb]
+    SvtMePuResult* d_results = nullptr;   // [cap][n_sb][85]
+    SvtMeSbDebug* d_debug = nullptr;      // [cap][n_sb]
+    DJob* d_jobs = nullptr;               // [cap]
+    DJob* h_jobs = nullptr;               // pinned
+    cudaEvent_t computed = nullptr;       // kernels of the last batch that used this entry are done
+    cudaEvent_t drained = nullptr;        // ... and its results have reached the host
+    bool used = false;
+};
+
 struct Slot {
     uint8_t* base = nullptr;      // one allocation: luma staging + three padded planes
     uint8_t* luma = nullptr;      // unpadded luma as uploaded (pitch = width)
     DPyramid pyr;
     size_t plane_bytes[3] = { 0, 0, 0 };
+    cudaEvent_t ready = nullptr;  // pyramid of the last upload is complete
+    int last_reader = -1;         // ring entry of the last batch that reads this slot ...
+    int64_t last_reader_seq = -1; // ... and that batch's sequence number
 };
 
 struct SvtMeContext {
     int device = 0, width = 0, height = 0, sb_cols = 0, sb_rows = 0, n_sb = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t join_ev = nullptr;
     std::vector<Slot> slots;
-    // batch state
-    int batch_cap = 0;
-    SbScratch* d_scratch = nullptr;       // [batch_cap][n_sb]
-    SvtMePuResult* d_results = nullptr;   // [batch_cap][n_sb][85]
-    SvtMeSbDebug* d_debug = nullptr;      // [batch_cap][n_sb]
-    DJob* d_jobs = nullptr;               // [batch_cap]
-    DJob* h_jobs = nullptr;               // pinned
+    Batch ring[kRing];
+    int next = 0, last = -1;              // ring entry for the next batch / of the latest batch
+    int64_t seq = 0;                      // batches submitted so far
     int64_t launches = 0;
     std::string err;
-    // optional per-kernel timing (CUDA events on the context stream)
+    // optional per-kernel timing (CUDA events on the launching stream)
     bool profiling = false;
     struct Timed { int kind; cudaEvent_t a, b; };
     std::vector<Timed> timed;
@@ -44,19 +65,19 @@ struct SvtMeContext {
 
 // Brackets one kernel launch with events when profiling is on.
 struct LaunchTimer {
-    SvtMeContext* c; int kind; cudaEvent_t a = nullptr, b = nullptr;
+    SvtMeContext* c; int kind; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
     static cudaEvent_t get(SvtMeContext* c) {
         cudaEvent_t e = nullptr;
         if (!c->event_pool.empty()) { e = c->event_pool.back(); c->event_pool.pop_back(); }
         else cudaEventCreate(&e);
         return e;
     }
-    LaunchTimer(SvtMeContext* ctx, int k) : c(ctx), kind(k) {
+    LaunchTimer(SvtMeContext* ctx, int k, cudaStream_t s) : c(ctx), kind(k), st(s) {
         c->launches++; c->kind_launches[k]++;
-        if (c->profiling) { a = get(c); b = get(c); cudaEventRecord(a, c->stream); }
+        if (c->profiling) { a = get(c); b = get(c); cudaEventRecord(a, st); }
     }
     ~LaunchTimer() {
-        if (a) { cudaEventRecord(b, c->stream); c->timed.push_back({ kind, a, b }); }
+        if (a) { cudaEventRecord(b, st); c->timed.push_back({ kind, a, b }); }
     }
 };
 
@@ -128,6 +149,13 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     *out = ctx;                                              // handed out even on failure so the error text is readable
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming));
+    for (auto& b : ctx->ring) {
+        CU(cudaEventCreateWithFlags(&b.computed, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&b.drained, cudaEventDisableTiming));
+    }
     CU(configure_fullpel());
     CU(configure_subpel());
     ctx->slots.resize(num_slots);
@@ -142,22 +170,35 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
         describe_plane(s.pyr.full, m, width, height, kPadFull); m += s.plane_bytes[0];
         describe_plane(s.pyr.quarter, m, width >> 1, height >> 1, kPadQuarter); m += s.plane_bytes[1];
         describe_plane(s.pyr.sixteenth, m, width >> 2, height >> 2, kPadSixteenth);
-        CU(cudaMemsetAsync(s.base, 0, luma_bytes + s.plane_bytes[0] + s.plane_bytes[1] + s.plane_bytes[2], ctx->stream));
+        CU(cudaMemsetAsync(s.base, 0, luma_bytes + s.plane_bytes[0] + s.plane_bytes[1] + s.plane_bytes[2], ctx->copy_in));
+        CU(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+        CU(cudaEventRecord(s.ready, ctx->copy_in));
     }
-    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->copy_in));
     return SVTME_OK;
+}
+
+static void free_batch(Batch& b) {
+    cudaFree(b.d_scratch); cudaFree(b.d_results); cudaFree(b.d_debug); cudaFree(b.d_jobs);
+    if (b.h_jobs) cudaFreeHost(b.h_jobs);
+    b.d_scratch = nullptr; b.d_results = nullptr; b.d_debug = nullptr; b.d_jobs = nullptr; b.h_jobs = nullptr;
+    b.cap = 0;
 }
 
 void svtme_destroy(SvtMeContext* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (cudaStream_t st : { ctx->copy_in, ctx->stream, ctx->copy_out }) if (st) cudaStreamSynchronize(st);
     for (auto& t : ctx->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
-    for (auto& s : ctx->slots) cudaFree(s.base);
-    cudaFree(ctx->d_scratch); cudaFree(ctx->d_results); cudaFree(ctx->d_debug); cudaFree(ctx->d_jobs);
-    if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); }
+    for (auto& b : ctx->ring) {
+        free_batch(b);
+        if (b.computed) cudaEventDestroy(b.computed);
+        if (b.drained) cudaEventDestroy(b.drained);
+    }
+    if (ctx->join_ev) cudaEventDestroy(ctx->join_ev);
+    for (cudaStream_t st : { ctx->copy_in, ctx->stream, ctx->copy_out }) if (st) cudaStreamDestroy(st);
     delete ctx;
 }
 
@@ -165,13 +206,27 @@ const char* svtme_last_error(const SvtMeContext* ctx) { return ctx ? ctx->err.c_
 void* svtme_stream(SvtMeContext* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 int64_t svtme_kernel_launches(const SvtMeContext* ctx) { return ctx ? ctx->launches : 0; }
 
+// A slot may be rewritten only after the last batch that reads it has finished its kernels.
+static int32_t guard_slot_rewrite(SvtMeContext* ctx, Slot& s) {
+    if (s.last_reader >= 0) CU(cudaStreamWaitEvent(ctx->copy_in, ctx->ring[s.last_reader].computed, 0));
+    return SVTME_OK;
+}
+
+static int32_t build_pyramid(SvtMeContext* ctx, Slot& s, const uint8_t* d_luma, int32_t stride) {
+    { LaunchTimer t(ctx, SVTME_KERNEL_PYRAMID, ctx->copy_in); launch_pyramid(d_luma, stride, s.pyr, ctx->copy_in); }
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s.ready, ctx->copy_in));
+    return SVTME_OK;
+}
+
 int32_t svtme_picture_upload_device(SvtMeContext* ctx, int32_t slot, const uint8_t* d_luma, int32_t stride) {
     if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || !d_luma || stride < ctx->width)
         return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_device: bad argument");
     CU(cudaSetDevice(ctx->device));
-    { LaunchTimer t(ctx, SVTME_KERNEL_PYRAMID); launch_pyramid(d_luma, stride, ctx->slots[slot].pyr, ctx->stream); }
-    CU(cudaGetLastError());
-    return SVTME_OK;
+    Slot& s = ctx->slots[slot];
+    int32_t rc = guard_slot_rewrite(ctx, s);
+    if (rc != SVTME_OK) return rc;
+    return build_pyramid(ctx, s, d_luma, stride);
 }
 
 int32_t svtme_picture_upload(SvtMeContext* ctx, int32_t slot, const uint8_t* luma, int32_t stride) {
@@ -179,8 +234,10 @@ int32_t svtme_picture_upload(SvtMeContext* ctx, int32_t slot, const uint8_t* lum
         return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload: bad argument");
     CU(cudaSetDevice(ctx->device));
     Slot& s = ctx->slots[slot];
-    CU(cudaMemcpy2DAsync(s.luma, ctx->width, luma, stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->stream));
-    return svtme_picture_upload_device(ctx, slot, s.luma, ctx->width);
+    int32_t rc = guard_slot_rewrite(ctx, s);
+    if (rc != SVTME_OK) return rc;
+    CU(cudaMemcpy2DAsync(s.luma, ctx->width, luma, stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
+    return build_pyramid(ctx, s, s.luma, ctx->width);
 }
 
 int32_t svtme_picture_download(SvtMeContext* ctx, int32_t slot, int32_t level, uint8_t* dst, size_t dst_bytes,
@@ -191,27 +248,24 @@ int32_t svtme_picture_download(SvtMeContext* ctx, int32_t slot, int32_t level, u
     const int w = pl.w + 2 * pl.ox, rows = pl.h + 2 * pl.oy;
     if (dst_bytes < (size_t)w * rows) return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_download: buffer too small");
     CU(cudaSetDevice(ctx->device));
-    CU(cudaMemcpy2DAsync(dst, w, pl.buf, pl.stride, w, rows, cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaMemcpy2DAsync(dst, w, pl.buf, pl.stride, w, rows, cudaMemcpyDeviceToHost, ctx->copy_in));
+    CU(cudaStreamSynchronize(ctx->copy_in));
     if (out_stride) *out_stride = w;
     if (out_rows) *out_rows = rows;
     if (out_pad) *out_pad = pl.ox;
     return SVTME_OK;
 }
 
-static int32_t ensure_batch(SvtMeContext* ctx, int n) {
-    if (n <= ctx->batch_cap) return SVTME_OK;
-    CU(cudaStreamSynchronize(ctx->stream));
-    cudaFree(ctx->d_scratch); cudaFree(ctx->d_results); cudaFree(ctx->d_debug); cudaFree(ctx->d_jobs);
-    if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
-    ctx->d_scratch = nullptr; ctx->d_results = nullptr; ctx->d_debug = nullptr; ctx->d_jobs = nullptr; ctx->h_jobs = nullptr;
-    ctx->batch_cap = 0;
-    CU(cudaMalloc(&ctx->d_scratch, sizeof(SbScratch) * (size_t)n * ctx->n_sb));
-    CU(cudaMalloc(&ctx->d_results, sizeof(SvtMePuResult) * (size_t)n * ctx->n_sb * kNumPu));
-    CU(cudaMalloc(&ctx->d_debug, sizeof(SvtMeSbDebug) * (size_t)n * ctx->n_sb));
-    CU(cudaMalloc(&ctx->d_jobs, sizeof(DJob) * (size_t)n));
-    CU(cudaMallocHost(&ctx->h_jobs, sizeof(DJob) * (size_t)n));
-    ctx->batch_cap = n;
+// Make ring entry `b` large enough for n pictures. The entry must be idle (its previous batch drained).
+static int32_t ensure_batch(SvtMeContext* ctx, Batch& b, int n) {
+    if (n <= b.cap) return SVTME_OK;
+    free_batch(b);
+    CU(cudaMalloc(&b.d_scratch, sizeof(SbScratch) * (size_t)n * ctx->n_sb));
+    CU(cudaMalloc(&b.d_results, sizeof(SvtMePuResult) * (size_t)n * ctx->n_sb * kNumPu));
+    CU(cudaMalloc(&b.d_debug, sizeof(SvtMeSbDebug) * (size_t)n * ctx->n_sb));
+    CU(cudaMalloc(&b.d_jobs, sizeof(DJob) * (size_t)n));
+    CU(cudaMallocHost(&b.h_jobs, sizeof(DJob) * (size_t)n));
+    b.cap = n;
     return SVTME_OK;
 }
 
@@ -250,45 +304,63 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
             return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: slot out of range");
         max_lists = j.params.num_lists > max_lists ? j.params.num_lists : max_lists;
     }
-    int32_t rc = ensure_batch(ctx, n_jobs);
+    const int bi = ctx->next;
+    Batch& b = ctx->ring[bi];
+    if (b.used) CU(cudaEventSynchronize(b.drained));     // the batch that used this entry kRing submissions ago
+    int32_t rc = ensure_batch(ctx, b, n_jobs);
     if (rc != SVTME_OK) return rc;
-    CU(cudaStreamSynchronize(ctx->stream));        // h_jobs is reused: the previous batch must have consumed it
     for (int i = 0; i < n_jobs; i++) {
         const SvtMeJob& j = jobs[i];
-        DJob& d = ctx->h_jobs[i];
+        DJob& d = b.h_jobs[i];
+        const int r1 = j.params.num_lists == 2 ? j.ref1_slot : j.ref0_slot;
         d.cur = ctx->slots[j.cur_slot].pyr;
         d.ref[0] = ctx->slots[j.ref0_slot].pyr;
-        d.ref[1] = ctx->slots[j.params.num_lists == 2 ? j.ref1_slot : j.ref0_slot].pyr;
+        d.ref[1] = ctx->slots[r1].pyr;
         d.prm = j.params;
-        d.scratch = ctx->d_scratch + (size_t)i * ctx->n_sb;
-        d.results = ctx->d_results + (size_t)i * ctx->n_sb * kNumPu;
-        d.debug = j.debug ? ctx->d_debug + (size_t)i * ctx->n_sb : nullptr;
+        d.scratch = b.d_scratch + (size_t)i * ctx->n_sb;
+        d.results = b.d_results + (size_t)i * ctx->n_sb * kNumPu;
+        d.debug = j.debug ? b.d_debug + (size_t)i * ctx->n_sb : nullptr;
         d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
+        for (int sl : { j.cur_slot, j.ref0_slot, r1 }) {
+            Slot& s = ctx->slots[sl];
+            if (s.last_reader_seq != ctx->seq) {        // first use by this batch: its pyramid must be complete
+                CU(cudaStreamWaitEvent(ctx->stream, s.ready, 0));
+                s.last_reader = bi; s.last_reader_seq = ctx->seq;
+            }
+        }
     }
-    CU(cudaMemcpyAsync(ctx->d_jobs, ctx->h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(b.d_jobs, b.h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
     for (int list = 0; list < max_lists; list++) {
-        { LaunchTimer t(ctx, SVTME_KERNEL_HME); launch_hme(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
-        { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL); launch_fullpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
-        { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL); launch_subpel(ctx->d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_HME, ctx->stream); launch_hme(b.d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, ctx->stream); launch_fullpel(b.d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, ctx->stream); launch_subpel(b.d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
     }
-    { LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK); launch_bipred_pack(ctx->d_jobs, n_jobs, ctx->n_sb, ctx->stream); }
+    { LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, ctx->stream); launch_bipred_pack(b.d_jobs, n_jobs, ctx->n_sb, ctx->stream); }
     CU(cudaGetLastError());
+    CU(cudaEventRecord(b.computed, ctx->stream));
+    // results travel on their own stream, straight into the caller's buffers
+    CU(cudaStreamWaitEvent(ctx->copy_out, b.computed, 0));
+    for (int i = 0; i < n_jobs; i++) {
+        if (jobs[i].results)
+            CU(cudaMemcpyAsync(jobs[i].results, b.d_results + (size_t)i * ctx->n_sb * kNumPu,
+                               sizeof(SvtMePuResult) * (size_t)ctx->n_sb * kNumPu, cudaMemcpyDeviceToHost, ctx->copy_out));
+        if (jobs[i].debug)
+            CU(cudaMemcpyAsync(jobs[i].debug, b.d_debug + (size_t)i * ctx->n_sb,
+                               sizeof(SvtMeSbDebug) * (size_t)ctx->n_sb, cudaMemcpyDeviceToHost, ctx->copy_out));
+    }
+    CU(cudaEventRecord(b.drained, ctx->copy_out));
+    b.used = true;
+    ctx->last = bi; ctx->seq++;
+    ctx->next = (bi + 1) % kRing;
     return SVTME_OK;
 }
 
+/* Wait until the results of every batch submitted so far are in the callers' buffers. */
 int32_t svtme_fetch_results(SvtMeContext* ctx, const SvtMeJob* jobs, int32_t n_jobs) {
-    if (!ctx || !jobs || n_jobs <= 0 || n_jobs > ctx->batch_cap)
-        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_fetch_results: bad batch");
+    (void)jobs; (void)n_jobs;
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
     CU(cudaSetDevice(ctx->device));
-    for (int i = 0; i < n_jobs; i++) {
-        if (jobs[i].results)
-            CU(cudaMemcpyAsync(jobs[i].results, ctx->d_results + (size_t)i * ctx->n_sb * kNumPu,
-                               sizeof(SvtMePuResult) * (size_t)ctx->n_sb * kNumPu, cudaMemcpyDeviceToHost, ctx->stream));
-        if (jobs[i].debug)
-            CU(cudaMemcpyAsync(jobs[i].debug, ctx->d_debug + (size_t)i * ctx->n_sb,
-                               sizeof(SvtMeSbDebug) * (size_t)ctx->n_sb, cudaMemcpyDeviceToHost, ctx->stream));
-    }
-    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->copy_out));
     return SVTME_OK;
 }
 
@@ -298,16 +370,37 @@ int32_t svtme_motion_estimate(SvtMeContext* ctx, const SvtMeJob* jobs, int32_t n
     return svtme_fetch_results(ctx, jobs, n_jobs);
 }
 
+/* Make the compute stream wait for everything enqueued so far on the transfer streams, so that an event
+ * recorded on svtme_stream() afterwards covers uploads, searches and result copies. */
+int32_t svtme_join(SvtMeContext* ctx) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord(ctx->join_ev, ctx->copy_in));
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->join_ev, 0));
+    CU(cudaEventRecord(ctx->join_ev, ctx->copy_out));
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->join_ev, 0));
+    return SVTME_OK;
+}
+
 int32_t svtme_set_profiling(SvtMeContext* ctx, int32_t enable) {
     if (!ctx) return SVTME_ERR_BAD_PARAMETER;
     ctx->profiling = enable != 0;
     return SVTME_OK;
 }
 
-int32_t svtme_kernel_times(SvtMeContext* ctx, double* ms, int64_t* launches, int32_t reset) {
+int32_t svtme_synchronize(SvtMeContext* ctx) {
     if (!ctx) return SVTME_ERR_BAD_PARAMETER;
     CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->copy_in));
     CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->copy_out));
+    return SVTME_OK;
+}
+
+int32_t svtme_kernel_times(SvtMeContext* ctx, double* ms, int64_t* launches, int32_t reset) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    const int32_t rc = svtme_synchronize(ctx);
+    if (rc != SVTME_OK) return rc;
     for (auto& t : ctx->timed) {
         float e = 0.f;
         CU(cudaEventElapsedTime(&e, t.a, t.b));
@@ -320,13 +413,6 @@ int32_t svtme_kernel_times(SvtMeContext* ctx, double* ms, int64_t* launches, int
         if (launches) launches[k] = ctx->kind_launches[k];
         if (reset) { ctx->kind_ms[k] = 0; ctx->kind_launches[k] = 0; }
     }
-    return SVTME_OK;
-}
-
-int32_t svtme_synchronize(SvtMeContext* ctx) {
-    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
-    CU(cudaSetDevice(ctx->device));
-    CU(cudaStreamSynchronize(ctx->stream));
     return SVTME_OK;
 }
 

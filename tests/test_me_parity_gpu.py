@@ -213,3 +213,28 @@ def test_error_codes(pkg):
     with pytest.raises(pkg.SvtMeError, match="0x80001005"):
         ctx.motion_estimate([(0, 1, 1, p)])
     ctx.close()
+
+
+def test_pipelined_batches_and_slot_reuse(pkg, meo):
+    """Several batches in flight on the three streams (upload / search / result copy), more batches than ring
+    entries, and slots re-uploaded while earlier batches still read their previous pictures."""
+    w, h = 320, 192
+    fr = M.synth_video(w, h, 12, seed=33, max_shift=16)
+    ctx = pkg.MeContext(w, h, 3)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    outs, keep = [], []
+    for b in range(5):                                   # batch b uses pictures 2b, 2b+1, 2b+2 in slots 0..2
+        for sl in range(3):
+            ctx.upload(sl, fr[2 * b + sl])
+        jobs, res, dbg = ctx.make_jobs([(1, 0, 2, p), (0, 1, 1, p)], want_debug=True)
+        ctx.motion_estimate_async(jobs)
+        outs.append((res, dbg)); keep.append(jobs)
+    ctx.fetch(keep[-1])
+    ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
+    mp = M.convert_params(M.MeoParams, p)
+    for b, (res, dbg) in enumerate(outs):
+        want0, _ = M.motion_estimate(meo, "meo", mp, pyr[2 * b + 1], pyr[2 * b], pyr[2 * b + 2])
+        want1, _ = M.motion_estimate(meo, "meo", mp, pyr[2 * b], pyr[2 * b + 1], pyr[2 * b + 1])
+        assert M.results_diff(res[0], want0) == [], b
+        assert M.results_diff(res[1], want1) == [], b
