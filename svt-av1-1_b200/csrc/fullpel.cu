@@ -61,13 +61,26 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
         src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
     if (tid < 96) keys[tid] = 0xFFFFFFFFu;
     {
+        // lane = window column (aligned word), warp pair = one quarter of the rows: three aligned loads give the
+        // four byte-shifted copies of a word (no integer division, 3 LDG + 4 SHF + 4 STS per word of the window)
         const int wrows = sah + 62;
         const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
-        const int per_copy = wrows * nfill;
-        for (int t = tid; t < 4 * per_copy; t += kFpThreads) {
-            const int s = t / per_copy, q = t - s * per_copy;
-            const int r = q / nfill, c = q - r * nfill;
-            win[(s * kWinRows + r) * kWinPitch + c] = ldg_u32_unaligned(rp.at(ox + sax + s + 4 * c, oy + say + r));
+        const int c = tid & 31;
+        if (c < nfill) {
+            const uint8_t* g0 = rp.at(ox + sax, oy + say);
+            const uint32_t m = (uint32_t)(uintptr_t)g0 & 3u;
+            const uint32_t* gw = reinterpret_cast<const uint32_t*>(g0 - m) + c;
+            const int wstride = rp.stride >> 2;
+            for (int r = tid >> 5; r < wrows; r += kFpThreads / 32) {
+                const uint32_t* w = gw + (size_t)r * wstride;
+                const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+#pragma unroll
+                for (int sc = 0; sc < 4; sc++) {
+                    const uint32_t o = m + sc;                       // byte offset of copy sc inside the aligned word
+                    const uint32_t lo = o < 4 ? w0 : w1, hi = o < 4 ? w1 : w2;
+                    win[(sc * kWinRows + r) * kWinPitch + c] = __funnelshift_r(lo, hi, (o & 3u) * 8u);
+                }
+            }
         }
     }
     __syncthreads();
@@ -122,7 +135,7 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
             for (int k = 0; k < 4; k++)
 #pragma unroll
                 for (int j = 0; j < 8; j++) acc[k][j] = 0;
-            if (live) {
+            {   // (threads past the last tile run on tile (0,0); their keys are masked by kmul/kadd)
 #pragma unroll
                 for (int rr = 0; rr < 4; rr++) {
                     const int r = 4 * b + rr;
