@@ -32,8 +32,13 @@ constexpr int kFpSmemBytes = (4 * kWinRows * kWinPitch + 32 * 16 + 96) * 4;
 // (bits 16, 8, 4, 2, 1) turn 32 keys x 32 lanes into one fully reduced key per lane at 4 instructions per key
 // (2 SEL + SHFL + VIMNMX), after which every lane issues one RED.MIN to its own PU slot: no per-key CREDUX,
 // leader election or branch.
-__device__ __forceinline__ uint32_t pair_min(uint32_t a, uint32_t b, int bit, bool hi) {
-    const uint32_t keep = hi ? b : a, send = hi ? a : b;
+// The keep/send selection is written as two IMADs (hi01 in {0,1}: keep = a + hi01*(b-a), send = b - hi01*(b-a)) so
+// that it runs on the FMA pipe: every ALU-pipe instruction costs as much as one VABSDIFF4 (both 64 lanes/clk/SM).
+__device__ __forceinline__ uint32_t pair_min(uint32_t a, uint32_t b, int bit, uint32_t hi01) {
+    uint32_t d, keep, send;
+    asm("sub.u32 %0, %1, %2;" : "=r"(d) : "r"(b), "r"(a));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(keep) : "r"(hi01), "r"(d), "r"(a));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(send) : "r"(0u - hi01), "r"(d), "r"(b));
     return min(keep, __shfl_xor_sync(0xffffffffu, send, bit));
 }
 __device__ __forceinline__ void red_min(uint32_t slot_addr, uint32_t key) {
@@ -93,7 +98,7 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const int s = tid & 3;
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
     const int lane = tid & 31;
-    const bool l16 = lane & 16, l8 = lane & 8, l4 = lane & 4, l2 = lane & 2, l1 = lane & 1;
+    const uint32_t l16 = (lane >> 4) & 1, l8 = (lane >> 3) & 1, l4 = (lane >> 2) & 1, l2 = (lane >> 1) & 1, l1 = lane & 1;
     // PU slot owned by this lane after the transpose-reductions (key index = bit-reversed lane):
     //   8x8  : column block j = (l16, l8, l4), block row within the half = (l2, l1); internal index = Morton(j, row)
     //   16x16: q = (l16, l8), row = (l4, l2);   32x32: q = l16, half = l8
@@ -213,29 +218,24 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
             if ((b & 3) != 3) continue;
             // ---- 32x32: two PUs of this half of the SB
             {
+                // quirk Q4 as a plain key: inside an 8-position group the reference takes the first-min of positions
+                // 0..3 ("lo") and of 4..7 ("hi"); lo wins only if strictly smaller and is then reported 4 to the right,
+                // hi 4 to the left. That is the minimum of (value, hi-before-lo, position), and the low three key bits
+                // (lo: 4 + s, hi: s) are exactly the reported index; groups are ordered (value, row, group) like the
+                // reference's strict-less scan. Leftover single positions use slots 8.. and a plain index.
+                uint32_t ka32[4], km32[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t a = single ? (((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3))
+                                              : (((uint32_t)y << 7) | ((uint32_t)(2 * G + (k >> 1)) << 3) | ((k & 1) ? 0u : 4u) | (uint32_t)s);
+                    ka32[k] = val[k] ? a : 0xFFFFFFFFu;
+                    km32[k] = kmul[k] << 1;
+                }
                 uint32_t k32[2];
 #pragma unroll
                 for (int q = 0; q < 2; q++) {
-                    uint32_t key = 0xFFFFFFFFu;
-                    // quirk Q4: per 8-position group, first-min of positions 0..3 ("lo") and of 4..7 ("hi");
-                    // lo wins only if strictly smaller and is then reported 4 to the right, hi 4 to the left.
-                    // (shuffles are executed by every lane; single-position tiles ignore the outcome)
-#pragma unroll
-                    for (int g2 = 0; g2 < 2; g2++) {
-                        uint32_t lo = (s32[2 * g2][q] << 2) | (uint32_t)s, hi = (s32[2 * g2 + 1][q] << 2) | (uint32_t)s;
-                        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 1)); lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, 2));
-                        hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 1)); hi = min(hi, __shfl_xor_sync(0xffffffffu, hi, 2));
-                        const uint32_t lv = lo >> 2, hv = hi >> 2;
-                        const uint32_t v = (hv > lv) ? lv : hv;
-                        const uint32_t idx = (hv > lv) ? (lo & 3u) + 4u : (hi & 3u);
-                        if (!single && val[2 * g2]) key = min(key, (v << 13) | ((uint32_t)y << 7) | ((uint32_t)(2 * G + g2) << 3) | idx);
-                    }
-                    if (single) {
-#pragma unroll
-                        for (int k = 0; k < 4; k++)
-                            if (val[k]) key = min(key, (s32[k][q] << 13) | ((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3));
-                    }
-                    k32[q] = key;
+                    k32[q] = min(min(s32[0][q] * km32[0] + ka32[0], s32[1][q] * km32[1] + ka32[1]),
+                                 min(s32[2][q] * km32[2] + ka32[2], s32[3][q] * km32[3] + ka32[3]));
 #pragma unroll
                     for (int k = 0; k < 4; k++) { s64[k] += s32[k][q]; s32[k][q] = 0; }
                 }
