@@ -1,0 +1,90 @@
+/* oracle/ref_txq.c -- TEST INFRASTRUCTURE ONLY.
+ * Thin accessors around the UNMODIFIED reference objects for the transform / quantisation family
+ * (compiled with the reference's headers where they lie under /root/reference, see oracle/Makefile):
+ * Av1EstimateTransform, av1_quantize_b_facade_II, av1_scan_orders, av1_build_quantizer. The function-pointer
+ * set-up mirrors setup_rtcd_internal for a CPU with AVX2 + SSE4.1 (aom_dsp_rtcd.h:2086-2096, 2660-2727), the only
+ * configuration the shipped encoder accepts. */
+#include "EbDefinitions.h"
+#include "aom_dsp_rtcd.h"
+#include "EbTransforms.h"
+#include "EbPictureControlSet.h"
+#include <string.h>
+#include <stdlib.h>
+
+extern void av1_quantize_b_facade_II(const tran_low_t *coeff_ptr, int32_t stride, int32_t width, int32_t height,
+                                     intptr_t n_coeffs, const MacroblockPlane *p, tran_low_t *qcoeff_ptr,
+                                     tran_low_t *dqcoeff_ptr, uint16_t *eob_ptr, const SCAN_ORDER *sc, const QUANT_PARAM *qparam);
+extern void av1_build_quantizer(aom_bit_depth_t bit_depth, int32_t y_dc_delta_q, int32_t u_dc_delta_q, int32_t u_ac_delta_q,
+                                int32_t v_dc_delta_q, int32_t v_ac_delta_q, Quants *const quants, Dequants *const deq);
+
+void ref_txq_init(void) {
+    aom_quantize_b = aom_highbd_quantize_b_avx2;
+    aom_quantize_b_32x32 = aom_highbd_quantize_b_32x32_avx2;
+#if INTRINSIC_OPT_2
+    aom_quantize_b_64x64 = aom_highbd_quantize_b_64x64_avx2;
+    av1_fwd_txfm2d_16x8 = av1_fwd_txfm2d_16x8_avx2;   av1_fwd_txfm2d_8x16 = av1_fwd_txfm2d_8x16_avx2;
+    av1_fwd_txfm2d_16x4 = av1_fwd_txfm2d_16x4_sse4_1; av1_fwd_txfm2d_4x16 = av1_fwd_txfm2d_4x16_sse4_1;
+    av1_fwd_txfm2d_8x4 = av1_fwd_txfm2d_8x4_sse4_1;   av1_fwd_txfm2d_4x8 = av1_fwd_txfm2d_4x8_sse4_1;
+    av1_fwd_txfm2d_16x16 = av1_fwd_txfm2d_16x16_avx2;
+#else
+    aom_quantize_b_64x64 = aom_quantize_b_64x64_c_II;
+    av1_fwd_txfm2d_16x8 = av1_fwd_txfm2d_16x8_c;   av1_fwd_txfm2d_8x16 = av1_fwd_txfm2d_8x16_c;
+    av1_fwd_txfm2d_16x4 = av1_fwd_txfm2d_16x4_c;   av1_fwd_txfm2d_4x16 = av1_fwd_txfm2d_4x16_c;
+    av1_fwd_txfm2d_8x4 = av1_fwd_txfm2d_8x4_c;     av1_fwd_txfm2d_4x8 = av1_fwd_txfm2d_4x8_c;
+    av1_fwd_txfm2d_16x16 = Av1TransformTwoD_16x16_c;
+#endif
+    av1_fwd_txfm2d_32x16 = av1_fwd_txfm2d_32x16_avx2; av1_fwd_txfm2d_32x8 = av1_fwd_txfm2d_32x8_avx2;
+    av1_fwd_txfm2d_8x32 = av1_fwd_txfm2d_8x32_avx2;   av1_fwd_txfm2d_16x32 = av1_fwd_txfm2d_16x32_avx2;
+    av1_fwd_txfm2d_32x64 = av1_fwd_txfm2d_32x64_avx2; av1_fwd_txfm2d_64x32 = av1_fwd_txfm2d_64x32_avx2;
+    av1_fwd_txfm2d_16x64 = av1_fwd_txfm2d_16x64_avx2; av1_fwd_txfm2d_64x16 = av1_fwd_txfm2d_64x16_avx2;
+    av1_fwd_txfm2d_64x64 = av1_fwd_txfm2d_64x64_avx2; av1_fwd_txfm2d_32x32 = av1_fwd_txfm2d_32x32_avx2;
+    av1_fwd_txfm2d_8x8 = av1_fwd_txfm2d_8x8_avx2;     av1_fwd_txfm2d_4x4 = av1_fwd_txfm2d_4x4_sse4_1;
+}
+
+static int tx_size_of(int w, int h) {
+    for (int t = 0; t < TX_SIZES_ALL; t++) if (tx_size_wide[t] == w && tx_size_high[t] == h) return t;
+    return -1;
+}
+
+/* Av1EstimateTransform on one block; coeff must hold w*h int32. Returns the TxSize used. */
+int ref_fwd_txfm(int16_t *residual, uint32_t stride, int32_t *coeff, int w, int h, int tx_type, int bit_increment,
+                 uint64_t *three_quad_energy) {
+    const int ts = tx_size_of(w, h);
+    *three_quad_energy = 0;
+    Av1EstimateTransform(residual, stride, coeff, (uint32_t)w, (TxSize)ts, three_quad_energy, NULL, (uint32_t)bit_increment,
+                         (TxType)tx_type, ASM_AVX2, PLANE_TYPE_Y, DEFAULT_SHAPE);
+    return ts;
+}
+
+/* q10 = { zbin_dc, zbin_ac, round_dc, round_ac, quant_dc, quant_ac, shift_dc, shift_ac, dequant_dc, dequant_ac } */
+void ref_quantize(const int32_t *coeff, int w, int h, int tx_type, const int16_t *q10, int32_t *qcoeff, int32_t *dqcoeff,
+                  uint16_t *eob) {
+    const int ts = tx_size_of(w, h);
+    int16_t lanes[5][8];
+    for (int k = 0; k < 5; k++) for (int i = 0; i < 8; i++) lanes[k][i] = q10[2 * k + (i != 0)];
+    MacroblockPlane p; memset(&p, 0, sizeof(p));
+    p.zbin_QTX = lanes[0]; p.round_QTX = lanes[1]; p.quant_QTX = lanes[2]; p.quant_shift_QTX = lanes[3]; p.dequant_QTX = lanes[4];
+    QUANT_PARAM qp; memset(&qp, 0, sizeof(qp));
+    qp.log_scale = av1_get_tx_scale((TxSize)ts); qp.tx_size = (TxSize)ts; qp.qmatrix = NULL; qp.iqmatrix = NULL;
+    const int pw = w < 32 ? w : 32, ph = h < 32 ? h : 32;
+    av1_quantize_b_facade_II(coeff, pw, pw, ph, av1_get_max_eob((TxSize)ts), &p, qcoeff, dqcoeff, eob,
+                             &av1_scan_orders[ts][tx_type], &qp);
+}
+
+const int16_t *ref_scan(int w, int h, int tx_type) { return av1_scan_orders[tx_size_of(w, h)][tx_type].scan; }
+const int16_t *ref_iscan(int w, int h, int tx_type) { return av1_scan_orders[tx_size_of(w, h)][tx_type].iscan; }
+int ref_max_eob(int w, int h) { return av1_get_max_eob((TxSize)tx_size_of(w, h)); }
+
+/* luma quantiser of one qindex as built by av1_build_quantizer (EbModeDecisionConfigurationProcess.c:417-520) */
+void ref_quant_params(int bit_depth, int qindex, int16_t *q10) {
+    static Quants *q[2]; static Dequants *d[2];
+    const int b = bit_depth == 10;
+    if (!q[b]) {
+        q[b] = (Quants *)calloc(1, sizeof(Quants)); d[b] = (Dequants *)calloc(1, sizeof(Dequants));
+        av1_build_quantizer(b ? AOM_BITS_10 : AOM_BITS_8, 0, 0, 0, 0, 0, q[b], d[b]);
+    }
+    for (int i = 0; i < 2; i++) {
+        q10[0 + i] = q[b]->y_zbin[qindex][i]; q10[2 + i] = q[b]->y_round[qindex][i]; q10[4 + i] = q[b]->y_quant[qindex][i];
+        q10[6 + i] = q[b]->y_quant_shift[qindex][i]; q10[8 + i] = d[b]->y_dequant_QTX[qindex][i];
+    }
+}

@@ -1,0 +1,119 @@
+"""ctypes views of the transform / quantisation oracle (oracle/txq_oracle.c) and of the reference accessors
+(oracle/ref_txq.c). Test infrastructure only."""
+import ctypes as C
+
+import numpy as np
+
+import me_common as M
+
+TX_SIZES = [(4, 4), (8, 8), (16, 16), (32, 32), (64, 64), (4, 8), (8, 4), (8, 16), (16, 8), (16, 32), (32, 16), (32, 64),
+            (64, 32), (4, 16), (16, 4), (8, 32), (32, 8), (16, 64), (64, 16)]
+TX_TYPE_NAMES = ["DCT_DCT", "ADST_DCT", "DCT_ADST", "ADST_ADST", "FLIPADST_DCT", "DCT_FLIPADST", "FLIPADST_FLIPADST",
+                 "ADST_FLIPADST", "FLIPADST_ADST", "IDTX", "V_DCT", "H_DCT", "V_ADST", "H_ADST", "V_FLIPADST", "H_FLIPADST"]
+_V = [0, 1, 0, 1, 2, 0, 2, 1, 2, 3, 0, 3, 1, 3, 2, 3]
+_H = [0, 0, 1, 1, 0, 2, 2, 2, 1, 3, 3, 0, 3, 1, 3, 2]
+
+
+def packed(w, h):
+    return min(w, 32), min(h, 32)
+
+
+def log_scale(w, h):
+    return int(w * h > 256) + int(w * h > 1024)
+
+
+def type_supported(w, h, t):
+    """(size, type) pairs with 1-D kernels on both axes: ADST only up to 16 points; 64-point only DCT."""
+    v, hh = _V[t], _H[t]
+    if v in (1, 2) and h > 16:
+        return False
+    if hh in (1, 2) and w > 16:
+        return False
+    if (w == 64 or h == 64) and t != 0:
+        return False
+    return True
+
+
+def oracle():
+    lib = M.load_oracle()
+    lib.meo_fwd_txfm.restype = C.c_int
+    lib.meo_fwd_txfm.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+    lib.meo_scan.restype = C.c_int
+    lib.meo_scan.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.meo_quantize_b.restype = None
+    lib.meo_quantize_b.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint16)]
+    return lib
+
+
+def reference():
+    lib = M.load_ref()
+    lib.ref_txq_init()
+    lib.ref_fwd_txfm.restype = C.c_int
+    lib.ref_fwd_txfm.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+    lib.ref_quantize.restype = None
+    lib.ref_quantize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint16)]
+    lib.ref_scan.restype = C.POINTER(C.c_int16)
+    lib.ref_scan.argtypes = [C.c_int] * 3
+    lib.ref_max_eob.restype = C.c_int
+    lib.ref_quant_params.restype = None
+    lib.ref_quant_params.argtypes = [C.c_int, C.c_int, C.c_void_p]
+    return lib
+
+
+def aligned(n, dtype, align=64):
+    """numpy array whose data pointer is `align`-byte aligned (the reference's AVX2 kernels use aligned stores)."""
+    item = np.dtype(dtype).itemsize
+    raw = np.zeros(n * item + align, dtype=np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n * item].view(dtype)
+
+
+def fwd_txfm(lib, prefix, res, w, h, t):
+    """res: int16 (h, w) C-contiguous. Returns (packed coefficients int32 (ph, pw), energy)."""
+    pw, ph = packed(w, h)
+    e = C.c_uint64(0)
+    res = np.ascontiguousarray(res, dtype=np.int16)
+    if prefix == "meo":
+        out = np.zeros(pw * ph, dtype=np.int32)
+        rc = lib.meo_fwd_txfm(res.ctypes.data, w, out.ctypes.data, w, h, t, C.byref(e))
+        assert rc == 0
+    else:
+        buf = aligned(w * h, np.int32)
+        rin = aligned(w * h, np.int16)
+        rin[:] = res.reshape(-1)
+        lib.ref_fwd_txfm(rin.ctypes.data, w, buf.ctypes.data, w, h, t, 0, C.byref(e))
+        out = buf[:pw * ph].copy()
+    return out.reshape(ph, pw), e.value
+
+
+def scan(lib, prefix, w, h, t):
+    pw, ph = packed(w, h)
+    if prefix == "meo":
+        s = np.zeros(pw * ph, dtype=np.int16)
+        assert lib.meo_scan(w, h, t, s.ctypes.data) == pw * ph
+        return s
+    p = lib.ref_scan(w, h, t)
+    return np.array([p[i] for i in range(pw * ph)], dtype=np.int16)
+
+
+def quantize(lib, prefix, coeff, w, h, t, q10):
+    pw, ph = packed(w, h)
+    n = pw * ph
+    coeff = np.ascontiguousarray(coeff, dtype=np.int32).reshape(-1)
+    q10 = np.ascontiguousarray(q10, dtype=np.int16)
+    qc, dq, eob = aligned(n, np.int32), aligned(n, np.int32), C.c_uint16(0)
+    ca = aligned(n, np.int32)
+    ca[:] = coeff
+    coeff = ca
+    if prefix == "meo":
+        s = scan(lib, "meo", w, h, t)
+        lib.meo_quantize_b(coeff.ctypes.data, n, q10.ctypes.data, log_scale(w, h), s.ctypes.data, qc.ctypes.data, dq.ctypes.data, C.byref(eob))
+    else:
+        lib.ref_quantize(coeff.ctypes.data, w, h, t, q10.ctypes.data, qc.ctypes.data, dq.ctypes.data, C.byref(eob))
+    return qc, dq, eob.value
+
+
+def quant_params(ref, qindex, bit_depth=8):
+    q10 = np.zeros(10, dtype=np.int16)
+    ref.ref_quant_params(bit_depth, qindex, q10.ctypes.data)
+    return q10
