@@ -19,10 +19,10 @@ def pkg_built(pkg):
     return pkg
 
 
-def declared_symbols():
-    txt = open(HEADER).read()
+def declared_symbols(header=HEADER, prefix="svtme_"):
+    txt = open(header).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-    return sorted(set(re.findall(r"\b(svtme_\w+)\s*\(", txt)))
+    return sorted(set(re.findall(r"\b(%s\w+)\s*\(" % prefix, txt)))
 
 
 def test_header_symbols_exported(pkg_built):
@@ -32,6 +32,32 @@ def test_header_symbols_exported(pkg_built):
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/svtme.h but not exported"
     assert set(names) == set(pkg_built.EXPORTED_SYMBOLS)
+
+
+def test_txq_header_symbols_exported(pkg_built):
+    lib = pkg_built.load_library()
+    names = declared_symbols(os.path.join(M.ROOT, "include", "svttxq.h"), "svttxq_")
+    assert len(names) >= 9
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/svttxq.h but not exported"
+    assert set(names) == set(pkg_built.TXQ_EXPORTED_SYMBOLS)
+    assert C.sizeof(pkg_built.SvtTxqQuant) == 20
+
+
+def test_txq_supported_matches_reference_kernels(pkg_built):
+    import txq_common as T
+    for (w, h) in T.TX_SIZES:
+        for t in range(16):
+            assert pkg_built.txq_supported(w, h, t) == T.type_supported(w, h, t), (w, h, t)
+    assert not pkg_built.txq_supported(64, 8, 0) and not pkg_built.txq_supported(12, 12, 0)
+    assert not pkg_built.txq_supported(8, 8, 16)
+
+
+def test_txq_no_cpu_fallback(pkg_built):
+    import torch
+    if not torch.cuda.is_available():
+        with pytest.raises(pkg_built.SvtMeError):
+            pkg_built.TxqContext(0)
 
 
 def test_struct_layouts(pkg_built):

@@ -117,3 +117,33 @@ def quant_params(ref, qindex, bit_depth=8):
     q10 = np.zeros(10, dtype=np.int16)
     ref.ref_quant_params(bit_depth, qindex, q10.ctypes.data)
     return q10
+
+
+def txq_plane(lib, res, w, h, t, q10):
+    """Oracle over a whole residual plane (int16 (H, W), rows may be strided): dict like TxqContext.fwd_txfm_quant."""
+    assert res.dtype == np.int16 and res.strides[1] == 2
+    height, width = res.shape
+    pw, ph = packed(w, h)
+    nb = (width // w) * (height // h)
+    out = {k: np.zeros((nb, pw * ph), np.int32) for k in ("coeff", "qcoeff", "dqcoeff")}
+    out["eob"] = np.zeros(nb, np.uint16)
+    out["energy"] = np.zeros(nb, np.uint64)
+    q10 = np.ascontiguousarray(q10, dtype=np.int16)
+    lib.meo_txq_plane.restype = C.c_int
+    lib.meo_txq_plane.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_void_p] * 6
+    rc = lib.meo_txq_plane(res.ctypes.data, res.strides[0] // 2, width, height, w, h, t, q10.ctypes.data,
+                           out["coeff"].ctypes.data, out["qcoeff"].ctypes.data, out["dqcoeff"].ctypes.data,
+                           out["eob"].ctypes.data, out["energy"].ctypes.data)
+    assert rc == nb
+    return out
+
+
+def synth_residual(rng, height, width, bit_depth=8, kind="mixed"):
+    """Residual-like int16 plane: smooth gradients + texture + sparse edges, clipped to the legal range."""
+    lim = (1 << bit_depth) - 1
+    if kind == "noise":
+        return rng.integers(-lim, lim + 1, size=(height, width)).astype(np.int16)
+    y, x = np.mgrid[0:height, 0:width]
+    base = 20 * np.sin(x / 7.3) * np.cos(y / 11.1) + rng.normal(0, 6, size=(height, width))
+    edges = (rng.random((height, width)) < 0.01) * rng.integers(-lim, lim + 1, size=(height, width))
+    return np.clip(np.rint(base + edges), -lim, lim).astype(np.int16)
