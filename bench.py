@@ -357,6 +357,270 @@ def run_gpu_impl(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------
+# Secondary kernel family: forward transform + quantisation sweep (BASELINE.json configs[3]); `--workload txq`
+TXQ_SIZES = [(4, 4), (8, 8), (16, 16), (32, 32), (64, 64), (4, 8), (8, 4), (8, 16), (16, 8), (16, 32), (32, 16), (32, 64),
+             (64, 32), (4, 16), (16, 4), (8, 32), (32, 8), (16, 64), (64, 16)]
+TXQ_PLANES = 8                                     # 1080p residual planes stacked per launch (outputs 200 MB > L2)
+TXQ_W, TXQ_H = 1920, 1088
+TXQ_CPU_REPS = 16                                  # repetitions of one 1920x128 strip per CPU task
+
+
+def txq_cases():
+    """(txw, txh, tx_type): DCT_DCT for every size, ADST_ADST and IDTX where the reference has them."""
+    out = []
+    for (w, h) in TXQ_SIZES:
+        out.append((w, h, 0))
+        if max(w, h) <= 16:
+            out.append((w, h, 3))
+        if max(w, h) <= 32:
+            out.append((w, h, 9))
+    return out
+
+
+def txq_residual(seed, planes):
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:TXQ_H, 0:TXQ_W]
+    base = 20 * np.sin(x / 7.3) * np.cos(y / 11.1)
+    out = np.empty((planes * TXQ_H, TXQ_W), np.int16)
+    for i in range(planes):
+        out[i * TXQ_H:(i + 1) * TXQ_H] = np.clip(np.rint(base + rng.normal(0, 8, size=base.shape)), -255, 255).astype(np.int16)
+    return out
+
+
+def _txq_cpu_init(kind):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import txq_common as T
+    _CPU["T"] = T
+    _CPU["kind"] = kind
+    _CPU["lib"] = T.reference() if kind == "reference" else T.oracle()
+    rows = 128
+    res = T.aligned(rows * TXQ_W, np.int16).reshape(rows, TXQ_W)
+    res[:] = txq_residual(3, 1)[:rows]
+    _CPU["res"] = res
+    _CPU["out"] = [T.aligned(rows * TXQ_W, np.int32) for _ in range(3)] + [T.aligned(rows * TXQ_W // 16, np.uint16), T.aligned(rows * TXQ_W // 16, np.uint64)]
+
+
+def _txq_cpu_task(job):
+    """One 1920x128 residual strip of one (size, type) through the reference's transform + quantiser on one core."""
+    w, h, t, q10 = job
+    lib, res, out = _CPU["lib"], _CPU["res"], _CPU["out"]
+    fn = lib.ref_txq_plane if _CPU["kind"] == "reference" else lib.meo_txq_plane
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_void_p] * 6
+    q = np.ascontiguousarray(q10, dtype=np.int16)
+    n = 0
+    for _ in range(TXQ_CPU_REPS):
+        n += fn(res.ctypes.data, TXQ_W, TXQ_W, res.shape[0], w, h, t, q.ctypes.data, *[o.ctypes.data for o in out])
+    return n * w * h
+
+
+class TxqCpuArm:
+    def __init__(self):
+        import multiprocessing as mp
+        self.kind = "reference" if cpu_reference_available() else "port"
+        self.cores = len(os.sched_getaffinity(0))
+        self.pool = mp.get_context("fork").Pool(self.cores, initializer=_txq_cpu_init, initargs=(self.kind,))
+
+    def run(self, case, q10, strips):
+        t0 = time.perf_counter()
+        pix = sum(self.pool.map(_txq_cpu_task, [case + (list(q10),)] * strips, chunksize=1))
+        return pix / (time.perf_counter() - t0)
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def txq_quant_params():
+    """Luma quantiser of qindex 124, 8-bit: from the golden file (the reference's own av1_build_quantizer tables)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "txq_golden.npz"))
+    for c, q in zip(g["cases"], g["q10"]):
+        if int(c[3]) == 8 and int(c[4]) == 124:
+            return [int(v) for v in q]
+    return [int(v) for v in g["q10"][0]]
+
+
+def run_txq(args, rank, world, local_rank):
+    """Sweep of svttxq_fwd_txfm_quant over TXQ_PLANES stacked 1080p residual planes per launch. One JSON line:
+    value = pixels/s over the whole sweep (resident), e2e through host buffers, per-case GB/s against the HBM peak."""
+    q10 = txq_quant_params()
+    cases = txq_cases()
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        arm = TxqCpuArm()
+        strips = 4 * arm.cores
+        per = {}
+        for _ in range(max(1, args.warmup // 3)):
+            arm.run(cases[0], q10, arm.cores)
+        t0 = time.perf_counter()
+        pix_total = 0
+        for _ in range(args.steps):
+            for c in cases:
+                r = arm.run(c, q10, strips)
+                per["%dx%d/%d" % c] = r / 1e6
+                pix_total += strips * TXQ_CPU_REPS * 128 * TXQ_W
+        dt = time.perf_counter() - t0
+        arm.close()
+        v = pix_total / dt / 1e6
+        sample = f"{strips} x {TXQ_CPU_REPS} strips of 1920x128 residual per case and step, {len(cases)} cases, {arm.cores} worker processes"
+        print(json.dumps({"impl": "reference", "metric": "txq_mpixels_per_sec", "value": v, "unit": "Mpixel/s", "n_gpus": args.gpus,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": txq_config(world),
+                          "cpu_baseline": {"value": v, "unit": "Mpixel/s", "cores": arm.cores, "kind": arm.kind, "sample": sample},
+                          "e2e": {"value": v, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                          "per_case_mpixels_per_sec": per, "gpu_launches": 0}), flush=True)
+        return
+
+    import torch
+    pkg = importlib.import_module("svt-av1-1_b200")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU arm)")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        arm = TxqCpuArm()
+        arm.run(cases[0], q10, arm.cores)
+        per, t0, pix = {}, time.perf_counter(), 0
+        strips = 4 * arm.cores
+        for c in cases:
+            per["%dx%d/%d" % c] = arm.run(c, q10, strips) / 1e6
+            pix += strips * TXQ_CPU_REPS * 128 * TXQ_W
+        dt = time.perf_counter() - t0
+        arm.close()
+        cpu = {"value": pix / dt / 1e6, "unit": "Mpixel/s", "cores": arm.cores, "kind": arm.kind,
+               "sample": f"{strips} x {TXQ_CPU_REPS} strips of 1920x128 residual per case, {len(cases)} cases, {arm.cores} worker processes, {dt:.1f} s wall",
+               "per_case": per}
+    torch.cuda.set_device(local_rank)
+    res = txq_residual(11 + rank, TXQ_PLANES)
+    host = torch.from_numpy(res).pin_memory()
+    dev = host.cuda()
+    Hs = TXQ_PLANES * TXQ_H
+    npix = Hs * TXQ_W
+    d_out = [torch.empty(npix, dtype=torch.int32, device="cuda") for _ in range(3)]
+    d_eob = torch.empty(npix // 16, dtype=torch.int16, device="cuda")
+    d_en = torch.empty(npix // 16, dtype=torch.int64, device="cuda")
+    h_out = [torch.empty(npix, dtype=torch.int32).pin_memory() for _ in range(3)]
+    h_eob = torch.empty(npix // 16, dtype=torch.int16).pin_memory()
+    h_en = torch.empty(npix // 16, dtype=torch.int64).pin_memory()
+    ctx = pkg.TxqContext(local_rank)
+    st = torch.cuda.ExternalStream(ctx.stream())
+    quant = pkg.SvtTxqQuant.from_q10(q10)
+
+    def launch(c):
+        ctx.fwd_txfm_quant_device(dev.data_ptr(), TXQ_W, TXQ_W, Hs, c[0], c[1], c[2], quant, d_out[0].data_ptr(), d_out[1].data_ptr(),
+                                  d_out[2].data_ptr(), d_eob.data_ptr(), d_en.data_ptr())
+
+    def host_call(c):
+        rc = ctx.lib.svttxq_fwd_txfm_quant(ctx._h, host.data_ptr(), TXQ_W, TXQ_W, Hs, c[0], c[1], c[2], C.byref(quant),
+                                           h_out[0].data_ptr(), h_out[1].data_ptr(), h_out[2].data_ptr(), h_eob.data_ptr(), h_en.data_ptr())
+        assert rc == 0
+
+    def sync_all():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    for _ in range(args.warmup):
+        for c in cases:
+            launch(c)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    per_ms = {}
+    sync_all()
+    l0 = ctx.kernel_launches()
+    e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    evs = []
+    e_all0.record(st)
+    for _ in range(args.steps):
+        for c in cases:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(st)
+            launch(c)
+            b.record(st)
+            evs.append((c, a, b))
+    e_all1.record(st)
+    sync_all()
+    launches = ctx.kernel_launches() - l0
+    ms = e_all0.elapsed_time(e_all1)
+    for c, a, b in evs:
+        per_ms.setdefault(c, []).append(a.elapsed_time(b))
+    clocks = sampler.stop() if sampler else None
+    # e2e: host buffers through the synchronous C-ABI call, H2D + kernel + D2H per call
+    for c in cases[:2]:
+        host_call(c)
+    sync_all()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 2))
+    for _ in range(e2e_steps):
+        for c in cases:
+            host_call(c)
+    sync_all()
+    ms_e2e = (time.perf_counter() - t0) * 1e3
+    if dist is not None:
+        t = torch.tensor([ms, ms_e2e], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0].item()), float(t[1].item())
+    checksum = int(h_out[1].sum(dtype=torch.int64).item())
+    ctx.close()
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        per = {}
+        tot_bytes = tot_ms = 0.0
+        for c in cases:
+            w, h, _ = c
+            pw, ph = min(w, 32), min(h, 32)
+            nb = npix // (w * h)
+            nbytes = 2 * npix + 12 * nb * pw * ph + 10 * nb
+            t = float(np.median(per_ms[c]))
+            per["%dx%d/%d" % c] = {"ms": t, "GB/s": nbytes / t / 1e6, "frac": nbytes / t / 1e6 / hbm_peak, "Gpixel/s": npix / t / 1e6}
+            tot_bytes += nbytes
+            tot_ms += t
+        worst = min(per, key=lambda k: per[k]["frac"])
+        v = world * npix * len(cases) * args.steps / (ms / 1e3) / 1e6
+        v_e2e = world * npix * len(cases) * e2e_steps / (ms_e2e / 1e3) / 1e6
+        pw_bytes = sum(12 * (npix // (w * h)) * min(w, 32) * min(h, 32) + 10 * (npix // (w * h)) for (w, h, _) in cases)
+        line = {"metric": "txq_mpixels_per_sec", "value": v, "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
+                "data": "synthetic", "config": txq_config(world),
+                "e2e": {"value": v_e2e, "unit": "Mpixel/s", "h2d_bytes_per_step": 2 * npix * len(cases), "d2h_bytes_per_step": pw_bytes,
+                        "ms_per_step": ms_e2e / e2e_steps, "timing": "host wall clock around synchronous svttxq_fwd_txfm_quant calls"},
+                "gpu_launches": int(launches),
+                "roofline": {"kernel": "txq_kernel<*>", "bound": "hbm", "achieved": tot_bytes / tot_ms / 1e6, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": tot_bytes / tot_ms / 1e6 / hbm_peak, "traffic": None,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                             "bytes_model": "2 B/pixel residual in + 12 B per kept coefficient (coeff, qcoeff, dqcoeff) + 10 B per block (eob, energy)",
+                             "worst_case": worst, "worst_frac": per[worst]["frac"]},
+                "per_case": per, "clocks": clocks, "result_checksum": checksum}
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def txq_config(n_gpus):
+    return {"workload": f"forward transform + quantisation sweep: {len(txq_cases())} (size, type) cases over the 19 AV1 transform sizes "
+                        f"(DCT_DCT everywhere, ADST_ADST up to 16 points, IDTX up to 32), each over {TXQ_PLANES} stacked 1920x1088 "
+                        "8-bit residual planes per launch, luma quantiser of qindex 124",
+            "pixels_per_launch": TXQ_PLANES * TXQ_H * TXQ_W, "parallelism": f"independent planes per GPU x{n_gpus}, no collective",
+            "l2_policy": "outputs of one launch (200 MB) exceed L2; consecutive launches use different kernels over the same 33 MB input"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -364,10 +628,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="me", choices=["me", "txq"],
+                    help="me: 1080p motion estimation (headline, BASELINE configs[1]); txq: transform + quantisation sweep (configs[3])")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "txq":
+        run_txq(args, rank, world, local_rank)
+        return
     if args.impl == "reference":
         run_reference_impl(args, rank)
         return

@@ -88,3 +88,22 @@ void ref_quant_params(int bit_depth, int qindex, int16_t *q10) {
         q10[6 + i] = q[b]->y_quant_shift[qindex][i]; q10[8 + i] = d[b]->y_dequant_QTX[qindex][i];
     }
 }
+
+/* Whole residual plane through the reference's own functions, block by block (the CPU arm of bench.py's
+ * transform/quantisation sweep and a second pin for meo_txq_plane). Buffers must be 32-byte aligned and the stride a
+ * multiple of 16 (AVX2 aligned loads). Output layout as in include/svttxq.h. Returns the number of blocks. */
+int ref_txq_plane(int16_t *res, int stride, int width, int height, int w, int h, int tx_type, const int16_t *q10,
+                  int32_t *coeff, int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob, uint64_t *energy) {
+    const int pw = w < 32 ? w : 32, ph = h < 32 ? h : 32, n = pw * ph;
+    static __attribute__((aligned(64))) int32_t tmp[64 * 64];
+    int b = 0;
+    for (int by = 0; by < height / h; by++)
+        for (int bx = 0; bx < width / w; bx++, b++) {
+            uint64_t e = 0;
+            ref_fwd_txfm(res + (size_t)by * h * stride + bx * w, (uint32_t)stride, tmp, w, h, tx_type, 0, &e);
+            memcpy(coeff + (size_t)b * n, tmp, sizeof(int32_t) * n);
+            ref_quantize(coeff + (size_t)b * n, w, h, tx_type, q10, qcoeff + (size_t)b * n, dqcoeff + (size_t)b * n, &eob[b]);
+            energy[b] = e;
+        }
+    return b;
+}

@@ -68,101 +68,150 @@ __host__ __device__ constexpr int shift1(int w, int h) {
 }
 __host__ __device__ constexpr int shift2(int w, int h) { return ((w == 64 && h == 64) || (w == 32 && h == 64) || (w == 64 && h == 32)) ? 2 : 0; }
 
+// Geometry of one CTA: B = 256 / min(TXW, TXH) transform blocks, consecutive in raster order. The column pass has
+// B * TXW work items (one TXH-point transform each), the row pass B * TXH items (one TXW-point transform each); the
+// 256 threads loop over them, so rectangular sizes keep every thread busy in both passes.
+template <int TXW, int TXH> struct TxqGeom {
+    static constexpr int B = 256 / cmin(TXW, TXH);
+    static constexpr int PITCH = TXW + 1;          // odd: row r of slot s starts at word PITCH * (s * TXH + r)
+    static constexpr int SLOT = TXH * PITCH;
+    static constexpr int PW = cmin(TXW, 32), PH = cmin(TXH, 32), N = PW * PH;
+    static constexpr int SMEM = B * SLOT * (int)sizeof(int32_t);
+    static constexpr bool BIG = TXW == 64 || TXH == 64;
+};
+
+struct QuantLane { int32_t zbin, round, quant_hi, qshift, dequant; };    // one lane (DC or AC) of the quantiser
+
+template <int LS> __device__ __forceinline__ QuantLane quant_lane(const SvtTxqQuant& q, int ac) {
+    constexpr int RND = LS ? (1 << (LS - 1)) : 0;
+    QuantLane l;
+    l.zbin = (int32_t)(int16_t)((uint16_t)((ac ? q.zbin[1] : q.zbin[0]) + RND) >> LS);
+    l.round = (int32_t)(int16_t)((uint16_t)((ac ? q.round[1] : q.round[0]) + RND) >> LS);
+    l.quant_hi = (int32_t)(ac ? q.quant[1] : q.quant[0]) << 16;           // (t * quant) >> 16 == mulhi(t, quant << 16)
+    l.qshift = ac ? q.quant_shift[1] : q.quant_shift[0];
+    l.dequant = ac ? q.dequant[1] : q.dequant[0];
+    return l;
+}
+
 template <int TXW, int TXH>
-__global__ void __launch_bounds__(256) txq_kernel(const TxqArgs a) {
-    constexpr int T = cmax(TXW, TXH);              // threads per transform block
-    constexpr int B = 256 / T;                     // transform blocks per CTA
-    constexpr int PITCH = TXW + 1;                 // odd pitch: column writes and row reads are conflict-free
-    constexpr int PW = cmin(TXW, 32), PH = cmin(TXH, 32);
+__global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::BIG ? 2 : 1) txq_kernel(const TxqArgs a) {
+    using G = TxqGeom<TXW, TXH>;
+    constexpr int B = G::B, PITCH = G::PITCH, SLOT = G::SLOT, PW = G::PW, PH = G::PH, N = G::N;
     constexpr int CC = kCosCol[ilog2(TXW) - 2][ilog2(TXH) - 2], CR = kCosRow[ilog2(TXW) - 2][ilog2(TXH) - 2];
     constexpr bool RECT = (ilog2(TXW) - ilog2(TXH) == 1) || (ilog2(TXH) - ilog2(TXW) == 1);
     extern __shared__ __align__(16) int32_t smem_txq[];
     __shared__ unsigned int s_eob[B];
     __shared__ unsigned long long s_energy[B];
-    const int slot = threadIdx.x / T, t = threadIdx.x % T;
-    const int blk = blockIdx.x * B + slot;
-    int32_t* buf = smem_txq + slot * (TXH * PITCH);
-    if (t == 0) { s_eob[slot] = 0; s_energy[slot] = 0; }
-    const bool on = blk < a.n_blocks;
-    const int bx = on ? blk % a.blocks_x : 0, by = on ? blk / a.blocks_x : 0;
-    const int16_t* in = a.residual + (size_t)by * TXH * a.stride + (size_t)bx * TXW;
+    const int tid = threadIdx.x;
+    const int blk0 = blockIdx.x * B;
+    const int n_here = min(B, a.n_blocks - blk0);            // blocks of this CTA that exist
+    if (tid < B) { s_eob[tid] = 0; s_energy[tid] = 0; }
 
-    // ---- vertical pass: thread t owns column t (Av1TranformTwoDCore_c, "Columns")
-    if (on && t < TXW) {
+    // ---- vertical pass: one item = one column of one block (Av1TranformTwoDCore_c, "Columns")
+#pragma unroll 1
+    for (int i = tid; i < B * TXW; i += 256) {
+        const int slot = i / TXW, c = i % TXW;
+        if (slot >= n_here) break;
+        const int blk = blk0 + slot, by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
+        const int16_t* in = a.residual + (size_t)by * TXH * a.stride + (size_t)bx * TXW + c;
         int32_t x[TXH];
         const bool ud = a.vk == K_FLIPADST;
 #pragma unroll
-        for (int r = 0; r < TXH; r++) x[r] = (int32_t)in[(size_t)(ud ? TXH - 1 - r : r) * a.stride + t] * (1 << shift0(TXW, TXH));
-        txfm1d<TXH, CC>(a.vk == K_FLIPADST ? K_ADST : a.vk, x);
-        const int c = a.hk == K_FLIPADST ? TXW - 1 - t : t;
+        for (int r = 0; r < TXH; r++) x[r] = (int32_t)in[(size_t)(ud ? TXH - 1 - r : r) * a.stride] * (1 << shift0(TXW, TXH));
+        txfm1d<TXH, CC>(ud ? K_ADST : a.vk, x);
+        int32_t* col = smem_txq + slot * SLOT + (a.hk == K_FLIPADST ? TXW - 1 - c : c);
 #pragma unroll
-        for (int r = 0; r < TXH; r++) buf[r * PITCH + c] = shift1(TXW, TXH) ? rshift_round(x[r], shift1(TXW, TXH)) : x[r];
+        for (int r = 0; r < TXH; r++) col[r * PITCH] = shift1(TXW, TXH) ? rshift_round(x[r], shift1(TXW, TXH)) : x[r];
     }
     __syncthreads();
-    // ---- horizontal pass: thread t owns row t ("Rows"), then the packed block goes back to shared memory
-    int32_t y[TXW];
-    unsigned long long dropped = 0;
-    if (on && t < TXH) {
+    // ---- horizontal pass: one item = one row of one block ("Rows"); the kept PW columns go back in place
+#pragma unroll 1
+    for (int j = tid; j < B * TXH; j += 256) {
+        const int slot = j / TXH, r = j % TXH;
+        if (slot >= n_here) break;
+        int32_t* row = smem_txq + j * PITCH;                  // == slot * SLOT + r * PITCH
+        int32_t y[TXW];
 #pragma unroll
-        for (int c = 0; c < TXW; c++) y[c] = buf[t * PITCH + c];
+        for (int c = 0; c < TXW; c++) y[c] = row[c];
         txfm1d<TXW, CR>(a.hk == K_FLIPADST ? K_ADST : a.hk, y);
 #pragma unroll
         for (int c = 0; c < TXW; c++) {
             if (shift2(TXW, TXH)) y[c] = rshift_round(y[c], shift2(TXW, TXH));
             if (RECT) y[c] = mul_sqrt2(y[c]);
         }
-        if (TXW > 32 || TXH > 32) {                // HandleTransform64x64_c & co: energy of what is dropped
+        if (G::BIG) {                                         // HandleTransform64x64_c & co: energy of what is dropped
+            unsigned long long dropped = 0;
 #pragma unroll
             for (int c = 0; c < TXW; c++)
-                if (c >= PW || t >= PH) dropped += (unsigned long long)((long long)y[c] * (long long)y[c]);
+                if (c >= PW || r >= PH) dropped += (unsigned long long)((long long)y[c] * (long long)y[c]);
+            if (dropped) atomicAdd(&s_energy[slot], dropped);
+        }
+        if (r < PH) {
+#pragma unroll
+            for (int c = 0; c < PW; c++) row[c] = y[c];
         }
     }
-    __syncthreads();
-    if (on && t < PH) {
-#pragma unroll
-        for (int c = 0; c < PW; c++) buf[t * PITCH + c] = y[c];
-    }
-    if ((TXW > 32 || TXH > 32) && dropped) atomicAdd(&s_energy[slot], dropped);
     __syncthreads();
 
-    // ---- quantisation, all T threads of the block, coalesced (aom_highbd_quantize_b*_avx2)
-    if (on) {
-        constexpr int LS = (TXW * TXH > 256) + (TXW * TXH > 1024);           // av1_get_tx_scale
-        constexpr int RND = LS ? (1 << (LS - 1)) : 0;
-        const size_t base = (size_t)blk * (PW * PH);
-        unsigned int my_eob = 0;
-        for (int rc = t; rc < PW * PH; rc += T) {
-            const int r = rc / PW, c = rc - r * PW;
-            const int32_t v = buf[r * PITCH + c];
-            if (a.coeff) a.coeff[base + rc] = v;
-            const int ac = rc != 0;
-            const int32_t zbin = (int32_t)(int16_t)((uint16_t)(a.q.zbin[ac] + RND) >> LS);
-            const int32_t round = (int32_t)(int16_t)((uint16_t)(a.q.round[ac] + RND) >> LS);
+    // ---- quantisation (aom_highbd_quantize_b*_avx2): the CTA's B * N coefficients are one contiguous run of each
+    // output array; thread tid takes elements tid, tid + 256, ... so every warp store is one full 128-byte line.
+    constexpr int LS = (TXW * TXH > 256) + (TXW * TXH > 1024);               // av1_get_tx_scale
+    constexpr int SUB = N >= 256 ? N / 256 : 1;                               // iterations per block
+    constexpr int SPI = N >= 256 ? 1 : 256 / N;                               // blocks per iteration
+    constexpr int ITER = B * N / 256;
+    const int slot0 = N >= 256 ? 0 : tid / N, rc0 = N >= 256 ? tid : tid % N;
+    const int off0 = slot0 * SLOT + (rc0 / PW) * PITCH + rc0 % PW;
+    const QuantLane ac = quant_lane<LS>(a.q, 1);
+    QuantLane first = ac;                                                     // lane of this thread's rc0 (DC for rc0 == 0)
+    if (rc0 == 0) first = quant_lane<LS>(a.q, 0);
+    int32_t isc[SUB];
+#pragma unroll
+    for (int u = 0; u < SUB; u++) isc[u] = (int32_t)__ldg(&a.iscan[rc0 + 256 * u]) + 1;
+    const size_t out0 = (size_t)blk0 * N + tid;
+    const int n_out = n_here * N;
+    unsigned int m = 0;
+#pragma unroll
+    for (int k = 0; k < ITER; k++) {
+        const int u = k % SUB;
+        const int slot = slot0 + (N >= 256 ? k / SUB : k * SPI);
+        const int off = off0 + (N >= 256 ? (k / SUB) * SLOT + u * (256 / PW) * PITCH : k * SPI * SLOT);
+        const bool live = tid + 256 * k < n_out;
+        if (u == 0) m = 0;
+        if (live) {
+            const QuantLane& L = u == 0 ? first : ac;
+            const int32_t v = smem_txq[off];
             const int32_t av = v < 0 ? -v : v;
-            int32_t q = 0, dq = 0;
-            if (av >= zbin) {
-                int32_t tq = av + round;
-                tq += (int32_t)(((int64_t)tq * a.q.quant[ac]) >> 16);
-                q = (int32_t)(((int64_t)tq * a.q.quant_shift[ac]) >> (16 - LS));
-                dq = (int32_t)((uint32_t)(q * (int32_t)a.q.dequant[ac]) >> LS);
-                if (v < 0) { q = -q; dq = -dq; }
-                if (dq != 0) my_eob = max(my_eob, (unsigned int)a.iscan[rc] + 1u);
-            }
-            if (a.qcoeff) a.qcoeff[base + rc] = q;
-            if (a.dqcoeff) a.dqcoeff[base + rc] = dq;
+            int32_t sgn = (v >> 31) | 1;
+            sgn = av >= L.zbin ? sgn : 0;
+            const int32_t t0 = av + L.round;
+            const int32_t t1 = __mulhi(t0, L.quant_hi) + t0;
+            const int32_t q = (int32_t)(((int64_t)t1 * L.qshift) >> (16 - LS));
+            const int32_t dq = (int32_t)((uint32_t)(q * L.dequant) >> LS);
+            const size_t o = out0 + 256 * k;
+            if (a.coeff) a.coeff[o] = v;
+            if (a.qcoeff) a.qcoeff[o] = q * sgn;
+            if (a.dqcoeff) a.dqcoeff[o] = dq * sgn;
+            if (dq * sgn != 0) m = max(m, (unsigned int)isc[u]);
         }
-        if (my_eob) atomicMax(&s_eob[slot], my_eob);
+        if (u == SUB - 1) {                                   // all of this thread's coefficients of block `slot` are done
+            if (N >= 32) {
+                m = __reduce_max_sync(0xffffffffu, m);
+                if ((tid & 31) == 0 && m) atomicMax(&s_eob[slot], m);
+            } else {
+                if (m) atomicMax(&s_eob[slot], m);
+            }
+        }
     }
     __syncthreads();
-    if (on && t == 0) {
-        if (a.eob) a.eob[blk] = (uint16_t)s_eob[slot];
-        if (a.energy) a.energy[blk] = s_energy[slot];
+    if (tid < n_here) {
+        if (a.eob) a.eob[blk0 + tid] = (uint16_t)s_eob[tid];
+        if (a.energy) a.energy[blk0 + tid] = s_energy[tid];
     }
 }
 
 template <int TXW, int TXH> static cudaError_t launch_one(const TxqArgs& a, cudaStream_t st) {
-    constexpr int T = cmax(TXW, TXH), B = 256 / T;
-    const int smem = B * TXH * (TXW + 1) * (int)sizeof(int32_t);
+    constexpr int B = TxqGeom<TXW, TXH>::B;
+    const int smem = TxqGeom<TXW, TXH>::SMEM;
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(txq_kernel<TXW, TXH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
