@@ -12,7 +12,7 @@ import bench  # noqa: E402
 
 pkg = importlib.import_module("svt-av1-1_b200")
 cases = sys.argv[1:] or ["4x4/0", "8x8/0", "16x16/3", "32x32/0", "64x64/0", "16x64/0"]
-planes = 2
+planes = int(os.environ.get("TXQ_PLANES", "8"))
 res = bench.txq_residual(11, planes)
 dev = torch.from_numpy(res).cuda()
 npix = res.size

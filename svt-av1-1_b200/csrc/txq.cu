@@ -78,23 +78,91 @@ template <int TXW, int TXH> struct TxqGeom {
     static constexpr int PW = cmin(TXW, 32), PH = cmin(TXH, 32), N = PW * PH;
     static constexpr int SMEM = B * SLOT * (int)sizeof(int32_t);
     static constexpr bool BIG = TXW == 64 || TXH == 64;
+    // resident CTAs per SM the register allocation is held to (256 threads each)
+    static constexpr int MIN_CTAS = BIG ? 2 : TXW * TXH <= 32 ? 8 : TXW * TXH <= 128 ? 6 : TXW * TXH <= 256 ? 4 : 3;
 };
 
-struct QuantLane { int32_t zbin, round, quant_hi, qshift, dequant; };    // one lane (DC or AC) of the quantiser
+__device__ __forceinline__ int32_t mul_shift(int32_t x, int32_t y, int sh) {   // (int64(x) * y) >> sh, low 32 bits
+    int64_t p;
+    asm("mul.wide.s32 %0, %1, %2;" : "=l"(p) : "r"(x), "r"(y));
+    return (int32_t)(p >> sh);
+}
+__device__ __forceinline__ int32_t top_bit_plus1(unsigned int bits) {            // 0 for 0, else 1 + index of the highest set bit
+    int32_t r;
+    asm("bfind.u32 %0, %1;" : "=r"(r) : "r"(bits));
+    return r + 1;
+}
 
-template <int LS> __device__ __forceinline__ QuantLane quant_lane(const SvtTxqQuant& q, int ac) {
-    constexpr int RND = LS ? (1 << (LS - 1)) : 0;
-    QuantLane l;
-    l.zbin = (int32_t)(int16_t)((uint16_t)((ac ? q.zbin[1] : q.zbin[0]) + RND) >> LS);
-    l.round = (int32_t)(int16_t)((uint16_t)((ac ? q.round[1] : q.round[0]) + RND) >> LS);
-    l.quant_hi = (int32_t)(ac ? q.quant[1] : q.quant[0]) << 16;           // (t * quant) >> 16 == mulhi(t, quant << 16)
-    l.qshift = ac ? q.quant_shift[1] : q.quant_shift[0];
-    l.dequant = ac ? q.dequant[1] : q.dequant[0];
-    return l;
+// Quantisation of the CTA's packed coefficients (aom_highbd_quantize_b*_avx2). The B * N coefficients of a CTA are one
+// contiguous run of each output array; warp w owns the w-th eighth of it and walks it 32 coefficients at a time, so
+// every warp store is one full 128-byte line and (for B >= 8) a transform block never leaves its warp: eob is a
+// per-lane running maximum of (iscan + 1) over non-zero dequantised values, reduced once per block.
+template <int TXW, int TXH, bool FULL>
+__device__ __forceinline__ void quant_phase(const TxqArgs& a, const int32_t* smem, unsigned int* s_eob, int blk0, int n_here) {
+    using G = TxqGeom<TXW, TXH>;
+    constexpr int B = G::B, PITCH = G::PITCH, SLOT = G::SLOT, PW = G::PW, N = G::N;
+    constexpr int LS = (TXW * TXH > 256) + (TXW * TXH > 1024);               // av1_get_tx_scale
+    constexpr int WARP_COEFS = B * N / 8, ITER = WARP_COEFS / 32;
+    constexpr bool OWNED = WARP_COEFS >= N;                                   // whole blocks per warp
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot_base = (warp * WARP_COEFS) / N, rc_base = (warp * WARP_COEFS) % N;
+    // blocks of up to 32 coefficients: lane l takes the l-th coefficient in SCAN order (the store still fills one
+    // line), so eob falls out of a ballot; larger blocks: raster order and a running maximum of iscan + 1
+    constexpr bool BALLOT = N <= 32;
+    const int rc_l = BALLOT ? (int)__ldg(a.scan + lane % N) : lane;
+    const int soff0 = (slot_base + (N >= 32 ? 0 : lane / N)) * SLOT + (rc_base / PW + rc_l / PW) * PITCH + rc_l % PW;
+    const int16_t* isc_ptr = a.iscan + rc_base + lane;
+    const TxqLane ac = a.ac;
+    TxqLane first = ac;                                                       // lane used where the block's scan restarts
+    if (rc_base == 0 && rc_l == 0) first = a.dc;
+    const size_t out0 = (size_t)blk0 * N + warp * WARP_COEFS + (BALLOT ? (lane / N) * N + rc_l : lane);
+    const int n_out = n_here * N - warp * WARP_COEFS - (BALLOT ? (lane / N) * N : lane);   // coefficients from this lane's first one on
+    // outer loop: one block (or 32 / N blocks of a 4x4 size, or this warp's share of a 64x64 block) per trip
+    constexpr int SUBS = N < 32 ? 1 : OWNED ? N / 32 : WARP_COEFS / 32, OUTER = ITER / SUBS;
+    constexpr int SLOTS_PER_TRIP = N >= 32 ? 1 : 32 / N;
+    constexpr int UNROLL_OUTER = SUBS >= 8 ? 1 : (8 / SUBS < OUTER ? 8 / SUBS : OUTER);
+#pragma unroll(UNROLL_OUTER)
+    for (int s = 0; s < OUTER; s++) {
+        const int32_t* src = smem + soff0 + s * SLOTS_PER_TRIP * SLOT;
+        const size_t o_s = out0 + (size_t)s * 32 * SUBS;
+        unsigned int m = 0;
+#pragma unroll(SUBS < 8 ? SUBS : 8)
+        for (int u = 0; u < SUBS; u++) {
+            if (FULL || s * 32 * SUBS + 32 * u < n_out) {
+                const TxqLane& L = u == 0 ? first : ac;
+                const int32_t v = src[((32 * u) / PW) * PITCH];
+                const int32_t isc = BALLOT ? 1 : (int32_t)__ldg(isc_ptr + 32 * u) + 1;
+                const int32_t av = v < 0 ? -v : v;
+                int32_t sgn = (v >> 31) | 1;
+                sgn = av >= L.zbin ? sgn : 0;
+                const int32_t t0 = av + L.round;
+                const int32_t t1 = __mulhi(t0, L.quant_hi) + t0;
+                const int32_t q = mul_shift(t1, L.qshift, 16 - LS);
+                const int32_t dq = (int32_t)((uint32_t)(q * L.dequant) >> LS);
+                const int32_t dqs = dq * sgn;
+                const size_t o = o_s + 32 * u;
+                if (FULL || a.coeff) a.coeff[o] = v;
+                if (FULL || a.qcoeff) a.qcoeff[o] = q * sgn;
+                if (FULL || a.dqcoeff) a.dqcoeff[o] = dqs;
+                m = max(m, dqs != 0 ? (unsigned int)isc : 0u);
+            }
+        }
+        const int slot = slot_base + s * SLOTS_PER_TRIP;
+        if (BALLOT) {
+            const unsigned int nz = __ballot_sync(0xffffffffu, m != 0);
+            if (lane < SLOTS_PER_TRIP) {
+                const unsigned int bits = N == 32 ? nz : (nz >> (lane * (N & 31))) & ((1u << (N & 31)) - 1u);
+                s_eob[slot + lane] = top_bit_plus1(bits);
+            }
+        } else {
+            m = __reduce_max_sync(0xffffffffu, m);
+            if (lane == 0) { if (OWNED) s_eob[slot] = m; else if (m) atomicMax(&s_eob[slot], m); }
+        }
+    }
 }
 
 template <int TXW, int TXH>
-__global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::BIG ? 2 : 1) txq_kernel(const TxqArgs a) {
+__global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(const TxqArgs a) {
     using G = TxqGeom<TXW, TXH>;
     constexpr int B = G::B, PITCH = G::PITCH, SLOT = G::SLOT, PW = G::PW, PH = G::PH, N = G::N;
     constexpr int CC = kCosCol[ilog2(TXW) - 2][ilog2(TXH) - 2], CR = kCosRow[ilog2(TXW) - 2][ilog2(TXH) - 2];
@@ -108,10 +176,10 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::BIG ? 2 : 1) txq_kerne
     if (tid < B) { s_eob[tid] = 0; s_energy[tid] = 0; }
 
     // ---- vertical pass: one item = one column of one block (Av1TranformTwoDCore_c, "Columns")
-#pragma unroll 1
+#pragma unroll
     for (int i = tid; i < B * TXW; i += 256) {
         const int slot = i / TXW, c = i % TXW;
-        if (slot >= n_here) break;
+        if (slot >= n_here) continue;
         const int blk = blk0 + slot, by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
         const int16_t* in = a.residual + (size_t)by * TXH * a.stride + (size_t)bx * TXW + c;
         int32_t x[TXH];
@@ -125,10 +193,10 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::BIG ? 2 : 1) txq_kerne
     }
     __syncthreads();
     // ---- horizontal pass: one item = one row of one block ("Rows"); the kept PW columns go back in place
-#pragma unroll 1
+#pragma unroll
     for (int j = tid; j < B * TXH; j += 256) {
         const int slot = j / TXH, r = j % TXH;
-        if (slot >= n_here) break;
+        if (slot >= n_here) continue;
         int32_t* row = smem_txq + j * PITCH;                  // == slot * SLOT + r * PITCH
         int32_t y[TXW];
 #pragma unroll
@@ -153,55 +221,9 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::BIG ? 2 : 1) txq_kerne
     }
     __syncthreads();
 
-    // ---- quantisation (aom_highbd_quantize_b*_avx2): the CTA's B * N coefficients are one contiguous run of each
-    // output array; thread tid takes elements tid, tid + 256, ... so every warp store is one full 128-byte line.
-    constexpr int LS = (TXW * TXH > 256) + (TXW * TXH > 1024);               // av1_get_tx_scale
-    constexpr int SUB = N >= 256 ? N / 256 : 1;                               // iterations per block
-    constexpr int SPI = N >= 256 ? 1 : 256 / N;                               // blocks per iteration
-    constexpr int ITER = B * N / 256;
-    const int slot0 = N >= 256 ? 0 : tid / N, rc0 = N >= 256 ? tid : tid % N;
-    const int off0 = slot0 * SLOT + (rc0 / PW) * PITCH + rc0 % PW;
-    const QuantLane ac = quant_lane<LS>(a.q, 1);
-    QuantLane first = ac;                                                     // lane of this thread's rc0 (DC for rc0 == 0)
-    if (rc0 == 0) first = quant_lane<LS>(a.q, 0);
-    int32_t isc[SUB];
-#pragma unroll
-    for (int u = 0; u < SUB; u++) isc[u] = (int32_t)__ldg(&a.iscan[rc0 + 256 * u]) + 1;
-    const size_t out0 = (size_t)blk0 * N + tid;
-    const int n_out = n_here * N;
-    unsigned int m = 0;
-#pragma unroll
-    for (int k = 0; k < ITER; k++) {
-        const int u = k % SUB;
-        const int slot = slot0 + (N >= 256 ? k / SUB : k * SPI);
-        const int off = off0 + (N >= 256 ? (k / SUB) * SLOT + u * (256 / PW) * PITCH : k * SPI * SLOT);
-        const bool live = tid + 256 * k < n_out;
-        if (u == 0) m = 0;
-        if (live) {
-            const QuantLane& L = u == 0 ? first : ac;
-            const int32_t v = smem_txq[off];
-            const int32_t av = v < 0 ? -v : v;
-            int32_t sgn = (v >> 31) | 1;
-            sgn = av >= L.zbin ? sgn : 0;
-            const int32_t t0 = av + L.round;
-            const int32_t t1 = __mulhi(t0, L.quant_hi) + t0;
-            const int32_t q = (int32_t)(((int64_t)t1 * L.qshift) >> (16 - LS));
-            const int32_t dq = (int32_t)((uint32_t)(q * L.dequant) >> LS);
-            const size_t o = out0 + 256 * k;
-            if (a.coeff) a.coeff[o] = v;
-            if (a.qcoeff) a.qcoeff[o] = q * sgn;
-            if (a.dqcoeff) a.dqcoeff[o] = dq * sgn;
-            if (dq * sgn != 0) m = max(m, (unsigned int)isc[u]);
-        }
-        if (u == SUB - 1) {                                   // all of this thread's coefficients of block `slot` are done
-            if (N >= 32) {
-                m = __reduce_max_sync(0xffffffffu, m);
-                if ((tid & 31) == 0 && m) atomicMax(&s_eob[slot], m);
-            } else {
-                if (m) atomicMax(&s_eob[slot], m);
-            }
-        }
-    }
+    // ---- quantisation: fast path when every block of the CTA exists and all three coefficient arrays are wanted
+    if (n_here == B && a.coeff && a.qcoeff && a.dqcoeff) quant_phase<TXW, TXH, true>(a, smem_txq, s_eob, blk0, n_here);
+    else quant_phase<TXW, TXH, false>(a, smem_txq, s_eob, blk0, n_here);
     __syncthreads();
     if (tid < n_here) {
         if (a.eob) a.eob[blk0 + tid] = (uint16_t)s_eob[tid];

@@ -75,9 +75,12 @@ static int32_t get_iscan(SvtTxqContext* ctx, int txw, int txh, int tx_type, cons
     auto it = ctx->iscan.find(key);
     if (it == ctx->iscan.end()) {
         const std::vector<int16_t> inv = make_iscan(txw, txh, tx_type);
+        std::vector<int16_t> both(inv);                           // inverse scan followed by the scan itself
+        both.resize(2 * inv.size());
+        for (size_t i = 0; i < inv.size(); i++) both[inv.size() + (size_t)inv[i]] = (int16_t)i;
         int16_t* d = nullptr;
-        TQ(cudaMalloc(&d, inv.size() * sizeof(int16_t)));
-        TQ(cudaMemcpyAsync(d, inv.data(), inv.size() * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->stream));
+        TQ(cudaMalloc(&d, both.size() * sizeof(int16_t)));
+        TQ(cudaMemcpyAsync(d, both.data(), both.size() * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->stream));
         TQ(cudaStreamSynchronize(ctx->stream));                  // `inv` is pageable and dies with this scope
         it = ctx->iscan.emplace(key, d).first;
     }
@@ -136,9 +139,19 @@ int32_t svttxq_fwd_txfm_quant_device(SvtTxqContext* ctx, const int16_t* d_residu
     TxqArgs a;
     a.residual = d_residual; a.stride = stride; a.blocks_x = width / txw; a.n_blocks = a.blocks_x * (height / txh);
     a.vk = kVertical[tx_type]; a.hk = kHorizontal[tx_type];
-    a.q = *quant;
+    const int ls = (txw * txh > 256) + (txw * txh > 1024);       // av1_get_tx_scale
+    const int rnd = ls ? (1 << (ls - 1)) : 0;
+    for (int i = 0; i < 2; i++) {
+        TxqLane& l = i ? a.ac : a.dc;
+        l.zbin = (int32_t)(int16_t)((uint16_t)(quant->zbin[i] + rnd) >> ls);
+        l.round = (int32_t)(int16_t)((uint16_t)(quant->round[i] + rnd) >> ls);
+        l.quant_hi = (int32_t)((uint32_t)(int32_t)quant->quant[i] << 16);
+        l.qshift = quant->quant_shift[i];
+        l.dequant = quant->dequant[i];
+    }
     const int32_t rc = get_iscan(ctx, txw, txh, tx_type, &a.iscan);
     if (rc != SVTME_OK) return rc;
+    a.scan = a.iscan + (size_t)(txw < 32 ? txw : 32) * (txh < 32 ? txh : 32);
     a.coeff = d_coeff; a.qcoeff = d_qcoeff; a.dqcoeff = d_dqcoeff; a.eob = d_eob; a.energy = (unsigned long long*)d_energy;
     ctx->launches++;
     TQ(launch_txq(txw, txh, a, ctx->stream));
