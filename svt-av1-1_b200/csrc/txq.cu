@@ -175,17 +175,19 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(c
     const int n_here = min(B, a.n_blocks - blk0);            // blocks of this CTA that exist
     if (tid < B) { s_eob[tid] = 0; s_energy[tid] = 0; }
 
+    const int by0 = blk0 / a.blocks_x, bx0 = blk0 - by0 * a.blocks_x;
     // ---- vertical pass: one item = one column of one block (Av1TranformTwoDCore_c, "Columns")
 #pragma unroll
     for (int i = tid; i < B * TXW; i += 256) {
         const int slot = i / TXW, c = i % TXW;
         if (slot >= n_here) continue;
-        const int blk = blk0 + slot, by = blk / a.blocks_x, bx = blk - by * a.blocks_x;
+        int bx = bx0 + slot, by = by0;                        // block (blk0 + slot) of the raster
+        while (bx >= a.blocks_x) { bx -= a.blocks_x; by++; }
         const int16_t* in = a.residual + (size_t)by * TXH * a.stride + (size_t)bx * TXW + c;
         int32_t x[TXH];
         const bool ud = a.vk == K_FLIPADST;
 #pragma unroll
-        for (int r = 0; r < TXH; r++) x[r] = (int32_t)in[(size_t)(ud ? TXH - 1 - r : r) * a.stride] * (1 << shift0(TXW, TXH));
+        for (int r = 0; r < TXH; r++) x[r] = (int32_t)__ldg(in + (size_t)(ud ? TXH - 1 - r : r) * a.stride) * (1 << shift0(TXW, TXH));
         txfm1d<TXH, CC>(ud ? K_ADST : a.vk, x);
         int32_t* col = smem_txq + slot * SLOT + (a.hk == K_FLIPADST ? TXW - 1 - c : c);
 #pragma unroll
