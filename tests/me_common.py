@@ -236,7 +236,7 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 
 
 def golden_cases():
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz"))
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("txq_"))
 
 
 def load_golden(name):
