@@ -173,7 +173,7 @@ def run_reference_impl(args, rank):
         return
     frames = synth_sequence(17, seed=1)
     arm = CpuArm(frames)
-    n_tasks = max(16, 4 * arm.cores)
+    n_tasks = max(32, 8 * arm.cores)
     for _ in range(args.warmup):
         arm.run(arm.cores)                                 # warm-up also fills each worker's pyramid cache
     times = [arm.run(n_tasks) for _ in range(args.steps)]
@@ -228,7 +228,7 @@ def run_gpu_impl(args, rank, world, local_rank):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         frames17 = synth_sequence(17, seed=1)
         arm = CpuArm(frames17)
-        n_tasks = max(32, 8 * arm.cores)                   # ~20-30 CPU-seconds of the reference's ME
+        n_tasks = max(64, 24 * arm.cores)                  # ~6 s wall of the reference's ME on every host core
         arm.run(arm.cores)
         t = arm.run(n_tasks)
         arm.close()
@@ -363,7 +363,7 @@ TXQ_SIZES = [(4, 4), (8, 8), (16, 16), (32, 32), (64, 64), (4, 8), (8, 4), (8, 1
              (64, 32), (4, 16), (16, 4), (8, 32), (32, 8), (16, 64), (64, 16)]
 TXQ_PLANES = 8                                     # 1080p residual planes stacked per launch (outputs 200 MB > L2)
 TXQ_W, TXQ_H = 1920, 1088
-TXQ_CPU_REPS = 16                                  # repetitions of one 1920x128 strip per CPU task
+TXQ_CPU_REPS = 32                                  # repetitions of one 1920x128 strip per CPU task
 
 
 def txq_cases():
@@ -517,9 +517,12 @@ def run_txq(args, rank, world, local_rank):
         ctx.fwd_txfm_quant_device(dev.data_ptr(), TXQ_W, TXQ_W, Hs, c[0], c[1], c[2], quant, d_out[0].data_ptr(), d_out[1].data_ptr(),
                                   d_out[2].data_ptr(), d_eob.data_ptr(), d_en.data_ptr())
 
-    def host_call(c):
+    def host_call(c, everything=True):
+        """everything: all five outputs (what Av1EstimateTransform + the quantiser produce); else the subset EncDec consumes
+        after quantisation (quantised levels for entropy coding, dequantised for reconstruction, eob)."""
         rc = ctx.lib.svttxq_fwd_txfm_quant(ctx._h, host.data_ptr(), TXQ_W, TXQ_W, Hs, c[0], c[1], c[2], C.byref(quant),
-                                           h_out[0].data_ptr(), h_out[1].data_ptr(), h_out[2].data_ptr(), h_eob.data_ptr(), h_en.data_ptr())
+                                           h_out[0].data_ptr() if everything else None, h_out[1].data_ptr(), h_out[2].data_ptr(),
+                                           h_eob.data_ptr(), h_en.data_ptr() if everything else None)
         assert rc == 0
 
     def sync_all():
@@ -565,10 +568,16 @@ def run_txq(args, rank, world, local_rank):
             host_call(c)
     sync_all()
     ms_e2e = (time.perf_counter() - t0) * 1e3
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        for c in cases:
+            host_call(c, everything=False)
+    sync_all()
+    ms_e2e_sub = (time.perf_counter() - t0) * 1e3
     if dist is not None:
-        t = torch.tensor([ms, ms_e2e], device="cuda")
+        t = torch.tensor([ms, ms_e2e, ms_e2e_sub], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = float(t[0].item()), float(t[1].item())
+        ms, ms_e2e, ms_e2e_sub = float(t[0].item()), float(t[1].item()), float(t[2].item())
     checksum = int(h_out[1].sum(dtype=torch.int64).item())
     ctx.close()
     if rank == 0:
@@ -598,6 +607,9 @@ def run_txq(args, rank, world, local_rank):
                 "data": "synthetic", "config": txq_config(world),
                 "e2e": {"value": v_e2e, "unit": "Mpixel/s", "h2d_bytes_per_step": 2 * npix * len(cases), "d2h_bytes_per_step": pw_bytes,
                         "ms_per_step": ms_e2e / e2e_steps, "timing": "host wall clock around synchronous svttxq_fwd_txfm_quant calls"},
+                "e2e_encdec_outputs": {"value": world * npix * len(cases) * e2e_steps / (ms_e2e_sub / 1e3) / 1e6, "unit": "Mpixel/s",
+                                       "outputs": "qcoeff + dqcoeff + eob (coeff and energy not copied back)",
+                                       "d2h_bytes_per_step": sum(8 * (npix // (w * h)) * min(w, 32) * min(h, 32) + 2 * (npix // (w * h)) for (w, h, _) in cases)},
                 "gpu_launches": int(launches),
                 "roofline": {"kernel": "txq_kernel<*>", "bound": "hbm", "achieved": tot_bytes / tot_ms / 1e6, "peak": hbm_peak, "unit": "GB/s",
                              "frac": tot_bytes / tot_ms / 1e6 / hbm_peak, "traffic": None,

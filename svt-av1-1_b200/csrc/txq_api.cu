@@ -21,7 +21,9 @@ static const uint8_t kHorizontal[16] = { K_DCT, K_DCT, K_ADST, K_ADST, K_DCT, K_
 
 struct SvtTxqContext {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;            // kernels + device-to-host copies
+    cudaStream_t copy_in = nullptr;           // host-to-device copies of the host-buffer entry point
+    cudaEvent_t in_done[8] = {};              // chunk i of the residual has arrived
     int64_t launches = 0;
     std::string err;
     std::map<int, int16_t*> iscan;         // (txw, txh, scan class) -> device inverse scan table
@@ -112,6 +114,8 @@ int32_t svttxq_create(SvtTxqContext** out, int32_t device) {
     *out = ctx;
     TQ(cudaSetDevice(device));
     TQ(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    TQ(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+    for (auto& e : ctx->in_done) TQ(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     return SVTME_OK;
 }
 
@@ -122,6 +126,8 @@ void svttxq_destroy(SvtTxqContext* ctx) {
     for (auto& kv : ctx->iscan) cudaFree(kv.second);
     cudaFree(ctx->d_in); cudaFree(ctx->d_out);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+    for (auto& e : ctx->in_done) if (e) cudaEventDestroy(e);
     delete ctx;
 }
 
@@ -186,17 +192,34 @@ int32_t svttxq_fwd_txfm_quant(SvtTxqContext* ctx, const int16_t* residual, int32
     uint8_t* o = (uint8_t*)ctx->d_out;
     int32_t* d_coeff = (int32_t*)o; int32_t* d_q = (int32_t*)(o + plane); int32_t* d_dq = (int32_t*)(o + 2 * plane);
     uint64_t* d_energy = (uint64_t*)(o + 3 * plane); uint16_t* d_eob = (uint16_t*)(o + 3 * plane + energy_bytes);
-    TQ(cudaMemcpyAsync(ctx->d_in, residual, (size_t)stride * (height - 1) * sizeof(int16_t) + (size_t)width * sizeof(int16_t),
-                       cudaMemcpyHostToDevice, ctx->stream));
-    const int32_t rc = svttxq_fwd_txfm_quant_device(ctx, (const int16_t*)ctx->d_in, stride, width, height, txw, txh, tx_type, quant,
-                                                    coeff ? d_coeff : nullptr, qcoeff ? d_q : nullptr, dqcoeff ? d_dq : nullptr,
-                                                    eob ? d_eob : nullptr, energy ? d_energy : nullptr);
-    if (rc != SVTME_OK) return rc;
-    if (coeff) TQ(cudaMemcpyAsync(coeff, d_coeff, n_blocks * per * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    if (qcoeff) TQ(cudaMemcpyAsync(qcoeff, d_q, n_blocks * per * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    if (dqcoeff) TQ(cudaMemcpyAsync(dqcoeff, d_dq, n_blocks * per * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    if (eob) TQ(cudaMemcpyAsync(eob, d_eob, n_blocks * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
-    if (energy) TQ(cudaMemcpyAsync(energy, d_energy, n_blocks * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    // Block rows go through in up to 8 chunks: the upload of chunk i+1 (copy_in stream) runs against the download of
+    // chunk i (main stream), so both directions of the link are busy at once.
+    const int block_rows = height / txh, blocks_x = width / txw;
+    int n_chunks = (int)(((size_t)width * height) >> 21);             // ~2 Mpixel per chunk
+    n_chunks = n_chunks < 1 ? 1 : n_chunks > 8 ? 8 : n_chunks;
+    if (n_chunks > block_rows) n_chunks = block_rows;
+    for (int c = 0; c < n_chunks; c++) {
+        const int r0 = (int)((int64_t)block_rows * c / n_chunks), r1 = (int)((int64_t)block_rows * (c + 1) / n_chunks);
+        const size_t first = (size_t)r0 * txh * stride;
+        const size_t elems = (size_t)((r1 - r0) * txh - 1) * stride + width;
+        TQ(cudaMemcpyAsync((int16_t*)ctx->d_in + first, residual + first, elems * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->copy_in));
+        TQ(cudaEventRecord(ctx->in_done[c], ctx->copy_in));
+    }
+    for (int c = 0; c < n_chunks; c++) {
+        const int r0 = (int)((int64_t)block_rows * c / n_chunks), r1 = (int)((int64_t)block_rows * (c + 1) / n_chunks);
+        const size_t b0 = (size_t)r0 * blocks_x, nb = (size_t)(r1 - r0) * blocks_x;
+        TQ(cudaStreamWaitEvent(ctx->stream, ctx->in_done[c], 0));
+        const int32_t rc = svttxq_fwd_txfm_quant_device(ctx, (const int16_t*)ctx->d_in + (size_t)r0 * txh * stride, stride, width, (r1 - r0) * txh,
+                                                        txw, txh, tx_type, quant, coeff ? d_coeff + b0 * per : nullptr,
+                                                        qcoeff ? d_q + b0 * per : nullptr, dqcoeff ? d_dq + b0 * per : nullptr,
+                                                        eob ? d_eob + b0 : nullptr, energy ? d_energy + b0 : nullptr);
+        if (rc != SVTME_OK) return rc;
+        if (coeff) TQ(cudaMemcpyAsync(coeff + b0 * per, d_coeff + b0 * per, nb * per * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (qcoeff) TQ(cudaMemcpyAsync(qcoeff + b0 * per, d_q + b0 * per, nb * per * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (dqcoeff) TQ(cudaMemcpyAsync(dqcoeff + b0 * per, d_dq + b0 * per, nb * per * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (eob) TQ(cudaMemcpyAsync(eob + b0, d_eob + b0, nb * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (energy) TQ(cudaMemcpyAsync(energy + b0, d_energy + b0, nb * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    }
     TQ(cudaStreamSynchronize(ctx->stream));
     return SVTME_OK;
 }
