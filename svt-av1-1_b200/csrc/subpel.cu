@@ -21,7 +21,12 @@ namespace svtme {
 constexpr int kSpThreads = 256;
 constexpr int kPlRows = 134;            // 64 + 63 + 7
 constexpr int kPlPitchW = 36;           // words (144 bytes >= 64 + 70 + one spare word for the last B taps)
-constexpr int kPlWords = kPlRows * kPlPitchW;
+constexpr int kPlWords = kPlRows * kPlPitchW + 132;  // + room for the row skew below
+// Word offset of window row r. Rows 8 apart would land on the same bank (8 * 36 = 9 * 32); the (monotonic) skew
+// moves each group of eight rows by 1 or 15 banks more than the previous one, so that the 8x4 blocks a warp reads
+// together (two words apart along x, eight rows apart along y) touch 32 different banks when they share a motion
+// vector: bank offsets of the four block rows are {0, 1, 16, 17} or {0, 15, 16, 31}.
+__device__ __forceinline__ int plane_row(int r) { return r * kPlPitchW + ((r >> 3) & 1) + (r & ~15); }
 constexpr int kMargin = 3;              // window starts 3 pixels left/above the search-area origin
 
 struct SpShared {
@@ -84,7 +89,7 @@ __device__ __forceinline__ void pu_blocks(int pu, int& L, int& bx, int& by, int&
 
 // 8 bytes at byte column c of row r of a plane (unaligned)
 __device__ __forceinline__ uint2 load8(const uint32_t* plane, int r, int c) {
-    const uint32_t* w = plane + r * kPlPitchW + (c >> 2);
+    const uint32_t* w = plane + plane_row(r) + (c >> 2);
     const uint32_t sh = (c & 3) * 8;
     const uint32_t a = w[0], b = w[1], d = w[2];
     return make_uint2(__funnelshift_r(a, b, sh), __funnelshift_r(b, d, sh));
@@ -123,6 +128,19 @@ __device__ __forceinline__ bool quarter_valid(int method, int dir, int k) {
     return dir == centre || dir == ((centre + 1) & 7) || dir == ((centre + 7) & 7);
 }
 
+// Lanes of a warp = 8x4 blocks (bx = lane & 7, by = lane >> 3) of one level L (warp-uniform). Sum over the blocks of
+// each PU that lie in this warp: all 32 for 64x64, 4x4 for 32x32, 2x2 for 16x16, the block itself for 8x8.
+__device__ __forceinline__ uint32_t pu_sum(uint32_t v, int L) {
+    if (L == 0) return __reduce_add_sync(0xffffffffu, v);
+    if (L == 3) return v;
+    v += __shfl_xor_sync(0xffffffffu, v, 1); v += __shfl_xor_sync(0xffffffffu, v, 8);
+    if (L == 1) { v += __shfl_xor_sync(0xffffffffu, v, 2); v += __shfl_xor_sync(0xffffffffu, v, 16); }
+    return v;
+}
+__device__ __forceinline__ bool pu_leader(int L, int lane) {
+    return L == 0 ? lane == 0 : L == 1 ? (lane & 0x1B) == 0 : L == 2 ? (lane & 0x09) == 0 : true;
+}
+
 __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SpShared& sh = *reinterpret_cast<SpShared*>(smem_raw);
@@ -143,55 +161,105 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     for (int t = tid; t < 64 * 16; t += kSpThreads)
         sh.src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + (t >> 4)));
     if (tid < kNumPu) { sh.pu_sad[tid] = scr.best_sad[list][tid]; sh.pu_mv[tid] = scr.best_mv[list][tid]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
+    const uint32_t inv_ww = 0xFFFFFFFFu / (uint32_t)ww + 1u;   // t / ww == umulhi(t, inv_ww) for t * ww < 2^32
     for (int t = tid; t < wr * ww; t += kSpThreads) {
-        const int r = t / ww, c = t - r * ww;
-        sh.plane[S_A][r * kPlPitchW + c] = ldg_u32_unaligned(rp.at(ox + sax - kMargin + 4 * c, oy + say - kMargin + r));
+        const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
+        sh.plane[S_A][plane_row(r) + c] = ldg_u32_unaligned(rp.at(ox + sax - kMargin + 4 * c, oy + say - kMargin + r));
     }
     __syncthreads();
     if (p.use_subpel == 1) {
-        // ---- planes B (horizontal) and H (vertical) from A; then J (vertical) from B
+        // ---- plane B (horizontal filter of A): B(x) = f(A[x-1], A[x], A[x+1], A[x+2]) on every word but the last
         for (int t = tid; t < wr * ww; t += kSpThreads) {
-            const int r = t / ww, c = t - r * ww;
-            const uint32_t* a = sh.plane[S_A] + r * kPlPitchW + c;
-            if (c >= 1 && c < ww - 1) {                   // B(x) = f(A[x-1], A[x], A[x+1], A[x+2])
-                const uint32_t w0 = a[-1], w1 = a[0], w2 = a[1];
-                sh.plane[S_B][r * kPlPitchW + c] = filt4(__funnelshift_r(w0, w1, 24), w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16));
-            } else if (c == 0) {
+            const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
+            const uint32_t* a = sh.plane[S_A] + plane_row(r) + c;
+            if (c < ww - 1) {
                 const uint32_t w1 = a[0], w2 = a[1];
-                sh.plane[S_B][r * kPlPitchW] = filt4(w1 << 8, w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16));
+                const uint32_t left = c ? __funnelshift_r(a[-1], w1, 24) : w1 << 8;
+                sh.plane[S_B][plane_row(r) + c] = filt4(left, w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16));
             }
-            if (r >= 1 && r < wr - 2)                     // H(y) = f(A[y-1], A[y], A[y+1], A[y+2])
-                sh.plane[S_H][r * kPlPitchW + c] = filt4(a[-kPlPitchW], a[0], a[kPlPitchW], a[2 * kPlPitchW]);
         }
         __syncthreads();
-        for (int t = tid; t < wr * ww; t += kSpThreads) {
-            const int r = t / ww, c = t - r * ww;
-            const uint32_t* b = sh.plane[S_B] + r * kPlPitchW + c;
-            if (r >= 1 && r < wr - 2)
-                sh.plane[S_J][r * kPlPitchW + c] = filt4(b[-kPlPitchW], b[0], b[kPlPitchW], b[2 * kPlPitchW]);
+        // ---- planes H (vertical filter of A) and J (vertical filter of B): each thread slides a four-row window down
+        // one word column over its share of the rows, so every row is read once: X(y) = f(X[y-1], X[y], X[y+1], X[y+2])
+        {
+            const int chunk = (int)__umulhi((uint32_t)tid, inv_ww), c = tid - chunk * ww;
+            const int n_chunks = kSpThreads / ww, rows = wr - 3;                 // output rows 1 .. wr-3
+            const int per = (rows + n_chunks - 1) / n_chunks;
+            const int r0 = 1 + chunk * per, r1 = min(r0 + per, wr - 2);
+            if (chunk < n_chunks && r0 < r1) {
+                const uint32_t* pa = sh.plane[S_A] + c; const uint32_t* pb = sh.plane[S_B] + c;
+                uint32_t a0 = pa[plane_row(r0 - 1)], a1 = pa[plane_row(r0)], a2 = pa[plane_row(r0 + 1)];
+                uint32_t b0 = pb[plane_row(r0 - 1)], b1 = pb[plane_row(r0)], b2 = pb[plane_row(r0 + 1)];
+#pragma unroll 2
+                for (int r = r0; r < r1; r++) {
+                    const int o2 = plane_row(r + 2), o = plane_row(r);
+                    const uint32_t a3 = pa[o2], b3 = pb[o2];
+                    sh.plane[S_H][o + c] = filt4(a0, a1, a2, a3);
+                    sh.plane[S_J][o + c] = filt4(b0, b1, b2, b3);
+                    a0 = a1; a1 = a2; a2 = a3; b0 = b1; b1 = b2; b2 = b3;
+                }
+            }
         }
         __syncthreads();
 
         for (int t = tid; t < 9 * kNumPu; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
-        // ---- half-pel: (level, block, candidate) tasks -> wrapping-SSD and SAD summed per (candidate, PU)
-        for (int t = tid; t < 4 * 64 * 9; t += kSpThreads) {
-            const int k = t % 9, blk = (t / 9) & 63, L = t / (9 * 64);
-            const int bx = blk & 7, by = blk >> 3;
+        // ---- half-pel: one thread per (level, 8x8 block) walks the ten plane rows its nine candidates share
+        // (L/R read the same three B words per row, T/B the same H rows, the four diagonals the same J rows and words);
+        // wrapping-SSD and SAD are summed per (candidate, PU) with shared atomics
+        for (int t = tid; t < 4 * 64; t += kSpThreads) {
+            const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
             const int pu = pu_of_block(L, bx, by);
             const uint32_t mv = sh.pu_imv[pu];
-            const int X = kMargin + (mv_x(mv) >> 2) - sax + bx * 8 + kHalf[k][1];
-            const int Y = kMargin + (mv_y(mv) >> 2) - say + by * 8 + kHalf[k][2];
-            const uint32_t* pl = sh.plane[kHalf[k][0]];
-            uint32_t ssd = 0, sad = 0;
+            const int X = kMargin + (mv_x(mv) >> 2) - sax + bx * 8, Y = kMargin + (mv_y(mv) >> 2) - say + by * 8;
+            const int wa = X >> 2, wb = (X - 1) >> 2;
+            const uint32_t sa = (X & 3) * 8, sb_ = ((X - 1) & 3) * 8;
+            uint2 src[8];
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const uint2 c = load8(pl, Y + r, X);
-                const uint32_t s0 = sh.src[(by * 8 + r) * 16 + bx * 2], s1 = sh.src[(by * 8 + r) * 16 + bx * 2 + 1];
-                ssd = wrap_ssd4(s0, c.x, ssd); ssd = wrap_ssd4(s1, c.y, ssd);
-                sad = sad4(s0, c.x, sad); sad = sad4(s1, c.y, sad);
+            for (int r = 0; r < 8; r++) src[r] = *reinterpret_cast<const uint2*>(&sh.src[(by * 8 + r) * 16 + bx * 2]);
+            uint32_t ssd[9], sad[9];
+#pragma unroll
+            for (int k = 0; k < 9; k++) { ssd[k] = 0; sad[k] = 0; }
+#define HP_ACC(k, lo, hi, s)                                                                           \
+            do { ssd[k] = wrap_ssd4((s).x, lo, ssd[k]); ssd[k] = wrap_ssd4((s).y, hi, ssd[k]);        \
+                 sad[k] = sad4((s).x, lo, sad[k]); sad[k] = sad4((s).y, hi, sad[k]); } while (0)
+#pragma unroll
+            for (int rr = -1; rr < 8; rr++) {
+                const int row = plane_row(Y + rr);
+                const uint32_t* ph = sh.plane[S_H] + row + wa;
+                const uint32_t h0 = ph[0], h1 = ph[1], h2 = ph[2];
+                const uint32_t hl = __funnelshift_r(h0, h1, sa), hh = __funnelshift_r(h1, h2, sa);
+                const uint32_t* pj = sh.plane[S_J] + row + wb;
+                const uint32_t j0 = pj[0], j1 = pj[1], j2 = pj[2];
+                const uint32_t jl0 = __funnelshift_r(j0, j1, sb_), jl1 = __funnelshift_r(j1, j2, sb_);     // from X - 1
+                const uint32_t jr0 = __funnelshift_r(jl0, jl1, 8), jr1 = __funnelshift_r(jl1, j2 >> sb_, 8); // from X
+                if (rr < 7) {                                  // candidates one row up: T, TL, TR against source row rr + 1
+                    HP_ACC(3, hl, hh, src[rr + 1]); HP_ACC(5, jl0, jl1, src[rr + 1]); HP_ACC(6, jr0, jr1, src[rr + 1]);
+                }
+                if (rr >= 0) {                                 // B, BR, BL, the integer position and L, R against source row rr
+                    HP_ACC(4, hl, hh, src[rr]); HP_ACC(7, jr0, jr1, src[rr]); HP_ACC(8, jl0, jl1, src[rr]);
+                    const uint32_t* pa = sh.plane[S_A] + row + wa;
+                    const uint32_t a0 = pa[0], a1 = pa[1], a2 = pa[2];
+                    const uint32_t al = __funnelshift_r(a0, a1, sa), ah = __funnelshift_r(a1, a2, sa);
+                    ssd[0] = wrap_ssd4(src[rr].x, al, ssd[0]); ssd[0] = wrap_ssd4(src[rr].y, ah, ssd[0]);
+                    const uint32_t* pb = sh.plane[S_B] + row + wb;
+                    const uint32_t b0 = pb[0], b1 = pb[1], b2 = pb[2];
+                    const uint32_t bl0 = __funnelshift_r(b0, b1, sb_), bl1 = __funnelshift_r(b1, b2, sb_);
+                    const uint32_t br0 = __funnelshift_r(bl0, bl1, 8), br1 = __funnelshift_r(bl1, b2 >> sb_, 8);
+                    HP_ACC(1, bl0, bl1, src[rr]); HP_ACC(2, br0, br1, src[rr]);
+                }
             }
-            atomicAdd(&sh.sum_ssd[k][pu], ssd); atomicAdd(&sh.sum_sad[k][pu], sad);
+#undef HP_ACC
+            // a warp holds 8x4 blocks of ONE level: sum the blocks of each PU inside the warp, one lane per PU writes
+            const bool leader = pu_leader(L, tid & 31);
+#pragma unroll
+            for (int k = 0; k < 9; k++) {
+                const uint32_t a = pu_sum(ssd[k], L), b = k ? pu_sum(sad[k], L) : 0u;
+                if (leader) {
+                    if (L == 0) { atomicAdd(&sh.sum_ssd[k][0], a); if (k) atomicAdd(&sh.sum_sad[k][0], b); }   // two warps share PU 0
+                    else { sh.sum_ssd[k][pu] = a; sh.sum_sad[k][pu] = b; }
+                }
+            }
         }
         __syncthreads();
         // ---- per PU: nine candidates in the reference's order, strict '<' on the SSD  (ME.c:1909-2239)
@@ -215,36 +283,40 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         for (int t = tid; t < 9 * kNumPu; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
 
-        // ---- quarter-pel: (level, block, candidate) tasks -> partial true-SSD and SAD of the averaged pair
-        // (exactly three of the eight positions are valid for a given half-pel direction: task index j picks one)
-        for (int t = tid; t < 4 * 64 * 3; t += kSpThreads) {
-            const int j = t % 3, blk = (t / 3) & 63, L = t / 192;
-            const int bx = blk & 7, by = blk >> 3;
-            uint32_t ssd = 0, sad = 0;
+        // ---- quarter-pel: one thread per (level, 8x8 block); exactly three of the eight positions are valid for a
+        // given half-pel direction -> partial true-SSD and SAD of the averaged plane pair, source rows kept in registers
+        {
+            const int blk = tid & 63, L = tid >> 6, bx = blk & 7, by = blk >> 3;
             const int pu = pu_of_block(L, bx, by);
             const bool in_area = (L != 0) || (bx < 4 && by < 4);          // quirk Q6: 64x64 refined on its top-left 32x32
-            if (in_area && (L != 3 || p.cu8x8_mode != 1)) {
-                const uint32_t mv = sh.pu_imv[pu];
-                const int xm = mv_x(mv), ym = mv_y(mv), dir = sh.pu_dir[pu];
-                const int method = (ym & 2) + ((xm & 2) >> 1);
-                int k = 0, cnt = 0;
+            const bool active = in_area && (L != 3 || p.cu8x8_mode != 1);
+            const uint32_t mv = sh.pu_imv[pu];
+            const int xm = mv_x(mv), ym = mv_y(mv), dir = sh.pu_dir[pu];
+            const int method = (ym & 2) + ((xm & 2) >> 1);
+            const int X = kMargin + ((xm + 2) >> 2) - sax + bx * 8, Y = kMargin + ((ym + 2) >> 2) - say + by * 8;
+            uint2 src[8];
 #pragma unroll
-                for (int kk = 0; kk < 8; kk++)
-                    if (quarter_valid(method, dir, kk)) { if (cnt == j) k = kk; cnt++; }
-                {
-                    const int8_t* q = kQuarter[method][k];
-                    const int X = kMargin + ((xm + 2) >> 2) - sax + bx * 8, Y = kMargin + ((ym + 2) >> 2) - say + by * 8;
+            for (int r = 0; r < 8; r++) src[r] = *reinterpret_cast<const uint2*>(&sh.src[(by * 8 + r) * 16 + bx * 2]);
+            const bool leader = active && pu_leader(L, tid & 31);         // lane 0 of the 64x64 level is inside the area
+            int kk = -1;
+#pragma unroll 1
+            for (int j = 0; j < 3; j++) {
+                do { kk++; } while (kk < 8 && !quarter_valid(method, dir, kk));   // kk < 8: inactive lanes may hold a stale dir
+                uint32_t ssd = 0, sad = 0;
+                if (active) {
+                    const int8_t* q = kQuarter[method][kk];
                     const uint32_t* p1 = sh.plane[q[0]]; const uint32_t* p2 = sh.plane[q[3]];
+                    const int x1 = X + q[1], y1 = Y + q[2], x2 = X + q[4], y2 = Y + q[5];
 #pragma unroll
                     for (int r = 0; r < 8; r++) {
-                        const uint2 c1 = load8(p1, Y + q[2] + r, X + q[1]), c2 = load8(p2, Y + q[5] + r, X + q[4]);
+                        const uint2 c1 = load8(p1, y1 + r, x1), c2 = load8(p2, y2 + r, x2);
                         const uint32_t a0 = __vavgu4(c1.x, c2.x), a1 = __vavgu4(c1.y, c2.y);
-                        const uint32_t s0 = sh.src[(by * 8 + r) * 16 + bx * 2], s1 = sh.src[(by * 8 + r) * 16 + bx * 2 + 1];
-                        ssd = true_ssd4(s0, a0, ssd); ssd = true_ssd4(s1, a1, ssd);
-                        sad = sad4(s0, a0, sad); sad = sad4(s1, a1, sad);
+                        ssd = true_ssd4(src[r].x, a0, ssd); ssd = true_ssd4(src[r].y, a1, ssd);
+                        sad = sad4(src[r].x, a0, sad); sad = sad4(src[r].y, a1, sad);
                     }
-                    atomicAdd(&sh.sum_ssd[k][pu], ssd); atomicAdd(&sh.sum_sad[k][pu], sad);
                 }
+                ssd = pu_sum(ssd, L); sad = pu_sum(sad, L);
+                if (leader) { sh.sum_ssd[kk][pu] = ssd; sh.sum_sad[kk][pu] = sad; }   // 64x64: only the first warp has active blocks
             }
         }
         __syncthreads();
