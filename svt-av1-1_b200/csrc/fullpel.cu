@@ -15,9 +15,10 @@
 //   * the reference kernels look at 8 rows of every 8x8 block sub-sampled by two (rows 0,2,4,6) and
 //     double the sum; per band of four such rows a tile owns 8 column blocks x 4 positions = 32
 //     accumulators; 16x16 / 32x32 / 64x64 SADs are sums of those;
-//   * argmin: 32-bit key = (sad << 12) | (row << 6) | col, reduced with one CREDUX.MIN per warp and one
-//     shared-memory atomicMin, which is exactly "smallest SAD, first in raster order"; the 32x32 PUs
-//     use (sad << 13) | (row << 7) | (group << 3) | idx to carry the reference's gcc-only MV quirk (Q4).
+//   * argmin: 32-bit key = sad * 4096 + (row << 6 | col), built with one IMAD (FMA pipe); the keys of a warp are
+//     reduced by a streaming transpose (pair_min below) and every lane issues one RED.MIN to its own PU slot,
+//     which is exactly "smallest SAD, first in raster order"; the 32x32 PUs use sad * 8192 + (row, group, idx)
+//     to carry the reference's gcc-only MV quirk (Q4); the 64x64 PU is one warp-wide minimum.
 #include "me_common.cuh"
 
 namespace svtme {
