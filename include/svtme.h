@@ -90,9 +90,15 @@ typedef struct SvtMeSbDebug {
 /* One picture to motion-estimate: slots name pictures previously uploaded into the context. */
 typedef struct SvtMeJob {
     int32_t        cur_slot, ref0_slot, ref1_slot;   /* ref1_slot ignored when params.num_lists == 1 */
+    /* SB rows [sb_row_begin, sb_row_end) of the picture to search; 0, 0 = the whole picture. The rows of one
+     * picture are independent (each SB reads only source pictures), which is how a 4K picture is sharded across
+     * GPUs: every GPU holds the pictures, searches its rows and returns only those rows (the ME segments of
+     * EbMotionEstimationProcess.c:478-556 are the same partition on the CPU). */
+    int32_t        sb_row_begin, sb_row_end;
+    int32_t        reserved;                         /* keeps params 8-byte aligned; set to 0 */
     SvtMeParams    params;
-    SvtMePuResult *results;                          /* HOST memory, [num_sb][params.num_pus]; may be NULL */
-    SvtMeSbDebug  *debug;                            /* HOST memory, [num_sb]; may be NULL */
+    SvtMePuResult *results;                          /* HOST memory, [SBs of the row range][params.num_pus]; may be NULL */
+    SvtMeSbDebug  *debug;                            /* HOST memory, [SBs of the row range]; may be NULL */
 } SvtMeJob;
 
 /* Default search parameters for a resolution: the M0 column every legal preset uses. */
@@ -109,6 +115,12 @@ const char *svtme_last_error(const SvtMeContext *ctx);
  * full / quarter / sixteenth planes on the device. Asynchronous, on the context's upload stream; a slot is
  * rewritten only after the batches that read its previous picture have finished. */
 int32_t svtme_picture_upload(SvtMeContext *ctx, int32_t slot, const uint8_t *luma, int32_t stride);
+/* 10-bit input: 'luma16' holds one sample per uint16_t ('stride' in samples). The 8-bit plane ME works on is
+ * sample >> 2 and the 2-bit remainder plane is (uint8_t)(sample << 6): UnPack2D, EbEncHandle.c:2954-2963 ->
+ * EB_ENC_msbUnPack2D, C_DEFAULT/EbPackUnPack_C.c:127-151. The split runs on the device, fused in front of the
+ * pyramid build; when 'bit_inc' is not NULL it receives the remainder plane (HOST memory, width bytes per row,
+ * height rows; in place by svtme_synchronize / svtme_join). */
+int32_t svtme_picture_upload_16bit(SvtMeContext *ctx, int32_t slot, const uint16_t *luma16, int32_t stride, uint8_t *bit_inc);
 /* Same, from a luma plane that already lives in device memory (no H2D copy). */
 int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8_t *d_luma, int32_t stride);
 /* Read one padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) as tightly packed rows of

@@ -707,3 +707,18 @@ int meo_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
     free(c);
     return 0;
 }
+
+/* UnPack2D (EbPictureOperators.c:642-662) -> EB_ENC_msbUnPack2D (C_DEFAULT/EbPackUnPack_C.c:127-151): the split of a
+ * 16-bit-per-sample 10-bit input plane done in CopyInputBuffer (EbEncHandle.c:2954-2963). ME reads the msb plane. */
+void meo_unpack16(const uint16_t *in, int32_t in_stride, uint8_t *msb, int32_t msb_stride, uint8_t *rem, int32_t rem_stride,
+                  int32_t width, int32_t height) {
+    for (int y = 0; y < height; y++)
+        for (int x = 0; x < width; x++) {
+            const uint16_t v = in[(size_t)y * in_stride + x];
+            msb[(size_t)y * msb_stride + x] = (uint8_t)(v >> 2);
+            /* quirk Q9 (ASM_SSE2/EbPackUnPack_Intrinsic_SSE2.c:139,180): the width == 32 and width == 64 special cases
+             * forget the << 6 on their last 16 samples (second row of each row pair for 32, every row for 64) */
+            const int q9 = (width == 64 && x >= 48) || (width == 32 && (y & 1) && x >= 16);
+            if (rem) rem[(size_t)y * rem_stride + x] = q9 ? (uint8_t)(v & 3) : (uint8_t)(v << 6);
+        }
+}

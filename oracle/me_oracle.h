@@ -96,6 +96,9 @@ void meo_default_params(MeoParams *p, int32_t width, int32_t height, int32_t num
  * copy + generate_padding + Decimation2D(2) + pad + Decimation2D(4) + pad
  * (EbPictureAnalysisProcess.c:4866-4937, EbMcp.c:173-216). Planes must be pre-described. */
 void meo_build_pyramid(const uint8_t *luma, int32_t src_stride, MeoPyramid *pyr);
+/* 10-bit input split: msb = sample >> 2, rem = (uint8_t)(sample << 6); strides in samples / bytes */
+void meo_unpack16(const uint16_t *in, int32_t in_stride, uint8_t *msb, int32_t msb_stride, uint8_t *rem, int32_t rem_stride,
+                  int32_t width, int32_t height);
 void ref_build_pyramid(const uint8_t *luma, int32_t src_stride, MeoPyramid *pyr);
 
 /* Motion-estimate every SB of one picture. results: [num_sb][params->num_pus];

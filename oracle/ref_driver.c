@@ -72,6 +72,12 @@ void ref_build_pyramid(const uint8_t *luma, int32_t src_stride, MeoPyramid *pyr)
     generate_padding(s->buf, s->stride, s->width, s->height, s->origin_x, s->origin_y);
 }
 
+/* the reference's own 10-bit input split, AVX2 dispatch row (UnPack2D picks the SSE2 kernel for width % 4 == 0, even height) */
+void ref_unpack16(uint16_t *in, int32_t in_stride, uint8_t *msb, int32_t msb_stride, uint8_t *rem, int32_t rem_stride,
+                  int32_t width, int32_t height) {
+    UnPack2D(in, (uint32_t)in_stride, msb, (uint32_t)msb_stride, rem, (uint32_t)rem_stride, (uint32_t)width, (uint32_t)height, ASM_AVX2);
+}
+
 int ref_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
                                 const MeoPyramid *ref0, const MeoPyramid *ref1,
                                 MeoPuResult *results, MeoSbDebug *debug) {

@@ -11,7 +11,7 @@ EXPORTED_SYMBOLS = (
     "svtme_default_params", "svtme_create", "svtme_destroy", "svtme_last_error", "svtme_picture_upload",
     "svtme_picture_upload_device", "svtme_picture_download", "svtme_motion_estimate",
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
-    "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join",
+    "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
 )
 KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
 
@@ -34,6 +34,7 @@ class SvtMeParams(C.Structure):
 
 class SvtMeJob(C.Structure):
     _fields_ = [("cur_slot", C.c_int32), ("ref0_slot", C.c_int32), ("ref1_slot", C.c_int32),
+                ("sb_row_begin", C.c_int32), ("sb_row_end", C.c_int32), ("reserved", C.c_int32),
                 ("params", SvtMeParams), ("results", C.c_void_p), ("debug", C.c_void_p)]
 
 
@@ -72,6 +73,8 @@ def load_library():
     lib.svtme_last_error.argtypes = [C.c_void_p]
     lib.svtme_picture_upload.restype = C.c_int32
     lib.svtme_picture_upload.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+    lib.svtme_picture_upload_16bit.restype = C.c_int32
+    lib.svtme_picture_upload_16bit.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]
     lib.svtme_picture_upload_device.restype = C.c_int32
     lib.svtme_picture_upload_device.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
     lib.svtme_picture_download.restype = C.c_int32
@@ -141,6 +144,16 @@ class MeContext:
         assert luma.dtype == np.uint8 and luma.shape == (self.height, self.width)
         self._check(self.lib.svtme_picture_upload(self._h, slot, luma.ctypes.data, luma.strides[0]), "svtme_picture_upload")
 
+    def upload16(self, slot, luma16, bit_inc=None):
+        """luma16: uint16 (height, width) samples of a 10-bit picture; bit_inc: optional uint8 (height, width) array that
+        receives the 2-bit remainder plane (valid after synchronize())."""
+        assert luma16.dtype == np.uint16 and luma16.shape == (self.height, self.width) and luma16.strides[1] == 2
+        if bit_inc is not None:
+            assert bit_inc.dtype == np.uint8 and bit_inc.shape == (self.height, self.width) and bit_inc.flags.c_contiguous
+        self._check(self.lib.svtme_picture_upload_16bit(self._h, slot, luma16.ctypes.data, luma16.strides[0] // 2,
+                                                        bit_inc.ctypes.data if bit_inc is not None else None),
+                    "svtme_picture_upload_16bit")
+
     def upload_ptr(self, slot, host_ptr, stride):
         self._check(self.lib.svtme_picture_upload(self._h, slot, host_ptr, stride), "svtme_picture_upload")
 
@@ -157,21 +170,26 @@ class MeContext:
         assert (s.value, r.value, p.value) == (w, h, pad)
         return out
 
-    def make_jobs(self, specs, want_debug=False, out_ptrs=None):
-        """specs: list of (cur_slot, ref0_slot, ref1_slot, SvtMeParams). Returns (jobs array, results, debug)."""
+    def make_jobs(self, specs, want_debug=False, out_ptrs=None, sb_rows=None):
+        """specs: list of (cur_slot, ref0_slot, ref1_slot, SvtMeParams). sb_rows = (begin, end): search only those SB rows
+        of every picture (results/debug then hold just the SBs of that range). Returns (jobs array, results, debug)."""
         n = len(specs)
         jobs = (SvtMeJob * n)()
-        results = np.zeros((n, self.n_sb, SQUARE_PU_COUNT), dtype=PU_RESULT_DTYPE) if out_ptrs is None else None
-        debug = np.zeros((n, self.n_sb), dtype=SB_DEBUG_DTYPE) if want_debug else None
+        sb_cols = (self.width + 63) // 64
+        n_sb = self.n_sb if sb_rows is None else (sb_rows[1] - sb_rows[0]) * sb_cols
+        results = np.zeros((n, n_sb, SQUARE_PU_COUNT), dtype=PU_RESULT_DTYPE) if out_ptrs is None else None
+        debug = np.zeros((n, n_sb), dtype=SB_DEBUG_DTYPE) if want_debug else None
         for i, (cur, r0, r1, prm) in enumerate(specs):
             jobs[i].cur_slot, jobs[i].ref0_slot, jobs[i].ref1_slot = cur, r0, (r1 if r1 is not None else r0)
+            if sb_rows is not None:
+                jobs[i].sb_row_begin, jobs[i].sb_row_end = sb_rows
             jobs[i].params = prm
             jobs[i].results = results[i].ctypes.data if out_ptrs is None else out_ptrs[i]
             jobs[i].debug = debug[i].ctypes.data if want_debug else None
         return jobs, results, debug
 
-    def motion_estimate(self, specs, want_debug=False):
-        jobs, results, debug = self.make_jobs(specs, want_debug)
+    def motion_estimate(self, specs, want_debug=False, sb_rows=None):
+        jobs, results, debug = self.make_jobs(specs, want_debug, sb_rows=sb_rows)
         self._check(self.lib.svtme_motion_estimate(self._h, jobs, len(specs)), "svtme_motion_estimate")
         return results, debug
 

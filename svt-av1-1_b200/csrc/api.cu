@@ -49,6 +49,8 @@ struct SvtMeContext {
     cudaStream_t stream = nullptr, copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t join_ev = nullptr;
     std::vector<Slot> slots;
+    uint16_t* d_in16 = nullptr;           // staging of a 16-bit luma plane (svtme_picture_upload_16bit), width * height samples
+    uint8_t* d_rem = nullptr;             // its 2-bit remainder plane
     Batch ring[kRing];
     int next = 0, last = -1;              // ring entry for the next batch / of the latest batch
     int64_t seq = 0;                      // batches submitted so far
@@ -192,6 +194,7 @@ void svtme_destroy(SvtMeContext* ctx) {
     for (auto& t : ctx->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); }
+    cudaFree(ctx->d_in16); cudaFree(ctx->d_rem);
     for (auto& b : ctx->ring) {
         free_batch(b);
         if (b.computed) cudaEventDestroy(b.computed);
@@ -237,6 +240,27 @@ int32_t svtme_picture_upload(SvtMeContext* ctx, int32_t slot, const uint8_t* lum
     int32_t rc = guard_slot_rewrite(ctx, s);
     if (rc != SVTME_OK) return rc;
     CU(cudaMemcpy2DAsync(s.luma, ctx->width, luma, stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
+    return build_pyramid(ctx, s, s.luma, ctx->width);
+}
+
+int32_t svtme_picture_upload_16bit(SvtMeContext* ctx, int32_t slot, const uint16_t* luma16, int32_t stride, uint8_t* bit_inc) {
+    if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || !luma16 || stride < ctx->width)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_16bit: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    Slot& s = ctx->slots[slot];
+    int32_t rc = guard_slot_rewrite(ctx, s);
+    if (rc != SVTME_OK) return rc;
+    const size_t n = (size_t)ctx->width * ctx->height;
+    if (!ctx->d_in16) {                                   // one staging plane per context; the upload stream serialises its use
+        CU(cudaMalloc(&ctx->d_in16, n * sizeof(uint16_t)));
+        CU(cudaMalloc(&ctx->d_rem, n));
+    }
+    CU(cudaMemcpy2DAsync(ctx->d_in16, (size_t)ctx->width * 2, luma16, (size_t)stride * 2, (size_t)ctx->width * 2, ctx->height,
+                         cudaMemcpyHostToDevice, ctx->copy_in));
+    launch_unpack16(ctx->d_in16, ctx->width, s.luma, bit_inc ? ctx->d_rem : nullptr, ctx->width, ctx->height, ctx->copy_in);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (bit_inc) CU(cudaMemcpyAsync(bit_inc, ctx->d_rem, n, cudaMemcpyDeviceToHost, ctx->copy_in));
     return build_pyramid(ctx, s, s.luma, ctx->width);
 }
 
@@ -302,6 +326,10 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         if (j.cur_slot < 0 || j.cur_slot >= nslots || j.ref0_slot < 0 || j.ref0_slot >= nslots ||
             (j.params.num_lists == 2 && (j.ref1_slot < 0 || j.ref1_slot >= nslots)))
             return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: slot out of range");
+        if (j.sb_row_begin != 0 || j.sb_row_end != 0) {
+            if (j.sb_row_begin < 0 || j.sb_row_end <= j.sb_row_begin || j.sb_row_end > ctx->sb_rows)
+                return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: SB row range out of the picture");
+        }
         max_lists = j.params.num_lists > max_lists ? j.params.num_lists : max_lists;
     }
     const int bi = ctx->next;
@@ -309,6 +337,7 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     if (b.used) CU(cudaEventSynchronize(b.drained));     // the batch that used this entry kRing submissions ago
     int32_t rc = ensure_batch(ctx, b, n_jobs);
     if (rc != SVTME_OK) return rc;
+    int max_sb = 0;                                       // grid width: the largest SB range of the batch
     for (int i = 0; i < n_jobs; i++) {
         const SvtMeJob& j = jobs[i];
         DJob& d = b.h_jobs[i];
@@ -321,6 +350,10 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         d.results = b.d_results + (size_t)i * ctx->n_sb * kNumPu;
         d.debug = j.debug ? b.d_debug + (size_t)i * ctx->n_sb : nullptr;
         d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
+        const bool whole = j.sb_row_begin == 0 && j.sb_row_end == 0;
+        d.sb_begin = whole ? 0 : j.sb_row_begin * ctx->sb_cols;
+        d.sb_end = whole ? ctx->n_sb : j.sb_row_end * ctx->sb_cols;
+        max_sb = d.sb_end - d.sb_begin > max_sb ? d.sb_end - d.sb_begin : max_sb;
         for (int sl : { j.cur_slot, j.ref0_slot, r1 }) {
             Slot& s = ctx->slots[sl];
             if (s.last_reader_seq != ctx->seq) {        // first use by this batch: its pyramid must be complete
@@ -331,22 +364,22 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     }
     CU(cudaMemcpyAsync(b.d_jobs, b.h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
     for (int list = 0; list < max_lists; list++) {
-        { LaunchTimer t(ctx, SVTME_KERNEL_HME, ctx->stream); launch_hme(b.d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
-        { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, ctx->stream); launch_fullpel(b.d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
-        { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, ctx->stream); launch_subpel(b.d_jobs, n_jobs, ctx->n_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_HME, ctx->stream); launch_hme(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, ctx->stream); launch_fullpel(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
+        { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, ctx->stream); launch_subpel(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
     }
-    { LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, ctx->stream); launch_bipred_pack(b.d_jobs, n_jobs, ctx->n_sb, ctx->stream); }
+    { LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, ctx->stream); launch_bipred_pack(b.d_jobs, n_jobs, max_sb, ctx->stream); }
     CU(cudaGetLastError());
     CU(cudaEventRecord(b.computed, ctx->stream));
     // results travel on their own stream, straight into the caller's buffers
     CU(cudaStreamWaitEvent(ctx->copy_out, b.computed, 0));
-    for (int i = 0; i < n_jobs; i++) {
+    for (int i = 0; i < n_jobs; i++) {                    // only the SBs of the job's row range travel
+        const size_t first = (size_t)i * ctx->n_sb + b.h_jobs[i].sb_begin, count = (size_t)(b.h_jobs[i].sb_end - b.h_jobs[i].sb_begin);
         if (jobs[i].results)
-            CU(cudaMemcpyAsync(jobs[i].results, b.d_results + (size_t)i * ctx->n_sb * kNumPu,
-                               sizeof(SvtMePuResult) * (size_t)ctx->n_sb * kNumPu, cudaMemcpyDeviceToHost, ctx->copy_out));
+            CU(cudaMemcpyAsync(jobs[i].results, b.d_results + first * kNumPu, sizeof(SvtMePuResult) * count * kNumPu,
+                               cudaMemcpyDeviceToHost, ctx->copy_out));
         if (jobs[i].debug)
-            CU(cudaMemcpyAsync(jobs[i].debug, b.d_debug + (size_t)i * ctx->n_sb,
-                               sizeof(SvtMeSbDebug) * (size_t)ctx->n_sb, cudaMemcpyDeviceToHost, ctx->copy_out));
+            CU(cudaMemcpyAsync(jobs[i].debug, b.d_debug + first, sizeof(SvtMeSbDebug) * count, cudaMemcpyDeviceToHost, ctx->copy_out));
     }
     CU(cudaEventRecord(b.drained, ctx->copy_out));
     b.used = true;

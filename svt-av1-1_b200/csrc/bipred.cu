@@ -14,8 +14,8 @@ constexpr int kBpThreads = 256;
 __global__ void __launch_bounds__(kBpThreads) bipred_pack_kernel(const DJob* __restrict__ jobs) {
     __shared__ uint32_t part[4][64];
     const DJob& job = jobs[blockIdx.y];
-    const int sb = blockIdx.x;
-    if (sb >= job.sb_cols * job.sb_rows) return;
+    const int sb = job.sb_begin + blockIdx.x;
+    if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
     const int tid = threadIdx.x;
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;

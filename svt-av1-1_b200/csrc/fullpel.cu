@@ -52,8 +52,8 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     uint32_t* src = smem + 4 * kWinRows * kWinPitch;
     uint32_t* keys = src + 32 * 16;
     const DJob& job = jobs[blockIdx.y];
-    const int sb = blockIdx.x;
-    if (sb >= job.sb_cols * job.sb_rows) return;
+    const int sb = job.sb_begin + blockIdx.x;
+    if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
     if (list >= p.num_lists) return;
     const int tid = threadIdx.x;

@@ -179,8 +179,8 @@ __device__ __forceinline__ int round_sa_width(int w) { return (w < 8) ? 8 : (w &
 __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restrict__ jobs, int list) {
     __shared__ HmeShared sh;
     const DJob& job = jobs[blockIdx.y];
-    const int sb = blockIdx.x;
-    if (sb >= job.sb_cols * job.sb_rows) return;
+    const int sb = job.sb_begin + blockIdx.x;
+    if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
     if (list >= p.num_lists) return;
     const int tid = threadIdx.x, warp = tid >> 5;

@@ -45,6 +45,7 @@ struct DJob {
     SvtMePuResult* results;      // [n_sb][85]  (device)
     SvtMeSbDebug* debug;         // [n_sb]      (device)
     int sb_cols, sb_rows;
+    int sb_begin, sb_end;        // SBs [sb_begin, sb_end) of the raster are searched (an SB-row range)
 };
 
 // raster index -> internal index (EbMotionEstimation.h:89-128)
@@ -103,6 +104,7 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 
 // host-side launchers (one per .cu)
 void launch_pyramid(const uint8_t* d_luma, int luma_stride, const DPyramid& pyr, cudaStream_t st);
+void launch_unpack16(const uint16_t* d_in, int in_stride, uint8_t* d_msb, uint8_t* d_rem, int width, int height, cudaStream_t st);
 void launch_hme(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);
 void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);
 void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);

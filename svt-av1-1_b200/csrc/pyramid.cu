@@ -31,6 +31,32 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const uint8_t* __restrict_
     }
 }
 
+// 10-bit input split (UnPack2D -> EB_ENC_msbUnPack2D, C_DEFAULT/EbPackUnPack_C.c:127-151): msb = sample >> 2 (the plane ME
+// searches), rem = (uint8_t)(sample << 6). One thread = four samples: two 64-bit loads, one or two 32-bit stores.
+__global__ void __launch_bounds__(256) unpack16_kernel(const uint16_t* __restrict__ in, int in_stride, uint8_t* __restrict__ msb,
+                                                       uint8_t* __restrict__ rem, int width, int height) {
+    const int x = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (x >= width) return;
+    for (int y = blockIdx.y; y < height; y += gridDim.y) {
+        const uint2 v = *reinterpret_cast<const uint2*>(in + (size_t)y * in_stride + x);      // width % 8 == 0, rows 8-byte aligned
+        const uint32_t s0 = v.x & 0xFFFFu, s1 = v.x >> 16, s2 = v.y & 0xFFFFu, s3 = v.y >> 16;
+        const uint32_t m = ((s0 >> 2) & 0xFF) | (((s1 >> 2) & 0xFF) << 8) | (((s2 >> 2) & 0xFF) << 16) | (((s3 >> 2) & 0xFF) << 24);
+        *reinterpret_cast<uint32_t*>(msb + (size_t)y * width + x) = m;
+        if (rem) {
+            // quirk Q9: the reference's width == 32 / width == 64 special cases leave the last 16 samples unshifted
+            const bool q9 = (width == 64 && x >= 48) || (width == 32 && (y & 1) && x >= 16);
+            const uint32_t lo = (s0 & 3) | ((s1 & 3) << 8) | ((s2 & 3) << 16) | ((s3 & 3) << 24);
+            const uint32_t r = q9 ? lo : lo << 6;
+            *reinterpret_cast<uint32_t*>(rem + (size_t)y * width + x) = r;
+        }
+    }
+}
+
+void launch_unpack16(const uint16_t* d_in, int in_stride, uint8_t* d_msb, uint8_t* d_rem, int width, int height, cudaStream_t st) {
+    dim3 grid((width / 4 + 255) / 256, height < 296 ? height : 296);
+    unpack16_kernel<<<grid, 256, 0, st>>>(d_in, in_stride, d_msb, d_rem, width, height);
+}
+
 void launch_pyramid(const uint8_t* d_luma, int luma_stride, const DPyramid& pyr, cudaStream_t st) {
     const int words = (pyr.full.w + 2 * pyr.full.ox + 3) >> 2;
     dim3 grid((words + 255) / 256, 148, 3);

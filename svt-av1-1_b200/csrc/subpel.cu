@@ -145,8 +145,8 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SpShared& sh = *reinterpret_cast<SpShared*>(smem_raw);
     const DJob& job = jobs[blockIdx.y];
-    const int sb = blockIdx.x;
-    if (sb >= job.sb_cols * job.sb_rows) return;
+    const int sb = job.sb_begin + blockIdx.x;
+    if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
     if (list >= p.num_lists) return;
     const int tid = threadIdx.x;

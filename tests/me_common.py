@@ -246,3 +246,15 @@ def load_golden(name):
 def plane_crc(a):
     import zlib
     return zlib.crc32(np.ascontiguousarray(a).tobytes()) & 0xFFFFFFFF
+
+
+def unpack16(lib, prefix, luma16):
+    """10-bit split of a uint16 (h, w) plane through the oracle ('meo') or the reference ('ref'): (msb, rem) uint8 planes."""
+    h, w = luma16.shape
+    src = np.ascontiguousarray(luma16)
+    msb, rem = np.zeros((h, w), np.uint8), np.zeros((h, w), np.uint8)
+    f = getattr(lib, prefix + "_unpack16")
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+    f(src.ctypes.data, w, msb.ctypes.data, w, rem.ctypes.data, w, w, h)
+    return msb, rem

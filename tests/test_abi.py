@@ -64,6 +64,7 @@ def test_struct_layouts(pkg_built):
     # byte image of MeCuResults_t (EbMotionEstimationLcuResults.h:62-75) and the parameter block
     assert pkg_built.PU_RESULT_DTYPE.itemsize == 40
     assert C.sizeof(pkg_built.SvtMeParams) == 4 * 34
+    assert C.sizeof(pkg_built.SvtMeJob) == 6 * 4 + 4 * 34 + 2 * 8 and pkg_built.SvtMeJob.params.offset == 24
     assert C.sizeof(M.MeoParams) == C.sizeof(pkg_built.SvtMeParams)
     assert pkg_built.SB_DEBUG_DTYPE.itemsize == 6 * 4 + 2 * 2 * 85 * 4
 

@@ -238,3 +238,78 @@ def test_pipelined_batches_and_slot_reuse(pkg, meo):
         want1, _ = M.motion_estimate(meo, "meo", mp, pyr[2 * b], pyr[2 * b + 1], pyr[2 * b + 1])
         assert M.results_diff(res[0], want0) == [], b
         assert M.results_diff(res[1], want1) == [], b
+
+
+def test_upload_16bit_matches_oracle_split(pkg, meo):
+    """10-bit input: the device-side split (msb = v >> 2 feeds ME, rem = v << 6) and the pyramid built from it."""
+    w, h = 416, 240
+    rng = np.random.default_rng(10)
+    f8 = M.synth_video(w, h, 1, seed=31)[0]
+    v = (f8.astype(np.uint16) << 2) | rng.integers(0, 4, size=(h, w), dtype=np.uint16)
+    big = np.zeros((h, w + 24), np.uint16)
+    big[:, 8:8 + w] = v
+    strided = big[:, 8:8 + w]                                   # stride 440 samples
+    msb, rem = M.unpack16(meo, "meo", v)
+    assert np.array_equal(msb, f8)
+    got_rem = np.zeros((h, w), np.uint8)
+    ctx = pkg.MeContext(w, h, 2)
+    ctx.upload16(0, strided, got_rem)
+    ctx.upload16(1, np.ascontiguousarray(v))                    # without the remainder plane
+    ctx.synchronize()
+    want = M.build_pyramid(meo, "meo", msb)
+    for lvl in range(3):
+        assert np.array_equal(ctx.download_plane(0, lvl), want.planes[lvl]), lvl
+        assert np.array_equal(ctx.download_plane(1, lvl), want.planes[lvl]), lvl
+    ctx.close()
+    assert np.array_equal(got_rem, rem)
+
+
+def test_sb_row_ranges_equal_whole_picture(pkg, meo):
+    """SB-row sharding: searching row ranges separately returns exactly the rows of the whole-picture call."""
+    w, h = 416, 240                                             # 7 x 4 SBs, last row 48 high
+    fr = M.synth_video(w, h, 3, seed=77, max_shift=20)
+    ctx = pkg.MeContext(w, h, 3)
+    for i, f in enumerate(fr):
+        ctx.upload(i, f)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    whole, wdbg = ctx.motion_estimate([(1, 0, 2, p)], want_debug=True)
+    parts, dparts = [], []
+    for rows in [(0, 1), (1, 3), (3, 4)]:
+        r, d = ctx.motion_estimate([(1, 0, 2, p), (1, 0, 2, p)], want_debug=True, sb_rows=rows)
+        assert r.shape[1] == (rows[1] - rows[0]) * 7 and np.array_equal(r[0], r[1])
+        parts.append(r[0]); dparts.append(d[0])
+    assert np.array_equal(np.concatenate(parts), whole[0])
+    assert np.array_equal(np.concatenate(dparts), wdbg[0])
+    with pytest.raises(pkg.SvtMeError):
+        ctx.motion_estimate([(1, 0, 2, p)], sb_rows=(2, 5))
+    with pytest.raises(pkg.SvtMeError):
+        ctx.motion_estimate([(1, 0, 2, p)], sb_rows=(3, 3))
+    ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
+    want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p), pyr[1], pyr[0], pyr[2])
+    assert M.results_diff(whole[0], want) == []
+
+
+def test_4k_sb_rows_against_oracle_and_properties(pkg, meo):
+    """BASELINE configs[2] geometry (3840x2160: 60 x 34 SBs). The oracle checks two SB-row ranges (first rows and the
+    ragged last rows) computed as a 2-way row shard would; the whole picture is checked through size-independent
+    properties (self-prediction is free; a translation is recovered)."""
+    w, h = 3840, 2160
+    rng = np.random.default_rng(2160)
+    base = M.synth_video(w // 4, h // 4, 3, seed=9, max_shift=8)
+    fr = [np.ascontiguousarray(np.kron(f, np.ones((4, 4), np.uint8))[:h, :w]) for f in base]
+    fr = [np.clip(f.astype(np.int16) + rng.integers(-6, 7, size=f.shape), 0, 255).astype(np.uint8) for f in fr]
+    ctx = pkg.MeContext(w, h, 3)
+    for i, f in enumerate(fr):
+        ctx.upload(i, f)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    top, _ = ctx.motion_estimate([(1, 0, 2, p)], sb_rows=(0, 2))
+    bottom, _ = ctx.motion_estimate([(1, 0, 2, p)], sb_rows=(32, 34))
+    self_res, _ = ctx.motion_estimate([(1, 1, 1, p)])
+    ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
+    want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p), pyr[1], pyr[0], pyr[2], want_debug=False)
+    assert M.results_diff(top[0], want[:2 * 60]) == []
+    assert M.results_diff(bottom[0], want[32 * 60:]) == []
+    sq = [0] + list(range(5, 85))
+    assert not self_res[0]["dist0"][:, sq].any()

@@ -94,3 +94,17 @@ def test_hme_level0_multipliers(libs, hl, tl):
     """HME_LEVEL_0_SEARCH_AREA_MULTIPLIER_X/Y[hierarchical_levels][temporal_layer] (EbDefinitions.h:2980-2996):
     up to 5.25x wider level-0 areas, clipped at the picture borders."""
     _compare(libs, 448, 256, seed=hl * 7 + tl, nl=2, tl=tl, hl=hl, synth=dict(max_shift=70))
+
+
+@pytest.mark.parametrize("w,h", [(64, 64), (32, 16), (416, 240), (1920, 34), (128, 8), (96, 6)])
+def test_unpack16_matches_reference(libs, w, h):
+    """10-bit input split (UnPack2D): oracle restatement against the reference's SSE2 kernel."""
+    meo, ref = libs
+    rng = np.random.default_rng(w + h)
+    v = rng.integers(0, 1024, size=(h, w), dtype=np.uint16)
+    v[0, :8] = [0, 1, 2, 3, 1020, 1021, 1022, 1023]
+    a, b = M.unpack16(meo, "meo", v), M.unpack16(ref, "ref", v)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    assert np.array_equal(a[0], (v >> 2).astype(np.uint8))
+    if w not in (32, 64):                                        # quirk Q9 lives in those two special cases only
+        assert np.array_equal(a[1], ((v & 3) << 6).astype(np.uint8))
