@@ -42,6 +42,18 @@ SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
 FULLPEL_BYTE_SADS_PER_SB_LIST = 64 * 64 * 64 * 32
 
 
+USE_16BIT = False                 # me4k: pictures arrive as 16-bit samples (10-bit), split on the device
+SHARD_SB_ROWS = False             # me4k: N ranks share every picture by SB rows (strong scaling)
+
+
+def select_workload(name):
+    """me: BASELINE configs[1] (1080p 8-bit, one stream per GPU). me4k: configs[2] (3840x2160 10-bit, SB rows sharded)."""
+    global W, H, N_PICS, SB_PER_FRAME, USE_16BIT, SHARD_SB_ROWS
+    if name == "me4k":
+        W, H, N_PICS, USE_16BIT, SHARD_SB_ROWS = 3840, 2160, 33, True, True
+        SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
+
+
 def gop_jobs():
     """[(poc, temporal_layer, ref0_poc, ref1_poc)] for pictures 1..120 in decode order."""
     jobs = []
@@ -182,9 +194,9 @@ def run_reference_impl(args, rank):
     fps = n_tasks * args.steps / total
     sample = f"{n_tasks} pictures per step drawn from the first two mini-GOPs of the 1080p sequence, one picture per task over {arm.cores} worker processes"
     line = {
-        "impl": "reference", "metric": "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": "2160p_me_frames_per_sec" if SHARD_SB_ROWS else "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "scaling": "strong" if SHARD_SB_ROWS else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(args.gpus),
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": arm.cores, "kind": arm.kind, "sample": sample},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -194,6 +206,12 @@ def run_reference_impl(args, rank):
 
 
 def workload_config(n_gpus):
+    if SHARD_SB_ROWS:
+        return {"workload": "3840x2160 10-bit luma (16-bit samples, split 8+2 on upload; ME on the 8-bit plane), 33 pictures (1 intra + 32 B), "
+                            "hierarchical mini-GOP 8 / 4 temporal layers, full open-loop ME per picture with the 4K search tables",
+                "frames_per_step": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": 85,
+                "parallelism": f"every picture on every GPU, SB rows of each picture sharded x{n_gpus}, no collective",
+                "l2_policy": "inputs larger than L2 (33 planes = 274 MB + 8-bit pyramids per step)"}
     return {"workload": "1920x1080 8-bit luma, 121 pictures (1 intra + 120 B), hierarchical mini-GOP 8 / 4 temporal layers, "
                         "full open-loop ME per picture: pyramid + HME L0/L1/L2 + 64x64 full-pel (85 PUs) + half/quarter-pel + bi-pred",
             "frames_per_step_per_gpu": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": 85,
@@ -236,9 +254,14 @@ def run_gpu_impl(args, rank, world, local_rank):
                "sample": f"{n_tasks} pictures of the first two mini-GOPs, {arm.cores} worker processes, {t:.1f} s wall"}
 
     torch.cuda.set_device(local_rank)
-    frames = synth_sequence(N_PICS, seed=1 + rank)
-    host = torch.from_numpy(frames).pin_memory()                       # pinned host planes (e2e source)
-    dev = host.cuda(non_blocking=False)                                 # HBM-resident planes (value source)
+    frames = synth_sequence(N_PICS, seed=1 if SHARD_SB_ROWS else 1 + rank)   # row sharding: every rank sees the same pictures
+    if USE_16BIT:
+        lsb = np.random.default_rng(5).integers(0, 4, size=frames.shape, dtype=np.uint16)
+        host = torch.from_numpy((frames.astype(np.uint16) << 2) | lsb).pin_memory()   # pinned 16-bit planes (e2e source)
+        dev = torch.from_numpy(frames).cuda()                                          # 8-bit planes resident in HBM (value source)
+    else:
+        host = torch.from_numpy(frames).pin_memory()                   # pinned host planes (e2e source)
+        dev = host.cuda(non_blocking=False)                             # HBM-resident planes (value source)
     jobs = gop_jobs()
     ctx = pkg.MeContext(W, H, N_PICS, device=local_rank)
     specs = []
@@ -246,13 +269,18 @@ def run_gpu_impl(args, rank, world, local_rank):
         p = pkg.default_params(W, H, 2, tl, 3, 1 if tl < 3 else 0)
         p.same_ref_poc = 1 if r0 == r1 else 0
         specs.append((poc, r0, r1, p))
-    n_sb = ctx.n_sb
+    sb_rows = None
+    if SHARD_SB_ROWS and world > 1:
+        shard = importlib.import_module("svt-av1-1_b200.sharding")
+        first, count = shard.sb_row_shard((H + 63) // 64, world, rank)
+        sb_rows = (first, first + count)
+    n_sb = ctx.n_sb if sb_rows is None else (sb_rows[1] - sb_rows[0]) * ((W + 63) // 64)
     out = torch.empty((len(jobs), n_sb, 85, 40), dtype=torch.uint8).pin_memory()     # host me_results images
     ptrs = [out[i].data_ptr() for i in range(len(jobs))]
-    job_resident, _, _ = ctx.make_jobs(specs, out_ptrs=[None] * len(jobs))           # results stay in HBM
+    job_resident, _, _ = ctx.make_jobs(specs, out_ptrs=[None] * len(jobs), sb_rows=sb_rows)   # results stay in HBM
     # e2e: one batch per mini-GOP (8 pictures) so that uploads, searches and result copies of consecutive
     # batches overlap on the context's three streams
-    gop_batches = [ctx.make_jobs(specs[g:g + 8], out_ptrs=ptrs[g:g + 8])[0] for g in range(0, len(jobs), 8)]
+    gop_batches = [ctx.make_jobs(specs[g:g + 8], out_ptrs=ptrs[g:g + 8], sb_rows=sb_rows)[0] for g in range(0, len(jobs), 8)]
     stride = W
 
     def step_resident():
@@ -262,7 +290,11 @@ def run_gpu_impl(args, rank, world, local_rank):
 
     def step_e2e():
         for i in range(N_PICS):
-            ctx.upload_ptr(i, host[i].data_ptr(), stride)
+            if USE_16BIT:
+                rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, i, host[i].data_ptr(), stride, None)
+                assert rc == 0
+            else:
+                ctx.upload_ptr(i, host[i].data_ptr(), stride)
         for jb in gop_batches:
             ctx.motion_estimate_async(jb)
 
@@ -312,13 +344,13 @@ def run_gpu_impl(args, rank, world, local_rank):
     ctx.close()
 
     if rank == 0:
-        frames_total = world * (N_PICS - 1) * args.steps
+        frames_total = (1 if SHARD_SB_ROWS else world) * (N_PICS - 1) * args.steps
         fps = frames_total / (ms / 1e3)
         fps_e2e = frames_total / (ms_e2e / 1e3)
         fp_ms, fp_n = kt["fullpel"]
         total_kernel_ms = sum(v[0] for v in kt.values())
         # algorithmic work of one full-pel launch: every SB of every picture of the batch, one list
-        sads_per_launch = FULLPEL_BYTE_SADS_PER_SB_LIST * SB_PER_FRAME * len(jobs)
+        sads_per_launch = FULLPEL_BYTE_SADS_PER_SB_LIST * n_sb * len(jobs)
         achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n else None
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965
         peak = int_pipe_peak(sm_mhz)
@@ -331,11 +363,12 @@ def run_gpu_impl(args, rank, world, local_rank):
         py_ms, py_n = kt["pyramid"]
         pyr_bytes = W * H + sum(((W >> s) + 2 * p) * ((H >> s) + 2 * p) for s, p in ((0, 68), (1, 32), (2, 16)))
         line = {
-            "metric": "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "metric": "2160p_me_frames_per_sec" if SHARD_SB_ROWS else "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s",
+            "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if SHARD_SB_ROWS else "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(world),
             "sb_per_sec": fps * SB_PER_FRAME,
-            "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": N_PICS * W * H,
+            "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": N_PICS * W * H * (2 if USE_16BIT else 1),
                     "d2h_bytes_per_step": len(jobs) * n_sb * 85 * 40, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
@@ -640,8 +673,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="me", choices=["me", "txq"],
-                    help="me: 1080p motion estimation (headline, BASELINE configs[1]); txq: transform + quantisation sweep (configs[3])")
+    ap.add_argument("--workload", default="me", choices=["me", "me4k", "txq"],
+                    help="me: 1080p motion estimation (headline, BASELINE configs[1]); me4k: 3840x2160 10-bit, SB rows sharded over "
+                         "the GPUs (configs[2]); txq: transform + quantisation sweep (configs[3])")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -649,6 +683,7 @@ def main():
     if args.workload == "txq":
         run_txq(args, rank, world, local_rank)
         return
+    select_workload(args.workload)
     if args.impl == "reference":
         run_reference_impl(args, rank)
         return

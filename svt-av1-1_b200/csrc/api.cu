@@ -239,7 +239,10 @@ int32_t svtme_picture_upload(SvtMeContext* ctx, int32_t slot, const uint8_t* lum
     Slot& s = ctx->slots[slot];
     int32_t rc = guard_slot_rewrite(ctx, s);
     if (rc != SVTME_OK) return rc;
-    CU(cudaMemcpy2DAsync(s.luma, ctx->width, luma, stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
+    if (stride == ctx->width)                             // contiguous plane: one linear copy
+        CU(cudaMemcpyAsync(s.luma, luma, (size_t)ctx->width * ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
+    else
+        CU(cudaMemcpy2DAsync(s.luma, ctx->width, luma, stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
     return build_pyramid(ctx, s, s.luma, ctx->width);
 }
 
@@ -255,8 +258,11 @@ int32_t svtme_picture_upload_16bit(SvtMeContext* ctx, int32_t slot, const uint16
         CU(cudaMalloc(&ctx->d_in16, n * sizeof(uint16_t)));
         CU(cudaMalloc(&ctx->d_rem, n));
     }
-    CU(cudaMemcpy2DAsync(ctx->d_in16, (size_t)ctx->width * 2, luma16, (size_t)stride * 2, (size_t)ctx->width * 2, ctx->height,
-                         cudaMemcpyHostToDevice, ctx->copy_in));
+    if (stride == ctx->width)
+        CU(cudaMemcpyAsync(ctx->d_in16, luma16, n * sizeof(uint16_t), cudaMemcpyHostToDevice, ctx->copy_in));
+    else
+        CU(cudaMemcpy2DAsync(ctx->d_in16, (size_t)ctx->width * 2, luma16, (size_t)stride * 2, (size_t)ctx->width * 2, ctx->height,
+                             cudaMemcpyHostToDevice, ctx->copy_in));
     launch_unpack16(ctx->d_in16, ctx->width, s.luma, bit_inc ? ctx->d_rem : nullptr, ctx->width, ctx->height, ctx->copy_in);
     ctx->launches++;
     CU(cudaGetLastError());
