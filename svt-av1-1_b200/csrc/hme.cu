@@ -88,6 +88,9 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
     const int chunk = max(1, kRegionWinWords / pitch - extra);
     const int rs = gtid & (RSPLIT - 1);
     constexpr int kTilesPerPass = kGroupThreads / RSPLIT;
+    // t / d as umulhi(t, 2^32 / d + 1): exact while t * d < 2^32 (t, d are a few thousand at most here); d == 1 would
+    // need the multiplier 2^32, so a one-tile row (search width <= 8) keeps the plain index
+    const uint32_t inv_wcols = 0xFFFFFFFFu / (uint32_t)(2 * tpr + W) + 1u, inv_tpr = tpr > 1 ? 0xFFFFFFFFu / (uint32_t)tpr + 1u : 0u;
     uint32_t best = 0xFFFFFFFFu;
     if (gtid == 0) *best_slot = 0xFFFFFFFFu;
     for (int i0 = 0; i0 < sah; i0 += chunk) {
@@ -97,7 +100,7 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
         group_bar(bar_id);                              // previous users of the window are done
 #pragma unroll 4
         for (int t = gtid; t < wrows * wcols; t += kGroupThreads) {
-            const int r = t / wcols, c = t - r * wcols;
+            const int r = (int)__umulhi((uint32_t)t, inv_wcols), c = t - r * wcols;
             win[r * pitch + c] = ldg_u32_unaligned(rp.at(rx + 4 * c, ry + i0 + r));
         }
         group_bar(bar_id);
@@ -105,7 +108,7 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
         for (int t0 = 0; t0 < ntiles; t0 += kTilesPerPass) {
             const int t = t0 + gtid / RSPLIT;
             const bool live = t < ntiles;
-            const int i = live ? t / tpr : 0, jt = live ? t - i * tpr : 0;
+            const int i = !live ? 0 : tpr > 1 ? (int)__umulhi((uint32_t)t, inv_tpr) : t, jt = live ? t - i * tpr : 0;
             uint32_t lo[2][4], hi[2][4];
 #pragma unroll
             for (int k = 0; k < 2; k++)
