@@ -263,7 +263,9 @@ def run_gpu_impl(args, rank, world, local_rank):
         host = torch.from_numpy(frames).pin_memory()                   # pinned host planes (e2e source)
         dev = host.cuda(non_blocking=False)                             # HBM-resident planes (value source)
     jobs = gop_jobs()
-    ctx = pkg.MeContext(W, H, N_PICS, device=local_rank)
+    # two sets of picture slots: consecutive e2e steps (consecutive sequences of a stream) alternate between them, so
+    # the uploads of one sequence overlap the searches of the previous one, as in a streaming encoder with look-ahead
+    ctx = pkg.MeContext(W, H, 2 * N_PICS, device=local_rank)
     specs = []
     for poc, tl, r0, r1 in jobs:
         p = pkg.default_params(W, H, 2, tl, 3, 1 if tl < 3 else 0)
@@ -280,22 +282,51 @@ def run_gpu_impl(args, rank, world, local_rank):
     job_resident, _, _ = ctx.make_jobs(specs, out_ptrs=[None] * len(jobs), sb_rows=sb_rows)   # results stay in HBM
     # e2e: one batch per mini-GOP (8 pictures) so that uploads, searches and result copies of consecutive
     # batches overlap on the context's three streams
-    gop_batches = [ctx.make_jobs(specs[g:g + 8], out_ptrs=ptrs[g:g + 8], sb_rows=sb_rows)[0] for g in range(0, len(jobs), 8)]
+    gop_batches = [[ctx.make_jobs([(c + o, r0 + o, r1 + o, p) for (c, r0, r1, p) in specs[g:g + 8]], out_ptrs=ptrs[g:g + 8], sb_rows=sb_rows)[0]
+                    for g in range(0, len(jobs), 8)] for o in (0, N_PICS)]
     stride = W
+    e2e_count = [0]
 
     def step_resident():
         for i in range(N_PICS):
             ctx.upload_device(i, dev[i].data_ptr(), stride)
         ctx.motion_estimate_async(job_resident)
 
-    def step_e2e():
+    # Optional: one rank uploads each picture and the others import it over NVLink (svtme_picture_upload_ipc). Off by default:
+    # on this box every GPU has its own host link, and the per-step hand-shakes cost more than the saved H2D bytes
+    # (N=2, 4K: 1155 frames/s replicated vs 1368 with independent uploads).
+    replicate = SHARD_SB_ROWS and world > 1 and os.environ.get("SVTME_BENCH_REPLICATE") == "1"
+    if replicate:
+        # one rank uploads each picture from the host; the others import it over NVLink (CUDA IPC + peer copy)
+        host_pg = dist.new_group(backend="gloo")            # host-side hand-shakes only
+        tokens = [None] * world
+        dist.all_gather_object(tokens, [ctx.export_slot(i) for i in range(2 * N_PICS)])
+
+    def step_e2e_replicated(base):
+        ctx.synchronize_uploads()                           # host waits for earlier copies only; the searches keep running
+        dist.barrier(group=host_pg)                         # ... on every rank: importers are done, owners may rewrite slots
+        for i in range(rank, N_PICS, world):
+            rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, base + i, host[i].data_ptr(), stride, None)
+            assert rc == 0
+        dist.barrier(group=host_pg)                         # every owner has issued its uploads
         for i in range(N_PICS):
-            if USE_16BIT:
-                rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, i, host[i].data_ptr(), stride, None)
-                assert rc == 0
-            else:
-                ctx.upload_ptr(i, host[i].data_ptr(), stride)
-        for jb in gop_batches:
+            if i % world != rank:
+                ctx.upload_ipc(base + i, tokens[i % world][base + i])
+
+    def step_e2e():
+        which = e2e_count[0] & 1
+        e2e_count[0] += 1
+        base = which * N_PICS
+        if replicate:
+            step_e2e_replicated(base)
+        else:
+            for i in range(N_PICS):
+                if USE_16BIT:
+                    rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, base + i, host[i].data_ptr(), stride, None)
+                    assert rc == 0
+                else:
+                    ctx.upload_ptr(base + i, host[i].data_ptr(), stride)
+        for jb in gop_batches[which]:
             ctx.motion_estimate_async(jb)
 
     def barrier():
@@ -339,7 +370,7 @@ def run_gpu_impl(args, rank, world, local_rank):
     for _ in range(max(1, args.warmup // 2)):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
-    ctx.fetch(gop_batches[-1])
+    ctx.fetch(gop_batches[0][-1])
     checksum = int(out.view(torch.int32).sum(dtype=torch.int64).item()) if rank == 0 else 0
     ctx.close()
 
@@ -368,7 +399,9 @@ def run_gpu_impl(args, rank, world, local_rank):
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if SHARD_SB_ROWS else "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(world),
             "sb_per_sec": fps * SB_PER_FRAME,
-            "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": N_PICS * W * H * (2 if USE_16BIT else 1),
+            "e2e": {"value": fps_e2e, "unit": "frames/s",
+                    "h2d_bytes_per_step": (len(range(rank, N_PICS, world)) if replicate else N_PICS) * W * H * (2 if USE_16BIT else 1),
+                    "replication": "each picture uploaded by one rank, imported by the others over NVLink (svtme_picture_upload_ipc)" if replicate else None,
                     "d2h_bytes_per_step": len(jobs) * n_sb * 85 * 40, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",

@@ -121,6 +121,26 @@ int32_t svtme_picture_upload(SvtMeContext *ctx, int32_t slot, const uint8_t *lum
  * pyramid build; when 'bit_inc' is not NULL it receives the remainder plane (HOST memory, width bytes per row,
  * height rows; in place by svtme_synchronize / svtme_join). */
 int32_t svtme_picture_upload_16bit(SvtMeContext *ctx, int32_t slot, const uint16_t *luma16, int32_t stride, uint8_t *bit_inc);
+/* Replicate a picture that another context of THIS process (normally on another GPU) already holds: the peer slot's
+ * luma crosses NVLink with a peer-to-peer copy (cudaMemcpy2DAsync between devices, peer access enabled on first use)
+ * and the pyramid is rebuilt locally. Ordered on-device after the peer's upload; the peer's next rewrite of that
+ * slot waits for this copy. This is how reference pictures are replicated when pictures / SB rows of one stream are
+ * sharded over the GPUs of a box (no collective, north_star). */
+int32_t svtme_picture_upload_peer(SvtMeContext *ctx, int32_t slot, SvtMeContext *peer, int32_t peer_slot);
+/* Same across PROCESSES (one process per GPU): the owner exports a slot once, ships the 152-byte token to the other
+ * ranks by any host channel, and they import pictures from it. Ordering is the caller's: the owner must have ISSUED
+ * its upload into the slot before an importer calls svtme_picture_upload_ipc (an inter-process event then orders the
+ * copy behind that upload on the device), and must not rewrite the slot until the importers have synchronised. */
+typedef struct SvtMeIpcSlot {
+    uint8_t  mem_handle[64], event_handle[64];   /* cudaIpcMemHandle_t of the slot allocation, cudaIpcEventHandle_t of its ready event */
+    int64_t  luma_offset;                        /* byte offset of pixel (0,0) of the padded full plane inside the allocation */
+    int32_t  pitch, device, width, height;
+} SvtMeIpcSlot;
+int32_t svtme_slot_export(SvtMeContext *ctx, int32_t slot, SvtMeIpcSlot *out);
+/* Wait (host) until every upload / import issued so far has landed; searches keep running. After it an importer may
+ * tell the owner that the exported slots can be rewritten. */
+int32_t svtme_synchronize_uploads(SvtMeContext *ctx);
+int32_t svtme_picture_upload_ipc(SvtMeContext *ctx, int32_t slot, const SvtMeIpcSlot *src);
 /* Same, from a luma plane that already lives in device memory (no H2D copy). */
 int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8_t *d_luma, int32_t stride);
 /* Read one padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) as tightly packed rows of

@@ -12,6 +12,7 @@ EXPORTED_SYMBOLS = (
     "svtme_picture_upload_device", "svtme_picture_download", "svtme_motion_estimate",
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
+    "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
 )
 KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
 
@@ -30,6 +31,11 @@ class SvtMeParams(C.Structure):
         ("hme_l1_h", C.c_int32 * 2), ("hme_l2_w", C.c_int32 * 2), ("hme_l2_h", C.c_int32 * 2),
         ("search_area_w", C.c_int32), ("search_area_h", C.c_int32),
         ("hme_l0_mult_x", C.c_int32), ("hme_l0_mult_y", C.c_int32)]
+
+
+class SvtMeIpcSlot(C.Structure):
+    _fields_ = [("mem_handle", C.c_uint8 * 64), ("event_handle", C.c_uint8 * 64), ("luma_offset", C.c_int64),
+                ("pitch", C.c_int32), ("device", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
 
 
 class SvtMeJob(C.Structure):
@@ -75,6 +81,12 @@ def load_library():
     lib.svtme_picture_upload.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
     lib.svtme_picture_upload_16bit.restype = C.c_int32
     lib.svtme_picture_upload_16bit.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]
+    lib.svtme_picture_upload_peer.restype = C.c_int32
+    lib.svtme_picture_upload_peer.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+    lib.svtme_slot_export.restype = C.c_int32
+    lib.svtme_slot_export.argtypes = [C.c_void_p, C.c_int32, C.POINTER(SvtMeIpcSlot)]
+    lib.svtme_picture_upload_ipc.restype = C.c_int32
+    lib.svtme_picture_upload_ipc.argtypes = [C.c_void_p, C.c_int32, C.POINTER(SvtMeIpcSlot)]
     lib.svtme_picture_upload_device.restype = C.c_int32
     lib.svtme_picture_upload_device.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
     lib.svtme_picture_download.restype = C.c_int32
@@ -86,6 +98,8 @@ def load_library():
         f.argtypes = [C.c_void_p, C.POINTER(SvtMeJob), C.c_int32]
     lib.svtme_synchronize.restype = C.c_int32
     lib.svtme_synchronize.argtypes = [C.c_void_p]
+    lib.svtme_synchronize_uploads.restype = C.c_int32
+    lib.svtme_synchronize_uploads.argtypes = [C.c_void_p]
     lib.svtme_join.restype = C.c_int32
     lib.svtme_join.argtypes = [C.c_void_p]
     lib.svtme_stream.restype = C.c_void_p
@@ -154,6 +168,20 @@ class MeContext:
                                                         bit_inc.ctypes.data if bit_inc is not None else None),
                     "svtme_picture_upload_16bit")
 
+    def upload_peer(self, slot, peer, peer_slot):
+        """Replicate picture `peer_slot` of another MeContext of this process (peer-to-peer copy + local pyramid)."""
+        self._check(self.lib.svtme_picture_upload_peer(self._h, slot, peer._h, peer_slot), "svtme_picture_upload_peer")
+
+    def export_slot(self, slot):
+        """Token (bytes) another PROCESS passes to upload_ipc to replicate pictures uploaded into this slot."""
+        t = SvtMeIpcSlot()
+        self._check(self.lib.svtme_slot_export(self._h, slot, C.byref(t)), "svtme_slot_export")
+        return bytes(t)
+
+    def upload_ipc(self, slot, token):
+        t = token if isinstance(token, SvtMeIpcSlot) else SvtMeIpcSlot.from_buffer_copy(token)
+        self._check(self.lib.svtme_picture_upload_ipc(self._h, slot, C.byref(t)), "svtme_picture_upload_ipc")
+
     def upload_ptr(self, slot, host_ptr, stride):
         self._check(self.lib.svtme_picture_upload(self._h, slot, host_ptr, stride), "svtme_picture_upload")
 
@@ -201,6 +229,9 @@ class MeContext:
 
     def synchronize(self):
         self._check(self.lib.svtme_synchronize(self._h), "svtme_synchronize")
+
+    def synchronize_uploads(self):
+        self._check(self.lib.svtme_synchronize_uploads(self._h), "svtme_synchronize_uploads")
 
     def join(self):
         self._check(self.lib.svtme_join(self._h), "svtme_join")

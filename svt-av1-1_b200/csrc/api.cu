@@ -10,6 +10,8 @@
 #include "me_common.cuh"
 #include <cstdio>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -40,8 +42,10 @@ struct Slot {
     DPyramid pyr;
     size_t plane_bytes[3] = { 0, 0, 0 };
     cudaEvent_t ready = nullptr;  // pyramid of the last upload is complete
+    cudaEvent_t ready_ipc = nullptr;   // same instant, inter-process flavour (exported by svtme_slot_export)
     int last_reader = -1;         // ring entry of the last batch that reads this slot ...
     int64_t last_reader_seq = -1; // ... and that batch's sequence number
+    std::vector<cudaEvent_t> peer_reads;   // copies other contexts took of this slot since its last rewrite (owned by them)
 };
 
 struct SvtMeContext {
@@ -49,6 +53,10 @@ struct SvtMeContext {
     cudaStream_t stream = nullptr, copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t join_ev = nullptr;
     std::vector<Slot> slots;
+    std::mutex peer_mu;                   // guards Slot::peer_reads (written by the contexts that copy from us)
+    std::vector<cudaEvent_t> peer_events; // events this context records after copying from a peer (round-robin)
+    size_t next_peer_event = 0;
+    std::map<std::string, std::pair<void*, cudaEvent_t>> ipc_open;   // imported slots: mem handle bytes -> (base, ready event)
     uint16_t* d_in16 = nullptr;           // staging of a 16-bit luma plane (svtme_picture_upload_16bit), width * height samples
     uint8_t* d_rem = nullptr;             // its 2-bit remainder plane
     Batch ring[kRing];
@@ -151,7 +159,12 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     *out = ctx;                                              // handed out even on failure so the error text is readable
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+    {   // the upload stream also runs the (tiny) split / pyramid kernels: highest priority, so their CTAs are placed as soon as
+        // any search CTA retires instead of waiting for the whole grid of a 10 ms search kernel to be issued
+        int least = 0, greatest = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        CU(cudaStreamCreateWithPriority(&ctx->copy_in, cudaStreamNonBlocking, greatest));
+    }
     CU(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming));
     for (auto& b : ctx->ring) {
@@ -174,7 +187,9 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
         describe_plane(s.pyr.sixteenth, m, width >> 2, height >> 2, kPadSixteenth);
         CU(cudaMemsetAsync(s.base, 0, luma_bytes + s.plane_bytes[0] + s.plane_bytes[1] + s.plane_bytes[2], ctx->copy_in));
         CU(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s.ready_ipc, cudaEventDisableTiming | cudaEventInterprocess));
         CU(cudaEventRecord(s.ready, ctx->copy_in));
+        CU(cudaEventRecord(s.ready_ipc, ctx->copy_in));
     }
     CU(cudaStreamSynchronize(ctx->copy_in));
     return SVTME_OK;
@@ -193,8 +208,10 @@ void svtme_destroy(SvtMeContext* ctx) {
     for (cudaStream_t st : { ctx->copy_in, ctx->stream, ctx->copy_out }) if (st) cudaStreamSynchronize(st);
     for (auto& t : ctx->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
-    for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); }
+    for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); if (s.ready_ipc) cudaEventDestroy(s.ready_ipc); }
     cudaFree(ctx->d_in16); cudaFree(ctx->d_rem);
+    for (auto e : ctx->peer_events) cudaEventDestroy(e);
+    for (auto& kv : ctx->ipc_open) { cudaIpcCloseMemHandle(kv.second.first); cudaEventDestroy(kv.second.second); }
     for (auto& b : ctx->ring) {
         free_batch(b);
         if (b.computed) cudaEventDestroy(b.computed);
@@ -212,6 +229,10 @@ int64_t svtme_kernel_launches(const SvtMeContext* ctx) { return ctx ? ctx->launc
 // A slot may be rewritten only after the last batch that reads it has finished its kernels.
 static int32_t guard_slot_rewrite(SvtMeContext* ctx, Slot& s) {
     if (s.last_reader >= 0) CU(cudaStreamWaitEvent(ctx->copy_in, ctx->ring[s.last_reader].computed, 0));
+    std::lock_guard<std::mutex> lock(ctx->peer_mu);
+    for (cudaEvent_t e : s.peer_reads)                    // peers still copying the old picture; a context that has been
+        if (cudaStreamWaitEvent(ctx->copy_in, e, 0) != cudaSuccess) (void)cudaGetLastError();   // destroyed since has drained its copies
+    s.peer_reads.clear();
     return SVTME_OK;
 }
 
@@ -219,6 +240,7 @@ static int32_t build_pyramid(SvtMeContext* ctx, Slot& s, const uint8_t* d_luma, 
     { LaunchTimer t(ctx, SVTME_KERNEL_PYRAMID, ctx->copy_in); launch_pyramid(d_luma, stride, s.pyr, ctx->copy_in); }
     CU(cudaGetLastError());
     CU(cudaEventRecord(s.ready, ctx->copy_in));
+    CU(cudaEventRecord(s.ready_ipc, ctx->copy_in));
     return SVTME_OK;
 }
 
@@ -268,6 +290,97 @@ int32_t svtme_picture_upload_16bit(SvtMeContext* ctx, int32_t slot, const uint16
     CU(cudaGetLastError());
     if (bit_inc) CU(cudaMemcpyAsync(bit_inc, ctx->d_rem, n, cudaMemcpyDeviceToHost, ctx->copy_in));
     return build_pyramid(ctx, s, s.luma, ctx->width);
+}
+
+// interior of the padded full plane = the picture itself; every upload flavour leaves it there
+static const uint8_t* slot_picture(const Slot& s) { return s.pyr.full.buf + (size_t)s.pyr.full.oy * s.pyr.full.stride + s.pyr.full.ox; }
+
+int32_t svtme_picture_upload_peer(SvtMeContext* ctx, int32_t slot, SvtMeContext* peer, int32_t peer_slot) {
+    if (!ctx || !peer || peer == ctx || slot < 0 || slot >= (int)ctx->slots.size() || peer_slot < 0 ||
+        peer_slot >= (int)peer->slots.size() || peer->width != ctx->width || peer->height != ctx->height)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_peer: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    bool direct = true;                                   // peer memory is addressable from our kernels
+    if (peer->device != ctx->device) {
+        int can = 0;
+        CU(cudaDeviceCanAccessPeer(&can, ctx->device, peer->device));
+        if (can) {
+            const cudaError_t e = cudaDeviceEnablePeerAccess(peer->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU(e);
+            (void)cudaGetLastError();                     // clear "already enabled"
+        }
+        direct = can != 0;
+    }
+    Slot& s = ctx->slots[slot];
+    Slot& ps = peer->slots[peer_slot];
+    int32_t rc = guard_slot_rewrite(ctx, s);
+    if (rc != SVTME_OK) return rc;
+    CU(cudaStreamWaitEvent(ctx->copy_in, ps.ready, 0));   // the peer's upload (and pyramid) of that picture
+    if (direct) {
+        // the pyramid kernel reads the peer's picture straight over NVLink: no staging copy, ~1.3 reads per pixel
+        rc = build_pyramid(ctx, s, slot_picture(ps), ps.pyr.full.stride);
+    } else {
+        cudaMemcpy3DPeerParms cp;                         // no peer access: the driver stages the copy
+        memset(&cp, 0, sizeof(cp));
+        cp.srcDevice = peer->device; cp.dstDevice = ctx->device;
+        cp.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t*>(slot_picture(ps)), ps.pyr.full.stride, ctx->width, ctx->height);
+        cp.dstPtr = make_cudaPitchedPtr(s.luma, ctx->width, ctx->width, ctx->height);
+        cp.extent = make_cudaExtent(ctx->width, ctx->height, 1);
+        CU(cudaMemcpy3DPeerAsync(&cp, ctx->copy_in));
+        rc = build_pyramid(ctx, s, s.luma, ctx->width);
+    }
+    if (rc != SVTME_OK) return rc;
+    if (ctx->peer_events.size() < 64) {
+        cudaEvent_t e = nullptr;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->peer_events.push_back(e);
+    }
+    cudaEvent_t done = ctx->peer_events[ctx->next_peer_event++ % ctx->peer_events.size()];
+    CU(cudaEventRecord(done, ctx->copy_in));              // the peer's next rewrite of that slot waits for this
+    { std::lock_guard<std::mutex> lock(peer->peer_mu); ps.peer_reads.push_back(done); }
+    return SVTME_OK;
+}
+
+int32_t svtme_slot_export(SvtMeContext* ctx, int32_t slot, SvtMeIpcSlot* out) {
+    if (!ctx || !out || slot < 0 || slot >= (int)ctx->slots.size()) return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_slot_export: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    const Slot& s = ctx->slots[slot];
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(cudaIpcEventHandle_t) == 64, "token layout");
+    memset(out, 0, sizeof(*out));
+    CU(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->mem_handle), s.base));
+    CU(cudaIpcGetEventHandle(reinterpret_cast<cudaIpcEventHandle_t*>(out->event_handle), s.ready_ipc));
+    out->luma_offset = (int64_t)(slot_picture(s) - s.base);
+    out->pitch = s.pyr.full.stride; out->device = ctx->device; out->width = ctx->width; out->height = ctx->height;
+    return SVTME_OK;
+}
+
+int32_t svtme_synchronize_uploads(SvtMeContext* ctx) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->copy_in));
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_upload_ipc(SvtMeContext* ctx, int32_t slot, const SvtMeIpcSlot* src) {
+    if (!ctx || !src || slot < 0 || slot >= (int)ctx->slots.size() || src->width != ctx->width || src->height != ctx->height)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_ipc: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    const std::string key(reinterpret_cast<const char*>(src->mem_handle), 64);
+    auto it = ctx->ipc_open.find(key);
+    if (it == ctx->ipc_open.end()) {
+        void* base = nullptr; cudaEvent_t ev = nullptr;
+        cudaIpcMemHandle_t mh; cudaIpcEventHandle_t eh;
+        memcpy(&mh, src->mem_handle, 64); memcpy(&eh, src->event_handle, 64);
+        CU(cudaIpcOpenMemHandle(&base, mh, cudaIpcMemLazyEnablePeerAccess));
+        CU(cudaIpcOpenEventHandle(&ev, eh));
+        it = ctx->ipc_open.emplace(key, std::make_pair(base, ev)).first;
+    }
+    Slot& s = ctx->slots[slot];
+    int32_t rc = guard_slot_rewrite(ctx, s);
+    if (rc != SVTME_OK) return rc;
+    CU(cudaStreamWaitEvent(ctx->copy_in, it->second.second, 0));
+    // the mapping is peer memory our kernels can address: the pyramid kernel reads the picture straight over NVLink
+    return build_pyramid(ctx, s, static_cast<const uint8_t*>(it->second.first) + src->luma_offset, src->pitch);
 }
 
 int32_t svtme_picture_download(SvtMeContext* ctx, int32_t slot, int32_t level, uint8_t* dst, size_t dst_bytes,
