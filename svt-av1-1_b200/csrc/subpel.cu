@@ -37,6 +37,7 @@ struct SpShared {
     uint32_t pu_sad[kNumPu], pu_mv[kNumPu], pu_ssd[kNumPu];
     int32_t  pu_dir[kNumPu];
     uint32_t pu_imv[kNumPu];            // MV at entry of the current stage
+    int32_t  bbox[4];                   // min X, min Y, max -X... see the kernel: bounding box of the blocks' window positions
 };
 constexpr int kSpSmemBytes = (int)sizeof(SpShared);
 
@@ -153,14 +154,32 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     SbScratch& scr = job.scratch[sb];
     const DPlane& rp = job.ref[list].full;
-    const int sax = scr.sa_x[list], say = scr.sa_y[list], saw = scr.sa_w[list], sah = scr.sa_h[list];
-    const int ww = ((saw + 63 + 7 + 3) >> 2) + 1;        // window words per row actually used (+1: taps of the last B word)
-    const int wr = sah + 63 + 7;                          // window rows
-
-    // ---- stage: source SB, PU state, plane A
+    // ---- stage: source SB, PU state
     for (int t = tid; t < 64 * 16; t += kSpThreads)
         sh.src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + (t >> 4)));
     if (tid < kNumPu) { sh.pu_sad[tid] = scr.best_sad[list][tid]; sh.pu_mv[tid] = scr.best_mv[list][tid]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
+    if (tid < 4) sh.bbox[tid] = 0x7FFFFFFF;
+    __syncthreads();
+    // The refinement only reads the window around the 256 (level, 8x8 block) positions the full-pel search chose
+    // (every later MV stays within one integer pixel of them), so the window that is staged and interpolated is their
+    // bounding box, not the whole search area: with coherent motion that is a fraction of it. The box becomes the new
+    // window origin (sax, say) and extent (ww words x wr rows); everything below is unchanged.
+    int sax = scr.sa_x[list], say = scr.sa_y[list];
+    {
+        const int blk = tid & 63, L = tid >> 6, bx = blk & 7, by = blk >> 3;
+        const uint32_t mv = sh.pu_mv[pu_of_block(L, bx, by)];
+        const int X = kMargin + (mv_x(mv) >> 2) - sax + bx * 8, Y = kMargin + (mv_y(mv) >> 2) - say + by * 8;
+        const int xmin = __reduce_min_sync(0xffffffffu, X), ymin = __reduce_min_sync(0xffffffffu, Y);
+        const int xneg = __reduce_min_sync(0xffffffffu, -X), yneg = __reduce_min_sync(0xffffffffu, -Y);
+        if ((tid & 31) == 0) { atomicMin(&sh.bbox[0], xmin); atomicMin(&sh.bbox[1], ymin); atomicMin(&sh.bbox[2], xneg); atomicMin(&sh.bbox[3], yneg); }
+    }
+    __syncthreads();
+    const int dx = (sh.bbox[0] - kMargin) & ~3, dy = sh.bbox[1] - kMargin;   // window origin moves by (dx, dy), dx word-aligned
+    sax += dx; say += dy;
+    const int ww = ((-sh.bbox[2] - dx + 15) >> 2) + 1;   // window words per row actually used (+1: taps of the last B word)
+    const int wr = -sh.bbox[3] - dy + 12;                 // window rows: 8 block rows + one above, three below for the taps
+
+    // ---- plane A
     const uint32_t inv_ww = 0xFFFFFFFFu / (uint32_t)ww + 1u;   // t / ww == umulhi(t, inv_ww) for t * ww < 2^32
     for (int t = tid; t < wr * ww; t += kSpThreads) {
         const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
