@@ -45,3 +45,20 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def qtables():
+    """tests/golden/txq_qtables.npz: the luma quantiser lanes of EVERY qindex (0..255) for 8- and 10-bit, straight from the
+    reference's av1_build_quantizer tables: q10[depth][qindex] = zbin dc,ac, round dc,ac, quant dc,ac, quant_shift dc,ac, dequant dc,ac."""
+    ref = T.reference()
+    tab = np.zeros((2, 256, 10), np.int16)
+    for d, bd in enumerate((8, 10)):
+        for qi in range(256):
+            tab[d, qi] = T.quant_params(ref, qi, bd)
+    out = os.path.join(HERE, "txq_qtables.npz")
+    np.savez_compressed(out, q10=tab)
+    print("wrote", out, os.path.getsize(out), "bytes")
+
+
+if __name__ == "__main__" and "--qtables" in sys.argv:
+    qtables()

@@ -35,3 +35,11 @@ def test_oracle_plane_equals_per_block():
                 assert np.array_equal(out["coeff"][k], c.reshape(-1)) and np.array_equal(out["qcoeff"][k], qc)
                 assert np.array_equal(out["dqcoeff"][k], dq) and out["eob"][k] == eob and out["energy"][k] == e
                 k += 1
+
+
+def test_qtables_fixture_shape_and_monotone_steps():
+    import os
+    tab = np.load(os.path.join(os.path.dirname(G.PATH), "txq_qtables.npz"))["q10"]
+    assert tab.shape == (2, 256, 10)
+    assert (np.diff(tab[:, :, 9].astype(np.int32), axis=1) >= 0).all()        # AC dequant step grows with qindex
+    assert (tab[:, :, 8] > 0).all() and (tab[:, :, 6] > 0).all()              # DC dequant step, quant_shift positive

@@ -156,3 +156,18 @@ def test_device_entry_point_and_launch_count(txq, q10s, pkg):
     want = T.txq_plane(meo, res, w, h, t, q10)
     assert np.array_equal(d_q.cpu().numpy(), want["qcoeff"])
     assert np.array_equal(d_eob.cpu().numpy().view(np.uint16), want["eob"])
+
+
+def test_every_qindex(txq):
+    """BASELINE configs[3] "all qindex": every luma quantiser (qindex 0..255, 8- and 10-bit; tables taken from the reference,
+    tests/golden/txq_qtables.npz) on three size classes (log_scale 0, 1, 2) against the oracle."""
+    import os
+    meo = T.oracle()
+    tab = np.load(os.path.join(os.path.dirname(G.PATH), "txq_qtables.npz"))["q10"]
+    rng = np.random.default_rng(255)
+    planes = {8: T.synth_residual(rng, 64, 128, 8), 10: T.synth_residual(rng, 64, 128, 10, "noise")}
+    for d, bd in enumerate((8, 10)):
+        for qi in range(256):
+            q10 = tab[d, qi]
+            w, h, t = [(8, 8, 0), (32, 16, 0), (64, 64, 0), (16, 16, 3), (4, 4, 9)][qi % 5]
+            assert_same(txq.fwd_txfm_quant(planes[bd], w, h, t, q10), T.txq_plane(meo, planes[bd], w, h, t, q10), f"qindex {qi} bd {bd} {w}x{h}")
