@@ -579,9 +579,9 @@ def run_txq(args, rank, world, local_rank):
     st = torch.cuda.ExternalStream(ctx.stream())
     quant = pkg.SvtTxqQuant.from_q10(q10)
 
-    def launch(c):
+    def launch(c, energy=True):
         ctx.fwd_txfm_quant_device(dev.data_ptr(), TXQ_W, TXQ_W, Hs, c[0], c[1], c[2], quant, d_out[0].data_ptr(), d_out[1].data_ptr(),
-                                  d_out[2].data_ptr(), d_eob.data_ptr(), d_en.data_ptr())
+                                  d_out[2].data_ptr(), d_eob.data_ptr(), d_en.data_ptr() if energy else None)
 
     def host_call(c, everything=True):
         """everything: all five outputs (what Av1EstimateTransform + the quantiser produce); else the subset EncDec consumes
@@ -623,6 +623,19 @@ def run_txq(args, rank, world, local_rank):
     for c, a, b in evs:
         per_ms.setdefault(c, []).append(a.elapsed_time(b))
     clocks = sampler.stop() if sampler else None
+    # outside the sweep: the 64-point sizes as EncDec calls them (no three_quad_energy wanted -> pruned kernels)
+    no_energy_ms = {}
+    for c in cases:
+        if 64 in c[:2]:
+            ts = []
+            for _ in range(args.warmup + args.steps):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(st)
+                launch(c, energy=False)
+                b.record(st)
+                ts.append((a, b))
+            sync_all()
+            no_energy_ms["%dx%d/%d" % c] = float(np.median([a.elapsed_time(b) for a, b in ts[args.warmup:]]))
     # e2e: host buffers through the synchronous C-ABI call, H2D + kernel + D2H per call
     for c in cases[:2]:
         host_call(c)
@@ -682,7 +695,10 @@ def run_txq(args, rank, world, local_rank):
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                              "bytes_model": "2 B/pixel residual in + 12 B per kept coefficient (coeff, qcoeff, dqcoeff) + 10 B per block (eob, energy)",
                              "worst_case": worst, "worst_frac": per[worst]["frac"]},
-                "per_case": per, "clocks": clocks, "result_checksum": checksum}
+                "per_case": per,
+                "per_case_without_energy": {k: {"ms": t, "Gpixel/s": npix / t / 1e6, "speedup_vs_with_energy": per[k]["ms"] / t}
+                                            for k, t in no_energy_ms.items()},
+                "clocks": clocks, "result_checksum": checksum}
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)

@@ -71,11 +71,15 @@ __host__ __device__ constexpr int shift2(int w, int h) { return ((w == 64 && h =
 // Geometry of one CTA: B = 256 / min(TXW, TXH) transform blocks, consecutive in raster order. The column pass has
 // B * TXW work items (one TXH-point transform each), the row pass B * TXH items (one TXW-point transform each); the
 // 256 threads loop over them, so rectangular sizes keep every thread busy in both passes.
-template <int TXW, int TXH> struct TxqGeom {
-    static constexpr int B = 256 / cmin(TXW, TXH);
-    static constexpr int PITCH = TXW + 1;          // odd: row r of slot s starts at word PITCH * (s * TXH + r)
-    static constexpr int SLOT = TXH * PITCH;
+// ENERGY = false (64-point sizes whose caller does not want three_quad_energy, e.g. the EncDec call sites): the rows and
+// columns that are only squared into the energy are never produced -- the column pass keeps ROWS = 32 rows, the row
+// pass reads 32 outputs, and the compiler prunes the straight-line 64-point graphs down to what feeds them.
+template <int TXW, int TXH, bool ENERGY> struct TxqGeom {
     static constexpr int PW = cmin(TXW, 32), PH = cmin(TXH, 32), N = PW * PH;
+    static constexpr int ROWS = ENERGY ? TXH : PH;  // rows of the column-pass output that are kept
+    static constexpr int B = 256 / cmin(TXW, ROWS);
+    static constexpr int PITCH = TXW + 1;          // odd: row r of slot s starts at word PITCH * (s * ROWS + r)
+    static constexpr int SLOT = ROWS * PITCH;
     static constexpr int SMEM = B * SLOT * (int)sizeof(int32_t);
     static constexpr bool BIG = TXW == 64 || TXH == 64;
     // resident CTAs per SM the register allocation is held to (256 threads each)
@@ -97,9 +101,9 @@ __device__ __forceinline__ int32_t top_bit_plus1(unsigned int bits) {           
 // contiguous run of each output array; warp w owns the w-th eighth of it and walks it 32 coefficients at a time, so
 // every warp store is one full 128-byte line and (for B >= 8) a transform block never leaves its warp: eob is a
 // per-lane running maximum of (iscan + 1) over non-zero dequantised values, reduced once per block.
-template <int TXW, int TXH, bool FULL>
+template <int TXW, int TXH, bool ENERGY, bool FULL>
 __device__ __forceinline__ void quant_phase(const TxqArgs& a, const int32_t* smem, unsigned int* s_eob, int blk0, int n_here) {
-    using G = TxqGeom<TXW, TXH>;
+    using G = TxqGeom<TXW, TXH, ENERGY>;
     constexpr int B = G::B, PITCH = G::PITCH, SLOT = G::SLOT, PW = G::PW, N = G::N;
     constexpr int LS = (TXW * TXH > 256) + (TXW * TXH > 1024);               // av1_get_tx_scale
     constexpr int WARP_COEFS = B * N / 8, ITER = WARP_COEFS / 32;
@@ -161,10 +165,10 @@ __device__ __forceinline__ void quant_phase(const TxqArgs& a, const int32_t* sme
     }
 }
 
-template <int TXW, int TXH>
-__global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(const TxqArgs a) {
-    using G = TxqGeom<TXW, TXH>;
-    constexpr int B = G::B, PITCH = G::PITCH, SLOT = G::SLOT, PW = G::PW, PH = G::PH, N = G::N;
+template <int TXW, int TXH, bool ENERGY>
+__global__ void __launch_bounds__(256, TxqGeom<TXW, TXH, ENERGY>::MIN_CTAS) txq_kernel(const TxqArgs a) {
+    using G = TxqGeom<TXW, TXH, ENERGY>;
+    constexpr int B = G::B, PITCH = G::PITCH, SLOT = G::SLOT, PW = G::PW, PH = G::PH, ROWS = G::ROWS;
     constexpr int CC = kCosCol[ilog2(TXW) - 2][ilog2(TXH) - 2], CR = kCosRow[ilog2(TXW) - 2][ilog2(TXH) - 2];
     constexpr bool RECT = (ilog2(TXW) - ilog2(TXH) == 1) || (ilog2(TXH) - ilog2(TXW) == 1);
     extern __shared__ __align__(16) int32_t smem_txq[];
@@ -191,13 +195,13 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(c
         txfm1d<TXH, CC>(ud ? K_ADST : a.vk, x);
         int32_t* col = smem_txq + slot * SLOT + (a.hk == K_FLIPADST ? TXW - 1 - c : c);
 #pragma unroll
-        for (int r = 0; r < TXH; r++) col[r * PITCH] = shift1(TXW, TXH) ? rshift_round(x[r], shift1(TXW, TXH)) : x[r];
+        for (int r = 0; r < ROWS; r++) col[r * PITCH] = shift1(TXW, TXH) ? rshift_round(x[r], shift1(TXW, TXH)) : x[r];
     }
     __syncthreads();
     // ---- horizontal pass: one item = one row of one block ("Rows"); the kept PW columns go back in place
 #pragma unroll
-    for (int j = tid; j < B * TXH; j += 256) {
-        const int slot = j / TXH, r = j % TXH;
+    for (int j = tid; j < B * ROWS; j += 256) {
+        const int slot = j / ROWS, r = j % ROWS;
         if (slot >= n_here) continue;
         int32_t* row = smem_txq + j * PITCH;                  // == slot * SLOT + r * PITCH
         int32_t y[TXW];
@@ -205,11 +209,11 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(c
         for (int c = 0; c < TXW; c++) y[c] = row[c];
         txfm1d<TXW, CR>(a.hk == K_FLIPADST ? K_ADST : a.hk, y);
 #pragma unroll
-        for (int c = 0; c < TXW; c++) {
+        for (int c = 0; c < (ENERGY ? TXW : PW); c++) {
             if (shift2(TXW, TXH)) y[c] = rshift_round(y[c], shift2(TXW, TXH));
             if (RECT) y[c] = mul_sqrt2(y[c]);
         }
-        if (G::BIG) {                                         // HandleTransform64x64_c & co: energy of what is dropped
+        if (G::BIG && ENERGY) {                                         // HandleTransform64x64_c & co: energy of what is dropped
             unsigned long long dropped = 0;
 #pragma unroll
             for (int c = 0; c < TXW; c++)
@@ -224,8 +228,8 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(c
     __syncthreads();
 
     // ---- quantisation: fast path when every block of the CTA exists and all three coefficient arrays are wanted
-    if (n_here == B && a.coeff && a.qcoeff && a.dqcoeff) quant_phase<TXW, TXH, true>(a, smem_txq, s_eob, blk0, n_here);
-    else quant_phase<TXW, TXH, false>(a, smem_txq, s_eob, blk0, n_here);
+    if (n_here == B && a.coeff && a.qcoeff && a.dqcoeff) quant_phase<TXW, TXH, ENERGY, true>(a, smem_txq, s_eob, blk0, n_here);
+    else quant_phase<TXW, TXH, ENERGY, false>(a, smem_txq, s_eob, blk0, n_here);
     __syncthreads();
     if (tid < n_here) {
         if (a.eob) a.eob[blk0 + tid] = (uint16_t)s_eob[tid];
@@ -233,17 +237,24 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH>::MIN_CTAS) txq_kernel(c
     }
 }
 
-template <int TXW, int TXH> static cudaError_t launch_one(const TxqArgs& a, cudaStream_t st) {
-    constexpr int B = TxqGeom<TXW, TXH>::B;
-    const int smem = TxqGeom<TXW, TXH>::SMEM;
+template <int TXW, int TXH, bool ENERGY> static cudaError_t launch_variant(const TxqArgs& a, cudaStream_t st) {
+    constexpr int B = TxqGeom<TXW, TXH, ENERGY>::B;
+    const int smem = TxqGeom<TXW, TXH, ENERGY>::SMEM;
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(txq_kernel<TXW, TXH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(txq_kernel<TXW, TXH, ENERGY>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    txq_kernel<TXW, TXH><<<(a.n_blocks + B - 1) / B, 256, smem, st>>>(a);
+    txq_kernel<TXW, TXH, ENERGY><<<(a.n_blocks + B - 1) / B, 256, smem, st>>>(a);
     return cudaGetLastError();
+}
+template <int TXW, int TXH> static cudaError_t launch_one(const TxqArgs& a, cudaStream_t st) {
+    if (TXW == 64 || TXH == 64) {                             // only the 64-point sizes drop coefficients
+        if (a.energy) return launch_variant<TXW, TXH, true>(a, st);
+        return launch_variant<TXW, TXH, (TXW != 64 && TXH != 64)>(a, st);
+    }
+    return launch_variant<TXW, TXH, true>(a, st);
 }
 
 cudaError_t launch_txq(int txw, int txh, const TxqArgs& a, cudaStream_t st) {

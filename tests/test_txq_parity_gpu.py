@@ -171,3 +171,20 @@ def test_every_qindex(txq):
             q10 = tab[d, qi]
             w, h, t = [(8, 8, 0), (32, 16, 0), (64, 64, 0), (16, 16, 3), (4, 4, 9)][qi % 5]
             assert_same(txq.fwd_txfm_quant(planes[bd], w, h, t, q10), T.txq_plane(meo, planes[bd], w, h, t, q10), f"qindex {qi} bd {bd} {w}x{h}")
+
+
+@pytest.mark.parametrize("size", [(64, 64), (64, 32), (32, 64), (16, 64), (64, 16)], ids=lambda s: f"{s[0]}x{s[1]}")
+def test_64_point_sizes_without_energy(txq, q10s, size):
+    """Callers that do not want three_quad_energy (EncDec) take the pruned kernels: same coefficients, levels and eob."""
+    w, h = size
+    meo = T.oracle()
+    rng = np.random.default_rng(64 + w + h)
+    for kind, key in (("mixed", sorted(q10s)[0]), ("noise", sorted(q10s)[-1])):
+        res = T.synth_residual(rng, 2 * h, 5 * w, key[0], kind)                  # 10 blocks: ragged last CTA
+        want = T.txq_plane(meo, res, w, h, 0, q10s[key])
+        got = txq.fwd_txfm_quant(res, w, h, 0, q10s[key], want=("coeff", "qcoeff", "dqcoeff", "eob"))
+        assert set(got) == {"coeff", "qcoeff", "dqcoeff", "eob"}
+        for k in got:
+            assert np.array_equal(got[k], want[k]), (w, h, kind, k)
+        only = txq.fwd_txfm_quant(res, w, h, 0, q10s[key], want=("qcoeff", "eob"))
+        assert np.array_equal(only["qcoeff"], want["qcoeff"]) and np.array_equal(only["eob"], want["eob"])
