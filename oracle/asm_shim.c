@@ -55,12 +55,17 @@ void ZeroOutCoeff32x32_SSE2(int16_t *b, uint32_t s, uint32_t o, uint32_t w, uint
 #define OFF_PATH(name) \
     void name(void) { fprintf(stderr, "asm_shim: off-path NASM symbol %s reached\n", #name); abort(); }
 
-OFF_PATH(aom_dc_128_predictor_16x16_sse2) OFF_PATH(aom_dc_128_predictor_4x4_sse2) OFF_PATH(aom_dc_128_predictor_8x8_sse2)
-OFF_PATH(aom_dc_left_predictor_16x16_sse2) OFF_PATH(aom_dc_left_predictor_4x4_sse2) OFF_PATH(aom_dc_left_predictor_8x8_sse2)
-OFF_PATH(aom_dc_predictor_16x16_sse2) OFF_PATH(aom_dc_predictor_4x4_sse2) OFF_PATH(aom_dc_predictor_8x8_sse2)
-OFF_PATH(aom_dc_top_predictor_16x16_sse2) OFF_PATH(aom_dc_top_predictor_4x4_sse2) OFF_PATH(aom_dc_top_predictor_8x8_sse2)
-OFF_PATH(aom_h_predictor_16x16_sse2) OFF_PATH(aom_h_predictor_4x4_sse2) OFF_PATH(aom_h_predictor_8x8_sse2)
-OFF_PATH(aom_v_predictor_16x16_sse2) OFF_PATH(aom_v_predictor_4x4_sse2) OFF_PATH(aom_v_predictor_8x8_sse2)
+/* NASM intra predictors: forwarded to the reference's own C versions (bit-identical by construction), so that the whole
+ * encoder can run from libsvtref.so (oracle/enc_driver.c dumps the ME stage of real encodes). */
+#include <stddef.h>
+#define FWD8(name, sz) \
+    void name##_##sz##_c(uint8_t *dst, ptrdiff_t stride, const uint8_t *above, const uint8_t *left); \
+    void name##_##sz##_sse2(uint8_t *dst, ptrdiff_t stride, const uint8_t *above, const uint8_t *left) { name##_##sz##_c(dst, stride, above, left); }
+#define FWD8_ALL(name) FWD8(name, 4x4) FWD8(name, 8x8) FWD8(name, 16x16)
+FWD8_ALL(aom_dc_128_predictor) FWD8_ALL(aom_dc_left_predictor) FWD8_ALL(aom_dc_predictor) FWD8_ALL(aom_dc_top_predictor)
+FWD8_ALL(aom_h_predictor) FWD8_ALL(aom_v_predictor)
+#define FWD16(name, sz) \
+    void name##_##sz##_c(uint16_t *dst, ptrdiff_t stride, const uint16_t *above, const uint16_t *left, int32_t bd); \
+    void name##_##sz##_sse2(uint16_t *dst, ptrdiff_t stride, const uint16_t *above, const uint16_t *left, int32_t bd) { name##_##sz##_c(dst, stride, above, left, bd); }
+FWD16(aom_highbd_dc_predictor, 4x4) FWD16(aom_highbd_dc_predictor, 8x8) FWD16(aom_highbd_v_predictor, 4x4) FWD16(aom_highbd_v_predictor, 8x8)
 OFF_PATH(aom_highbd_calc16x16var_sse2) OFF_PATH(aom_highbd_calc8x8var_sse2)
-OFF_PATH(aom_highbd_dc_predictor_4x4_sse2) OFF_PATH(aom_highbd_dc_predictor_8x8_sse2)
-OFF_PATH(aom_highbd_v_predictor_4x4_sse2) OFF_PATH(aom_highbd_v_predictor_8x8_sse2)

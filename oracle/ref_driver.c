@@ -10,7 +10,12 @@
  * EbMotionEstimation.c is #included (unity build) so its static functions are reachable;
  * no reference source is copied into this repository.
  */
+/* The reference's MotionEstimateLcu is compiled under another name so that the wrapper at the end of this file can
+ * record what the REAL encoder (oracle/enc_driver.c) feeds it and what it returns; with no dump open it is a plain call. */
+#define MotionEstimateLcu MotionEstimateLcu_reference
 #include "EbMotionEstimation.c"          /* resolved through -I$(REF)/Lib/Codec */
+#undef MotionEstimateLcu
+EbErrorType MotionEstimateLcu(PictureParentControlSet_t *, uint32_t, uint32_t, uint32_t, MeContext_t *, EbPictureBufferDesc_t *);
 #include "EbMotionEstimationProcess.h"
 #include "EbPictureAnalysisProcess.h"
 #include "EbMcp.h"
@@ -247,4 +252,55 @@ void ref_default_params(MeoParams *p, int32_t width, int32_t height, int32_t num
     p->hme_l0_mult_x = HME_LEVEL_0_SEARCH_AREA_MULTIPLIER_X[hierarchical_levels][temporal_layer_index];
     p->hme_l0_mult_y = HME_LEVEL_0_SEARCH_AREA_MULTIPLIER_Y[hierarchical_levels][temporal_layer_index];
     free(ctx); free(pcs); free(scs);
+}
+
+
+/* ---- ME dump of real encodes (golden vectors of BASELINE configs[0]) ------------------------------------------------
+ * Record per MotionEstimateLcu call: what the encoder's own processes set up for it (slice type, layers, HME flags,
+ * the MeContext search parameters, reference POCs), the source luma once per picture, and the MeCuResults_t rows it
+ * produced. Layout: a stream of int32 records, see tests/golden/make_encoder_golden.py. */
+#include <pthread.h>
+#include <stdio.h>
+static FILE *g_dump;
+static pthread_mutex_t g_dump_mu = PTHREAD_MUTEX_INITIALIZER;
+static uint64_t g_seen[4096]; static int g_nseen;
+
+int ref_me_dump_open(const char *path) { g_dump = fopen(path, "wb"); g_nseen = 0; return g_dump ? 0 : -1; }
+void ref_me_dump_close(void) { if (g_dump) fclose(g_dump); g_dump = NULL; }
+
+EbErrorType MotionEstimateLcu(PictureParentControlSet_t *pcs, uint32_t sb_index, uint32_t sb_origin_x, uint32_t sb_origin_y,
+                              MeContext_t *ctx, EbPictureBufferDesc_t *input_ptr) {
+    const EbErrorType rc = MotionEstimateLcu_reference(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
+    if (!g_dump) return rc;
+    SequenceControlSet_t *scs = (SequenceControlSet_t *)pcs->sequence_control_set_wrapper_ptr->objectPtr;
+    pthread_mutex_lock(&g_dump_mu);
+    int first = 1;
+    for (int i = 0; i < g_nseen; i++) if (g_seen[i] == pcs->picture_number) first = 0;
+    if (first && g_nseen < 4096) g_seen[g_nseen++] = pcs->picture_number;
+    int32_t h[48]; memset(h, 0, sizeof(h));
+    h[0] = 0x4D454447;                                    /* 'MEDG' */
+    h[1] = (int32_t)pcs->picture_number; h[2] = (int32_t)sb_index; h[3] = (int32_t)sb_origin_x; h[4] = (int32_t)sb_origin_y;
+    h[5] = scs->luma_width; h[6] = scs->luma_height;
+    h[7] = pcs->slice_type == P_SLICE ? 1 : pcs->slice_type == B_SLICE ? 2 : 0;
+    h[8] = pcs->temporal_layer_index; h[9] = pcs->hierarchical_levels; h[10] = pcs->is_used_as_reference_flag;
+    h[11] = (int32_t)pcs->ref_pic_poc_array[0]; h[12] = (int32_t)pcs->ref_pic_poc_array[1];
+    h[13] = pcs->enable_hme_flag; h[14] = pcs->enable_hme_level0_flag; h[15] = pcs->enable_hme_level1_flag; h[16] = pcs->enable_hme_level2_flag;
+    h[17] = pcs->use_subpel_flag; h[18] = pcs->max_number_of_pus_per_sb; h[19] = pcs->cu8x8_mode;
+    h[20] = ctx->number_hme_search_region_in_width; h[21] = ctx->number_hme_search_region_in_height;
+    h[22] = ctx->hme_level0_total_search_area_width; h[23] = ctx->hme_level0_total_search_area_height;
+    for (int i = 0; i < 2; i++) {
+        h[24 + i] = ctx->hme_level0_search_area_in_width_array[i]; h[26 + i] = ctx->hme_level0_search_area_in_height_array[i];
+        h[28 + i] = ctx->hme_level1_search_area_in_width_array[i]; h[30 + i] = ctx->hme_level1_search_area_in_height_array[i];
+        h[32 + i] = ctx->hme_level2_search_area_in_width_array[i]; h[34 + i] = ctx->hme_level2_search_area_in_height_array[i];
+    }
+    h[36] = ctx->search_area_width; h[37] = ctx->search_area_height;
+    h[38] = pcs->enc_mode; h[39] = pcs->pic_depth_mode; h[40] = first;
+    h[41] = (int32_t)sizeof(MeCuResults_t);
+    fwrite(h, sizeof(h), 1, g_dump);
+    if (first)                                            /* source luma of this picture (interior of the padded input plane) */
+        for (uint32_t y = 0; y < scs->luma_height; y++)
+            fwrite(input_ptr->bufferY + (size_t)(input_ptr->origin_y + y) * input_ptr->strideY + input_ptr->origin_x, 1, scs->luma_width, g_dump);
+    fwrite(pcs->me_results[sb_index], sizeof(MeCuResults_t), pcs->max_number_of_pus_per_sb, g_dump);
+    pthread_mutex_unlock(&g_dump_mu);
+    return rc;
 }

@@ -1,0 +1,83 @@
+"""tests/golden/enc_*.npz: the ME stage of REAL encodes by the unmodified reference encoder (BASELINE configs[0]).
+
+oracle/_ref/enc_dump (oracle/enc_driver.c) drives the whole reference encoder through its public API
+(eb_init_handle / eb_svt_enc_set_parameter / eb_svt_enc_send_picture / eb_svt_get_packet) on a synthetic yuv420p clip;
+the MotionEstimateLcu wrapper in oracle/ref_driver.c records, for every SB of every inter picture, what the encoder's own
+processes set up (slice type, layers, reference POCs, HME flags, MeContext search tables) and the MeCuResults_t rows it
+produced. The clip itself is regenerated from its seed by the tests (CRCs stored here).
+Run in the build container only:  python tests/golden/make_encoder_golden.py
+"""
+import os
+import subprocess
+import sys
+import tempfile
+import zlib
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import me_common as M  # noqa: E402
+
+CASES = [  # name, width, height, frames, enc_mode, hierarchical_levels, seed, synth kwargs
+    # enc_mode 3 is the default preset and the highest this reference version accepts (MAX_ENC_PRESET 3); modes 0-2 switch
+    # reference pictures to the 209-PU search, which is row (h) of DESIGN.md
+    ("enc_416x240_m3", 416, 240, 30, 3, 3, 416, dict(max_shift=12)),
+    # (this reference version accepts hierarchical_levels 3 only); CIF: the last SB row is half height
+    ("enc_352x288_m3", 352, 288, 19, 3, 3, 352, dict(max_shift=6, noise=4.0)),
+]
+HDR = 48
+
+
+def parse(path, w, h):
+    raw = np.fromfile(path, dtype=np.uint8)
+    pos, pics = 0, {}
+    while pos < raw.size:
+        hd = raw[pos:pos + 4 * HDR].view(np.int32)
+        assert hd[0] == 0x4D454447, "bad record"
+        pos += 4 * HDR
+        poc, sb, first, num_pus, rowsz = int(hd[1]), int(hd[2]), int(hd[40]), int(hd[18]), int(hd[41])
+        assert rowsz == 40 and (hd[5], hd[6]) == (w, h)
+        pic = pics.setdefault(poc, {"hdr": hd.copy(), "rows": {}, "luma": None})
+        assert np.array_equal(pic["hdr"][5:40], hd[5:40]), "per-picture settings changed between SBs"
+        if first:
+            pic["luma"] = raw[pos:pos + w * h].reshape(h, w).copy()
+            pos += w * h
+        pic["rows"][sb] = raw[pos:pos + num_pus * 40].copy()
+        pos += num_pus * 40
+    return pics
+
+
+def main():
+    M.build_oracle(ref=True)
+    exe = os.path.join(M.ORACLE_DIR, "_ref", "enc_dump")
+    for name, w, h, n, mode, hl, seed, kw in CASES:
+        frames = M.synth_video(w, h, n, seed=seed, **kw)
+        with tempfile.TemporaryDirectory() as td:
+            yuv, dump = os.path.join(td, "in.yuv"), os.path.join(td, "out.medump")
+            with open(yuv, "wb") as f:
+                for x in frames:
+                    f.write(np.ascontiguousarray(x).tobytes())
+                    f.write(np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes())
+            subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump, str(hl)], check=True, stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
+            pics = parse(dump, w, h)
+        n_sb = ((w + 63) // 64) * ((h + 63) // 64)
+        pocs = sorted(pics)
+        hdrs, rows = [], []
+        for poc in pocs:
+            p = pics[poc]
+            assert len(p["rows"]) == n_sb and p["luma"] is not None
+            assert np.array_equal(p["luma"], frames[poc]), "the encoder's input picture is not the clip frame"
+            hdrs.append(p["hdr"])
+            rows.append(np.stack([p["rows"][sb] for sb in range(n_sb)]))
+        num_pus = {int(hd[18]) for hd in hdrs}
+        assert len(num_pus) == 1
+        out = os.path.join(HERE, name + ".npz")
+        np.savez_compressed(out, geometry=np.array([w, h, n, mode, seed, hl], np.int32), synth=np.array([repr(kw)]),
+                            frame_crc=np.array([zlib.crc32(np.ascontiguousarray(x).tobytes()) & 0xFFFFFFFF for x in frames], np.uint32),
+                            hdr=np.stack(hdrs), rows=np.stack(rows))
+        print("wrote", out, len(pocs), "inter pictures,", num_pus.pop(), "PUs per SB,", os.path.getsize(out), "bytes")
+
+
+if __name__ == "__main__":
+    main()

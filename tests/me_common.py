@@ -236,7 +236,7 @@ GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 
 
 def golden_cases():
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("txq_"))
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("txq_", "enc_")))
 
 
 def load_golden(name):
@@ -258,3 +258,44 @@ def unpack16(lib, prefix, luma16):
     f.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
     f(src.ctypes.data, w, msb.ctypes.data, w, rem.ctypes.data, w, w, h)
     return msb, rem
+
+
+# ---- goldens recorded from whole-encoder runs of the reference (tests/golden/make_encoder_golden.py) ----
+
+def encoder_cases():
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and f.startswith("enc_"))
+
+
+def encoder_clip(g):
+    """Regenerate the synthetic clip an enc_* golden was encoded from and check it against the stored CRCs."""
+    w, h, n, _mode, seed, _hl = (int(v) for v in g["geometry"])
+    frames = synth_video(w, h, n, seed=seed, **eval(str(g["synth"][0]), {"dict": dict}))
+    assert [plane_crc(f) for f in frames] == [int(v) for v in g["frame_crc"]], "synthetic clip drifted from the golden"
+    return frames
+
+
+def encoder_params(cls, hd, defaults):
+    """ME parameters of one dumped picture: `defaults` (the library's table defaults for the picture's layer) with every
+    field the encoder's own processes set (dump header, oracle/ref_driver.c) written over it. Returns (params, mismatches)
+    where mismatches lists the fields whose default differs from what the encoder used."""
+    enc = {"width": hd[5], "height": hd[6], "num_lists": hd[7], "temporal_layer_index": hd[8], "hierarchical_levels": hd[9],
+           "is_used_as_reference": hd[10], "same_ref_poc": int(hd[7] == 2 and hd[11] == hd[12]),
+           "enable_hme_flag": hd[13], "enable_hme_level0": hd[14], "enable_hme_level1": hd[15], "enable_hme_level2": hd[16],
+           "use_subpel": hd[17], "num_pus": hd[18], "cu8x8_mode": hd[19], "num_hme_regions_w": hd[20], "num_hme_regions_h": hd[21],
+           "hme_l0_total_w": hd[22], "hme_l0_total_h": hd[23], "hme_l0_w": hd[24:26], "hme_l0_h": hd[26:28],
+           "hme_l1_w": hd[28:30], "hme_l1_h": hd[30:32], "hme_l2_w": hd[32:34], "hme_l2_h": hd[34:36],
+           "search_area_w": hd[36], "search_area_h": hd[37]}
+    p = convert_params(cls, defaults)
+    bad = []
+    for k, v in enc.items():
+        cur = getattr(p, k)
+        if hasattr(cur, "__len__"):
+            if [int(x) for x in cur] != [int(x) for x in v]:
+                bad.append(k)
+            for i in range(len(cur)):
+                cur[i] = int(v[i])
+        else:
+            if k != "same_ref_poc" and int(cur) != int(v):
+                bad.append(k)
+            setattr(p, k, int(v))
+    return p, bad

@@ -313,3 +313,30 @@ def test_4k_sb_rows_against_oracle_and_properties(pkg, meo):
     assert M.results_diff(bottom[0], want[32 * 60:]) == []
     sq = [0] + list(range(5, 85))
     assert not self_res[0]["dist0"][:, sq].any()
+
+
+@pytest.mark.parametrize("name", M.encoder_cases())
+def test_real_encoder_me_results(pkg, name):
+    """The CUDA path against what the unmodified reference ENCODER computed: every inter picture of a clip encoded through
+    the reference's public API (tests/golden/enc_*.npz, BASELINE configs[0]), with the per-picture settings the encoder's
+    own processes chose, all pictures of the clip in one batched call. No oracle in between."""
+    g = M.load_golden(name)
+    frames = M.encoder_clip(g)
+    h, w = frames[0].shape
+    jobs, lists = [], []
+    for hd in g["hdr"]:
+        nl = int(hd[7])
+        prm, bad = M.encoder_params(pkg.SvtMeParams, hd, pkg.default_params(w, h, nl, int(hd[8]), int(hd[9]), int(hd[10])))
+        assert bad == [], (name, int(hd[1]), bad)
+        jobs.append((int(hd[1]), int(hd[11]), int(hd[12]) if nl == 2 else int(hd[11]), prm))
+        lists.append(nl)
+    ctx = pkg.MeContext(w, h, len(frames))
+    try:
+        for i, f in enumerate(frames):
+            ctx.upload(i, f)
+        res, _ = ctx.motion_estimate(jobs)
+    finally:
+        ctx.close()
+    for j, (hd, rows) in enumerate(zip(g["hdr"], g["rows"])):
+        want = rows.view(M.PU_RESULT_DTYPE).reshape(res[j].shape)
+        assert M.results_diff(res[j], want, lists[j]) == [], (name, int(hd[1]))
