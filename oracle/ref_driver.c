@@ -255,28 +255,32 @@ void ref_default_params(MeoParams *p, int32_t width, int32_t height, int32_t num
 }
 
 
-/* ---- ME dump of real encodes (golden vectors of BASELINE configs[0]) ------------------------------------------------
- * Record per MotionEstimateLcu call: what the encoder's own processes set up for it (slice type, layers, HME flags,
+/* ---- ME dump / ME hook of real encodes (golden vectors of BASELINE configs[0]; encoder-in-the-loop test) -------------
+ * Dump: record per MotionEstimateLcu call what the encoder's own processes set up for it (slice type, layers, HME flags,
  * the MeContext search parameters, reference POCs), the source luma once per picture, and the MeCuResults_t rows it
- * produced. Layout: a stream of int32 records, see tests/golden/make_encoder_golden.py. */
+ * produced. Layout: a stream of int32 records, see tests/golden/make_encoder_golden.py.
+ * Hook: when one is installed (oracle/enc_driver.c --cuda-me) the reference's MotionEstimateLcu is NOT run; the hook
+ * receives the same header, the luma planes of the source and of the two PA reference pictures, and fills
+ * me_results[sb_index] itself. Everything else the encoder does stays the reference's. */
 #include <pthread.h>
 #include <stdio.h>
+typedef int (*ref_me_hook_fn)(void *user, const int32_t *hdr, const uint8_t *cur, int cur_stride, const uint8_t *ref0, int ref0_stride,
+                              const uint8_t *ref1, int ref1_stride, void *row_out);
 static FILE *g_dump;
 static pthread_mutex_t g_dump_mu = PTHREAD_MUTEX_INITIALIZER;
 static uint64_t g_seen[4096]; static int g_nseen;
+static ref_me_hook_fn g_hook; static void *g_hook_user;
 
 int ref_me_dump_open(const char *path) { g_dump = fopen(path, "wb"); g_nseen = 0; return g_dump ? 0 : -1; }
 void ref_me_dump_close(void) { if (g_dump) fclose(g_dump); g_dump = NULL; }
+void ref_me_hook_set(ref_me_hook_fn fn, void *user) { g_hook = fn; g_hook_user = user; }
+
+static const uint8_t *luma_origin(const EbPictureBufferDesc_t *p) { return p->bufferY + (size_t)p->origin_y * p->strideY + p->origin_x; }
 
 EbErrorType MotionEstimateLcu(PictureParentControlSet_t *pcs, uint32_t sb_index, uint32_t sb_origin_x, uint32_t sb_origin_y,
                               MeContext_t *ctx, EbPictureBufferDesc_t *input_ptr) {
-    const EbErrorType rc = MotionEstimateLcu_reference(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
-    if (!g_dump) return rc;
+    if (!g_hook && !g_dump) return MotionEstimateLcu_reference(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
     SequenceControlSet_t *scs = (SequenceControlSet_t *)pcs->sequence_control_set_wrapper_ptr->objectPtr;
-    pthread_mutex_lock(&g_dump_mu);
-    int first = 1;
-    for (int i = 0; i < g_nseen; i++) if (g_seen[i] == pcs->picture_number) first = 0;
-    if (first && g_nseen < 4096) g_seen[g_nseen++] = pcs->picture_number;
     int32_t h[48]; memset(h, 0, sizeof(h));
     h[0] = 0x4D454447;                                    /* 'MEDG' */
     h[1] = (int32_t)pcs->picture_number; h[2] = (int32_t)sb_index; h[3] = (int32_t)sb_origin_x; h[4] = (int32_t)sb_origin_y;
@@ -294,12 +298,34 @@ EbErrorType MotionEstimateLcu(PictureParentControlSet_t *pcs, uint32_t sb_index,
         h[32 + i] = ctx->hme_level2_search_area_in_width_array[i]; h[34 + i] = ctx->hme_level2_search_area_in_height_array[i];
     }
     h[36] = ctx->search_area_width; h[37] = ctx->search_area_height;
-    h[38] = pcs->enc_mode; h[39] = pcs->pic_depth_mode; h[40] = first;
+    h[38] = pcs->enc_mode; h[39] = pcs->pic_depth_mode;
     h[41] = (int32_t)sizeof(MeCuResults_t);
+    EbErrorType rc = EB_ErrorNone;
+    if (g_hook) {
+        const EbPictureBufferDesc_t *r0 = ((EbPaReferenceObject_t *)pcs->ref_pa_pic_ptr_array[0]->objectPtr)->inputPaddedPicturePtr;
+        const EbPictureBufferDesc_t *r1 = h[7] == 2 ? ((EbPaReferenceObject_t *)pcs->ref_pa_pic_ptr_array[1]->objectPtr)->inputPaddedPicturePtr : r0;
+        if (g_hook(g_hook_user, h, luma_origin(input_ptr), input_ptr->strideY, luma_origin(r0), r0->strideY, luma_origin(r1), r1->strideY,
+                   pcs->me_results[sb_index]) != 0) {
+            fprintf(stderr, "ref_driver: the ME hook failed (picture %d, SB %d)\n", h[1], h[2]);
+            abort();                                      /* no silent fallback to the CPU path */
+        }
+        if (scs->static_config.rate_control_mode) {       /* EbMotionEstimation.c:7150-7157 */
+            pcs->rc_me_distortion[sb_index] = 0;
+            for (int i = 0; i < 16; i++) pcs->rc_me_distortion[sb_index] += pcs->me_results[sb_index][5 + i].distortionDirection[0].distortion;
+        }
+    } else {
+        rc = MotionEstimateLcu_reference(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
+    }
+    if (!g_dump) return rc;
+    pthread_mutex_lock(&g_dump_mu);
+    int first = 1;
+    for (int i = 0; i < g_nseen; i++) if (g_seen[i] == pcs->picture_number) first = 0;
+    if (first && g_nseen < 4096) g_seen[g_nseen++] = pcs->picture_number;
+    h[40] = first;
     fwrite(h, sizeof(h), 1, g_dump);
     if (first)                                            /* source luma of this picture (interior of the padded input plane) */
         for (uint32_t y = 0; y < scs->luma_height; y++)
-            fwrite(input_ptr->bufferY + (size_t)(input_ptr->origin_y + y) * input_ptr->strideY + input_ptr->origin_x, 1, scs->luma_width, g_dump);
+            fwrite(luma_origin(input_ptr) + (size_t)y * input_ptr->strideY, 1, scs->luma_width, g_dump);
     fwrite(pcs->me_results[sb_index], sizeof(MeCuResults_t), pcs->max_number_of_pus_per_sb, g_dump);
     pthread_mutex_unlock(&g_dump_mu);
     return rc;

@@ -8,5 +8,6 @@ fallback: loading fails loudly when the library has not been built, and ``MeCont
 CUDA device is present.
 """
 from .binding import (MeContext, SvtMeError, SvtMeParams, SvtMeJob, SvtMeIpcSlot, PU_RESULT_DTYPE, SB_DEBUG_DTYPE, KERNEL_KINDS,  # noqa: F401
-                      default_params, load_library, library_path, EXPORTED_SYMBOLS)
+                      default_params, load_library, library_path, EXPORTED_SYMBOLS, LCU_EXPORTED_SYMBOLS, MeLcuSession,
+                      SvtMeLcuPicture)
 from .txq_binding import TxqContext, SvtTxqQuant, TXQ_EXPORTED_SYMBOLS, TX_TYPES, supported as txq_supported, packed_dims  # noqa: F401,E402

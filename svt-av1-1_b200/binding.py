@@ -14,6 +14,8 @@ EXPORTED_SYMBOLS = (
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
     "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
 )
+LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
+                        "svtme_lcu_motion_estimate", "svtme_lcu_session_stats")
 KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
 
 
@@ -36,6 +38,10 @@ class SvtMeParams(C.Structure):
 class SvtMeIpcSlot(C.Structure):
     _fields_ = [("mem_handle", C.c_uint8 * 64), ("event_handle", C.c_uint8 * 64), ("luma_offset", C.c_int64),
                 ("pitch", C.c_int32), ("device", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
+
+
+class SvtMeLcuPicture(C.Structure):
+    _fields_ = [("picture_number", C.c_uint64), ("luma", C.c_void_p), ("stride", C.c_int32), ("reserved", C.c_int32)]
 
 
 class SvtMeJob(C.Structure):
@@ -110,6 +116,17 @@ def load_library():
     lib.svtme_set_profiling.argtypes = [C.c_void_p, C.c_int32]
     lib.svtme_kernel_times.restype = C.c_int32
     lib.svtme_kernel_times.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]
+    lib.svtme_lcu_session_create.restype = C.c_int32
+    lib.svtme_lcu_session_create.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    lib.svtme_lcu_session_destroy.restype = None
+    lib.svtme_lcu_session_destroy.argtypes = [C.c_void_p]
+    lib.svtme_lcu_last_error.restype = C.c_char_p
+    lib.svtme_lcu_last_error.argtypes = [C.c_void_p]
+    lib.svtme_lcu_motion_estimate.restype = C.c_int32
+    lib.svtme_lcu_motion_estimate.argtypes = [C.c_void_p, C.POINTER(SvtMeParams), C.POINTER(SvtMeLcuPicture), C.POINTER(SvtMeLcuPicture),
+                                              C.POINTER(SvtMeLcuPicture), C.c_int32, C.c_void_p]
+    lib.svtme_lcu_session_stats.restype = None
+    lib.svtme_lcu_session_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     _lib = lib
     return lib
 
@@ -253,3 +270,57 @@ class MeContext:
         n = (C.c_int64 * len(KERNEL_KINDS))()
         self._check(self.lib.svtme_kernel_times(self._h, ms, n, 1 if reset else 0), "svtme_kernel_times")
         return {k: (ms[i], n[i]) for i, k in enumerate(KERNEL_KINDS)}
+
+
+class MeLcuSession:
+    """SB-granular facade (include/svtme_lcu.h): the call shape of the reference's MotionEstimateLcu
+    (EbMotionEstimation.c:6152) -- one call per SB, from any thread -- served from whole-picture GPU launches."""
+
+    def __init__(self, width, height, num_slots=16, device=0):
+        self.lib = load_library()
+        self.width, self.height = width, height
+        self.n_sb = ((width + 63) // 64) * ((height + 63) // 64)
+        self._h = C.c_void_p()
+        rc = self.lib.svtme_lcu_session_create(C.byref(self._h), device, width, height, num_slots)
+        if rc != 0:
+            self._h = C.c_void_p()
+            raise SvtMeError(f"svtme_lcu_session_create failed (0x{rc & 0xffffffff:08x}): no CUDA device / bad geometry / < 3 slots")
+
+    def close(self):
+        if self._h:
+            self.lib.svtme_lcu_session_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def _pic(number, luma):
+        assert luma.dtype == np.uint8 and luma.strides[1] == 1
+        return SvtMeLcuPicture(int(number), luma.ctypes.data, luma.strides[0], 0)
+
+    def motion_estimate_sb(self, params, cur, ref0, ref1, sb_index):
+        """cur / ref0 / ref1: (picture_number, uint8 luma array) pairs (ref1 None for P pictures). Returns the SB's
+        PU_RESULT row ([num_pus])."""
+        row = np.zeros(params.num_pus, dtype=PU_RESULT_DTYPE)
+        c, r0 = self._pic(*cur), self._pic(*ref0)
+        r1 = self._pic(*ref1) if ref1 is not None else None
+        rc = self.lib.svtme_lcu_motion_estimate(self._h, C.byref(params), C.byref(c), C.byref(r0),
+                                                C.byref(r1) if r1 is not None else None, sb_index, row.ctypes.data)
+        if rc != 0:
+            raise SvtMeError(f"svtme_lcu_motion_estimate failed (0x{rc & 0xffffffff:08x}): {self.lib.svtme_lcu_last_error(self._h).decode()}")
+        return row
+
+    def stats(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        self.lib.svtme_lcu_session_stats(self._h, C.byref(a), C.byref(b), C.byref(c))
+        return {"pictures": a.value, "uploads": b.value, "rows": c.value}

@@ -59,7 +59,7 @@ def main():
                 for x in frames:
                     f.write(np.ascontiguousarray(x).tobytes())
                     f.write(np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes())
-            subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump, str(hl)], check=True, stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
+            subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump], check=True, stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
             pics = parse(dump, w, h)
         n_sb = ((w + 63) // 64) * ((h + 63) // 64)
         pocs = sorted(pics)
@@ -69,7 +69,15 @@ def main():
             assert len(p["rows"]) == n_sb and p["luma"] is not None
             assert np.array_equal(p["luma"], frames[poc]), "the encoder's input picture is not the clip frame"
             hdrs.append(p["hdr"])
-            rows.append(np.stack([p["rows"][sb] for sb in range(n_sb)]))
+            r = np.stack([p["rows"][sb] for sb in range(n_sb)])
+            if int(p["hdr"][7]) == 1:
+                # P pictures: xMvL1 / yMvL1 are copies of whatever the calling ME thread's context held from an earlier SB
+                # (EbMotionEstimation.c:7137-7140, DESIGN Q8) -- they change from run to run with thread scheduling, so
+                # they are zeroed here to keep the fixture reproducible (the tests ignore them for P pictures anyway)
+                v = r.view(M.PU_RESULT_DTYPE)
+                v["xMvL1"] = 0
+                v["yMvL1"] = 0
+            rows.append(r)
         num_pus = {int(hd[18]) for hd in hdrs}
         assert len(num_pus) == 1
         out = os.path.join(HERE, name + ".npz")

@@ -34,6 +34,19 @@ def test_header_symbols_exported(pkg_built):
     assert set(names) == set(pkg_built.EXPORTED_SYMBOLS)
 
 
+def test_lcu_header_symbols_exported(pkg_built):
+    lib = pkg_built.load_library()
+    names = declared_symbols(os.path.join(M.ROOT, "include", "svtme_lcu.h"), "svtme_lcu_")
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/svtme_lcu.h but not exported"
+    assert set(names) == set(pkg_built.LCU_EXPORTED_SYMBOLS)
+    assert C.sizeof(pkg_built.SvtMeLcuPicture) == 24
+    import torch
+    if not torch.cuda.is_available():                      # no device: the facade fails too, it never falls back
+        with pytest.raises(pkg_built.SvtMeError):
+            pkg_built.MeLcuSession(128, 128)
+
+
 def test_txq_header_symbols_exported(pkg_built):
     lib = pkg_built.load_library()
     names = declared_symbols(os.path.join(M.ROOT, "include", "svttxq.h"), "svttxq_")

@@ -1,0 +1,69 @@
+"""Encoder in the loop: the UNMODIFIED reference encoder (oracle/_ref/libsvtref.so, every process, public API) encodes a clip
+twice -- once stock, once with every MotionEstimateLcu call served by the CUDA library through its SB facade
+(include/svtme_lcu.h; the hook is oracle/enc_driver.c --cuda-me, the binding INTEGRATION.md section 6 describes).
+The ME rows the rest of the encoder sees and the AV1 bitstream it writes must be identical. Needs a B200 and the prebuilt
+oracle/_ref (it travels to the GPU box; it cannot be built there)."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import me_common as M
+
+pytestmark = pytest.mark.gpu
+
+sys.path.insert(0, os.path.join(M.ROOT, "tests", "golden"))
+ENC = os.path.join(M.ORACLE_DIR, "_ref", "enc_dump")
+
+
+def _env():
+    env = dict(os.environ)
+    extra = ["/usr/local/cuda/lib64"]
+    try:
+        import nvidia.cuda_runtime as rt
+        extra.insert(0, os.path.join(list(rt.__path__)[0], "lib"))
+    except Exception:
+        pass
+    env["LD_LIBRARY_PATH"] = ":".join([env.get("LD_LIBRARY_PATH", "")] + extra).strip(":")
+    return env
+
+
+def _encode(td, tag, yuv, w, h, n, extra):
+    dump, obu = os.path.join(td, tag + ".medump"), os.path.join(td, tag + ".obu")
+    r = subprocess.run([ENC, yuv, str(w), str(h), str(n), "3", dump, "--bitstream", obu] + extra, env=_env(),
+                       stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    return dump, open(obu, "rb").read(), r.stderr
+
+
+@pytest.mark.skipif(not os.path.exists(ENC), reason="oracle/_ref/enc_dump not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("w,h,n,seed", [(416, 240, 20, 7), (352, 288, 12, 11)])
+def test_reference_encoder_with_cuda_me_is_bit_identical(pkg, tmp_path, w, h, n, seed):
+    from make_encoder_golden import parse
+    frames = M.synth_video(w, h, n, seed=seed, max_shift=8)
+    yuv = str(tmp_path / "in.yuv")
+    with open(yuv, "wb") as f:
+        for x in frames:
+            f.write(np.ascontiguousarray(x).tobytes())
+            f.write(np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes())
+    d0, bs0, _ = _encode(str(tmp_path), "stock", yuv, w, h, n, [])
+    d1, bs1, log = _encode(str(tmp_path), "cuda", yuv, w, h, n, ["--cuda-me", pkg.library_path()])
+    p0, p1 = parse(d0, w, h), parse(d1, w, h)
+    assert sorted(p0) == sorted(p1) and len(p0) == n - 1            # every picture but the key frame is inter
+    n_sb = ((w + 63) // 64) * ((h + 63) // 64)
+    for poc in sorted(p0):
+        lists = int(p0[poc]["hdr"][7])
+        assert np.array_equal(p0[poc]["hdr"][5:40], p1[poc]["hdr"][5:40])
+        for sb in range(n_sb):
+            a = p0[poc]["rows"][sb].view(M.PU_RESULT_DTYPE)
+            b = p1[poc]["rows"][sb].view(M.PU_RESULT_DTYPE)
+            assert M.results_diff(b, a, lists) == [], (poc, sb)
+    m = re.search(r"cuda-me pictures (\d+) uploads (\d+) rows (\d+)", log)
+    assert m, log[-500:]
+    pictures, uploads, rows = (int(v) for v in m.groups())
+    assert pictures == n - 1 and rows == (n - 1) * n_sb             # one whole-picture launch sequence per inter picture
+    assert n <= uploads <= n + 8                                    # each picture crosses PCIe once (16 resident slots)
+    assert len(bs0) > 1000 and bs0 == bs1, (len(bs0), len(bs1))     # the encode does not change

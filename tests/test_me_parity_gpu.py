@@ -340,3 +340,43 @@ def test_real_encoder_me_results(pkg, name):
     for j, (hd, rows) in enumerate(zip(g["hdr"], g["rows"])):
         want = rows.view(M.PU_RESULT_DTYPE).reshape(res[j].shape)
         assert M.results_diff(res[j], want, lists[j]) == [], (name, int(hd[1]))
+
+
+def test_sb_facade_call_shape(pkg, meo):
+    """include/svtme_lcu.h: one call per SB, from several threads, in scrambled order, with only 3 resident slots (so
+    pictures are evicted and re-uploaded): every row equals the oracle's, each picture is searched exactly once."""
+    import threading
+    w, h = 320, 200
+    fr = M.synth_video(w, h, 5, seed=33, max_shift=10)
+    n_sb = 5 * 4
+    pics = [(2, 0, 4, 2), (1, 0, 2, 2), (3, 2, 4, 2), (4, 0, 0, 1)]           # (cur, ref0, ref1, lists)
+    prms = []
+    for cur, r0, r1, nl in pics:
+        p = pkg.default_params(w, h, nl, 1, 3, 1)
+        prms.append(p)
+    calls = [(j, sb) for j in range(len(pics)) for sb in range(n_sb)]
+    np.random.default_rng(5).shuffle(calls)
+    got = np.zeros((len(pics), n_sb, 85), dtype=pkg.PU_RESULT_DTYPE)
+    errors = []
+    with pkg.MeLcuSession(w, h, num_slots=3) as ses:
+        def worker(part):
+            try:
+                for j, sb in part:
+                    cur, r0, r1, nl = pics[j]
+                    got[j, sb] = ses.motion_estimate_sb(prms[j], (cur, fr[cur]), (r0, fr[r0]), (r1, fr[r1]) if nl == 2 else None, sb)
+            except Exception as e:                                              # noqa: BLE001
+                errors.append(e)
+        ths = [threading.Thread(target=worker, args=(calls[i::4],)) for i in range(4)]
+        [t.start() for t in ths]
+        [t.join() for t in ths]
+        assert errors == []
+        st = ses.stats()
+        assert st["rows"] == len(calls) and st["pictures"] >= len(pics) and st["uploads"] >= 5
+        with pytest.raises(pkg.SvtMeError):
+            ses.motion_estimate_sb(prms[0], (2, fr[2]), (0, fr[0]), (4, fr[4]), n_sb)          # SB index out of range
+        with pytest.raises(pkg.SvtMeError):
+            ses.motion_estimate_sb(prms[0], (2, fr[2]), (0, fr[0]), None, 0)                   # B picture without list 1
+    pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
+    for j, (cur, r0, r1, nl) in enumerate(pics):
+        want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, prms[j]), pyr[cur], pyr[r0], pyr[r1] if nl == 2 else None)
+        assert M.results_diff(got[j], want, nl) == [], j
