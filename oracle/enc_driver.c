@@ -4,6 +4,7 @@
  * MotionEstimateLcu wrapper in ref_driver.c: BASELINE configs[0] ("run the encoder on CPU, dump MotionEstimateLcu
  * MVs/SADs as golden"). usage: enc_dump in.yuv width height frames enc_mode out.medump [--bitstream out.obu] [--cuda-me lib.so]
  *   out.medump      "-" = no dump
+ *   --txq-dump      record forward transform + quantisation blocks of the EncDec stage (ref_txq.c wrappers)
  *   --bitstream     write the packets the encoder returns, in order
  *   --cuda-me       encoder-in-the-loop: dlopen libsvtme_cuda.so and serve every MotionEstimateLcu call of the encode from
  *                   its SB facade (include/svtme_lcu.h) instead of the reference's C function. This hook is the whole
@@ -18,6 +19,8 @@
 
 int ref_me_dump_open(const char *path);
 void ref_me_dump_close(void);
+int ref_txq_dump_open(const char *path, int every, int cap);
+void ref_txq_dump_close(void);
 typedef int (*ref_me_hook_fn)(void *user, const int32_t *hdr, const uint8_t *cur, int cur_stride, const uint8_t *ref0, int ref0_stride,
                               const uint8_t *ref1, int ref1_stride, void *row_out);
 void ref_me_hook_set(ref_me_hook_fn fn, void *user);
@@ -68,11 +71,12 @@ static int cuda_me_open(const char *path, int w, int h) {
 }
 
 int main(int argc, char **argv) {
-    if (argc < 7) { fprintf(stderr, "usage: %s in.yuv width height frames enc_mode out.medump|- [--bitstream out.obu] [--cuda-me lib.so]\n", argv[0]); return 2; }
-    const char *bitstream_path = NULL, *cuda_me = NULL;
+    if (argc < 7) { fprintf(stderr, "usage: %s in.yuv width height frames enc_mode out.medump|- [--bitstream out.obu] [--txq-dump out.txqdump] [--cuda-me lib.so]\n", argv[0]); return 2; }
+    const char *bitstream_path = NULL, *cuda_me = NULL, *txq_dump = NULL;
     for (int i = 7; i + 1 < argc; i += 2) {
         if (!strcmp(argv[i], "--bitstream")) bitstream_path = argv[i + 1];
         else if (!strcmp(argv[i], "--cuda-me")) cuda_me = argv[i + 1];
+        else if (!strcmp(argv[i], "--txq-dump")) txq_dump = argv[i + 1];
         else { fprintf(stderr, "unknown option %s\n", argv[i]); return 2; }
     }
     const int w = atoi(argv[2]), h = atoi(argv[3]), n = atoi(argv[4]), mode = atoi(argv[5]);
@@ -88,6 +92,7 @@ int main(int argc, char **argv) {
     cfg.frame_rate = 30 << 16; cfg.frame_rate_numerator = 0; cfg.frame_rate_denominator = 0;
     if (eb_svt_enc_set_parameter(enc, &cfg) != EB_ErrorNone) { fprintf(stderr, "eb_svt_enc_set_parameter failed\n"); return 1; }
     if (strcmp(argv[6], "-") && ref_me_dump_open(argv[6]) != 0) { perror(argv[6]); return 2; }
+    if (txq_dump && ref_txq_dump_open(txq_dump, 0, 0) != 0) { perror(txq_dump); return 2; }
     if (cuda_me && cuda_me_open(cuda_me, w, h) != 0) return 3;
     FILE *bs = bitstream_path ? fopen(bitstream_path, "wb") : NULL;
     if (bitstream_path && !bs) { perror(bitstream_path); return 2; }
@@ -124,6 +129,7 @@ int main(int argc, char **argv) {
         }
     }
     ref_me_dump_close();
+    ref_txq_dump_close();
     if (bs) fclose(bs);
     fprintf(stderr, "enc_dump: %d packets, %zu bytes\n", packets, bytes);
     eb_deinit_encoder(enc);

@@ -107,3 +107,119 @@ int ref_txq_plane(int16_t *res, int stride, int width, int height, int w, int h,
         }
     return b;
 }
+
+/* ---- transform / quantisation dump of real encodes (BASELINE configs[0], "txfm/quant coeffs as golden") ---------------
+ * libsvtref.so is linked with -Wl,--wrap=Av1EstimateTransform,--wrap=Av1QuantizeInvQuantize (oracle/Makefile), so the
+ * calls the encoder's EncDec stage makes (EbCodingLoop.c:661-700 and its chroma twins) arrive here first. The real
+ * functions run unchanged; when a dump is open, a forward transform followed on the same thread by the quantisation of
+ * the buffer it wrote is recorded as one block: residual in, quantiser lanes, coefficients / three-quad energy /
+ * levels / dequantised levels / eob out. Records are thinned per (size, type, plane) so the fixture stays small.
+ * Layout: int32 header[16] then the arrays, see tests/golden/make_encoder_golden.py. */
+#include <pthread.h>
+#include <stdio.h>
+EbErrorType __real_Av1EstimateTransform(int16_t *residual_buffer, uint32_t residualStride, int32_t *coeffBuffer, uint32_t coeffStride,
+                                        TxSize transform_size, uint64_t *three_quad_energy, int16_t *transform_inner_array_ptr,
+                                        uint32_t bitIncrement, TxType transform_type, EbAsm asm_type, PLANE_TYPE componentType,
+                                        EB_TRANS_COEFF_SHAPE transCoeffShape);
+void __real_Av1QuantizeInvQuantize(PictureControlSet_t *pcs, int32_t *coeff, const uint32_t coeffStride, int32_t *quantCoeff,
+                                   int32_t *reconCoeff, uint32_t qp, uint32_t width, uint32_t height, TxSize txsize, uint16_t *eob,
+                                   MacroblockPlane candidate_plane, EbAsm asm_type, uint32_t *y_count_non_zero_coeffs, EbPfMode pfMode,
+                                   uint8_t enableContouringQCUpdateFlag, uint32_t componentType, uint32_t bitIncrement, TxType tx_type,
+                                   EbBool cleanSparseCoeffFlag);
+
+static FILE *g_txq_dump;
+static pthread_mutex_t g_txq_mu = PTHREAD_MUTEX_INITIALIZER;
+static int g_txq_every = 29, g_txq_cap = 24;
+static uint32_t g_txq_seen[TX_SIZES_ALL][TX_TYPES][3], g_txq_kept[TX_SIZES_ALL][TX_TYPES][3];
+/* the last two transforms of this thread: EncDec transforms Cb and Cr back to back, then quantises Cb and Cr */
+static __thread struct TLast { int32_t *coeff; int ts, type, bit_inc; uint64_t energy; int16_t residual[64 * 64]; } t_ring[2];
+static __thread int t_next;
+#define t_last t_ring[t_slot]
+
+int ref_txq_dump_open(const char *path, int every, int cap) {
+    g_txq_dump = fopen(path, "wb");
+    if (every > 0) g_txq_every = every;
+    if (cap > 0) g_txq_cap = cap;
+    memset(g_txq_seen, 0, sizeof(g_txq_seen)); memset(g_txq_kept, 0, sizeof(g_txq_kept));
+    return g_txq_dump ? 0 : -1;
+}
+void ref_txq_dump_close(void) { if (g_txq_dump) fclose(g_txq_dump); g_txq_dump = NULL; }
+
+EbErrorType __wrap_Av1EstimateTransform(int16_t *residual_buffer, uint32_t residualStride, int32_t *coeffBuffer, uint32_t coeffStride,
+                                        TxSize transform_size, uint64_t *three_quad_energy, int16_t *transform_inner_array_ptr,
+                                        uint32_t bitIncrement, TxType transform_type, EbAsm asm_type, PLANE_TYPE componentType,
+                                        EB_TRANS_COEFF_SHAPE transCoeffShape) {
+    const int t_slot = t_next;
+    if (g_txq_dump) {                                     /* the input, before the call (in place is not used, but be safe) */
+        const int w = tx_size_wide[transform_size], h = tx_size_high[transform_size];
+        for (int y = 0; y < h; y++) memcpy(t_last.residual + y * w, residual_buffer + (size_t)y * residualStride, sizeof(int16_t) * w);
+        if (w == 64 || h == 64) *three_quad_energy = 0;
+    }
+    const EbErrorType rc = __real_Av1EstimateTransform(residual_buffer, residualStride, coeffBuffer, coeffStride, transform_size,
+                                                       three_quad_energy, transform_inner_array_ptr, bitIncrement, transform_type,
+                                                       asm_type, componentType, transCoeffShape);
+    if (g_txq_dump) {
+        const int w = tx_size_wide[transform_size], h = tx_size_high[transform_size];
+        t_last.coeff = coeffBuffer; t_last.ts = transform_size; t_last.type = transform_type; t_last.bit_inc = (int)bitIncrement;
+        t_last.energy = (w == 64 || h == 64) ? *three_quad_energy : 0;
+        t_next ^= 1;
+    }
+    return rc;
+}
+
+void __wrap_Av1QuantizeInvQuantize(PictureControlSet_t *pcs, int32_t *coeff, const uint32_t coeffStride, int32_t *quantCoeff,
+                                   int32_t *reconCoeff, uint32_t qp, uint32_t width, uint32_t height, TxSize txsize, uint16_t *eob,
+                                   MacroblockPlane candidate_plane, EbAsm asm_type, uint32_t *y_count_non_zero_coeffs, EbPfMode pfMode,
+                                   uint8_t enableContouringQCUpdateFlag, uint32_t componentType, uint32_t bitIncrement, TxType tx_type,
+                                   EbBool cleanSparseCoeffFlag) {
+    int t_slot = -1;
+    for (int k = 0; k < 2 && g_txq_dump && componentType < 3; k++)
+        if (t_ring[k].coeff == coeff && t_ring[k].ts == (int)txsize && t_ring[k].type == (int)tx_type && t_ring[k].bit_inc == (int)bitIncrement)
+            t_slot = k;
+    const int paired = t_slot >= 0;
+    const int n = av1_get_max_eob(txsize);
+    int32_t *coeff_in = NULL;
+    if (paired) { coeff_in = (int32_t *)malloc(sizeof(int32_t) * n); memcpy(coeff_in, coeff, sizeof(int32_t) * n); }
+    __real_Av1QuantizeInvQuantize(pcs, coeff, coeffStride, quantCoeff, reconCoeff, qp, width, height, txsize, eob, candidate_plane,
+                                  asm_type, y_count_non_zero_coeffs, pfMode, enableContouringQCUpdateFlag, componentType, bitIncrement,
+                                  tx_type, cleanSparseCoeffFlag);
+    if (!paired) return;
+    t_last.coeff = NULL;
+    pthread_mutex_lock(&g_txq_mu);
+    const uint32_t seen = g_txq_seen[txsize][tx_type][componentType]++;
+    if (g_txq_dump && seen % (uint32_t)g_txq_every == 0 && g_txq_kept[txsize][tx_type][componentType] < (uint32_t)g_txq_cap) {
+        g_txq_kept[txsize][tx_type][componentType]++;
+        /* the quantiser Av1QuantizeInvQuantize_II picks: EbFullLoop.c:721-800 (ADD_DELTA_QP_SUPPORT is 0) */
+        const PictureParentControlSet_t *pp = pcs->parent_pcs_ptr;
+        const uint32_t qi = pp->base_qindex;
+        const Quants *q = bitIncrement == 0 ? &pp->quantsMd : &pp->quants;
+        const Dequants *d = bitIncrement == 0 ? &pp->deqMd : &pp->deq;
+        int16_t q10[10];
+        for (int i = 0; i < 2; i++) {
+            if (componentType == COMPONENT_LUMA) {
+                q10[0 + i] = q->y_zbin[qi][i]; q10[2 + i] = q->y_round[qi][i]; q10[4 + i] = q->y_quant[qi][i];
+                q10[6 + i] = q->y_quant_shift[qi][i]; q10[8 + i] = d->y_dequant_QTX[qi][i];
+            } else if (componentType == COMPONENT_CHROMA_CB) {
+                q10[0 + i] = q->u_zbin[qi][i]; q10[2 + i] = q->u_round[qi][i]; q10[4 + i] = q->u_quant[qi][i];
+                q10[6 + i] = q->u_quant_shift[qi][i]; q10[8 + i] = d->u_dequant_QTX[qi][i];
+            } else {
+                q10[0 + i] = q->v_zbin[qi][i]; q10[2 + i] = q->v_round[qi][i]; q10[4 + i] = q->v_quant[qi][i];
+                q10[6 + i] = q->v_quant_shift[qi][i]; q10[8 + i] = d->v_dequant_QTX[qi][i];
+            }
+        }
+        const int w = tx_size_wide[txsize], h = tx_size_high[txsize];
+        int32_t hd[16]; memset(hd, 0, sizeof(hd));
+        hd[0] = 0x54584647;                               /* 'TXFG' */
+        hd[1] = txsize; hd[2] = w; hd[3] = h; hd[4] = tx_type; hd[5] = (int32_t)componentType; hd[6] = (int32_t)bitIncrement;
+        hd[7] = n; hd[8] = (int32_t)qi; hd[9] = (int32_t)pp->picture_number; hd[10] = *eob;
+        hd[11] = (int32_t)(t_last.energy & 0xffffffffu); hd[12] = (int32_t)(t_last.energy >> 32);
+        fwrite(hd, sizeof(hd), 1, g_txq_dump);
+        fwrite(q10, sizeof(q10), 1, g_txq_dump);
+        fwrite(t_last.residual, sizeof(int16_t), (size_t)w * h, g_txq_dump);
+        fwrite(coeff_in, sizeof(int32_t), n, g_txq_dump);
+        fwrite(quantCoeff, sizeof(int32_t), n, g_txq_dump);
+        fwrite(reconCoeff, sizeof(int32_t), n, g_txq_dump);
+    }
+    pthread_mutex_unlock(&g_txq_mu);
+    free(coeff_in);
+}

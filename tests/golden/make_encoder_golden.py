@@ -48,6 +48,36 @@ def parse(path, w, h):
     return pics
 
 
+def chroma_planes(frames, i):
+    """Non-flat synthetic chroma (ME reads luma only; this only gives the EncDec transform/quantisation dump chroma work)."""
+    a = frames[i][::2, ::2].astype(np.int32)
+    b = frames[(i + 1) % len(frames)][1::2, 1::2].astype(np.int32)
+    cb = np.clip(128 + (a - 128) // 3, 0, 255).astype(np.uint8)
+    cr = np.clip(128 - (b - 128) // 4, 0, 255).astype(np.uint8)
+    return cb, cr
+
+
+TXQ_HDR = 16
+
+
+def parse_txq(path):
+    """Records of oracle/ref_txq.c's EncDec wrappers -> flat arrays."""
+    raw = np.fromfile(path, dtype=np.uint8)
+    pos, hdr, q10, res, coeff, qc, dq = 0, [], [], [], [], [], []
+    while pos < raw.size:
+        hd = raw[pos:pos + 4 * TXQ_HDR].view(np.int32).copy()
+        assert hd[0] == 0x54584647, "bad txq record"
+        pos += 4 * TXQ_HDR
+        w, h, n = int(hd[2]), int(hd[3]), int(hd[7])
+        q10.append(raw[pos:pos + 20].view(np.int16).copy()); pos += 20
+        res.append(raw[pos:pos + 2 * w * h].view(np.int16).copy()); pos += 2 * w * h
+        for dst in (coeff, qc, dq):
+            dst.append(raw[pos:pos + 4 * n].view(np.int32).copy()); pos += 4 * n
+        hdr.append(hd)
+    return dict(hdr=np.stack(hdr), q10=np.stack(q10), residual=np.concatenate(res), coeff=np.concatenate(coeff),
+                qcoeff=np.concatenate(qc), dqcoeff=np.concatenate(dq))
+
+
 def main():
     M.build_oracle(ref=True)
     exe = os.path.join(M.ORACLE_DIR, "_ref", "enc_dump")
@@ -56,11 +86,15 @@ def main():
         with tempfile.TemporaryDirectory() as td:
             yuv, dump = os.path.join(td, "in.yuv"), os.path.join(td, "out.medump")
             with open(yuv, "wb") as f:
-                for x in frames:
+                for i, x in enumerate(frames):
                     f.write(np.ascontiguousarray(x).tobytes())
-                    f.write(np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes())
-            subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump], check=True, stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
+                    for c in chroma_planes(frames, i):
+                        f.write(np.ascontiguousarray(c).tobytes())
+            txq_dump = os.path.join(td, "out.txqdump")
+            subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump, "--txq-dump", txq_dump], check=True,
+                           stderr=subprocess.DEVNULL, stdout=subprocess.DEVNULL)
             pics = parse(dump, w, h)
+            txq = parse_txq(txq_dump)
         n_sb = ((w + 63) // 64) * ((h + 63) // 64)
         pocs = sorted(pics)
         hdrs, rows = [], []
@@ -85,6 +119,11 @@ def main():
                             frame_crc=np.array([zlib.crc32(np.ascontiguousarray(x).tobytes()) & 0xFFFFFFFF for x in frames], np.uint32),
                             hdr=np.stack(hdrs), rows=np.stack(rows))
         print("wrote", out, len(pocs), "inter pictures,", num_pus.pop(), "PUs per SB,", os.path.getsize(out), "bytes")
+        # EncDec forward transform + quantisation blocks of the same encode ("txq_" prefix: read by tests/test_txq_encoder_golden.py)
+        out = os.path.join(HERE, "txq_" + name + ".npz")
+        np.savez_compressed(out, **txq)
+        combos = {(int(a[2]), int(a[3]), int(a[4]), int(a[5])) for a in txq["hdr"]}
+        print("wrote", out, len(txq["hdr"]), "blocks,", len(combos), "(size, type, plane) combinations,", os.path.getsize(out), "bytes")
 
 
 if __name__ == "__main__":

@@ -188,3 +188,16 @@ def test_64_point_sizes_without_energy(txq, q10s, size):
             assert np.array_equal(got[k], want[k]), (w, h, kind, k)
         only = txq.fwd_txfm_quant(res, w, h, 0, q10s[key], want=("qcoeff", "eob"))
         assert np.array_equal(only["qcoeff"], want["qcoeff"]) and np.array_equal(only["eob"], want["eob"])
+
+
+@pytest.mark.parametrize("name", T.encoder_block_files())
+def test_real_encoder_encdec_blocks(txq, name):
+    """The CUDA path against what the unmodified reference ENCODER computed in its EncDec stage (tests/golden/txq_enc_*.npz,
+    BASELINE configs[0]): residual blocks in; coefficients, levels, dequantised levels, eob, three-quad energy out. No oracle
+    in between."""
+    blocks = 0
+    for w, h, t, q10, plane, want in T.encoder_block_groups(name):
+        got = txq.fwd_txfm_quant(plane, w, h, t, q10)
+        T.check_encoder_blocks(got, want, w, h, (name, w, h, t))
+        blocks += len(want["eob"])
+    assert blocks > 300

@@ -1,6 +1,7 @@
 """ctypes views of the transform / quantisation oracle (oracle/txq_oracle.c) and of the reference accessors
 (oracle/ref_txq.c). Test infrastructure only."""
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -147,3 +148,37 @@ def synth_residual(rng, height, width, bit_depth=8, kind="mixed"):
     base = 20 * np.sin(x / 7.3) * np.cos(y / 11.1) + rng.normal(0, 6, size=(height, width))
     edges = (rng.random((height, width)) < 0.01) * rng.integers(-lim, lim + 1, size=(height, width))
     return np.clip(np.rint(base + edges), -lim, lim).astype(np.int16)
+
+
+# ---- blocks recorded from the EncDec stage of whole-encoder runs (tests/golden/txq_enc_*.npz, make_encoder_golden.py) ----
+
+def encoder_block_files():
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    return sorted(f[:-4] for f in os.listdir(d) if f.startswith("txq_enc_") and f.endswith(".npz"))
+
+
+def encoder_block_groups(name):
+    """Yield (w, h, tx_type, q10, residual plane (h, k*w) int16, expected) per (size, type, quantiser) group of one file:
+    the k blocks of a group side by side, which is the raster the plane entry points take."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    hdr, q10s = g["hdr"], g["q10"]
+    r_off = np.concatenate([[0], np.cumsum(hdr[:, 2].astype(np.int64) * hdr[:, 3])])
+    c_off = np.concatenate([[0], np.cumsum(hdr[:, 7].astype(np.int64))])
+    groups = {}
+    for i, hd in enumerate(hdr):
+        assert int(hd[6]) == 0                                   # 8-bit encodes
+        groups.setdefault((int(hd[2]), int(hd[3]), int(hd[4]), tuple(int(v) for v in q10s[i])), []).append(i)
+    for (w, h, t, q10), idx in sorted(groups.items()):
+        n = int(hdr[idx[0]][7])
+        assert (n,) == (packed(w, h)[0] * packed(w, h)[1],)
+        plane = np.concatenate([g["residual"][r_off[i]:r_off[i + 1]].reshape(h, w) for i in idx], axis=1)
+        want = {k: np.stack([g[k][c_off[i]:c_off[i + 1]] for i in idx]) for k in ("coeff", "qcoeff", "dqcoeff")}
+        want["eob"] = np.array([hdr[i][10] for i in idx], np.uint16)
+        want["energy"] = np.array([(int(hdr[i][11]) & 0xffffffff) | (int(hdr[i][12]) << 32) for i in idx], np.uint64)
+        yield w, h, t, np.array(q10, np.int16), np.ascontiguousarray(plane), want
+
+
+def check_encoder_blocks(got, want, w, h, tag):
+    keys = ("coeff", "qcoeff", "dqcoeff", "eob") + (("energy",) if 64 in (w, h) else ())
+    for k in keys:
+        assert np.array_equal(got[k], want[k]), (tag, k)
