@@ -6,6 +6,8 @@
  *   out.medump      "-" = no dump
  *   --txq-dump      record forward transform + quantisation blocks of the EncDec stage (ref_txq.c wrappers)
  *   --bitstream     write the packets the encoder returns, in order
+ *   --cuda-txq      same for the secondary family: every 8-bit Av1EstimateTransform / EncDec Av1QuantizeInvQuantize call of the
+ *                   encode is served by svttxq_fwd_txfm_quant (include/svttxq.h), one block per call
  *   --cuda-me       encoder-in-the-loop: dlopen libsvtme_cuda.so and serve every MotionEstimateLcu call of the encode from
  *                   its SB facade (include/svtme_lcu.h) instead of the reference's C function. This hook is the whole
  *                   reference-side binding; the bitstream must not change.
@@ -16,6 +18,8 @@
 #include <dlfcn.h>
 #include "EbApi.h"
 #include "svtme_lcu.h"
+#include "svttxq.h"
+#include <pthread.h>
 
 int ref_me_dump_open(const char *path);
 void ref_me_dump_close(void);
@@ -70,13 +74,62 @@ static int cuda_me_open(const char *path, int w, int h) {
     return 0;
 }
 
+/* ---- the binding of the secondary family: Av1EstimateTransform + Av1QuantizeInvQuantize -> svttxq_fwd_txfm_quant ------------
+ * One block per call, because that is the granularity of the reference's call sites; this proves results, not speed
+ * (the batched, plane-level use is INTEGRATION.md section 4). */
+typedef int (*ref_txq_hook_fn)(void *user, const int16_t *residual, int w, int h, int tx_type, const int16_t *q10, int32_t *coeff,
+                               int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob, uint64_t *energy);
+void ref_txq_hook_set(ref_txq_hook_fn fn, void *user);
+void ref_txq_hook_stats(long *transforms, long *quants);
+static struct {
+    void *lib;
+    SvtTxqContext *ctx;
+    pthread_mutex_t mu;
+    int32_t (*create)(SvtTxqContext **, int32_t);
+    void (*destroy)(SvtTxqContext *);
+    const char *(*last_error)(const SvtTxqContext *);
+    int32_t (*run)(SvtTxqContext *, const int16_t *, int32_t, int32_t, int32_t, int32_t, int32_t, int32_t, const SvtTxqQuant *,
+                   int32_t *, int32_t *, int32_t *, uint16_t *, uint64_t *);
+} g_txq;
+
+static int cuda_txq_hook(void *user, const int16_t *residual, int w, int h, int tx_type, const int16_t *q10, int32_t *coeff,
+                         int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob, uint64_t *energy) {
+    (void)user;
+    SvtTxqQuant q;
+    if (q10) {
+        for (int i = 0; i < 2; i++) { q.zbin[i] = q10[i]; q.round[i] = q10[2 + i]; q.quant[i] = q10[4 + i]; q.quant_shift[i] = q10[6 + i]; q.dequant[i] = q10[8 + i]; }
+    } else {                                              /* transform only: any legal quantiser, its outputs are dropped */
+        for (int i = 0; i < 2; i++) { q.zbin[i] = 16; q.round[i] = 8; q.quant[i] = -1; q.quant_shift[i] = 16384; q.dequant[i] = 16; }
+    }
+    pthread_mutex_lock(&g_txq.mu);
+    const int32_t rc = g_txq.run(g_txq.ctx, residual, w, w, h, w, h, tx_type, &q, coeff, q10 ? qcoeff : NULL, q10 ? dqcoeff : NULL,
+                                 q10 ? eob : NULL, energy);
+    if (rc != 0) fprintf(stderr, "svttxq_fwd_txfm_quant: 0x%08x %s\n", (unsigned)rc, g_txq.last_error(g_txq.ctx));
+    pthread_mutex_unlock(&g_txq.mu);
+    return rc;
+}
+
+static int cuda_txq_open(const char *path) {
+    g_txq.lib = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    if (!g_txq.lib) { fprintf(stderr, "dlopen %s: %s\n", path, dlerror()); return -1; }
+#define SYM(field, name) do { *(void **)&g_txq.field = dlsym(g_txq.lib, name); if (!g_txq.field) { fprintf(stderr, "missing %s\n", name); return -1; } } while (0)
+    SYM(create, "svttxq_create"); SYM(destroy, "svttxq_destroy"); SYM(last_error, "svttxq_last_error"); SYM(run, "svttxq_fwd_txfm_quant");
+#undef SYM
+    pthread_mutex_init(&g_txq.mu, NULL);
+    const int32_t rc = g_txq.create(&g_txq.ctx, 0);
+    if (rc != 0) { fprintf(stderr, "svttxq_create failed: 0x%08x (no CUDA device?)\n", (unsigned)rc); return -1; }
+    ref_txq_hook_set(cuda_txq_hook, NULL);
+    return 0;
+}
+
 int main(int argc, char **argv) {
     if (argc < 7) { fprintf(stderr, "usage: %s in.yuv width height frames enc_mode out.medump|- [--bitstream out.obu] [--txq-dump out.txqdump] [--cuda-me lib.so]\n", argv[0]); return 2; }
-    const char *bitstream_path = NULL, *cuda_me = NULL, *txq_dump = NULL;
+    const char *bitstream_path = NULL, *cuda_me = NULL, *txq_dump = NULL, *cuda_txq = NULL;
     for (int i = 7; i + 1 < argc; i += 2) {
         if (!strcmp(argv[i], "--bitstream")) bitstream_path = argv[i + 1];
         else if (!strcmp(argv[i], "--cuda-me")) cuda_me = argv[i + 1];
         else if (!strcmp(argv[i], "--txq-dump")) txq_dump = argv[i + 1];
+        else if (!strcmp(argv[i], "--cuda-txq")) cuda_txq = argv[i + 1];
         else { fprintf(stderr, "unknown option %s\n", argv[i]); return 2; }
     }
     const int w = atoi(argv[2]), h = atoi(argv[3]), n = atoi(argv[4]), mode = atoi(argv[5]);
@@ -94,6 +147,7 @@ int main(int argc, char **argv) {
     if (strcmp(argv[6], "-") && ref_me_dump_open(argv[6]) != 0) { perror(argv[6]); return 2; }
     if (txq_dump && ref_txq_dump_open(txq_dump, 0, 0) != 0) { perror(txq_dump); return 2; }
     if (cuda_me && cuda_me_open(cuda_me, w, h) != 0) return 3;
+    if (cuda_txq && cuda_txq_open(cuda_txq) != 0) return 3;
     FILE *bs = bitstream_path ? fopen(bitstream_path, "wb") : NULL;
     if (bitstream_path && !bs) { perror(bitstream_path); return 2; }
     if (eb_init_encoder(enc) != EB_ErrorNone) { fprintf(stderr, "eb_init_encoder failed\n"); return 1; }
@@ -140,6 +194,13 @@ int main(int argc, char **argv) {
         fprintf(stderr, "enc_dump: cuda-me pictures %lld uploads %lld rows %lld\n", (long long)pics, (long long)ups, (long long)rows);
         ref_me_hook_set(NULL, NULL);
         g_cuda.destroy(g_cuda.session);
+    }
+    if (g_txq.ctx) {
+        long t = 0, q = 0;
+        ref_txq_hook_stats(&t, &q);
+        fprintf(stderr, "enc_dump: cuda-txq transforms %ld quantisations %ld\n", t, q);
+        ref_txq_hook_set(NULL, NULL);
+        g_txq.destroy(g_txq.ctx);
     }
     free(frame); fclose(f);
     return 0;

@@ -127,6 +127,17 @@ void __real_Av1QuantizeInvQuantize(PictureControlSet_t *pcs, int32_t *coeff, con
                                    uint8_t enableContouringQCUpdateFlag, uint32_t componentType, uint32_t bitIncrement, TxType tx_type,
                                    EbBool cleanSparseCoeffFlag);
 
+/* Hook (oracle/enc_driver.c --cuda-txq): when installed, 8-bit blocks are NOT computed by the reference's functions; the hook
+ * gets the residual block and the quantiser (q10 NULL = transform only wanted) and fills coefficients, three-quad energy,
+ * levels, dequantised levels and eob. Used by the encoder-in-the-loop test of the secondary kernel family. */
+typedef int (*ref_txq_hook_fn)(void *user, const int16_t *residual, int w, int h, int tx_type, const int16_t *q10, int32_t *coeff,
+                               int32_t *qcoeff, int32_t *dqcoeff, uint16_t *eob, uint64_t *energy);
+static ref_txq_hook_fn g_txq_hook; static void *g_txq_hook_user;
+static long g_txq_hook_calls[2];
+void ref_txq_hook_set(ref_txq_hook_fn fn, void *user) { g_txq_hook = fn; g_txq_hook_user = user; }
+void ref_txq_hook_stats(long *transforms, long *quants) { *transforms = g_txq_hook_calls[0]; *quants = g_txq_hook_calls[1]; }
+static void luma_or_chroma_q10(const PictureControlSet_t *pcs, uint32_t componentType, uint32_t bitIncrement, int16_t *q10);
+
 static FILE *g_txq_dump;
 static pthread_mutex_t g_txq_mu = PTHREAD_MUTEX_INITIALIZER;
 static int g_txq_every = 29, g_txq_cap = 24;
@@ -150,6 +161,22 @@ EbErrorType __wrap_Av1EstimateTransform(int16_t *residual_buffer, uint32_t resid
                                         uint32_t bitIncrement, TxType transform_type, EbAsm asm_type, PLANE_TYPE componentType,
                                         EB_TRANS_COEFF_SHAPE transCoeffShape) {
     const int t_slot = t_next;
+    if (g_txq_hook && bitIncrement == 0) {
+        const int w = tx_size_wide[transform_size], h = tx_size_high[transform_size], n = av1_get_max_eob(transform_size);
+        for (int y = 0; y < h; y++) memcpy(t_last.residual + y * w, residual_buffer + (size_t)y * residualStride, sizeof(int16_t) * w);
+        int32_t q[1024], dq[1024]; uint16_t eob = 0; uint64_t energy = 0;
+        if (g_txq_hook(g_txq_hook_user, t_last.residual, w, h, (int)transform_type, NULL, coeffBuffer, q, dq, &eob, &energy) != 0) {
+            fprintf(stderr, "ref_txq: the transform hook failed (%dx%d type %d)\n", w, h, (int)transform_type);
+            abort();
+        }
+        (void)n;
+        if (w == 64 || h == 64) *three_quad_energy = energy;
+        t_last.coeff = coeffBuffer; t_last.ts = transform_size; t_last.type = transform_type; t_last.bit_inc = 0;
+        t_last.energy = (w == 64 || h == 64) ? energy : 0;
+        t_next ^= 1;
+        __sync_fetch_and_add(&g_txq_hook_calls[0], 1);
+        return EB_ErrorNone;
+    }
     if (g_txq_dump) {                                     /* the input, before the call (in place is not used, but be safe) */
         const int w = tx_size_wide[transform_size], h = tx_size_high[transform_size];
         for (int y = 0; y < h; y++) memcpy(t_last.residual + y * w, residual_buffer + (size_t)y * residualStride, sizeof(int16_t) * w);
@@ -173,11 +200,29 @@ void __wrap_Av1QuantizeInvQuantize(PictureControlSet_t *pcs, int32_t *coeff, con
                                    uint8_t enableContouringQCUpdateFlag, uint32_t componentType, uint32_t bitIncrement, TxType tx_type,
                                    EbBool cleanSparseCoeffFlag) {
     int t_slot = -1;
-    for (int k = 0; k < 2 && g_txq_dump && componentType < 3; k++)
+    for (int k = 0; k < 2 && (g_txq_dump || g_txq_hook) && componentType < 3; k++)
         if (t_ring[k].coeff == coeff && t_ring[k].ts == (int)txsize && t_ring[k].type == (int)tx_type && t_ring[k].bit_inc == (int)bitIncrement)
             t_slot = k;
     const int paired = t_slot >= 0;
     const int n = av1_get_max_eob(txsize);
+    if (g_txq_hook && paired && bitIncrement == 0) {
+        int16_t q10[10];
+        luma_or_chroma_q10(pcs, componentType, bitIncrement, q10);
+        int32_t c[1024]; uint64_t energy = 0;
+        for (uint32_t i = 0; i < height; i++) {           /* what Av1QuantizeInvQuantize clears first, EbFullLoop.c:903-907 */
+            memset(quantCoeff + i * width, 0, width * sizeof(int32_t));
+            memset(reconCoeff + i * width, 0, width * sizeof(int32_t));
+        }
+        if (g_txq_hook(g_txq_hook_user, t_last.residual, tx_size_wide[txsize], tx_size_high[txsize], (int)tx_type, q10, c, quantCoeff,
+                       reconCoeff, eob, &energy) != 0 || memcmp(c, coeff, sizeof(int32_t) * n) != 0) {
+            fprintf(stderr, "ref_txq: the quantisation hook failed\n");
+            abort();
+        }
+        *y_count_non_zero_coeffs = *eob;
+        t_last.coeff = NULL;
+        __sync_fetch_and_add(&g_txq_hook_calls[1], 1);
+        return;
+    }
     int32_t *coeff_in = NULL;
     if (paired) { coeff_in = (int32_t *)malloc(sizeof(int32_t) * n); memcpy(coeff_in, coeff, sizeof(int32_t) * n); }
     __real_Av1QuantizeInvQuantize(pcs, coeff, coeffStride, quantCoeff, reconCoeff, qp, width, height, txsize, eob, candidate_plane,
@@ -189,24 +234,10 @@ void __wrap_Av1QuantizeInvQuantize(PictureControlSet_t *pcs, int32_t *coeff, con
     const uint32_t seen = g_txq_seen[txsize][tx_type][componentType]++;
     if (g_txq_dump && seen % (uint32_t)g_txq_every == 0 && g_txq_kept[txsize][tx_type][componentType] < (uint32_t)g_txq_cap) {
         g_txq_kept[txsize][tx_type][componentType]++;
-        /* the quantiser Av1QuantizeInvQuantize_II picks: EbFullLoop.c:721-800 (ADD_DELTA_QP_SUPPORT is 0) */
         const PictureParentControlSet_t *pp = pcs->parent_pcs_ptr;
         const uint32_t qi = pp->base_qindex;
-        const Quants *q = bitIncrement == 0 ? &pp->quantsMd : &pp->quants;
-        const Dequants *d = bitIncrement == 0 ? &pp->deqMd : &pp->deq;
         int16_t q10[10];
-        for (int i = 0; i < 2; i++) {
-            if (componentType == COMPONENT_LUMA) {
-                q10[0 + i] = q->y_zbin[qi][i]; q10[2 + i] = q->y_round[qi][i]; q10[4 + i] = q->y_quant[qi][i];
-                q10[6 + i] = q->y_quant_shift[qi][i]; q10[8 + i] = d->y_dequant_QTX[qi][i];
-            } else if (componentType == COMPONENT_CHROMA_CB) {
-                q10[0 + i] = q->u_zbin[qi][i]; q10[2 + i] = q->u_round[qi][i]; q10[4 + i] = q->u_quant[qi][i];
-                q10[6 + i] = q->u_quant_shift[qi][i]; q10[8 + i] = d->u_dequant_QTX[qi][i];
-            } else {
-                q10[0 + i] = q->v_zbin[qi][i]; q10[2 + i] = q->v_round[qi][i]; q10[4 + i] = q->v_quant[qi][i];
-                q10[6 + i] = q->v_quant_shift[qi][i]; q10[8 + i] = d->v_dequant_QTX[qi][i];
-            }
-        }
+        luma_or_chroma_q10(pcs, componentType, bitIncrement, q10);
         const int w = tx_size_wide[txsize], h = tx_size_high[txsize];
         int32_t hd[16]; memset(hd, 0, sizeof(hd));
         hd[0] = 0x54584647;                               /* 'TXFG' */
@@ -222,4 +253,24 @@ void __wrap_Av1QuantizeInvQuantize(PictureControlSet_t *pcs, int32_t *coeff, con
     }
     pthread_mutex_unlock(&g_txq_mu);
     free(coeff_in);
+}
+
+/* the quantiser Av1QuantizeInvQuantize_II picks: EbFullLoop.c:721-800 (ADD_DELTA_QP_SUPPORT is 0) */
+static void luma_or_chroma_q10(const PictureControlSet_t *pcs, uint32_t componentType, uint32_t bitIncrement, int16_t *q10) {
+    const PictureParentControlSet_t *pp = pcs->parent_pcs_ptr;
+    const uint32_t qi = pp->base_qindex;
+    const Quants *q = bitIncrement == 0 ? &pp->quantsMd : &pp->quants;
+    const Dequants *d = bitIncrement == 0 ? &pp->deqMd : &pp->deq;
+    for (int i = 0; i < 2; i++) {
+        if (componentType == COMPONENT_LUMA) {
+            q10[0 + i] = q->y_zbin[qi][i]; q10[2 + i] = q->y_round[qi][i]; q10[4 + i] = q->y_quant[qi][i];
+            q10[6 + i] = q->y_quant_shift[qi][i]; q10[8 + i] = d->y_dequant_QTX[qi][i];
+        } else if (componentType == COMPONENT_CHROMA_CB) {
+            q10[0 + i] = q->u_zbin[qi][i]; q10[2 + i] = q->u_round[qi][i]; q10[4 + i] = q->u_quant[qi][i];
+            q10[6 + i] = q->u_quant_shift[qi][i]; q10[8 + i] = d->u_dequant_QTX[qi][i];
+        } else {
+            q10[0 + i] = q->v_zbin[qi][i]; q10[2 + i] = q->v_round[qi][i]; q10[4 + i] = q->v_quant[qi][i];
+            q10[6 + i] = q->v_quant_shift[qi][i]; q10[8 + i] = d->v_dequant_QTX[qi][i];
+        }
+    }
 }

@@ -67,3 +67,28 @@ def test_reference_encoder_with_cuda_me_is_bit_identical(pkg, tmp_path, w, h, n,
     assert pictures == n - 1 and rows == (n - 1) * n_sb             # one whole-picture launch sequence per inter picture
     assert n <= uploads <= n + 8                                    # each picture crosses PCIe once (16 resident slots)
     assert len(bs0) > 1000 and bs0 == bs1, (len(bs0), len(bs1))     # the encode does not change
+
+
+@pytest.mark.skipif(not os.path.exists(ENC), reason="oracle/_ref/enc_dump not built (needs /root/reference at build time)")
+def test_reference_encoder_with_cuda_txq_and_me_is_bit_identical(pkg, tmp_path):
+    """Both kernel families in the loop: every 8-bit Av1EstimateTransform call (mode decision and EncDec) and every EncDec
+    Av1QuantizeInvQuantize call goes to svttxq_fwd_txfm_quant, one block per call (the granularity of the reference's call
+    sites -- this checks results, not speed), and ME goes through the SB facade. Same bitstream as the stock encoder."""
+    w, h, n = 416, 240, 6
+    frames = M.synth_video(w, h, n, seed=19, max_shift=8)
+    from make_encoder_golden import chroma_planes
+    yuv = str(tmp_path / "in.yuv")
+    with open(yuv, "wb") as f:
+        for i, x in enumerate(frames):
+            f.write(np.ascontiguousarray(x).tobytes())
+            for c in chroma_planes(frames, i):
+                f.write(np.ascontiguousarray(c).tobytes())
+    _, bs0, _ = _encode(str(tmp_path), "stock", yuv, w, h, n, [])
+    _, bs1, log1 = _encode(str(tmp_path), "txq", yuv, w, h, n, ["--cuda-txq", pkg.library_path()])
+    m = re.search(r"cuda-txq transforms (\d+) quantisations (\d+)", log1)
+    assert m, log1[-500:]
+    transforms, quants = int(m.group(1)), int(m.group(2))
+    assert quants > 1000 and transforms >= quants
+    assert len(bs0) > 1000 and bs0 == bs1, (len(bs0), len(bs1))
+    _, bs2, log2 = _encode(str(tmp_path), "both", yuv, w, h, n, ["--cuda-txq", pkg.library_path(), "--cuda-me", pkg.library_path()])
+    assert "cuda-me pictures %d " % (n - 1) in log2 and bs2 == bs0
