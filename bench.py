@@ -383,6 +383,12 @@ def run_gpu_impl(args, rank, world, local_rank):
         # algorithmic work of one full-pel launch: every SB of every picture of the batch, one list
         sads_per_launch = FULLPEL_BYTE_SADS_PER_SB_LIST * n_sb * len(jobs)
         achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n else None
+        traffic = None                                    # DRAM bytes per launch, scaled from the committed ncu capture
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))
+            traffic = tj["fullpel_kernel"]["dram_bytes_per_sb_list"] * n_sb * len(jobs)
+        except Exception:
+            pass
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965
         peak = int_pipe_peak(sm_mhz)
         peaks = {}
@@ -405,7 +411,8 @@ def run_gpu_impl(args, rank, world, local_rank):
                     "d2h_bytes_per_step": len(jobs) * n_sb * 85 * 40, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+                         "traffic_source": "dram__bytes_read+write per SB-list from profiles/r01/traffic.json (ncu --set full) x SB-lists per launch; bytes",
                          "peak_source": f"148 SM x 64 lanes/clk x 4 bytes x {sm_mhz} MHz (VABSDIFF4 issue rate, profiles/microbench)",
                          "launch_ms": fp_ms / fp_n if fp_n else None, "share_of_kernel_time": fp_ms / total_kernel_ms if total_kernel_ms else None},
             "roofline_hbm": {"kernel": "pyramid_kernel", "bound": "hbm", "achieved": (pyr_bytes / (py_ms / py_n / 1e3) / 1e9) if py_n else None,
