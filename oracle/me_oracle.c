@@ -23,7 +23,12 @@
  *
  * Supported geometry: width, height multiples of 8; width % 64 in {0, 32} (the reference itself
  * dispatches a void function for 40/56-wide edge SBs: EbComputeSAD.h:143-147).
- * 85-PU (square) mode only in this file; num_pus == 209 returns -2.
+ *   Q10 width-8 PUs taller than 8 (8x16, 8x32; 209-PU mode): the half-pel "SSD" kernel picked by
+ *       Log2f(width) is the fixed 8x8 one, so only the top eight rows are ranked   ME.c:1909-1916,
+ *                                                     ASM_SSE4_1/EbPictureOperators_Intrinsic_SSE4_1.c:534-569
+ *   Q11 209-PU full-pel search: the update test of 32x16 PU #5 (internal order) reads the stale
+ *       variable `sad` (= the bottom 64x32 sum) but stores its own sum             ME.c:363-367
+ * 85-PU (square, FullPelSearch_LCU) and 209-PU (open_loop_me_fullpel_search_sblock) modes.
  */
 #include "me_oracle.h"
 #include <stdlib.h>
@@ -192,10 +197,10 @@ typedef struct SbCtx {
     uint8_t  quarter_sb[32 * 32];           /* quarter_sb_buffer (persists across SBs like the reference's) */
     uint8_t  sixteenth_sb[16 * 16];         /* sixteenth_sb_buffer: every 2nd row, stride 16 */
     int      sa_x[2], sa_y[2], sa_w[2], sa_h[2];
-    uint32_t best_sad[2][MEO_SQUARE_PU_COUNT], best_mv[2][MEO_SQUARE_PU_COUNT];
-    uint32_t best_ssd[2][MEO_SQUARE_PU_COUNT];
-    uint8_t  sub_dir[MEO_SQUARE_PU_COUNT];  /* psub_pel_direction*, shared by both lists like the reference */
-    uint32_t bipred_sad[MEO_SQUARE_PU_COUNT];
+    uint32_t best_sad[2][MEO_MAX_PU_COUNT], best_mv[2][MEO_MAX_PU_COUNT];   /* internal order, like p_sb_best_sad */
+    uint32_t best_ssd[2][MEO_MAX_PU_COUNT];
+    uint8_t  sub_dir[MEO_MAX_PU_COUNT];  /* psub_pel_direction*, shared by both lists like the reference */
+    uint32_t bipred_sad[MEO_MAX_PU_COUNT];
     int      hx[3][2][2], hy[3][2][2];      /* per-region HME centres of level 0/1/2 (live across lists: Q7) */
     uint64_t hs[3][2][2];
 } SbCtx;
@@ -425,6 +430,82 @@ static void full_pel_search(SbCtx *c, int list) {
     }
 }
 
+/* ------------------------------------------------------------------ 209-PU mode: PU classes */
+/* EbMotionEstimation.h:123-175 (raster index inside a class -> internal index inside the class) */
+static const uint8_t TAB_ID[4] = { 0, 1, 2, 3 };
+static const uint8_t TAB32x16[8] = { 0, 2, 1, 3, 4, 6, 5, 7 };
+static const uint8_t TAB16x32[8] = { 0, 1, 2, 3, 4, 5, 6, 7 };
+static const uint8_t TAB32x8[16] = { 0, 4, 1, 5, 2, 6, 3, 7, 8, 12, 9, 13, 10, 14, 11, 15 };
+static const uint8_t TAB8x32[16] = { 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15 };
+static const uint8_t TAB16x8[32] = { 0, 2, 8, 10, 1, 3, 9, 11, 4, 6, 12, 14, 5, 7, 13, 15,
+                                     16, 18, 24, 26, 17, 19, 25, 27, 20, 22, 28, 30, 21, 23, 29, 31 };
+static const uint8_t TAB8x16[32] = { 0, 1, 2, 3, 8, 9, 10, 11, 4, 5, 6, 7, 12, 13, 14, 15,
+                                     16, 17, 18, 19, 24, 25, 26, 27, 20, 21, 22, 23, 28, 29, 30, 31 };
+/* pu_index ranges (EbMotionEstimation.h:176-262, EbMotionEstimationContext.h:45-261): raster inside each class */
+typedef struct PuClass { int base, w, h, count; const uint8_t *tab; } PuClass;
+static const PuClass PU_CLASS[14] = {
+    { 0, 64, 64, 1, TAB_ID },   { 1, 32, 32, 4, TAB_ID },     { 5, 16, 16, 16, TAB16 },     { 21, 8, 8, 64, TAB8 },
+    { 85, 64, 32, 2, TAB_ID },  { 87, 32, 16, 8, TAB32x16 },  { 95, 16, 8, 32, TAB16x8 },
+    { 127, 32, 64, 2, TAB_ID }, { 129, 16, 32, 8, TAB16x32 }, { 137, 8, 16, 32, TAB8x16 },
+    { 169, 32, 8, 16, TAB32x8 }, { 185, 8, 32, 16, TAB8x32 }, { 201, 64, 16, 4, TAB_ID },   { 205, 16, 64, 4, TAB_ID } };
+
+/* open_loop_me_fullpel_search_sblock, ME.c:1556-1595: one position at a time, raster order, every update a plain
+ * strict '<' (ExtSadCalculation_8x8_16x16 / _32x32_64x64 SSE4.1 kernels, ASM_SSE4_1/EbComputeSAD_Intrinsic_SSE4_1.c:21-164,
+ * and the C ExtSadCalculation, ME.c:266-1053, for the 124 non-square PUs built from the 8x8 / 16x16 / 32x32 SADs). */
+static void full_pel_search_ext(SbCtx *c, int list) {
+    const MeoPlane *rp = &c->ref[list]->full;
+    const int sax = c->sa_x[list], say = c->sa_y[list], saw = c->sa_w[list], sah = c->sa_h[list];
+    uint32_t *bs = c->best_sad[list], *bm = c->best_mv[list];
+    for (int i = 0; i < MEO_MAX_PU_COUNT; i++) bs[i] = MAX_SAD_VALUE;   /* InitializeBuffer_32bits(.., 52, 1, ..) = 209 words */
+#define UPD(base, k, v) do { if ((v) < bs[(base) + (k)]) { bs[(base) + (k)] = (v); bm[(base) + (k)] = mv; } } while (0)
+    for (int ys = 0; ys < sah; ys++) {
+        const uint8_t *rrow = px(rp, c->ox + sax, c->oy + say + ys);
+        for (int xs = 0; xs < saw; xs++) {
+            uint32_t s8[64], s16[16], s32[4], s64;
+            s64 = position_sads(c, rrow + xs, rp->stride, s8, s16, s32) << 1;
+            for (int b = 0; b < 64; b++) s8[b] <<= 1;
+            for (int b = 0; b < 16; b++) s16[b] <<= 1;
+            for (int b = 0; b < 4; b++) s32[b] <<= 1;
+            const uint32_t mv = mkmv((int16_t)((sax + xs) * 4), (int16_t)((say + ys) * 4));
+            for (int b = 0; b < 64; b++) UPD(21, b, s8[b]);
+            for (int b = 0; b < 16; b++) UPD(5, b, s16[b]);
+            for (int b = 0; b < 4; b++) UPD(1, b, s32[b]);
+            UPD(0, 0, s64);
+            uint32_t s16x8[32], s8x16[32], s32x16[8], s16x32[8], sad;
+            /* 64x32 */
+            sad = s32[0] + s32[1]; UPD(85, 0, sad);
+            sad = s32[2] + s32[3]; UPD(85, 1, sad);
+            /* 32x16: entry 5 tests the stale `sad` (quirk Q11) */
+            for (int k = 0; k < 8; k++) {
+                s32x16[k] = s16[2 * k] + s16[2 * k + 1];
+                if (k == 5) { if (sad < bs[87 + 5]) { bs[87 + 5] = s32x16[5]; bm[87 + 5] = mv; } }
+                else UPD(87, k, s32x16[k]);
+            }
+            /* 64x16 */
+            UPD(201, 0, s32x16[0] + s32x16[2]); UPD(201, 1, s32x16[1] + s32x16[3]);
+            UPD(201, 2, s32x16[4] + s32x16[6]); UPD(201, 3, s32x16[5] + s32x16[7]);
+            /* 16x8 */
+            for (int k = 0; k < 32; k++) { s16x8[k] = s8[2 * k] + s8[2 * k + 1]; UPD(95, k, s16x8[k]); }
+            /* 32x64 */
+            UPD(127, 0, s32[0] + s32[2]); UPD(127, 1, s32[1] + s32[3]);
+            /* 16x32, 16x64 */
+            for (int m = 0; m < 4; m++) for (int i = 0; i < 2; i++) {
+                s16x32[2 * m + i] = s16[4 * m + i] + s16[4 * m + i + 2]; UPD(129, 2 * m + i, s16x32[2 * m + i]);
+            }
+            for (int k = 0; k < 4; k++) UPD(205, k, s16x32[k] + s16x32[k + 4]);
+            /* 8x16 */
+            for (int m = 0; m < 16; m++) for (int i = 0; i < 2; i++) {
+                s8x16[2 * m + i] = s8[4 * m + i] + s8[4 * m + i + 2]; UPD(137, 2 * m + i, s8x16[2 * m + i]);
+            }
+            /* 32x8 */
+            for (int m = 0; m < 8; m++) for (int i = 0; i < 2; i++) UPD(169, 2 * m + i, s16x8[4 * m + i] + s16x8[4 * m + i + 2]);
+            /* 8x32 */
+            for (int m = 0; m < 4; m++) for (int i = 0; i < 4; i++) UPD(185, 4 * m + i, s8x16[8 * m + i] + s8x16[8 * m + i + 4]);
+        }
+    }
+#undef UPD
+}
+
 /* ------------------------------------------------------------------ sub-pel samples */
 /* AVC-style 4-tap {-2,18,18,-2}, +16 >> 5, clipped to u8
  * (ASM_SSSE3/EbAvcStyleMcp_Intrinsic_SSSE3.c:200-440, fracPos = 2). All three half-pel planes are
@@ -478,7 +559,8 @@ static void half_pel_pu(SbCtx *c, int list, int px0, int py0, int w, int h, int 
     const int X = c->ox + px0 + (xm >> 2), Y = c->oy + py0 + (ym >> 2);
     const uint8_t *src = c->src + (size_t)py0 * c->src_stride + px0;
     uint8_t blk[64 * 64];
-    *bssd = wrap_ssd(src, c->src_stride, px(rp, X, Y), rp->stride, w, h);
+    const int hs = (w == 8) ? 8 : h;                                  /* quirk Q10: the 8-wide kernel ranks eight rows */
+    *bssd = wrap_ssd(src, c->src_stride, px(rp, X, Y), rp->stride, w, hs);
     /* order L R T B TL TR BR BL */
     static const int8_t ty[8] = { S_B, S_B, S_H, S_H, S_J, S_J, S_J, S_J };
     static const int8_t dx[8] = { -1, 0, 0, 0, -1, 0, 0, -1 };
@@ -488,7 +570,7 @@ static void half_pel_pu(SbCtx *c, int list, int px0, int py0, int w, int h, int 
     uint64_t dist[8];
     for (int k = 0; k < 8; k++) {
         fetch_block(rp, ty[k], X + dx[k], Y + dy[k], w, h, blk);
-        dist[k] = wrap_ssd(src, c->src_stride, blk, 64, w, h);
+        dist[k] = wrap_ssd(src, c->src_stride, blk, 64, w, hs);
         if (dist[k] < *bssd) {
             *bsad = sad_wxh(src, c->src_stride, blk, 64, w, h);
             *bmv = mkmv((int16_t)(xm + mx[k]), (int16_t)(ym + my[k]));
@@ -574,6 +656,18 @@ static void subpel_search(SbCtx *c, int list) {
     for (int i = 0; i < 16; i++) quarter_pel_pu(c, list, (i & 3) << 4, (i >> 2) << 4, 16, 16, 5 + TAB16[i]);
     if (c->prm->cu8x8_mode != 1)
         for (int i = 0; i < 64; i++) quarter_pel_pu(c, list, (i & 7) << 3, (i >> 3) << 3, 8, 8, 21 + TAB8[i]);
+    if (c->prm->num_pus != MEO_MAX_PU_COUNT) return;
+    /* the ten non-square classes, ME.c:2417-2790 and 3582-4110 */
+    for (int pass = 0; pass < 2; pass++)
+        for (int k = 4; k < 14; k++) {
+            const PuClass *pc = &PU_CLASS[k];
+            const int ncols = 64 / pc->w;
+            for (int i = 0; i < pc->count; i++) {
+                const int x = (i % ncols) * pc->w, y = (i / ncols) * pc->h, idx = pc->base + pc->tab[i];
+                if (pass == 0) half_pel_pu(c, list, x, y, pc->w, pc->h, idx);
+                else           quarter_pel_pu(c, list, x, y, pc->w, pc->h, idx);
+            }
+        }
 }
 
 /* ------------------------------------------------------------------ bi-prediction + packing */
@@ -613,23 +707,25 @@ static uint32_t bipred_sad(const SbCtx *c, int px0, int py0, int w, int h, uint3
 }
 
 /* pu_index (raster inside each size class) -> geometry and internal index */
-static void pu_geom(int pu, int *x, int *y, int *sz, int *nidx) {
-    if (pu == 0)      { *x = 0; *y = 0; *sz = 64; *nidx = 0; }
-    else if (pu < 5)  { int i = pu - 1;  *x = (i & 1) << 5; *y = (i >> 1) << 5; *sz = 32; *nidx = pu; }
-    else if (pu < 21) { int i = pu - 5;  *x = (i & 3) << 4; *y = (i >> 2) << 4; *sz = 16; *nidx = 5 + TAB16[i]; }
-    else              { int i = pu - 21; *x = (i & 7) << 3; *y = (i >> 3) << 3; *sz = 8;  *nidx = 21 + TAB8[i]; }
+static void pu_geom(int pu, int *x, int *y, int *w, int *h, int *nidx) {
+    int k = 13;
+    while (pu < PU_CLASS[k].base) k--;
+    const PuClass *pc = &PU_CLASS[k];
+    const int i = pu - pc->base, ncols = 64 / pc->w;
+    *x = (i % ncols) * pc->w; *y = (i / ncols) * pc->h; *w = pc->w; *h = pc->h; *nidx = pc->base + pc->tab[i];
 }
 
 /* The tail of MotionEstimateLcu, ME.c:6973-7146 */
 static void pack_results(SbCtx *c, MeoPuResult *out) {
     const MeoParams *p = c->prm;
-    for (int pu = 0; pu < MEO_SQUARE_PU_COUNT; pu++) {
-        int x, y, sz, n; pu_geom(pu, &x, &y, &sz, &n);
+    const int ext = p->num_pus == MEO_MAX_PU_COUNT;
+    for (int pu = 0; pu < p->num_pus; pu++) {
+        int x, y, w, h, n; pu_geom(pu, &x, &y, &w, &h, &n);
         MeoPuResult *o = &out[pu];
         memset(o, 0, sizeof(*o));
         int total = p->num_lists;
-        if (p->num_lists == 2 && (p->cu8x8_mode == 0 || pu < 21)) {
-            c->bipred_sad[n] = bipred_sad(c, x, y, sz, sz, c->best_mv[0][n], c->best_mv[1][n]);
+        if (p->num_lists == 2 && (p->cu8x8_mode == 0 || pu < 21 || ext)) {
+            c->bipred_sad[n] = bipred_sad(c, x, y, w, h, c->best_mv[0][n], c->best_mv[1][n]);
             total = 3;
         }
         o->total_cand = (uint8_t)total;
@@ -655,7 +751,7 @@ static void pack_results(SbCtx *c, MeoPuResult *out) {
 int meo_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
                                 const MeoPyramid *ref0, const MeoPyramid *ref1,
                                 MeoPuResult *results, MeoSbDebug *debug) {
-    if (prm->num_pus != MEO_SQUARE_PU_COUNT) return -2;
+    if (prm->num_pus != MEO_SQUARE_PU_COUNT && prm->num_pus != MEO_MAX_PU_COUNT) return -2;
     if ((prm->width & 7) || (prm->height & 7) || ((prm->width & 63) != 0 && (prm->width & 63) != 32)) return -3;
     SbCtx *c = (SbCtx *)calloc(1, sizeof(SbCtx));
     if (!c) return -1;
@@ -690,7 +786,7 @@ int meo_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
             clip_search_area(c->ox, &sax, &saw, 63, prm->width);
             clip_search_area(c->oy, &say, &sah, 63, prm->height);
             c->sa_x[list] = sax; c->sa_y[list] = say; c->sa_w[list] = saw; c->sa_h[list] = sah;
-            full_pel_search(c, list);
+            if (prm->num_pus == MEO_MAX_PU_COUNT) full_pel_search_ext(c, list); else full_pel_search(c, list);
             if (prm->use_subpel == 1) subpel_search(c, list);
             if (debug) {
                 MeoSbDebug *d = &debug[sb];
@@ -698,7 +794,7 @@ int meo_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
                 d->search_center_x[list] = (int16_t)xsc; d->search_center_y[list] = (int16_t)ysc;
                 d->sa_origin_x[list] = (int16_t)sax; d->sa_origin_y[list] = (int16_t)say;
                 d->sa_width[list] = (int16_t)saw; d->sa_height[list] = (int16_t)sah;
-                memcpy(d->best_sad[list], c->best_sad[list], sizeof(d->best_sad[list]));
+                memcpy(d->best_sad[list], c->best_sad[list], sizeof(d->best_sad[list]));   /* square PUs only */
                 memcpy(d->best_mv[list], c->best_mv[list], sizeof(d->best_mv[list]));
             }
         }

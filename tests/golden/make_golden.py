@@ -29,6 +29,12 @@ CASES = [
     ("g256x128_b_nohme", 256, 128, 18, dict(noise=3.0, max_shift=20), (2, 1, 3, 1, {"enable_hme_flag": 0})),
     ("g256x128_b_sa24", 256, 128, 19, dict(noise=3.0, max_shift=20), (2, 1, 3, 1, {"search_area_w": 24, "search_area_h": 17})),
     ("g256x128_b_nosubpel", 256, 128, 20, dict(noise=3.0, max_shift=20), (2, 1, 3, 1, {"use_subpel": 0})),
+    # 209-PU mode (PIC_ALL_DEPTH_MODE: enc-mode 0-2 reference pictures): open_loop_me_fullpel_search_sblock + non-square PUs
+    ("g416x240_b_ext209", 416, 240, 21, dict(noise=3.0, max_shift=24), (2, 1, 3, 1, {"num_pus": 209})),
+    ("g256x192_p_ext209", 256, 192, 22, dict(noise=2.0, max_shift=40), (1, 0, 3, 1, {"num_pus": 209})),
+    ("g256x128_b_ext209_fullpel", 256, 128, 23, dict(noise=5.0, max_shift=30, contrast=2.0), (2, 2, 3, 1, {"num_pus": 209, "use_subpel": 0})),
+    ("g192x128_b_ext209_flat", 192, 128, 24, dict(noise=0.0, max_shift=6, contrast=0.05), (2, 0, 3, 1, {"num_pus": 209})),
+    ("g160x136_b_ext209_sa", 160, 136, 25, dict(noise=3.0, max_shift=20), (2, 1, 3, 1, {"num_pus": 209, "search_area_w": 27, "search_area_h": 13})),
 ]
 
 
@@ -39,7 +45,10 @@ def crc(a):
 def main():
     M.build_oracle(ref=True)
     ref = M.load_ref()
+    only = sys.argv[1:]                   # optional: generate just the named cases (substring match)
     for name, w, h, seed, kw, (nl, tl, hl, is_ref, over) in CASES:
+        if only and not any(o in name for o in only):
+            continue
         frames = M.synth_video(w, h, 3, seed=seed, **kw)
         pyr = [M.build_pyramid(ref, "ref", f) for f in frames]
         prm = M.default_params(ref, "ref", w, h, num_lists=nl, tl=tl, hl=hl, is_ref=is_ref)

