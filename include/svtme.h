@@ -37,6 +37,7 @@ extern "C" {
 #define SVTME_ERR_BAD_PARAMETER           ((int32_t)0x80001005)
 
 #define SVTME_SQUARE_PU_COUNT 85
+#define SVTME_MAX_PU_COUNT    209   /* MAX_ME_PU_COUNT: PIC_ALL_DEPTH_MODE pictures (enc-mode 0-2 reference pictures) */
 #define SVTME_MAX_BATCH       128
 
 /* kernel kinds, for svtme_kernel_times */

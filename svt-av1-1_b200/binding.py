@@ -5,6 +5,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SQUARE_PU_COUNT = 85
+MAX_PU_COUNT = 209
 MAX_BATCH = 128
 
 EXPORTED_SYMBOLS = (
@@ -222,7 +223,14 @@ class MeContext:
         jobs = (SvtMeJob * n)()
         sb_cols = (self.width + 63) // 64
         n_sb = self.n_sb if sb_rows is None else (sb_rows[1] - sb_rows[0]) * sb_cols
-        results = np.zeros((n, n_sb, SQUARE_PU_COUNT), dtype=PU_RESULT_DTYPE) if out_ptrs is None else None
+        # every job's rows are [n_sb][its own num_pus]: one array when the batch is uniform (85 or 209), else a list
+        pus = [int(sp[3].num_pus) for sp in specs]
+        if out_ptrs is not None:
+            results = None
+        elif len(set(pus)) <= 1:
+            results = np.zeros((n, n_sb, pus[0] if pus else SQUARE_PU_COUNT), dtype=PU_RESULT_DTYPE)
+        else:
+            results = [np.zeros((n_sb, k), dtype=PU_RESULT_DTYPE) for k in pus]
         debug = np.zeros((n, n_sb), dtype=SB_DEBUG_DTYPE) if want_debug else None
         for i, (cur, r0, r1, prm) in enumerate(specs):
             jobs[i].cur_slot, jobs[i].ref0_slot, jobs[i].ref1_slot = cur, r0, (r1 if r1 is not None else r0)

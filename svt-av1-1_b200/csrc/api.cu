@@ -19,6 +19,7 @@ using namespace svtme;
 
 namespace svtme {
 cudaError_t configure_fullpel();
+cudaError_t configure_fullpel_ext();
 cudaError_t configure_subpel();
 }
 
@@ -27,7 +28,10 @@ constexpr int kRing = 3;
 struct Batch {
     int cap = 0;                          // pictures this entry can hold
     SbScratch* d_scratch = nullptr;       // [cap][n_sb]
-    SvtMePuResult* d_results = nullptr;   // [cap][n_sb][85]
+    SbScratchExt* d_scratch_ext = nullptr;// [cap][n_sb], allocated when a batch first holds a 209-PU job
+    SvtMePuResult* d_results = nullptr;   // [cap][n_sb][res_pus] rows; a job's rows are packed with its own num_pus
+    int res_pus = 0;                      // 85, or 209 once a batch held a 209-PU job
+    size_t res_off[SVTME_MAX_BATCH];      // first result row of every job of the batch in d_results
     SvtMeSbDebug* d_debug = nullptr;      // [cap][n_sb]
     DJob* d_jobs = nullptr;               // [cap]
     DJob* h_jobs = nullptr;               // pinned
@@ -172,6 +176,7 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
         CU(cudaEventCreateWithFlags(&b.drained, cudaEventDisableTiming));
     }
     CU(configure_fullpel());
+    CU(configure_fullpel_ext());
     CU(configure_subpel());
     ctx->slots.resize(num_slots);
     for (auto& s : ctx->slots) {
@@ -196,9 +201,9 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
 }
 
 static void free_batch(Batch& b) {
-    cudaFree(b.d_scratch); cudaFree(b.d_results); cudaFree(b.d_debug); cudaFree(b.d_jobs);
+    cudaFree(b.d_scratch); cudaFree(b.d_scratch_ext); cudaFree(b.d_results); cudaFree(b.d_debug); cudaFree(b.d_jobs);
     if (b.h_jobs) cudaFreeHost(b.h_jobs);
-    b.d_scratch = nullptr; b.d_results = nullptr; b.d_debug = nullptr; b.d_jobs = nullptr; b.h_jobs = nullptr;
+    b.d_scratch = nullptr; b.d_scratch_ext = nullptr; b.res_pus = 0; b.d_results = nullptr; b.d_debug = nullptr; b.d_jobs = nullptr; b.h_jobs = nullptr;
     b.cap = 0;
 }
 
@@ -400,11 +405,15 @@ int32_t svtme_picture_download(SvtMeContext* ctx, int32_t slot, int32_t level, u
 }
 
 // Make ring entry `b` large enough for n pictures. The entry must be idle (its previous batch drained).
-static int32_t ensure_batch(SvtMeContext* ctx, Batch& b, int n) {
-    if (n <= b.cap) return SVTME_OK;
+static int32_t ensure_batch(SvtMeContext* ctx, Batch& b, int n, bool ext) {
+    const int pus = (ext || b.res_pus == kMaxPu) ? kMaxPu : kNumPu;
+    if (n <= b.cap && pus == b.res_pus) return SVTME_OK;
+    n = n > b.cap ? n : b.cap;
     free_batch(b);
     CU(cudaMalloc(&b.d_scratch, sizeof(SbScratch) * (size_t)n * ctx->n_sb));
-    CU(cudaMalloc(&b.d_results, sizeof(SvtMePuResult) * (size_t)n * ctx->n_sb * kNumPu));
+    if (pus == kMaxPu) CU(cudaMalloc(&b.d_scratch_ext, sizeof(SbScratchExt) * (size_t)n * ctx->n_sb));
+    CU(cudaMalloc(&b.d_results, sizeof(SvtMePuResult) * (size_t)n * ctx->n_sb * pus));
+    b.res_pus = pus;
     CU(cudaMalloc(&b.d_debug, sizeof(SvtMeSbDebug) * (size_t)n * ctx->n_sb));
     CU(cudaMalloc(&b.d_jobs, sizeof(DJob) * (size_t)n));
     CU(cudaMallocHost(&b.h_jobs, sizeof(DJob) * (size_t)n));
@@ -416,7 +425,7 @@ static bool params_ok(const SvtMeContext* ctx, const SvtMeParams& p, std::string
 #define REQ(c) if (!(c)) { why = "unsupported SvtMeParams: " #c; return false; }
     REQ(p.width == ctx->width && p.height == ctx->height);
     REQ(p.num_lists == 1 || p.num_lists == 2);
-    REQ(p.num_pus == SVTME_SQUARE_PU_COUNT);
+    REQ(p.num_pus == SVTME_SQUARE_PU_COUNT || p.num_pus == SVTME_MAX_PU_COUNT);
     REQ(p.hierarchical_levels >= 0 && p.hierarchical_levels <= 5);
     REQ(p.temporal_layer_index >= 0 && p.temporal_layer_index <= p.hierarchical_levels);
     REQ(p.num_hme_regions_w >= 1 && p.num_hme_regions_w <= 2 && p.num_hme_regions_h >= 1 && p.num_hme_regions_h <= 2);
@@ -438,8 +447,10 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     CU(cudaSetDevice(ctx->device));
     const int nslots = (int)ctx->slots.size();
     int max_lists = 1;
+    bool any_sq = false, any_ext = false;
     for (int i = 0; i < n_jobs; i++) {
         const SvtMeJob& j = jobs[i];
+        (j.params.num_pus == SVTME_MAX_PU_COUNT ? any_ext : any_sq) = true;
         std::string why;
         if (!params_ok(ctx, j.params, why)) return fail(ctx, SVTME_ERR_BAD_PARAMETER, why);
         if (j.cur_slot < 0 || j.cur_slot >= nslots || j.ref0_slot < 0 || j.ref0_slot >= nslots ||
@@ -454,9 +465,10 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     const int bi = ctx->next;
     Batch& b = ctx->ring[bi];
     if (b.used) CU(cudaEventSynchronize(b.drained));     // the batch that used this entry kRing submissions ago
-    int32_t rc = ensure_batch(ctx, b, n_jobs);
+    int32_t rc = ensure_batch(ctx, b, n_jobs, any_ext);
     if (rc != SVTME_OK) return rc;
     int max_sb = 0;                                       // grid width: the largest SB range of the batch
+    size_t res_rows = 0;
     for (int i = 0; i < n_jobs; i++) {
         const SvtMeJob& j = jobs[i];
         DJob& d = b.h_jobs[i];
@@ -466,7 +478,10 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         d.ref[1] = ctx->slots[r1].pyr;
         d.prm = j.params;
         d.scratch = b.d_scratch + (size_t)i * ctx->n_sb;
-        d.results = b.d_results + (size_t)i * ctx->n_sb * kNumPu;
+        d.scratch_ext = j.params.num_pus == SVTME_MAX_PU_COUNT ? b.d_scratch_ext + (size_t)i * ctx->n_sb : nullptr;
+        b.res_off[i] = res_rows;
+        d.results = b.d_results + res_rows;
+        res_rows += (size_t)ctx->n_sb * j.params.num_pus;
         d.debug = j.debug ? b.d_debug + (size_t)i * ctx->n_sb : nullptr;
         d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
         const bool whole = j.sb_row_begin == 0 && j.sb_row_end == 0;
@@ -484,18 +499,26 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     CU(cudaMemcpyAsync(b.d_jobs, b.h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
     for (int list = 0; list < max_lists; list++) {
         { LaunchTimer t(ctx, SVTME_KERNEL_HME, ctx->stream); launch_hme(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
-        { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, ctx->stream); launch_fullpel(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
-        { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, ctx->stream); launch_subpel(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
+        // the square (85-PU) and ext (209-PU) variants cover the same grid; a CTA of the other mode exits at once
+        for (int ext = 0; ext < 2; ext++) {
+            if (!(ext ? any_ext : any_sq)) continue;
+            { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, ctx->stream); launch_fullpel(b.d_jobs, n_jobs, max_sb, list, ext != 0, ctx->stream); }
+            { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, ctx->stream); launch_subpel(b.d_jobs, n_jobs, max_sb, list, ext != 0, ctx->stream); }
+        }
     }
-    { LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, ctx->stream); launch_bipred_pack(b.d_jobs, n_jobs, max_sb, ctx->stream); }
+    for (int ext = 0; ext < 2; ext++) {
+        if (!(ext ? any_ext : any_sq)) continue;
+        LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, ctx->stream); launch_bipred_pack(b.d_jobs, n_jobs, max_sb, ext != 0, ctx->stream);
+    }
     CU(cudaGetLastError());
     CU(cudaEventRecord(b.computed, ctx->stream));
     // results travel on their own stream, straight into the caller's buffers
     CU(cudaStreamWaitEvent(ctx->copy_out, b.computed, 0));
     for (int i = 0; i < n_jobs; i++) {                    // only the SBs of the job's row range travel
         const size_t first = (size_t)i * ctx->n_sb + b.h_jobs[i].sb_begin, count = (size_t)(b.h_jobs[i].sb_end - b.h_jobs[i].sb_begin);
+        const size_t pus = (size_t)jobs[i].params.num_pus;
         if (jobs[i].results)
-            CU(cudaMemcpyAsync(jobs[i].results, b.d_results + first * kNumPu, sizeof(SvtMePuResult) * count * kNumPu,
+            CU(cudaMemcpyAsync(jobs[i].results, b.d_results + b.res_off[i] + (size_t)b.h_jobs[i].sb_begin * pus, sizeof(SvtMePuResult) * count * pus,
                                cudaMemcpyDeviceToHost, ctx->copy_out));
         if (jobs[i].debug)
             CU(cudaMemcpyAsync(jobs[i].debug, b.d_debug + first, sizeof(SvtMeSbDebug) * count, cudaMemcpyDeviceToHost, ctx->copy_out));

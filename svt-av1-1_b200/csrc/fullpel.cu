@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
-    if (list >= p.num_lists) return;
+    if (list >= p.num_lists || p.num_pus != kNumPu) return;     // 209-PU jobs are searched by fullpel_ext_kernel
     const int tid = threadIdx.x;
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     SbScratch& scr = job.scratch[sb];
@@ -281,8 +281,11 @@ cudaError_t configure_fullpel() {
     return cudaFuncSetAttribute(fullpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpSmemBytes);
 }
 
-void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
-    fullpel_kernel<<<dim3(max_sb, n_jobs), kFpThreads, kFpSmemBytes, st>>>(d_jobs, list);
+void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);   // fullpel_ext.cu
+
+void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st) {
+    if (ext) launch_fullpel_ext(d_jobs, n_jobs, max_sb, list, st);
+    else     fullpel_kernel<<<dim3(max_sb, n_jobs), kFpThreads, kFpSmemBytes, st>>>(d_jobs, list);
 }
 
 }  // namespace svtme

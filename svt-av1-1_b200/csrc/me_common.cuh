@@ -14,6 +14,9 @@ namespace svtme {
 
 constexpr int kPadFull = 68, kPadQuarter = 32, kPadSixteenth = 16;
 constexpr int kNumPu = SVTME_SQUARE_PU_COUNT;
+constexpr int kMaxPu = SVTME_MAX_PU_COUNT;              // 209-PU mode (PIC_ALL_DEPTH_MODE pictures)
+constexpr int kNumNsq = kMaxPu - kNumPu;                // the 124 non-square PUs
+constexpr int kNumLevels = 4, kMaxLevels = 14;          // PU classes ("levels"): 4 square + 10 non-square
 constexpr uint32_t kMaxSadValue = 128u * 128u * 255u;   // EbMotionEstimation.h:78
 
 struct DPlane {
@@ -38,11 +41,19 @@ struct SbScratch {
     uint8_t  pred[2][4][64 * 64];                    // final uni-pred blocks per list and PU size level
 };
 
+// Extra state of the 209-PU mode: the non-square PUs (internal index 85..208) and their uni-prediction blocks.
+struct SbScratchExt {
+    uint32_t best_sad[2][kNumNsq];
+    uint32_t best_mv[2][kNumNsq];
+    uint8_t  pred[2][kMaxLevels - kNumLevels][64 * 64];
+};
+
 struct DJob {
     DPyramid cur, ref[2];
     SvtMeParams prm;
     SbScratch* scratch;          // [n_sb]
-    SvtMePuResult* results;      // [n_sb][85]  (device)
+    SbScratchExt* scratch_ext;   // [n_sb], only for jobs with prm.num_pus == 209
+    SvtMePuResult* results;      // [n_sb][prm.num_pus]  (device)
     SvtMeSbDebug* debug;         // [n_sb]      (device)
     int sb_cols, sb_rows;
     int sb_begin, sb_end;        // SBs [sb_begin, sb_end) of the raster are searched (an SB-row range)
@@ -53,6 +64,35 @@ __device__ __constant__ const uint8_t kTab16[16] = { 0, 1, 4, 5, 2, 3, 6, 7, 8, 
 __device__ __constant__ const uint8_t kTab8[64] = {
     0, 1, 4, 5, 16, 17, 20, 21, 2, 3, 6, 7, 18, 19, 22, 23, 8, 9, 12, 13, 24, 25, 28, 29, 10, 11, 14, 15, 26, 27, 30, 31,
     32, 33, 36, 37, 48, 49, 52, 53, 34, 35, 38, 39, 50, 51, 54, 55, 40, 41, 44, 45, 56, 57, 60, 61, 42, 43, 46, 47, 58, 59, 62, 63 };
+
+// PU classes of the 209-PU mode, in pu_index order (EbMotionEstimation.h:176-262, EbMotionEstimationContext.h:45-261):
+// first pu_index, width and height in 8x8 blocks. Inside a class pu_index runs in raster order.
+__device__ __constant__ const uint8_t kLevelBase[kMaxLevels] = { 0, 1, 5, 21, 85, 87, 95, 127, 129, 137, 169, 185, 201, 205 };
+__device__ __constant__ const uint8_t kLevelWb[kMaxLevels]   = { 8, 4, 2, 1, 8, 4, 2, 4, 2, 1, 4, 1, 8, 2 };
+__device__ __constant__ const uint8_t kLevelHb[kMaxLevels]   = { 8, 4, 2, 1, 4, 2, 1, 8, 4, 2, 1, 4, 2, 8 };
+// pu_index -> internal index (p_sb_best_sad order): tab16x16 / tab8x8 / tab32x16 / tab16x8 / tab16x32 / tab8x16 / tab32x8 /
+// tab8x32 of EbMotionEstimation.h:89-175 with the class bases added
+__device__ __constant__ const uint8_t kInternal[kMaxPu] = {
+    0, 1, 2, 3, 4,
+    5, 6, 9, 10, 7, 8, 11, 12, 13, 14, 17, 18, 15, 16, 19, 20,
+    21, 22, 25, 26, 37, 38, 41, 42, 23, 24, 27, 28, 39, 40, 43, 44, 29, 30, 33, 34, 45, 46, 49, 50, 31, 32, 35, 36, 47, 48, 51, 52,
+    53, 54, 57, 58, 69, 70, 73, 74, 55, 56, 59, 60, 71, 72, 75, 76, 61, 62, 65, 66, 77, 78, 81, 82, 63, 64, 67, 68, 79, 80, 83, 84,
+    85, 86,
+    87, 89, 88, 90, 91, 93, 92, 94,
+    95, 97, 103, 105, 96, 98, 104, 106, 99, 101, 107, 109, 100, 102, 108, 110,
+    111, 113, 119, 121, 112, 114, 120, 122, 115, 117, 123, 125, 116, 118, 124, 126,
+    127, 128,
+    129, 130, 131, 132, 133, 134, 135, 136,
+    137, 138, 139, 140, 145, 146, 147, 148, 141, 142, 143, 144, 149, 150, 151, 152,
+    153, 154, 155, 156, 161, 162, 163, 164, 157, 158, 159, 160, 165, 166, 167, 168,
+    169, 173, 170, 174, 171, 175, 172, 176, 177, 181, 178, 182, 179, 183, 180, 184,
+    185, 186, 187, 188, 189, 190, 191, 192, 193, 194, 195, 196, 197, 198, 199, 200,
+    201, 202, 203, 204, 205, 206, 207, 208 };
+// internal index of the PU of class L that contains 8x8 block (bx, by)
+__device__ __forceinline__ int pu_of_block_any(int L, int bx, int by) {
+    const int wb = kLevelWb[L], hb = kLevelHb[L];
+    return kInternal[kLevelBase[L] + (by / hb) * (8 / wb) + bx / wb];
+}
 
 __device__ __forceinline__ int mv_x(uint32_t mv) { return (int16_t)(mv & 0xFFFFu); }
 __device__ __forceinline__ int mv_y(uint32_t mv) { return (int16_t)(mv >> 16); }
@@ -106,9 +146,11 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 void launch_pyramid(const uint8_t* d_luma, int luma_stride, const DPyramid& pyr, cudaStream_t st);
 void launch_unpack16(const uint16_t* d_in, int in_stride, uint8_t* d_msb, uint8_t* d_rem, int width, int height, cudaStream_t st);
 void launch_hme(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);
-void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);
-void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);
-void launch_bipred_pack(const DJob* d_jobs, int n_jobs, int max_sb, cudaStream_t st);
+// The square-mode and ext-mode kernels are separate launches over the same grid; a CTA whose job is of the other
+// mode exits at once. `ext` selects the 209-PU variant.
+void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st);
+void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st);
+void launch_bipred_pack(const DJob* d_jobs, int n_jobs, int max_sb, bool ext, cudaStream_t st);
 cudaError_t configure_kernels();
 
 }  // namespace svtme

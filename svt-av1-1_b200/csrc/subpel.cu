@@ -29,17 +29,17 @@ constexpr int kPlWords = kPlRows * kPlPitchW + 132;  // + room for the row skew 
 __device__ __forceinline__ int plane_row(int r) { return r * kPlPitchW + ((r >> 3) & 1) + (r & ~15); }
 constexpr int kMargin = 3;              // window starts 3 pixels left/above the search-area origin
 
-struct SpShared {
+template <int NPU>
+struct SpSharedT {
     uint32_t plane[4][kPlWords];        // A, B, H, J
     uint32_t src[64 * 16];
-    uint32_t sum_ssd[9][kNumPu];        // per (candidate, PU) distortion sums, accumulated with shared atomics
-    uint32_t sum_sad[9][kNumPu];
-    uint32_t pu_sad[kNumPu], pu_mv[kNumPu], pu_ssd[kNumPu];
-    int32_t  pu_dir[kNumPu];
-    uint32_t pu_imv[kNumPu];            // MV at entry of the current stage
+    uint32_t sum_ssd[9][NPU];           // per (candidate, PU) distortion sums, accumulated with shared atomics
+    uint32_t sum_sad[9][NPU];
+    uint32_t pu_sad[NPU], pu_mv[NPU], pu_ssd[NPU];
+    int32_t  pu_dir[NPU];
+    uint32_t pu_imv[NPU];               // MV at entry of the current stage
     int32_t  bbox[4];                   // min X, min Y, max -X... see the kernel: bounding box of the blocks' window positions
 };
-constexpr int kSpSmemBytes = (int)sizeof(SpShared);
 
 enum { S_A = 0, S_B = 1, S_H = 2, S_J = 3 };
 enum { D_TL = 0, D_T = 1, D_TR = 2, D_R = 3, D_BR = 4, D_B = 5, D_BL = 6, D_L = 7 };   // EbMotionEstimation.h:62-69
@@ -141,15 +141,36 @@ __device__ __forceinline__ uint32_t pu_sum(uint32_t v, int L) {
 __device__ __forceinline__ bool pu_leader(int L, int lane) {
     return L == 0 ? lane == 0 : L == 1 ? (lane & 0x1B) == 0 : L == 2 ? (lane & 0x09) == 0 : true;
 }
+// The same for any of the 14 PU classes of the 209-PU mode (wb x hb blocks, warp-uniform): a warp holds block rows
+// 4w .. 4w+3, so PUs eight blocks tall are shared by the two warps of the level (the caller adds those with atomics).
+__device__ __forceinline__ uint32_t pu_sum_any(uint32_t v, int wb, int hb) {
+    if (wb > 1) v += __shfl_xor_sync(0xffffffffu, v, 1);
+    if (wb > 2) v += __shfl_xor_sync(0xffffffffu, v, 2);
+    if (wb > 4) v += __shfl_xor_sync(0xffffffffu, v, 4);
+    if (hb > 1) v += __shfl_xor_sync(0xffffffffu, v, 8);
+    if (hb > 2) v += __shfl_xor_sync(0xffffffffu, v, 16);
+    return v;
+}
+__device__ __forceinline__ bool pu_leader_any(int wb, int hb, int lane) {
+    return (lane & ((wb - 1) | ((min(hb, 4) - 1) << 3))) == 0;
+}
 
+// Ext = the 209-PU mode: 14 PU classes ("levels") instead of 4; the non-square PUs live in SbScratchExt. Every level
+// is 64 8x8-block tasks, so a warp always works on one level.
+template <bool Ext>
 __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
+    constexpr int NPU = Ext ? kMaxPu : kNumPu, NLEV = Ext ? kMaxLevels : kNumLevels;
+    using SpShared = SpSharedT<NPU>;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SpShared& sh = *reinterpret_cast<SpShared*>(smem_raw);
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
-    if (list >= p.num_lists) return;
+    if (list >= p.num_lists || (p.num_pus == kMaxPu) != Ext) return;
+    auto block_pu = [](int L, int bx, int by) { if constexpr (Ext) return pu_of_block_any(L, bx, by); else return pu_of_block(L, bx, by); };
+    // 8x8 half/quarter-pel is switched off by cu8x8_mode 1 (disable8x8CuInMeFlag); the non-square classes never are
+    auto pu_enabled = [&](int pu) { return pu < 21 || pu >= kNumPu || p.cu8x8_mode != 1; };
     const int tid = threadIdx.x;
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     SbScratch& scr = job.scratch[sb];
@@ -158,6 +179,10 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     for (int t = tid; t < 64 * 16; t += kSpThreads)
         sh.src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + (t >> 4)));
     if (tid < kNumPu) { sh.pu_sad[tid] = scr.best_sad[list][tid]; sh.pu_mv[tid] = scr.best_mv[list][tid]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
+    if constexpr (Ext) {
+        const SbScratchExt& scx = job.scratch_ext[sb];
+        if (tid >= kNumPu && tid < NPU) { sh.pu_sad[tid] = scx.best_sad[list][tid - kNumPu]; sh.pu_mv[tid] = scx.best_mv[list][tid - kNumPu]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
+    }
     if (tid < 4) sh.bbox[tid] = 0x7FFFFFFF;
     __syncthreads();
     // The refinement only reads the window around the 256 (level, 8x8 block) positions the full-pel search chose
@@ -165,9 +190,9 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     // bounding box, not the whole search area: with coherent motion that is a fraction of it. The box becomes the new
     // window origin (sax, say) and extent (ww words x wr rows); everything below is unchanged.
     int sax = scr.sa_x[list], say = scr.sa_y[list];
-    {
-        const int blk = tid & 63, L = tid >> 6, bx = blk & 7, by = blk >> 3;
-        const uint32_t mv = sh.pu_mv[pu_of_block(L, bx, by)];
+    for (int t = tid; t < NLEV * 64; t += kSpThreads) {
+        const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
+        const uint32_t mv = sh.pu_mv[block_pu(L, bx, by)];
         const int X = kMargin + (mv_x(mv) >> 2) - sax + bx * 8, Y = kMargin + (mv_y(mv) >> 2) - say + by * 8;
         const int xmin = __reduce_min_sync(0xffffffffu, X), ymin = __reduce_min_sync(0xffffffffu, Y);
         const int xneg = __reduce_min_sync(0xffffffffu, -X), yneg = __reduce_min_sync(0xffffffffu, -Y);
@@ -221,14 +246,14 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         }
         __syncthreads();
 
-        for (int t = tid; t < 9 * kNumPu; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
+        for (int t = tid; t < 9 * NPU; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
         // ---- half-pel: one thread per (level, 8x8 block) walks the ten plane rows its nine candidates share
         // (L/R read the same three B words per row, T/B the same H rows, the four diagonals the same J rows and words);
         // wrapping-SSD and SAD are summed per (candidate, PU) with shared atomics
-        for (int t = tid; t < 4 * 64; t += kSpThreads) {
+        for (int t = tid; t < NLEV * 64; t += kSpThreads) {
             const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
-            const int pu = pu_of_block(L, bx, by);
+            const int pu = block_pu(L, bx, by);
             const uint32_t mv = sh.pu_imv[pu];
             const int X = kMargin + (mv_x(mv) >> 2) - sax + bx * 8, Y = kMargin + (mv_y(mv) >> 2) - say + by * 8;
             const int wa = X >> 2, wb = (X - 1) >> 2;
@@ -270,19 +295,34 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             }
 #undef HP_ACC
             // a warp holds 8x4 blocks of ONE level: sum the blocks of each PU inside the warp, one lane per PU writes
-            const bool leader = pu_leader(L, tid & 31);
+            if constexpr (Ext) {
+                const int pwb = kLevelWb[L], phb = kLevelHb[L];
+                // quirk Q10: for 8-wide PUs taller than 8 the reference ranks the candidates on the top eight rows only
+                const bool ranked = !(pwb == 1 && phb > 1 && (by % phb) != 0);
+                const bool leader = pu_leader_any(pwb, phb, tid & 31);
 #pragma unroll
-            for (int k = 0; k < 9; k++) {
-                const uint32_t a = pu_sum(ssd[k], L), b = k ? pu_sum(sad[k], L) : 0u;
-                if (leader) {
-                    if (L == 0) { atomicAdd(&sh.sum_ssd[k][0], a); if (k) atomicAdd(&sh.sum_sad[k][0], b); }   // two warps share PU 0
-                    else { sh.sum_ssd[k][pu] = a; sh.sum_sad[k][pu] = b; }
+                for (int k = 0; k < 9; k++) {
+                    const uint32_t a = pu_sum_any(ranked ? ssd[k] : 0u, pwb, phb), b = k ? pu_sum_any(sad[k], pwb, phb) : 0u;
+                    if (leader) {
+                        if (phb == 8) { atomicAdd(&sh.sum_ssd[k][pu], a); if (k) atomicAdd(&sh.sum_sad[k][pu], b); }   // two warps share the PU
+                        else { sh.sum_ssd[k][pu] = a; sh.sum_sad[k][pu] = b; }
+                    }
+                }
+            } else {
+                const bool leader = pu_leader(L, tid & 31);
+#pragma unroll
+                for (int k = 0; k < 9; k++) {
+                    const uint32_t a = pu_sum(ssd[k], L), b = k ? pu_sum(sad[k], L) : 0u;
+                    if (leader) {
+                        if (L == 0) { atomicAdd(&sh.sum_ssd[k][0], a); if (k) atomicAdd(&sh.sum_sad[k][0], b); }   // two warps share PU 0
+                        else { sh.sum_ssd[k][pu] = a; sh.sum_sad[k][pu] = b; }
+                    }
                 }
             }
         }
         __syncthreads();
         // ---- per PU: nine candidates in the reference's order, strict '<' on the SSD  (ME.c:1909-2239)
-        if (tid < kNumPu && (tid < 21 || p.cu8x8_mode != 1)) {
+        if (tid < NPU && pu_enabled(tid)) {
             uint32_t dist[9], sadv[9];
 #pragma unroll
             for (int k = 0; k < 9; k++) { dist[k] = sh.sum_ssd[k][tid]; sadv[k] = sh.sum_sad[k][tid]; }
@@ -298,15 +338,15 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             sh.pu_ssd[tid] = bssd; sh.pu_sad[tid] = bsad; sh.pu_mv[tid] = bmv; sh.pu_dir[tid] = dir;
         }
         __syncthreads();
-        if (tid < kNumPu) sh.pu_imv[tid] = sh.pu_mv[tid];
-        for (int t = tid; t < 9 * kNumPu; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
+        if (tid < NPU) sh.pu_imv[tid] = sh.pu_mv[tid];
+        for (int t = tid; t < 9 * NPU; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
 
         // ---- quarter-pel: one thread per (level, 8x8 block); exactly three of the eight positions are valid for a
         // given half-pel direction -> partial true-SSD and SAD of the averaged plane pair, source rows kept in registers
-        {
-            const int blk = tid & 63, L = tid >> 6, bx = blk & 7, by = blk >> 3;
-            const int pu = pu_of_block(L, bx, by);
+        for (int t = tid; t < NLEV * 64; t += kSpThreads) {
+            const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
+            const int pu = block_pu(L, bx, by);
             const bool in_area = (L != 0) || (bx < 4 && by < 4);          // quirk Q6: 64x64 refined on its top-left 32x32
             const bool active = in_area && (L != 3 || p.cu8x8_mode != 1);
             const uint32_t mv = sh.pu_imv[pu];
@@ -316,7 +356,10 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             uint2 src[8];
 #pragma unroll
             for (int r = 0; r < 8; r++) src[r] = *reinterpret_cast<const uint2*>(&sh.src[(by * 8 + r) * 16 + bx * 2]);
-            const bool leader = active && pu_leader(L, tid & 31);         // lane 0 of the 64x64 level is inside the area
+            int pwb = 1, phb = 1;
+            if constexpr (Ext) { pwb = kLevelWb[L]; phb = kLevelHb[L]; }
+            // lane 0 of the 64x64 level is inside the area
+            const bool leader = active && (Ext ? pu_leader_any(pwb, phb, tid & 31) : pu_leader(L, tid & 31));
             int kk = -1;
 #pragma unroll 1
             for (int j = 0; j < 3; j++) {
@@ -334,12 +377,20 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                         sad = sad4(src[r].x, a0, sad); sad = sad4(src[r].y, a1, sad);
                     }
                 }
-                ssd = pu_sum(ssd, L); sad = pu_sum(sad, L);
-                if (leader) { sh.sum_ssd[kk][pu] = ssd; sh.sum_sad[kk][pu] = sad; }   // 64x64: only the first warp has active blocks
+                if constexpr (Ext) {
+                    ssd = pu_sum_any(ssd, pwb, phb); sad = pu_sum_any(sad, pwb, phb);
+                    if (leader) {
+                        if (L != 0 && phb == 8) { atomicAdd(&sh.sum_ssd[kk][pu], ssd); atomicAdd(&sh.sum_sad[kk][pu], sad); }   // both warps hold blocks
+                        else { sh.sum_ssd[kk][pu] = ssd; sh.sum_sad[kk][pu] = sad; }
+                    }
+                } else {
+                    ssd = pu_sum(ssd, L); sad = pu_sum(sad, L);
+                    if (leader) { sh.sum_ssd[kk][pu] = ssd; sh.sum_sad[kk][pu] = sad; }   // 64x64: only the first warp has active blocks
+                }
             }
         }
         __syncthreads();
-        if (tid < kNumPu && (tid < 21 || p.cu8x8_mode != 1)) {
+        if (tid < NPU && pu_enabled(tid)) {
             const uint32_t imv = sh.pu_imv[tid];
             const int method = (mv_y(imv) & 2) + ((mv_x(imv) & 2) >> 1), dir = sh.pu_dir[tid];
             uint32_t bssd = sh.pu_ssd[tid], bsad = sh.pu_sad[tid], bmv = imv;
@@ -353,19 +404,25 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         }
         __syncthreads();
         if (tid < kNumPu) { scr.best_sad[list][tid] = sh.pu_sad[tid]; scr.best_mv[list][tid] = sh.pu_mv[tid]; }
+        if constexpr (Ext) {
+            SbScratchExt& scx = job.scratch_ext[sb];
+            if (tid >= kNumPu && tid < NPU) { scx.best_sad[list][tid - kNumPu] = sh.pu_sad[tid]; scx.best_mv[list][tid - kNumPu] = sh.pu_mv[tid]; }
+        }
     } else {
         // planes B/H/J are not needed: integer MVs only use plane A below
     }
 
     // ---- final uni-prediction blocks of this list for every PU level (consumed by bipred_pack_kernel)
     if (p.num_lists == 2) {
-        for (int t = tid; t < 4 * 64; t += kSpThreads) {
+        for (int t = tid; t < NLEV * 64; t += kSpThreads) {
             const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
-            const uint32_t mv = sh.pu_mv[pu_of_block(L, bx, by)];
+            const uint32_t mv = sh.pu_mv[block_pu(L, bx, by)];
             const int xm = mv_x(mv), ym = mv_y(mv);
             const int8_t* f = kFrac[(xm & 3) + ((ym & 3) << 2)];
             const int X = kMargin + (xm >> 2) - sax + bx * 8, Y = kMargin + (ym >> 2) - say + by * 8;
-            uint32_t* dst = reinterpret_cast<uint32_t*>(scr.pred[list][L]) + (by * 8) * 16 + bx * 2;
+            uint8_t* pred = scr.pred[list][L < kNumLevels ? L : 0];
+            if constexpr (Ext) { if (L >= kNumLevels) pred = job.scratch_ext[sb].pred[list][L - kNumLevels]; }
+            uint32_t* dst = reinterpret_cast<uint32_t*>(pred) + (by * 8) * 16 + bx * 2;
 #pragma unroll
             for (int r = 0; r < 8; r++) {
                 uint2 c = load8(sh.plane[f[0]], Y + f[2] + r, X + f[1]);
@@ -380,11 +437,14 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
 }
 
 cudaError_t configure_subpel() {
-    return cudaFuncSetAttribute(subpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSpSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(subpel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SpSharedT<kNumPu>));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(subpel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SpSharedT<kMaxPu>));
 }
 
-void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
-    subpel_kernel<<<dim3(max_sb, n_jobs), kSpThreads, kSpSmemBytes, st>>>(d_jobs, list);
+void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st) {
+    if (ext) subpel_kernel<true><<<dim3(max_sb, n_jobs), kSpThreads, sizeof(SpSharedT<kMaxPu>), st>>>(d_jobs, list);
+    else     subpel_kernel<false><<<dim3(max_sb, n_jobs), kSpThreads, sizeof(SpSharedT<kNumPu>), st>>>(d_jobs, list);
 }
 
 }  // namespace svtme

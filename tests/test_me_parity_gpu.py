@@ -203,7 +203,7 @@ def test_error_codes(pkg):
     w, h = 128, 128
     ctx = pkg.MeContext(w, h, 2)
     p = pkg.default_params(w, h, 2, 1, 3, 1)
-    p.num_pus = 209
+    p.num_pus = 100                      # only 85 and 209 exist
     with pytest.raises(pkg.SvtMeError, match="0x80001005"):
         ctx.motion_estimate([(0, 1, 1, p)])
     p = pkg.default_params(w, h, 2, 1, 3, 1)
