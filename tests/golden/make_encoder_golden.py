@@ -25,6 +25,10 @@ CASES = [  # name, width, height, frames, enc_mode, hierarchical_levels, seed, s
     ("enc_416x240_m3", 416, 240, 30, 3, 3, 416, dict(max_shift=12)),
     # (this reference version accepts hierarchical_levels 3 only); CIF: the last SB row is half height
     ("enc_352x288_m3", 352, 288, 19, 3, 3, 352, dict(max_shift=6, noise=4.0)),
+    # enc-mode 2: reference pictures are PIC_ALL_C_DEPTH_MODE (209 PUs), non-reference ones 85 -- a mixed clip;
+    # enc-mode 0: every picture is PIC_ALL_DEPTH_MODE (EbPictureDecisionProcess.c:357-379)
+    ("enc_256x192_m2", 256, 192, 19, 2, 3, 256, dict(max_shift=10)),
+    ("enc_192x128_m0", 192, 128, 19, 0, 3, 192, dict(max_shift=8, noise=4.0)),
 ]
 HDR = 48
 
@@ -81,7 +85,10 @@ def parse_txq(path):
 def main():
     M.build_oracle(ref=True)
     exe = os.path.join(M.ORACLE_DIR, "_ref", "enc_dump")
+    only = sys.argv[1:]                   # optional: generate just the named cases (substring match)
     for name, w, h, n, mode, hl, seed, kw in CASES:
+        if only and not any(o in name for o in only):
+            continue
         frames = M.synth_video(w, h, n, seed=seed, **kw)
         with tempfile.TemporaryDirectory() as td:
             yuv, dump = os.path.join(td, "in.yuv"), os.path.join(td, "out.medump")
@@ -113,12 +120,14 @@ def main():
                 v["yMvL1"] = 0
             rows.append(r)
         num_pus = {int(hd[18]) for hd in hdrs}
-        assert len(num_pus) == 1
+        # a picture's rows are [n_sb][its own num_pus (hdr[18])] x 40 bytes, zero-padded to the widest picture of the clip
+        width = max(num_pus) * 40
+        rows = [np.pad(r, ((0, 0), (0, width - r.shape[1]))) for r in rows]
         out = os.path.join(HERE, name + ".npz")
         np.savez_compressed(out, geometry=np.array([w, h, n, mode, seed, hl], np.int32), synth=np.array([repr(kw)]),
                             frame_crc=np.array([zlib.crc32(np.ascontiguousarray(x).tobytes()) & 0xFFFFFFFF for x in frames], np.uint32),
                             hdr=np.stack(hdrs), rows=np.stack(rows))
-        print("wrote", out, len(pocs), "inter pictures,", num_pus.pop(), "PUs per SB,", os.path.getsize(out), "bytes")
+        print("wrote", out, len(pocs), "inter pictures,", sorted(num_pus), "PUs per SB,", os.path.getsize(out), "bytes")
         # EncDec forward transform + quantisation blocks of the same encode ("txq_" prefix: read by tests/test_txq_encoder_golden.py)
         out = os.path.join(HERE, "txq_" + name + ".npz")
         np.savez_compressed(out, **txq)

@@ -266,6 +266,11 @@ def encoder_cases():
     return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and f.startswith("enc_"))
 
 
+def encoder_rows(hd, rows):
+    """MeCuResults_t rows of one dumped picture: [n_sb][hdr[18] PUs] (fixtures pad the rows of mixed clips to 209 PUs)."""
+    return np.ascontiguousarray(rows[:, :int(hd[18]) * 40]).view(PU_RESULT_DTYPE)
+
+
 def encoder_clip(g):
     """Regenerate the synthetic clip an enc_* golden was encoded from and check it against the stored CRCs."""
     w, h, n, _mode, seed, _hl = (int(v) for v in g["geometry"])
@@ -286,6 +291,10 @@ def encoder_params(cls, hd, defaults):
            "hme_l1_w": hd[28:30], "hme_l1_h": hd[30:32], "hme_l2_w": hd[32:34], "hme_l2_h": hd[34:36],
            "search_area_w": hd[36], "search_area_h": hd[37]}
     p = convert_params(cls, defaults)
+    # signal_derivation_multi_processes_oq (EbPictureDecisionProcess.c:357-379): PIC_ALL(_C)_DEPTH_MODE = 209 PUs for every
+    # picture of enc-mode 0 and for the reference pictures of enc-modes 1 and 2; 85 otherwise. The library default is 85.
+    if len(hd) > 38 and (int(hd[38]) == 0 or (int(hd[38]) in (1, 2) and int(hd[10]))):
+        p.num_pus = 209
     bad = []
     for k, v in enc.items():
         cur = getattr(p, k)

@@ -30,7 +30,7 @@ def test_oracle_reproduces_encoder_me(meo, name):
             if k not in pyr:
                 pyr[k] = M.build_pyramid(meo, "meo", frames[k])
         res, _ = M.motion_estimate(meo, "meo", prm, pyr[poc], pyr[refs[0]], pyr[refs[1]] if lists == 2 else None, want_debug=False)
-        want = rows.view(M.PU_RESULT_DTYPE).reshape(res.shape)
+        want = M.encoder_rows(hd, rows).reshape(res.shape)
         assert M.results_diff(res, want, lists) == [], (name, poc, refs)
         n_b += lists == 2
         n_p += lists == 1

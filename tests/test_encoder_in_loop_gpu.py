@@ -31,17 +31,21 @@ def _env():
     return env
 
 
-def _encode(td, tag, yuv, w, h, n, extra):
+def _encode(td, tag, yuv, w, h, n, extra, mode=3):
     dump, obu = os.path.join(td, tag + ".medump"), os.path.join(td, tag + ".obu")
-    r = subprocess.run([ENC, yuv, str(w), str(h), str(n), "3", dump, "--bitstream", obu] + extra, env=_env(),
+    r = subprocess.run([ENC, yuv, str(w), str(h), str(n), str(mode), dump, "--bitstream", obu] + extra, env=_env(),
                        stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     return dump, open(obu, "rb").read(), r.stderr
 
 
 @pytest.mark.skipif(not os.path.exists(ENC), reason="oracle/_ref/enc_dump not built (needs /root/reference at build time)")
-@pytest.mark.parametrize("w,h,n,seed", [(416, 240, 20, 7), (352, 288, 12, 11)])
-def test_reference_encoder_with_cuda_me_is_bit_identical(pkg, tmp_path, w, h, n, seed):
+@pytest.mark.parametrize("w,h,n,seed,mode", [
+    (416, 240, 20, 7, 3), (352, 288, 12, 11, 3),
+    (256, 192, 12, 13, 2),      # enc-mode 2: reference pictures searched with 209 PUs, the others with 85 (mixed batches)
+    (192, 128, 10, 17, 0),      # enc-mode 0: 209 PUs everywhere
+])
+def test_reference_encoder_with_cuda_me_is_bit_identical(pkg, tmp_path, w, h, n, seed, mode):
     from make_encoder_golden import parse
     frames = M.synth_video(w, h, n, seed=seed, max_shift=8)
     yuv = str(tmp_path / "in.yuv")
@@ -49,9 +53,10 @@ def test_reference_encoder_with_cuda_me_is_bit_identical(pkg, tmp_path, w, h, n,
         for x in frames:
             f.write(np.ascontiguousarray(x).tobytes())
             f.write(np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes())
-    d0, bs0, _ = _encode(str(tmp_path), "stock", yuv, w, h, n, [])
-    d1, bs1, log = _encode(str(tmp_path), "cuda", yuv, w, h, n, ["--cuda-me", pkg.library_path()])
+    d0, bs0, _ = _encode(str(tmp_path), "stock", yuv, w, h, n, [], mode)
+    d1, bs1, log = _encode(str(tmp_path), "cuda", yuv, w, h, n, ["--cuda-me", pkg.library_path()], mode)
     p0, p1 = parse(d0, w, h), parse(d1, w, h)
+    assert {int(v["hdr"][18]) for v in p0.values()} == {3: {85}, 2: {85, 209}, 0: {209}}[mode]
     assert sorted(p0) == sorted(p1) and len(p0) == n - 1            # every picture but the key frame is inter
     n_sb = ((w + 63) // 64) * ((h + 63) // 64)
     for poc in sorted(p0):
