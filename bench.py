@@ -44,11 +44,14 @@ FULLPEL_BYTE_SADS_PER_SB_LIST = 64 * 64 * 64 * 32
 
 USE_16BIT = False                 # me4k: pictures arrive as 16-bit samples (10-bit), split on the device
 SHARD_SB_ROWS = False             # me4k: N ranks share every picture by SB rows (strong scaling)
+NUM_PUS = 85                      # me209: every picture searched with all 209 PUs (PIC_ALL_DEPTH_MODE, enc-mode 0)
 
 
 def select_workload(name):
     """me: BASELINE configs[1] (1080p 8-bit, one stream per GPU). me4k: configs[2] (3840x2160 10-bit, SB rows sharded)."""
-    global W, H, N_PICS, SB_PER_FRAME, USE_16BIT, SHARD_SB_ROWS
+    global W, H, N_PICS, SB_PER_FRAME, USE_16BIT, SHARD_SB_ROWS, NUM_PUS
+    if name == "me209":
+        NUM_PUS = 209
     if name == "me4k":
         W, H, N_PICS, USE_16BIT, SHARD_SB_ROWS = 3840, 2160, 33, True, True
         SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
@@ -145,6 +148,7 @@ def _cpu_task(job):
             _CPU["pyr"][i] = M.build_pyramid(lib, pre, _CPU["frames"][i])
     prm = M.default_params(M.load_oracle(), "meo", W, H, 2, tl, 3, 1 if tl < 3 else 0)
     prm.same_ref_poc = 1 if r0 == r1 else 0
+    prm.num_pus = NUM_PUS
     res, _ = M.motion_estimate(lib, pre, prm, _CPU["pyr"][poc], _CPU["pyr"][r0], _CPU["pyr"][r1], want_debug=False)
     return int(res["dist0"].sum() & 0xFFFFFFFF)
 
@@ -213,8 +217,9 @@ def workload_config(n_gpus):
                 "parallelism": f"every picture on every GPU, SB rows of each picture sharded x{n_gpus}, no collective",
                 "l2_policy": "inputs larger than L2 (33 planes = 274 MB + 8-bit pyramids per step)"}
     return {"workload": "1920x1080 8-bit luma, 121 pictures (1 intra + 120 B), hierarchical mini-GOP 8 / 4 temporal layers, "
-                        "full open-loop ME per picture: pyramid + HME L0/L1/L2 + 64x64 full-pel (85 PUs) + half/quarter-pel + bi-pred",
-            "frames_per_step_per_gpu": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": 85,
+                        f"full open-loop ME per picture: pyramid + HME L0/L1/L2 + 64x64 full-pel ({NUM_PUS} PUs) + half/quarter-pel + bi-pred"
+                        + (" [209-PU mode: every picture as an enc-mode 0 PIC_ALL_DEPTH_MODE picture]" if NUM_PUS == 209 else ""),
+            "frames_per_step_per_gpu": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": NUM_PUS,
             "streams": n_gpus, "parallelism": f"one picture stream per GPU x{n_gpus}, no collective",
             "l2_policy": "inputs larger than L2 (121 luma planes = 251 MB + 306 MB of padded pyramids per step)"}
 
@@ -270,6 +275,7 @@ def run_gpu_impl(args, rank, world, local_rank):
     for poc, tl, r0, r1 in jobs:
         p = pkg.default_params(W, H, 2, tl, 3, 1 if tl < 3 else 0)
         p.same_ref_poc = 1 if r0 == r1 else 0
+        p.num_pus = NUM_PUS
         specs.append((poc, r0, r1, p))
     sb_rows = None
     if SHARD_SB_ROWS and world > 1:
@@ -277,7 +283,7 @@ def run_gpu_impl(args, rank, world, local_rank):
         first, count = shard.sb_row_shard((H + 63) // 64, world, rank)
         sb_rows = (first, first + count)
     n_sb = ctx.n_sb if sb_rows is None else (sb_rows[1] - sb_rows[0]) * ((W + 63) // 64)
-    out = torch.empty((len(jobs), n_sb, 85, 40), dtype=torch.uint8).pin_memory()     # host me_results images
+    out = torch.empty((len(jobs), n_sb, NUM_PUS, 40), dtype=torch.uint8).pin_memory()     # host me_results images
     ptrs = [out[i].data_ptr() for i in range(len(jobs))]
     job_resident, _, _ = ctx.make_jobs(specs, out_ptrs=[None] * len(jobs), sb_rows=sb_rows)   # results stay in HBM
     # e2e: one batch per mini-GOP (8 pictures) so that uploads, searches and result copies of consecutive
@@ -386,7 +392,7 @@ def run_gpu_impl(args, rank, world, local_rank):
         traffic = None                                    # DRAM bytes per launch, scaled from the committed ncu capture
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))
-            traffic = tj["fullpel_kernel"]["dram_bytes_per_sb_list"] * n_sb * len(jobs)
+            traffic = tj["fullpel_ext_kernel" if NUM_PUS == 209 else "fullpel_kernel"]["dram_bytes_per_sb_list"] * n_sb * len(jobs)
         except Exception:
             pass
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965
@@ -408,9 +414,9 @@ def run_gpu_impl(args, rank, world, local_rank):
             "e2e": {"value": fps_e2e, "unit": "frames/s",
                     "h2d_bytes_per_step": (len(range(rank, N_PICS, world)) if replicate else N_PICS) * W * H * (2 if USE_16BIT else 1),
                     "replication": "each picture uploaded by one rank, imported by the others over NVLink (svtme_picture_upload_ipc)" if replicate else None,
-                    "d2h_bytes_per_step": len(jobs) * n_sb * 85 * 40, "ms_per_step": ms_e2e / args.steps},
+                    "d2h_bytes_per_step": len(jobs) * n_sb * NUM_PUS * 40, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
+            "roofline": {"kernel": "fullpel_ext_kernel" if NUM_PUS == 209 else "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                          "traffic_source": "dram__bytes_read+write per SB-list from profiles/r01/traffic.json (ncu --set full) x SB-lists per launch; bytes",
                          "peak_source": f"148 SM x 64 lanes/clk x 4 bytes x {sm_mhz} MHz (VABSDIFF4 issue rate, profiles/microbench)",
@@ -729,7 +735,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="me", choices=["me", "me4k", "txq"],
+    ap.add_argument("--workload", default="me", choices=["me", "me4k", "me209", "txq"],
                     help="me: 1080p motion estimation (headline, BASELINE configs[1]); me4k: 3840x2160 10-bit, SB rows sharded over "
                          "the GPUs (configs[2]); txq: transform + quantisation sweep (configs[3])")
     args = ap.parse_args()
