@@ -18,11 +18,11 @@
 // one RED.SHARED.MIN per PU class. The non-square SADs are sums of the 8x8 SADs: horizontal sums inside a band of
 // eight rows, vertical sums carried across bands in registers (this is what costs the registers: 1 CTA per SM).
 #include "me_common.cuh"
+#include <cstdlib>
 
 namespace svtme {
 namespace {
 
-constexpr int kFxThreads = 256;
 constexpr int kWinRows = 126;          // 64 search rows + 62
 constexpr int kWinPitch = 36;          // words; = 4 (mod 32): the 8 row-distinct LDS.128 of a warp are conflict-free
 constexpr int kWinWords = 4 * kWinRows * kWinPitch;
@@ -78,7 +78,9 @@ __device__ __forceinline__ int lane_pu(int table, int lane) {
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
+// kFxThreads x CTAs per SM = 256 threads per SM either way (255 registers): 256 x 1 or 128 x 2
+template <int kFxThreads>
+__global__ void __launch_bounds__(kFxThreads, 256 / kFxThreads) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* win = smem;
     uint32_t* src = win + kWinWords;
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     // ---- stage source (even rows), the slot tables and the four byte-shifted window copies (as in fullpel.cu)
     for (int t = tid; t < kSrcWords; t += kFxThreads)
         src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
-    if (tid < kKeyWords) keys[tid] = 0xFFFFFFFFu;
+    for (int t = tid; t < kKeyWords; t += kFxThreads) keys[t] = 0xFFFFFFFFu;
     for (int t = tid; t < kNumTables * 32; t += kFxThreads) lane_slot[t >> 5][t & 31] = keys_addr + 4u * (uint32_t)lane_pu(t >> 5, t & 31);
     {
         const int wrows = sah + 62;
@@ -389,44 +391,66 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     __syncthreads();
 
     // ---- quirk Q11: replay the sequential update rule of 32x16 PU #5 over the positions in raster order.
-    // best strictly decreases (T <= S), so inside a chunk of 32 positions only lanes with S < best can fire: take the
-    // first, lower best to its T, re-test the lanes after it.
-    if (tid < 32) {
-        uint32_t best = 0xFFFFFFFFu, best_pos = 0;
-        for (int y = 0; y < sah; y++)
-            for (int xc = 0; xc < saw; xc += 32) {
-                const int x = xc + lane;
-                const bool in = x < saw;
-                const uint32_t S = in ? q11_s[(y << 6) | x] : 0xFFFFFFFFu;
-                const uint32_t T = in ? (uint32_t)q11_t[(y << 6) | x] : 0u;
-                uint32_t mask = __ballot_sync(0xffffffffu, S < best);
-                while (mask) {
-                    const int first = __ffs(mask) - 1;
-                    best = __shfl_sync(0xffffffffu, T, first);
-                    best_pos = (uint32_t)((y << 6) | (xc + first));
-                    mask = __ballot_sync(0xffffffffu, S < best) & ~((2u << first) - 1u);
-                }
+    // `best` strictly decreases (T <= S), so the rule is a short chain of queries "first position after n whose S is
+    // below best": every thread keeps its share of the S table in registers and the CTA answers one query per step
+    // (a handful of steps: S covers four times the area of T, so it rarely drops below an earlier T).
+    {
+        constexpr int kPer = 4096 / kFxThreads;
+        uint32_t S[kPer];
+#pragma unroll
+        for (int i = 0; i < kPer; i++) {
+            const int n = tid + kFxThreads * i;                       // raster index (row << 6 | col)
+            S[i] = ((n & 63) < saw && (n >> 6) < sah) ? q11_s[n] : 0xFFFFFFFFu;
+        }
+        uint32_t* red = keys + kMaxPu;                                // three spare words of the key table
+        uint32_t best = 0xFFFFFFFFu;
+        int cur = -1;
+        for (;;) {
+            uint32_t cand = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = kPer - 1; i >= 0; i--) {
+                const int n = tid + kFxThreads * i;
+                if (n > cur && S[i] < best) cand = (uint32_t)n;
             }
-        if (lane == 0) keys[87 + 5] = (best << 12) | best_pos;
+            cand = __reduce_min_sync(0xffffffffu, cand);
+            if (tid == 0) red[0] = 0xFFFFFFFFu;
+            __syncthreads();
+            if (lane == 0 && cand != 0xFFFFFFFFu) atomicMin(&red[0], cand);
+            __syncthreads();
+            const uint32_t first = red[0];
+            __syncthreads();
+            if (first == 0xFFFFFFFFu) break;
+            cur = (int)first; best = q11_t[first];
+        }
+        if (tid == 0) {
+            scx.best_sad[list][87 + 5 - kNumPu] = best << 1;
+            scx.best_mv[list][87 + 5 - kNumPu] = make_mv((int16_t)((sax + (cur & 63)) * 4), (int16_t)((say + (cur >> 6)) * 4));
+        }
     }
-    __syncthreads();
 
     // ---- decode the winning keys into p_sb_best_sad / p_sb_best_mv form (internal index = slot)
-    if (tid < kMaxPu) {
-        const uint32_t key = keys[tid];
+    for (int t = tid; t < kMaxPu; t += kFxThreads) {
+        if (t == 87 + 5) continue;
+        const uint32_t key = keys[t];
         const uint32_t v = key >> 12; const int y = (key >> 6) & 63, x = key & 63;
         const uint32_t sad = v << 1, mv = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
-        if (tid < kNumPu) { scr.best_sad[list][tid] = sad; scr.best_mv[list][tid] = mv; }
-        else { scx.best_sad[list][tid - kNumPu] = sad; scx.best_mv[list][tid - kNumPu] = mv; }
+        if (t < kNumPu) { scr.best_sad[list][t] = sad; scr.best_mv[list][t] = mv; }
+        else { scx.best_sad[list][t - kNumPu] = sad; scx.best_mv[list][t - kNumPu] = mv; }
     }
 }
 
+static int g_fx_threads = 256;
+
 cudaError_t configure_fullpel_ext() {
-    return cudaFuncSetAttribute(fullpel_ext_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
+    if (const char* e = getenv("SVTME_FX_THREADS")) g_fx_threads = atoi(e) == 128 ? 128 : 256;    // tuning knob
+    cudaError_t rc = cudaFuncSetAttribute(fullpel_ext_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
+    if (rc != cudaSuccess) return rc;
+    return cudaFuncSetAttribute(fullpel_ext_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
 }
 
 void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
-    fullpel_ext_kernel<<<dim3(max_sb, n_jobs), kFxThreads, kFxSmemBytes, st>>>(d_jobs, list);
+    if (g_fx_threads == 128) fullpel_ext_kernel<128><<<dim3(max_sb, n_jobs), 128, kFxSmemBytes, st>>>(d_jobs, list);
+    else                     fullpel_ext_kernel<256><<<dim3(max_sb, n_jobs), 256, kFxSmemBytes, st>>>(d_jobs, list);
 }
 
 }  // namespace svtme
