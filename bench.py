@@ -293,9 +293,12 @@ def run_gpu_impl(args, rank, world, local_rank):
     stride = W
     e2e_count = [0]
 
+    dev_ptrs = [dev[i].data_ptr() for i in range(N_PICS)]
+
     def step_resident():
-        for i in range(N_PICS):
-            ctx.upload_device(i, dev[i].data_ptr(), stride)
+        # the pyramids of the whole sequence in one launch (svtme_pictures_upload_device; <= 128 pictures per call)
+        for i0 in range(0, N_PICS, 128):
+            ctx.upload_device_batch(list(range(i0, min(i0 + 128, N_PICS))), dev_ptrs[i0:i0 + 128], stride)
         ctx.motion_estimate_async(job_resident)
 
     # Optional: one rank uploads each picture and the others import it over NVLink (svtme_picture_upload_ipc). Off by default:
@@ -421,8 +424,10 @@ def run_gpu_impl(args, rank, world, local_rank):
                          "traffic_source": "dram__bytes_read+write per SB-list from profiles/r01/traffic.json (ncu --set full) x SB-lists per launch; bytes",
                          "peak_source": f"148 SM x 64 lanes/clk x 4 bytes x {sm_mhz} MHz (VABSDIFF4 issue rate, profiles/microbench)",
                          "launch_ms": fp_ms / fp_n if fp_n else None, "share_of_kernel_time": fp_ms / total_kernel_ms if total_kernel_ms else None},
-            "roofline_hbm": {"kernel": "pyramid_kernel", "bound": "hbm", "achieved": (pyr_bytes / (py_ms / py_n / 1e3) / 1e9) if py_n else None,
-                             "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes / (py_ms / py_n / 1e3) / 1e9 / hbm_peak) if py_n else None,
+            # one launch builds the pyramids of the whole sequence: bytes of all N_PICS pictures over the launches' time
+            "roofline_hbm": {"kernel": "pyramid_batch_kernel", "bound": "hbm", "pictures_per_launch": N_PICS * args.steps / py_n if py_n else None,
+                             "achieved": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9) if py_n else None,
+                             "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9 / hbm_peak) if py_n else None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
             "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
             "kernel_launches_per_step": {k: v[1] / args.steps for k, v in kt.items()},

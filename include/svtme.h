@@ -144,6 +144,10 @@ int32_t svtme_synchronize_uploads(SvtMeContext *ctx);
 int32_t svtme_picture_upload_ipc(SvtMeContext *ctx, int32_t slot, const SvtMeIpcSlot *src);
 /* Same, from a luma plane that already lives in device memory (no H2D copy). */
 int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8_t *d_luma, int32_t stride);
+/* A batch of pictures (n <= SVTME_MAX_BATCH) that already live in device memory, all with the same row stride: ONE
+ * pyramid launch for all of them (a 1080p picture is about a microsecond of HBM time; per-picture launches are
+ * launch-latency bound). slots[i] receives d_lumas[i]. */
+int32_t svtme_pictures_upload_device(SvtMeContext *ctx, int32_t n, const int32_t *slots, const uint8_t *const *d_lumas, int32_t stride);
 /* Read one padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) as tightly packed rows of
  * (width>>level + 2*pad) bytes; *out_stride / *out_rows receive its geometry. Synchronous. */
 int32_t svtme_picture_download(SvtMeContext *ctx, int32_t slot, int32_t level, uint8_t *dst, size_t dst_bytes,

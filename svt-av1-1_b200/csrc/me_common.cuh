@@ -142,7 +142,14 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
     return v;
 }
 
+// Pictures of one batched pyramid launch: source luma and slot base pointer per picture
+struct PyramidBatch {
+    const uint8_t* luma[SVTME_MAX_BATCH];
+    uint8_t* base[SVTME_MAX_BATCH];
+};
+
 // host-side launchers (one per .cu)
+void launch_pyramid_batch(const PyramidBatch& batch, int n, int luma_stride, const DPyramid& geom, const uint8_t* geom_base, cudaStream_t st);
 void launch_pyramid(const uint8_t* d_luma, int luma_stride, const DPyramid& pyr, cudaStream_t st);
 void launch_unpack16(const uint16_t* d_in, int in_stride, uint8_t* d_msb, uint8_t* d_rem, int width, int height, cudaStream_t st);
 void launch_hme(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);

@@ -10,6 +10,25 @@
 
 namespace svtme {
 
+// Four consecutive output bytes x0 .. x0+3 of a padded plane row: source bytes clamp(x) << shift of `srow`.
+// Interior words of an aligned source row come from ONE vector load (4, 8 or 16 source bytes) and a byte permute;
+// the words that touch the replicated border take the byte path.
+__device__ __forceinline__ uint32_t gather_word(const uint8_t* srow, int x0, int w, int shift, bool aligned) {
+    if (aligned && x0 >= 0 && x0 + 3 < w) {
+        if (shift == 0) return __ldg(reinterpret_cast<const uint32_t*>(srow + x0));
+        if (shift == 1) {
+            const uint2 v = __ldg(reinterpret_cast<const uint2*>(srow + 2 * x0));
+            return __byte_perm(v.x, v.y, 0x6420);
+        }
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(srow + 4 * x0));
+        return __byte_perm(__byte_perm(v.x, v.y, 0x0040), __byte_perm(v.z, v.w, 0x0040), 0x5410);
+    }
+    uint32_t v = 0;
+#pragma unroll
+    for (int b = 0; b < 4; b++) v |= (uint32_t)__ldg(srow + (min(max(x0 + b, 0), w - 1) << shift)) << (8 * b);
+    return v;
+}
+
 __global__ void __launch_bounds__(256) pyramid_kernel(const uint8_t* __restrict__ luma, int luma_stride,
                                                       DPyramid pyr) {
     const DPlane pl = blockIdx.z == 0 ? pyr.full : blockIdx.z == 1 ? pyr.quarter : pyr.sixteenth;
@@ -18,17 +37,38 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const uint8_t* __restrict_
     const int words = (pl.w + 2 * pl.ox + 3) >> 2;      // row pitch has slack for the last partial word
     const int wx = blockIdx.x * blockDim.x + threadIdx.x;
     if (wx >= words) return;
+    // pad (68 / 32 / 16) and the picture width are multiples of 4, so x0 << shift is 4 / 8 / 16-byte aligned inside a row
+    const bool aligned = (((uintptr_t)luma | (uintptr_t)luma_stride) & 15) == 0 && (pl.ox & 3) == 0;
     for (int y = blockIdx.y; y < rows; y += gridDim.y) {
         const int sy = min(max(y - pl.oy, 0), pl.h - 1) << shift;
-        const uint8_t* srow = luma + (size_t)sy * luma_stride;
-        uint32_t v = 0;
-#pragma unroll
-        for (int b = 0; b < 4; b++) {
-            const int sx = min(max(wx * 4 + b - pl.ox, 0), pl.w - 1) << shift;
-            v |= (uint32_t)__ldg(srow + sx) << (8 * b);
-        }
-        *reinterpret_cast<uint32_t*>(pl.buf + (size_t)y * pl.stride + wx * 4) = v;
+        *reinterpret_cast<uint32_t*>(pl.buf + (size_t)y * pl.stride + wx * 4) = gather_word(luma + (size_t)sy * luma_stride, wx * 4 - pl.ox, pl.w, shift, aligned);
     }
+}
+
+// The same for a batch of pictures of one context in ONE launch (blockIdx.z = 3 * picture + level): a single picture is
+// 5.4 MB at 1080p, i.e. about one microsecond of HBM time -- per-picture launches are launch-latency bound.
+// All slots of a context share the plane geometry; only the base pointers differ.
+__global__ void __launch_bounds__(256) pyramid_batch_kernel(PyramidBatch batch, int luma_stride, DPyramid geom, const uint8_t* geom_base) {
+    const int pic = blockIdx.z / 3, shift = blockIdx.z % 3;
+    DPlane pl = shift == 0 ? geom.full : shift == 1 ? geom.quarter : geom.sixteenth;
+    pl.buf = batch.base[pic] + (pl.buf - geom_base);
+    const uint8_t* luma = batch.luma[pic];
+    const int rows = pl.h + 2 * pl.oy;
+    const int words = (pl.w + 2 * pl.ox + 3) >> 2;
+    const int wx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (wx >= words) return;
+    // pad (68 / 32 / 16) and the picture width are multiples of 4, so x0 << shift is 4 / 8 / 16-byte aligned inside a row
+    const bool aligned = (((uintptr_t)luma | (uintptr_t)luma_stride) & 15) == 0 && (pl.ox & 3) == 0;
+    for (int y = blockIdx.y; y < rows; y += gridDim.y) {
+        const int sy = min(max(y - pl.oy, 0), pl.h - 1) << shift;
+        *reinterpret_cast<uint32_t*>(pl.buf + (size_t)y * pl.stride + wx * 4) = gather_word(luma + (size_t)sy * luma_stride, wx * 4 - pl.ox, pl.w, shift, aligned);
+    }
+}
+
+void launch_pyramid_batch(const PyramidBatch& batch, int n, int luma_stride, const DPyramid& geom, const uint8_t* geom_base, cudaStream_t st) {
+    const int words = (geom.full.w + 2 * geom.full.ox + 3) >> 2;
+    dim3 grid((words + 255) / 256, 37, 3 * n);
+    pyramid_batch_kernel<<<grid, 256, 0, st>>>(batch, luma_stride, geom, geom_base);
 }
 
 // 10-bit input split (UnPack2D -> EB_ENC_msbUnPack2D, C_DEFAULT/EbPackUnPack_C.c:127-151): msb = sample >> 2 (the plane ME

@@ -80,6 +80,26 @@ def test_pyramid_strided_and_device_upload(pkg, meo):
         assert np.array_equal(x, z) and np.array_equal(y, z)
 
 
+def test_batched_device_upload(pkg, meo):
+    """svtme_pictures_upload_device: one pyramid launch for many pictures gives the planes of the per-picture calls."""
+    import torch
+    w, h = 416, 240
+    fr = M.synth_video(w, h, 5, seed=77)
+    wide = np.zeros((5, h, w + 24), dtype=np.uint8)
+    wide[:, :, :w] = np.stack(fr)
+    d = torch.from_numpy(wide).cuda()
+    torch.cuda.synchronize()
+    ctx = pkg.MeContext(w, h, 6)
+    ctx.upload_device_batch([4, 0, 2, 5, 1], [d[i].data_ptr() for i in range(5)], d.stride(1))
+    for slot, i in zip([4, 0, 2, 5, 1], range(5)):
+        want = M.build_pyramid(meo, "meo", fr[i])
+        for lvl, x in enumerate(want.planes):
+            assert np.array_equal(ctx.download_plane(slot, lvl), x), (slot, lvl)
+    with pytest.raises(pkg.SvtMeError, match="0x80001005"):
+        ctx.upload_device_batch([0, 9], [d[0].data_ptr(), d[1].data_ptr()], d.stride(1))
+    ctx.close()
+
+
 @pytest.mark.parametrize("name", M.golden_cases())
 def test_cuda_matches_reference_golden(pkg, name):
     """CUDA path against vectors produced by the unmodified reference objects."""
