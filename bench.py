@@ -45,11 +45,14 @@ FULLPEL_BYTE_SADS_PER_SB_LIST = 64 * 64 * 64 * 32
 USE_16BIT = False                 # me4k: pictures arrive as 16-bit samples (10-bit), split on the device
 SHARD_SB_ROWS = False             # me4k: N ranks share every picture by SB rows (strong scaling)
 NUM_PUS = 85                      # me209: every picture searched with all 209 PUs (PIC_ALL_DEPTH_MODE, enc-mode 0)
+WITH_TXQ = False                  # streams: every frame also gets its luma residual plane transformed + quantised
 
 
 def select_workload(name):
     """me: BASELINE configs[1] (1080p 8-bit, one stream per GPU). me4k: configs[2] (3840x2160 10-bit, SB rows sharded)."""
-    global W, H, N_PICS, SB_PER_FRAME, USE_16BIT, SHARD_SB_ROWS, NUM_PUS
+    global W, H, N_PICS, SB_PER_FRAME, USE_16BIT, SHARD_SB_ROWS, NUM_PUS, WITH_TXQ
+    if name == "streams":
+        WITH_TXQ = True
     if name == "me209":
         NUM_PUS = 209
     if name == "me4k":
@@ -197,8 +200,24 @@ def run_reference_impl(args, rank):
     total = sum(times)
     fps = n_tasks * args.steps / total
     sample = f"{n_tasks} pictures per step drawn from the first two mini-GOPs of the 1080p sequence, one picture per task over {arm.cores} worker processes"
+    if WITH_TXQ:                                           # streams: the same cores then transform + quantise one residual plane per frame
+        tarm = TxqCpuArm()
+        q10c = txq_quant_params()
+        sizes = [(w_, h_, 0) for (w_, h_) in TXQ_SIZES]
+        tarm.run(sizes[0], q10c, tarm.cores)
+        t0, pix = time.perf_counter(), 0
+        for _ in range(args.steps):
+            for c in sizes:
+                tarm.run(c, q10c, tarm.cores)
+                pix += tarm.cores * TXQ_CPU_REPS * 128 * TXQ_W
+        dt = time.perf_counter() - t0
+        tarm.close()
+        txq_fps = pix / dt / (TXQ_W * TXQ_H)
+        fps = 1.0 / (1.0 / fps + 1.0 / txq_fps)
+        total = n_tasks * args.steps / fps
+        sample += f"; plus {len(sizes)} transform sizes x {tarm.cores} x {TXQ_CPU_REPS} strips of 1920x128 residual per step ({txq_fps:.0f} planes/s); frame time = ME time + transform time"
     line = {
-        "impl": "reference", "metric": "2160p_me_frames_per_sec" if SHARD_SB_ROWS else "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": "2160p_me_frames_per_sec" if SHARD_SB_ROWS else "1080p_stream_frames_per_sec" if WITH_TXQ else "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True,
         "scaling": "strong" if SHARD_SB_ROWS else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(args.gpus),
@@ -218,7 +237,9 @@ def workload_config(n_gpus):
                 "l2_policy": "inputs larger than L2 (33 planes = 274 MB + 8-bit pyramids per step)"}
     return {"workload": "1920x1080 8-bit luma, 121 pictures (1 intra + 120 B), hierarchical mini-GOP 8 / 4 temporal layers, "
                         f"full open-loop ME per picture: pyramid + HME L0/L1/L2 + 64x64 full-pel ({NUM_PUS} PUs) + half/quarter-pel + bi-pred"
-                        + (" [209-PU mode: every picture as an enc-mode 0 PIC_ALL_DEPTH_MODE picture]" if NUM_PUS == 209 else ""),
+                        + (" [209-PU mode: every picture as an enc-mode 0 PIC_ALL_DEPTH_MODE picture]" if NUM_PUS == 209 else "")
+                        + (" + forward transform and quantisation of one 1920x1088 luma residual plane per frame (the 19 DCT_DCT sizes in turn, "
+                           "8 planes per launch) on a second stream of the same GPU [BASELINE configs[4]: one such stream per GPU]" if WITH_TXQ else ""),
             "frames_per_step_per_gpu": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": NUM_PUS,
             "streams": n_gpus, "parallelism": f"one picture stream per GPU x{n_gpus}, no collective",
             "l2_policy": "inputs larger than L2 (121 luma planes = 251 MB + 306 MB of padded pyramids per step)"}
@@ -257,6 +278,22 @@ def run_gpu_impl(args, rank, world, local_rank):
         arm.close()
         cpu = {"value": n_tasks / t, "unit": "frames/s", "cores": arm.cores, "kind": arm.kind,
                "sample": f"{n_tasks} pictures of the first two mini-GOPs, {arm.cores} worker processes, {t:.1f} s wall"}
+        if WITH_TXQ:                                       # the same cores then transform + quantise: time per frame adds up
+            tarm = TxqCpuArm()
+            q10c = txq_quant_params()
+            sizes = [(w_, h_, 0) for (w_, h_) in TXQ_SIZES]
+            tarm.run(sizes[0], q10c, tarm.cores)
+            t0 = time.perf_counter()
+            pix = 0
+            for c in sizes:
+                tarm.run(c, q10c, 2 * tarm.cores)
+                pix += 2 * tarm.cores * TXQ_CPU_REPS * 128 * TXQ_W
+            dt = time.perf_counter() - t0
+            tarm.close()
+            txq_fps = pix / dt / (TXQ_W * TXQ_H)
+            cpu["me_frames_per_sec"], cpu["txq_frames_per_sec"] = cpu["value"], txq_fps
+            cpu["value"] = 1.0 / (1.0 / cpu["value"] + 1.0 / txq_fps)
+            cpu["sample"] += f"; then {len(sizes)} transform sizes x {2 * tarm.cores} x {TXQ_CPU_REPS} strips of 1920x128 residual, {dt:.1f} s wall"
 
     torch.cuda.set_device(local_rank)
     frames = synth_sequence(N_PICS, seed=1 if SHARD_SB_ROWS else 1 + rank)   # row sharding: every rank sees the same pictures
@@ -292,14 +329,64 @@ def run_gpu_impl(args, rank, world, local_rank):
                     for g in range(0, len(jobs), 8)] for o in (0, N_PICS)]
     stride = W
     e2e_count = [0]
+    txq = None
+    if WITH_TXQ:
+        # second kernel family on its own stream of the same GPU: 120 residual planes per step, 8 stacked planes per launch
+        tq = {"ctx": pkg.TxqContext(local_rank), "quant": pkg.SvtTxqQuant.from_q10(txq_quant_params()),
+              "sizes": [(w_, h_, 0) for (w_, h_) in TXQ_SIZES], "n": 0}
+        res = txq_residual(11 + rank, TXQ_PLANES)
+        tq["host"] = torch.from_numpy(res).pin_memory()
+        tq["dev"] = tq["host"].cuda()
+        npix = TXQ_PLANES * TXQ_H * TXQ_W
+        tq["d_out"] = [torch.empty(npix, dtype=torch.int32, device="cuda") for _ in range(3)]
+        tq["d_eob"] = torch.empty(npix // 16, dtype=torch.int16, device="cuda")
+        tq["h_out"] = [torch.empty(npix, dtype=torch.int32).pin_memory() for _ in range(2)]
+        tq["h_eob"] = torch.empty(npix // 16, dtype=torch.int16).pin_memory()
+        tq["st"] = torch.cuda.ExternalStream(tq["ctx"].stream())
+        tq["me_st"] = torch.cuda.ExternalStream(ctx.stream)
+        tq["launches_per_step"] = (N_PICS - 1) // TXQ_PLANES
+        txq = tq
+
+    def txq_mark():
+        a = torch.cuda.Event()
+        a.record(txq["me_st"])
+        return a
+
+    def txq_step_resident(a):
+        """15 launches x 8 planes on the transform stream, overlapping this step's searches: they start at the ME stream's
+        position `a` (taken before the searches were enqueued) and the ME stream waits for them at the end of the step."""
+        txq["st"].wait_event(a)
+        for _ in range(txq["launches_per_step"]):
+            c = txq["sizes"][txq["n"] % len(txq["sizes"])]
+            txq["n"] += 1
+            txq["ctx"].fwd_txfm_quant_device(txq["dev"].data_ptr(), TXQ_W, TXQ_W, TXQ_PLANES * TXQ_H, c[0], c[1], c[2], txq["quant"],
+                                             txq["d_out"][0].data_ptr(), txq["d_out"][1].data_ptr(), txq["d_out"][2].data_ptr(),
+                                             txq["d_eob"].data_ptr(), None)
+        b = torch.cuda.Event()
+        b.record(txq["st"])
+        txq["me_st"].wait_event(b)
+
+    def txq_step_e2e():
+        """The same through host buffers: residual planes H2D, quantised + dequantised coefficients and eob D2H (the subset EncDec
+        consumes), synchronous calls on this thread while the ME batches run asynchronously."""
+        for _ in range(txq["launches_per_step"]):
+            c = txq["sizes"][txq["n"] % len(txq["sizes"])]
+            txq["n"] += 1
+            rc = txq["ctx"].lib.svttxq_fwd_txfm_quant(txq["ctx"]._h, txq["host"].data_ptr(), TXQ_W, TXQ_W, TXQ_PLANES * TXQ_H, c[0], c[1], c[2],
+                                                      C.byref(txq["quant"]), None, txq["h_out"][0].data_ptr(), txq["h_out"][1].data_ptr(),
+                                                      txq["h_eob"].data_ptr(), None)
+            assert rc == 0
 
     dev_ptrs = [dev[i].data_ptr() for i in range(N_PICS)]
 
     def step_resident():
+        mark = txq_mark() if txq else None
         # the pyramids of the whole sequence in one launch (svtme_pictures_upload_device; <= 128 pictures per call)
         for i0 in range(0, N_PICS, 128):
             ctx.upload_device_batch(list(range(i0, min(i0 + 128, N_PICS))), dev_ptrs[i0:i0 + 128], stride)
         ctx.motion_estimate_async(job_resident)
+        if txq:
+            txq_step_resident(mark)
 
     # Optional: one rank uploads each picture and the others import it over NVLink (svtme_picture_upload_ipc). Off by default:
     # on this box every GPU has its own host link, and the per-step hand-shakes cost more than the saved H2D bytes
@@ -337,6 +424,8 @@ def run_gpu_impl(args, rank, world, local_rank):
                     ctx.upload_ptr(base + i, host[i].data_ptr(), stride)
         for jb in gop_batches[which]:
             ctx.motion_estimate_async(jb)
+        if txq:
+            txq_step_e2e()
 
     def barrier():
         ctx.synchronize()
@@ -370,8 +459,10 @@ def run_gpu_impl(args, rank, world, local_rank):
     ctx.set_profiling(True)
     ctx.kernel_times(reset=True)
     l0 = ctx.kernel_launches
+    tl0 = txq["ctx"].kernel_launches() if txq else 0
     ms = timed(step_resident, args.steps)
     launches = ctx.kernel_launches - l0
+    txq_resident_launches = (txq["ctx"].kernel_launches() - tl0) if txq else 0
     kt = ctx.kernel_times(reset=True)
     ctx.set_profiling(False)
     clocks = sampler.stop() if sampler else None
@@ -407,18 +498,25 @@ def run_gpu_impl(args, rank, world, local_rank):
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         py_ms, py_n = kt["pyramid"]
+        txq_h2d = txq_d2h = txq_launches = 0
+        if txq:                                           # per step: 15 launches of 8 planes; e2e moves the residual in and qcoeff/dqcoeff/eob out
+            plane_px = TXQ_PLANES * TXQ_H * TXQ_W
+            txq_h2d = txq["launches_per_step"] * 2 * plane_px
+            txq_d2h = sum(txq["launches_per_step"] * (8 * (plane_px // (w_ * h_)) * min(w_, 32) * min(h_, 32) + 2 * (plane_px // (w_ * h_)))
+                          for (w_, h_, _) in txq["sizes"]) // len(txq["sizes"])
+            txq_launches = txq_resident_launches
         pyr_bytes = W * H + sum(((W >> s) + 2 * p) * ((H >> s) + 2 * p) for s, p in ((0, 68), (1, 32), (2, 16)))
         line = {
-            "metric": "2160p_me_frames_per_sec" if SHARD_SB_ROWS else "1080p_me_frames_per_sec", "value": fps, "unit": "frames/s",
-            "n_gpus": world, "steps": args.steps,
+            "metric": "2160p_me_frames_per_sec" if SHARD_SB_ROWS else "1080p_stream_frames_per_sec" if WITH_TXQ else "1080p_me_frames_per_sec",
+            "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if SHARD_SB_ROWS else "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(world),
             "sb_per_sec": fps * SB_PER_FRAME,
             "e2e": {"value": fps_e2e, "unit": "frames/s",
-                    "h2d_bytes_per_step": (len(range(rank, N_PICS, world)) if replicate else N_PICS) * W * H * (2 if USE_16BIT else 1),
+                    "h2d_bytes_per_step": (len(range(rank, N_PICS, world)) if replicate else N_PICS) * W * H * (2 if USE_16BIT else 1) + txq_h2d,
                     "replication": "each picture uploaded by one rank, imported by the others over NVLink (svtme_picture_upload_ipc)" if replicate else None,
-                    "d2h_bytes_per_step": len(jobs) * n_sb * NUM_PUS * 40, "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": int(launches),
+                    "d2h_bytes_per_step": len(jobs) * n_sb * NUM_PUS * 40 + txq_d2h, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches) + txq_launches,
             "roofline": {"kernel": "fullpel_ext_kernel" if NUM_PUS == 209 else "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                          "traffic_source": "dram__bytes_read+write per SB-list from profiles/r01/traffic.json (ncu --set full) x SB-lists per launch; bytes",
@@ -740,7 +838,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="me", choices=["me", "me4k", "me209", "txq"],
+    ap.add_argument("--workload", default="me", choices=["me", "me4k", "me209", "streams", "txq"],
                     help="me: 1080p motion estimation (headline, BASELINE configs[1]); me4k: 3840x2160 10-bit, SB rows sharded over "
                          "the GPUs (configs[2]); txq: transform + quantisation sweep (configs[3])")
     args = ap.parse_args()
