@@ -80,7 +80,7 @@ __device__ __forceinline__ int lane_pu(int table, int lane) {
 
 // kFxThreads x CTAs per SM = 256 threads per SM either way (255 registers): 256 x 1 or 128 x 2
 template <int kFxThreads>
-__global__ void __launch_bounds__(kFxThreads, 256 / kFxThreads) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
+__global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxThreads) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* win = smem;
     uint32_t* src = win + kWinWords;
@@ -442,14 +442,17 @@ __global__ void __launch_bounds__(kFxThreads, 256 / kFxThreads) fullpel_ext_kern
 static int g_fx_threads = 256;
 
 cudaError_t configure_fullpel_ext() {
-    if (const char* e = getenv("SVTME_FX_THREADS")) g_fx_threads = atoi(e) == 128 ? 128 : 256;    // tuning knob
+    if (const char* e = getenv("SVTME_FX_THREADS")) { const int t = atoi(e); g_fx_threads = (t == 128 || t == 512) ? t : 256; }   // tuning knob
     cudaError_t rc = cudaFuncSetAttribute(fullpel_ext_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
+    if (rc != cudaSuccess) return rc;
+    rc = cudaFuncSetAttribute(fullpel_ext_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
     if (rc != cudaSuccess) return rc;
     return cudaFuncSetAttribute(fullpel_ext_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
 }
 
 void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
     if (g_fx_threads == 128) fullpel_ext_kernel<128><<<dim3(max_sb, n_jobs), 128, kFxSmemBytes, st>>>(d_jobs, list);
+    else if (g_fx_threads == 512) fullpel_ext_kernel<512><<<dim3(max_sb, n_jobs), 512, kFxSmemBytes, st>>>(d_jobs, list);
     else                     fullpel_ext_kernel<256><<<dim3(max_sb, n_jobs), 256, kFxSmemBytes, st>>>(d_jobs, list);
 }
 
