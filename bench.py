@@ -323,10 +323,11 @@ def run_gpu_impl(args, rank, world, local_rank):
     out = torch.empty((len(jobs), n_sb, NUM_PUS, 40), dtype=torch.uint8).pin_memory()     # host me_results images
     ptrs = [out[i].data_ptr() for i in range(len(jobs))]
     job_resident, _, _ = ctx.make_jobs(specs, out_ptrs=[None] * len(jobs), sb_rows=sb_rows)   # results stay in HBM
-    # e2e: one batch per mini-GOP (8 pictures) so that uploads, searches and result copies of consecutive
-    # batches overlap on the context's three streams
-    gop_batches = [[ctx.make_jobs([(c + o, r0 + o, r1 + o, p) for (c, r0, r1, p) in specs[g:g + 8]], out_ptrs=ptrs[g:g + 8], sb_rows=sb_rows)[0]
-                    for g in range(0, len(jobs), 8)] for o in (0, N_PICS)]
+    # e2e: one batch per few mini-GOPs so that uploads, searches and result copies of consecutive batches overlap on the
+    # context's three streams
+    EB = 8 * int(os.environ.get("SVTME_BENCH_E2E_GOPS", "1"))     # pictures per e2e batch: whole mini-GOPs (measured: 1, 3, 5 mini-GOPs per batch give 39.5, 40.1, 39.2 ms per step)
+    gop_batches = [[ctx.make_jobs([(c + o, r0 + o, r1 + o, p) for (c, r0, r1, p) in specs[g:g + EB]], out_ptrs=ptrs[g:g + EB], sb_rows=sb_rows)[0]
+                    for g in range(0, len(jobs), EB)] for o in (0, N_PICS)]
     stride = W
     e2e_count = [0]
     txq = None
@@ -378,6 +379,7 @@ def run_gpu_impl(args, rank, world, local_rank):
             assert rc == 0
 
     dev_ptrs = [dev[i].data_ptr() for i in range(N_PICS)]
+    host_ptrs = [host[i].data_ptr() for i in range(N_PICS)]
 
     def step_resident():
         mark = txq_mark() if txq else None
@@ -416,12 +418,15 @@ def run_gpu_impl(args, rank, world, local_rank):
         if replicate:
             step_e2e_replicated(base)
         else:
-            for i in range(N_PICS):
-                if USE_16BIT:
+            if USE_16BIT:
+                for i in range(N_PICS):
                     rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, base + i, host[i].data_ptr(), stride, None)
                     assert rc == 0
-                else:
-                    ctx.upload_ptr(base + i, host[i].data_ptr(), stride)
+            else:
+                # pictures arrive a few mini-GOPs at a time (picture 0 with the first group): their copies + one pyramid launch
+                for g in range(0, N_PICS - 1, EB):
+                    pics = list(range(0 if g == 0 else g + 1, min(g + EB, N_PICS - 1) + 1))
+                    ctx.upload_ptr_batch([base + i for i in pics], [host_ptrs[i] for i in pics], stride)
         for jb in gop_batches[which]:
             ctx.motion_estimate_async(jb)
         if txq:

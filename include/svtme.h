@@ -144,6 +144,9 @@ int32_t svtme_synchronize_uploads(SvtMeContext *ctx);
 int32_t svtme_picture_upload_ipc(SvtMeContext *ctx, int32_t slot, const SvtMeIpcSlot *src);
 /* Same, from a luma plane that already lives in device memory (no H2D copy). */
 int32_t svtme_picture_upload_device(SvtMeContext *ctx, int32_t slot, const uint8_t *d_luma, int32_t stride);
+/* A batch of host pictures (n <= SVTME_MAX_BATCH, same row stride): n host-to-device copies followed by ONE pyramid launch
+ * for all of them (e.g. the pictures of a mini-GOP as the look-ahead releases them). Asynchronous like svtme_picture_upload. */
+int32_t svtme_pictures_upload(SvtMeContext *ctx, int32_t n, const int32_t *slots, const uint8_t *const *lumas, int32_t stride);
 /* A batch of pictures (n <= SVTME_MAX_BATCH) that already live in device memory, all with the same row stride: ONE
  * pyramid launch for all of them (a 1080p picture is about a microsecond of HBM time; per-picture launches are
  * launch-latency bound). slots[i] receives d_lumas[i]. */

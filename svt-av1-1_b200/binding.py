@@ -14,7 +14,7 @@ EXPORTED_SYMBOLS = (
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
     "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
-    "svtme_pictures_upload_device",
+    "svtme_pictures_upload_device", "svtme_pictures_upload",
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
                         "svtme_lcu_motion_estimate", "svtme_lcu_session_stats")
@@ -97,6 +97,8 @@ def load_library():
     lib.svtme_picture_upload_ipc.argtypes = [C.c_void_p, C.c_int32, C.POINTER(SvtMeIpcSlot)]
     lib.svtme_picture_upload_device.restype = C.c_int32
     lib.svtme_picture_upload_device.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32]
+    lib.svtme_pictures_upload.restype = C.c_int32
+    lib.svtme_pictures_upload.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.c_int32]
     lib.svtme_pictures_upload_device.restype = C.c_int32
     lib.svtme_pictures_upload_device.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_void_p), C.c_int32]
     lib.svtme_picture_download.restype = C.c_int32
@@ -208,6 +210,12 @@ class MeContext:
 
     def upload_device(self, slot, dev_ptr, stride):
         self._check(self.lib.svtme_picture_upload_device(self._h, slot, dev_ptr, stride), "svtme_picture_upload_device")
+
+    def upload_ptr_batch(self, slots, host_ptrs, stride):
+        """n host-to-device copies + one pyramid launch (svtme_pictures_upload)."""
+        n = len(slots)
+        self._check(self.lib.svtme_pictures_upload(self._h, n, (C.c_int32 * n)(*slots), (C.c_void_p * n)(*host_ptrs), stride),
+                    "svtme_pictures_upload")
 
     def upload_device_batch(self, slots, dev_ptrs, stride):
         """One pyramid launch for len(slots) pictures that already live in device memory (svtme_pictures_upload_device)."""

@@ -284,6 +284,35 @@ int32_t svtme_pictures_upload_device(SvtMeContext* ctx, int32_t n, const int32_t
     return SVTME_OK;
 }
 
+int32_t svtme_pictures_upload(SvtMeContext* ctx, int32_t n, const int32_t* slots, const uint8_t* const* lumas, int32_t stride) {
+    if (!ctx || n <= 0 || n > SVTME_MAX_BATCH || !slots || !lumas || stride < ctx->width)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_pictures_upload: bad argument");
+    for (int i = 0; i < n; i++)
+        if (slots[i] < 0 || slots[i] >= (int)ctx->slots.size() || !lumas[i])
+            return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_pictures_upload: bad slot or plane");
+    CU(cudaSetDevice(ctx->device));
+    PyramidBatch batch;
+    for (int i = 0; i < n; i++) {
+        Slot& s = ctx->slots[slots[i]];
+        int32_t rc = guard_slot_rewrite(ctx, s);
+        if (rc != SVTME_OK) return rc;
+        if (stride == ctx->width)
+            CU(cudaMemcpyAsync(s.luma, lumas[i], (size_t)ctx->width * ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
+        else
+            CU(cudaMemcpy2DAsync(s.luma, ctx->width, lumas[i], stride, ctx->width, ctx->height, cudaMemcpyHostToDevice, ctx->copy_in));
+        batch.luma[i] = s.luma; batch.base[i] = s.base;
+    }
+    const Slot& g = ctx->slots[slots[0]];
+    { LaunchTimer t(ctx, SVTME_KERNEL_PYRAMID, ctx->copy_in); launch_pyramid_batch(batch, n, ctx->width, g.pyr, g.base, ctx->copy_in); }
+    CU(cudaGetLastError());
+    for (int i = 0; i < n; i++) {
+        Slot& s = ctx->slots[slots[i]];
+        CU(cudaEventRecord(s.ready, ctx->copy_in));
+        CU(cudaEventRecord(s.ready_ipc, ctx->copy_in));
+    }
+    return SVTME_OK;
+}
+
 int32_t svtme_picture_upload(SvtMeContext* ctx, int32_t slot, const uint8_t* luma, int32_t stride) {
     if (!ctx || slot < 0 || slot >= (int)ctx->slots.size() || !luma || stride < ctx->width)
         return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload: bad argument");

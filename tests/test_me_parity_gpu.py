@@ -97,6 +97,14 @@ def test_batched_device_upload(pkg, meo):
             assert np.array_equal(ctx.download_plane(slot, lvl), x), (slot, lvl)
     with pytest.raises(pkg.SvtMeError, match="0x80001005"):
         ctx.upload_device_batch([0, 9], [d[0].data_ptr(), d[1].data_ptr()], d.stride(1))
+    # the same from host memory (svtme_pictures_upload), strided and contiguous
+    ctx.upload_ptr_batch([1, 3, 0], [wide[i].ctypes.data for i in (2, 4, 1)], wide.strides[1])
+    cont = [np.ascontiguousarray(fr[i]) for i in (0, 3)]
+    ctx.upload_ptr_batch([5, 2], [c.ctypes.data for c in cont], w)
+    for slot, i in ((1, 2), (3, 4), (0, 1), (5, 0), (2, 3)):
+        want = M.build_pyramid(meo, "meo", fr[i])
+        for lvl, x in enumerate(want.planes):
+            assert np.array_equal(ctx.download_plane(slot, lvl), x), (slot, lvl)
     ctx.close()
 
 
