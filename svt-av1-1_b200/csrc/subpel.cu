@@ -38,6 +38,7 @@ struct SpSharedT {
     uint32_t pu_sad[NPU], pu_mv[NPU], pu_ssd[NPU];
     int32_t  pu_dir[NPU];
     uint32_t pu_imv[NPU];               // MV at entry of the current stage
+    uint32_t pu_win[NPU];               // winning half-pel candidate (1..8) of the PU, 0 = the integer position stays
     int32_t  bbox[4];                   // min X, min Y, max -X... see the kernel: bounding box of the blocks' window positions
 };
 
@@ -127,6 +128,12 @@ __device__ __forceinline__ bool quarter_valid(int method, int dir, int k) {
     const int q8 = k == 0 ? D_L : k == 1 ? D_R : k == 2 ? D_T : k == 3 ? D_B : k == 4 ? D_TL : k == 5 ? D_TR : k == 6 ? D_BR : D_BL;
     const int centre = method ? ((q8 + 4) & 7) : q8;
     return dir == centre || dir == ((centre + 1) & 7) || dir == ((centre + 7) & 7);
+}
+// The same as a bit mask over k (exactly three bits set), from a packed table: byte d of the constant is the mask for
+// direction d with method == 0; a fractional half-pel MV (method != 0) mirrors the direction (d + 4).
+__device__ __forceinline__ uint32_t quarter_mask(int method, int dir) {
+    const unsigned long long table = 0x9189C84A62263415ull;
+    return (uint32_t)(table >> (8 * ((dir + (method ? 4 : 0)) & 7))) & 0xFFu;
 }
 
 // Lanes of a warp = 8x4 blocks (bx = lane & 7, by = lane >> 3) of one level L (warp-uniform). Sum over the blocks of
@@ -251,7 +258,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         // ---- half-pel: one thread per (level, 8x8 block) walks the ten plane rows its nine candidates share
         // (L/R read the same three B words per row, T/B the same H rows, the four diagonals the same J rows and words);
         // wrapping-SSD and SAD are summed per (candidate, PU) with shared atomics
-        for (int t = tid; t < NLEV * 64; t += kSpThreads) {
+        // Only the SAD of the WINNING candidate of a PU is ever used (ME.c:1934-1950), so the eight per-block SADs stay
+        // with the thread (packed 16-bit, <= 16320 each) and only the winner's is summed over the PU after the decision.
+        constexpr int kIters = (NLEV * 64 + kSpThreads - 1) / kSpThreads;
+        uint4 blk_sad[kIters];
+        for (int t = tid, it = 0; t < NLEV * 64; t += kSpThreads, it++) {
             const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
             const int pu = block_pu(L, bx, by);
             const uint32_t mv = sh.pu_imv[pu];
@@ -294,6 +305,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                 }
             }
 #undef HP_ACC
+            blk_sad[it] = make_uint4(sad[1] | (sad[2] << 16), sad[3] | (sad[4] << 16), sad[5] | (sad[6] << 16), sad[7] | (sad[8] << 16));
             // a warp holds 8x4 blocks of ONE level: sum the blocks of each PU inside the warp, one lane per PU writes
             if constexpr (Ext) {
                 const int pwb = kLevelWb[L], phb = kLevelHb[L];
@@ -302,42 +314,64 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                 const bool leader = pu_leader_any(pwb, phb, tid & 31);
 #pragma unroll
                 for (int k = 0; k < 9; k++) {
-                    const uint32_t a = pu_sum_any(ranked ? ssd[k] : 0u, pwb, phb), b = k ? pu_sum_any(sad[k], pwb, phb) : 0u;
+                    const uint32_t a = pu_sum_any(ranked ? ssd[k] : 0u, pwb, phb);
                     if (leader) {
-                        if (phb == 8) { atomicAdd(&sh.sum_ssd[k][pu], a); if (k) atomicAdd(&sh.sum_sad[k][pu], b); }   // two warps share the PU
-                        else { sh.sum_ssd[k][pu] = a; sh.sum_sad[k][pu] = b; }
+                        if (phb == 8) atomicAdd(&sh.sum_ssd[k][pu], a);   // two warps share the PU
+                        else sh.sum_ssd[k][pu] = a;
                     }
                 }
             } else {
                 const bool leader = pu_leader(L, tid & 31);
 #pragma unroll
                 for (int k = 0; k < 9; k++) {
-                    const uint32_t a = pu_sum(ssd[k], L), b = k ? pu_sum(sad[k], L) : 0u;
+                    const uint32_t a = pu_sum(ssd[k], L);
                     if (leader) {
-                        if (L == 0) { atomicAdd(&sh.sum_ssd[k][0], a); if (k) atomicAdd(&sh.sum_sad[k][0], b); }   // two warps share PU 0
-                        else { sh.sum_ssd[k][pu] = a; sh.sum_sad[k][pu] = b; }
+                        if (L == 0) atomicAdd(&sh.sum_ssd[k][0], a);      // two warps share PU 0
+                        else sh.sum_ssd[k][pu] = a;
                     }
                 }
             }
         }
         __syncthreads();
         // ---- per PU: nine candidates in the reference's order, strict '<' on the SSD  (ME.c:1909-2239)
+        if (tid < NPU) sh.pu_win[tid] = 0;
         if (tid < NPU && pu_enabled(tid)) {
-            uint32_t dist[9], sadv[9];
+            uint32_t dist[9];
 #pragma unroll
-            for (int k = 0; k < 9; k++) { dist[k] = sh.sum_ssd[k][tid]; sadv[k] = sh.sum_sad[k][tid]; }
+            for (int k = 0; k < 9; k++) dist[k] = sh.sum_ssd[k][tid];
             const uint32_t imv = sh.pu_imv[tid];
-            uint32_t bssd = dist[0], bsad = sh.pu_sad[tid], bmv = imv;
+            uint32_t bssd = dist[0], bmv = imv;
+            int kw = 0;
             for (int k = 1; k < 9; k++)
-                if (dist[k] < bssd) { bssd = dist[k]; bsad = sadv[k]; bmv = make_mv((int16_t)(mv_x(imv) + kHalf[k][3]), (int16_t)(mv_y(imv) + kHalf[k][4])); }
+                if (dist[k] < bssd) { bssd = dist[k]; kw = k; bmv = make_mv((int16_t)(mv_x(imv) + kHalf[k][3]), (int16_t)(mv_y(imv) + kHalf[k][4])); }
             uint32_t best = dist[1];
             for (int k = 2; k < 9; k++) best = min(best, dist[k]);
             // tie order L R T B TL TR BL BR
             const int dir = best == dist[1] ? D_L : best == dist[2] ? D_R : best == dist[3] ? D_T : best == dist[4] ? D_B :
                             best == dist[5] ? D_TL : best == dist[6] ? D_TR : best == dist[8] ? D_BL : D_BR;
-            sh.pu_ssd[tid] = bssd; sh.pu_sad[tid] = bsad; sh.pu_mv[tid] = bmv; sh.pu_dir[tid] = dir;
+            sh.pu_ssd[tid] = bssd; sh.pu_mv[tid] = bmv; sh.pu_dir[tid] = dir;
+            sh.pu_win[tid] = (uint32_t)kw;
+            if (kw) sh.pu_sad[tid] = 0;                       // re-summed below from the blocks' SADs of candidate kw
         }
         __syncthreads();
+        // ---- SAD of the winning half-pel candidate, summed over the PU's blocks
+        for (int t = tid, it = 0; t < NLEV * 64; t += kSpThreads, it++) {
+            const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
+            const int pu = block_pu(L, bx, by);
+            const int kw = (int)sh.pu_win[pu];
+            const uint4 pk = blk_sad[it];
+            const int w = (kw - 1) >> 1;
+            const uint32_t word = w == 0 ? pk.x : w == 1 ? pk.y : w == 2 ? pk.z : pk.w;
+            uint32_t v = kw ? ((word >> (((kw - 1) & 1) * 16)) & 0xFFFFu) : 0u;
+            if constexpr (Ext) {
+                const int pwb = kLevelWb[L], phb = kLevelHb[L];
+                v = pu_sum_any(v, pwb, phb);
+                if (kw && pu_leader_any(pwb, phb, tid & 31)) { if (phb == 8) atomicAdd(&sh.pu_sad[pu], v); else sh.pu_sad[pu] = v; }
+            } else {
+                v = pu_sum(v, L);
+                if (kw && pu_leader(L, tid & 31)) { if (L == 0) atomicAdd(&sh.pu_sad[0], v); else sh.pu_sad[pu] = v; }
+            }
+        }
         if (tid < NPU) sh.pu_imv[tid] = sh.pu_mv[tid];
         for (int t = tid; t < 9 * NPU; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
@@ -360,10 +394,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             if constexpr (Ext) { pwb = kLevelWb[L]; phb = kLevelHb[L]; }
             // lane 0 of the 64x64 level is inside the area
             const bool leader = active && (Ext ? pu_leader_any(pwb, phb, tid & 31) : pu_leader(L, tid & 31));
-            int kk = -1;
+            uint32_t kmask = quarter_mask(method, dir);                    // inactive lanes may hold a stale dir: still three bits
 #pragma unroll 1
             for (int j = 0; j < 3; j++) {
-                do { kk++; } while (kk < 8 && !quarter_valid(method, dir, kk));   // kk < 8: inactive lanes may hold a stale dir
+                const int kk = __ffs(kmask) - 1;
+                kmask &= kmask - 1;
                 uint32_t ssd = 0, sad = 0;
                 if (active) {
                     const int8_t* q = kQuarter[method][kk];
@@ -394,9 +429,10 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             const uint32_t imv = sh.pu_imv[tid];
             const int method = (mv_y(imv) & 2) + ((mv_x(imv) & 2) >> 1), dir = sh.pu_dir[tid];
             uint32_t bssd = sh.pu_ssd[tid], bsad = sh.pu_sad[tid], bmv = imv;
+            const uint32_t kmask = quarter_mask(method, dir);
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-                if (!quarter_valid(method, dir, k)) continue;
+                if (!((kmask >> k) & 1u)) continue;
                 const uint32_t a = sh.sum_ssd[k][tid], b = sh.sum_sad[k][tid];
                 if (a < bssd) { bssd = a; bsad = b; bmv = make_mv((int16_t)(mv_x(imv) + kQmv[k][0]), (int16_t)(mv_y(imv) + kQmv[k][1])); }
             }
