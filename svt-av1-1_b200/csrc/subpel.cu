@@ -182,9 +182,12 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     SbScratch& scr = job.scratch[sb];
     const DPlane& rp = job.ref[list].full;
-    // ---- stage: source SB, PU state
-    for (int t = tid; t < 64 * 16; t += kSpThreads)
-        sh.src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + (t >> 4)));
+    // ---- stage: source SB (asynchronous copies: first read in the half-pel phase, three barriers from here), PU state
+    for (int t = tid; t < 64 * 16; t += kSpThreads) {
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&sh.src[t]);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(job.cur.full.at(ox + 4 * (t & 15), oy + (t >> 4))) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
     if (tid < kNumPu) { sh.pu_sad[tid] = scr.best_sad[list][tid]; sh.pu_mv[tid] = scr.best_mv[list][tid]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
     if constexpr (Ext) {
         const SbScratchExt& scx = job.scratch_ext[sb];
@@ -254,6 +257,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         __syncthreads();
 
         for (int t = tid; t < 9 * NPU; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");             // the source SB has landed
         __syncthreads();
         // ---- half-pel: one thread per (level, 8x8 block) walks the ten plane rows its nine candidates share
         // (L/R read the same three B words per row, T/B the same H rows, the four diagonals the same J rows and words);
@@ -446,6 +450,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         }
     } else {
         // planes B/H/J are not needed: integer MVs only use plane A below
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
 
     // ---- final uni-prediction blocks of this list for every PU level (consumed by bipred_pack_kernel)
