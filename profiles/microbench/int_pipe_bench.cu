@@ -85,6 +85,123 @@ __global__ void __launch_bounds__(256) bench(uint32_t* out, uint32_t seed) {
         } else if (MODE == 7) {  // 8 x dp4a alone
             c0 = __dp4a(a0, b0, c0); c1 = __dp4a(a1, b1, c1); c2 = __dp4a(a2, b2, c2); c3 = __dp4a(a3, b3, c3);
             c4 = __dp4a(a0, b1, c4); c5 = __dp4a(a1, b2, c5); c6 = __dp4a(a2, b3, c6); c7 = __dp4a(a3, b0, c7);
+        } else if (MODE == 8) {  // 8 x VABSDIFF4 + 4 x min.u32
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("min.u32 %0, %0, %1;" : "+r"(b0) : "r"(c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("min.u32 %0, %0, %1;" : "+r"(b1) : "r"(c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("min.u32 %0, %0, %1;" : "+r"(b2) : "r"(c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("min.u32 %0, %0, %1;" : "+r"(b3) : "r"(c3));
+        } else if (MODE == 9) {  // 8 x VABSDIFF4 + 4 x min.f32
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("min.f32 %0, %0, %1;" : "+f"(*(float*)&b0) : "f"(*(float*)&c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("min.f32 %0, %0, %1;" : "+f"(*(float*)&b1) : "f"(*(float*)&c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("min.f32 %0, %0, %1;" : "+f"(*(float*)&b2) : "f"(*(float*)&c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("min.f32 %0, %0, %1;" : "+f"(*(float*)&b3) : "f"(*(float*)&c3));
+        } else if (MODE == 10) {  // 8 x VABSDIFF4 + 4 x min.f16x2
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("min.f16x2 %0, %0, %1;" : "+r"(b0) : "r"(c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("min.f16x2 %0, %0, %1;" : "+r"(b1) : "r"(c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("min.f16x2 %0, %0, %1;" : "+r"(b2) : "r"(c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("min.f16x2 %0, %0, %1;" : "+r"(b3) : "r"(c3));
+        } else if (MODE == 11) {  // 8 x VABSDIFF4 + 4 x min.u16x2
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("min.u16x2 %0, %0, %1;" : "+r"(b0) : "r"(c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("min.u16x2 %0, %0, %1;" : "+r"(b1) : "r"(c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("min.u16x2 %0, %0, %1;" : "+r"(b2) : "r"(c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("min.u16x2 %0, %0, %1;" : "+r"(b3) : "r"(c3));
+        } else if (MODE == 12) {  // 8 x VABSDIFF4 + 4 x min3.u32 (min(min))
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("{.reg .u32 t; min.u32 t, %0, %1; min.u32 %0, t, %2;}" : "+r"(b0) : "r"(c0), "r"(a3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("{.reg .u32 t; min.u32 t, %0, %1; min.u32 %0, t, %2;}" : "+r"(b1) : "r"(c1), "r"(a3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("{.reg .u32 t; min.u32 t, %0, %1; min.u32 %0, t, %2;}" : "+r"(b2) : "r"(c2), "r"(a3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("{.reg .u32 t; min.u32 t, %0, %1; min.u32 %0, t, %2;}" : "+r"(b3) : "r"(c3), "r"(a3));
+        } else if (MODE == 13) {  // 8 x VABSDIFF4 + 4 x fma.rn.f32
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(*(float*)&b0) : "f"(*(float*)&c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(*(float*)&b1) : "f"(*(float*)&c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(*(float*)&b2) : "f"(*(float*)&c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(*(float*)&b3) : "f"(*(float*)&c3));
+        } else if (MODE == 14) {  // 8 x VABSDIFF4 + 4 x lop3 xor
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("xor.b32 %0, %0, %1;" : "+r"(b0) : "r"(c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("xor.b32 %0, %0, %1;" : "+r"(b1) : "r"(c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("xor.b32 %0, %0, %1;" : "+r"(b2) : "r"(c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("xor.b32 %0, %0, %1;" : "+r"(b3) : "r"(c3));
+        } else if (MODE == 15) {  // 8 x VABSDIFF4 + 4 x prmt
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("prmt.b32 %0, %0, %1, 0x5410;" : "+r"(b0) : "r"(c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("prmt.b32 %0, %0, %1, 0x5410;" : "+r"(b1) : "r"(c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("prmt.b32 %0, %0, %1, 0x5410;" : "+r"(b2) : "r"(c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("prmt.b32 %0, %0, %1, 0x5410;" : "+r"(b3) : "r"(c3));
+        } else if (MODE == 16) {  // 8 x VABSDIFF4 + 4 x sel (setp+selp)
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c0) : "r"(a0), "r"(b0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c1) : "r"(a1), "r"(b1));
+            asm volatile("{.reg .pred p; setp.lt.u32 p, %0, %1; selp.u32 %0, %0, %1, p;}" : "+r"(b0) : "r"(c0));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c2) : "r"(a2), "r"(b2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c3) : "r"(a3), "r"(b3));
+            asm volatile("{.reg .pred p; setp.lt.u32 p, %0, %1; selp.u32 %0, %0, %1, p;}" : "+r"(b1) : "r"(c1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c4) : "r"(a0), "r"(b1));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c5) : "r"(a1), "r"(b2));
+            asm volatile("{.reg .pred p; setp.lt.u32 p, %0, %1; selp.u32 %0, %0, %1, p;}" : "+r"(b2) : "r"(c2));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c6) : "r"(a2), "r"(b3));
+            asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(c7) : "r"(a3), "r"(b0));
+            asm volatile("{.reg .pred p; setp.lt.u32 p, %0, %1; selp.u32 %0, %0, %1, p;}" : "+r"(b3) : "r"(c3));
         }
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = c0 + c1 + c2 + c3 + c4 + c5 + c6 + c7 + b0 + b1 + b2 + b3;
@@ -117,6 +234,15 @@ int main() {
     run<5>("min.u32 x8", 8, d_out);
     run<6>("vabsdiff4 + dp4a x4 (counted: 4 word-sads)", 4, d_out);
     run<7>("dp4a x8", 8, d_out);
+    run<8>("vabsdiff4.acc x8 + min.u32 x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<9>("vabsdiff4.acc x8 + min.f32 x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<10>("vabsdiff4.acc x8 + min.f16x2 x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<11>("vabsdiff4.acc x8 + min.u16x2 x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<12>("vabsdiff4.acc x8 + min3.u32 (min(min)) x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<13>("vabsdiff4.acc x8 + fma.rn.f32 x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<14>("vabsdiff4.acc x8 + lop3 xor x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<15>("vabsdiff4.acc x8 + prmt x4 (counted: 8 vabsdiff4)", 8, d_out);
+    run<16>("vabsdiff4.acc x8 + sel (setp+selp) x4 (counted: 8 vabsdiff4)", 8, d_out);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { printf("CUDA error %s\n", cudaGetErrorString(e)); return 1; }
     return 0;
