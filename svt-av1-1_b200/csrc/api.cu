@@ -13,6 +13,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <algorithm>
 #include <vector>
 
 using namespace svtme;
@@ -56,6 +57,13 @@ struct SvtMeContext {
     int device = 0, width = 0, height = 0, sb_cols = 0, sb_rows = 0, n_sb = 0;
     cudaStream_t stream = nullptr, copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t join_ev = nullptr;
+    // chunked submission: a small batch (one mini-GOP: a handful of waves per kernel) is cut into two chunks of pictures that
+    // run their kernel sequences on two streams, so the tail of one chunk's kernel is filled by the other chunk's CTAs.
+    // SVTME_CHUNKS overrides (1 = never); large batches and profiled runs (per-kernel event times) stay on one stream.
+    static constexpr int kChunkStreams = 8;
+    int chunks = 0;                       // 0 = automatic
+    cudaStream_t cstream[kChunkStreams] = {};
+    cudaEvent_t fork_ev = nullptr, cjoin_ev[kChunkStreams] = {};
     std::vector<Slot> slots;
     std::mutex peer_mu;                   // guards Slot::peer_reads (written by the contexts that copy from us)
     std::vector<cudaEvent_t> peer_events; // events this context records after copying from a peer (round-robin)
@@ -171,6 +179,14 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     }
     CU(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming));
+    if (const char* e = getenv("SVTME_CHUNKS")) ctx->chunks = std::max(0, std::min(atoi(e), 64));
+    if (ctx->chunks != 1) {
+        CU(cudaEventCreateWithFlags(&ctx->fork_ev, cudaEventDisableTiming));
+        for (int i = 0; i < (ctx->chunks ? std::min(ctx->chunks, (int)SvtMeContext::kChunkStreams) : 2); i++) {
+            CU(cudaStreamCreateWithFlags(&ctx->cstream[i], cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&ctx->cjoin_ev[i], cudaEventDisableTiming));
+        }
+    }
     for (auto& b : ctx->ring) {
         CU(cudaEventCreateWithFlags(&b.computed, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&b.drained, cudaEventDisableTiming));
@@ -223,6 +239,11 @@ void svtme_destroy(SvtMeContext* ctx) {
         if (b.drained) cudaEventDestroy(b.drained);
     }
     if (ctx->join_ev) cudaEventDestroy(ctx->join_ev);
+    if (ctx->fork_ev) cudaEventDestroy(ctx->fork_ev);
+    for (int i = 0; i < SvtMeContext::kChunkStreams; i++) {
+        if (ctx->cstream[i]) cudaStreamDestroy(ctx->cstream[i]);
+        if (ctx->cjoin_ev[i]) cudaEventDestroy(ctx->cjoin_ev[i]);
+    }
     for (cudaStream_t st : { ctx->copy_in, ctx->stream, ctx->copy_out }) if (st) cudaStreamDestroy(st);
     delete ctx;
 }
@@ -551,18 +572,31 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         }
     }
     CU(cudaMemcpyAsync(b.d_jobs, b.h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
-    for (int list = 0; list < max_lists; list++) {
-        { LaunchTimer t(ctx, SVTME_KERNEL_HME, ctx->stream); launch_hme(b.d_jobs, n_jobs, max_sb, list, ctx->stream); }
-        // the square (85-PU) and ext (209-PU) variants cover the same grid; a CTA of the other mode exits at once
+    const int n_chunks = ctx->profiling ? 1 : ctx->chunks ? std::min(ctx->chunks, n_jobs) : (n_jobs >= 2 && n_jobs <= 16) ? 2 : 1;
+    if (n_chunks > 1) CU(cudaEventRecord(ctx->fork_ev, ctx->stream));
+    const int n_cs = std::min(n_chunks, (int)SvtMeContext::kChunkStreams);
+    for (int i = 0; i < (n_chunks > 1 ? n_cs : 0); i++) CU(cudaStreamWaitEvent(ctx->cstream[i], ctx->fork_ev, 0));
+    for (int c = 0; c < n_chunks; c++) {
+        const int j0 = (int)((int64_t)n_jobs * c / n_chunks), j1 = (int)((int64_t)n_jobs * (c + 1) / n_chunks), nj = j1 - j0;
+        const DJob* dj = b.d_jobs + j0;
+        cudaStream_t st = n_chunks > 1 ? ctx->cstream[c % n_cs] : ctx->stream;
+        for (int list = 0; list < max_lists; list++) {
+            { LaunchTimer t(ctx, SVTME_KERNEL_HME, st); launch_hme(dj, nj, max_sb, list, st); }
+            // the square (85-PU) and ext (209-PU) variants cover the same grid; a CTA of the other mode exits at once
+            for (int ext = 0; ext < 2; ext++) {
+                if (!(ext ? any_ext : any_sq)) continue;
+                { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, st); launch_fullpel(dj, nj, max_sb, list, ext != 0, st); }
+                { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, st); launch_subpel(dj, nj, max_sb, list, ext != 0, st); }
+            }
+        }
         for (int ext = 0; ext < 2; ext++) {
             if (!(ext ? any_ext : any_sq)) continue;
-            { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, ctx->stream); launch_fullpel(b.d_jobs, n_jobs, max_sb, list, ext != 0, ctx->stream); }
-            { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, ctx->stream); launch_subpel(b.d_jobs, n_jobs, max_sb, list, ext != 0, ctx->stream); }
+            LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, st); launch_bipred_pack(dj, nj, max_sb, ext != 0, st);
         }
     }
-    for (int ext = 0; ext < 2; ext++) {
-        if (!(ext ? any_ext : any_sq)) continue;
-        LaunchTimer t(ctx, SVTME_KERNEL_BIPRED_PACK, ctx->stream); launch_bipred_pack(b.d_jobs, n_jobs, max_sb, ext != 0, ctx->stream);
+    for (int i = 0; i < (n_chunks > 1 ? n_cs : 0); i++) {
+        CU(cudaEventRecord(ctx->cjoin_ev[i], ctx->cstream[i]));
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->cjoin_ev[i], 0));
     }
     CU(cudaGetLastError());
     CU(cudaEventRecord(b.computed, ctx->stream));
