@@ -42,6 +42,23 @@ SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
 FULLPEL_BYTE_SADS_PER_SB_LIST = 64 * 64 * 64 * 32
 
 
+def hme_byte_sads_per_sb_list(prm):
+    """Nominal byte-SADs of the HME levels of one full-height SB and one list (search sizes before picture-edge clipping):
+    level 0 = 16x16 block of the sixteenth picture, level 1 = 32x32 of the quarter picture, level 2 = 64x64, even rows only."""
+    def rnd(w):
+        return 8 if w < 8 else (w + (w & 7)) if (w & 7) else w
+    total = 0
+    for rw in range(prm.num_hme_regions_w):
+        for rh in range(prm.num_hme_regions_h):
+            if prm.enable_hme_level0:
+                total += (prm.hme_l0_w[rw] * prm.hme_l0_mult_x // 100) * (prm.hme_l0_h[rh] * prm.hme_l0_mult_y // 100) * 16 * 8
+            if prm.enable_hme_level1:
+                total += rnd(prm.hme_l1_w[rw]) * prm.hme_l1_h[rh] * 32 * 16
+            if prm.enable_hme_level2:
+                total += rnd(prm.hme_l2_w[rw]) * prm.hme_l2_h[rh] * 64 * 32
+    return total
+
+
 USE_16BIT = False                 # me4k: pictures arrive as 16-bit samples (10-bit), split on the device
 SHARD_SB_ROWS = False             # me4k: N ranks share every picture by SB rows (strong scaling)
 NUM_PUS = 85                      # me209: every picture searched with all 209 PUs (PIC_ALL_DEPTH_MODE, enc-mode 0)
@@ -488,6 +505,9 @@ def run_gpu_impl(args, rank, world, local_rank):
         # algorithmic work of one full-pel launch: every SB of every picture of the batch, one list
         sads_per_launch = FULLPEL_BYTE_SADS_PER_SB_LIST * n_sb * len(jobs)
         achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n else None
+        sb_cols_, n_sb_pic, full_rows_sb = (W + 63) // 64, ((W + 63) // 64) * ((H + 63) // 64), (H // 64) * ((W + 63) // 64)
+        step_sads = (1 if SHARD_SB_ROWS else world) * sum(
+            sp[3].num_lists * (FULLPEL_BYTE_SADS_PER_SB_LIST * n_sb_pic + hme_byte_sads_per_sb_list(sp[3]) * full_rows_sb) for sp in specs)
         traffic = None                                    # DRAM bytes per launch, scaled from the committed ncu capture
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))
@@ -532,6 +552,12 @@ def run_gpu_impl(args, rank, world, local_rank):
                              "achieved": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9) if py_n else None,
                              "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9 / hbm_peak) if py_n else None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
+            # the whole step against the same peak: HME + full-pel byte-SADs of every (picture, SB, list) over the step time
+            # (the sub-pel / bi-pred arithmetic is not counted, so this under-states the work done)
+            "roofline_step": {"bound": "int", "unit": "Tbyte-SAD/s", "peak": peak * world,
+                              "achieved": step_sads / (ms / args.steps / 1e3) / 1e12,
+                              "frac": step_sads / (ms / args.steps / 1e3) / 1e12 / (peak * world),
+                              "byte_sads_per_step": step_sads},
             "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
             "kernel_launches_per_step": {k: v[1] / args.steps for k, v in kt.items()},
             "clocks": clocks, "result_checksum": checksum,
