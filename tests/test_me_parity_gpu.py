@@ -196,6 +196,14 @@ def test_mixed_batch(pkg, meo):
     _check_against_oracle(pkg, meo, fr, prms, jobs)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks", ["1", "3", "9"])
+def test_chunked_submission(pkg, meo, chunks, monkeypatch):
+    """SVTME_CHUNKS: the pictures of a batch run as 1 / 3 / 9 chunks on separate streams (api.cu); results do not change."""
+    monkeypatch.setenv("SVTME_CHUNKS", chunks)
+    test_mixed_batch(pkg, meo)
+
+
 def test_1080p_full_size_parity(pkg, meo):
     """BASELINE config 2 geometry (1920x1080: 30x17 SBs, last SB row 56 high -> no HME there)."""
     w, h = 1920, 1080
