@@ -26,7 +26,8 @@ namespace svtme {
 constexpr int kFpThreads = 256;
 constexpr int kWinRows = 126;          // 64 search rows + 62
 constexpr int kWinPitch = 36;          // words; = 4 (mod 32) keeps the 8 row-distinct LDS.128 of a warp conflict-free
-constexpr int kFpSmemBytes = (4 * kWinRows * kWinPitch + 32 * 16 + 96) * 4;
+constexpr int kRawPitch = 40;          // words: one raw window row = ten 16-byte granules from the aligned address below its first byte
+constexpr int kFpSmemBytes = (4 * kWinRows * kWinPitch + 32 * 16 + 96 + kWinRows * kRawPitch) * 4;
 
 // One step of a streaming transpose-reduction: two keys a, b live in every lane; afterwards lanes whose `bit` is
 // clear hold min(a) over {lane, lane ^ bit} and lanes whose bit is set hold the same for b. Five such steps
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     uint32_t* win = smem;
     uint32_t* src = smem + 4 * kWinRows * kWinPitch;
     uint32_t* keys = src + 32 * 16;
+    uint32_t* raw = keys + 96;                                   // 16-byte aligned: (4 * 126 * 36 + 512 + 96) * 4 = 16 * 4688
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
@@ -62,24 +64,42 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const DPlane& rp = job.ref[list].full;
     const int sax = scr.sa_x[list], say = scr.sa_y[list], saw = scr.sa_w[list], sah = scr.sa_h[list];
 
-    // ---- stage source (even rows) and the four byte-shifted window copies
+    // ---- stage source (even rows) and the four byte-shifted window copies.
+    // The window first lands RAW in shared memory as 16-byte cp.async granules (fire and forget: no thread holds a
+    // register or waits per row, the whole window costs one L2 round trip), then every warp shifts its rows out of the raw
+    // buffer into the four copies (3 LDS + 4 SHF + 4 STS per word, no global latency inside the loop). With ordinary
+    // loads the staging loop was sixteen dependent L2 round trips per warp, a fifth of the CTA's lifetime, during which
+    // the other CTA of the SM was alone on the SAD pipe. (TMA cannot make the copies: tensor boxes must start on a
+    // 16-byte boundary, profiles/microbench/tma_probe_r01.txt.)
+    const int wrows = sah + 62;
+    const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
+    const uint8_t* g0 = rp.at(ox + sax, oy + say);
+    const uint32_t m16 = (uint32_t)(uintptr_t)g0 & 15u;           // the same for every row: the pitch is a multiple of 64
+    {
+        const int ngran = ((int)(m16 >> 2) + nfill + 2 + 3) >> 2;     // granules per row that hold the words read below (<= 10)
+        const uint8_t* ga = g0 - m16;
+        const uint32_t raw_addr = (uint32_t)__cvta_generic_to_shared(raw);
+        for (int t = tid; t < wrows * ngran; t += kFpThreads) {
+            const int r = t / ngran, g = t - r * ngran;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(raw_addr + (uint32_t)(r * kRawPitch * 4 + g * 16)),
+                         "l"(ga + (size_t)r * rp.stride + g * 16) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     for (int t = tid; t < 32 * 16; t += kFpThreads)
         src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
     if (tid < 96) keys[tid] = 0xFFFFFFFFu;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
     {
-        // lane = window column (aligned word), warp pair = one quarter of the rows: three aligned loads give the
-        // four byte-shifted copies of a word (no integer division, 3 LDG + 4 SHF + 4 STS per word of the window)
-        const int wrows = sah + 62;
-        const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
+        // lane = window column (word), warp = every eighth row: three raw words give the four byte-shifted copies of a word
         const int c = tid & 31;
         if (c < nfill) {
-            const uint8_t* g0 = rp.at(ox + sax, oy + say);
-            const uint32_t m = (uint32_t)(uintptr_t)g0 & 3u;
-            const uint32_t* gw = reinterpret_cast<const uint32_t*>(g0 - m) + c;
-            const int wstride = rp.stride >> 2;
+            const uint32_t m = m16 & 3u;
+            const uint32_t* rw = raw + (m16 >> 2) + c;
             for (int r = tid >> 5; r < wrows; r += kFpThreads / 32) {
-                const uint32_t* w = gw + (size_t)r * wstride;
-                const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+                const uint32_t* w = rw + r * kRawPitch;
+                const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
 #pragma unroll
                 for (int sc = 0; sc < 4; sc++) {
                     const uint32_t o = m + sc;                       // byte offset of copy sc inside the aligned word

@@ -28,7 +28,8 @@ constexpr int kWinPitch = 36;          // words; = 4 (mod 32): the 8 row-distinc
 constexpr int kWinWords = 4 * kWinRows * kWinPitch;
 constexpr int kSrcWords = 32 * 16;
 constexpr int kKeyWords = 212;         // 209 PU slots (internal index), padded
-constexpr int kFxSmemBytes = (kWinWords + kSrcWords + kKeyWords + 4096) * 4 + 4096 * 2;
+constexpr int kRawPitch = 40;          // words per raw window row (ten 16-byte granules), see fullpel.cu
+constexpr int kFxSmemBytes = (kWinWords + kSrcWords + kKeyWords + 4096) * 4 + 4096 * 2 + kWinRows * kRawPitch * 4;
 
 // see fullpel.cu: lanes whose `bit` is clear keep min(a) over {lane, lane ^ bit}, the others the same for b
 __device__ __forceinline__ uint32_t pair_min(uint32_t a, uint32_t b, int bit, uint32_t hi01) {
@@ -87,6 +88,7 @@ __global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxT
     uint32_t* keys = src + kSrcWords;
     uint32_t* q11_s = keys + kKeyWords;                                  // bottom 64x32 SAD of every position
     uint16_t* q11_t = reinterpret_cast<uint16_t*>(q11_s + 4096);         // 32x16 (x 0, y 48) SAD of every position
+    uint32_t* raw = reinterpret_cast<uint32_t*>(q11_t + 4096);           // raw window rows (byte offset 100048 = 16 * 6253)
     __shared__ uint32_t lane_slot[kNumTables][32];                       // shared ADDRESS of the PU slot a lane owns
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
@@ -101,23 +103,37 @@ __global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxT
     const int sax = scr.sa_x[list], say = scr.sa_y[list], saw = scr.sa_w[list], sah = scr.sa_h[list];
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
 
-    // ---- stage source (even rows), the slot tables and the four byte-shifted window copies (as in fullpel.cu)
+    // ---- stage source (even rows), the slot tables and the four byte-shifted window copies (as in fullpel.cu: the window
+    // lands raw in shared memory as 16-byte cp.async granules, then the warps shift it into the four copies)
+    const int wrows = sah + 62;
+    const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
+    const uint8_t* g0 = rp.at(ox + sax, oy + say);
+    const uint32_t m16 = (uint32_t)(uintptr_t)g0 & 15u;
+    {
+        const int ngran = ((int)(m16 >> 2) + nfill + 2 + 3) >> 2;
+        const uint8_t* ga = g0 - m16;
+        const uint32_t raw_addr = (uint32_t)__cvta_generic_to_shared(raw);
+        for (int t = tid; t < wrows * ngran; t += kFxThreads) {
+            const int r = t / ngran, g = t - r * ngran;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(raw_addr + (uint32_t)(r * kRawPitch * 4 + g * 16)),
+                         "l"(ga + (size_t)r * rp.stride + g * 16) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
     for (int t = tid; t < kSrcWords; t += kFxThreads)
         src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
     for (int t = tid; t < kKeyWords; t += kFxThreads) keys[t] = 0xFFFFFFFFu;
     for (int t = tid; t < kNumTables * 32; t += kFxThreads) lane_slot[t >> 5][t & 31] = keys_addr + 4u * (uint32_t)lane_pu(t >> 5, t & 31);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
     {
-        const int wrows = sah + 62;
-        const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
         const int c = tid & 31;
         if (c < nfill) {
-            const uint8_t* g0 = rp.at(ox + sax, oy + say);
-            const uint32_t m = (uint32_t)(uintptr_t)g0 & 3u;
-            const uint32_t* gw = reinterpret_cast<const uint32_t*>(g0 - m) + c;
-            const int wstride = rp.stride >> 2;
+            const uint32_t m = m16 & 3u;
+            const uint32_t* rw = raw + (m16 >> 2) + c;
             for (int r = tid >> 5; r < wrows; r += kFxThreads / 32) {
-                const uint32_t* w = gw + (size_t)r * wstride;
-                const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+                const uint32_t* w = rw + r * kRawPitch;
+                const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
 #pragma unroll
                 for (int sc = 0; sc < 4; sc++) {
                     const uint32_t o = m + sc;
