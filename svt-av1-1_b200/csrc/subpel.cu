@@ -27,6 +27,8 @@ constexpr int kPlWords = kPlRows * kPlPitchW + 132;  // + room for the row skew 
 // together (two words apart along x, eight rows apart along y) touch 32 different banks when they share a motion
 // vector: bank offsets of the four block rows are {0, 1, 16, 17} or {0, 15, 16, 31}.
 __device__ __forceinline__ int plane_row(int r) { return r * kPlPitchW + ((r >> 3) & 1) + (r & ~15); }
+constexpr int kRawPitchSp = 44;         // words per raw window row: eleven 16-byte granules (3 + 36 + 1 words at most)
+static_assert(kPlRows * kRawPitchSp <= 2 * kPlWords, "the raw window must fit the storage of planes H and J");
 constexpr int kMargin = 3;              // window starts 3 pixels left/above the search-area origin
 
 template <int NPU>
@@ -216,9 +218,30 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
 
     // ---- plane A
     const uint32_t inv_ww = 0xFFFFFFFFu / (uint32_t)ww + 1u;   // t / ww == umulhi(t, inv_ww) for t * ww < 2^32
-    for (int t = tid; t < wr * ww; t += kSpThreads) {
-        const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
-        sh.plane[S_A][plane_row(r) + c] = ldg_u32_unaligned(rp.at(ox + sax - kMargin + 4 * c, oy + say - kMargin + r));
+    // The window lands raw (16-byte cp.async granules from the aligned address below its first byte: one L2 round trip
+    // for the whole window instead of one per loop iteration) in the storage of planes H and J, which are written only
+    // after A and B are complete; the threads then shift it into plane A's skewed rows from shared memory.
+    {
+        const uint8_t* g0 = rp.at(ox + sax - kMargin, oy + say - kMargin);
+        const uint32_t m16 = (uint32_t)(uintptr_t)g0 & 15u;           // the same for every row: the pitch is a multiple of 64
+        const int q = (int)(m16 >> 2), ngran = (q + ww + 1 + 3) >> 2; // words q .. q + ww of a raw row are read below
+        const uint8_t* ga = g0 - m16;
+        uint32_t* raw = sh.plane[S_H];                                // kRawPitchSp words per row, <= 2 planes in total
+        const uint32_t raw_addr = (uint32_t)__cvta_generic_to_shared(raw);
+        for (int t = tid; t < wr * ngran; t += kSpThreads) {
+            const int r = t / ngran, g = t - r * ngran;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(raw_addr + (uint32_t)(r * kRawPitchSp * 4 + g * 16)),
+                         "l"(ga + (size_t)r * rp.stride + g * 16) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        const uint32_t bs = (m16 & 3u) * 8u;
+        for (int t = tid; t < wr * ww; t += kSpThreads) {
+            const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
+            const uint32_t* w = raw + r * kRawPitchSp + q + c;
+            sh.plane[S_A][plane_row(r) + c] = __funnelshift_r(w[0], w[1], bs);
+        }
     }
     __syncthreads();
     if (p.use_subpel == 1) {
