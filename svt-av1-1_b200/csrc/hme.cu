@@ -90,7 +90,7 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
     constexpr int kTilesPerPass = kGroupThreads / RSPLIT;
     // t / d as umulhi(t, 2^32 / d + 1): exact while t * d < 2^32 (t, d are a few thousand at most here); d == 1 would
     // need the multiplier 2^32, so a one-tile row (search width <= 8) keeps the plain index
-    const uint32_t inv_wcols = 0xFFFFFFFFu / (uint32_t)(2 * tpr + W) + 1u, inv_tpr = tpr > 1 ? 0xFFFFFFFFu / (uint32_t)tpr + 1u : 0u;
+    const uint32_t inv_tpr = tpr > 1 ? 0xFFFFFFFFu / (uint32_t)tpr + 1u : 0u;
     uint32_t best = 0xFFFFFFFFu;
     if (gtid == 0) *best_slot = 0xFFFFFFFFu;
     for (int i0 = 0; i0 < sah; i0 += chunk) {
@@ -98,10 +98,20 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
         const int wrows = i1 - i0 + extra;
         const int wcols = 2 * tpr + W;
         group_bar(bar_id);                              // previous users of the window are done
+        {   // lane = window column, the two warps of the group take alternate rows: the row pointer advances by a constant,
+            // the misalignment of the window's first byte is the same on every row (the pitch is a multiple of 64), so a
+            // word costs two loads, one funnel shift and one store (the per-word division and 64-bit address arithmetic
+            // of a flat index were a quarter of this kernel's instructions)
+            const uint8_t* p0 = rp.at(rx, ry + i0);
+            const uint32_t m = (uint32_t)(uintptr_t)p0 & 3u, sh8 = m * 8u;
+            const int wstride = rp.stride >> 2, wi = gtid >> 5;
+            for (int c = gtid & 31; c < wcols; c += 32) {
+                const uint32_t* a = reinterpret_cast<const uint32_t*>(p0 - m) + c + wi * wstride;
+                uint32_t* d = win + wi * pitch + c;
 #pragma unroll 4
-        for (int t = gtid; t < wrows * wcols; t += kGroupThreads) {
-            const int r = (int)__umulhi((uint32_t)t, inv_wcols), c = t - r * wcols;
-            win[r * pitch + c] = ldg_u32_unaligned(rp.at(rx + 4 * c, ry + i0 + r));
+                for (int r = wi; r < wrows; r += 2, a += 2 * wstride, d += 2 * pitch)
+                    *d = __funnelshift_r(__ldg(a), __ldg(a + 1), sh8);
+            }
         }
         group_bar(bar_id);
         const int ntiles = (i1 - i0) * tpr;
