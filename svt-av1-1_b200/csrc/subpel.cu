@@ -98,9 +98,17 @@ __device__ __forceinline__ uint2 load8(const uint32_t* plane, int r, int c) {
     const uint32_t a = w[0], b = w[1], d = w[2];
     return make_uint2(__funnelshift_r(a, b, sh), __funnelshift_r(b, d, sh));
 }
+// Quirk Q5 squares the per-byte difference (a - b) mod 256 read as int8. |a - b| read as int8 has the same square
+// (for a < b the two bytes are negatives of each other mod 256, and -128 squares like 128), so one VABSDIFF4 replaces
+// the five-instruction byte-wise subtraction and the same word also gives the SAD by a second dp4a (FMA pipe).
 __device__ __forceinline__ uint32_t wrap_ssd4(uint32_t a, uint32_t b, uint32_t acc) {
-    const uint32_t t = __vsub4(a, b);                     // per-byte (a-b) mod 256, read as int8: quirk Q5
+    const uint32_t t = __vabsdiffu4(a, b);
     return (uint32_t)__dp4a((int)t, (int)t, (int)acc);
+}
+__device__ __forceinline__ void wrap_ssd_sad4(uint32_t a, uint32_t b, uint32_t& ssd, uint32_t& sad) {
+    const uint32_t t = __vabsdiffu4(a, b);
+    ssd = (uint32_t)__dp4a((int)t, (int)t, (int)ssd);
+    sad = __dp4a(t, 0x01010101u, sad);
 }
 __device__ __forceinline__ uint32_t true_ssd4(uint32_t a, uint32_t b, uint32_t acc) {
     const uint32_t d = __vabsdiffu4(a, b);
@@ -303,8 +311,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
 #pragma unroll
             for (int k = 0; k < 9; k++) { ssd[k] = 0; sad[k] = 0; }
 #define HP_ACC(k, lo, hi, s)                                                                           \
-            do { ssd[k] = wrap_ssd4((s).x, lo, ssd[k]); ssd[k] = wrap_ssd4((s).y, hi, ssd[k]);        \
-                 sad[k] = sad4((s).x, lo, sad[k]); sad[k] = sad4((s).y, hi, sad[k]); } while (0)
+            do { wrap_ssd_sad4((s).x, lo, ssd[k], sad[k]); wrap_ssd_sad4((s).y, hi, ssd[k], sad[k]); } while (0)
 #pragma unroll
             for (int rr = -1; rr < 8; rr++) {
                 const int row = plane_row(Y + rr);
