@@ -41,6 +41,7 @@ struct SpSharedT {
     int32_t  pu_dir[NPU];
     uint32_t pu_imv[NPU];               // MV at entry of the current stage
     uint32_t pu_win[NPU];               // winning half-pel candidate (1..8) of the PU, 0 = the integer position stays
+    uint32_t rowoff[kPlRows + 2];       // plane_row() of every window row: one LDS instead of five integer instructions
     int32_t  bbox[4];                   // min X, min Y, max -X... see the kernel: bounding box of the blocks' window positions
 };
 
@@ -92,8 +93,8 @@ __device__ __forceinline__ void pu_blocks(int pu, int& L, int& bx, int& by, int&
 }
 
 // 8 bytes at byte column c of row r of a plane (unaligned)
-__device__ __forceinline__ uint2 load8(const uint32_t* plane, int r, int c) {
-    const uint32_t* w = plane + plane_row(r) + (c >> 2);
+__device__ __forceinline__ uint2 load8(const uint32_t* plane, const uint32_t* rowoff, int r, int c) {
+    const uint32_t* w = plane + rowoff[r] + (c >> 2);
     const uint32_t sh = (c & 3) * 8;
     const uint32_t a = w[0], b = w[1], d = w[2];
     return make_uint2(__funnelshift_r(a, b, sh), __funnelshift_r(b, d, sh));
@@ -174,6 +175,7 @@ __device__ __forceinline__ bool pu_leader_any(int wb, int hb, int lane) {
 
 // Ext = the 209-PU mode: 14 PU classes ("levels") instead of 4; the non-square PUs live in SbScratchExt. Every level
 // is 64 8x8-block tasks, so a warp always works on one level.
+#define PROW(r) ((int)sh.rowoff[r])
 template <bool Ext>
 __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
     constexpr int NPU = Ext ? kMaxPu : kNumPu, NLEV = Ext ? kMaxLevels : kNumLevels;
@@ -204,6 +206,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         if (tid >= kNumPu && tid < NPU) { sh.pu_sad[tid] = scx.best_sad[list][tid - kNumPu]; sh.pu_mv[tid] = scx.best_mv[list][tid - kNumPu]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
     }
     if (tid < 4) sh.bbox[tid] = 0x7FFFFFFF;
+    if (tid < kPlRows + 2) sh.rowoff[tid] = (uint32_t)plane_row(tid);
     __syncthreads();
     // The refinement only reads the window around the 256 (level, 8x8 block) positions the full-pel search chose
     // (every later MV stays within one integer pixel of them), so the window that is staged and interpolated is their
@@ -248,7 +251,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         for (int t = tid; t < wr * ww; t += kSpThreads) {
             const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
             const uint32_t* w = raw + r * kRawPitchSp + q + c;
-            sh.plane[S_A][plane_row(r) + c] = __funnelshift_r(w[0], w[1], bs);
+            sh.plane[S_A][PROW(r) + c] = __funnelshift_r(w[0], w[1], bs);
         }
     }
     __syncthreads();
@@ -256,11 +259,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         // ---- plane B (horizontal filter of A): B(x) = f(A[x-1], A[x], A[x+1], A[x+2]) on every word but the last
         for (int t = tid; t < wr * ww; t += kSpThreads) {
             const int r = (int)__umulhi((uint32_t)t, inv_ww), c = t - r * ww;
-            const uint32_t* a = sh.plane[S_A] + plane_row(r) + c;
+            const uint32_t* a = sh.plane[S_A] + PROW(r) + c;
             if (c < ww - 1) {
                 const uint32_t w1 = a[0], w2 = a[1];
                 const uint32_t left = c ? __funnelshift_r(a[-1], w1, 24) : w1 << 8;
-                sh.plane[S_B][plane_row(r) + c] = filt4(left, w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16));
+                sh.plane[S_B][PROW(r) + c] = filt4(left, w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16));
             }
         }
         __syncthreads();
@@ -273,11 +276,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             const int r0 = 1 + chunk * per, r1 = min(r0 + per, wr - 2);
             if (chunk < n_chunks && r0 < r1) {
                 const uint32_t* pa = sh.plane[S_A] + c; const uint32_t* pb = sh.plane[S_B] + c;
-                uint32_t a0 = pa[plane_row(r0 - 1)], a1 = pa[plane_row(r0)], a2 = pa[plane_row(r0 + 1)];
-                uint32_t b0 = pb[plane_row(r0 - 1)], b1 = pb[plane_row(r0)], b2 = pb[plane_row(r0 + 1)];
+                uint32_t a0 = pa[PROW(r0 - 1)], a1 = pa[PROW(r0)], a2 = pa[PROW(r0 + 1)];
+                uint32_t b0 = pb[PROW(r0 - 1)], b1 = pb[PROW(r0)], b2 = pb[PROW(r0 + 1)];
 #pragma unroll 2
                 for (int r = r0; r < r1; r++) {
-                    const int o2 = plane_row(r + 2), o = plane_row(r);
+                    const int o2 = PROW(r + 2), o = PROW(r);
                     const uint32_t a3 = pa[o2], b3 = pb[o2];
                     sh.plane[S_H][o + c] = filt4(a0, a1, a2, a3);
                     sh.plane[S_J][o + c] = filt4(b0, b1, b2, b3);
@@ -314,7 +317,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             do { wrap_ssd_sad4((s).x, lo, ssd[k], sad[k]); wrap_ssd_sad4((s).y, hi, ssd[k], sad[k]); } while (0)
 #pragma unroll
             for (int rr = -1; rr < 8; rr++) {
-                const int row = plane_row(Y + rr);
+                const int row = PROW(Y + rr);
                 const uint32_t* ph = sh.plane[S_H] + row + wa;
                 const uint32_t h0 = ph[0], h1 = ph[1], h2 = ph[2];
                 const uint32_t hl = __funnelshift_r(h0, h1, sa), hh = __funnelshift_r(h1, h2, sa);
@@ -440,7 +443,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                     const int x1 = X + q[1], y1 = Y + q[2], x2 = X + q[4], y2 = Y + q[5];
 #pragma unroll
                     for (int r = 0; r < 8; r++) {
-                        const uint2 c1 = load8(p1, y1 + r, x1), c2 = load8(p2, y2 + r, x2);
+                        const uint2 c1 = load8(p1, sh.rowoff, y1 + r, x1), c2 = load8(p2, sh.rowoff, y2 + r, x2);
                         const uint32_t a0 = __vavgu4(c1.x, c2.x), a1 = __vavgu4(c1.y, c2.y);
                         ssd = true_ssd4(src[r].x, a0, ssd); ssd = true_ssd4(src[r].y, a1, ssd);
                         sad = sad4(src[r].x, a0, sad); sad = sad4(src[r].y, a1, sad);
@@ -496,9 +499,9 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             uint32_t* dst = reinterpret_cast<uint32_t*>(pred) + (by * 8) * 16 + bx * 2;
 #pragma unroll
             for (int r = 0; r < 8; r++) {
-                uint2 c = load8(sh.plane[f[0]], Y + f[2] + r, X + f[1]);
+                uint2 c = load8(sh.plane[f[0]], sh.rowoff, Y + f[2] + r, X + f[1]);
                 if (f[3] >= 0) {
-                    const uint2 d = load8(sh.plane[f[3]], Y + f[5] + r, X + f[4]);
+                    const uint2 d = load8(sh.plane[f[3]], sh.rowoff, Y + f[5] + r, X + f[4]);
                     c.x = __vavgu4(c.x, d.x); c.y = __vavgu4(c.y, d.y);
                 }
                 dst[r * 16] = c.x; dst[r * 16 + 1] = c.y;
