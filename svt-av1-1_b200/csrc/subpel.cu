@@ -127,10 +127,22 @@ __device__ __forceinline__ uint32_t filt4_lanes(uint32_t a, uint32_t b, uint32_t
     v = __vmaxu2(v, 0x01000100u);
     return __vminu2(v, 0x01FF01FFu);
 }
-__device__ __forceinline__ uint32_t filt4(uint32_t t0, uint32_t t1, uint32_t t2, uint32_t t3) {
-    const uint32_t e = filt4_lanes(__byte_perm(t0, 0, 0x4240), __byte_perm(t1, 0, 0x4240), __byte_perm(t2, 0, 0x4240), __byte_perm(t3, 0, 0x4240));
-    const uint32_t o = filt4_lanes(__byte_perm(t0, 0, 0x4341), __byte_perm(t1, 0, 0x4341), __byte_perm(t2, 0, 0x4341), __byte_perm(t3, 0, 0x4341));
-    return __byte_perm(e, o, 0x6240);
+// The same filter from tap words already split into their even / odd byte lanes (a vertical pass slides over the rows:
+// every row word is split once instead of four times) ...
+struct Lanes { uint32_t e, o; };
+__device__ __forceinline__ Lanes split_lanes(uint32_t t) {
+    Lanes l; l.e = __byte_perm(t, 0, 0x4240); l.o = __byte_perm(t, 0, 0x4341); return l;
+}
+__device__ __forceinline__ uint32_t filt4_split(const Lanes& a, const Lanes& b, const Lanes& c, const Lanes& d) {
+    return __byte_perm(filt4_lanes(a.e, b.e, c.e, d.e), filt4_lanes(a.o, b.o, c.o, d.o), 0x6240);
+}
+// ... and along a row: with left = bytes x-1..x+2, w1 = x..x+3, w2 = x+4..x+7 the eight lane words of the four byte-shifted
+// taps are only five different byte pairs (x-1,x+1) (x,x+2) (x+1,x+3) (x+2,x+4) (x+3,x+5)
+__device__ __forceinline__ uint32_t filt4_row(uint32_t left, uint32_t w1, uint32_t w2) {
+    const uint32_t f16 = __funnelshift_r(w1, w2, 16);
+    const uint32_t pm = __byte_perm(left, 0, 0x4240), p0 = __byte_perm(w1, 0, 0x4240), p1 = __byte_perm(w1, 0, 0x4341);
+    const uint32_t p2 = __byte_perm(f16, 0, 0x4240), p3 = __byte_perm(f16, 0, 0x4341);
+    return __byte_perm(filt4_lanes(pm, p0, p1, p2), filt4_lanes(p0, p1, p2, p3), 0x6240);
 }
 // validity of quarter-pel candidate k (order L R T B TL TR BR BL) given the best half-pel direction (ME.c:2859-2881):
 // the candidate itself or one of its two neighbours in the 8-cycle TL,T,TR,R,BR,B,BL,L; mirrored when the
@@ -263,7 +275,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             if (c < ww - 1) {
                 const uint32_t w1 = a[0], w2 = a[1];
                 const uint32_t left = c ? __funnelshift_r(a[-1], w1, 24) : w1 << 8;
-                sh.plane[S_B][PROW(r) + c] = filt4(left, w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16));
+                sh.plane[S_B][PROW(r) + c] = filt4_row(left, w1, w2);
             }
         }
         __syncthreads();
@@ -276,14 +288,14 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             const int r0 = 1 + chunk * per, r1 = min(r0 + per, wr - 2);
             if (chunk < n_chunks && r0 < r1) {
                 const uint32_t* pa = sh.plane[S_A] + c; const uint32_t* pb = sh.plane[S_B] + c;
-                uint32_t a0 = pa[PROW(r0 - 1)], a1 = pa[PROW(r0)], a2 = pa[PROW(r0 + 1)];
-                uint32_t b0 = pb[PROW(r0 - 1)], b1 = pb[PROW(r0)], b2 = pb[PROW(r0 + 1)];
+                Lanes a0 = split_lanes(pa[PROW(r0 - 1)]), a1 = split_lanes(pa[PROW(r0)]), a2 = split_lanes(pa[PROW(r0 + 1)]);
+                Lanes b0 = split_lanes(pb[PROW(r0 - 1)]), b1 = split_lanes(pb[PROW(r0)]), b2 = split_lanes(pb[PROW(r0 + 1)]);
 #pragma unroll 2
                 for (int r = r0; r < r1; r++) {
                     const int o2 = PROW(r + 2), o = PROW(r);
-                    const uint32_t a3 = pa[o2], b3 = pb[o2];
-                    sh.plane[S_H][o + c] = filt4(a0, a1, a2, a3);
-                    sh.plane[S_J][o + c] = filt4(b0, b1, b2, b3);
+                    const Lanes a3 = split_lanes(pa[o2]), b3 = split_lanes(pb[o2]);
+                    sh.plane[S_H][o + c] = filt4_split(a0, a1, a2, a3);
+                    sh.plane[S_J][o + c] = filt4_split(b0, b1, b2, b3);
                     a0 = a1; a1 = a2; a2 = a3; b0 = b1; b1 = b2; b2 = b3;
                 }
             }
@@ -445,8 +457,9 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                     for (int r = 0; r < 8; r++) {
                         const uint2 c1 = load8(p1, sh.rowoff, y1 + r, x1), c2 = load8(p2, sh.rowoff, y2 + r, x2);
                         const uint32_t a0 = __vavgu4(c1.x, c2.x), a1 = __vavgu4(c1.y, c2.y);
-                        ssd = true_ssd4(src[r].x, a0, ssd); ssd = true_ssd4(src[r].y, a1, ssd);
-                        sad = sad4(src[r].x, a0, sad); sad = sad4(src[r].y, a1, sad);
+                        const uint32_t d0 = __vabsdiffu4(src[r].x, a0), d1 = __vabsdiffu4(src[r].y, a1);   // SSD and SAD from one word
+                        ssd = __dp4a(d0, d0, ssd); ssd = __dp4a(d1, d1, ssd);
+                        sad = __dp4a(d0, 0x01010101u, sad); sad = __dp4a(d1, 0x01010101u, sad);
                     }
                 }
                 if constexpr (Ext) {
