@@ -98,18 +98,21 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
         const int wrows = i1 - i0 + extra;
         const int wcols = 2 * tpr + W;
         group_bar(bar_id);                              // previous users of the window are done
-        {   // lane = window column, the two warps of the group take alternate rows: the row pointer advances by a constant,
-            // the misalignment of the window's first byte is the same on every row (the pitch is a multiple of 64), so a
-            // word costs two loads, one funnel shift and one store (the per-word division and 64-bit address arithmetic
-            // of a flat index were a quarter of this kernel's instructions)
+        {   // lane = (row within the warp's row bundle, window column): narrow windows (<= 16 / <= 8 words) put 2 / 4 rows
+            // on a warp so that few lanes idle; the two warps of the group take alternate bundles. The row pointer advances
+            // by a constant and the misalignment of the window's first byte is the same on every row (the pitch is a
+            // multiple of 64), so a word costs two loads, one funnel shift and one store (the per-word division and
+            // 64-bit address arithmetic of a flat index were a quarter of this kernel's instructions)
             const uint8_t* p0 = rp.at(rx, ry + i0);
             const uint32_t m = (uint32_t)(uintptr_t)p0 & 3u, sh8 = m * 8u;
-            const int wstride = rp.stride >> 2, wi = gtid >> 5;
-            for (int c = gtid & 31; c < wcols; c += 32) {
-                const uint32_t* a = reinterpret_cast<const uint32_t*>(p0 - m) + c + wi * wstride;
-                uint32_t* d = win + wi * pitch + c;
+            const int csh = wcols <= 8 ? 3 : wcols <= 16 ? 4 : 5, rpi = 32 >> csh;       // rows per warp iteration
+            const int lane = gtid & 31, c0 = lane & ((1 << csh) - 1), rfirst = (gtid >> 5) * rpi + (lane >> csh);
+            const int wstride = rp.stride >> 2;
+            for (int c = c0; c < wcols; c += 32) {
+                const uint32_t* a = reinterpret_cast<const uint32_t*>(p0 - m) + c + rfirst * wstride;
+                uint32_t* d = win + rfirst * pitch + c;
 #pragma unroll 4
-                for (int r = wi; r < wrows; r += 2, a += 2 * wstride, d += 2 * pitch)
+                for (int r = rfirst; r < wrows; r += 2 * rpi, a += 2 * rpi * wstride, d += 2 * rpi * pitch)
                     *d = __funnelshift_r(__ldg(a), __ldg(a + 1), sh8);
             }
         }
