@@ -18,7 +18,7 @@ namespace svtme {
 constexpr int kHmeThreads = 256;
 constexpr int kGroupThreads = 64;
 constexpr int kRegionWinWords = 2560;
-constexpr int kSrcPitch = 17, kQPitch = 9;      // padded so that lanes on different block rows hit different banks          // 10 KB window buffer per region group
+constexpr int kSrcPitch = 18, kQPitch = 10;      // padded so that lanes on different block rows hit different banks          // 10 KB window buffer per region group
 
 struct HmeShared {
     uint32_t src_even[32 * kSrcPitch];   // even rows of the 64x64 source SB
@@ -85,12 +85,17 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
     const int tpr = (saw + 7) >> 3;                     // 8-position tiles per search row
     const int pitch = (2 * tpr + W) | 1;                // window words per row (odd)
     const int extra = 2 * (rows - 1);
-    const int chunk = max(1, kRegionWinWords / pitch - extra);
+    // (2560 / pitch by an approximate float division: a non-integer quotient is at least 1/pitch >= 1/131 away from an
+    // integer, the approximation error is below 1e-3, and +0.002 keeps exact quotients from truncating one too low)
+    const int chunk = max(1, (int)(__fdividef((float)kRegionWinWords, (float)pitch) + 0.002f) - extra);
     const int rs = gtid & (RSPLIT - 1);
     constexpr int kTilesPerPass = kGroupThreads / RSPLIT;
     // t / d as umulhi(t, 2^32 / d + 1): exact while t * d < 2^32 (t, d are a few thousand at most here); d == 1 would
     // need the multiplier 2^32, so a one-tile row (search width <= 8) keeps the plain index
-    const uint32_t inv_tpr = tpr > 1 ? 0xFFFFFFFFu / (uint32_t)tpr + 1u : 0u;
+    // reciprocal over-estimated by 2e-6 relative (>= the 2.4e-7 error of the approximate division): umulhi(t, inv) is then
+    // floor(t / tpr + t / tpr * 2.3e-6), exact for the t < 2^13, tpr <= 63 of a window chunk; an integer division here
+    // cost every thread ~25 instructions per level
+    const uint32_t inv_tpr = tpr > 1 ? (uint32_t)(__fdividef(4294967296.0f, (float)tpr) * 1.000002f) : 0u;
     uint32_t best = 0xFFFFFFFFu;
     if (gtid == 0) *best_slot = 0xFFFFFFFFu;
     for (int i0 = 0; i0 < sah; i0 += chunk) {
@@ -132,12 +137,14 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
                 const uint32_t* sr = src + rs * SP;
                 for (int r = rs; r < rows; r += RSPLIT, wr += 2 * RSPLIT * pitch, sr += RSPLIT * SP) {
                     uint32_t a = wr[0], sprev = 0;
+                    uint2 spair = make_uint2(0u, 0u);
 #pragma unroll
                     for (int c = 0; c <= W; c++) {
                         const uint32_t b = wr[c + 1];
                         const uint32_t v1 = __funnelshift_r(a, b, 8), v2 = __funnelshift_r(a, b, 16), v3 = __funnelshift_r(a, b, 24);
                         if (c < W) {                    // positions 8jt + phase: source word c
-                            const uint32_t sw = sr[c];
+                            if ((c & 1) == 0) spair = *reinterpret_cast<const uint2*>(sr + c);   // rows are 8-byte aligned: W, SP even
+                            const uint32_t sw = (c & 1) ? spair.y : spair.x;
                             if (QUIRK && c >= 4) { hi[0][0] = sad4(sw, a, hi[0][0]); hi[0][1] = sad4(sw, v1, hi[0][1]); hi[0][2] = sad4(sw, v2, hi[0][2]); hi[0][3] = sad4(sw, v3, hi[0][3]); }
                             else                 { lo[0][0] = sad4(sw, a, lo[0][0]); lo[0][1] = sad4(sw, v1, lo[0][1]); lo[0][2] = sad4(sw, v2, lo[0][2]); lo[0][3] = sad4(sw, v3, lo[0][3]); }
                             if (c >= 1) {               // positions 8jt + 4 + phase: source word c - 1
@@ -193,7 +200,7 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
 __device__ __forceinline__ int round_sa_width(int w) { return (w < 8) ? 8 : (w & 7) ? w + (w - ((w >> 3) << 3)) : w; }
 
 __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restrict__ jobs, int list) {
-    __shared__ HmeShared sh;
+    __shared__ __align__(16) HmeShared sh;
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
