@@ -101,15 +101,10 @@ __device__ __forceinline__ uint2 load8(const uint32_t* plane, const uint32_t* ro
 }
 // Quirk Q5 squares the per-byte difference (a - b) mod 256 read as int8. |a - b| read as int8 has the same square
 // (for a < b the two bytes are negatives of each other mod 256, and -128 squares like 128), so one VABSDIFF4 replaces
-// the five-instruction byte-wise subtraction and the same word also gives the SAD by a second dp4a (FMA pipe).
+// the five-instruction byte-wise subtraction.
 __device__ __forceinline__ uint32_t wrap_ssd4(uint32_t a, uint32_t b, uint32_t acc) {
     const uint32_t t = __vabsdiffu4(a, b);
     return (uint32_t)__dp4a((int)t, (int)t, (int)acc);
-}
-__device__ __forceinline__ void wrap_ssd_sad4(uint32_t a, uint32_t b, uint32_t& ssd, uint32_t& sad) {
-    const uint32_t t = __vabsdiffu4(a, b);
-    ssd = (uint32_t)__dp4a((int)t, (int)t, (int)ssd);
-    sad = __dp4a(t, 0x01010101u, sad);
 }
 __device__ __forceinline__ uint32_t true_ssd4(uint32_t a, uint32_t b, uint32_t acc) {
     const uint32_t d = __vabsdiffu4(a, b);
@@ -307,12 +302,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         __syncthreads();
         // ---- half-pel: one thread per (level, 8x8 block) walks the ten plane rows its nine candidates share
         // (L/R read the same three B words per row, T/B the same H rows, the four diagonals the same J rows and words);
-        // wrapping-SSD and SAD are summed per (candidate, PU) with shared atomics
-        // Only the SAD of the WINNING candidate of a PU is ever used (ME.c:1934-1950), so the eight per-block SADs stay
-        // with the thread (packed 16-bit, <= 16320 each) and only the winner's is summed over the PU after the decision.
-        constexpr int kIters = (NLEV * 64 + kSpThreads - 1) / kSpThreads;
-        uint4 blk_sad[kIters];
-        for (int t = tid, it = 0; t < NLEV * 64; t += kSpThreads, it++) {
+        // the wrapping SSD is summed per (candidate, PU).
+        // Only the SAD of the WINNING candidate of a PU is ever used (ME.c:1934-1950), so the candidates' SADs
+        // are not computed here at all: after the decision every block recomputes the SAD of its PU's winner (eight rows of
+        // one plane) and that is summed over the PU.
+        for (int t = tid; t < NLEV * 64; t += kSpThreads) {
             const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
             const int pu = block_pu(L, bx, by);
             const uint32_t mv = sh.pu_imv[pu];
@@ -322,11 +316,11 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
             uint2 src[8];
 #pragma unroll
             for (int r = 0; r < 8; r++) src[r] = *reinterpret_cast<const uint2*>(&sh.src[(by * 8 + r) * 16 + bx * 2]);
-            uint32_t ssd[9], sad[9];
+            uint32_t ssd[9];
 #pragma unroll
-            for (int k = 0; k < 9; k++) { ssd[k] = 0; sad[k] = 0; }
+            for (int k = 0; k < 9; k++) ssd[k] = 0;
 #define HP_ACC(k, lo, hi, s)                                                                           \
-            do { wrap_ssd_sad4((s).x, lo, ssd[k], sad[k]); wrap_ssd_sad4((s).y, hi, ssd[k], sad[k]); } while (0)
+            do { ssd[k] = wrap_ssd4((s).x, lo, ssd[k]); ssd[k] = wrap_ssd4((s).y, hi, ssd[k]); } while (0)
 #pragma unroll
             for (int rr = -1; rr < 8; rr++) {
                 const int row = PROW(Y + rr);
@@ -354,7 +348,6 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                 }
             }
 #undef HP_ACC
-            blk_sad[it] = make_uint4(sad[1] | (sad[2] << 16), sad[3] | (sad[4] << 16), sad[5] | (sad[6] << 16), sad[7] | (sad[8] << 16));
             // a warp holds 8x4 blocks of ONE level: sum the blocks of each PU inside the warp, one lane per PU writes
             if constexpr (Ext) {
                 const int pwb = kLevelWb[L], phb = kLevelHb[L];
@@ -404,14 +397,22 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         }
         __syncthreads();
         // ---- SAD of the winning half-pel candidate, summed over the PU's blocks
-        for (int t = tid, it = 0; t < NLEV * 64; t += kSpThreads, it++) {
+        for (int t = tid; t < NLEV * 64; t += kSpThreads) {
             const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
             const int pu = block_pu(L, bx, by);
             const int kw = (int)sh.pu_win[pu];
-            const uint4 pk = blk_sad[it];
-            const int w = (kw - 1) >> 1;
-            const uint32_t word = w == 0 ? pk.x : w == 1 ? pk.y : w == 2 ? pk.z : pk.w;
-            uint32_t v = kw ? ((word >> (((kw - 1) & 1) * 16)) & 0xFFFFu) : 0u;
+            uint32_t v = 0;
+            if (kw) {                                          // the block's SAD at the winning candidate's plane position
+                const uint32_t mv = sh.pu_imv[pu];
+                const int x = kMargin + (mv_x(mv) >> 2) - sax + bx * 8 + kHalf[kw][1], y = kMargin + (mv_y(mv) >> 2) - say + by * 8 + kHalf[kw][2];
+                const uint32_t* pl = sh.plane[kHalf[kw][0]];
+#pragma unroll
+                for (int r = 0; r < 8; r++) {
+                    const uint2 c = load8(pl, sh.rowoff, y + r, x);
+                    const uint2 sv = *reinterpret_cast<const uint2*>(&sh.src[(by * 8 + r) * 16 + bx * 2]);
+                    v = sad4(sv.x, c.x, v); v = sad4(sv.y, c.y, v);
+                }
+            }
             if constexpr (Ext) {
                 const int pwb = kLevelWb[L], phb = kLevelHb[L];
                 v = pu_sum_any(v, pwb, phb);
@@ -421,6 +422,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
                 if (kw && pu_leader(L, tid & 31)) { if (L == 0) atomicAdd(&sh.pu_sad[0], v); else sh.pu_sad[pu] = v; }
             }
         }
+        __syncthreads();                                       // the loop above reads pu_imv
         if (tid < NPU) sh.pu_imv[tid] = sh.pu_mv[tid];
         for (int t = tid; t < 9 * NPU; t += kSpThreads) { (&sh.sum_ssd[0][0])[t] = 0; (&sh.sum_sad[0][0])[t] = 0; }
         __syncthreads();
