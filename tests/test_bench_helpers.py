@@ -1,0 +1,33 @@
+"""Host-side helpers of bench.py (no GPU): the algorithmic work model behind `roofline` / `roofline_step` and the mini-GOP job list."""
+import importlib
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+
+pkg = importlib.import_module("svt-av1-1_b200")
+
+
+def test_fullpel_work_model():
+    # 64 x 64 positions x 64 x 32 source bytes (even rows only): DESIGN.md section 3.1
+    assert bench.FULLPEL_BYTE_SADS_PER_SB_LIST == 4096 * 2048
+
+
+def test_hme_work_model_follows_the_layer_multipliers():
+    # 1080p, hierarchical levels 3: level-0 regions 48 x 24 scaled by 200 / 140 / 100 / 70 % (EbDefinitions.h:2980-2996)
+    want = {0: 4 * (96 * 48 * 128 + 16 * 16 * 512 + 8 * 8 * 2048), 1: 4 * (67 * 33 * 128 + 16 * 16 * 512 + 8 * 8 * 2048),
+            2: 4 * (48 * 24 * 128 + 16 * 16 * 512 + 8 * 8 * 2048), 3: 4 * (33 * 16 * 128 + 16 * 16 * 512 + 8 * 8 * 2048)}
+    for tl, w in want.items():
+        p = pkg.default_params(1920, 1080, 2, tl, 3, 1)
+        assert bench.hme_byte_sads_per_sb_list(p) == w, tl
+
+
+def test_gop_jobs_cover_every_picture_once():
+    jobs = bench.gop_jobs()
+    assert len(jobs) == bench.N_PICS - 1
+    assert sorted(j[0] for j in jobs) == list(range(1, bench.N_PICS))
+    for poc, tl, r0, r1 in jobs:
+        assert 0 <= r0 < bench.N_PICS and 0 <= r1 < bench.N_PICS and r0 != poc and r1 != poc
+        assert tl == (0 if poc % 8 == 0 else 1 if poc % 4 == 0 else 2 if poc % 2 == 0 else 3)
