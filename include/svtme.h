@@ -171,6 +171,21 @@ int32_t svtme_synchronize(SvtMeContext *ctx);
 /* Make the compute stream wait for all transfers enqueued so far (for timing with events on svtme_stream). */
 int32_t svtme_join(SvtMeContext *ctx);
 
+/* Allocation-free variant of svtme_motion_estimate for ONE picture in the 85-PU mode. It has no counterpart in the
+ * reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it). The job table, the inter-kernel SB scratch, the
+ * result rows and the debug rows live in ONE file-scope device array of the library (about 10 MB, resident on every
+ * GPU that loads the library until the process exits) instead of the context's cudaMalloc'ed batch ring; the call
+ * itself calls no cudaMalloc / cudaFree / cudaMallocHost and creates no stream or event. The caller still passes the
+ * inputs (pictures uploaded into the context's slots beforehand) and the outputs (job->results / job->debug, host
+ * memory). Limits: pictures of at most SVTME_STATIC_MAX_SBS 64x64 SBs (e.g. 1280x720 = 240) and num_pus == 85,
+ * anything else returns SVTME_ERR_BAD_PARAMETER with the reason in svtme_last_error. Synchronous: it returns when the
+ * rows are in the caller's buffers. Every context of the process on one device shares the array, which keeps the
+ * previous call's contents (this call's output rows are cleared first); the library serialises calls of one process
+ * with a mutex, and calls that overlap on the GPU by any other route would race on it. */
+#define SVTME_STATIC_MAX_SBS 256
+int32_t svtme_motion_estimate_static(SvtMeContext *ctx, const SvtMeJob *job);
+
 /* Introspection for benchmarks: the CUDA stream (cudaStream_t as void*) and the number of kernel
  * launches issued so far. */
 void   *svtme_stream(SvtMeContext *ctx);

@@ -14,7 +14,7 @@ EXPORTED_SYMBOLS = (
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
     "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
-    "svtme_pictures_upload_device", "svtme_pictures_upload",
+    "svtme_pictures_upload_device", "svtme_pictures_upload", "svtme_motion_estimate_static",
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
                         "svtme_lcu_motion_estimate", "svtme_lcu_session_stats")
@@ -108,6 +108,8 @@ def load_library():
         f = getattr(lib, name)
         f.restype = C.c_int32
         f.argtypes = [C.c_void_p, C.POINTER(SvtMeJob), C.c_int32]
+    lib.svtme_motion_estimate_static.restype = C.c_int32
+    lib.svtme_motion_estimate_static.argtypes = [C.c_void_p, C.POINTER(SvtMeJob)]
     lib.svtme_synchronize.restype = C.c_int32
     lib.svtme_synchronize.argtypes = [C.c_void_p]
     lib.svtme_synchronize_uploads.restype = C.c_int32
@@ -262,6 +264,12 @@ class MeContext:
     def motion_estimate(self, specs, want_debug=False, sb_rows=None):
         jobs, results, debug = self.make_jobs(specs, want_debug, sb_rows=sb_rows)
         self._check(self.lib.svtme_motion_estimate(self._h, jobs, len(specs)), "svtme_motion_estimate")
+        return results, debug
+
+    def motion_estimate_static(self, spec, want_debug=False, sb_rows=None):
+        """svtme_motion_estimate_static: one picture, no device allocation inside the call (static scratch array)."""
+        jobs, results, debug = self.make_jobs([spec], want_debug, sb_rows=sb_rows)
+        self._check(self.lib.svtme_motion_estimate_static(self._h, C.byref(jobs[0])), "svtme_motion_estimate_static")
         return results, debug
 
     def motion_estimate_async(self, jobs):

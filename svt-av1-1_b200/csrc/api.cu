@@ -680,3 +680,95 @@ int32_t svtme_kernel_times(SvtMeContext* ctx, double* ms, int64_t* launches, int
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// svtme_motion_estimate_static: the one-picture ME chain with its job table, inter-kernel SbScratch, result rows and
+// debug rows in a file-scope device array instead of cudaMalloc'ed ring buffers (for callers that may not allocate:
+// CUDA graph capture, tight serving loops). No counterpart in the reference.
+//
+// g_static_arena is a HOST-SIDE STAND-IN in this file's host code, not a device address: the address the kernels get
+// comes from cudaGetSymbolAddress, asked once per device with that device current (static_arena_base). Every context
+// of the process on one device shares the array and it keeps the previous call's contents; the call holds
+// g_static_mu until its results are on the host, so calls of one process never overlap on the GPU.
+struct StaticArena {
+    DJob job;
+    SbScratch scratch[SVTME_STATIC_MAX_SBS];
+    SvtMePuResult results[(size_t)SVTME_STATIC_MAX_SBS * kNumPu];
+    SvtMeSbDebug debug[SVTME_STATIC_MAX_SBS];
+};
+static __device__ __align__(256) unsigned char g_static_arena[(sizeof(StaticArena) + 255) / 256 * 256];
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static StaticArena* g_static_base[kStaticMaxDevices] = {};   // device address of g_static_arena per device
+
+// caller holds g_static_mu and has made ctx->device current
+static int32_t static_arena_base(SvtMeContext* ctx, StaticArena** out) {
+    if (ctx->device < 0 || ctx->device >= kStaticMaxDevices)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: device ordinal beyond 63");
+    if (!g_static_base[ctx->device]) {
+        void* p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_static_arena));
+        if (!p || ((uintptr_t)p & 255)) return fail(ctx, SVTME_ERR_UNDEFINED, "svtme_motion_estimate_static: bad symbol address");
+        g_static_base[ctx->device] = static_cast<StaticArena*>(p);
+    }
+    *out = g_static_base[ctx->device];
+    return SVTME_OK;
+}
+
+extern "C" int32_t svtme_motion_estimate_static(SvtMeContext* ctx, const SvtMeJob* job) {
+    if (!ctx || !job) return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: null argument");
+    const SvtMeJob& j = *job;
+    std::string why;
+    if (!params_ok(ctx, j.params, why)) return fail(ctx, SVTME_ERR_BAD_PARAMETER, why);
+    if (j.params.num_pus != SVTME_SQUARE_PU_COUNT)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: only the 85-PU mode has static scratch (num_pus must be 85)");
+    if (ctx->n_sb > SVTME_STATIC_MAX_SBS)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: picture has " + std::to_string(ctx->n_sb) +
+                    " SBs, the static scratch holds SVTME_STATIC_MAX_SBS = " + std::to_string(SVTME_STATIC_MAX_SBS));
+    const int nslots = (int)ctx->slots.size();
+    const int r1 = j.params.num_lists == 2 ? j.ref1_slot : j.ref0_slot;
+    if (j.cur_slot < 0 || j.cur_slot >= nslots || j.ref0_slot < 0 || j.ref0_slot >= nslots || r1 < 0 || r1 >= nslots)
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: slot out of range");
+    const bool whole = j.sb_row_begin == 0 && j.sb_row_end == 0;
+    if (!whole && (j.sb_row_begin < 0 || j.sb_row_end <= j.sb_row_begin || j.sb_row_end > ctx->sb_rows))
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: SB row range out of the picture");
+    CU(cudaSetDevice(ctx->device));
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    StaticArena* a = nullptr;
+    int32_t rc = static_arena_base(ctx, &a);
+    if (rc != SVTME_OK) return rc;
+    DJob d;
+    memset(&d, 0, sizeof(d));
+    d.cur = ctx->slots[j.cur_slot].pyr; d.ref[0] = ctx->slots[j.ref0_slot].pyr; d.ref[1] = ctx->slots[r1].pyr;
+    d.prm = j.params;
+    d.scratch = a->scratch; d.scratch_ext = nullptr; d.results = a->results;
+    d.debug = j.debug ? a->debug : nullptr;
+    d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
+    d.sb_begin = whole ? 0 : j.sb_row_begin * ctx->sb_cols;
+    d.sb_end = whole ? ctx->n_sb : j.sb_row_end * ctx->sb_cols;
+    const int n_sb = d.sb_end - d.sb_begin;
+    cudaStream_t st = ctx->stream;
+    for (int sl : { j.cur_slot, j.ref0_slot, r1 }) CU(cudaStreamWaitEvent(st, ctx->slots[sl].ready, 0));
+    // the array keeps the previous call's rows: clear the outputs of this call's range so that nothing stale can be
+    // mistaken for a result (the kernels themselves write every field they later read; SbScratch needs no clearing)
+    CU(cudaMemsetAsync(a->results + (size_t)d.sb_begin * kNumPu, 0, sizeof(SvtMePuResult) * (size_t)n_sb * kNumPu, st));
+    if (j.debug) CU(cudaMemsetAsync(a->debug + d.sb_begin, 0, sizeof(SvtMeSbDebug) * (size_t)n_sb, st));
+    CU(cudaMemcpyAsync(&a->job, &d, sizeof(DJob), cudaMemcpyHostToDevice, st));
+    for (int list = 0; list < j.params.num_lists; list++) {
+        launch_hme(&a->job, 1, n_sb, list, st);
+        launch_fullpel(&a->job, 1, n_sb, list, false, st);
+        launch_subpel(&a->job, 1, n_sb, list, false, st);
+        ctx->launches += 3;
+    }
+    launch_bipred_pack(&a->job, 1, n_sb, false, st);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (j.results)
+        CU(cudaMemcpyAsync(j.results, a->results + (size_t)d.sb_begin * kNumPu, sizeof(SvtMePuResult) * (size_t)n_sb * kNumPu,
+                           cudaMemcpyDeviceToHost, st));
+    if (j.debug)
+        CU(cudaMemcpyAsync(j.debug, a->debug + d.sb_begin, sizeof(SvtMeSbDebug) * (size_t)n_sb, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));                        // the pictures have been read and the rows are in the caller's buffers
+    return SVTME_OK;
+}
