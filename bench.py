@@ -28,6 +28,7 @@ import subprocess
 import sys
 import threading
 import time
+import zlib
 
 import numpy as np
 
@@ -38,8 +39,6 @@ W, H = 1920, 1080
 N_PICS = 121                      # POC 0 (intra) + 15 mini-GOPs of 8
 MINIGOP = [(8, 0, 0, 8), (4, 1, -4, 4), (2, 2, -2, 2), (6, 2, -2, 2), (1, 3, -1, 1), (3, 3, -1, 1), (5, 3, -1, 1), (7, 3, -1, 1)]
 SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
-# algorithmic work of the full-pel kernel per SB and list: 64x64 positions x (64 x 32 sub-sampled pixels)
-FULLPEL_BYTE_SADS_PER_SB_LIST = 64 * 64 * 64 * 32
 
 
 def hme_byte_sads_per_sb_list(prm):
@@ -63,6 +62,19 @@ USE_16BIT = False                 # me4k: pictures arrive as 16-bit samples (10-
 SHARD_SB_ROWS = False             # me4k: N ranks share every picture by SB rows (strong scaling)
 NUM_PUS = 85                      # me209: every picture searched with all 209 PUs (PIC_ALL_DEPTH_MODE, enc-mode 0)
 WITH_TXQ = False                  # streams: every frame also gets its luma residual plane transformed + quantised
+SEARCH_AREA = None                # --search-area N: full-pel search area N x N instead of the preset's 64 x 64 (the reference searches MIN(N, 127))
+
+
+def apply_search_area(prm):
+    if SEARCH_AREA:
+        prm.search_area_w = prm.search_area_h = SEARCH_AREA
+    return prm
+
+
+def fullpel_byte_sads_per_sb_list():
+    """algorithmic work of the full-pel kernel per SB and list: positions x (64 x 32 sub-sampled pixels)"""
+    n = min(SEARCH_AREA or 64, 127)
+    return n * n * 64 * 32
 
 
 def select_workload(name):
@@ -169,8 +181,9 @@ def _cpu_task(job):
     prm = M.default_params(M.load_oracle(), "meo", W, H, 2, tl, 3, 1 if tl < 3 else 0)
     prm.same_ref_poc = 1 if r0 == r1 else 0
     prm.num_pus = NUM_PUS
+    apply_search_area(prm)
     res, _ = M.motion_estimate(lib, pre, prm, _CPU["pyr"][poc], _CPU["pyr"][r0], _CPU["pyr"][r1], want_debug=False)
-    return int(res["dist0"].sum() & 0xFFFFFFFF)
+    return zlib.crc32(res.tobytes())                      # the whole me_results image of the picture (40-byte rows)
 
 
 def cpu_reference_available():
@@ -195,7 +208,8 @@ class CpuArm:
     def run(self, n_tasks):
         tasks = [self.jobs16[i % 16] for i in range(n_tasks)]
         t0 = time.perf_counter()
-        self.pool.map(_cpu_task, tasks, chunksize=1)
+        crcs = self.pool.map(_cpu_task, tasks, chunksize=1)
+        self.crc = {tasks[i][0]: crcs[i] for i in range(min(16, n_tasks))}     # poc -> CRC of the reference's me_results image
         return time.perf_counter() - t0
 
     def close(self):
@@ -209,6 +223,10 @@ def run_reference_impl(args, rank):
         return
     frames = synth_sequence(17, seed=1)
     arm = CpuArm(frames)
+    if arm.kind == "reference":                            # the workers run it; mapping it here too lets the driver's record of this
+        sys.path.insert(0, os.path.join(ROOT, "tests"))    # process's libraries show which CPU implementation the arm timed
+        import me_common as M_
+        M_.load_ref()
     n_tasks = max(32, 8 * arm.cores)
     for _ in range(args.warmup):
         arm.run(arm.cores)                                 # warm-up also fills each worker's pyramid cache
@@ -330,6 +348,7 @@ def run_gpu_impl(args, rank, world, local_rank):
         p = pkg.default_params(W, H, 2, tl, 3, 1 if tl < 3 else 0)
         p.same_ref_poc = 1 if r0 == r1 else 0
         p.num_pus = NUM_PUS
+        apply_search_area(p)
         specs.append((poc, r0, r1, p))
     sb_rows = None
     if SHARD_SB_ROWS and world > 1:
@@ -503,11 +522,11 @@ def run_gpu_impl(args, rank, world, local_rank):
         fp_ms, fp_n = kt["fullpel"]
         total_kernel_ms = sum(v[0] for v in kt.values())
         # algorithmic work of one full-pel launch: every SB of every picture of the batch, one list
-        sads_per_launch = FULLPEL_BYTE_SADS_PER_SB_LIST * n_sb * len(jobs)
+        sads_per_launch = fullpel_byte_sads_per_sb_list() * n_sb * len(jobs)
         achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n else None
         sb_cols_, n_sb_pic, full_rows_sb = (W + 63) // 64, ((W + 63) // 64) * ((H + 63) // 64), (H // 64) * ((W + 63) // 64)
         step_sads = (1 if SHARD_SB_ROWS else world) * sum(
-            sp[3].num_lists * (FULLPEL_BYTE_SADS_PER_SB_LIST * n_sb_pic + hme_byte_sads_per_sb_list(sp[3]) * full_rows_sb) for sp in specs)
+            sp[3].num_lists * (fullpel_byte_sads_per_sb_list() * n_sb_pic + hme_byte_sads_per_sb_list(sp[3]) * full_rows_sb) for sp in specs)
         traffic = None                                    # DRAM bytes per launch, scaled from the committed ncu capture
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))

@@ -21,8 +21,19 @@
  * PARITY PIN: checked bit-exactly against oracle/_ref/libsvtref.so (the reference's own objects)
  * by tests/test_oracle_vs_ref.py and against tests/golden/ vectors generated from it.
  *
- * Supported geometry: width, height multiples of 8; width % 64 in {0, 32} (the reference itself
- * dispatches a void function for 40/56-wide edge SBs: EbComputeSAD.h:143-147).
+ * Supported geometry: width, height multiples of 8; every width except width % 64 in {40, 56}: for those two
+ * edge-SB widths the reference dispatches a void function in hme_mv_center_check (EbComputeSAD.h:143-147) and its
+ * result is undefined. Edge SBs 8, 16, 24, 32 and 48 wide run the leaves the reference picks for them (ME.c:4417-4496,
+ * 4579-4615, 4711-4750): the C SadLoopKernel (C_DEFAULT/EbComputeSAD_C.c:72-120) for the block widths 2, 6, 12 of the
+ * decimated levels, the AVX2 cases 4 / 8 / 16 / 24 / 48 otherwise, with two more leaf quirks:
+ *   Q12 4-wide blocks, height % 4 == 0 (HME level 0 of 16-wide SBs, level 1 of 8-wide SBs): the 8-position groups of
+ *       the AVX2 kernels pair reference row 2 with source row 0 and reference row 0 with source row 2 inside every
+ *       group of four rows (the 128-bit halves of ss0 are swapped); the leftover (< 8 positions) code is right
+ *                                                     ASM_AVX2/EbComputeSAD_Intrinsic_AVX2.c:1650-1652, 3973-3975
+ *   Q13 24-wide blocks, height <= 16 (HME level 1 of 48-wide SBs): 16-bit sums with the min-subtraction trick of Q3,
+ *       value = min(a + b, 65535 + min_group(a)), a = columns 0-7 and 16-23, b = columns 8-15
+ *                                                     ASM_AVX2/EbComputeSAD_Intrinsic_AVX2.c:2123-2160
+ * Search areas up to 127 x 127 (MIN(search_area, 127), ME.c:6644-6645).
  *   Q10 width-8 PUs taller than 8 (8x16, 8x32; 209-PU mode): the half-pel "SSD" kernel picked by
  *       Log2f(width) is the fixed 8x8 one, so only the top eight rows are ranked   ME.c:1909-1916,
  *                                                     ASM_SSE4_1/EbPictureOperators_Intrinsic_SSE4_1.c:534-569
@@ -154,11 +165,22 @@ static int clip_center(int org, int c, int pad, int dim) {
 
 /* SadLoopKernel_AVX2_INTRIN / _HmeL0_ (EbComputeSAD_Intrinsic_AVX2.c:1609-3182, 3940-4139):
  * exhaustive search, positions visited row by row, eight at a time; a group replaces the
- * best only when strictly smaller, and inside a group the lowest index wins.
- *   l1_quirk = 1 reproduces the 32-wide, <=16-row branch (Q3); everything else used by the
+ * best only when strictly smaller, and inside a group the lowest index wins. The C SadLoopKernel
+ * (C_DEFAULT/EbComputeSAD_C.c:72-120: one position at a time, strict '<') is the same argmin.
+ *   quirk = SL_Q3  reproduces the 32-wide, <=16-row branch (Q3), SL_Q13 the 24-wide one (Q13), SL_Q12 the swapped
+ *   rows of the 4-wide kernels (Q12, full groups only); everything else used by the
  *   ME path is an exact 32-bit argmin (the 16-bit overflow branches recompute exactly). */
+enum { SL_EXACT = 0, SL_Q3 = 1, SL_Q13 = 2, SL_Q12 = 3 };
+static uint32_t sad4_rows_swapped(const uint8_t *s, int ss, const uint8_t *r, int rs, int h) {
+    uint32_t acc = 0;
+    for (int y = 0; y < h; y++) {
+        const int ry = (y & 3) == 0 ? y + 2 : (y & 3) == 2 ? y - 2 : y;     /* reference rows 0 and 2 of every four trade places */
+        for (int x = 0; x < 4; x++) acc += (uint32_t)abs((int)s[y * ss + x] - (int)r[ry * rs + x]);
+    }
+    return acc;
+}
 static void sad_loop(const uint8_t *src, int ss, const uint8_t *ref, int rs, int h, int w,
-                     int ref_row_stride, int saw, int sah, int l1_quirk,
+                     int ref_row_stride, int saw, int sah, int quirk,
                      uint64_t *best_sad, int *best_x, int *best_y) {
     uint32_t low = 0xffffff; int bx = 0, by = 0;
     for (int i = 0; i < sah; i++) {
@@ -166,17 +188,23 @@ static void sad_loop(const uint8_t *src, int ss, const uint8_t *ref, int rs, int
         for (int j = 0; j < saw; j += 8) {
             int n = MIN(8, saw - j);
             uint32_t v[8];
-            if (l1_quirk) {
+            if (quirk == SL_Q3 || quirk == SL_Q13) {
                 uint32_t lo[8], hi[8], mlo = 65535;
                 for (int k = 0; k < 8; k++) {
-                    if (k < n) {
+                    if (k >= n) lo[k] = hi[k] = 65535;     /* _mm_or_si128(s, s8) */
+                    else if (quirk == SL_Q3) {
                         lo[k] = sad_wxh(src, ss, rrow + j + k, rs, 16, h);
                         hi[k] = sad_wxh(src + 16, ss, rrow + j + k + 16, rs, 16, h);
-                    } else lo[k] = hi[k] = 65535;          /* _mm_or_si128(s, s8) */
+                    } else {
+                        lo[k] = sad_wxh(src, ss, rrow + j + k, rs, 8, h) + sad_wxh(src + 16, ss, rrow + j + k + 16, rs, 8, h);
+                        hi[k] = sad_wxh(src + 8, ss, rrow + j + k + 8, rs, 8, h);
+                    }
                     mlo = MIN(mlo, lo[k]);
                 }
                 for (int k = 0; k < 8; k++) v[k] = MIN(lo[k] + hi[k], 65535 + mlo);
                 n = 8;                                     /* masked lanes take part in minpos */
+            } else if (quirk == SL_Q12 && n == 8) {
+                for (int k = 0; k < 8; k++) v[k] = sad4_rows_swapped(src, ss, rrow + j + k, rs, h);
             } else {
                 for (int k = 0; k < n; k++) v[k] = sad_wxh(src, ss, rrow + j + k, rs, w, h);
             }
@@ -186,6 +214,13 @@ static void sad_loop(const uint8_t *src, int ss, const uint8_t *ref, int rs, int
         }
     }
     *best_sad = low; *best_x = bx; *best_y = by;
+}
+/* which leaf quirk applies to a block of w x h (h = rows actually summed) */
+static int sad_loop_quirk(int w, int h) {
+    if (w == 32 && h <= 16) return SL_Q3;
+    if (w == 24 && h <= 16) return SL_Q13;
+    if (w == 4 && (h & 3) == 0) return SL_Q12;
+    return SL_EXACT;
 }
 
 /* ------------------------------------------------------------------ per-SB state */
@@ -257,7 +292,7 @@ static void hme_level0(SbCtx *c, int list, int rw, int rh, int xc, int yc,
     clip_search_area(oy, &say, &sah, rp->origin_y - 1, rp->height);
     int bx, by;
     sad_loop(c->sixteenth_sb, 16, px(rp, ox + sax, oy + say), rp->stride * 2, h >> 1, w,
-             rp->stride, saw, sah, 0, sad, &bx, &by);
+             rp->stride, saw, sah, sad_loop_quirk(w, h >> 1), sad, &bx, &by);
     *sad *= 2;
     *xo = (int16_t)((bx + sax) * 4); *yo = (int16_t)((by + say) * 4);
 }
@@ -275,7 +310,7 @@ static void hme_level1(SbCtx *c, int list, int rw, int rh, int xc, int yc,
     clip_search_area(oy, &say, &sah, rp->origin_y - 1, rp->height);
     int bx, by;
     sad_loop(c->quarter_sb, 32 * 2, px(rp, ox + sax, oy + say), rp->stride * 2, h >> 1, w,
-             rp->stride, saw, sah, (w == 32 && (h >> 1) <= 16), sad, &bx, &by);
+             rp->stride, saw, sah, sad_loop_quirk(w, h >> 1), sad, &bx, &by);
     *sad *= 2;
     *xo = (int16_t)((bx + sax) * 2); *yo = (int16_t)((by + say) * 2);
 }
@@ -752,7 +787,7 @@ int meo_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
                                 const MeoPyramid *ref0, const MeoPyramid *ref1,
                                 MeoPuResult *results, MeoSbDebug *debug) {
     if (prm->num_pus != MEO_SQUARE_PU_COUNT && prm->num_pus != MEO_MAX_PU_COUNT) return -2;
-    if ((prm->width & 7) || (prm->height & 7) || ((prm->width & 63) != 0 && (prm->width & 63) != 32)) return -3;
+    if ((prm->width & 7) || (prm->height & 7) || (prm->width & 63) == 40 || (prm->width & 63) == 56) return -3;
     SbCtx *c = (SbCtx *)calloc(1, sizeof(SbCtx));
     if (!c) return -1;
     c->prm = prm; c->cur = cur; c->ref[0] = ref0; c->ref[1] = ref1 ? ref1 : ref0;

@@ -158,7 +158,7 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     if (!out) return SVTME_ERR_BAD_PARAMETER;
     *out = nullptr;
     if (width <= 0 || height <= 0 || (width & 7) || (height & 7) || num_slots <= 0 ||
-        ((width & 63) != 0 && (width & 63) != 32) || width > 8192 || height > 8192)
+        (width & 63) == 40 || (width & 63) == 56 || width > 8192 || height > 8192)   /* 40/56-wide edge SBs: void kernel in the reference, EbComputeSAD.h:143-147 */
         return SVTME_ERR_BAD_PARAMETER;
     SvtMeContext* ctx = new (std::nothrow) SvtMeContext();
     if (!ctx) return SVTME_ERR_INSUFFICIENT_RESOURCES;
@@ -504,7 +504,8 @@ static bool params_ok(const SvtMeContext* ctx, const SvtMeParams& p, std::string
     REQ(p.hierarchical_levels >= 0 && p.hierarchical_levels <= 5);
     REQ(p.temporal_layer_index >= 0 && p.temporal_layer_index <= p.hierarchical_levels);
     REQ(p.num_hme_regions_w >= 1 && p.num_hme_regions_w <= 2 && p.num_hme_regions_h >= 1 && p.num_hme_regions_h <= 2);
-    REQ(p.search_area_w >= 1 && p.search_area_w <= 64 && p.search_area_h >= 1 && p.search_area_h <= 64);
+    /* the reference keeps the search area in a uint8_t (EbMotionEstimationContext.h:403-404) and searches MIN(area, 127) */
+    REQ(p.search_area_w >= 1 && p.search_area_w <= 255 && p.search_area_h >= 1 && p.search_area_h <= 255);
     REQ(p.hme_l0_mult_x > 0 && p.hme_l0_mult_y > 0);
     for (int i = 0; i < 2; i++) {
         REQ(p.hme_l0_w[i] >= 1 && p.hme_l0_h[i] >= 1 && p.hme_l1_w[i] >= 1 && p.hme_l1_h[i] >= 1 && p.hme_l2_w[i] >= 0 && p.hme_l2_h[i] >= 0);
@@ -523,9 +524,11 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     const int nslots = (int)ctx->slots.size();
     int max_lists = 1;
     bool any_sq = false, any_ext = false;
+    bool cls[2][2] = { { false, false }, { false, false } };   // [209-PU mode][search area beyond 64 x 64]: kernel variants this batch needs
     for (int i = 0; i < n_jobs; i++) {
         const SvtMeJob& j = jobs[i];
         (j.params.num_pus == SVTME_MAX_PU_COUNT ? any_ext : any_sq) = true;
+        cls[j.params.num_pus == SVTME_MAX_PU_COUNT][wide_search(j.params)] = true;
         std::string why;
         if (!params_ok(ctx, j.params, why)) return fail(ctx, SVTME_ERR_BAD_PARAMETER, why);
         if (j.cur_slot < 0 || j.cur_slot >= nslots || j.ref0_slot < 0 || j.ref0_slot >= nslots ||
@@ -582,11 +585,11 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         cudaStream_t st = n_chunks > 1 ? ctx->cstream[c % n_cs] : ctx->stream;
         for (int list = 0; list < max_lists; list++) {
             { LaunchTimer t(ctx, SVTME_KERNEL_HME, st); launch_hme(dj, nj, max_sb, list, st); }
-            // the square (85-PU) and ext (209-PU) variants cover the same grid; a CTA of the other mode exits at once
-            for (int ext = 0; ext < 2; ext++) {
-                if (!(ext ? any_ext : any_sq)) continue;
-                { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, st); launch_fullpel(dj, nj, max_sb, list, ext != 0, st); }
-                { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, st); launch_subpel(dj, nj, max_sb, list, ext != 0, st); }
+            // the square (85-PU) / ext (209-PU) and narrow / wide-area variants cover the same grid; a CTA of another class exits at once
+            for (int ext = 0; ext < 2; ext++) for (int wide = 0; wide < 2; wide++) {
+                if (!cls[ext][wide]) continue;
+                { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, st); launch_fullpel(dj, nj, max_sb, list, ext != 0, wide != 0, st); }
+                { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, st); launch_subpel(dj, nj, max_sb, list, ext != 0, wide != 0, st); }
             }
         }
         for (int ext = 0; ext < 2; ext++) {
@@ -757,8 +760,8 @@ extern "C" int32_t svtme_motion_estimate_static(SvtMeContext* ctx, const SvtMeJo
     CU(cudaMemcpyAsync(&a->job, &d, sizeof(DJob), cudaMemcpyHostToDevice, st));
     for (int list = 0; list < j.params.num_lists; list++) {
         launch_hme(&a->job, 1, n_sb, list, st);
-        launch_fullpel(&a->job, 1, n_sb, list, false, st);
-        launch_subpel(&a->job, 1, n_sb, list, false, st);
+        launch_fullpel(&a->job, 1, n_sb, list, false, wide_search(j.params), st);
+        launch_subpel(&a->job, 1, n_sb, list, false, wide_search(j.params), st);
         ctx->launches += 3;
     }
     launch_bipred_pack(&a->job, 1, n_sb, false, st);

@@ -19,6 +19,11 @@
 //     reduced by a streaming transpose (pair_min below) and every lane issues one RED.MIN to its own PU slot,
 //     which is exactly "smallest SAD, first in raster order"; the 32x32 PUs use sad * 8192 + (row, group, idx)
 //     to carry the reference's gcc-only MV quirk (Q4); the 64x64 PU is one warp-wide minimum.
+//   * search areas wider or taller than 64 (MIN(search_area, 127), ME.c:6644-6645; template parameter Wide): the area
+//     is cut into sub-areas of at most 64x64 positions on multiples of 64 from its origin (so the reference's
+//     8-position groups are not split), each sub-area is staged and searched exactly as above, and the winners are
+//     merged per PU in the reference's order: smaller SAD, then earlier row, then earlier group / column. The
+//     narrow instantiation compiles to the single-area code.
 #include "me_common.cuh"
 
 namespace svtme {
@@ -47,8 +52,10 @@ __device__ __forceinline__ void red_min(uint32_t slot_addr, uint32_t key) {
     asm volatile("red.shared.min.u32 [%0], %1;" :: "r"(slot_addr), "r"(key) : "memory");
 }
 
+template <bool Wide>
 __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __restrict__ jobs, int list) {
     extern __shared__ __align__(16) uint32_t smem[];
+    __shared__ uint32_t merged_v[Wide ? kNumPu : 1], merged_o[Wide ? kNumPu : 1];   // Wide: running winner per PU (value, order key)
     uint32_t* win = smem;
     uint32_t* src = smem + 4 * kWinRows * kWinPitch;
     uint32_t* keys = src + 32 * 16;
@@ -58,11 +65,19 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
     if (list >= p.num_lists || p.num_pus != kNumPu) return;     // 209-PU jobs are searched by fullpel_ext_kernel
+    if (wide_search(p) != Wide) return;
     const int tid = threadIdx.x;
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     SbScratch& scr = job.scratch[sb];
     const DPlane& rp = job.ref[list].full;
-    const int sax = scr.sa_x[list], say = scr.sa_y[list], saw = scr.sa_w[list], sah = scr.sa_h[list];
+    const int area_x = scr.sa_x[list], area_y = scr.sa_y[list], area_w = scr.sa_w[list], area_h = scr.sa_h[list];
+    if (Wide && tid < kNumPu) { merged_v[tid] = 0xFFFFFFFFu; merged_o[tid] = 0xFFFFFFFFu; }
+#pragma unroll 1
+    for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
+    // sub-area of this pass: the whole area, or (Wide) one of up to 2 x 2 pieces of at most 64 x 64 positions
+    const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
+    if (Wide && (tx0 >= area_w || ty0 >= area_h)) continue;       // CTA-uniform
+    const int sax = area_x + tx0, say = area_y + ty0, saw = min(64, area_w - tx0), sah = min(64, area_h - ty0);
 
     // ---- stage source (even rows) and the four byte-shifted window copies.
     // The window first lands RAW in shared memory as 16-byte cp.async granules (fire and forget: no thread holds a
@@ -86,8 +101,10 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    for (int t = tid; t < 32 * 16; t += kFpThreads)
-        src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
+    if (!Wide || sub == 0) {                                      // behind the window's asynchronous copies
+        for (int t = tid; t < 32 * 16; t += kFpThreads)
+            src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
+    }
     if (tid < 96) keys[tid] = 0xFFFFFFFFu;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
@@ -292,20 +309,37 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
         } else {
             v = key >> 12; y = (key >> 6) & 63; x = key & 63;
         }
-        scr.best_sad[list][tid] = v << 1;
-        scr.best_mv[list][tid] = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
+        if (!Wide) {
+            scr.best_sad[list][tid] = v << 1;
+            scr.best_mv[list][tid] = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
+        } else if (key != 0xFFFFFFFFu) {
+            // merge in the reference's visiting order: row, then 8-position group, then (32x32: the quirk's in-group rank =
+            // the low key bits; others: the column). Sub-areas start on multiples of 64, so groups keep their identity.
+            const uint32_t o = (tid >= 1 && tid <= 4) ? (((uint32_t)(ty0 + y) << 8) | ((uint32_t)((tx0 >> 3) + ((key >> 3) & 15)) << 3) | (key & 7))
+                                                      : (((uint32_t)(ty0 + y) << 8) | (uint32_t)(tx0 + x));
+            if (v < merged_v[tid] || (v == merged_v[tid] && o < merged_o[tid])) {
+                merged_v[tid] = v; merged_o[tid] = o;
+                scr.best_sad[list][tid] = v << 1;
+                scr.best_mv[list][tid] = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
+            }
+        }
     }
+    if (Wide) __syncthreads();                                    // before the next sub-area's window and key reset
+    }   // sub-areas
 }
 
 cudaError_t configure_fullpel() {
-    return cudaFuncSetAttribute(fullpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(fullpel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpSmemBytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(fullpel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpSmemBytes);
 }
 
-void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);   // fullpel_ext.cu
+void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool wide, cudaStream_t st);   // fullpel_ext.cu
 
-void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st) {
-    if (ext) launch_fullpel_ext(d_jobs, n_jobs, max_sb, list, st);
-    else     fullpel_kernel<<<dim3(max_sb, n_jobs), kFpThreads, kFpSmemBytes, st>>>(d_jobs, list);
+void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st) {
+    if (ext)       launch_fullpel_ext(d_jobs, n_jobs, max_sb, list, wide, st);
+    else if (wide) fullpel_kernel<true><<<dim3(max_sb, n_jobs), kFpThreads, kFpSmemBytes, st>>>(d_jobs, list);
+    else           fullpel_kernel<false><<<dim3(max_sb, n_jobs), kFpThreads, kFpSmemBytes, st>>>(d_jobs, list);
 }
 
 }  // namespace svtme

@@ -1,7 +1,7 @@
 // fullpel_ext.cu -- integer full-pel search of one 64x64 SB against one reference list in the 209-PU mode
 // (PIC_ALL_DEPTH_MODE pictures, i.e. enc-mode 0-2 reference pictures): SADs of the 85 square PUs AND of the 124
 // non-square ones (64x32, 32x16, 16x8, 32x64, 16x32, 8x16, 32x8, 8x32, 64x16, 16x64) at every position of the
-// (<= 64x64) search area, and the per-PU argmin. Bit-exact with open_loop_me_fullpel_search_sblock and its leaves
+// search area, and the per-PU argmin. Bit-exact with open_loop_me_fullpel_search_sblock and its leaves
 // (reference Source/Lib/Codec/EbMotionEstimation.c:159-1236, 1556-1595,
 //  Source/Lib/ASM_SSE4_1/EbComputeSAD_Intrinsic_SSE4_1.c:21-164).
 //
@@ -17,6 +17,9 @@
 // reduced across the warp by streaming transpose-reductions (pair_min) so that at the end of a tile every lane issues
 // one RED.SHARED.MIN per PU class. The non-square SADs are sums of the 8x8 SADs: horizontal sums inside a band of
 // eight rows, vertical sums carried across bands in registers (this is what costs the registers: 1 CTA per SM).
+// Search areas beyond 64x64 (template parameter Wide, MIN(search_area, 127), ME.c:6644-6645) are cut into sub-areas of at
+// most 64x64 positions exactly like fullpel.cu and merged per PU by (SAD, row, column); the S / T tables of quirk Q11
+// then cover 128 x 128 positions and are replayed once after the last sub-area.
 #include "me_common.cuh"
 #include <cstdlib>
 
@@ -29,7 +32,11 @@ constexpr int kWinWords = 4 * kWinRows * kWinPitch;
 constexpr int kSrcWords = 32 * 16;
 constexpr int kKeyWords = 212;         // 209 PU slots (internal index), padded
 constexpr int kRawPitch = 40;          // words per raw window row (ten 16-byte granules), see fullpel.cu
-constexpr int kFxSmemBytes = (kWinWords + kSrcWords + kKeyWords + 4096) * 4 + 4096 * 2 + kWinRows * kRawPitch * 4;
+constexpr int kFxThreads = 256;        // x 1 CTA per SM (255 registers)
+template <bool Wide> struct Q11 { static constexpr int kShift = Wide ? 7 : 6, kEntries = 1 << (2 * kShift); };
+template <bool Wide> constexpr int fx_smem_bytes() {
+    return (kWinWords + kSrcWords + kKeyWords + Q11<Wide>::kEntries) * 4 + Q11<Wide>::kEntries * 2 + kWinRows * kRawPitch * 4;
+}
 
 // see fullpel.cu: lanes whose `bit` is clear keep min(a) over {lane, lane ^ bit}, the others the same for b
 __device__ __forceinline__ uint32_t pair_min(uint32_t a, uint32_t b, int bit, uint32_t hi01) {
@@ -79,29 +86,36 @@ __device__ __forceinline__ int lane_pu(int table, int lane) {
 }
 }  // namespace
 
-// kFxThreads x CTAs per SM = 256 threads per SM either way (255 registers): 256 x 1 or 128 x 2
-template <int kFxThreads>
-__global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxThreads) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
+template <bool Wide>
+__global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
+    constexpr int QS = Q11<Wide>::kShift, QN = Q11<Wide>::kEntries;
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* win = smem;
     uint32_t* src = win + kWinWords;
     uint32_t* keys = src + kSrcWords;
     uint32_t* q11_s = keys + kKeyWords;                                  // bottom 64x32 SAD of every position
-    uint16_t* q11_t = reinterpret_cast<uint16_t*>(q11_s + 4096);         // 32x16 (x 0, y 48) SAD of every position
-    uint32_t* raw = reinterpret_cast<uint32_t*>(q11_t + 4096);           // raw window rows (byte offset 100048 = 16 * 6253)
+    uint16_t* q11_t = reinterpret_cast<uint16_t*>(q11_s + QN);           // 32x16 (x 0, y 48) SAD of every position
+    uint32_t* raw = reinterpret_cast<uint32_t*>(q11_t + QN);             // raw window rows (byte offset 100048 = 16 * 6253; Wide 173776 = 16 * 10861)
     __shared__ uint32_t lane_slot[kNumTables][32];                       // shared ADDRESS of the PU slot a lane owns
+    __shared__ uint32_t merged_v[Wide ? kMaxPu : 1], merged_o[Wide ? kMaxPu : 1];   // Wide: running winner per PU (value, row << 8 | column)
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
-    if (list >= p.num_lists || p.num_pus != kMaxPu) return;
+    if (list >= p.num_lists || p.num_pus != kMaxPu || wide_search(p) != Wide) return;
     const int tid = threadIdx.x;
     const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     SbScratch& scr = job.scratch[sb];
     SbScratchExt& scx = job.scratch_ext[sb];
     const DPlane& rp = job.ref[list].full;
-    const int sax = scr.sa_x[list], say = scr.sa_y[list], saw = scr.sa_w[list], sah = scr.sa_h[list];
+    const int area_x = scr.sa_x[list], area_y = scr.sa_y[list], area_w = scr.sa_w[list], area_h = scr.sa_h[list];
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
+    if (Wide) for (int t = tid; t < kMaxPu; t += kFxThreads) { merged_v[t] = 0xFFFFFFFFu; merged_o[t] = 0xFFFFFFFFu; }
+#pragma unroll 1
+    for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
+    const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
+    if (Wide && (tx0 >= area_w || ty0 >= area_h)) continue;       // CTA-uniform
+    const int sax = area_x + tx0, say = area_y + ty0, saw = min(64, area_w - tx0), sah = min(64, area_h - ty0);
 
     // ---- stage source (even rows), the slot tables and the four byte-shifted window copies (as in fullpel.cu: the window
     // lands raw in shared memory as 16-byte cp.async granules, then the warps shift it into the four copies)
@@ -120,10 +134,12 @@ __global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxT
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    for (int t = tid; t < kSrcWords; t += kFxThreads)
-        src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
+    if (!Wide || sub == 0) {
+        for (int t = tid; t < kSrcWords; t += kFxThreads)
+            src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
+        for (int t = tid; t < kNumTables * 32; t += kFxThreads) lane_slot[t >> 5][t & 31] = keys_addr + 4u * (uint32_t)lane_pu(t >> 5, t & 31);
+    }
     for (int t = tid; t < kKeyWords; t += kFxThreads) keys[t] = 0xFFFFFFFFu;
-    for (int t = tid; t < kNumTables * 32; t += kFxThreads) lane_slot[t >> 5][t & 31] = keys_addr + 4u * (uint32_t)lane_pu(t >> 5, t & 31);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     {
@@ -382,7 +398,7 @@ __global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxT
 #pragma unroll
                 for (int q = 0; q < 4; q++) w16[k][q] += v16[k][q];
                 w32[k][0] += s32[k][0]; w32[k][1] += s32[k][1]; s64[k] += s64h[k];
-                if (val[k]) { const int pos = (y << 6) | (x0 + 4 * k); q11_s[pos] = s64h[k]; q11_t[pos] = (uint16_t)m32[k][0]; }
+                if (val[k]) { const int pos = ((ty0 + y) << QS) | (tx0 + x0 + 4 * k); q11_s[pos] = s64h[k]; q11_t[pos] = (uint16_t)m32[k][0]; }
             }
             {
                 uint32_t kq[4];
@@ -406,27 +422,51 @@ __global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxT
 #undef SLOT
     __syncthreads();
 
+    // ---- decode the winning keys into p_sb_best_sad / p_sb_best_mv form (internal index = slot)
+    for (int t = tid; t < kMaxPu; t += kFxThreads) {
+        if (t == 87 + 5) continue;                                  // quirk Q11: replayed below
+        const uint32_t key = keys[t];
+        const uint32_t v = key >> 12; const int y = (key >> 6) & 63, x = key & 63;
+        if (Wide) {                                                 // merge: smaller SAD, then earlier row, then earlier column
+            const uint32_t o = ((uint32_t)(ty0 + y) << 8) | (uint32_t)(tx0 + x);
+            if (key == 0xFFFFFFFFu || !(v < merged_v[t] || (v == merged_v[t] && o < merged_o[t]))) continue;
+            merged_v[t] = v; merged_o[t] = o;
+        }
+        const uint32_t sad = v << 1, mv = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
+        if (t < kNumPu) { scr.best_sad[list][t] = sad; scr.best_mv[list][t] = mv; }
+        else { scx.best_sad[list][t - kNumPu] = sad; scx.best_mv[list][t - kNumPu] = mv; }
+    }
+    if (Wide) __syncthreads();                                      // before the next sub-area's window and key reset
+    }   // sub-areas
+
     // ---- quirk Q11: replay the sequential update rule of 32x16 PU #5 over the positions in raster order.
     // `best` strictly decreases (T <= S), so the rule is a short chain of queries "first position after n whose S is
-    // below best": every thread keeps its share of the S table in registers and the CTA answers one query per step
-    // (a handful of steps: S covers four times the area of T, so it rarely drops below an earlier T).
+    // below best": every thread keeps its share of the S table in registers (Wide: reads it from shared memory) and the
+    // CTA answers one query per step (a handful of steps: S covers four times the area of T, so it rarely drops below an
+    // earlier T).
     {
-        constexpr int kPer = 4096 / kFxThreads;
-        uint32_t S[kPer];
+        constexpr int kPer = QN / kFxThreads;
+        auto s_of = [&](int n) { return ((n & ((1 << QS) - 1)) < area_w && (n >> QS) < area_h) ? q11_s[n] : 0xFFFFFFFFu; };
+        uint32_t S[Wide ? 1 : kPer];
+        if (!Wide) {
 #pragma unroll
-        for (int i = 0; i < kPer; i++) {
-            const int n = tid + kFxThreads * i;                       // raster index (row << 6 | col)
-            S[i] = ((n & 63) < saw && (n >> 6) < sah) ? q11_s[n] : 0xFFFFFFFFu;
+            for (int i = 0; i < kPer; i++) S[i] = s_of(tid + kFxThreads * i);      // raster index (row << QS | col)
         }
         uint32_t* red = keys + kMaxPu;                                // three spare words of the key table
         uint32_t best = 0xFFFFFFFFu;
         int cur = -1;
+        const int lane = tid & 31;
         for (;;) {
             uint32_t cand = 0xFFFFFFFFu;
+            if (!Wide) {
 #pragma unroll
-            for (int i = kPer - 1; i >= 0; i--) {
-                const int n = tid + kFxThreads * i;
-                if (n > cur && S[i] < best) cand = (uint32_t)n;
+                for (int i = kPer - 1; i >= 0; i--) {
+                    const int n = tid + kFxThreads * i;
+                    if (n > cur && S[i] < best) cand = (uint32_t)n;
+                }
+            } else {
+                for (int n = tid + kFxThreads * max(0, (cur + 1 - tid + kFxThreads - 1) / kFxThreads); n < QN && (n >> QS) < area_h; n += kFxThreads)
+                    if (n > cur && s_of(n) < best) { cand = (uint32_t)n; break; }
             }
             cand = __reduce_min_sync(0xffffffffu, cand);
             if (tid == 0) red[0] = 0xFFFFFFFFu;
@@ -440,36 +480,20 @@ __global__ void __launch_bounds__(kFxThreads, kFxThreads >= 256 ? 1 : 256 / kFxT
         }
         if (tid == 0) {
             scx.best_sad[list][87 + 5 - kNumPu] = best << 1;
-            scx.best_mv[list][87 + 5 - kNumPu] = make_mv((int16_t)((sax + (cur & 63)) * 4), (int16_t)((say + (cur >> 6)) * 4));
+            scx.best_mv[list][87 + 5 - kNumPu] = make_mv((int16_t)((area_x + (cur & ((1 << QS) - 1))) * 4), (int16_t)((area_y + (cur >> QS)) * 4));
         }
     }
-
-    // ---- decode the winning keys into p_sb_best_sad / p_sb_best_mv form (internal index = slot)
-    for (int t = tid; t < kMaxPu; t += kFxThreads) {
-        if (t == 87 + 5) continue;
-        const uint32_t key = keys[t];
-        const uint32_t v = key >> 12; const int y = (key >> 6) & 63, x = key & 63;
-        const uint32_t sad = v << 1, mv = make_mv((int16_t)((sax + x) * 4), (int16_t)((say + y) * 4));
-        if (t < kNumPu) { scr.best_sad[list][t] = sad; scr.best_mv[list][t] = mv; }
-        else { scx.best_sad[list][t - kNumPu] = sad; scx.best_mv[list][t - kNumPu] = mv; }
-    }
 }
-
-static int g_fx_threads = 256;
 
 cudaError_t configure_fullpel_ext() {
-    if (const char* e = getenv("SVTME_FX_THREADS")) { const int t = atoi(e); g_fx_threads = (t == 128 || t == 512) ? t : 256; }   // tuning knob
-    cudaError_t rc = cudaFuncSetAttribute(fullpel_ext_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
+    cudaError_t rc = cudaFuncSetAttribute(fullpel_ext_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fx_smem_bytes<false>());
     if (rc != cudaSuccess) return rc;
-    rc = cudaFuncSetAttribute(fullpel_ext_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
-    if (rc != cudaSuccess) return rc;
-    return cudaFuncSetAttribute(fullpel_ext_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFxSmemBytes);
+    return cudaFuncSetAttribute(fullpel_ext_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fx_smem_bytes<true>());
 }
 
-void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
-    if (g_fx_threads == 128) fullpel_ext_kernel<128><<<dim3(max_sb, n_jobs), 128, kFxSmemBytes, st>>>(d_jobs, list);
-    else if (g_fx_threads == 512) fullpel_ext_kernel<512><<<dim3(max_sb, n_jobs), 512, kFxSmemBytes, st>>>(d_jobs, list);
-    else                     fullpel_ext_kernel<256><<<dim3(max_sb, n_jobs), 256, kFxSmemBytes, st>>>(d_jobs, list);
+void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool wide, cudaStream_t st) {
+    if (wide) fullpel_ext_kernel<true><<<dim3(max_sb, n_jobs), kFxThreads, fx_smem_bytes<true>(), st>>>(d_jobs, list);
+    else      fullpel_ext_kernel<false><<<dim3(max_sb, n_jobs), kFxThreads, fx_smem_bytes<false>(), st>>>(d_jobs, list);
 }
 
 }  // namespace svtme

@@ -197,6 +197,65 @@ __device__ uint32_t group_search(uint32_t* win, uint32_t* best_slot, int bar_id,
     return *best_slot;
 }
 
+// The same search for ANY block width (edge SBs 8 / 16 / 24 / 48 pixels wide, i.e. 2 .. 48-pixel blocks on the decimated
+// levels; the reference runs them through the C SadLoopKernel or the 4 / 8 / 16 / 24 / 48 cases of the AVX2 one,
+// ME.c:4417-4496, 4579-4615, 4711-4750). One search position per thread, the block width in pixels at run time, the last
+// partial word masked. Only the right-most SB column of such pictures comes here, so this path is written for
+// size, not speed. Quirk Q12: 4-pixel-wide blocks with rows % 4 == 0 -- inside the full 8-position groups the AVX2
+// kernels pair reference row 2 with source row 0 and reference row 0 with source row 2 of every four rows
+// (EbComputeSAD_Intrinsic_AVX2.c:1650-1652, 3973-3975); the leftover positions (search width & 7) are right.
+template <int VS, int RS>
+__device__ uint32_t group_search_any(uint32_t* win, uint32_t* best_slot, int bar_id, int gtid, const uint32_t* src, int sp, int wpx, int rows,
+                                     const DPlane& rp, int rx, int ry, int saw, int sah) {
+    const int W = (wpx + 3) >> 2;
+    const uint32_t last_mask = (wpx & 3) ? (0xFFFFFFFFu >> (32 - 8 * (wpx & 3))) : 0xFFFFFFFFu;
+    const bool q12 = wpx == 4 && (rows & 3) == 0;
+    const int full = saw & ~7;                          // positions below this belong to full 8-position groups
+    const int wcols = ((saw + 3) >> 2) + W + 1;         // window words per row
+    const int pitch = wcols | 1;
+    const int extra = 2 * (rows - 1);
+    const int chunk = max(1, kRegionWinWords / pitch - extra);
+    uint32_t best = 0xFFFFFFFFu;
+    if (gtid == 0) *best_slot = 0xFFFFFFFFu;
+    for (int i0 = 0; i0 < sah; i0 += chunk) {
+        const int i1 = min(sah, i0 + chunk);
+        const int wrows = i1 - i0 + extra;
+        group_bar(bar_id);
+        {
+            const uint8_t* p0 = rp.at(rx, ry + i0);
+            const uint32_t m = (uint32_t)(uintptr_t)p0 & 3u, sh8 = m * 8u;
+            const int wstride = rp.stride >> 2;
+            for (int t = gtid; t < wrows * wcols; t += kGroupThreads) {
+                const int r = t / wcols, c = t - r * wcols;
+                const uint32_t* a = reinterpret_cast<const uint32_t*>(p0 - m) + c + r * wstride;
+                win[r * pitch + c] = __funnelshift_r(__ldg(a), __ldg(a + 1), sh8);
+            }
+        }
+        group_bar(bar_id);
+        for (int t = gtid; t < (i1 - i0) * saw; t += kGroupThreads) {
+            const int i = t / saw, x = t - i * saw;
+            const uint32_t sh8 = (x & 3) * 8u;
+            const bool swap = q12 && x < full;
+            uint32_t sad = 0;
+            for (int r = 0; r < rows; r++) {
+                const int rr = (swap && !(r & 1)) ? (r ^ 2) : r;
+                const uint32_t* wr = win + (i + 2 * rr) * pitch + (x >> 2);
+                const uint32_t* sr = src + r * sp;
+                for (int c = 0; c < W; c++) {
+                    uint32_t v = __funnelshift_r(wr[c], wr[c + 1], sh8), sw = sr[c];
+                    if (c == W - 1) { v &= last_mask; sw &= last_mask; }
+                    sad = sad4(sw, v, sad);
+                }
+            }
+            best = min(best, (sad << VS) | ((uint32_t)(i0 + i) << RS) | (uint32_t)x);
+        }
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if ((gtid & 31) == 0) atomicMin(best_slot, best);
+    group_bar(bar_id);
+    return *best_slot;
+}
+
 __device__ __forceinline__ int round_sa_width(int w) { return (w < 8) ? 8 : (w & 7) ? w + (w - ((w >> 3) << 3)) : w; }
 
 __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restrict__ jobs, int list) {
@@ -268,6 +327,7 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
                 const int w = g % nw, h = g / nw, bar = 1 + g;
                 uint32_t* win = sh.win[g];
                 const bool half = sb_w == 32;                     // right-edge SB of a width % 64 == 32 picture
+                const bool odd = sb_w != 64 && sb_w != 32;        // 8 / 16 / 24 / 48-wide edge SB: the any-width search
                 if (p.enable_hme_level0) {                        // HmeLevel0, ME.c:4306-4503 (sixteenth picture)
                     const DPlane& rp = ref.sixteenth;
                     int saw = (int16_t)((p.hme_l0_w[w] * p.hme_l0_mult_x) / 100);
@@ -279,7 +339,7 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
                     int say = -(int16_t)(((p.hme_l0_total_h * p.hme_l0_mult_y) / 100) >> 1) + yd;
                     clip_search_area(ox >> 2, sax, saw, rp.ox - 1, rp.w);
                     clip_search_area(oy >> 2, say, sah, rp.oy - 1, rp.h);
-                    const uint32_t k = half
+                    const uint32_t k = odd ? group_search_any<17, 9>(win, &sh.best[g], bar, gtid, sh.s_even, 4, sb_w >> 2, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah) : half
                         ? group_search<2, 4, false, 17, 9, 1>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah)
                         : group_search<4, 4, false, 17, 9, 1>(win, &sh.best[g], bar, gtid, sh.s_even, 8, rp, (ox >> 2) + sax, (oy >> 2) + say, saw, sah);
                     if (gtid == 0) {
@@ -295,7 +355,7 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
                     int sax = -(saw >> 1) + (sh.x[0][w][h] >> 1), say = -(sah >> 1) + (sh.y[0][w][h] >> 1);
                     clip_search_area(ox >> 1, sax, saw, rp.ox - 1, rp.w);
                     clip_search_area(oy >> 1, say, sah, rp.oy - 1, rp.h);
-                    const uint32_t k = half
+                    const uint32_t k = odd ? group_search_any<13, 7>(win, &sh.best[4 + g], bar, gtid, sh.q_even, kQPitch, sb_w >> 1, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah) : half
                         ? group_search<4, kQPitch, false, 13, 7, 2>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah)
                         : group_search<8, kQPitch, true, 13, 7, 2>(win, &sh.best[4 + g], bar, gtid, sh.q_even, 16, rp, (ox >> 1) + sax, (oy >> 1) + say, saw, sah);
                     if (gtid == 0) {
@@ -311,7 +371,7 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
                     int sax = -(saw >> 1) + sh.x[1][w][h], say = -(sah >> 1) + sh.y[1][w][h];
                     clip_search_area(ox, sax, saw, 63, rp.w);
                     clip_search_area(oy, say, sah, 63, rp.h);
-                    const uint32_t k = half
+                    const uint32_t k = odd ? group_search_any<13, 7>(win, &sh.best[8 + g], bar, gtid, sh.src_even, kSrcPitch, sb_w, 32, rp, ox + sax, oy + say, saw, sah) : half
                         ? group_search<8, kSrcPitch, false, 13, 7, 8>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah)
                         : group_search<16, kSrcPitch, false, 13, 7, 8>(win, &sh.best[8 + g], bar, gtid, sh.src_even, 32, rp, ox + sax, oy + say, saw, sah);
                     if (gtid == 0) {

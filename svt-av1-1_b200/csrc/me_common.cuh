@@ -142,6 +142,11 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
     return v;
 }
 
+// Search areas beyond 64 x 64 positions (the reference searches MIN(search_area, 127), ME.c:6644-6645) run in the Wide
+// instantiations of the full-pel and sub-pel kernels. Decided on the job's parameters (uniform per picture), not on the
+// clipped area of an SB.
+__host__ __device__ inline bool wide_search(const SvtMeParams& p) { return p.search_area_w > 64 || p.search_area_h > 64; }
+
 // Pictures of one batched pyramid launch: source luma and slot base pointer per picture
 struct PyramidBatch {
     const uint8_t* luma[SVTME_MAX_BATCH];
@@ -154,9 +159,9 @@ void launch_pyramid(const uint8_t* d_luma, int luma_stride, const DPyramid& pyr,
 void launch_unpack16(const uint16_t* d_in, int in_stride, uint8_t* d_msb, uint8_t* d_rem, int width, int height, cudaStream_t st);
 void launch_hme(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st);
 // The square-mode and ext-mode kernels are separate launches over the same grid; a CTA whose job is of the other
-// mode exits at once. `ext` selects the 209-PU variant.
-void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st);
-void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st);
+// mode exits at once. `ext` selects the 209-PU variant, `wide` the one for search areas beyond 64 x 64.
+void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st);
+void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st);
 void launch_bipred_pack(const DJob* d_jobs, int n_jobs, int max_sb, bool ext, cudaStream_t st);
 cudaError_t configure_kernels();
 

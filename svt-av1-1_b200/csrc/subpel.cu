@@ -19,21 +19,27 @@
 namespace svtme {
 
 constexpr int kSpThreads = 256;
-constexpr int kPlRows = 134;            // 64 + 63 + 7
-constexpr int kPlPitchW = 36;           // words (144 bytes >= 64 + 70 + one spare word for the last B taps)
-constexpr int kPlWords = kPlRows * kPlPitchW + 132;  // + room for the row skew below
+// Plane geometry: the window is the bounding box of the 256 (level, block) positions, at most (area - 1) + 56 + 15 rows and
+// the same + 6 bytes (+ one spare word for the last B taps) per row. Narrow = search areas up to 64 x 64 (2 CTAs per SM);
+// Wide = up to 127 x 127 (MIN(search_area, 127), ME.c:6644-6645): 198 rows x 52 words, one CTA per SM.
+template <bool Wide> struct PlaneGeom {
+    static constexpr int kRows = Wide ? 198 : 134;            // 127 (64) - 1 + 56 + 15 + 1
+    static constexpr int kPitchW = Wide ? 52 : 36;            // words
+    static constexpr int kWords = kRows * kPitchW + (Wide ? 196 : 132);   // + room for the row skew below
+    static constexpr int kRawPitch = Wide ? 56 : 44;          // words per raw window row: 16-byte granules (3 + pitch + 1 words at most)
+};
 // Word offset of window row r. Rows 8 apart would land on the same bank (8 * 36 = 9 * 32); the (monotonic) skew
 // moves each group of eight rows by 1 or 15 banks more than the previous one, so that the 8x4 blocks a warp reads
 // together (two words apart along x, eight rows apart along y) touch 32 different banks when they share a motion
 // vector: bank offsets of the four block rows are {0, 1, 16, 17} or {0, 15, 16, 31}.
-__device__ __forceinline__ int plane_row(int r) { return r * kPlPitchW + ((r >> 3) & 1) + (r & ~15); }
-constexpr int kRawPitchSp = 44;         // words per raw window row: eleven 16-byte granules (3 + 36 + 1 words at most)
-static_assert(kPlRows * kRawPitchSp <= 2 * kPlWords, "the raw window must fit the storage of planes H and J");
+template <bool Wide> __device__ __forceinline__ int plane_row(int r) { return r * PlaneGeom<Wide>::kPitchW + ((r >> 3) & 1) + (r & ~15); }
+static_assert(PlaneGeom<false>::kRows * PlaneGeom<false>::kRawPitch <= 2 * PlaneGeom<false>::kWords &&
+              PlaneGeom<true>::kRows * PlaneGeom<true>::kRawPitch <= 2 * PlaneGeom<true>::kWords, "the raw window must fit the storage of planes H and J");
 constexpr int kMargin = 3;              // window starts 3 pixels left/above the search-area origin
 
-template <int NPU>
+template <int NPU, bool Wide>
 struct SpSharedT {
-    uint32_t plane[4][kPlWords];        // A, B, H, J
+    uint32_t plane[4][PlaneGeom<Wide>::kWords];   // A, B, H, J
     uint32_t src[64 * 16];
     uint32_t sum_ssd[9][NPU];           // per (candidate, PU) distortion sums, accumulated with shared atomics
     uint32_t sum_sad[9][NPU];
@@ -41,7 +47,7 @@ struct SpSharedT {
     int32_t  pu_dir[NPU];
     uint32_t pu_imv[NPU];               // MV at entry of the current stage
     uint32_t pu_win[NPU];               // winning half-pel candidate (1..8) of the PU, 0 = the integer position stays
-    uint32_t rowoff[kPlRows + 2];       // plane_row() of every window row: one LDS instead of five integer instructions
+    uint32_t rowoff[PlaneGeom<Wide>::kRows + 2];  // plane_row() of every window row: one LDS instead of five integer instructions
     int32_t  bbox[4];                   // min X, min Y, max -X... see the kernel: bounding box of the blocks' window positions
 };
 
@@ -183,17 +189,18 @@ __device__ __forceinline__ bool pu_leader_any(int wb, int hb, int lane) {
 // Ext = the 209-PU mode: 14 PU classes ("levels") instead of 4; the non-square PUs live in SbScratchExt. Every level
 // is 64 8x8-block tasks, so a warp always works on one level.
 #define PROW(r) ((int)sh.rowoff[r])
-template <bool Ext>
-__global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
+template <bool Ext, bool Wide>
+__global__ void __launch_bounds__(kSpThreads, Wide ? 1 : 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
     constexpr int NPU = Ext ? kMaxPu : kNumPu, NLEV = Ext ? kMaxLevels : kNumLevels;
-    using SpShared = SpSharedT<NPU>;
+    constexpr int kPlRows = PlaneGeom<Wide>::kRows, kRawPitchSp = PlaneGeom<Wide>::kRawPitch;
+    using SpShared = SpSharedT<NPU, Wide>;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SpShared& sh = *reinterpret_cast<SpShared*>(smem_raw);
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
-    if (list >= p.num_lists || (p.num_pus == kMaxPu) != Ext) return;
+    if (list >= p.num_lists || (p.num_pus == kMaxPu) != Ext || wide_search(p) != Wide) return;
     auto block_pu = [](int L, int bx, int by) { if constexpr (Ext) return pu_of_block_any(L, bx, by); else return pu_of_block(L, bx, by); };
     // 8x8 half/quarter-pel is switched off by cu8x8_mode 1 (disable8x8CuInMeFlag); the non-square classes never are
     auto pu_enabled = [&](int pu) { return pu < 21 || pu >= kNumPu || p.cu8x8_mode != 1; };
@@ -213,7 +220,7 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
         if (tid >= kNumPu && tid < NPU) { sh.pu_sad[tid] = scx.best_sad[list][tid - kNumPu]; sh.pu_mv[tid] = scx.best_mv[list][tid - kNumPu]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
     }
     if (tid < 4) sh.bbox[tid] = 0x7FFFFFFF;
-    if (tid < kPlRows + 2) sh.rowoff[tid] = (uint32_t)plane_row(tid);
+    if (tid < kPlRows + 2) sh.rowoff[tid] = (uint32_t)plane_row<Wide>(tid);
     __syncthreads();
     // The refinement only reads the window around the 256 (level, 8x8 block) positions the full-pel search chose
     // (every later MV stays within one integer pixel of them), so the window that is staged and interpolated is their
@@ -525,15 +532,23 @@ __global__ void __launch_bounds__(kSpThreads, 2) subpel_kernel(const DJob* __res
     }
 }
 
+template <bool Ext, bool Wide> static cudaError_t configure_one() {
+    return cudaFuncSetAttribute(subpel_kernel<Ext, Wide>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SpSharedT<Ext ? kMaxPu : kNumPu, Wide>));
+}
 cudaError_t configure_subpel() {
-    cudaError_t e = cudaFuncSetAttribute(subpel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SpSharedT<kNumPu>));
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(subpel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SpSharedT<kMaxPu>));
+    cudaError_t e = configure_one<false, false>();
+    if (e == cudaSuccess) e = configure_one<true, false>();
+    if (e == cudaSuccess) e = configure_one<false, true>();
+    if (e == cudaSuccess) e = configure_one<true, true>();
+    return e;
 }
 
-void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, cudaStream_t st) {
-    if (ext) subpel_kernel<true><<<dim3(max_sb, n_jobs), kSpThreads, sizeof(SpSharedT<kMaxPu>), st>>>(d_jobs, list);
-    else     subpel_kernel<false><<<dim3(max_sb, n_jobs), kSpThreads, sizeof(SpSharedT<kNumPu>), st>>>(d_jobs, list);
+template <bool Ext, bool Wide> static void launch_one(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
+    subpel_kernel<Ext, Wide><<<dim3(max_sb, n_jobs), kSpThreads, sizeof(SpSharedT<Ext ? kMaxPu : kNumPu, Wide>), st>>>(d_jobs, list);
+}
+void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st) {
+    if (ext) { if (wide) launch_one<true, true>(d_jobs, n_jobs, max_sb, list, st); else launch_one<true, false>(d_jobs, n_jobs, max_sb, list, st); }
+    else     { if (wide) launch_one<false, true>(d_jobs, n_jobs, max_sb, list, st); else launch_one<false, false>(d_jobs, n_jobs, max_sb, list, st); }
 }
 
 }  // namespace svtme

@@ -12,7 +12,12 @@ pkg = importlib.import_module("svt-av1-1_b200")
 
 def test_fullpel_work_model():
     # 64 x 64 positions x 64 x 32 source bytes (even rows only): DESIGN.md section 3.1
-    assert bench.FULLPEL_BYTE_SADS_PER_SB_LIST == 4096 * 2048
+    assert bench.fullpel_byte_sads_per_sb_list() == 4096 * 2048
+    bench.SEARCH_AREA = 200                                # --search-area: the reference searches MIN(area, 127)
+    try:
+        assert bench.fullpel_byte_sads_per_sb_list() == 127 * 127 * 2048
+    finally:
+        bench.SEARCH_AREA = None
 
 
 def test_hme_work_model_follows_the_layer_multipliers():

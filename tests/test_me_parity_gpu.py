@@ -133,6 +133,103 @@ def test_sizes_and_layers(pkg, meo, w, h, nl, tl):
     _check_against_oracle(pkg, meo, fr, [pkg.default_params(w, h, nl, tl, 3, 1)], [(1, 0, 2)])
 
 
+@pytest.mark.parametrize("w,h", [(80, 64), (72, 64), (88, 128), (112, 64), (144, 128), (200, 72), (720, 480), (848, 480), (1368, 128)])
+@pytest.mark.parametrize("nl,tl,pus", [(2, 1, 85), (1, 0, 85), (2, 0, 209)])
+def test_edge_sb_widths(pkg, meo, w, h, nl, tl, pus):
+    """Edge SBs 8 / 16 / 24 / 48 pixels wide (EbComputeSAD.h:139-150): centre check and HME levels on the narrow blocks
+    (any-width search of hme.cu, quirk Q12), full-pel / sub-pel / bi-pred on the padded 64x64 SB like the reference."""
+    for seed in range(2):
+        fr = M.synth_video(w, h, 3, seed=w + h + nl + 17 * seed, max_shift=30)
+        p = pkg.default_params(w, h, nl, tl, 3, 1)
+        p.num_pus = pus
+        if pus == 85:
+            _check_against_oracle(pkg, meo, fr, [p], [(1, 0, 2)])
+        else:
+            _check_results_against_oracle(pkg, meo, fr, p)
+
+
+def _check_results_against_oracle(pkg, meo, fr, p):
+    h, w = fr[0].shape
+    ctx = pkg.MeContext(w, h, 3)
+    try:
+        for i, f in enumerate(fr):
+            ctx.upload(i, f)
+        res, _ = ctx.motion_estimate([(1, 0, 2, p)])
+    finally:
+        ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
+    want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p), pyr[1], pyr[0], pyr[2] if p.num_lists == 2 else None)
+    assert M.results_diff(res[0], want, p.num_lists) == []
+
+
+def test_widths_without_a_reference_kernel_are_rejected(pkg):
+    for w in (104, 120, 1960):
+        with pytest.raises(pkg.SvtMeError, match="0x80001005"):
+            pkg.MeContext(w, 64, 2)
+
+
+WIDE = [
+    {"search_area_w": 65, "search_area_h": 65}, {"search_area_w": 96, "search_area_h": 80},
+    {"search_area_w": 127, "search_area_h": 127}, {"search_area_w": 127, "search_area_h": 33},
+    {"search_area_w": 71, "search_area_h": 127}, {"search_area_w": 200, "search_area_h": 255},
+    {"search_area_w": 121, "search_area_h": 3}, {"search_area_w": 16, "search_area_h": 100},
+]
+
+
+@pytest.mark.parametrize("over", WIDE)
+@pytest.mark.parametrize("pus", [85, 209])
+def test_wide_search_areas(pkg, meo, over, pus):
+    """Search areas beyond 64 x 64 (the reference searches MIN(search_area, 127), ME.c:6644-6645): the Wide instantiations
+    of the full-pel kernels (sub-areas merged in the reference's visiting order, quirks Q4 and Q11 across sub-areas) and of
+    the sub-pel kernel (198-row planes)."""
+    w, h = 320, 192
+    fr = M.synth_video(w, h, 3, seed=len(str(over)) + pus, max_shift=70)
+    p = pkg.default_params(w, h, 2, 1, 3, 1)
+    _set(p, over)
+    p.num_pus = pus
+    if pus == 85:
+        _check_against_oracle(pkg, meo, fr, [p], [(1, 0, 2)])
+        q = pkg.default_params(208, 136, 1, 0, 3, 1)
+        _set(q, over)
+        _check_against_oracle(pkg, meo, M.synth_video(208, 136, 3, seed=len(str(over)), max_shift=50), [q], [(1, 0, 2)])
+    else:
+        _check_results_against_oracle(pkg, meo, fr, p)
+
+
+@pytest.mark.parametrize("synth", [dict(noise=0.0, contrast=0.0), dict(noise=12.0, contrast=4.0, max_shift=60)])
+def test_wide_search_content_extremes(pkg, meo, synth):
+    """Flat pictures: every SAD ties, so the merge of the sub-areas must reproduce the pure visiting order."""
+    w, h = 256, 192
+    fr = M.synth_video(w, h, 3, seed=11, **synth)
+    for pus in (85, 209):
+        p = pkg.default_params(w, h, 2, 1, 3, 1)
+        p.search_area_w, p.search_area_h, p.num_pus = 127, 100, pus
+        _check_results_against_oracle(pkg, meo, fr, p)
+
+
+def test_mixed_narrow_and_wide_batch(pkg, meo):
+    """One batch holding narrow / wide-area and 85 / 209-PU pictures: four kernel classes over the same grid."""
+    w, h = 256, 128
+    fr = M.synth_video(w, h, 4, seed=3, max_shift=40)
+    prms = []
+    for sa, pus in ((64, 85), (100, 85), (127, 209), (48, 209)):
+        p = pkg.default_params(w, h, 2, 1, 3, 1)
+        p.search_area_w = p.search_area_h = sa
+        p.num_pus = pus
+        prms.append(p)
+    ctx = pkg.MeContext(w, h, 4)
+    try:
+        for i, f in enumerate(fr):
+            ctx.upload(i, f)
+        res, _ = ctx.motion_estimate([(1, 0, 2, prms[0]), (2, 1, 3, prms[1]), (1, 0, 3, prms[2]), (2, 0, 3, prms[3])])
+    finally:
+        ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
+    for r, p, (c, a, b) in zip(res, prms, ((1, 0, 2), (2, 1, 3), (1, 0, 3), (2, 0, 3))):
+        want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p), pyr[c], pyr[a], pyr[b])
+        assert M.results_diff(r, want) == []
+
+
 SWEEP = [
     {"search_area_w": 24, "search_area_h": 17}, {"search_area_w": 7, "search_area_h": 5},
     {"search_area_w": 43, "search_area_h": 64}, {"search_area_w": 1, "search_area_h": 1},
@@ -245,7 +342,7 @@ def test_error_codes(pkg):
     p = pkg.default_params(w, h, 2, 1, 3, 1)
     with pytest.raises(pkg.SvtMeError, match="0x80001005"):
         ctx.motion_estimate([(0, 5, 1, p)])
-    p.search_area_w = 200
+    p.search_area_w = 256                # the reference holds the area in a uint8_t: 255 is its largest value
     with pytest.raises(pkg.SvtMeError, match="0x80001005"):
         ctx.motion_estimate([(0, 1, 1, p)])
     ctx.close()

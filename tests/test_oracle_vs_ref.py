@@ -59,6 +59,49 @@ def test_parameter_sweep(libs, over):
     _compare(libs, 320, 192, seed=len(str(over)), nl=2, tl=1, over=over, synth=dict(max_shift=40))
 
 
+@pytest.mark.parametrize("w,h", [(80, 64), (72, 64), (88, 128), (112, 64), (144, 128), (200, 72), (720, 480), (848, 480), (1368, 128)])
+@pytest.mark.parametrize("nl,tl", [(2, 1), (1, 0), (2, 0)])
+def test_edge_sb_widths(libs, w, h, nl, tl):
+    """Edge SBs 8 / 16 / 24 / 48 wide (every width % 64 the reference has a live NxM kernel for, EbComputeSAD.h:139-150):
+    hme_mv_center_check on the narrow block, the HME levels on 2..24-wide decimated blocks (C SadLoopKernel for the widths
+    the AVX2 kernel has no case for; quirks Q12 and Q13 in the 4- and 24-wide AVX2 cases)."""
+    for seed in range(2 if w * h > 100000 else 4):
+        _compare(libs, w, h, seed=w + h + nl + 17 * seed, nl=nl, tl=tl, synth=dict(max_shift=30))
+
+
+@pytest.mark.parametrize("w", [72, 80, 88, 112])
+def test_edge_sb_widths_saturating_content(libs, w):
+    _compare(libs, w, 128, seed=w, nl=2, tl=1, synth=dict(noise=12.0, contrast=4.0, max_shift=60))
+    _compare(libs, w, 128, seed=w + 1, nl=2, tl=1, over={"num_pus": 209}, synth=dict(noise=12.0, contrast=4.0, max_shift=60))
+
+
+def test_widths_without_a_live_kernel_are_rejected(libs):
+    """40- and 56-wide edge SBs: the reference's hme_mv_center_check calls NxMSadKernelVoidFunc (EbComputeSAD.h:143-147),
+    its result is undefined; the oracle refuses them instead of inventing one."""
+    meo, _ = libs
+    for w in (104, 120):
+        fr = M.synth_video(w, 64, 3, seed=1)
+        po = [M.build_pyramid(meo, "meo", f) for f in fr]
+        p = M.default_params(meo, "meo", w, 64)
+        with pytest.raises(Exception):
+            M.motion_estimate(meo, "meo", p, po[1], po[0], po[2])
+
+
+@pytest.mark.parametrize("over", [
+    {"search_area_w": 65, "search_area_h": 65}, {"search_area_w": 96, "search_area_h": 80},
+    {"search_area_w": 127, "search_area_h": 127}, {"search_area_w": 127, "search_area_h": 33},
+    {"search_area_w": 71, "search_area_h": 127}, {"search_area_w": 200, "search_area_h": 255},
+    {"search_area_w": 121, "search_area_h": 3},
+])
+@pytest.mark.parametrize("pus", [85, 209])
+def test_wide_search_areas(libs, over, pus):
+    """MotionEstimateLcu searches MIN(search_area, 127) (ME.c:6644-6645); the context fields are uint8_t
+    (EbMotionEstimationContext.h:403-404), so 255 is the largest value the reference can hold."""
+    _compare(libs, 320, 192, seed=len(str(over)) + pus, nl=2, tl=1, over=dict(over, num_pus=pus), synth=dict(max_shift=70))
+    if pus == 85:
+        _compare(libs, 208, 136, seed=len(str(over)), nl=1, tl=0, over=over, synth=dict(max_shift=50))
+
+
 @pytest.mark.parametrize("w,h,nl,tl,over", [
     (256, 192, 2, 1, {}), (128, 128, 1, 0, {}), (160, 72, 2, 2, {}), (320, 136, 2, 0, {"same_ref_poc": 1}),
     (128, 128, 2, 1, {"use_subpel": 0}), (256, 128, 2, 1, {"cu8x8_mode": 1}), (192, 128, 2, 3, {"search_area_w": 21, "search_area_h": 9}),
@@ -86,10 +129,11 @@ def test_content_extremes(libs, synth):
     _compare(libs, 256, 192, seed=8, nl=2, tl=2, is_ref=0, synth=synth)
 
 
-def test_black_white_checker(libs):
-    """0/255 checkerboards: the worst case for the 16-bit saturating partial sums (quirk Q3)."""
+@pytest.mark.parametrize("w", [256, 112, 80, 72, 88])
+def test_black_white_checker(libs, w):
+    """0/255 checkerboards: the worst case for the 16-bit saturating partial sums (quirks Q3, Q13)."""
     meo, ref = libs
-    w, h = 256, 128
+    h = 128
     yy, xx = np.mgrid[0:h, 0:w]
     a = (((xx // 3 + yy // 5) & 1) * 255).astype(np.uint8)
     b = (((xx // 3 + yy // 5 + 1) & 1) * 255).astype(np.uint8)
