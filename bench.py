@@ -89,10 +89,10 @@ def select_workload(name):
         SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
 
 
-def gop_jobs():
+def gop_jobs(n_pics=None):
     """[(poc, temporal_layer, ref0_poc, ref1_poc)] for pictures 1..120 in decode order."""
     jobs = []
-    for g in range((N_PICS - 1) // 8):
+    for g in range(((n_pics or N_PICS) - 1) // 8):
         base = g * 8
         for off, tl, d0, d1 in MINIGOP:
             poc = base + off
@@ -103,8 +103,9 @@ def gop_jobs():
     return jobs
 
 
-def synth_sequence(n, seed):
+def synth_sequence(n, seed, w=None, h=None):
     """n luma planes of a panning, noisy synthetic scene (uint8, HxW)."""
+    W, H = (w or globals()["W"]), (h or globals()["H"])
     rng = np.random.default_rng(seed)
     big = rng.integers(0, 256, size=((H + 512) // 8, (W + 768) // 8), dtype=np.uint8).astype(np.float32)
     big = np.kron(big, np.ones((8, 8), dtype=np.float32))
@@ -263,11 +264,19 @@ def run_reference_impl(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def search_area_note():
+    if not SEARCH_AREA:
+        return "64x64 (preset tables)"
+    n = min(SEARCH_AREA, 127)
+    return f"{n}x{n} (--search-area {SEARCH_AREA}; the reference searches MIN(area, 127)): {n * n / 4096:.2f}x the algorithmic full-pel work of 64x64"
+
+
 def workload_config(n_gpus):
     if SHARD_SB_ROWS:
         return {"workload": "3840x2160 10-bit luma (16-bit samples, split 8+2 on upload; ME on the 8-bit plane), 33 pictures (1 intra + 32 B), "
                             "hierarchical mini-GOP 8 / 4 temporal layers, full open-loop ME per picture with the 4K search tables",
                 "frames_per_step": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": 85,
+                "search_area": search_area_note(),
                 "parallelism": f"every picture on every GPU, SB rows of each picture sharded x{n_gpus}, no collective",
                 "l2_policy": "inputs larger than L2 (33 planes = 274 MB + 8-bit pyramids per step)"}
     return {"workload": "1920x1080 8-bit luma, 121 pictures (1 intra + 120 B), hierarchical mini-GOP 8 / 4 temporal layers, "
@@ -276,8 +285,272 @@ def workload_config(n_gpus):
                         + (" + forward transform and quantisation of one 1920x1088 luma residual plane per frame (the 19 DCT_DCT sizes in turn, "
                            "8 planes per launch) on a second stream of the same GPU [BASELINE configs[4]: one such stream per GPU]" if WITH_TXQ else ""),
             "frames_per_step_per_gpu": N_PICS - 1, "sb_per_frame": SB_PER_FRAME, "lists_per_frame": 2, "pus_per_sb": NUM_PUS,
-            "streams": n_gpus, "parallelism": f"one picture stream per GPU x{n_gpus}, no collective",
+            "search_area": search_area_note(), "streams": n_gpus, "parallelism": f"one picture stream per GPU x{n_gpus}, no collective",
             "l2_policy": "inputs larger than L2 (121 luma planes = 251 MB + 306 MB of padded pyramids per step)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# Sharded modes (north_star: "pictures shard by picture, and by SB row within 4K frames, across the GPUs of one box;
+# references replicated peer-to-peer over NVLink; no NCCL collective"). Measured OUTSIDE the headline's timed region and
+# reported as extra keys of the default line:
+#   strong_1080p  ONE 120-picture 1080p stream dealt to the N ranks (sharding.picture_shard_contiguous); every picture
+#                 is uploaded from the host by its owner only and imported by the ranks that reference it straight from the
+#                 owner's HBM (svtme_slot_export / svtme_picture_upload_ipc); results return to host memory
+#   strong_4k     3840x2160 10-bit pictures, every picture on every GPU, its 2040 SBs sharded in raster order
+#                 (SvtMeJob.range_in_sbs, sharding.sb_shard)
+#   peer_parity   the sharded 1080p run's me_results of ALL 120 pictures against the single-GPU run of the same stream
+#                 (CRC per picture) + the pyramid of one imported picture against a local upload
+# Both carry an in-run single-GPU baseline (rank 0 alone runs the whole job while the other ranks wait), so
+# efficiency = T(1 GPU) / (N x T(N GPUs)) comes from one process set on one box.
+def _timed_steps(torch, ctx, fn, steps, sync_all):
+    st = torch.cuda.ExternalStream(ctx.stream)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record(st)
+    for _ in range(steps):
+        fn()
+    ctx.join()
+    e1.record(st)
+    sync_all()
+    return e0.elapsed_time(e1)
+
+
+def _max_over_ranks(torch, dist, ms):
+    if dist is None:
+        return ms
+    t = torch.tensor([ms], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def measure_strong_1080p(pkg, torch, dist, host_pg, rank, world, local_rank, host, steps, warmup):
+    """host: pinned uint8 tensor [N_PICS, H, W] holding the SAME sequence on every rank."""
+    shard = importlib.import_module("svt-av1-1_b200.sharding")
+    jobs = gop_jobs()
+    ctx = pkg.MeContext(W, H, 2 * N_PICS, device=local_rank)
+    host_ptrs = [host[i].data_ptr() for i in range(N_PICS)]
+    count = [0]
+
+    def sync_all():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+
+    def plan(my_jobs):
+        specs = []
+        for poc, tl, r0, r1 in my_jobs:
+            p = pkg.default_params(W, H, 2, tl, 3, 1 if tl < 3 else 0)
+            p.same_ref_poc = 1 if r0 == r1 else 0
+            specs.append((poc, r0, r1, p))
+        res = torch.zeros((len(my_jobs), ctx.n_sb, 85, 40), dtype=torch.uint8).pin_memory()
+        ptrs = [res[i].data_ptr() for i in range(len(my_jobs))]
+        batches = [[ctx.make_jobs([(c + o, a + o, b + o, p) for (c, a, b, p) in specs[g:g + 8]], out_ptrs=ptrs[g:g + 8])[0]
+                    for g in range(0, len(specs), 8)] for o in (0, N_PICS)]
+        return res, batches
+
+    def crcs(my_jobs, res):
+        ctx.synchronize()
+        return {j[0]: zlib.crc32(res[i].numpy().tobytes()) for i, j in enumerate(my_jobs)}
+
+    # ---- rank 0 alone: the whole stream on one GPU
+    alone_ms, alone_crc = None, None
+    if rank == 0:
+        res_all, batches_all = plan(jobs)
+
+        def step_alone():
+            base = (count[0] & 1) * N_PICS
+            count[0] += 1
+            for g in range(0, N_PICS - 1, 8):
+                pics = list(range(0 if g == 0 else g + 1, g + 9))
+                ctx.upload_ptr_batch([base + i for i in pics], [host_ptrs[i] for i in pics], W)
+            for jb in batches_all[(count[0] - 1) & 1]:
+                ctx.motion_estimate_async(jb)
+        for _ in range(max(3, warmup)):                   # >= 3: every entry of the context's batch ring allocates on first use
+            step_alone()
+        alone_ms = _timed_steps(torch, ctx, step_alone, steps, sync_all) / steps
+        alone_crc = crcs(jobs, res_all)
+    if world == 1:
+        ctx.close()
+        return {"n_gpus": 1, "frames_per_sec": (N_PICS - 1) / (alone_ms / 1e3), "ms_per_step": alone_ms, "efficiency": 1.0}, "n/a (one GPU)"
+    dist.barrier(group=host_pg)
+
+    # ---- all ranks: the stream dealt by picture, references imported from their owners
+    mine, need, owner = shard.picture_shard_contiguous(jobs, world, rank)
+    own = [p for p in range(N_PICS) if owner.get(p) == rank]
+    imports = [p for p in need if owner[p] != rank]
+    tokens = [None] * world
+    dist.all_gather_object(tokens, [ctx.export_slot(i) for i in range(2 * N_PICS)], group=host_pg)
+    res_mine, batches_mine = plan(mine)
+    count[0] = 0
+
+    def step_sharded():
+        which = count[0] & 1
+        base = which * N_PICS
+        count[0] += 1
+        ctx.synchronize_uploads()                       # my imports of the previous step have landed ...
+        for i0 in range(0, len(own), 64):
+            ctx.upload_ptr_batch([base + i for i in own[i0:i0 + 64]], [host_ptrs[i] for i in own[i0:i0 + 64]], W)
+        dist.barrier(group=host_pg)                     # ... on every rank, and every owner has ISSUED this step's uploads
+        for i in imports:                               # ordered behind the owner's upload on the device (inter-process event)
+            ctx.upload_ipc(base + i, tokens[owner[i]][base + i])
+        for jb in batches_mine[which]:
+            ctx.motion_estimate_async(jb)
+
+    def sync_ranks():
+        sync_all()
+        dist.barrier(group=host_pg)
+    for _ in range(max(3, warmup)):
+        step_sharded()
+    ms = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, step_sharded, steps, sync_ranks) / steps)
+    # ---- parity: every rank's rows against rank 0's single-GPU run; one imported picture's pyramid against a local upload
+    my_crc = crcs(mine, res_mine)
+    pyr_ok = True
+    if imports:
+        i = imports[0]
+        last = ((count[0] - 1) & 1) * N_PICS           # slot set of the last step
+        other = N_PICS - last
+        ctx.upload_ptr(other + i, host_ptrs[i], W)
+        ctx.synchronize()
+        pyr_ok = all(np.array_equal(ctx.download_plane(last + i, lvl), ctx.download_plane(other + i, lvl)) for lvl in range(3))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (my_crc, pyr_ok, len(own), len(imports)), group=host_pg)
+    dist.barrier(group=host_pg)
+    ctx.close()
+    if rank != 0:
+        return None, None
+    bad = [poc for g in gathered for poc, c in g[0].items() if alone_crc[poc] != c]
+    n_checked = sum(len(g[0]) for g in gathered)
+    parity = ("ok: %d pictures' me_results identical to the single-GPU run, imported pyramids identical" % n_checked
+              if not bad and all(g[1] for g in gathered) and n_checked == len(jobs) else "MISMATCH: pictures %s, pyramids %s" % (bad[:8], [g[1] for g in gathered]))
+    return {"n_gpus": world, "frames_per_sec": (N_PICS - 1) / (ms / 1e3), "ms_per_step": ms,
+            "single_gpu_frames_per_sec": (N_PICS - 1) / (alone_ms / 1e3), "single_gpu_ms_per_step": alone_ms,
+            "efficiency": alone_ms / (world * ms),
+            "pictures_per_rank": [len(g[0]) for g in gathered], "uploaded_per_rank": [g[2] for g in gathered],
+            "imported_over_nvlink_per_rank": [g[3] for g in gathered],
+            "h2d_bytes_per_step_per_rank": max(g[2] for g in gathered) * W * H,
+            "what": "one 120-picture 1080p stream, pictures dealt to the ranks in contiguous runs of the decode order; host buffers in, "
+                    "me_results to host memory out, inside the timed region; one host barrier per step, no data-path collective"}, parity
+
+
+def measure_strong_4k(pkg, torch, dist, host_pg, rank, world, local_rank, steps, warmup):
+    shard = importlib.import_module("svt-av1-1_b200.sharding")
+    w4, h4, n_pics = 3840, 2160, 33
+    frames = synth_sequence(n_pics, seed=1, w=w4, h=h4)
+    lsb = np.random.default_rng(5).integers(0, 4, size=frames.shape, dtype=np.uint16)
+    host16 = torch.from_numpy((frames.astype(np.uint16) << 2) | lsb).pin_memory()
+    dev8 = torch.from_numpy(frames).cuda()
+    del frames, lsb
+    jobs = gop_jobs(n_pics)
+    ctx = pkg.MeContext(w4, h4, 2 * n_pics, device=local_rank)
+    dev_ptrs = [dev8[i].data_ptr() for i in range(n_pics)]
+    specs = []
+    for poc, tl, r0, r1 in jobs:
+        p = pkg.default_params(w4, h4, 2, tl, 3, 1 if tl < 3 else 0)
+        p.same_ref_poc = 1 if r0 == r1 else 0
+        specs.append((poc, r0, r1, p))
+    count = [0]
+
+    def sync_all():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+
+    def sync_ranks():
+        sync_all()
+        if dist is not None:
+            dist.barrier(group=host_pg)
+
+    def plan(sb_range):
+        n_sb = ctx.n_sb if sb_range is None else sb_range[1] - sb_range[0]
+        res = torch.zeros((len(jobs), n_sb, 85, 40), dtype=torch.uint8).pin_memory()
+        ptrs = [res[i].data_ptr() for i in range(len(jobs))]
+        resident = ctx.make_jobs(specs, out_ptrs=[None] * len(jobs), sb_range=sb_range)[0]
+        e2e = [[ctx.make_jobs([(c + o, a + o, b + o, p) for (c, a, b, p) in specs[g:g + 8]], out_ptrs=ptrs[g:g + 8], sb_range=sb_range)[0]
+                for g in range(0, len(specs), 8)] for o in (0, n_pics)]
+        return res, resident, e2e
+
+    def make_steps(resident, e2e):
+        def step_resident():
+            ctx.upload_device_batch(list(range(n_pics)), dev_ptrs, w4)
+            ctx.motion_estimate_async(resident)
+
+        def step_e2e():
+            which = count[0] & 1
+            count[0] += 1
+            for i in range(n_pics):                    # every rank needs every picture: each uploads all of them over its own host link
+                rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, which * n_pics + i, host16[i].data_ptr(), w4, None)
+                assert rc == 0
+            for jb in e2e[which]:
+                ctx.motion_estimate_async(jb)
+
+        def step_e2e_replicated():
+            """each picture crosses the host link ONCE (owner = picture index mod N); the other ranks read it from the owner's
+            HBM over NVLink while building their own pyramid (svtme_picture_upload_ipc)"""
+            which = count[0] & 1
+            base = which * n_pics
+            count[0] += 1
+            ctx.synchronize_uploads()                   # my imports of the previous step have landed ...
+            for i in range(rank, n_pics, world):
+                rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, base + i, host16[i].data_ptr(), w4, None)
+                assert rc == 0
+            dist.barrier(group=host_pg)                 # ... on every rank, and every owner has ISSUED this step's uploads
+            for i in range(n_pics):
+                if i % world != rank:
+                    ctx.upload_ipc(base + i, tokens[i % world][base + i])
+            for jb in e2e[which]:
+                ctx.motion_estimate_async(jb)
+        return step_resident, step_e2e, step_e2e_replicated
+
+    alone = None
+    if rank == 0:
+        _, resident, e2e = plan(None)
+        sr, se, _ = make_steps(resident, e2e)
+        for _ in range(max(3, warmup)):
+            sr(); se()
+        alone = (_timed_steps(torch, ctx, sr, steps, sync_all) / steps, _timed_steps(torch, ctx, se, steps, sync_all) / steps)
+    out = {"n_gpus": world, "frames_per_step": n_pics - 1, "sb_per_frame": ctx.n_sb,
+           "what": "3840x2160 10-bit (16-bit samples split on upload), 33 pictures, every picture on every GPU, the 2040 SBs of each picture "
+                   "sharded in raster order (SvtMeJob.range_in_sbs); HME level 2 off as in the enc-mode 3 4K tables"}
+    if world == 1:
+        ctx.close()
+        out.update({"resident": {"frames_per_sec": (n_pics - 1) / (alone[0] / 1e3), "ms_per_step": alone[0], "efficiency": 1.0},
+                    "e2e": {"frames_per_sec": (n_pics - 1) / (alone[1] / 1e3), "ms_per_step": alone[1], "efficiency": 1.0}})
+        return out
+    dist.barrier(group=host_pg)
+    first, cnt = shard.sb_shard(ctx.n_sb, world, rank)
+    res_mine, resident, e2e = plan((first, first + cnt))
+    tokens = [None] * world
+    dist.all_gather_object(tokens, [ctx.export_slot(i) for i in range(2 * n_pics)], group=host_pg)
+    sr, se, sx = make_steps(resident, e2e)
+    count[0] = 0
+    for _ in range(max(3, warmup)):
+        sr(); se()
+    ms_r = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, sr, steps, sync_ranks) / steps)
+    ms_e = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, se, steps, sync_ranks) / steps)
+    ctx.synchronize()
+    crc_own = zlib.crc32(res_mine.numpy().tobytes())    # rows from independently uploaded pictures
+    count[0] = 0
+    res_mine.zero_()
+    for _ in range(3):
+        sx()
+    ms_x = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, sx, steps, sync_ranks) / steps)
+    ctx.synchronize()
+    same = [None] * world
+    dist.all_gather_object(same, zlib.crc32(res_mine.numpy().tobytes()) == crc_own, group=host_pg)
+    dist.barrier(group=host_pg)
+    ctx.close()
+    if rank != 0:
+        return None
+    out["sbs_per_rank"] = cnt
+    out["resident"] = {"frames_per_sec": (n_pics - 1) / (ms_r / 1e3), "ms_per_step": ms_r, "single_gpu_ms_per_step": alone[0],
+                       "efficiency": alone[0] / (world * ms_r)}
+    out["e2e"] = {"frames_per_sec": (n_pics - 1) / (ms_e / 1e3), "ms_per_step": ms_e, "single_gpu_ms_per_step": alone[1],
+                  "efficiency": alone[1] / (world * ms_e), "h2d_bytes_per_step_per_rank": n_pics * w4 * h4 * 2,
+                  "note": "every rank uploads every picture over its own host link: the upload does not shrink with N"}
+    out["e2e_replicated"] = {"frames_per_sec": (n_pics - 1) / (ms_x / 1e3), "ms_per_step": ms_x, "single_gpu_ms_per_step": alone[1],
+                             "efficiency": alone[1] / (world * ms_x), "h2d_bytes_per_step_per_rank": len(range(0, n_pics, world)) * w4 * h4 * 2,
+                             "rows_identical_to_independent_uploads": all(same),
+                             "note": "each picture uploaded by one rank (index mod N) and read by the others from that rank's HBM over NVLink "
+                                     "(svtme_picture_upload_ipc); one host barrier per step"}
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -303,7 +576,7 @@ def run_gpu_impl(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     # ---- CPU baseline first (rank 0, N=1 only), while this process has no CUDA context yet
-    cpu = None
+    cpu, cpu_crc = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         frames17 = synth_sequence(17, seed=1)
         arm = CpuArm(frames17)
@@ -311,6 +584,7 @@ def run_gpu_impl(args, rank, world, local_rank):
         arm.run(arm.cores)
         t = arm.run(n_tasks)
         arm.close()
+        cpu_crc = dict(arm.crc)                            # CRC of the CPU implementation's me_results image, pictures 1..16
         cpu = {"value": n_tasks / t, "unit": "frames/s", "cores": arm.cores, "kind": arm.kind,
                "sample": f"{n_tasks} pictures of the first two mini-GOPs, {arm.cores} worker processes, {t:.1f} s wall"}
         if WITH_TXQ:                                       # the same cores then transform + quantise: time per frame adds up
@@ -508,12 +782,38 @@ def run_gpu_impl(args, rank, world, local_rank):
     ctx.set_profiling(False)
     clocks = sampler.stop() if sampler else None
 
+    # ---- parity of the bench's own workload (outside the timed regions): the me_results images of the first 16 pictures,
+    # from the resident path's slots and again after the e2e steps, against the CPU implementation's (the checker, cpu_baseline)
+    def check_rows():
+        ctx.synchronize()
+        return sum(1 for i, j in enumerate(jobs) if j[0] in cpu_crc and zlib.crc32(out[i].numpy().tobytes()) == cpu_crc[j[0]])
+    parity_checked = None
+    whole_pictures = sb_rows is None
+    if cpu_crc and whole_pictures:
+        for jb in gop_batches[0][:(16 + EB - 1) // EB]:
+            ctx.motion_estimate_async(jb)                  # slots 0..16 as the resident steps left them
+        n_res = check_rows()
+        out.zero_()
     for _ in range(max(1, args.warmup // 2)):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
     ctx.fetch(gop_batches[0][-1])
+    if cpu_crc and whole_pictures:
+        n_e2e = check_rows()
+        n_want = sum(1 for j in jobs if j[0] in cpu_crc)
+        parity_checked = {"pictures": n_want, "resident_identical": n_res, "e2e_identical": n_e2e,
+                          "against": cpu["kind"] + " (whole 40-byte me_results rows of every SB and PU, CRC per picture)",
+                          "ok": n_res == n_want and n_e2e == n_want}
     checksum = int(out.view(torch.int32).sum(dtype=torch.int64).item()) if rank == 0 else 0
     ctx.close()
+    del dev
+    strong_1080p = strong_4k = peer_parity = None
+    if args.workload == "me" and not SEARCH_AREA and not args.no_strong:
+        host_pg = dist.new_group(backend="gloo") if dist is not None else None      # host-side hand-shakes only
+        host1 = host if rank == 0 else torch.from_numpy(synth_sequence(N_PICS, seed=1)).pin_memory()   # ONE stream, the same on every rank
+        strong_1080p, peer_parity = measure_strong_1080p(pkg, torch, dist, host_pg, rank, world, local_rank, host1, max(2, args.steps // 2), args.warmup)
+        del host1
+        strong_4k = measure_strong_4k(pkg, torch, dist, host_pg, rank, world, local_rank, max(2, args.steps // 2), args.warmup)
 
     if rank == 0:
         frames_total = (1 if SHARD_SB_ROWS else world) * (N_PICS - 1) * args.steps
@@ -579,7 +879,8 @@ def run_gpu_impl(args, rank, world, local_rank):
                               "byte_sads_per_step": step_sads},
             "kernel_ms_per_step": {k: v[0] / args.steps for k, v in kt.items()},
             "kernel_launches_per_step": {k: v[1] / args.steps for k, v in kt.items()},
-            "clocks": clocks, "result_checksum": checksum,
+            "clocks": clocks, "result_checksum": checksum, "parity_checked": parity_checked,
+            "strong_1080p": strong_1080p, "strong_4k": strong_4k, "peer_parity": peer_parity,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
@@ -888,6 +1189,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the sharded-mode measurements (strong_1080p / strong_4k keys)")
+    ap.add_argument("--search-area", type=int, default=0,
+                    help="full-pel search area N x N (1..255; the reference searches MIN(N, 127)) instead of the preset's 64 x 64")
     ap.add_argument("--workload", default="me", choices=["me", "me4k", "me209", "streams", "txq"],
                     help="me: 1080p motion estimation (headline, BASELINE configs[1]); me4k: 3840x2160 10-bit, SB rows sharded over "
                          "the GPUs (configs[2]); txq: transform + quantisation sweep (configs[3])")
@@ -899,6 +1203,9 @@ def main():
         run_txq(args, rank, world, local_rank)
         return
     select_workload(args.workload)
+    if args.search_area:
+        global SEARCH_AREA
+        SEARCH_AREA = args.search_area
     if args.impl == "reference":
         run_reference_impl(args, rank)
         return

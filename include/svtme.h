@@ -96,7 +96,10 @@ typedef struct SvtMeJob {
      * GPUs: every GPU holds the pictures, searches its rows and returns only those rows (the ME segments of
      * EbMotionEstimationProcess.c:478-556 are the same partition on the CPU). */
     int32_t        sb_row_begin, sb_row_end;
-    int32_t        reserved;                         /* keeps params 8-byte aligned; set to 0 */
+    /* 0: the range above counts SB rows. 1: it counts SBs in raster order, [sb_row_begin, sb_row_end) of the picture's
+     * SBs -- the finer shard (a 4K picture has 34 SB rows but 2040 SBs: eight GPUs take 255 SBs each, whole rows would
+     * leave the busiest GPU with 5 rows against 4.25 on average). Results / debug hold the SBs of the range either way. */
+    int32_t        range_in_sbs;
     SvtMeParams    params;
     SvtMePuResult *results;                          /* HOST memory, [SBs of the row range][params.num_pus]; may be NULL */
     SvtMeSbDebug  *debug;                            /* HOST memory, [SBs of the row range]; may be NULL */

@@ -48,7 +48,7 @@ class SvtMeLcuPicture(C.Structure):
 
 class SvtMeJob(C.Structure):
     _fields_ = [("cur_slot", C.c_int32), ("ref0_slot", C.c_int32), ("ref1_slot", C.c_int32),
-                ("sb_row_begin", C.c_int32), ("sb_row_end", C.c_int32), ("reserved", C.c_int32),
+                ("sb_row_begin", C.c_int32), ("sb_row_end", C.c_int32), ("range_in_sbs", C.c_int32),
                 ("params", SvtMeParams), ("results", C.c_void_p), ("debug", C.c_void_p)]
 
 
@@ -236,13 +236,14 @@ class MeContext:
         assert (s.value, r.value, p.value) == (w, h, pad)
         return out
 
-    def make_jobs(self, specs, want_debug=False, out_ptrs=None, sb_rows=None):
+    def make_jobs(self, specs, want_debug=False, out_ptrs=None, sb_rows=None, sb_range=None):
         """specs: list of (cur_slot, ref0_slot, ref1_slot, SvtMeParams). sb_rows = (begin, end): search only those SB rows
-        of every picture (results/debug then hold just the SBs of that range). Returns (jobs array, results, debug)."""
+        of every picture; sb_range = (begin, end): only those SBs in raster order (results/debug then hold just the SBs of
+        that range). Returns (jobs array, results, debug)."""
         n = len(specs)
         jobs = (SvtMeJob * n)()
         sb_cols = (self.width + 63) // 64
-        n_sb = self.n_sb if sb_rows is None else (sb_rows[1] - sb_rows[0]) * sb_cols
+        n_sb = (sb_range[1] - sb_range[0]) if sb_range is not None else self.n_sb if sb_rows is None else (sb_rows[1] - sb_rows[0]) * sb_cols
         # every job's rows are [n_sb][its own num_pus]: one array when the batch is uniform (85 or 209), else a list
         pus = [int(sp[3].num_pus) for sp in specs]
         if out_ptrs is not None:
@@ -254,15 +255,17 @@ class MeContext:
         debug = np.zeros((n, n_sb), dtype=SB_DEBUG_DTYPE) if want_debug else None
         for i, (cur, r0, r1, prm) in enumerate(specs):
             jobs[i].cur_slot, jobs[i].ref0_slot, jobs[i].ref1_slot = cur, r0, (r1 if r1 is not None else r0)
-            if sb_rows is not None:
+            if sb_range is not None:
+                jobs[i].sb_row_begin, jobs[i].sb_row_end, jobs[i].range_in_sbs = sb_range[0], sb_range[1], 1
+            elif sb_rows is not None:
                 jobs[i].sb_row_begin, jobs[i].sb_row_end = sb_rows
             jobs[i].params = prm
             jobs[i].results = results[i].ctypes.data if out_ptrs is None else out_ptrs[i]
             jobs[i].debug = debug[i].ctypes.data if want_debug else None
         return jobs, results, debug
 
-    def motion_estimate(self, specs, want_debug=False, sb_rows=None):
-        jobs, results, debug = self.make_jobs(specs, want_debug, sb_rows=sb_rows)
+    def motion_estimate(self, specs, want_debug=False, sb_rows=None, sb_range=None):
+        jobs, results, debug = self.make_jobs(specs, want_debug, sb_rows=sb_rows, sb_range=sb_range)
         self._check(self.lib.svtme_motion_estimate(self._h, jobs, len(specs)), "svtme_motion_estimate")
         return results, debug
 

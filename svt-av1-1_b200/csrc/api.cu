@@ -254,7 +254,12 @@ int64_t svtme_kernel_launches(const SvtMeContext* ctx) { return ctx ? ctx->launc
 
 // A slot may be rewritten only after the last batch that reads it has finished its kernels.
 static int32_t guard_slot_rewrite(SvtMeContext* ctx, Slot& s) {
-    if (s.last_reader >= 0) CU(cudaStreamWaitEvent(ctx->copy_in, ctx->ring[s.last_reader].computed, 0));
+    // The ring entry's event belongs to the slot's last reader only until the entry is reused, kRing submissions later; by then
+    // that batch has drained (svtme_motion_estimate_async waits for it before reusing the entry), so no wait is needed at all.
+    // (Waiting on the recycled event made the upload of a sequence's NEXT pictures wait for the batches submitted just before
+    // it, i.e. uploads did not overlap the searches.)
+    if (s.last_reader >= 0 && ctx->seq - s.last_reader_seq <= kRing)
+        CU(cudaStreamWaitEvent(ctx->copy_in, ctx->ring[s.last_reader].computed, 0));
     std::lock_guard<std::mutex> lock(ctx->peer_mu);
     for (cudaEvent_t e : s.peer_reads)                    // peers still copying the old picture; a context that has been
         if (cudaStreamWaitEvent(ctx->copy_in, e, 0) != cudaSuccess) (void)cudaGetLastError();   // destroyed since has drained its copies
@@ -535,9 +540,10 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
             (j.params.num_lists == 2 && (j.ref1_slot < 0 || j.ref1_slot >= nslots)))
             return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: slot out of range");
         if (j.sb_row_begin != 0 || j.sb_row_end != 0) {
-            if (j.sb_row_begin < 0 || j.sb_row_end <= j.sb_row_begin || j.sb_row_end > ctx->sb_rows)
-                return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: SB row range out of the picture");
+            if (j.sb_row_begin < 0 || j.sb_row_end <= j.sb_row_begin || j.sb_row_end > (j.range_in_sbs ? ctx->n_sb : ctx->sb_rows))
+                return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: SB range out of the picture");
         }
+        if (j.range_in_sbs != 0 && j.range_in_sbs != 1) return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate: range_in_sbs must be 0 or 1");
         max_lists = j.params.num_lists > max_lists ? j.params.num_lists : max_lists;
     }
     const int bi = ctx->next;
@@ -563,8 +569,9 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         d.debug = j.debug ? b.d_debug + (size_t)i * ctx->n_sb : nullptr;
         d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
         const bool whole = j.sb_row_begin == 0 && j.sb_row_end == 0;
-        d.sb_begin = whole ? 0 : j.sb_row_begin * ctx->sb_cols;
-        d.sb_end = whole ? ctx->n_sb : j.sb_row_end * ctx->sb_cols;
+        const int unit = j.range_in_sbs ? 1 : ctx->sb_cols;
+        d.sb_begin = whole ? 0 : j.sb_row_begin * unit;
+        d.sb_end = whole ? ctx->n_sb : j.sb_row_end * unit;
         max_sb = d.sb_end - d.sb_begin > max_sb ? d.sb_end - d.sb_begin : max_sb;
         for (int sl : { j.cur_slot, j.ref0_slot, r1 }) {
             Slot& s = ctx->slots[sl];
@@ -734,8 +741,9 @@ extern "C" int32_t svtme_motion_estimate_static(SvtMeContext* ctx, const SvtMeJo
     if (j.cur_slot < 0 || j.cur_slot >= nslots || j.ref0_slot < 0 || j.ref0_slot >= nslots || r1 < 0 || r1 >= nslots)
         return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: slot out of range");
     const bool whole = j.sb_row_begin == 0 && j.sb_row_end == 0;
-    if (!whole && (j.sb_row_begin < 0 || j.sb_row_end <= j.sb_row_begin || j.sb_row_end > ctx->sb_rows))
-        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: SB row range out of the picture");
+    if (j.range_in_sbs != 0 && j.range_in_sbs != 1) return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: range_in_sbs must be 0 or 1");
+    if (!whole && (j.sb_row_begin < 0 || j.sb_row_end <= j.sb_row_begin || j.sb_row_end > (j.range_in_sbs ? ctx->n_sb : ctx->sb_rows)))
+        return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_motion_estimate_static: SB range out of the picture");
     CU(cudaSetDevice(ctx->device));
     std::lock_guard<std::mutex> lock(g_static_mu);
     StaticArena* a = nullptr;
@@ -748,8 +756,8 @@ extern "C" int32_t svtme_motion_estimate_static(SvtMeContext* ctx, const SvtMeJo
     d.scratch = a->scratch; d.scratch_ext = nullptr; d.results = a->results;
     d.debug = j.debug ? a->debug : nullptr;
     d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
-    d.sb_begin = whole ? 0 : j.sb_row_begin * ctx->sb_cols;
-    d.sb_end = whole ? ctx->n_sb : j.sb_row_end * ctx->sb_cols;
+    d.sb_begin = whole ? 0 : j.sb_row_begin * (j.range_in_sbs ? 1 : ctx->sb_cols);
+    d.sb_end = whole ? ctx->n_sb : j.sb_row_end * (j.range_in_sbs ? 1 : ctx->sb_cols);
     const int n_sb = d.sb_end - d.sb_begin;
     cudaStream_t st = ctx->stream;
     for (int sl : { j.cur_slot, j.ref0_slot, r1 }) CU(cudaStreamWaitEvent(st, ctx->slots[sl].ready, 0));
