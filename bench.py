@@ -382,18 +382,31 @@ def measure_strong_1080p(pkg, torch, dist, host_pg, rank, world, local_rank, hos
     res_mine, batches_mine = plan(mine)
     count[0] = 0
 
-    def step_sharded():
-        which = count[0] & 1
+    def fetch_pictures(which):
+        """pictures of one sequence into slot set `which`: my own from the host, the others' from their owners' HBM"""
         base = which * N_PICS
-        count[0] += 1
-        ctx.synchronize_uploads()                       # my imports of the previous step have landed ...
+        ctx.synchronize_uploads()                       # my imports of the previous sequence have landed ...
         for i0 in range(0, len(own), 64):
             ctx.upload_ptr_batch([base + i for i in own[i0:i0 + 64]], [host_ptrs[i] for i in own[i0:i0 + 64]], W)
-        dist.barrier(group=host_pg)                     # ... on every rank, and every owner has ISSUED this step's uploads
+        dist.barrier(group=host_pg)                     # ... on every rank, and every owner has ISSUED this sequence's uploads
         for i in imports:                               # ordered behind the owner's upload on the device (inter-process event)
             ctx.upload_ipc(base + i, tokens[owner[i]][base + i])
+
+    def step_sharded():
+        # software pipeline, as a streaming encoder's look-ahead would run it: the NEXT sequence's pictures are fetched (host
+        # copies, barrier, NVLink imports) while this sequence is searched; every timed step holds one fetch and one search
+        which = count[0] & 1
+        count[0] += 1
+        for jb in batches_mine[which]:                  # searches first: the GPU has work queued while the host sits in the barrier
+            ctx.motion_estimate_async(jb)
+        fetch_pictures(which ^ 1)
+
+    def step_search_only():                             # diagnostic: the same batches with the pictures left in their slots
+        which = count[0] & 1
+        count[0] += 1
         for jb in batches_mine[which]:
             ctx.motion_estimate_async(jb)
+    fetch_pictures(0)
 
     def sync_ranks():
         sync_all()
@@ -401,6 +414,7 @@ def measure_strong_1080p(pkg, torch, dist, host_pg, rank, world, local_rank, hos
     for _ in range(max(3, warmup)):
         step_sharded()
     ms = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, step_sharded, steps, sync_ranks) / steps)
+    ms_search = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, step_search_only, steps, sync_ranks) / steps)
     # ---- parity: every rank's rows against rank 0's single-GPU run; one imported picture's pyramid against a local upload
     my_crc = crcs(mine, res_mine)
     pyr_ok = True
@@ -408,9 +422,10 @@ def measure_strong_1080p(pkg, torch, dist, host_pg, rank, world, local_rank, hos
         i = imports[0]
         last = ((count[0] - 1) & 1) * N_PICS           # slot set of the last step
         other = N_PICS - last
-        ctx.upload_ptr(other + i, host_ptrs[i], W)
+        spare = [p for p in range(N_PICS) if p not in need][0]      # a slot no job of this rank reads
+        ctx.upload_ptr(other + spare, host_ptrs[i], W)
         ctx.synchronize()
-        pyr_ok = all(np.array_equal(ctx.download_plane(last + i, lvl), ctx.download_plane(other + i, lvl)) for lvl in range(3))
+        pyr_ok = all(np.array_equal(ctx.download_plane(last + i, lvl), ctx.download_plane(other + spare, lvl)) for lvl in range(3))
     gathered = [None] * world
     dist.all_gather_object(gathered, (my_crc, pyr_ok, len(own), len(imports)), group=host_pg)
     dist.barrier(group=host_pg)
@@ -424,6 +439,9 @@ def measure_strong_1080p(pkg, torch, dist, host_pg, rank, world, local_rank, hos
     return {"n_gpus": world, "frames_per_sec": (N_PICS - 1) / (ms / 1e3), "ms_per_step": ms,
             "single_gpu_frames_per_sec": (N_PICS - 1) / (alone_ms / 1e3), "single_gpu_ms_per_step": alone_ms,
             "efficiency": alone_ms / (world * ms),
+            "search_only_ms_per_step": ms_search, "search_only_efficiency": alone_ms / (world * ms_search),
+            "search_only_note": "the same per-rank batches with no fetch (pictures left in their slots, results still copied out): "
+                                "what the smaller per-rank batches cost on the GPU; the rest of the gap is the fetch (host copies, barrier, imports)",
             "pictures_per_rank": [len(g[0]) for g in gathered], "uploaded_per_rank": [g[2] for g in gathered],
             "imported_over_nvlink_per_rank": [g[3] for g in gathered],
             "h2d_bytes_per_step_per_rank": max(g[2] for g in gathered) * W * H,
@@ -481,22 +499,27 @@ def measure_strong_4k(pkg, torch, dist, host_pg, rank, world, local_rank, steps,
             for jb in e2e[which]:
                 ctx.motion_estimate_async(jb)
 
-        def step_e2e_replicated():
+        def fetch_replicated(which):
             """each picture crosses the host link ONCE (owner = picture index mod N); the other ranks read it from the owner's
             HBM over NVLink while building their own pyramid (svtme_picture_upload_ipc)"""
-            which = count[0] & 1
             base = which * n_pics
-            count[0] += 1
-            ctx.synchronize_uploads()                   # my imports of the previous step have landed ...
+            ctx.synchronize_uploads()                   # my imports of the previous sequence have landed ...
             for i in range(rank, n_pics, world):
                 rc = ctx.lib.svtme_picture_upload_16bit(ctx._h, base + i, host16[i].data_ptr(), w4, None)
                 assert rc == 0
-            dist.barrier(group=host_pg)                 # ... on every rank, and every owner has ISSUED this step's uploads
+            dist.barrier(group=host_pg)                 # ... on every rank, and every owner has ISSUED this sequence's uploads
             for i in range(n_pics):
                 if i % world != rank:
                     ctx.upload_ipc(base + i, tokens[i % world][base + i])
+
+        def step_e2e_replicated():
+            # software pipeline: fetch the next sequence's pictures while this one is searched (one fetch + one search per step)
+            which = count[0] & 1
+            count[0] += 1
             for jb in e2e[which]:
                 ctx.motion_estimate_async(jb)
+            fetch_replicated(which ^ 1)
+        step_e2e_replicated.prime = lambda: fetch_replicated(0)
         return step_resident, step_e2e, step_e2e_replicated
 
     alone = None
@@ -529,6 +552,7 @@ def measure_strong_4k(pkg, torch, dist, host_pg, rank, world, local_rank, steps,
     crc_own = zlib.crc32(res_mine.numpy().tobytes())    # rows from independently uploaded pictures
     count[0] = 0
     res_mine.zero_()
+    sx.prime()
     for _ in range(3):
         sx()
     ms_x = _max_over_ranks(torch, dist, _timed_steps(torch, ctx, sx, steps, sync_ranks) / steps)
