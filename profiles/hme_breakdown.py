@@ -12,12 +12,14 @@ def run(tag, over, tls=None):
         p.same_ref_poc = 1 if r0 == r1 else 0
         for k,v in over.items(): setattr(p,k,v)
         specs.append((poc, r0, r1, p))
-    jobs,_,_ = ctx.make_jobs(specs)
+    jobs, keep, _ = ctx.make_jobs(specs)      # `keep`: the jobs point into this host array
+    run.keep = keep
     ctx.set_profiling(True)
     for _ in range(2): ctx.motion_estimate_async(jobs)
     ctx.kernel_times(reset=True)
     for _ in range(5): ctx.motion_estimate_async(jobs)
     kt = ctx.kernel_times(reset=True)
+    ctx.synchronize()
     print(tag, len(specs), 'jobs: hme ms/job', round(kt['hme'][0]/5/len(specs),4), 'fullpel', round(kt['fullpel'][0]/5/len(specs),4), 'subpel', round(kt['subpel'][0]/5/len(specs),4))
 run('all', {})
 run('no hme (center only)', {'enable_hme_flag':0})

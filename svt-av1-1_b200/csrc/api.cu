@@ -35,6 +35,7 @@ struct Batch {
     size_t res_off[SVTME_MAX_BATCH];      // first result row of every job of the batch in d_results
     SvtMeSbDebug* d_debug = nullptr;      // [cap][n_sb]
     DJob* d_jobs = nullptr;               // [cap]
+    uint32_t* d_worklist = nullptr;       // [cap][n_sb + 1]: deferred-SB lists of the sub-pel passes, one region per chunk (counter first)
     DJob* h_jobs = nullptr;               // pinned
     cudaEvent_t computed = nullptr;       // kernels of the last batch that used this entry are done
     cudaEvent_t drained = nullptr;        // ... and its results have reached the host
@@ -217,9 +218,9 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
 }
 
 static void free_batch(Batch& b) {
-    cudaFree(b.d_scratch); cudaFree(b.d_scratch_ext); cudaFree(b.d_results); cudaFree(b.d_debug); cudaFree(b.d_jobs);
+    cudaFree(b.d_scratch); cudaFree(b.d_scratch_ext); cudaFree(b.d_results); cudaFree(b.d_debug); cudaFree(b.d_jobs); cudaFree(b.d_worklist);
     if (b.h_jobs) cudaFreeHost(b.h_jobs);
-    b.d_scratch = nullptr; b.d_scratch_ext = nullptr; b.res_pus = 0; b.d_results = nullptr; b.d_debug = nullptr; b.d_jobs = nullptr; b.h_jobs = nullptr;
+    b.d_scratch = nullptr; b.d_scratch_ext = nullptr; b.res_pus = 0; b.d_results = nullptr; b.d_debug = nullptr; b.d_jobs = nullptr; b.d_worklist = nullptr; b.h_jobs = nullptr;
     b.cap = 0;
 }
 
@@ -496,6 +497,7 @@ static int32_t ensure_batch(SvtMeContext* ctx, Batch& b, int n, bool ext) {
     b.res_pus = pus;
     CU(cudaMalloc(&b.d_debug, sizeof(SvtMeSbDebug) * (size_t)n * ctx->n_sb));
     CU(cudaMalloc(&b.d_jobs, sizeof(DJob) * (size_t)n));
+    CU(cudaMalloc(&b.d_worklist, sizeof(uint32_t) * (size_t)n * (ctx->n_sb + 1)));
     CU(cudaMallocHost(&b.h_jobs, sizeof(DJob) * (size_t)n));
     b.cap = n;
     return SVTME_OK;
@@ -596,7 +598,8 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
             for (int ext = 0; ext < 2; ext++) for (int wide = 0; wide < 2; wide++) {
                 if (!cls[ext][wide]) continue;
                 { LaunchTimer t(ctx, SVTME_KERNEL_FULLPEL, st); launch_fullpel(dj, nj, max_sb, list, ext != 0, wide != 0, st); }
-                { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, st); launch_subpel(dj, nj, max_sb, list, ext != 0, wide != 0, st); }
+                { LaunchTimer t(ctx, SVTME_KERNEL_SUBPEL, st); launch_subpel(dj, nj, max_sb, list, ext != 0, wide != 0, b.d_worklist + (size_t)j0 * (ctx->n_sb + 1) + 1, st); }
+                if (!wide) ctx->launches++;              // narrow areas: small-window pass + deferred pass
             }
         }
         for (int ext = 0; ext < 2; ext++) {
@@ -705,6 +708,7 @@ struct StaticArena {
     SbScratch scratch[SVTME_STATIC_MAX_SBS];
     SvtMePuResult results[(size_t)SVTME_STATIC_MAX_SBS * kNumPu];
     SvtMeSbDebug debug[SVTME_STATIC_MAX_SBS];
+    uint32_t worklist[SVTME_STATIC_MAX_SBS + 4];      // counter + deferred SBs of the sub-pel passes
 };
 static __device__ __align__(256) unsigned char g_static_arena[(sizeof(StaticArena) + 255) / 256 * 256];
 
@@ -769,8 +773,8 @@ extern "C" int32_t svtme_motion_estimate_static(SvtMeContext* ctx, const SvtMeJo
     for (int list = 0; list < j.params.num_lists; list++) {
         launch_hme(&a->job, 1, n_sb, list, st);
         launch_fullpel(&a->job, 1, n_sb, list, false, wide_search(j.params), st);
-        launch_subpel(&a->job, 1, n_sb, list, false, wide_search(j.params), st);
-        ctx->launches += 3;
+        launch_subpel(&a->job, 1, n_sb, list, false, wide_search(j.params), a->worklist + 1, st);
+        ctx->launches += wide_search(j.params) ? 3 : 4;
     }
     launch_bipred_pack(&a->job, 1, n_sb, false, st);
     ctx->launches++;

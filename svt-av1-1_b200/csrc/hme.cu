@@ -42,24 +42,38 @@ __device__ __forceinline__ void group_bar(int id) {
     }
 }
 
-// SAD of the (sub-sampled) SB against the reference picture at displacement (dx,dy): one warp.
-// NxMSadKernel with doubled strides, ME.c:5918-5926.
-__device__ uint32_t warp_sb_sad(const uint32_t* src_even, const DPlane& rp, int x, int y, int w_words, int rows) {
+// SAD of the (sub-sampled) SB against the reference picture at displacement (dx,dy): one warp, lane = source row.
+// NxMSadKernel with doubled strides, ME.c:5918-5926. Split in two so that the reference words can be in flight while the
+// source SB is still being staged (the centre check is L2-latency bound: three dependent round trips per CTA before).
+struct SbSadRow { uint32_t v[17]; uint32_t sh; };
+__device__ __forceinline__ void warp_sb_sad_load(SbSadRow& row, const DPlane& rp, int x, int y, int w_words, int rows) {
+    const int lane = threadIdx.x & 31;
+    row.sh = 0;
+#pragma unroll
+    for (int c = 0; c < 17; c++) row.v[c] = 0u;
+    if (lane < rows) {
+        // 17 independent aligned loads in flight, then one funnel shift per word
+        const uint8_t* r = rp.at(x, y + 2 * lane);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>((uintptr_t)r & ~(uintptr_t)3);
+        row.sh = ((uint32_t)(uintptr_t)r & 3u) * 8u;
+#pragma unroll
+        for (int c = 0; c < 17; c++) if (c <= w_words) row.v[c] = __ldg(w + c);
+    }
+}
+__device__ __forceinline__ uint32_t warp_sb_sad_finish(const SbSadRow& row, const uint32_t* src_even, int w_words, int rows) {
     const int lane = threadIdx.x & 31;
     uint32_t acc = 0;
     if (lane < rows) {
-        // 17 independent aligned loads in flight, then one funnel shift per word (the path is L2-latency bound)
-        const uint8_t* r = rp.at(x, y + 2 * lane);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>((uintptr_t)r & ~(uintptr_t)3);
-        const uint32_t sh = ((uint32_t)(uintptr_t)r & 3u) * 8u;
-        uint32_t v[17];
-#pragma unroll
-        for (int c = 0; c < 17; c++) v[c] = (c <= w_words) ? __ldg(w + c) : 0u;
 #pragma unroll
         for (int c = 0; c < 16; c++)
-            if (c < w_words) acc = sad4(src_even[lane * kSrcPitch + c], __funnelshift_r(v[c], v[c + 1], sh), acc);
+            if (c < w_words) acc = sad4(src_even[lane * kSrcPitch + c], __funnelshift_r(row.v[c], row.v[c + 1], row.sh), acc);
     }
     return __reduce_add_sync(0xffffffffu, acc);
+}
+__device__ uint32_t warp_sb_sad(const uint32_t* src_even, const DPlane& rp, int x, int y, int w_words, int rows) {
+    SbSadRow row;
+    warp_sb_sad_load(row, rp, x, y, w_words, rows);
+    return warp_sb_sad_finish(row, src_even, w_words, rows);
 }
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
@@ -271,6 +285,23 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
     SbScratch& scr = job.scratch[sb];
     const DPyramid& ref = job.ref[list];
 
+    // ---- hme_mv_center_check, ME.c:5882-6145: the candidates' reference rows are requested first, so that their L2 round
+    // trip overlaps the staging of the source SB below (position A is evaluated at the zero-MV address: quirk Q2)
+    const bool do_center = (p.temporal_layer_index > 0 || list == 0);
+    const int tw = p.hme_l0_total_w, th = p.hme_l0_total_h;
+    int dxv = 0, dyv = 0;
+    SbSadRow cand_row;
+    const bool cand_live = do_center && (warp < 4 || (warp == 4 && list == 1));
+    if (do_center && list == 1) {
+        const uint32_t mv0 = scr.best_mv[0][0];
+        dxv = (int16_t)(0 - (mv_x(mv0) >> 2)); dyv = (int16_t)(0 - (mv_y(mv0) >> 2));
+    }
+    if (cand_live) {
+        int cx = 0, cy = 0;
+        if (warp == 1) cx = tw; else if (warp == 2) cy = -th; else if (warp == 3) cy = th;
+        else if (warp == 4) { cx = dxv; cy = dyv; }
+        warp_sb_sad_load(cand_row, ref.full, ox + clip_center(ox, cx, 63, ref.full.w), oy + clip_center(oy, cy, 63, ref.full.h), sb_w >> 2, sb_h >> 1);
+    }
     // ---- stage the source SB (even rows only: every SAD on this path is row-subsampled)
     for (int t = tid; t < 32 * 16; t += kHmeThreads)
         sh.src_even[(t >> 4) * kSrcPitch + (t & 15)] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
@@ -281,23 +312,9 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
     __syncthreads();
 
     int xsc = 0, ysc = 0;
-    const bool do_center = (p.temporal_layer_index > 0 || list == 0);
     if (do_center) {
-        // ---- hme_mv_center_check, ME.c:5882-6145 (position A is evaluated at the zero-MV address: quirk Q2)
-        const int tw = p.hme_l0_total_w, th = p.hme_l0_total_h;
-        int dxv = 0, dyv = 0;
-        if (list == 1) {
-            const uint32_t mv0 = scr.best_mv[0][0];
-            dxv = (int16_t)(0 - (mv_x(mv0) >> 2)); dyv = (int16_t)(0 - (mv_y(mv0) >> 2));
-        }
         if (warp < 5) {
-            int cx = 0, cy = 0;
-            if (warp == 1) cx = tw; else if (warp == 2) cy = -th; else if (warp == 3) cy = th;
-            else if (warp == 4) { cx = dxv; cy = dyv; }
-            uint32_t s = 0xFFFFFFFFu;
-            if (warp < 4 || list == 1)
-                s = warp_sb_sad(sh.src_even, ref.full, ox + clip_center(ox, cx, 63, ref.full.w),
-                                oy + clip_center(oy, cy, 63, ref.full.h), sb_w >> 2, sb_h >> 1);
+            const uint32_t s = cand_live ? warp_sb_sad_finish(cand_row, sh.src_even, sb_w >> 2, sb_h >> 1) : 0xFFFFFFFFu;
             if ((tid & 31) == 0) sh.cand_sad[warp] = s;
         }
         __syncthreads();

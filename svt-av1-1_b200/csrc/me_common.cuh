@@ -161,7 +161,9 @@ void launch_hme(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream
 // The square-mode and ext-mode kernels are separate launches over the same grid; a CTA whose job is of the other
 // mode exits at once. `ext` selects the 209-PU variant, `wide` the one for search areas beyond 64 x 64.
 void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st);
-void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st);
+// `worklist`: room for n_jobs * max_sb 32-bit entries preceded by one 32-bit counter (worklist[-1]); owned by this launch
+// sequence until it has run (the small-window sub-pel pass defers the SBs whose window does not fit to a second pass)
+void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, uint32_t* worklist, cudaStream_t st);
 void launch_bipred_pack(const DJob* d_jobs, int n_jobs, int max_sb, bool ext, cudaStream_t st);
 cudaError_t configure_kernels();
 

@@ -20,26 +20,33 @@ namespace svtme {
 
 constexpr int kSpThreads = 256;
 // Plane geometry: the window is the bounding box of the 256 (level, block) positions, at most (area - 1) + 56 + 15 rows and
-// the same + 6 bytes (+ one spare word for the last B taps) per row. Narrow = search areas up to 64 x 64 (2 CTAs per SM);
-// Wide = up to 127 x 127 (MIN(search_area, 127), ME.c:6644-6645): 198 rows x 52 words, one CTA per SM.
-template <bool Wide> struct PlaneGeom {
-    static constexpr int kRows = Wide ? 198 : 134;            // 127 (64) - 1 + 56 + 15 + 1
-    static constexpr int kPitchW = Wide ? 52 : 36;            // words
-    static constexpr int kWords = kRows * kPitchW + (Wide ? 196 : 132);   // + room for the row skew below
-    static constexpr int kRawPitch = Wide ? 56 : 44;          // words per raw window row: 16-byte granules (3 + pitch + 1 words at most)
+// the same + 6 bytes (+ one spare word for the last B taps) per row.
+//   kGeomSmall   88 rows x 28 words: boxes of SBs whose best full-pel positions lie within about 17 rows / 30 columns of each
+//                other (coherent motion: all but 0.03-0.3 % of the SBs of the bench sequence) -- 53 KB of shared memory and
+//                64 registers, FOUR CTAs per SM. An SB whose box does not fit is appended to a work list instead and
+//                searched by the kGeomFull instantiation afterwards.
+//   kGeomFull    134 x 36: any box of a search area up to 64 x 64 (two CTAs per SM); persistent CTAs over the work list
+//   kGeomWide    198 x 52: search areas up to 127 x 127 (MIN(search_area, 127), ME.c:6644-6645), one CTA per SM
+enum { kGeomSmall = 0, kGeomFull = 1, kGeomWide = 2 };
+template <int Geom> struct PlaneGeom {
+    static constexpr int kRows = Geom == kGeomWide ? 198 : Geom == kGeomFull ? 134 : 88;
+    static constexpr int kPitchW = Geom == kGeomWide ? 52 : Geom == kGeomFull ? 36 : 28;          // words
+    static constexpr int kWords = kRows * kPitchW + ((kRows - 1) & ~15) + 4;                    // + room for the row skew below
+    static constexpr int kRawPitch = kPitchW + 8;                                               // words per raw window row: 16-byte granules (3 + pitch + 1 words at most)
+    static constexpr int kCtasPerSm = Geom == kGeomWide ? 1 : Geom == kGeomFull ? 2 : 4;
 };
 // Word offset of window row r. Rows 8 apart would land on the same bank (8 * 36 = 9 * 32); the (monotonic) skew
 // moves each group of eight rows by 1 or 15 banks more than the previous one, so that the 8x4 blocks a warp reads
 // together (two words apart along x, eight rows apart along y) touch 32 different banks when they share a motion
 // vector: bank offsets of the four block rows are {0, 1, 16, 17} or {0, 15, 16, 31}.
-template <bool Wide> __device__ __forceinline__ int plane_row(int r) { return r * PlaneGeom<Wide>::kPitchW + ((r >> 3) & 1) + (r & ~15); }
-static_assert(PlaneGeom<false>::kRows * PlaneGeom<false>::kRawPitch <= 2 * PlaneGeom<false>::kWords &&
-              PlaneGeom<true>::kRows * PlaneGeom<true>::kRawPitch <= 2 * PlaneGeom<true>::kWords, "the raw window must fit the storage of planes H and J");
+template <int Geom> __device__ __forceinline__ int plane_row(int r) { return r * PlaneGeom<Geom>::kPitchW + ((r >> 3) & 1) + (r & ~15); }
+static_assert(PlaneGeom<0>::kRows * PlaneGeom<0>::kRawPitch <= 2 * PlaneGeom<0>::kWords && PlaneGeom<1>::kRows * PlaneGeom<1>::kRawPitch <= 2 * PlaneGeom<1>::kWords &&
+              PlaneGeom<2>::kRows * PlaneGeom<2>::kRawPitch <= 2 * PlaneGeom<2>::kWords, "the raw window must fit the storage of planes H and J");
 constexpr int kMargin = 3;              // window starts 3 pixels left/above the search-area origin
 
-template <int NPU, bool Wide>
+template <int NPU, int Geom>
 struct SpSharedT {
-    uint32_t plane[4][PlaneGeom<Wide>::kWords];   // A, B, H, J
+    uint32_t plane[4][PlaneGeom<Geom>::kWords];   // A, B, H, J
     uint32_t src[64 * 16];
     uint32_t sum_ssd[9][NPU];           // per (candidate, PU) distortion sums, accumulated with shared atomics
     uint32_t sum_sad[9][NPU];
@@ -47,7 +54,7 @@ struct SpSharedT {
     int32_t  pu_dir[NPU];
     uint32_t pu_imv[NPU];               // MV at entry of the current stage
     uint32_t pu_win[NPU];               // winning half-pel candidate (1..8) of the PU, 0 = the integer position stays
-    uint32_t rowoff[PlaneGeom<Wide>::kRows + 2];  // plane_row() of every window row: one LDS instead of five integer instructions
+    uint32_t rowoff[PlaneGeom<Geom>::kRows + 2];  // plane_row() of every window row: one LDS instead of five integer instructions
     int32_t  bbox[4];                   // min X, min Y, max -X... see the kernel: bounding box of the blocks' window positions
 };
 
@@ -189,18 +196,15 @@ __device__ __forceinline__ bool pu_leader_any(int wb, int hb, int lane) {
 // Ext = the 209-PU mode: 14 PU classes ("levels") instead of 4; the non-square PUs live in SbScratchExt. Every level
 // is 64 8x8-block tasks, so a warp always works on one level.
 #define PROW(r) ((int)sh.rowoff[r])
-template <bool Ext, bool Wide>
-__global__ void __launch_bounds__(kSpThreads, Wide ? 1 : 2) subpel_kernel(const DJob* __restrict__ jobs, int list) {
+// One SB. Returns false (and has done nothing else) when the SB's window does not fit this instantiation's planes: only the
+// kGeomSmall one can say so, the caller then leaves the SB to the kGeomFull pass.
+template <bool Ext, int Geom>
+__device__ __forceinline__ bool subpel_sb(const DJob& job, const int sb, const int list, uint8_t* smem_raw) {
     constexpr int NPU = Ext ? kMaxPu : kNumPu, NLEV = Ext ? kMaxLevels : kNumLevels;
-    constexpr int kPlRows = PlaneGeom<Wide>::kRows, kRawPitchSp = PlaneGeom<Wide>::kRawPitch;
-    using SpShared = SpSharedT<NPU, Wide>;
-    extern __shared__ __align__(16) uint8_t smem_raw[];
+    constexpr int kPlRows = PlaneGeom<Geom>::kRows, kRawPitchSp = PlaneGeom<Geom>::kRawPitch;
+    using SpShared = SpSharedT<NPU, Geom>;
     SpShared& sh = *reinterpret_cast<SpShared*>(smem_raw);
-    const DJob& job = jobs[blockIdx.y];
-    const int sb = job.sb_begin + blockIdx.x;
-    if (sb >= job.sb_end) return;
     const SvtMeParams& p = job.prm;
-    if (list >= p.num_lists || (p.num_pus == kMaxPu) != Ext || wide_search(p) != Wide) return;
     auto block_pu = [](int L, int bx, int by) { if constexpr (Ext) return pu_of_block_any(L, bx, by); else return pu_of_block(L, bx, by); };
     // 8x8 half/quarter-pel is switched off by cu8x8_mode 1 (disable8x8CuInMeFlag); the non-square classes never are
     auto pu_enabled = [&](int pu) { return pu < 21 || pu >= kNumPu || p.cu8x8_mode != 1; };
@@ -220,7 +224,7 @@ __global__ void __launch_bounds__(kSpThreads, Wide ? 1 : 2) subpel_kernel(const 
         if (tid >= kNumPu && tid < NPU) { sh.pu_sad[tid] = scx.best_sad[list][tid - kNumPu]; sh.pu_mv[tid] = scx.best_mv[list][tid - kNumPu]; sh.pu_imv[tid] = sh.pu_mv[tid]; }
     }
     if (tid < 4) sh.bbox[tid] = 0x7FFFFFFF;
-    if (tid < kPlRows + 2) sh.rowoff[tid] = (uint32_t)plane_row<Wide>(tid);
+    if (tid < kPlRows + 2) sh.rowoff[tid] = (uint32_t)plane_row<Geom>(tid);
     __syncthreads();
     // The refinement only reads the window around the 256 (level, 8x8 block) positions the full-pel search chose
     // (every later MV stays within one integer pixel of them), so the window that is staged and interpolated is their
@@ -240,6 +244,10 @@ __global__ void __launch_bounds__(kSpThreads, Wide ? 1 : 2) subpel_kernel(const 
     sax += dx; say += dy;
     const int ww = ((-sh.bbox[2] - dx + 15) >> 2) + 1;   // window words per row actually used (+1: taps of the last B word)
     const int wr = -sh.bbox[3] - dy + 12;                 // window rows: 8 block rows + one above, three below for the taps
+    if (Geom == kGeomSmall && (ww > PlaneGeom<Geom>::kPitchW || wr > kPlRows)) {     // CTA-uniform: the box is wider than these planes
+        asm volatile("cp.async.wait_group 0;" ::: "memory");                     // (the source SB's copies target this CTA's memory)
+        return false;
+    }
 
     // ---- plane A
     const uint32_t inv_ww = 0xFFFFFFFFu / (uint32_t)ww + 1u;   // t / ww == umulhi(t, inv_ww) for t * ww < 2^32
@@ -530,25 +538,58 @@ __global__ void __launch_bounds__(kSpThreads, Wide ? 1 : 2) subpel_kernel(const 
             }
         }
     }
+    return true;
 }
 
-template <bool Ext, bool Wide> static cudaError_t configure_one() {
-    return cudaFuncSetAttribute(subpel_kernel<Ext, Wide>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SpSharedT<Ext ? kMaxPu : kNumPu, Wide>));
+// Direct grid (one CTA per SB of the batch). The kGeomSmall instantiation appends the SBs it cannot hold to `worklist`
+// (entry = job index << 16 | SB offset inside the job's range; worklist[-1] is the counter, zeroed by the host before).
+template <bool Ext, int Geom>
+__global__ void __launch_bounds__(kSpThreads, PlaneGeom<Geom>::kCtasPerSm) subpel_kernel(const DJob* __restrict__ jobs, int list, uint32_t* __restrict__ worklist) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const DJob& job = jobs[blockIdx.y];
+    const int sb = job.sb_begin + blockIdx.x;
+    if (sb >= job.sb_end) return;
+    const SvtMeParams& p = job.prm;
+    if (list >= p.num_lists || (p.num_pus == kMaxPu) != Ext || wide_search(p) != (Geom == kGeomWide)) return;
+    if (!subpel_sb<Ext, Geom>(job, sb, list, smem_raw) && threadIdx.x == 0)
+        worklist[atomicAdd(worklist - 1, 1u)] = ((uint32_t)blockIdx.y << 16) | (uint32_t)blockIdx.x;
 }
-cudaError_t configure_subpel() {
-    cudaError_t e = configure_one<false, false>();
-    if (e == cudaSuccess) e = configure_one<true, false>();
-    if (e == cudaSuccess) e = configure_one<false, true>();
-    if (e == cudaSuccess) e = configure_one<true, true>();
+
+// Persistent CTAs over the work list the kGeomSmall pass left (normally a few SBs, often none).
+template <bool Ext>
+__global__ void __launch_bounds__(kSpThreads, PlaneGeom<kGeomFull>::kCtasPerSm) subpel_deferred_kernel(const DJob* __restrict__ jobs, int list, const uint32_t* __restrict__ worklist) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const uint32_t n = worklist[-1];
+    for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
+        const uint32_t item = worklist[i];
+        const DJob& job = jobs[item >> 16];
+        subpel_sb<Ext, kGeomFull>(job, job.sb_begin + (int)(item & 0xFFFFu), list, smem_raw);
+        __syncthreads();                                   // the next SB reuses the shared planes
+    }
+}
+
+template <bool Ext, int Geom> static constexpr size_t sp_smem() { return sizeof(SpSharedT<Ext ? kMaxPu : kNumPu, Geom>); }
+template <bool Ext> static cudaError_t configure_ext() {
+    cudaError_t e = cudaFuncSetAttribute(subpel_kernel<Ext, kGeomSmall>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp_smem<Ext, kGeomSmall>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(subpel_kernel<Ext, kGeomWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp_smem<Ext, kGeomWide>());
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(subpel_deferred_kernel<Ext>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp_smem<Ext, kGeomFull>());
     return e;
 }
-
-template <bool Ext, bool Wide> static void launch_one(const DJob* d_jobs, int n_jobs, int max_sb, int list, cudaStream_t st) {
-    subpel_kernel<Ext, Wide><<<dim3(max_sb, n_jobs), kSpThreads, sizeof(SpSharedT<Ext ? kMaxPu : kNumPu, Wide>), st>>>(d_jobs, list);
+cudaError_t configure_subpel() {
+    const cudaError_t e = configure_ext<false>();
+    return e != cudaSuccess ? e : configure_ext<true>();
 }
-void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, cudaStream_t st) {
-    if (ext) { if (wide) launch_one<true, true>(d_jobs, n_jobs, max_sb, list, st); else launch_one<true, false>(d_jobs, n_jobs, max_sb, list, st); }
-    else     { if (wide) launch_one<false, true>(d_jobs, n_jobs, max_sb, list, st); else launch_one<false, false>(d_jobs, n_jobs, max_sb, list, st); }
+
+// `worklist` points just behind a 32-bit counter; both are private to this launch sequence (stream) until it has run.
+template <bool Ext> static void launch_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool wide, uint32_t* worklist, cudaStream_t st) {
+    if (wide) { subpel_kernel<Ext, kGeomWide><<<dim3(max_sb, n_jobs), kSpThreads, sp_smem<Ext, kGeomWide>(), st>>>(d_jobs, list, nullptr); return; }
+    cudaMemsetAsync(worklist - 1, 0, sizeof(uint32_t), st);
+    subpel_kernel<Ext, kGeomSmall><<<dim3(max_sb, n_jobs), kSpThreads, sp_smem<Ext, kGeomSmall>(), st>>>(d_jobs, list, worklist);
+    subpel_deferred_kernel<Ext><<<2 * 148, kSpThreads, sp_smem<Ext, kGeomFull>(), st>>>(d_jobs, list, worklist);
+}
+void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, uint32_t* worklist, cudaStream_t st) {
+    if (ext) launch_ext<true>(d_jobs, n_jobs, max_sb, list, wide, worklist, st);
+    else     launch_ext<false>(d_jobs, n_jobs, max_sb, list, wide, worklist, st);
 }
 
 }  // namespace svtme
