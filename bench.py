@@ -675,8 +675,10 @@ def run_gpu_impl(args, rank, world, local_rank):
         npix = TXQ_PLANES * TXQ_H * TXQ_W
         tq["d_out"] = [torch.empty(npix, dtype=torch.int32, device="cuda") for _ in range(3)]
         tq["d_eob"] = torch.empty(npix // 16, dtype=torch.int16, device="cuda")
-        tq["h_out"] = [torch.empty(npix, dtype=torch.int32).pin_memory() for _ in range(2)]
+        tq["h_lv"] = torch.empty(npix, dtype=torch.int16).pin_memory()
+        tq["h_off"] = torch.empty(npix // 16 + 1, dtype=torch.int32).pin_memory()
         tq["h_eob"] = torch.empty(npix // 16, dtype=torch.int16).pin_memory()
+        tq["levels"] = 0
         tq["st"] = torch.cuda.ExternalStream(tq["ctx"].stream())
         tq["me_st"] = torch.cuda.ExternalStream(ctx.stream)
         tq["launches_per_step"] = (N_PICS - 1) // TXQ_PLANES
@@ -701,16 +703,19 @@ def run_gpu_impl(args, rank, world, local_rank):
         b.record(txq["st"])
         txq["me_st"].wait_event(b)
 
-    def txq_step_e2e():
-        """The same through host buffers: residual planes H2D, quantised + dequantised coefficients and eob D2H (the subset EncDec
-        consumes), synchronous calls on this thread while the ME batches run asynchronously."""
-        for _ in range(txq["launches_per_step"]):
+    def txq_step_e2e(n_calls=None):
+        """The same through host buffers: residual planes H2D; eob, level offsets and the eob leading quantised levels of every
+        block D2H (svttxq_fwd_txfm_quant_compact: what the entropy coder reads, dqcoeff is rebuilt by the caller); synchronous
+        calls on this thread while the ME batches run asynchronously."""
+        for _ in range(txq["launches_per_step"] if n_calls is None else n_calls):
             c = txq["sizes"][txq["n"] % len(txq["sizes"])]
             txq["n"] += 1
-            rc = txq["ctx"].lib.svttxq_fwd_txfm_quant(txq["ctx"]._h, txq["host"].data_ptr(), TXQ_W, TXQ_W, TXQ_PLANES * TXQ_H, c[0], c[1], c[2],
-                                                      C.byref(txq["quant"]), None, txq["h_out"][0].data_ptr(), txq["h_out"][1].data_ptr(),
-                                                      txq["h_eob"].data_ptr(), None)
+            n = C.c_size_t(0)
+            rc = txq["ctx"].lib.svttxq_fwd_txfm_quant_compact(txq["ctx"]._h, txq["host"].data_ptr(), TXQ_W, TXQ_W, TXQ_PLANES * TXQ_H, c[0], c[1], c[2],
+                                                              C.byref(txq["quant"]), txq["h_eob"].data_ptr(), txq["h_off"].data_ptr(),
+                                                              txq["h_lv"].data_ptr(), txq["h_lv"].numel(), C.byref(n))
             assert rc == 0
+            txq["levels"] += n.value
 
     dev_ptrs = [dev[i].data_ptr() for i in range(N_PICS)]
     host_ptrs = [host[i].data_ptr() for i in range(N_PICS)]
@@ -761,10 +766,15 @@ def run_gpu_impl(args, rank, world, local_rank):
                 for g in range(0, N_PICS - 1, EB):
                     pics = list(range(0 if g == 0 else g + 1, min(g + EB, N_PICS - 1) + 1))
                     ctx.upload_ptr_batch([base + i for i in pics], [host_ptrs[i] for i in pics], stride)
+        if txq:
+            # the transform calls are synchronous, so they run on their own host thread (ctypes releases the GIL) like the EncDec
+            # threads of a pipelined encoder, beside this thread's asynchronous ME submissions; joined at the end of the step
+            th = threading.Thread(target=txq_step_e2e)
+            th.start()
         for jb in gop_batches[which]:
             ctx.motion_estimate_async(jb)
         if txq:
-            txq_step_e2e()
+            th.join()
 
     def barrier():
         ctx.synchronize()
@@ -870,8 +880,9 @@ def run_gpu_impl(args, rank, world, local_rank):
         if txq:                                           # per step: 15 launches of 8 planes; e2e moves the residual in and qcoeff/dqcoeff/eob out
             plane_px = TXQ_PLANES * TXQ_H * TXQ_W
             txq_h2d = txq["launches_per_step"] * 2 * plane_px
-            txq_d2h = sum(txq["launches_per_step"] * (8 * (plane_px // (w_ * h_)) * min(w_, 32) * min(h_, 32) + 2 * (plane_px // (w_ * h_)))
-                          for (w_, h_, _) in txq["sizes"]) // len(txq["sizes"])
+            e2e_calls = max(1, (max(1, args.warmup // 2) + args.steps) * txq["launches_per_step"])
+            txq_d2h = txq["launches_per_step"] * (2 * txq["levels"] // e2e_calls) + sum(
+                txq["launches_per_step"] * 6 * (plane_px // (w_ * h_)) for (w_, h_, _) in txq["sizes"]) // len(txq["sizes"])
             txq_launches = txq_resident_launches
         pyr_bytes = W * H + sum(((W >> s) + 2 * p) * ((H >> s) + 2 * p) for s, p in ((0, 68), (1, 32), (2, 16)))
         line = {
@@ -1066,6 +1077,8 @@ def run_txq(args, rank, world, local_rank):
     h_out = [torch.empty(npix, dtype=torch.int32).pin_memory() for _ in range(3)]
     h_eob = torch.empty(npix // 16, dtype=torch.int16).pin_memory()
     h_en = torch.empty(npix // 16, dtype=torch.int64).pin_memory()
+    h_lv = torch.empty(npix, dtype=torch.int16).pin_memory()              # compact return path: levels, offsets (eob reuses h_eob)
+    h_off = torch.empty(npix // 16 + 1, dtype=torch.int32).pin_memory()
     ctx = pkg.TxqContext(local_rank)
     st = torch.cuda.ExternalStream(ctx.stream())
     quant = pkg.SvtTxqQuant.from_q10(q10)
@@ -1081,6 +1094,16 @@ def run_txq(args, rank, world, local_rank):
                                            h_out[0].data_ptr() if everything else None, h_out[1].data_ptr(), h_out[2].data_ptr(),
                                            h_eob.data_ptr(), h_en.data_ptr() if everything else None)
         assert rc == 0
+
+    compact_levels = {}
+
+    def compact_call(c):
+        """the eob-bounded return path: eob + offsets + the eob leading levels of every block in scan order (int16)"""
+        n = C.c_size_t(0)
+        rc = ctx.lib.svttxq_fwd_txfm_quant_compact(ctx._h, host.data_ptr(), TXQ_W, TXQ_W, Hs, c[0], c[1], c[2], C.byref(quant),
+                                                   h_eob.data_ptr(), h_off.data_ptr(), h_lv.data_ptr(), npix, C.byref(n))
+        assert rc == 0
+        compact_levels[c] = n.value
 
     def sync_all():
         ctx.synchronize()
@@ -1144,10 +1167,19 @@ def run_txq(args, rank, world, local_rank):
             host_call(c, everything=False)
     sync_all()
     ms_e2e_sub = (time.perf_counter() - t0) * 1e3
+    for c in cases[:2]:
+        compact_call(c)
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        for c in cases:
+            compact_call(c)
+    sync_all()
+    ms_e2e_compact = (time.perf_counter() - t0) * 1e3
     if dist is not None:
-        t = torch.tensor([ms, ms_e2e, ms_e2e_sub], device="cuda")
+        t = torch.tensor([ms, ms_e2e, ms_e2e_sub, ms_e2e_compact], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e, ms_e2e_sub = float(t[0].item()), float(t[1].item()), float(t[2].item())
+        ms, ms_e2e, ms_e2e_sub, ms_e2e_compact = float(t[0].item()), float(t[1].item()), float(t[2].item()), float(t[3].item())
     checksum = int(h_out[1].sum(dtype=torch.int64).item())
     ctx.close()
     if rank == 0:
@@ -1171,12 +1203,20 @@ def run_txq(args, rank, world, local_rank):
         worst = min(per, key=lambda k: per[k]["frac"])
         v = world * npix * len(cases) * args.steps / (ms / 1e3) / 1e6
         v_e2e = world * npix * len(cases) * e2e_steps / (ms_e2e / 1e3) / 1e6
+        v_compact = world * npix * len(cases) * e2e_steps / (ms_e2e_compact / 1e3) / 1e6
+        compact_bytes = sum(2 * compact_levels[c] + 6 * (npix // (c[0] * c[1])) + 4 for c in cases)
         pw_bytes = sum(12 * (npix // (w * h)) * min(w, 32) * min(h, 32) + 10 * (npix // (w * h)) for (w, h, _) in cases)
         line = {"metric": "txq_mpixels_per_sec", "value": v, "unit": "Mpixel/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
                 "data": "synthetic", "config": txq_config(world),
-                "e2e": {"value": v_e2e, "unit": "Mpixel/s", "h2d_bytes_per_step": 2 * npix * len(cases), "d2h_bytes_per_step": pw_bytes,
-                        "ms_per_step": ms_e2e / e2e_steps, "timing": "host wall clock around synchronous svttxq_fwd_txfm_quant calls"},
+                "e2e": {"value": v_compact, "unit": "Mpixel/s", "h2d_bytes_per_step": 2 * npix * len(cases), "d2h_bytes_per_step": compact_bytes,
+                        "ms_per_step": ms_e2e_compact / e2e_steps, "call": "svttxq_fwd_txfm_quant_compact",
+                        "outputs": "per block: eob (u16), level offset (u32) and the eob leading quantised levels in scan order (i16) -- "
+                                   "what the entropy coder reads; dqcoeff is rebuilt by the caller (EbFullLoop.c:596-662)",
+                        "kept_levels_per_pixel": sum(compact_levels.values()) / (npix * len(cases)),
+                        "timing": "host wall clock around synchronous calls, pinned host buffers"},
+                "e2e_all_outputs": {"value": v_e2e, "unit": "Mpixel/s", "h2d_bytes_per_step": 2 * npix * len(cases), "d2h_bytes_per_step": pw_bytes,
+                                    "ms_per_step": ms_e2e / e2e_steps, "call": "svttxq_fwd_txfm_quant (coeff + qcoeff + dqcoeff as int32, eob, energy)"},
                 "e2e_encdec_outputs": {"value": world * npix * len(cases) * e2e_steps / (ms_e2e_sub / 1e3) / 1e6, "unit": "Mpixel/s",
                                        "outputs": "qcoeff + dqcoeff + eob (coeff and energy not copied back)",
                                        "d2h_bytes_per_step": sum(8 * (npix // (w * h)) * min(w, 32) * min(h, 32) + 2 * (npix // (w * h)) for (w, h, _) in cases)},

@@ -49,6 +49,18 @@ int32_t svttxq_fwd_txfm_quant(SvtTxqContext *ctx, const int16_t *residual, int32
 int32_t svttxq_fwd_txfm_quant_device(SvtTxqContext *ctx, const int16_t *d_residual, int32_t stride, int32_t width, int32_t height,
                                      int32_t txw, int32_t txh, int32_t tx_type, const SvtTxqQuant *quant,
                                      int32_t *d_coeff, int32_t *d_qcoeff, int32_t *d_dqcoeff, uint16_t *d_eob, uint64_t *d_energy);
+/* Eob-bounded return path for host buffers: what the consumer of a quantised block reads is its eob and the `eob` leading
+ * levels in scan order (the entropy coder walks the scan backwards from eob - 1; dqcoeff = (level * dequant[i != 0]) >>
+ * log_scale with the level's sign is rebuilt where reconstruction needs it: av1_quantize_b_facade_II, EbFullLoop.c:596-662,
+ * aom_highbd_quantize_b*_avx2, ASM_AVX2/highbd_quantize_intrin_avx2.c:82-200). So instead of three int32 planes this call
+ * returns eob[n_blocks], level_offset[n_blocks + 1] (exclusive prefix sum of eob; may be NULL: the caller can sum eob itself)
+ * and levels[level_offset[b] + i] = qcoeff of block b at scan position i, i < eob[b], as int16 -- 2 bytes per block + 2 bytes
+ * per kept level over the host link. *n_levels receives the total; SVTME_ERR_INSUFFICIENT_RESOURCES when it exceeds
+ * levels_cap (n_blocks * pw * ph always suffices), SVTME_ERR_BAD_PARAMETER when a level does not fit 16 bits (only
+ * possible above 8-bit video: use svttxq_fwd_txfm_quant then). Synchronous. */
+int32_t svttxq_fwd_txfm_quant_compact(SvtTxqContext *ctx, const int16_t *residual, int32_t stride, int32_t width, int32_t height,
+                                      int32_t txw, int32_t txh, int32_t tx_type, const SvtTxqQuant *quant,
+                                      uint16_t *eob, uint32_t *level_offset, int16_t *levels, size_t levels_cap, size_t *n_levels);
 int32_t svttxq_synchronize(SvtTxqContext *ctx);
 void   *svttxq_stream(SvtTxqContext *ctx);
 int64_t svttxq_kernel_launches(const SvtTxqContext *ctx);

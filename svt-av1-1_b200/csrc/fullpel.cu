@@ -72,12 +72,11 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const DPlane& rp = job.ref[list].full;
     const int area_x = scr.sa_x[list], area_y = scr.sa_y[list], area_w = scr.sa_w[list], area_h = scr.sa_h[list];
     if (Wide && tid < kNumPu) { merged_v[tid] = 0xFFFFFFFFu; merged_o[tid] = 0xFFFFFFFFu; }
-#pragma unroll 1
     for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
     // sub-area of this pass: the whole area, or (Wide) one of up to 2 x 2 pieces of at most 64 x 64 positions
     const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
     if (Wide && (tx0 >= area_w || ty0 >= area_h)) continue;       // CTA-uniform
-    const int sax = area_x + tx0, say = area_y + ty0, saw = min(64, area_w - tx0), sah = min(64, area_h - ty0);
+    const int sax = area_x + tx0, say = area_y + ty0, saw = Wide ? min(64, area_w - tx0) : area_w, sah = Wide ? min(64, area_h - ty0) : area_h;
 
     // ---- stage source (even rows) and the four byte-shifted window copies.
     // The window first lands RAW in shared memory as 16-byte cp.async granules (fire and forget: no thread holds a

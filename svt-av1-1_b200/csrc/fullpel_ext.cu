@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
     const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
     if (Wide && (tx0 >= area_w || ty0 >= area_h)) continue;       // CTA-uniform
-    const int sax = area_x + tx0, say = area_y + ty0, saw = min(64, area_w - tx0), sah = min(64, area_h - ty0);
+    const int sax = area_x + tx0, say = area_y + ty0, saw = Wide ? min(64, area_w - tx0) : area_w, sah = Wide ? min(64, area_h - ty0) : area_h;
 
     // ---- stage source (even rows), the slot tables and the four byte-shifted window copies (as in fullpel.cu: the window
     // lands raw in shared memory as 16-byte cp.async granules, then the warps shift it into the four copies)

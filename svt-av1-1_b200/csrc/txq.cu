@@ -8,12 +8,13 @@
 // 12 B + 2 B out per pixel). One thread owns one column for the vertical pass and one row for the horizontal
 // pass (straight-line generated code, txfm1d_gen.cuh, cospi folded at compile time); the transpose goes through
 // shared memory with an odd pitch (conflict-free both ways). The packed coefficients return to shared memory and
-// are quantised by all threads of the block with coalesced 128-byte stores; eob is a shared-memory atomicMax over
-// (iscan + 1) of the non-zero dequantised coefficients. Several blocks share a CTA so that every CTA has 256
-// threads even for 4x4.
+// are quantised by all threads of the block with coalesced 128-byte stores; eob comes from a warp ballot (blocks of up to 32
+// coefficients, visited in scan order) or a per-lane running maximum of (iscan + 1) over the non-zero dequantised
+// coefficients reduced once per block (REDUX). Several blocks share a CTA so that every CTA has 256 threads even for 4x4.
 #include "me_common.cuh"
 #include "txfm1d_gen.cuh"
 #include "txq.cuh"
+#include <mutex>
 
 namespace svtme {
 
@@ -240,11 +241,19 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH, ENERGY>::MIN_CTAS) txq_
 template <int TXW, int TXH, bool ENERGY> static cudaError_t launch_variant(const TxqArgs& a, cudaStream_t st) {
     constexpr int B = TxqGeom<TXW, TXH, ENERGY>::B;
     const int smem = TxqGeom<TXW, TXH, ENERGY>::SMEM;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(txq_kernel<TXW, TXH, ENERGY>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return e;
-        configured = true;
+    // the attribute is per device and launches may come from any thread: one bit per device ordinal under a mutex
+    static std::mutex mu;
+    static uint64_t configured = 0;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (dev < 0 || dev > 63 || !((configured >> dev) & 1u)) {
+            e = cudaFuncSetAttribute(txq_kernel<TXW, TXH, ENERGY>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            if (e != cudaSuccess) return e;
+            if (dev >= 0 && dev <= 63) configured |= (uint64_t)1 << dev;
+        }
     }
     txq_kernel<TXW, TXH, ENERGY><<<(a.n_blocks + B - 1) / B, 256, smem, st>>>(a);
     return cudaGetLastError();

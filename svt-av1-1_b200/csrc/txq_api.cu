@@ -30,7 +30,16 @@ struct SvtTxqContext {
     // staging for the host-buffer entry point
     void* d_in = nullptr; size_t in_cap = 0;
     void* d_out = nullptr; size_t out_cap = 0;
+    // compact return path (svttxq_fwd_txfm_quant_compact): result copies on their own stream, chunk totals in pinned memory
+    cudaStream_t copy_out = nullptr;
+    cudaEvent_t out_ready[8] = {};            // chunk i: eob / offsets / running total have reached the host
+    uint32_t* h_flags = nullptr;              // pinned [8][2]: running total of levels after chunk i, int16 overflow flag
 };
+
+namespace svtme {
+void launch_txq_compact(const int32_t* d_qcoeff, const uint16_t* d_eob, int n_blocks, int n_coef, const int16_t* d_scan,
+                        uint32_t* d_tile_sums, uint32_t* d_offsets, int16_t* d_levels, uint32_t* d_flags, const uint32_t* d_carry, cudaStream_t st);
+}
 
 #define TQ(call)                                                                                   \
     do {                                                                                           \
@@ -113,9 +122,17 @@ int32_t svttxq_create(SvtTxqContext** out, int32_t device) {
     ctx->device = device;
     *out = ctx;
     TQ(cudaSetDevice(device));
-    TQ(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    {   // the transform kernels are tiny next to the ME kernels they usually share the GPU with: highest stream priority, so
+        // their CTAs are placed as soon as any search CTA retires instead of behind a whole 10 ms grid
+        int least = 0, greatest = 0;
+        TQ(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+        TQ(cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, greatest));
+    }
     TQ(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
     for (auto& e : ctx->in_done) TQ(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    TQ(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+    for (auto& e : ctx->out_ready) TQ(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    TQ(cudaMallocHost(&ctx->h_flags, 8 * 2 * sizeof(uint32_t)));
     return SVTME_OK;
 }
 
@@ -127,7 +144,10 @@ void svttxq_destroy(SvtTxqContext* ctx) {
     cudaFree(ctx->d_in); cudaFree(ctx->d_out);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+    if (ctx->copy_out) { cudaStreamSynchronize(ctx->copy_out); cudaStreamDestroy(ctx->copy_out); }
     for (auto& e : ctx->in_done) if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->out_ready) if (e) cudaEventDestroy(e);
+    if (ctx->h_flags) cudaFreeHost(ctx->h_flags);
     delete ctx;
 }
 
@@ -221,6 +241,104 @@ int32_t svttxq_fwd_txfm_quant(SvtTxqContext* ctx, const int16_t* residual, int32
         if (energy) TQ(cudaMemcpyAsync(energy + b0, d_energy + b0, nb * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     }
     TQ(cudaStreamSynchronize(ctx->stream));
+    return SVTME_OK;
+}
+
+/* The eob-bounded return path: per block its eob and the eob leading quantised levels in scan order as int16 (what the
+ * entropy coder reads; dqcoeff = (level * dequant) >> log_scale is rebuilt by the caller where it needs it,
+ * EbFullLoop.c:596-662). Block rows go through in chunks: upload (copy_in), transform + quantisation + prefix sum +
+ * gather (stream), then -- once the chunk's running total has reached the host -- the copy of exactly that many levels
+ * (copy_out), so both directions of the link stay busy and 2 B per block + 2 B per kept level cross it. */
+int32_t svttxq_fwd_txfm_quant_compact(SvtTxqContext* ctx, const int16_t* residual, int32_t stride, int32_t width, int32_t height,
+                                      int32_t txw, int32_t txh, int32_t tx_type, const SvtTxqQuant* quant,
+                                      uint16_t* eob, uint32_t* level_offset, int16_t* levels, size_t levels_cap, size_t* n_levels) {
+    if (!ctx) return SVTME_ERR_BAD_PARAMETER;
+    if (!residual || !quant || !eob || !levels || !n_levels || width <= 0 || height <= 0 || stride < width ||
+        !svttxq_supported(txw, txh, tx_type) || width % txw || height % txh) {
+        ctx->err = "svttxq_fwd_txfm_quant_compact: bad parameter"; return SVTME_ERR_BAD_PARAMETER;
+    }
+    *n_levels = 0;
+    TQ(cudaSetDevice(ctx->device));
+    const int block_rows = height / txh, blocks_x = width / txw;
+    const size_t n_blocks = (size_t)blocks_x * block_rows;
+    const size_t per = (size_t)(txw < 32 ? txw : 32) * (txh < 32 ? txh : 32);
+    if (n_blocks * per >= ((size_t)1 << 32)) { ctx->err = "svttxq_fwd_txfm_quant_compact: more than 2^32 coefficients"; return SVTME_ERR_BAD_PARAMETER; }
+    const size_t in_bytes = align_up((size_t)stride * height * sizeof(int16_t), 256);
+    const size_t q_bytes = align_up(n_blocks * per * sizeof(int32_t), 256), lv_bytes = align_up(n_blocks * per * sizeof(int16_t), 256);
+    const size_t eob_bytes = align_up(n_blocks * sizeof(uint16_t), 256), off_bytes = align_up((n_blocks + 9) * sizeof(uint32_t), 256);
+    const size_t tile_bytes = align_up((n_blocks / 2048 + 32) * sizeof(uint32_t), 256), flag_bytes = 256;
+    const size_t out_bytes = q_bytes + lv_bytes + eob_bytes + off_bytes + tile_bytes + flag_bytes;
+    if (in_bytes > ctx->in_cap) {
+        TQ(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_in); ctx->d_in = nullptr; ctx->in_cap = 0;
+        TQ(cudaMalloc(&ctx->d_in, in_bytes)); ctx->in_cap = in_bytes;
+    }
+    if (out_bytes > ctx->out_cap) {
+        TQ(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_out); ctx->d_out = nullptr; ctx->out_cap = 0;
+        TQ(cudaMalloc(&ctx->d_out, out_bytes)); ctx->out_cap = out_bytes;
+    }
+    uint8_t* o = (uint8_t*)ctx->d_out;
+    int32_t* d_q = (int32_t*)o; o += q_bytes;
+    int16_t* d_lv = (int16_t*)o; o += lv_bytes;
+    uint16_t* d_eob = (uint16_t*)o; o += eob_bytes;
+    uint32_t* d_off = (uint32_t*)o; o += off_bytes;
+    uint32_t* d_tiles = (uint32_t*)o; o += tile_bytes;
+    uint32_t* d_flags = (uint32_t*)o;                                     // [8][2] like h_flags
+    const int16_t* d_scan = nullptr;
+    {
+        const int32_t rc = get_iscan(ctx, txw, txh, tx_type, &d_scan);
+        if (rc != SVTME_OK) return rc;
+        d_scan += per;                                                    // the scan itself follows its inverse
+    }
+    int n_chunks = (int)(((size_t)width * height) >> 21);                 // ~2 Mpixel per chunk
+    n_chunks = n_chunks < 1 ? 1 : n_chunks > 8 ? 8 : n_chunks;
+    if (n_chunks > block_rows) n_chunks = block_rows;
+    TQ(cudaMemsetAsync(d_flags, 0, 8 * 2 * sizeof(uint32_t), ctx->stream));
+    for (int c = 0; c < n_chunks; c++) {
+        const int r0 = (int)((int64_t)block_rows * c / n_chunks), r1 = (int)((int64_t)block_rows * (c + 1) / n_chunks);
+        const size_t first = (size_t)r0 * txh * stride;
+        const size_t elems = (size_t)((r1 - r0) * txh - 1) * stride + width;
+        TQ(cudaMemcpyAsync((int16_t*)ctx->d_in + first, residual + first, elems * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->copy_in));
+        TQ(cudaEventRecord(ctx->in_done[c], ctx->copy_in));
+    }
+    size_t tile0 = 0;
+    for (int c = 0; c < n_chunks; c++) {
+        const int r0 = (int)((int64_t)block_rows * c / n_chunks), r1 = (int)((int64_t)block_rows * (c + 1) / n_chunks);
+        const size_t b0 = (size_t)r0 * blocks_x, nb = (size_t)(r1 - r0) * blocks_x;
+        TQ(cudaStreamWaitEvent(ctx->stream, ctx->in_done[c], 0));
+        const int32_t rc = svttxq_fwd_txfm_quant_device(ctx, (const int16_t*)ctx->d_in + (size_t)r0 * txh * stride, stride, width, (r1 - r0) * txh,
+                                                        txw, txh, tx_type, quant, nullptr, d_q + b0 * per, nullptr, d_eob + b0, nullptr);
+        if (rc != SVTME_OK) return rc;
+        // offsets continue across chunks: the running total of the chunk before is this chunk's carry (stream order)
+        launch_txq_compact(d_q + b0 * per, d_eob + b0, (int)nb, (int)per, d_scan, d_tiles + tile0, d_off + b0 + c, d_lv, d_flags + 2 * c,
+                           c ? d_flags + 2 * (c - 1) : nullptr, ctx->stream);
+        ctx->launches += 4;
+        TQ(cudaGetLastError());
+        tile0 += nb / 2048 + 2;
+        TQ(cudaMemcpyAsync(eob + b0, d_eob + b0, nb * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (level_offset) TQ(cudaMemcpyAsync(level_offset + b0, d_off + b0 + c, (nb + (c == n_chunks - 1 ? 1 : 0)) * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        TQ(cudaMemcpyAsync(ctx->h_flags + 2 * c, d_flags + 2 * c, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        TQ(cudaEventRecord(ctx->out_ready[c], ctx->stream));
+    }
+    size_t done = 0;
+    bool wide = false;
+    for (int c = 0; c < n_chunks; c++) {
+        TQ(cudaEventSynchronize(ctx->out_ready[c]));
+        const size_t total = ctx->h_flags[2 * c];
+        wide |= ctx->h_flags[2 * c + 1] != 0;
+        if (total > levels_cap) {
+            TQ(cudaStreamSynchronize(ctx->stream)); TQ(cudaStreamSynchronize(ctx->copy_out));
+            ctx->err = "svttxq_fwd_txfm_quant_compact: levels buffer too small (" + std::to_string(total) + " levels so far)";
+            return SVTME_ERR_INSUFFICIENT_RESOURCES;
+        }
+        if (total > done) TQ(cudaMemcpyAsync(levels + done, d_lv + done, (total - done) * sizeof(int16_t), cudaMemcpyDeviceToHost, ctx->copy_out));
+        done = total;
+    }
+    TQ(cudaStreamSynchronize(ctx->copy_out));
+    TQ(cudaStreamSynchronize(ctx->stream));
+    *n_levels = done;
+    if (wide) { ctx->err = "svttxq_fwd_txfm_quant_compact: a level does not fit 16 bits (use svttxq_fwd_txfm_quant)"; return SVTME_ERR_BAD_PARAMETER; }
     return SVTME_OK;
 }
 

@@ -7,6 +7,7 @@ from .binding import SvtMeError, load_library
 TXQ_EXPORTED_SYMBOLS = (
     "svttxq_create", "svttxq_destroy", "svttxq_last_error", "svttxq_supported", "svttxq_fwd_txfm_quant",
     "svttxq_fwd_txfm_quant_device", "svttxq_synchronize", "svttxq_stream", "svttxq_kernel_launches",
+    "svttxq_fwd_txfm_quant_compact",
 )
 # TxType order of the reference (EbDefinitions.h)
 TX_TYPES = ("DCT_DCT", "ADST_DCT", "DCT_ADST", "ADST_ADST", "FLIPADST_DCT", "DCT_FLIPADST", "FLIPADST_FLIPADST",
@@ -44,6 +45,9 @@ def _lib():
             f = getattr(lib, name)
             f.restype = C.c_int32
             f.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int32] * 6 + [C.POINTER(SvtTxqQuant)] + [C.c_void_p] * 5
+        lib.svttxq_fwd_txfm_quant_compact.restype = C.c_int32
+        lib.svttxq_fwd_txfm_quant_compact.argtypes = ([C.c_void_p, C.c_void_p] + [C.c_int32] * 6 + [C.POINTER(SvtTxqQuant)] +
+                                                      [C.c_void_p] * 3 + [C.c_size_t, C.POINTER(C.c_size_t)])
         lib.svttxq_synchronize.restype = C.c_int32
         lib.svttxq_synchronize.argtypes = [C.c_void_p]
         lib.svttxq_stream.restype = C.c_void_p
@@ -114,6 +118,23 @@ class TxqContext:
                                             ptr(out["eob"]), ptr(out["energy"]))
         self._check(rc, "svttxq_fwd_txfm_quant")
         return {k: v for k, v in out.items() if v is not None}
+
+    def fwd_txfm_quant_compact(self, residual, txw, txh, tx_type, quant, levels=None, eob=None, level_offset=None):
+        """Eob-bounded return path: (eob [n_blocks] uint16, level_offset [n_blocks + 1] uint32, levels [total] int16): block b's
+        quantised levels in scan order are levels[level_offset[b] : level_offset[b] + eob[b]]."""
+        assert residual.dtype == np.int16 and residual.ndim == 2 and residual.strides[1] == 2
+        height, width = residual.shape
+        n_blocks = (width // txw) * (height // txh)
+        pw, ph = packed_dims(txw, txh)
+        eob = np.empty(n_blocks, np.uint16) if eob is None else eob
+        level_offset = np.empty(n_blocks + 1, np.uint32) if level_offset is None else level_offset
+        levels = np.empty(n_blocks * pw * ph, np.int16) if levels is None else levels
+        q = quant if isinstance(quant, SvtTxqQuant) else SvtTxqQuant.from_q10(quant)
+        n = C.c_size_t(0)
+        rc = self.lib.svttxq_fwd_txfm_quant_compact(self._h, residual.ctypes.data, residual.strides[0] // 2, width, height, txw, txh, tx_type,
+                                                    C.byref(q), eob.ctypes.data, level_offset.ctypes.data, levels.ctypes.data, levels.size, C.byref(n))
+        self._check(rc, "svttxq_fwd_txfm_quant_compact")
+        return eob, level_offset, levels[:n.value]
 
     def fwd_txfm_quant_device(self, d_residual, stride, width, height, txw, txh, tx_type, quant,
                               d_coeff=None, d_qcoeff=None, d_dqcoeff=None, d_eob=None, d_energy=None):

@@ -62,6 +62,49 @@ def test_every_type_against_oracle(txq, q10s, size):
                     f"{w}x{h} type {t} bd {bd} q {qi}")
 
 
+def _rebuild(eob, off, levels, scan, n_coef, dequant, ls):
+    """What a consumer of the compact form does: levels back to raster qcoeff, dqcoeff = (|q| * dequant) >> log_scale with q's sign."""
+    nb = len(eob)
+    q = np.zeros((nb, n_coef), np.int32)
+    for b in range(nb):
+        q[b, scan[:eob[b]]] = levels[off[b]:off[b] + eob[b]]
+    dq_mag = (np.abs(q).astype(np.int64) * np.where(np.arange(n_coef) == 0, dequant[0], dequant[1])) >> ls
+    return q, (np.sign(q) * dq_mag).astype(np.int32)
+
+
+@pytest.mark.parametrize("size", T.TX_SIZES, ids=lambda s: f"{s[0]}x{s[1]}")
+def test_compact_return_path(txq, q10s, size):
+    """svttxq_fwd_txfm_quant_compact: eob + the eob leading levels in scan order (int16) + their offsets reproduce the
+    oracle's qcoeff, dqcoeff and eob for every size; several chunks (the plane exceeds 2 Mpixel for the larger cases)."""
+    w, h = size
+    meo = T.oracle()
+    rng = np.random.default_rng(w * 7 + h)
+    keys = [k for k in sorted(q10s) if k[0] == 8]
+    for t in (0, 9, 3, 10, 11):
+        if not T.type_supported(w, h, t):
+            continue
+        q10 = q10s[keys[(t + w + h) % len(keys)]]
+        rows, cols = (9 * h, 11 * w) if t else (max(9 * h, 1088), 2048)          # DCT_DCT case: > 2 Mpixel -> 2 chunks
+        res = T.synth_residual(rng, rows // h * h, cols // w * w, 8, "noise" if t % 2 else "mixed")
+        want = T.txq_plane(meo, res, w, h, t, q10)
+        eob, off, levels = txq.fwd_txfm_quant_compact(res, w, h, t, q10)
+        assert np.array_equal(eob, want["eob"]), (w, h, t)
+        assert off[0] == 0 and np.array_equal(np.diff(off.astype(np.int64)), eob.astype(np.int64)) and off[-1] == len(levels)
+        q, dq = _rebuild(eob, off, levels, T.scan(meo, "meo", w, h, t), want["qcoeff"].shape[1], (q10[8], q10[9]), T.log_scale(w, h))
+        assert np.array_equal(q, want["qcoeff"]) and np.array_equal(dq, want["dqcoeff"]), (w, h, t)
+
+
+def test_compact_return_path_limits(txq, q10s, pkg):
+    q10 = q10s[sorted(q10s)[0]]
+    res = T.synth_residual(np.random.default_rng(1), 64, 64, 8, "noise")
+    eob = np.empty(64, np.uint16)
+    with pytest.raises(pkg.SvtMeError, match="0x80001000"):                  # levels buffer too small
+        txq.fwd_txfm_quant_compact(res, 8, 8, 0, q10, levels=np.empty(3, np.int16), eob=eob)
+    z = np.zeros((64, 64), np.int16)                                          # all-zero residual: eob 0 everywhere, no levels
+    e, off, lv = txq.fwd_txfm_quant_compact(z, 16, 16, 0, q10)
+    assert not e.any() and not off.any() and len(lv) == 0
+
+
 def test_strided_plane_and_optional_outputs(txq, q10s):
     meo = T.oracle()
     rng = np.random.default_rng(77)
