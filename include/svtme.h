@@ -88,6 +88,10 @@ typedef struct SvtMeSbDebug {
     uint32_t best_mv[2][SVTME_SQUARE_PU_COUNT];
 } SvtMeSbDebug;
 
+/* rc_me_distortion[sb] as MotionEstimateLcu leaves it when rate control is on (EbMotionEstimation.c:7150-7157): the sum
+ * of the best distortions of the SB's sixteen 16x16 PUs (pu_index 5..20). sb_rows = the SB's result rows. */
+uint32_t svtme_rc_me_distortion(const SvtMePuResult *sb_rows);
+
 /* One picture to motion-estimate: slots name pictures previously uploaded into the context. */
 typedef struct SvtMeJob {
     int32_t        cur_slot, ref0_slot, ref1_slot;   /* ref1_slot ignored when params.num_lists == 1 */

@@ -28,6 +28,9 @@ void ref_txq_dump_close(void);
 typedef int (*ref_me_hook_fn)(void *user, const int32_t *hdr, const uint8_t *cur, int cur_stride, const uint8_t *ref0, int ref0_stride,
                               const uint8_t *ref1, int ref1_stride, void *row_out);
 void ref_me_hook_set(ref_me_hook_fn fn, void *user);
+void ref_me_timing_enable(int on);
+void ref_me_timing_get(long long *ns, long long *calls);
+#include <time.h>
 
 /* ---- the reference-side binding: MotionEstimateLcu -> svtme_lcu_motion_estimate ------------------------------------ */
 static struct {
@@ -151,6 +154,9 @@ int main(int argc, char **argv) {
     FILE *bs = bitstream_path ? fopen(bitstream_path, "wb") : NULL;
     if (bitstream_path && !bs) { perror(bitstream_path); return 2; }
     if (eb_init_encoder(enc) != EB_ErrorNone) { fprintf(stderr, "eb_init_encoder failed\n"); return 1; }
+    ref_me_timing_enable(1);
+    struct timespec t_begin, t_end;
+    clock_gettime(CLOCK_MONOTONIC, &t_begin);
 
     const size_t ysz = (size_t)w * h, csz = ysz / 4;
     uint8_t *frame = (uint8_t *)malloc(ysz + 2 * csz);
@@ -181,6 +187,13 @@ int main(int argc, char **argv) {
             eb_svt_release_out_buffer(&out);
             if (eos) { done = 1; break; }
         }
+    }
+    clock_gettime(CLOCK_MONOTONIC, &t_end);
+    {   /* one machine-readable line for profiles/encoder_timing.py: encode wall clock, time inside MotionEstimateLcu over all threads */
+        long long ns = 0, calls = 0;
+        ref_me_timing_get(&ns, &calls);
+        fprintf(stderr, "enc_dump: timing wall_s %.3f me_thread_s %.3f me_calls %lld frames %d\n",
+                (double)(t_end.tv_sec - t_begin.tv_sec) + 1e-9 * (double)(t_end.tv_nsec - t_begin.tv_nsec), 1e-9 * (double)ns, calls, n);
     }
     ref_me_dump_close();
     ref_txq_dump_close();

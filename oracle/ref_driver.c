@@ -277,8 +277,28 @@ void ref_me_hook_set(ref_me_hook_fn fn, void *user) { g_hook = fn; g_hook_user =
 
 static const uint8_t *luma_origin(const EbPictureBufferDesc_t *p) { return p->bufferY + (size_t)p->origin_y * p->strideY + p->origin_x; }
 
+/* ME-stage time: nanoseconds spent inside MotionEstimateLcu summed over the encoder's ME threads, and the number of calls
+ * (profiles/encoder_timing.py: stock vs hooked encoder) */
+#include <time.h>
+static long long g_me_ns, g_me_calls;
+static int g_me_timing;
+void ref_me_timing_enable(int on) { g_me_timing = on; __atomic_store_n(&g_me_ns, 0, __ATOMIC_RELAXED); __atomic_store_n(&g_me_calls, 0, __ATOMIC_RELAXED); }
+void ref_me_timing_get(long long *ns, long long *calls) { *ns = __atomic_load_n(&g_me_ns, __ATOMIC_RELAXED); *calls = __atomic_load_n(&g_me_calls, __ATOMIC_RELAXED); }
+static EbErrorType motion_estimate_lcu_impl(PictureParentControlSet_t *pcs, uint32_t sb_index, uint32_t sb_origin_x, uint32_t sb_origin_y,
+                                            MeContext_t *ctx, EbPictureBufferDesc_t *input_ptr);
 EbErrorType MotionEstimateLcu(PictureParentControlSet_t *pcs, uint32_t sb_index, uint32_t sb_origin_x, uint32_t sb_origin_y,
                               MeContext_t *ctx, EbPictureBufferDesc_t *input_ptr) {
+    if (!g_me_timing) return motion_estimate_lcu_impl(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
+    struct timespec a, b;
+    clock_gettime(CLOCK_MONOTONIC, &a);
+    const EbErrorType rc = motion_estimate_lcu_impl(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
+    clock_gettime(CLOCK_MONOTONIC, &b);
+    __atomic_fetch_add(&g_me_ns, (b.tv_sec - a.tv_sec) * 1000000000LL + (b.tv_nsec - a.tv_nsec), __ATOMIC_RELAXED);
+    __atomic_fetch_add(&g_me_calls, 1, __ATOMIC_RELAXED);
+    return rc;
+}
+static EbErrorType motion_estimate_lcu_impl(PictureParentControlSet_t *pcs, uint32_t sb_index, uint32_t sb_origin_x, uint32_t sb_origin_y,
+                                            MeContext_t *ctx, EbPictureBufferDesc_t *input_ptr) {
     if (!g_hook && !g_dump) return MotionEstimateLcu_reference(pcs, sb_index, sb_origin_x, sb_origin_y, ctx, input_ptr);
     SequenceControlSet_t *scs = (SequenceControlSet_t *)pcs->sequence_control_set_wrapper_ptr->objectPtr;
     int32_t h[48]; memset(h, 0, sizeof(h));

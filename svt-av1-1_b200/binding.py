@@ -14,7 +14,7 @@ EXPORTED_SYMBOLS = (
     "svtme_motion_estimate_async", "svtme_fetch_results", "svtme_synchronize", "svtme_stream",
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
     "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
-    "svtme_pictures_upload_device", "svtme_pictures_upload", "svtme_motion_estimate_static",
+    "svtme_pictures_upload_device", "svtme_pictures_upload", "svtme_motion_estimate_static", "svtme_rc_me_distortion",
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
                         "svtme_lcu_motion_estimate", "svtme_lcu_session_stats")
@@ -110,6 +110,8 @@ def load_library():
         f.argtypes = [C.c_void_p, C.POINTER(SvtMeJob), C.c_int32]
     lib.svtme_motion_estimate_static.restype = C.c_int32
     lib.svtme_motion_estimate_static.argtypes = [C.c_void_p, C.POINTER(SvtMeJob)]
+    lib.svtme_rc_me_distortion.restype = C.c_uint32
+    lib.svtme_rc_me_distortion.argtypes = [C.c_void_p]
     lib.svtme_synchronize.restype = C.c_int32
     lib.svtme_synchronize.argtypes = [C.c_void_p]
     lib.svtme_synchronize_uploads.restype = C.c_int32

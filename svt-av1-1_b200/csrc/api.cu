@@ -249,6 +249,12 @@ void svtme_destroy(SvtMeContext* ctx) {
     delete ctx;
 }
 
+uint32_t svtme_rc_me_distortion(const SvtMePuResult* sb_rows) {      /* EbMotionEstimation.c:7150-7157 */
+    uint32_t sum = 0;
+    for (int i = 0; i < 16; i++) sum += sb_rows[5 + i].cand[0].distortion;
+    return sum;
+}
+
 const char* svtme_last_error(const SvtMeContext* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 void* svtme_stream(SvtMeContext* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 int64_t svtme_kernel_launches(const SvtMeContext* ctx) { return ctx ? ctx->launches : 0; }

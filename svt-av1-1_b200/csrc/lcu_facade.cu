@@ -1,8 +1,10 @@
 // lcu_facade.cu -- host side of include/svtme_lcu.h: the per-SB call shape of the reference's MotionEstimateLcu
 // (EbMotionEstimation.c:6152) on top of the picture-level CUDA path. No kernels here; everything it launches goes
 // through svtme_picture_upload / svtme_motion_estimate (api.cu).
+#include <condition_variable>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -22,6 +24,10 @@ struct PictureRows {
     SvtMeParams params;
     int32_t fetched = 0;
     uint64_t born = 0;
+    // The first SB call of a picture (its "leader") submits the picture and waits for the rows OUTSIDE the session lock;
+    // the other callers of that picture sleep on `cv` meanwhile and other pictures can be submitted behind it.
+    enum { kSubmitted, kReady, kFailed } state = kSubmitted;
+    int32_t rc = SVTME_OK;
 };
 
 }  // namespace
@@ -31,7 +37,8 @@ struct SvtMeLcuSession {
     int32_t width = 0, height = 0, n_sb = 0;
     std::mutex mu;
     std::vector<Resident> slots;
-    std::map<uint64_t, PictureRows> pictures;       // keyed by picture_number of the current picture
+    std::map<uint64_t, std::shared_ptr<PictureRows>> pictures;   // keyed by picture_number of the current picture
+    std::condition_variable cv;                     // a picture changed state
     uint64_t tick = 0;
     int64_t n_pictures = 0, n_uploads = 0, n_rows = 0;
     std::string err;
@@ -85,7 +92,7 @@ static int32_t run_picture(SvtMeLcuSession *s, const SvtMeParams *params, const 
     job.cur_slot = used[0]; job.ref0_slot = used[1]; job.ref1_slot = used[2];
     job.params = *params;
     job.results = out->rows.data();
-    rc = svtme_motion_estimate(s->ctx, &job, 1);     // returns with the rows in host memory
+    rc = svtme_motion_estimate_async(s->ctx, &job, 1);   // enqueued; the rows arrive on the context's result stream
     if (rc != SVTME_OK) s->err = svtme_last_error(s->ctx);
     return rc;
 }
@@ -121,34 +128,49 @@ const char *svtme_lcu_last_error(const SvtMeLcuSession *s) { return s ? s->err.c
 int32_t svtme_lcu_motion_estimate(SvtMeLcuSession *s, const SvtMeParams *params, const SvtMeLcuPicture *cur, const SvtMeLcuPicture *ref0,
                                   const SvtMeLcuPicture *ref1, int32_t sb_index, SvtMePuResult *row_out) {
     if (!s || !params || !cur || !ref0 || !row_out) return SVTME_ERR_BAD_PARAMETER;
-    std::lock_guard<std::mutex> lock(s->mu);
+    std::unique_lock<std::mutex> lock(s->mu);
     if (sb_index < 0 || sb_index >= s->n_sb || params->width != s->width || params->height != s->height ||
         (params->num_lists == 2 && !ref1)) {
         s->err = "bad SB index / geometry / missing list-1 reference";
         return SVTME_ERR_BAD_PARAMETER;
     }
+    std::shared_ptr<PictureRows> pr;
     auto it = s->pictures.find(cur->picture_number);
     if (it == s->pictures.end()) {
         if ((int)s->pictures.size() >= kMaxPendingPictures) {
-            auto oldest = s->pictures.begin();
+            auto oldest = s->pictures.end();
             for (auto p = s->pictures.begin(); p != s->pictures.end(); ++p)
-                if (p->second.born < oldest->second.born) oldest = p;
-            s->pictures.erase(oldest);
+                if (p->second->state != PictureRows::kSubmitted && (oldest == s->pictures.end() || p->second->born < oldest->second->born)) oldest = p;
+            if (oldest != s->pictures.end()) s->pictures.erase(oldest);
         }
-        PictureRows fresh;
-        fresh.born = ++s->tick;
-        const int32_t rc = run_picture(s, params, cur, ref0, ref1, &fresh);
+        // leader of this picture: uploads + launch sequence are enqueued under the lock (the context is not thread-safe) ...
+        pr = std::make_shared<PictureRows>();
+        pr->born = ++s->tick;
+        const int32_t rc = run_picture(s, params, cur, ref0, ref1, pr.get());
         if (rc != SVTME_OK) return rc;
         s->n_pictures++;
-        it = s->pictures.emplace(cur->picture_number, std::move(fresh)).first;
-    } else if (std::memcmp(&it->second.params, params, sizeof(SvtMeParams)) != 0) {
-        s->err = "search parameters changed between the SBs of one picture";
-        return SVTME_ERR_BAD_PARAMETER;
+        s->pictures.emplace(cur->picture_number, pr);
+        // ... and the wait for the rows is not: other ME threads submit THEIR pictures behind this one meanwhile (the GPU runs
+        // them back to back), and threads asking for other SBs of this picture sleep on the condition variable
+        lock.unlock();
+        const int32_t wrc = svtme_fetch_results(s->ctx, nullptr, 0);
+        lock.lock();
+        pr->rc = wrc;
+        pr->state = wrc == SVTME_OK ? PictureRows::kReady : PictureRows::kFailed;
+        if (wrc != SVTME_OK) s->err = svtme_last_error(s->ctx);
+        s->cv.notify_all();
+    } else {
+        pr = it->second;
+        if (std::memcmp(&pr->params, params, sizeof(SvtMeParams)) != 0) {
+            s->err = "search parameters changed between the SBs of one picture";
+            return SVTME_ERR_BAD_PARAMETER;
+        }
+        s->cv.wait(lock, [&] { return pr->state != PictureRows::kSubmitted; });
     }
-    PictureRows &pr = it->second;
-    std::memcpy(row_out, pr.rows.data() + (size_t)sb_index * params->num_pus, sizeof(SvtMePuResult) * params->num_pus);
+    if (pr->state == PictureRows::kFailed) return pr->rc;
+    std::memcpy(row_out, pr->rows.data() + (size_t)sb_index * params->num_pus, sizeof(SvtMePuResult) * params->num_pus);
     s->n_rows++;
-    if (++pr.fetched == s->n_sb) s->pictures.erase(it);
+    if (++pr->fetched == s->n_sb) s->pictures.erase(cur->picture_number);
     return SVTME_OK;
 }
 
