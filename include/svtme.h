@@ -109,7 +109,12 @@ typedef struct SvtMeJob {
     SvtMeSbDebug  *debug;                            /* HOST memory, [SBs of the row range]; may be NULL */
 } SvtMeJob;
 
-/* Default search parameters for a resolution: the M0 column every legal preset uses. */
+/* Default search parameters for a resolution: the search sizes of column M0 of the reference's tables (every legal preset
+ * of this version uses them, EbMotionEstimationProcess.c:102) with the HME level enables of ENC-MODE 3 (the only entry
+ * that differs between presets is HME level 2 at 4K: on for enc-modes 0-1, off for 2-3, EbResourceCoordinationProcess.c:
+ * 366-380) and 85 PUs. A hook that serves an encoder must copy the picture's own flags (enable_hme_*, num_pus, cu8x8_mode)
+ * over these, as oracle/enc_driver.c does. hierarchical_levels is clamped to 0..5 and temporal_layer_index to
+ * 0..hierarchical_levels. */
 void    svtme_default_params(SvtMeParams *p, int32_t width, int32_t height, int32_t num_lists,
                              int32_t temporal_layer_index, int32_t hierarchical_levels,
                              int32_t is_used_as_reference);
@@ -129,11 +134,13 @@ int32_t svtme_picture_upload(SvtMeContext *ctx, int32_t slot, const uint8_t *lum
  * pyramid build; when 'bit_inc' is not NULL it receives the remainder plane (HOST memory, width bytes per row,
  * height rows; in place by svtme_synchronize / svtme_join). */
 int32_t svtme_picture_upload_16bit(SvtMeContext *ctx, int32_t slot, const uint16_t *luma16, int32_t stride, uint8_t *bit_inc);
-/* Replicate a picture that another context of THIS process (normally on another GPU) already holds: the peer slot's
- * luma crosses NVLink with a peer-to-peer copy (cudaMemcpy2DAsync between devices, peer access enabled on first use)
- * and the pyramid is rebuilt locally. Ordered on-device after the peer's upload; the peer's next rewrite of that
- * slot waits for this copy. This is how reference pictures are replicated when pictures / SB rows of one stream are
- * sharded over the GPUs of a box (no collective, north_star). */
+/* Replicate a picture that another context of THIS process (normally on another GPU) already holds: with peer access
+ * (enabled on first use) the local pyramid kernel reads the peer slot's picture straight over NVLink while it builds the
+ * three padded planes -- no staging copy; without peer access the luma is staged by cudaMemcpy3DPeerAsync first. Ordered
+ * on-device after the peer's upload; the peer's next rewrite of that slot waits for this read. This is how reference
+ * pictures are replicated when pictures / SB rows of one stream are sharded over the GPUs of a box (no collective,
+ * north_star). Threading: neither context may be used by another thread during the call (the peer's slot table is read
+ * without a lock); svtme_destroy of either context must not overlap calls on the other. */
 int32_t svtme_picture_upload_peer(SvtMeContext *ctx, int32_t slot, SvtMeContext *peer, int32_t peer_slot);
 /* Same across PROCESSES (one process per GPU): the owner exports a slot once, ships the 152-byte token to the other
  * ranks by any host channel, and they import pictures from it. Ordering is the caller's: the owner must have ISSUED

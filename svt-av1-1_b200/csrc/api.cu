@@ -135,6 +135,8 @@ void svtme_default_params(SvtMeParams* p, int32_t width, int32_t height, int32_t
     static const int8_t en_l2[5] = { 1, 1, 1, 1, 0 };
     static const int16_t mult[6][6] = { { 100 }, { 100, 100 }, { 100, 100, 100 }, { 200, 140, 100, 70 },
                                         { 350, 200, 100, 100, 100 }, { 525, 350, 200, 100, 100, 100 } };
+    hierarchical_levels = std::max(0, std::min(hierarchical_levels, 5));
+    temporal_layer_index = std::max(0, std::min(temporal_layer_index, hierarchical_levels));
     const uint32_t size = (uint32_t)width * (uint32_t)height;
     const int ir = size < 0xB71B0 ? 0 : size < 0x1AB3F0 ? 1 : size < 0x29F630 ? 2 : 3;
     const uint32_t ratio = (uint32_t)width / (uint32_t)height;
@@ -456,6 +458,11 @@ int32_t svtme_synchronize_uploads(SvtMeContext* ctx) {
 int32_t svtme_picture_upload_ipc(SvtMeContext* ctx, int32_t slot, const SvtMeIpcSlot* src) {
     if (!ctx || !src || slot < 0 || slot >= (int)ctx->slots.size() || src->width != ctx->width || src->height != ctx->height)
         return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_ipc: bad argument");
+    {   // the token must describe a slot of a context with this geometry: same pitch and luma offset as our own slots
+        const Slot& own = ctx->slots[slot];
+        if (src->pitch != own.pyr.full.stride || src->luma_offset != (int64_t)(slot_picture(own) - own.base))
+            return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_picture_upload_ipc: token pitch / offset do not match this geometry");
+    }
     CU(cudaSetDevice(ctx->device));
     const std::string key(reinterpret_cast<const char*>(src->mem_handle), 64);
     auto it = ctx->ipc_open.find(key);
