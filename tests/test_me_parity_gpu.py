@@ -446,6 +446,16 @@ def test_4k_sb_rows_against_oracle_and_properties(pkg, meo):
     assert M.results_diff(bottom[0], want[32 * 60:]) == []
     sq = [0] + list(range(5, 85))
     assert not self_res[0]["dist0"][:, sq].any()
+    # the WHOLE picture through the 10-bit path (16-bit samples split on the device, ME on the 8-bit plane), and the same
+    # picture as three uneven raster ranges of SBs (SvtMeJob.range_in_sbs: the shard of bench.py's strong_4k)
+    ctx = pkg.MeContext(w, h, 3)
+    for i, f in enumerate(fr):
+        ctx.upload16(i, (f.astype(np.uint16) << 2) | rng.integers(0, 4, size=f.shape, dtype=np.uint16))
+    whole, _ = ctx.motion_estimate([(1, 0, 2, p)])
+    parts = [ctx.motion_estimate([(1, 0, 2, p)], sb_range=r)[0][0] for r in ((0, 255), (255, 1277), (1277, 2040))]
+    ctx.close()
+    assert M.results_diff(whole[0], want) == []
+    assert np.concatenate(parts).tobytes() == whole[0].tobytes()
 
 
 @pytest.mark.parametrize("name", M.encoder_cases())
