@@ -51,6 +51,17 @@ int32_t svtme_lcu_motion_estimate(SvtMeLcuSession *session, const SvtMeParams *p
                                   const SvtMeLcuPicture *ref0, const SvtMeLcuPicture *ref1, int32_t sb_index,
                                   SvtMePuResult *row_out);
 
+/* The same for one ME SEGMENT, the unit the reference's ME threads work in (MotionEstimationKernel takes one segment of
+ * me_segments_column_count x me_segments_row_count per input message, EbMotionEstimationProcess.c:432-439, and runs the SB
+ * loop :478-556 over it): SB columns [sb_x0, sb_x1) x SB rows [sb_y0, sb_y1). rows_out[i] = where the row of the i-th SB
+ * of the rectangle (raster order) goes, normally PictureParentControlSet_t::me_results[sb_index]; rc_me_distortion (may be
+ * NULL) receives rc_me_distortion[sb_index] for the same SBs (EbMotionEstimation.c:7150-7157). The first segment of a
+ * picture to arrive submits the whole picture to the GPU, every segment then copies its rows: this is the picture-level
+ * drop-in of integration/svt_cuda_me.patch. */
+int32_t svtme_lcu_motion_estimate_segment(SvtMeLcuSession *session, const SvtMeParams *params, const SvtMeLcuPicture *cur,
+                                          const SvtMeLcuPicture *ref0, const SvtMeLcuPicture *ref1, int32_t sb_x0, int32_t sb_x1,
+                                          int32_t sb_y0, int32_t sb_y1, SvtMePuResult *const *rows_out, uint32_t *rc_me_distortion);
+
 /* Counters for tests and logs: pictures motion-estimated, picture uploads, SB rows served. */
 void    svtme_lcu_session_stats(const SvtMeLcuSession *session, int64_t *pictures, int64_t *uploads, int64_t *rows);
 

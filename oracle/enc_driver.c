@@ -12,6 +12,7 @@
  *                   its SB facade (include/svtme_lcu.h) instead of the reference's C function. This hook is the whole
  *                   reference-side binding; the bitstream must not change.
  */
+#define _GNU_SOURCE
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -154,6 +155,11 @@ int main(int argc, char **argv) {
     FILE *bs = bitstream_path ? fopen(bitstream_path, "wb") : NULL;
     if (bitstream_path && !bs) { perror(bitstream_path); return 2; }
     if (eb_init_encoder(enc) != EB_ErrorNone) { fprintf(stderr, "eb_init_encoder failed\n"); return 1; }
+    {   /* the patched library (integration/svt_cuda_me.patch) creates its CUDA session on first use: do it ahead of the timed encode,
+           like cuda_me_open above does for the hook */
+        int (*prepare)(uint32_t, uint32_t) = (int (*)(uint32_t, uint32_t))dlsym(RTLD_DEFAULT, "svt_cuda_me_open");
+        if (prepare) prepare((uint32_t)w, (uint32_t)h);
+    }
     ref_me_timing_enable(1);
     struct timespec t_begin, t_end;
     clock_gettime(CLOCK_MONOTONIC, &t_begin);

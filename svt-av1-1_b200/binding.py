@@ -17,7 +17,7 @@ EXPORTED_SYMBOLS = (
     "svtme_pictures_upload_device", "svtme_pictures_upload", "svtme_motion_estimate_static", "svtme_rc_me_distortion",
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
-                        "svtme_lcu_motion_estimate", "svtme_lcu_session_stats")
+                        "svtme_lcu_motion_estimate", "svtme_lcu_session_stats", "svtme_lcu_motion_estimate_segment")
 KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
 
 

@@ -174,6 +174,69 @@ int32_t svtme_lcu_motion_estimate(SvtMeLcuSession *s, const SvtMeParams *params,
     return SVTME_OK;
 }
 
+/* The same for a rectangle of SBs -- one ME segment of MotionEstimationKernel (EbMotionEstimationProcess.c:432-439, 478-556):
+ * SB columns [sb_x0, sb_x1) x SB rows [sb_y0, sb_y1) of the picture. rows_out[i] receives the row of the i-th SB of the rectangle
+ * in raster order (the caller passes PictureParentControlSet_t::me_results[sb_index] pointers); rc_me_distortion, when not
+ * NULL, receives the matching sums of the sixteen 16x16 distortions (EbMotionEstimation.c:7150-7157). One lock and one wait
+ * per segment instead of one per SB. */
+int32_t svtme_lcu_motion_estimate_segment(SvtMeLcuSession *s, const SvtMeParams *params, const SvtMeLcuPicture *cur, const SvtMeLcuPicture *ref0,
+                                          const SvtMeLcuPicture *ref1, int32_t sb_x0, int32_t sb_x1, int32_t sb_y0, int32_t sb_y1,
+                                          SvtMePuResult *const *rows_out, uint32_t *rc_me_distortion) {
+    if (!s || !params || !cur || !ref0 || !rows_out) return SVTME_ERR_BAD_PARAMETER;
+    const int32_t sb_cols = (s->width + 63) / 64, sb_rows = (s->height + 63) / 64;
+    std::unique_lock<std::mutex> lock(s->mu);
+    if (sb_x0 < 0 || sb_x1 > sb_cols || sb_x0 >= sb_x1 || sb_y0 < 0 || sb_y1 > sb_rows || sb_y0 >= sb_y1 || params->width != s->width ||
+        params->height != s->height || (params->num_lists == 2 && !ref1)) {
+        s->err = "bad SB rectangle / geometry / missing list-1 reference";
+        return SVTME_ERR_BAD_PARAMETER;
+    }
+    std::shared_ptr<PictureRows> pr;
+    auto it = s->pictures.find(cur->picture_number);
+    if (it == s->pictures.end()) {
+        if ((int)s->pictures.size() >= kMaxPendingPictures) {
+            auto oldest = s->pictures.end();
+            for (auto p = s->pictures.begin(); p != s->pictures.end(); ++p)
+                if (p->second->state != PictureRows::kSubmitted && (oldest == s->pictures.end() || p->second->born < oldest->second->born)) oldest = p;
+            if (oldest != s->pictures.end()) s->pictures.erase(oldest);
+        }
+        pr = std::make_shared<PictureRows>();
+        pr->born = ++s->tick;
+        const int32_t rc = run_picture(s, params, cur, ref0, ref1, pr.get());
+        if (rc != SVTME_OK) return rc;
+        s->n_pictures++;
+        s->pictures.emplace(cur->picture_number, pr);
+        lock.unlock();                                   // the wait is outside the lock: see svtme_lcu_motion_estimate
+        const int32_t wrc = svtme_fetch_results(s->ctx, nullptr, 0);
+        lock.lock();
+        pr->rc = wrc;
+        pr->state = wrc == SVTME_OK ? PictureRows::kReady : PictureRows::kFailed;
+        if (wrc != SVTME_OK) s->err = svtme_last_error(s->ctx);
+        s->cv.notify_all();
+    } else {
+        pr = it->second;
+        if (std::memcmp(&pr->params, params, sizeof(SvtMeParams)) != 0) {
+            s->err = "search parameters changed between the segments of one picture";
+            return SVTME_ERR_BAD_PARAMETER;
+        }
+        s->cv.wait(lock, [&] { return pr->state != PictureRows::kSubmitted; });
+    }
+    if (pr->state == PictureRows::kFailed) return pr->rc;
+    const int32_t n = (sb_x1 - sb_x0) * (sb_y1 - sb_y0);
+    lock.unlock();                                       // the rows are immutable once ready; the copies need no lock
+    int32_t i = 0;
+    for (int32_t y = sb_y0; y < sb_y1; y++)
+        for (int32_t x = sb_x0; x < sb_x1; x++, i++) {
+            const SvtMePuResult *row = pr->rows.data() + (size_t)(y * sb_cols + x) * params->num_pus;
+            std::memcpy(rows_out[i], row, sizeof(SvtMePuResult) * params->num_pus);
+            if (rc_me_distortion) rc_me_distortion[i] = svtme_rc_me_distortion(row);
+        }
+    lock.lock();
+    s->n_rows += n;
+    pr->fetched += n;
+    if (pr->fetched == s->n_sb) s->pictures.erase(cur->picture_number);
+    return SVTME_OK;
+}
+
 void svtme_lcu_session_stats(const SvtMeLcuSession *s, int64_t *pictures, int64_t *uploads, int64_t *rows) {
     if (!s) return;
     if (pictures) *pictures = s->n_pictures;

@@ -17,6 +17,7 @@ pytestmark = pytest.mark.gpu
 
 sys.path.insert(0, os.path.join(M.ROOT, "tests", "golden"))
 ENC = os.path.join(M.ORACLE_DIR, "_ref", "enc_dump")
+ENC_PATCHED = os.path.join(M.ORACLE_DIR, "_ref", "enc_dump_patched")      # the encoder with integration/svt_cuda_me.patch applied
 
 
 def _env():
@@ -31,9 +32,11 @@ def _env():
     return env
 
 
-def _encode(td, tag, yuv, w, h, n, extra, mode=3):
+def _encode(td, tag, yuv, w, h, n, extra, mode=3, exe=ENC, env_extra=None):
     dump, obu = os.path.join(td, tag + ".medump"), os.path.join(td, tag + ".obu")
-    r = subprocess.run([ENC, yuv, str(w), str(h), str(n), str(mode), dump, "--bitstream", obu] + extra, env=_env(),
+    env = _env()
+    env.update(env_extra or {})
+    r = subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump, "--bitstream", obu] + extra, env=env,
                        stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     return dump, open(obu, "rb").read(), r.stderr
@@ -97,3 +100,27 @@ def test_reference_encoder_with_cuda_txq_and_me_is_bit_identical(pkg, tmp_path):
     assert len(bs0) > 1000 and bs0 == bs1, (len(bs0), len(bs1))
     _, bs2, log2 = _encode(str(tmp_path), "both", yuv, w, h, n, ["--cuda-txq", pkg.library_path(), "--cuda-me", pkg.library_path()])
     assert "cuda-me pictures %d " % (n - 1) in log2 and bs2 == bs0
+
+
+@pytest.mark.skipif(not os.path.exists(ENC_PATCHED), reason="oracle/_ref/enc_dump_patched not built (needs /root/reference at build time)")
+@pytest.mark.parametrize("w,h,n,seed,mode", [(416, 240, 20, 7, 3), (720, 480, 10, 5, 3), (256, 192, 12, 13, 2), (192, 128, 10, 17, 0)])
+def test_patched_encoder_picture_level_drop_in_is_bit_identical(pkg, tmp_path, w, h, n, seed, mode):
+    """The picture-level drop-in AS CODE: integration/svt_cuda_me.patch applied to the reference's MotionEstimationKernel (a scratch
+    copy compiled into oracle/_ref/libsvtref_cuda.so). With SVT_CUDA_ME_LIB set, each ME segment calls
+    svtme_lcu_motion_estimate_segment instead of running the SB loop; the bitstream must equal the stock encoder's. 720x480 has
+    16-pixel-wide edge SBs (the any-width HME search)."""
+    frames = M.synth_video(w, h, n, seed=seed, max_shift=8)
+    yuv = str(tmp_path / "in.yuv")
+    with open(yuv, "wb") as f:
+        for x in frames:
+            f.write(np.ascontiguousarray(x).tobytes())
+            f.write(np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes())
+    _, bs0, _ = _encode(str(tmp_path), "stock", yuv, w, h, n, [], mode)
+    _, bs1, log = _encode(str(tmp_path), "patched", yuv, w, h, n, [], mode, exe=ENC_PATCHED,
+                          env_extra={"SVT_CUDA_ME_LIB": pkg.library_path(), "SVT_CUDA_ME_STATS": "1"})
+    m = re.search(r"svt_cuda_me: pictures (\d+) uploads (\d+) rows (\d+)", log)
+    assert m, log[-800:]
+    n_sb = ((w + 63) // 64) * ((h + 63) // 64)
+    assert int(m.group(1)) == n - 1 and int(m.group(3)) == (n - 1) * n_sb and n <= int(m.group(2)) <= n + 8
+    assert "me_calls 0 " in log                                     # MotionEstimateLcu itself never ran
+    assert len(bs0) > 1000 and bs0 == bs1, (len(bs0), len(bs1))
