@@ -332,17 +332,16 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
             const int nw = p.num_hme_regions_w, nh = p.num_hme_regions_h;
             // quirk Q7 (ME.c:6323-6345): the reference initialises the per-region centres for list 0 only;
             // list 1 inherits whatever list 0 left there (visible when an HME level is disabled).
-            if (tid < 12) {
-                const int l = tid >> 2, w = (tid >> 1) & 1, h = tid & 1;
-                sh.x[l][w][h] = list == 0 ? xsc : scr.hme_x[l][w][h];
-                sh.y[l][w][h] = list == 0 ? ysc : scr.hme_y[l][w][h];
-                sh.sad[l][w][h] = 0;
-            }
-            __syncthreads();
             const int g = tid >> 6, gtid = tid & 63;             // region group
             if (g < nw * nh) {
                 const int w = g % nw, h = g / nw, bar = 1 + g;
                 uint32_t* win = sh.win[g];
+                if (gtid < 3) {                                   // the group initialises its own region (a group barrier, not a CTA one)
+                    sh.x[gtid][w][h] = list == 0 ? xsc : scr.hme_x[gtid][w][h];
+                    sh.y[gtid][w][h] = list == 0 ? ysc : scr.hme_y[gtid][w][h];
+                    sh.sad[gtid][w][h] = 0;
+                }
+                group_bar(bar);
                 const bool half = sb_w == 32;                     // right-edge SB of a width % 64 == 32 picture
                 const bool odd = sb_w != 64 && sb_w != 32;        // 8 / 16 / 24 / 48-wide edge SB: the any-width search
                 if (p.enable_hme_level0) {                        // HmeLevel0, ME.c:4306-4503 (sixteenth picture)
@@ -399,12 +398,15 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
                 }
             }
             __syncthreads();
+            // What is left is one warp's work: the other seven retire here instead of sitting in four more CTA barriers
+            if (warp != 0) return;
             if (list == 0 && p.num_lists == 2 && tid < 12) {
                 const int l = tid >> 2, w = (tid >> 1) & 1, h = tid & 1;
-                scr.hme_x[l][w][h] = sh.x[l][w][h]; scr.hme_y[l][w][h] = sh.y[l][w][h];
+                if (w < nw && h < nh) { scr.hme_x[l][w][h] = sh.x[l][w][h]; scr.hme_y[l][w][h] = sh.y[l][w][h]; }
+                else { scr.hme_x[l][w][h] = xsc; scr.hme_y[l][w][h] = ysc; }   // regions no group owns keep the list-0 initialisation (Q7)
             }
+            int xh = 0, yh = 0;
             if (tid == 0) {
-                int xh = 0, yh = 0;
                 const int lvl = p.enable_hme_level2 ? 2 : p.enable_hme_level1 ? 1 : p.enable_hme_level0 ? 0 : -1;
                 if (lvl >= 0) {
                     xh = sh.x[lvl][0][0]; yh = sh.y[lvl][0][0];
@@ -424,25 +426,20 @@ __global__ void __launch_bounds__(kHmeThreads, 4) hme_kernel(const DJob* __restr
                         xh = sh.x[2][0][1]; yh = sh.y[2][0][1];
                     }
                 }
-                sh.center[0] = xh; sh.center[1] = yh;
             }
-            __syncthreads();
-            xsc = sh.center[0]; ysc = sh.center[1];
+            xsc = __shfl_sync(0xffffffffu, xh, 0); ysc = __shfl_sync(0xffffffffu, yh, 0);
         }
     }
+    if (warp != 0) return;                                        // (paths without HME: every thread holds the same xsc / ysc)
 
-    // ---- CheckZeroZeroCenter, ME.c:5466-5552
+    // ---- CheckZeroZeroCenter, ME.c:5466-5552: warp 0 alone. The zero-MV SAD is the centre check's first candidate (a non-zero
+    // centre only ever comes out of that check)
     int saw = min(p.search_area_w, 127), sah = min(p.search_area_h, 127);
     if ((xsc != 0 || ysc != 0) && p.is_used_as_reference) {
         xsc = clip_center(ox, xsc, 63, ref.full.w);
         ysc = clip_center(oy, ysc, 63, ref.full.h);
-        __syncthreads();
-        if (warp < 2) {
-            const uint32_t s = warp_sb_sad(sh.src_even, ref.full, ox + (warp ? xsc : 0), oy + (warp ? ysc : 0), sb_w >> 2, sb_h >> 1);
-            if ((tid & 31) == 0) sh.cand_sad[warp] = s;
-        }
-        __syncthreads();
-        if (sh.cand_sad[0] <= sh.cand_sad[1]) { xsc = 0; ysc = 0; }
+        const uint32_t at_center = warp_sb_sad(sh.src_even, ref.full, ox + xsc, oy + ysc, sb_w >> 2, sb_h >> 1);
+        if (sh.cand_sad[0] <= at_center) { xsc = 0; ysc = 0; }
     }
     if (tid == 0) {
         int sax = xsc - (saw >> 1), say = ysc - (sah >> 1);
