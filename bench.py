@@ -902,7 +902,7 @@ def run_gpu_impl(args, rank, world, local_rank):
                          "peak_source": f"148 SM x 64 lanes/clk x 4 bytes x {sm_mhz} MHz (VABSDIFF4 issue rate, profiles/microbench)",
                          "launch_ms": fp_ms / fp_n if fp_n else None, "share_of_kernel_time": fp_ms / total_kernel_ms if total_kernel_ms else None},
             # one launch builds the pyramids of the whole sequence: bytes of all N_PICS pictures over the launches' time
-            "roofline_hbm": {"kernel": "pyramid_batch_kernel", "bound": "hbm", "pictures_per_launch": N_PICS * args.steps / py_n if py_n else None,
+            "roofline_hbm": {"kernel": "pyramid_flat_kernel", "bound": "hbm", "pictures_per_launch": N_PICS * args.steps / py_n if py_n else None,
                              "achieved": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9) if py_n else None,
                              "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9 / hbm_peak) if py_n else None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
