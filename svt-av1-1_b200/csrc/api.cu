@@ -26,6 +26,12 @@ cudaError_t configure_subpel();
 
 constexpr int kRing = 3;
 
+// Contexts alive in this process: svtme_picture_upload_peer leaves events of the COPYING context in the slots of the
+// OWNING one, so a context that is destroyed has to take its events back out of every live peer first.
+#include <set>
+static std::mutex g_live_mu;
+static std::set<SvtMeContext*> g_live;
+
 struct Batch {
     int cap = 0;                          // pictures this entry can hold
     SbScratch* d_scratch = nullptr;       // [cap][n_sb]
@@ -169,6 +175,7 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
         delete ctx; return SVTME_ERR_UNDEFINED;             // no GPU: fail loudly, there is no CPU path
     }
+    { std::lock_guard<std::mutex> lock(g_live_mu); g_live.insert(ctx); }
     ctx->device = device; ctx->width = width; ctx->height = height;
     ctx->sb_cols = (width + 63) / 64; ctx->sb_rows = (height + 63) / 64; ctx->n_sb = ctx->sb_cols * ctx->sb_rows;
     *out = ctx;                                              // handed out even on failure so the error text is readable
@@ -230,6 +237,22 @@ void svtme_destroy(SvtMeContext* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     for (cudaStream_t st : { ctx->copy_in, ctx->stream, ctx->copy_out }) if (st) cudaStreamSynchronize(st);
+    {   // our peer copies have completed (copy_in is idle): take our events out of the slots of every live peer before they die,
+        // and wait for the peers that are still reading OUR slots before the memory goes
+        std::lock_guard<std::mutex> live(g_live_mu);
+        g_live.erase(ctx);
+        for (SvtMeContext* other : g_live) {
+            std::lock_guard<std::mutex> lock(other->peer_mu);
+            for (auto& s : other->slots)
+                for (cudaEvent_t e : ctx->peer_events)
+                    s.peer_reads.erase(std::remove(s.peer_reads.begin(), s.peer_reads.end(), e), s.peer_reads.end());
+        }
+        std::lock_guard<std::mutex> lock(ctx->peer_mu);
+        for (auto& s : ctx->slots) {
+            for (cudaEvent_t e : s.peer_reads) cudaEventSynchronize(e);
+            s.peer_reads.clear();
+        }
+    }
     for (auto& t : ctx->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); if (s.ready_ipc) cudaEventDestroy(s.ready_ipc); }
