@@ -863,7 +863,7 @@ def run_gpu_impl(args, rank, world, local_rank):
             sp[3].num_lists * (fullpel_byte_sads_per_sb_list() * n_sb_pic + hme_byte_sads_per_sb_list(sp[3]) * full_rows_sb) for sp in specs)
         traffic = None                                    # DRAM bytes per launch, scaled from the committed ncu capture
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01", "traffic.json")))
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r02", "traffic.json")))
             traffic = tj["fullpel_ext_kernel" if NUM_PUS == 209 else "fullpel_kernel"]["dram_bytes_per_sb_list"] * n_sb * len(jobs)
         except Exception:
             pass
@@ -898,7 +898,7 @@ def run_gpu_impl(args, rank, world, local_rank):
             "gpu_launches": int(launches) + txq_launches,
             "roofline": {"kernel": "fullpel_ext_kernel" if NUM_PUS == 209 else "fullpel_kernel", "bound": "int", "achieved": achieved, "peak": peak, "unit": "Tbyte-SAD/s",
                          "frac": (achieved / peak) if achieved else None, "traffic": traffic,
-                         "traffic_source": "dram__bytes_read+write per SB-list from profiles/r01/traffic.json (ncu --set full) x SB-lists per launch; bytes",
+                         "traffic_source": "dram__bytes_read+write per SB-list from profiles/r02/traffic.json (ncu --set full) x SB-lists per launch; bytes",
                          "peak_source": f"148 SM x 64 lanes/clk x 4 bytes x {sm_mhz} MHz (VABSDIFF4 issue rate, profiles/microbench)",
                          "launch_ms": fp_ms / fp_n if fp_n else None, "share_of_kernel_time": fp_ms / total_kernel_ms if total_kernel_ms else None},
             # one launch builds the pyramids of the whole sequence: bytes of all N_PICS pictures over the launches' time
@@ -1201,6 +1201,20 @@ def run_txq(args, rank, world, local_rank):
             tot_bytes += nbytes
             tot_ms += t
         worst = min(per, key=lambda k: per[k]["frac"])
+        # DRAM bytes per launch: the byte model of every case scaled by the measured / model ratio of its size class in the
+        # committed ncu capture (profiles/r02/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one launch)
+        traffic = None
+        try:
+            tc = json.load(open(os.path.join(ROOT, "profiles", "r02", "traffic.json")))["txq_kernel"]["cases"]
+            small = np.mean([v["ratio"] for k, v in tc.items() if "64" not in k])
+            big = np.mean([v["ratio"] for k, v in tc.items() if "64" in k])
+            tb = 0.0
+            for (w, h, _) in cases:
+                nb = npix // (w * h)
+                tb += (2 * npix + 12 * nb * min(w, 32) * min(h, 32) + 10 * nb) * (big if 64 in (w, h) else small)
+            traffic = tb / len(cases)
+        except Exception:
+            pass
         v = world * npix * len(cases) * args.steps / (ms / 1e3) / 1e6
         v_e2e = world * npix * len(cases) * e2e_steps / (ms_e2e / 1e3) / 1e6
         v_compact = world * npix * len(cases) * e2e_steps / (ms_e2e_compact / 1e3) / 1e6
@@ -1222,7 +1236,11 @@ def run_txq(args, rank, world, local_rank):
                                        "d2h_bytes_per_step": sum(8 * (npix // (w * h)) * min(w, 32) * min(h, 32) + 2 * (npix // (w * h)) for (w, h, _) in cases)},
                 "gpu_launches": int(launches),
                 "roofline": {"kernel": "txq_kernel<*>", "bound": "hbm", "achieved": tot_bytes / tot_ms / 1e6, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": tot_bytes / tot_ms / 1e6 / hbm_peak, "traffic": None,
+                             "frac": tot_bytes / tot_ms / 1e6 / hbm_peak, "traffic": traffic,
+                             "traffic_source": "average DRAM bytes per launch over the sweep: byte model x measured/model ratio per size class from "
+                                               "profiles/r02/traffic.json (ncu --set full: 0.75 up to 32 points, 0.47-0.59 for 64-point sizes; below the "
+                                               "model because part of a launch's 200 MB of output is still dirty in the 126 MB L2 when the kernel ends)",
+                             "algorithmic_bytes_per_launch": tot_bytes / len(cases),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                              "bytes_model": "2 B/pixel residual in + 12 B per kept coefficient (coeff, qcoeff, dqcoeff) + 10 B per block (eob, energy)",
                              "worst_case": worst, "worst_frac": per[worst]["frac"]},
