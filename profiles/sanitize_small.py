@@ -1,8 +1,7 @@
 """compute-sanitizer target: a small mixed batch (85- and 209-PU pictures, B and P, HME on/off) through the C-ABI, checked
 against the oracle, plus one transform/quantisation call. Run as
     compute-sanitizer --tool {memcheck,racecheck,synccheck,initcheck} python profiles/sanitize_small.py
-(compute-sanitizer is closed on this round's GPU pool -- it answers "closed on this pool" -- so the script has only been run
-plain there: "me ok / txq ok". It stays as the small target for a box where the tool is available.)"""
+(In round 1 compute-sanitizer answered "closed on this pool"; see profiles/r02/sanitizer.md for round 2.)"""
 import importlib
 import os
 import sys
@@ -28,7 +27,9 @@ def prm(nl, tl, **over):
 
 
 specs = [(1, 0, 2, prm(2, 1)), (2, 0, 3, prm(2, 2, num_pus=209)), (3, 0, 0, prm(1, 0)), (1, 0, 2, prm(2, 3, num_pus=209, enable_hme_flag=0)),
-         (2, 1, 3, prm(2, 1, search_area_w=21, search_area_h=9, use_subpel=0))]
+         (2, 1, 3, prm(2, 1, search_area_w=21, search_area_h=9, use_subpel=0)),
+         (1, 0, 2, prm(2, 1, search_area_w=127, search_area_h=90)),                   # Wide instantiations (sub-areas, 198-row sub-pel planes)
+         (2, 1, 3, prm(2, 2, search_area_w=71, search_area_h=127, num_pus=209))]
 ctx = pkg.MeContext(w, h, 4)
 for i, f in enumerate(fr):
     ctx.upload(i, f)
@@ -38,6 +39,21 @@ pyr = [M.build_pyramid(meo, "meo", f) for f in fr]
 for j, (c, r0, r1, p) in enumerate(specs):
     want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p), pyr[c], pyr[r0], pyr[r1] if p.num_lists == 2 else None)
     assert M.results_diff(res[j], want, p.num_lists) == [], j
+# edge SBs 16 and 24 pixels wide (any-width HME search), the allocation-free entry point, SB-granular ranges
+for w2 in (208, 88):
+    fr2 = M.synth_video(w2, 128, 3, seed=w2, max_shift=16)
+    c2 = pkg.MeContext(w2, 128, 3)
+    for i, f in enumerate(fr2):
+        c2.upload(i, f)
+    p2 = pkg.default_params(w2, 128, 2, 1, 3, 1)
+    a, _ = c2.motion_estimate([(1, 0, 2, p2)])
+    b, _ = c2.motion_estimate_static((1, 0, 2, p2))
+    n2 = a[0].shape[0]
+    parts = [c2.motion_estimate([(1, 0, 2, p2)], sb_range=r)[0][0] for r in ((0, 1), (1, n2))]
+    c2.close()
+    py2 = [M.build_pyramid(meo, "meo", f) for f in fr2]
+    want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, p2), py2[1], py2[0], py2[2])
+    assert M.results_diff(a[0], want) == [] and a[0].tobytes() == b[0].tobytes() == np.concatenate(parts).tobytes(), w2
 print("me ok")
 
 # ---- transform + quantisation: every size once (type 0; 64-point sizes with and without the energy output)
@@ -56,4 +72,9 @@ with pkg.TxqContext(0) as txq:
             assert np.array_equal(got[k], want[k]), (tw, th, k)
         if max(tw, th) == 64:
             txq.fwd_txfm_quant(res_, tw, th, 0, q10, want=("qcoeff", "dqcoeff", "eob"))
+    for (tw, th) in ((4, 4), (16, 8), (64, 64)):                                  # compact return path (prefix sum + gather)
+        res_ = T.synth_residual(rng, 4 * th, 6 * tw, 8, "mixed")
+        eob, off, lv = txq.fwd_txfm_quant_compact(res_, tw, th, 0, q10)
+        want = T.txq_plane(txo, res_, tw, th, 0, q10)
+        assert np.array_equal(eob, want["eob"]) and off[-1] == len(lv) == int(eob.astype(np.int64).sum()), (tw, th)
 print("txq ok")
