@@ -128,9 +128,13 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     __syncthreads();
 
     const int ngroups = saw >> 3, mult8 = ngroups << 3, leftover = saw - mult8;
-    const int ngpairs = (ngroups + 1) >> 1;
+    // Wide: the width & 7 leftover positions (the reference's single-position SSE2 kernels) ride in the tiles of the
+    // 16-position pair they fall into -- the empty half of the last pair when the number of groups is odd (a 63-wide
+    // sub-area), else one more pair; they differ from group members only in their 32x32 key. The narrow instantiation keeps
+    // separate single-position tiles: with 64-wide preset areas there are none, and the per-position test costs it 1 %.
+    const int ngpairs = Wide ? (saw + 15) >> 4 : (ngroups + 1) >> 1;
     const int tiles_g = sah * ngpairs * 4;                         // 8-position-group tiles
-    const int tiles_s = leftover ? sah * 4 : 0;                    // single-position tiles (width & 7 leftovers)
+    const int tiles_s = (!Wide && leftover) ? sah * 4 : 0;         // single-position tiles (width & 7 leftovers)
     const int total = tiles_g + tiles_s;
     const int s = tid & 3;
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
@@ -146,11 +150,16 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     for (int u0 = 0; u0 < total; u0 += kFpThreads) {
         const int u = u0 + tid;
         const bool live = u < total;
-        const bool single = live && u >= tiles_g;
+        const bool single = !Wide && live && u >= tiles_g;
         int y = 0, x0 = 0, G = 0;
         bool val[4] = { false, false, false, false };
         if (live) {
-            if (!single) {
+            if (Wide) {
+                const int q = u >> 2;
+                G = q % ngpairs; y = q / ngpairs; x0 = 16 * G + s;
+#pragma unroll
+                for (int k = 0; k < 4; k++) val[k] = x0 + 4 * k < saw;
+            } else if (!single) {
                 const int q = u >> 2;
                 G = q % ngpairs; y = q / ngpairs; x0 = 16 * G + s;
                 val[0] = val[1] = (2 * G < ngroups); val[2] = val[3] = (2 * G + 1 < ngroups);
@@ -263,8 +272,14 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
                 uint32_t ka32[4], km32[4];
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    const uint32_t a = single ? (((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3))
-                                              : (((uint32_t)y << 7) | ((uint32_t)(2 * G + (k >> 1)) << 3) | ((k & 1) ? 0u : 4u) | (uint32_t)s);
+                    uint32_t a;
+                    if (Wide) {     // from kadd = row << 6 | x: (group << 3 | lo/hi | s) is x with bit 2 flipped; leftovers: slot 8.., plain index
+                        const uint32_t x = kadd[k] & 63u, y7 = (kadd[k] & ~63u) << 1;
+                        a = (int)x >= mult8 ? (y7 | ((8u + x - (uint32_t)mult8) << 3)) : (y7 | (x ^ 4u));
+                    } else {
+                        a = single ? (((uint32_t)y << 7) | ((uint32_t)(8 + x0 + 4 * k - mult8) << 3))
+                                   : (((uint32_t)y << 7) | ((uint32_t)(2 * G + (k >> 1)) << 3) | ((k & 1) ? 0u : 4u) | (uint32_t)s);
+                    }
                     ka32[k] = val[k] ? a : 0xFFFFFFFFu;
                     km32[k] = kmul[k] << 1;
                 }

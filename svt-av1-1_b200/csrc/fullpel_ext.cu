@@ -12,11 +12,13 @@
 //     best <- T(pos)  whenever  S(pos) < best          (S = bottom 64x32 SAD >= T = the PU's own SAD)
 // which the kernel replays after the search from per-position S / T tables kept in shared memory.
 //
-// B200 mapping: same as fullpel.cu -- four byte-shifted copies of the reference window in shared memory, one thread =
-// 4 positions x, x+4, x+8, x+12 of one row, VABSDIFF4.U8.ACC on the ALU pipe, keys built with IMAD on the FMA pipe and
-// reduced across the warp by streaming transpose-reductions (pair_min) so that at the end of a tile every lane issues
-// one RED.SHARED.MIN per PU class. The non-square SADs are sums of the 8x8 SADs: horizontal sums inside a band of
-// eight rows, vertical sums carried across bands in registers (this is what costs the registers: 1 CTA per SM).
+// B200 mapping: as in fullpel.cu -- four byte-shifted copies of the reference window in shared memory, VABSDIFF4.U8.ACC
+// on the ALU pipe, keys built with IMAD on the FMA pipe and reduced across the warp by streaming transpose-reductions
+// (pair_min) so that at the end of a tile every lane issues at most one RED.SHARED.MIN per PU class. The non-square SADs
+// are sums of the 8x8 SADs: horizontal sums inside a band of eight rows, vertical sums carried across bands in registers.
+// Those carried sums are what costs registers, so a quad of positions (x, x+4, x+8, x+12 of one row) is shared by TWO
+// lanes, one per 32-column half of the SB (lane bit 16): half the sums per thread, 128 registers, two CTAs (16 warps)
+// per SM instead of one 255-register CTA. The three 64-wide classes add the two halves with one shuffle per position.
 // Search areas beyond 64x64 (template parameter Wide, MIN(search_area, 127), ME.c:6644-6645) are cut into sub-areas of at
 // most 64x64 positions exactly like fullpel.cu and merged per PU by (SAD, row, column); the S / T tables of quirk Q11
 // then cover 128 x 128 positions and are replayed once after the last sub-area.
@@ -32,11 +34,16 @@ constexpr int kWinWords = 4 * kWinRows * kWinPitch;
 constexpr int kSrcWords = 32 * 16;
 constexpr int kKeyWords = 212;         // 209 PU slots (internal index), padded
 constexpr int kRawPitch = 40;          // words per raw window row (ten 16-byte granules), see fullpel.cu
-constexpr int kFxThreads = 256;        // x 1 CTA per SM (255 registers)
+template <bool Wide> struct FxCfg {    // 256 threads x 2 CTAs per SM; the 128x128 Q11 tables of Wide leave room for one CTA: 512 threads
+    static constexpr int kThreads = Wide ? 512 : 256, kCtas = Wide ? 1 : 2;
+};
 template <bool Wide> struct Q11 { static constexpr int kShift = Wide ? 7 : 6, kEntries = 1 << (2 * kShift); };
+// The raw window rows (20160 bytes) are dead once the four copies are made and the Q11 tables are first written by the
+// search: the narrow instantiation overlays them (24576 bytes of tables); Wide restages per sub-area while its tables live on.
 template <bool Wide> constexpr int fx_smem_bytes() {
-    return (kWinWords + kSrcWords + kKeyWords + Q11<Wide>::kEntries) * 4 + Q11<Wide>::kEntries * 2 + kWinRows * kRawPitch * 4;
+    return (kWinWords + kSrcWords + kKeyWords + Q11<Wide>::kEntries) * 4 + Q11<Wide>::kEntries * 2 + (Wide ? kWinRows * kRawPitch * 4 : 0);
 }
+static_assert(kWinRows * kRawPitch * 4 <= Q11<false>::kEntries * 6, "raw rows must fit inside the narrow Q11 tables");
 
 // see fullpel.cu: lanes whose `bit` is clear keep min(a) over {lane, lane ^ bit}, the others the same for b
 __device__ __forceinline__ uint32_t pair_min(uint32_t a, uint32_t b, int bit, uint32_t hi01) {
@@ -58,28 +65,55 @@ struct Keyer {                       // key = sad * 4096 + (row << 6 | col) as o
     }
 };
 
+// The reductions transpose over lane bits 8, 4, 2, 1 in that order (lb[i] = lane bit (8 >> i) as 0 / 1): first the
+// thread's own columns (cols4 / cols2: register index bit i -> lane bit i of the order), then time.
+// cols4: the four per-thread columns of a class -> one key, lane bits (8, 4) = column within the half
+template <typename V> __device__ __forceinline__ uint32_t cols4(const Keyer& K, const V& v, const uint32_t (&lb)[4]) {
+    uint32_t k[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) k[j] = K(v[0][j], v[1][j], v[2][j], v[3][j]);
+    return pair_min(pair_min(k[0], k[1], 8, lb[0]), pair_min(k[2], k[3], 8, lb[0]), 4, lb[1]);
+}
+template <typename V> __device__ __forceinline__ uint32_t cols2(const Keyer& K, const V& v, const uint32_t (&lb)[4]) {
+    return pair_min(K(v[0][0], v[1][0], v[2][0], v[3][0]), K(v[0][1], v[1][1], v[2][1], v[3][1]), 8, lb[0]);
+}
+// Streaming reduction over time: value v arrives at step t (a constant after unrolling) of 2^LT steps; step bit i is
+// transposed onto lane bit 8 >> (LC + i) (LC = bits the columns took). True when the reduced key of all steps drops out.
+template <int LC, int LT> __device__ __forceinline__ bool chain(uint32_t (&c)[3], int t, uint32_t v, uint32_t& out, const uint32_t (&lb)[4]) {
+#pragma unroll
+    for (int i = 0; i < LT; i++) {
+        if (((t >> i) & 1) == 0) { c[i] = v; return false; }
+        v = pair_min(c[i], v, 8 >> (LC + i), lb[LC + i]);
+    }
+    out = v;
+    return true;
+}
+
 }  // namespace
 
 namespace {
 // per-lane PU slot tables: which PU (internal index) a lane owns after the transpose-reductions of each class
 enum { T8A = 0, T8B, T16x8, T32x8, T8x16, T16x16, T32x16, T64x16, T8x32, T16x32, T32x32, T64x32, T16x64, T32x64, kNumTables };
 
+// Lane bit 16 = column half H; lane bits 8, 4, 2, 1 = v[0..3]. A class whose threads hold 2^LC columns and that runs
+// over 2^LT time steps ends with column = v[0..LC-1] (+ H above them) and step = v[LC..LC+LT-1]; lanes with any
+// later bit set issue nothing (their entry is unused).
 __device__ __forceinline__ int lane_pu(int table, int lane) {
-    const int l16 = (lane >> 4) & 1, l8 = (lane >> 3) & 1, l4 = (lane >> 2) & 1, l2 = (lane >> 1) & 1, l1 = lane & 1;
-    const int j = l16 + 2 * l8 + 4 * l4, q = l16 + 2 * l8, p = l16;
+    const int H = (lane >> 4) & 1, v0 = (lane >> 3) & 1, v1 = (lane >> 2) & 1, v2 = (lane >> 1) & 1, v3 = lane & 1;
+    const int j = v0 + 2 * v1 + 4 * H, q = v0 + 2 * H, p = H;       // 8-, 16-, 32-pixel column
     switch (table) {
-        case T8A:    return kInternal[21 + (l2 + 2 * l1) * 8 + j];
-        case T8B:    return kInternal[21 + (4 + l2 + 2 * l1) * 8 + j];
-        case T16x8:  return kInternal[95 + (l4 + 2 * l2 + 4 * l1) * 4 + q];
-        case T32x8:  return kInternal[169 + (l8 + 2 * l4 + 4 * l2) * 2 + p];
-        case T8x16:  return kInternal[137 + (l2 + 2 * l1) * 8 + j];
-        case T16x16: return kInternal[5 + (l4 + 2 * l2) * 4 + q];
-        case T32x16: return kInternal[87 + (l8 + 2 * l4) * 2 + p];
-        case T64x16: return 201 + l16 + 2 * l8;
-        case T8x32:  return kInternal[185 + l2 * 8 + j];
-        case T16x32: return kInternal[129 + l4 * 4 + q];
-        case T32x32: return 1 + l8 * 2 + p;
-        case T64x32: return 85 + l16;
+        case T8A:    return kInternal[21 + (v2 + 2 * v3) * 8 + j];
+        case T8B:    return kInternal[21 + (4 + v2 + 2 * v3) * 8 + j];
+        case T16x8:  return kInternal[95 + (v1 + 2 * v2 + 4 * v3) * 4 + q];
+        case T32x8:  return kInternal[169 + (v0 + 2 * v1 + 4 * v2) * 2 + p];
+        case T8x16:  return kInternal[137 + (v2 + 2 * v3) * 8 + j];
+        case T16x16: return kInternal[5 + (v1 + 2 * v2) * 4 + q];
+        case T32x16: return kInternal[87 + (v0 + 2 * v1) * 2 + p];
+        case T64x16: return 201 + v0 + 2 * v1;
+        case T8x32:  return kInternal[185 + v2 * 8 + j];
+        case T16x32: return kInternal[129 + v1 * 4 + q];
+        case T32x32: return 1 + v0 * 2 + p;
+        case T64x32: return 85 + v0;
         case T16x64: return 205 + q;
         default:     return 127 + p;      // T32x64
     }
@@ -87,15 +121,16 @@ __device__ __forceinline__ int lane_pu(int table, int lane) {
 }  // namespace
 
 template <bool Wide>
-__global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
-    constexpr int QS = Q11<Wide>::kShift, QN = Q11<Wide>::kEntries;
+__global__ void __launch_bounds__(FxCfg<Wide>::kThreads, FxCfg<Wide>::kCtas) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
+    constexpr int QS = Q11<Wide>::kShift, QN = Q11<Wide>::kEntries, NT = FxCfg<Wide>::kThreads;
     extern __shared__ __align__(16) uint32_t smem[];
     uint32_t* win = smem;
     uint32_t* src = win + kWinWords;
     uint32_t* keys = src + kSrcWords;
     uint32_t* q11_s = keys + kKeyWords;                                  // bottom 64x32 SAD of every position
     uint16_t* q11_t = reinterpret_cast<uint16_t*>(q11_s + QN);           // 32x16 (x 0, y 48) SAD of every position
-    uint32_t* raw = reinterpret_cast<uint32_t*>(q11_t + QN);             // raw window rows (byte offset 100048 = 16 * 6253; Wide 173776 = 16 * 10861)
+    // raw window rows: over the Q11 tables (byte offset 75472 = 16 * 4717), Wide behind them (173776 = 16 * 10861)
+    uint32_t* raw = Wide ? reinterpret_cast<uint32_t*>(q11_t + QN) : q11_s;
     __shared__ uint32_t lane_slot[kNumTables][32];                       // shared ADDRESS of the PU slot a lane owns
     __shared__ uint32_t merged_v[Wide ? kMaxPu : 1], merged_o[Wide ? kMaxPu : 1];   // Wide: running winner per PU (value, row << 8 | column)
     const DJob& job = jobs[blockIdx.y];
@@ -110,7 +145,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     const DPlane& rp = job.ref[list].full;
     const int area_x = scr.sa_x[list], area_y = scr.sa_y[list], area_w = scr.sa_w[list], area_h = scr.sa_h[list];
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
-    if (Wide) for (int t = tid; t < kMaxPu; t += kFxThreads) { merged_v[t] = 0xFFFFFFFFu; merged_o[t] = 0xFFFFFFFFu; }
+    if (Wide) for (int t = tid; t < kMaxPu; t += NT) { merged_v[t] = 0xFFFFFFFFu; merged_o[t] = 0xFFFFFFFFu; }
 #pragma unroll 1
     for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
     const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
@@ -127,7 +162,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
         const int ngran = ((int)(m16 >> 2) + nfill + 2 + 3) >> 2;
         const uint8_t* ga = g0 - m16;
         const uint32_t raw_addr = (uint32_t)__cvta_generic_to_shared(raw);
-        for (int t = tid; t < wrows * ngran; t += kFxThreads) {
+        for (int t = tid; t < wrows * ngran; t += NT) {
             const int r = t / ngran, g = t - r * ngran;
             asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(raw_addr + (uint32_t)(r * kRawPitch * 4 + g * 16)),
                          "l"(ga + (size_t)r * rp.stride + g * 16) : "memory");
@@ -135,11 +170,11 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if (!Wide || sub == 0) {
-        for (int t = tid; t < kSrcWords; t += kFxThreads)
+        for (int t = tid; t < kSrcWords; t += NT)
             src[t] = *reinterpret_cast<const uint32_t*>(job.cur.full.at(ox + 4 * (t & 15), oy + 2 * (t >> 4)));
-        for (int t = tid; t < kNumTables * 32; t += kFxThreads) lane_slot[t >> 5][t & 31] = keys_addr + 4u * (uint32_t)lane_pu(t >> 5, t & 31);
+        for (int t = tid; t < kNumTables * 32; t += NT) lane_slot[t >> 5][t & 31] = keys_addr + 4u * (uint32_t)lane_pu(t >> 5, t & 31);
     }
-    for (int t = tid; t < kKeyWords; t += kFxThreads) keys[t] = 0xFFFFFFFFu;
+    for (int t = tid; t < kKeyWords; t += NT) keys[t] = 0xFFFFFFFFu;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     {
@@ -147,7 +182,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
         if (c < nfill) {
             const uint32_t m = m16 & 3u;
             const uint32_t* rw = raw + (m16 >> 2) + c;
-            for (int r = tid >> 5; r < wrows; r += kFxThreads / 32) {
+            for (int r = tid >> 5; r < wrows; r += NT / 32) {
                 const uint32_t* w = rw + r * kRawPitch;
                 const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
 #pragma unroll
@@ -162,16 +197,17 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     __syncthreads();
 
     const int ngp = (saw + 15) >> 4;                   // 16-position groups per row
-    const int total = sah * ngp * 4;
-    const int s = tid & 3, lane = tid & 31;
-    const uint32_t l16 = (lane >> 4) & 1, l8 = (lane >> 3) & 1, l4 = (lane >> 2) & 1, l2 = (lane >> 1) & 1, l1 = lane & 1;
+    const int nquads = sah * ngp;                      // quad = the 4 positions x0, x0 + 4, x0 + 8, x0 + 12 of one (row, group, phase)
+    const int lane = tid & 31, s = lane & 3, H = lane >> 4;
+    // lane bits 8, 4, 2, 1 as 0 / 1 (the transposition bits of the reductions, in the order the chains use them)
+    const uint32_t lb[4] = { (uint32_t)(lane >> 3) & 1u, (uint32_t)(lane >> 2) & 1u, (uint32_t)(lane >> 1) & 1u, (uint32_t)lane & 1u };
 #define SLOT(t) lane_slot[t][lane]
 
-    for (int u0 = 0; u0 < total; u0 += kFxThreads) {
-        const int u = u0 + tid;
-        const bool live = u < total;
+    for (int q0 = 0; q0 < nquads; q0 += NT / 8) {
+        const int qi = q0 + (tid >> 5) * 4 + ((lane >> 2) & 3);
+        const bool live = qi < nquads;
         int y = 0, x0 = s;
-        if (live) { const int q = u >> 2; const int G = q % ngp; y = q / ngp; x0 = 16 * G + s; }
+        if (live) { const int G = qi % ngp; y = qi / ngp; x0 = 16 * G + s; }
         Keyer K;
         bool val[4];
 #pragma unroll
@@ -180,34 +216,32 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
             K.mul[k] = val[k] ? 4096u : 0u;
             K.add[k] = val[k] ? (uint32_t)((y << 6) | (x0 + 4 * k)) : 0xFFFFFFFFu;
         }
-        uint32_t acc[2][4][8];                          // 8x8 SADs of the current band [b & 1] and of the band before
-        uint32_t h16[4][4], v16[4][4], w16[4][4];       // 16x16 (band pair), 16x32 (half), 16x64 column sums
-        uint32_t c32[4][8];                             // 8x32 column sums of the current half
-        uint32_t s32[4][2], w32[4][2], s64h[4], s64[4]; // 32x32 of the half, 32x64, 64x32 of the half, 64x64
+        uint32_t acc[2][4][4];                          // 8x8 SADs of the current band [b & 1] and of the band before (this thread's four columns)
+        uint32_t h16[4][2], v16[4][2], w16[4][2];       // 16x16 (band pair), 16x32 (half), 16x64 column sums
+        uint32_t c32[4][4];                             // 8x32 column sums of the current half
+        uint32_t w32[4];                                // 32x64 of this thread's 32 columns
         // carries of the streaming transpose-reductions, one chain per PU class
-        uint32_t c8a = 0, c8b = 0, c168a = 0, c168b = 0, c168c = 0, c328a = 0, c328b = 0, c328c = 0;
-        uint32_t c816a = 0, c816b = 0, c1616a = 0, c1616b = 0, c3216a = 0, c3216b = 0, c6416a = 0, c6416b = 0;
-        uint32_t c832 = 0, c1632 = 0, c3232 = 0, c6432 = 0;
+        uint32_t c8[3], c168[3], c328[3], c816[3], c1616[3], c3216[3], c6416[3], c832[3], c1632[3], c3232[3], c6432[3];
 #pragma unroll
         for (int b = 0; b < 8; b++) {
-            uint32_t (&A)[4][8] = acc[b & 1];
+            uint32_t (&A)[4][4] = acc[b & 1];
 #pragma unroll
             for (int k = 0; k < 4; k++)
 #pragma unroll
-                for (int j = 0; j < 8; j++) A[k][j] = 0;
+                for (int j = 0; j < 4; j++) A[k][j] = 0;
 #pragma unroll
             for (int rr = 0; rr < 4; rr++) {
                 const int r = 4 * b + rr;
-                const uint4* wp = reinterpret_cast<const uint4*>(win + (s * kWinRows + y + 2 * r) * kWinPitch + (x0 >> 2));
-                uint32_t ref[20];
+                const uint4* wp = reinterpret_cast<const uint4*>(win + (s * kWinRows + y + 2 * r) * kWinPitch + (x0 >> 2) + 8 * H);
+                uint32_t ref[12];
 #pragma unroll
-                for (int i = 0; i < 5; i++) {
+                for (int i = 0; i < 3; i++) {
                     const uint4 v = wp[i];
                     ref[4 * i] = v.x; ref[4 * i + 1] = v.y; ref[4 * i + 2] = v.z; ref[4 * i + 3] = v.w;
                 }
-                const uint4* sp = reinterpret_cast<const uint4*>(src + r * 16);
+                const uint4* sp = reinterpret_cast<const uint4*>(src + r * 16 + 8 * H);
 #pragma unroll
-                for (int cc = 0; cc < 4; cc++) {
+                for (int cc = 0; cc < 2; cc++) {
                     const uint4 sv = sp[cc];
                     const uint32_t sw[4] = { sv.x, sv.y, sv.z, sv.w };
 #pragma unroll
@@ -218,201 +252,83 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
                     }
                 }
             }
+            uint32_t out;
             // ---- band b (rows 8b .. 8b+7): 8x8, 16x8, 32x8 PUs of this band
-            uint32_t h[4][4], g[4][2];
+            uint32_t h[4][2], g[4];
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-#pragma unroll
-                for (int q = 0; q < 4; q++) h[k][q] = A[k][2 * q] + A[k][2 * q + 1];
-                g[k][0] = h[k][0] + h[k][1]; g[k][1] = h[k][2] + h[k][3];
+                h[k][0] = A[k][0] + A[k][1]; h[k][1] = A[k][2] + A[k][3];
+                g[k] = h[k][0] + h[k][1];
             }
-            {   // 8x8: lanes end up with column (l16,l8,l4) and band-in-half (l2,l1)
-                uint32_t k8[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) k8[j] = K(A[0][j], A[1][j], A[2][j], A[3][j]);
-                const uint32_t a0 = pair_min(k8[0], k8[1], 16, l16), a1 = pair_min(k8[2], k8[3], 16, l16);
-                const uint32_t a2 = pair_min(k8[4], k8[5], 16, l16), a3 = pair_min(k8[6], k8[7], 16, l16);
-                const uint32_t t3 = pair_min(pair_min(a0, a1, 8, l8), pair_min(a2, a3, 8, l8), 4, l4);
-                if ((b & 1) == 0) c8a = t3;
-                else {
-                    const uint32_t t4 = pair_min(c8a, t3, 2, l2);
-                    if ((b & 3) == 1) c8b = t4;
-                    else red_min(b == 3 ? SLOT(T8A) : SLOT(T8B), pair_min(c8b, t4, 1, l1));
-                }
-            }
-            {   // 16x8: column (l16,l8), band (l4,l2,l1)
-                uint32_t kq[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) kq[q] = K(h[0][q], h[1][q], h[2][q], h[3][q]);
-                const uint32_t r2 = pair_min(pair_min(kq[0], kq[1], 16, l16), pair_min(kq[2], kq[3], 16, l16), 8, l8);
-                if ((b & 1) == 0) c168a = r2;
-                else {
-                    const uint32_t r3 = pair_min(c168a, r2, 4, l4);
-                    if ((b & 3) == 1) c168b = r3;
-                    else {
-                        const uint32_t r4 = pair_min(c168b, r3, 2, l2);
-                        if (b == 3) c168c = r4; else red_min(SLOT(T16x8), pair_min(c168c, r4, 1, l1));
-                    }
-                }
-            }
-            {   // 32x8: column l16, band (l8,l4,l2); bit 1 by shuffle
-                const uint32_t r1 = pair_min(K(g[0][0], g[1][0], g[2][0], g[3][0]), K(g[0][1], g[1][1], g[2][1], g[3][1]), 16, l16);
-                if ((b & 1) == 0) c328a = r1;
-                else {
-                    const uint32_t r2 = pair_min(c328a, r1, 8, l8);
-                    if ((b & 3) == 1) c328b = r2;
-                    else {
-                        const uint32_t r3 = pair_min(c328b, r2, 4, l4);
-                        if (b == 3) c328c = r3;
-                        else { const uint32_t f = shfl_min(pair_min(c328c, r3, 2, l2), 1); if (!l1) red_min(SLOT(T32x8), f); }
-                    }
-                }
-            }
+            if (chain<2, 2>(c8, b & 3, cols4(K, A, lb), out, lb)) red_min(b == 3 ? SLOT(T8A) : SLOT(T8B), out);
+            if (chain<1, 3>(c168, b, cols2(K, h, lb), out, lb)) red_min(SLOT(T16x8), out);
+            if (chain<0, 3>(c328, b, K(g[0], g[1], g[2], g[3]), out, lb)) { out = shfl_min(out, 1); if (!lb[3]) red_min(SLOT(T32x8), out); }
             if ((b & 1) == 0) {
 #pragma unroll
-                for (int k = 0; k < 4; k++)
-#pragma unroll
-                    for (int q = 0; q < 4; q++) h16[k][q] = h[k][q];
+                for (int k = 0; k < 4; k++) { h16[k][0] = h[k][0]; h16[k][1] = h[k][1]; }
                 continue;
             }
             // ---- band pair (rows 16*pair .. +15): 8x16, 16x16, 32x16, 64x16
             const int pair = b >> 1;
-            uint32_t (&E)[4][8] = acc[0];               // the even band of the pair (A is acc[1] here)
-            uint32_t m32[4][2];
+            uint32_t (&E)[4][4] = acc[0];               // the even band of the pair (A is acc[1] here)
+            uint32_t m32[4], m64[4];
 #pragma unroll
             for (int k = 0; k < 4; k++) {
 #pragma unroll
-                for (int j = 0; j < 8; j++) E[k][j] += A[k][j];          // E becomes the 8x16 column sums
-#pragma unroll
-                for (int q = 0; q < 4; q++) h16[k][q] += h[k][q];
-                m32[k][0] = h16[k][0] + h16[k][1]; m32[k][1] = h16[k][2] + h16[k][3];
+                for (int j = 0; j < 4; j++) E[k][j] += A[k][j];          // E becomes the 8x16 column sums
+                h16[k][0] += h[k][0]; h16[k][1] += h[k][1];
+                m32[k] = h16[k][0] + h16[k][1];
+                m64[k] = m32[k] + __shfl_xor_sync(0xffffffffu, m32[k], 16);
             }
-            {   // 8x16: column (l16,l8,l4), pair (l2,l1)
-                uint32_t k8[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) k8[j] = K(E[0][j], E[1][j], E[2][j], E[3][j]);
-                const uint32_t a0 = pair_min(k8[0], k8[1], 16, l16), a1 = pair_min(k8[2], k8[3], 16, l16);
-                const uint32_t a2 = pair_min(k8[4], k8[5], 16, l16), a3 = pair_min(k8[6], k8[7], 16, l16);
-                const uint32_t t3 = pair_min(pair_min(a0, a1, 8, l8), pair_min(a2, a3, 8, l8), 4, l4);
-                if ((pair & 1) == 0) c816a = t3;
-                else {
-                    const uint32_t t4 = pair_min(c816a, t3, 2, l2);
-                    if (pair == 1) c816b = t4; else red_min(SLOT(T8x16), pair_min(c816b, t4, 1, l1));
-                }
-            }
-            {   // 16x16: column (l16,l8), pair (l4,l2); bit 1 by shuffle
-                uint32_t kq[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) kq[q] = K(h16[0][q], h16[1][q], h16[2][q], h16[3][q]);
-                const uint32_t r2 = pair_min(pair_min(kq[0], kq[1], 16, l16), pair_min(kq[2], kq[3], 16, l16), 8, l8);
-                if ((pair & 1) == 0) c1616a = r2;
-                else {
-                    const uint32_t r3 = pair_min(c1616a, r2, 4, l4);
-                    if (pair == 1) c1616b = r3;
-                    else { const uint32_t f = shfl_min(pair_min(c1616b, r3, 2, l2), 1); if (!l1) red_min(SLOT(T16x16), f); }
-                }
-            }
-            {   // 32x16: column l16, pair (l8,l4); bits 2,1 by shuffle. The slot of PU #5 (x 0, y 48) is overwritten by the
-                // replay of quirk Q11 after the search.
-                const uint32_t r1 = pair_min(K(m32[0][0], m32[1][0], m32[2][0], m32[3][0]), K(m32[0][1], m32[1][1], m32[2][1], m32[3][1]), 16, l16);
-                if ((pair & 1) == 0) c3216a = r1;
-                else {
-                    const uint32_t r2 = pair_min(c3216a, r1, 8, l8);
-                    if (pair == 1) c3216b = r2;
-                    else { const uint32_t f = shfl_min(shfl_min(pair_min(c3216b, r2, 4, l4), 2), 1); if ((lane & 3) == 0) red_min(SLOT(T32x16), f); }
-                }
-            }
-            {   // 64x16: pair (l16,l8); bits 4,2,1 by shuffle
-                const uint32_t r0 = K(m32[0][0] + m32[0][1], m32[1][0] + m32[1][1], m32[2][0] + m32[2][1], m32[3][0] + m32[3][1]);
-                if ((pair & 1) == 0) c6416a = r0;
-                else {
-                    const uint32_t r1 = pair_min(c6416a, r0, 16, l16);
-                    if (pair == 1) c6416b = r1;
-                    else { const uint32_t f = shfl_min(shfl_min(shfl_min(pair_min(c6416b, r1, 8, l8), 4), 2), 1); if ((lane & 7) == 0) red_min(SLOT(T64x16), f); }
-                }
-            }
+            if (chain<2, 2>(c816, pair, cols4(K, E, lb), out, lb)) red_min(SLOT(T8x16), out);
+            if (chain<1, 2>(c1616, pair, cols2(K, h16, lb), out, lb)) { out = shfl_min(out, 1); if (!lb[3]) red_min(SLOT(T16x16), out); }
+            // (the slot of 32x16 PU #5 (x 0, y 48) is overwritten by the replay of quirk Q11 after the search)
+            if (chain<0, 2>(c3216, pair, K(m32[0], m32[1], m32[2], m32[3]), out, lb)) { out = shfl_min(shfl_min(out, 2), 1); if (!(lane & 3)) red_min(SLOT(T32x16), out); }
+            if (chain<0, 2>(c6416, pair, K(m64[0], m64[1], m64[2], m64[3]), out, lb)) { out = shfl_min(shfl_min(out, 2), 1); if (!(lane & 19)) red_min(SLOT(T64x16), out); }
             if ((pair & 1) == 0) {
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
 #pragma unroll
-                    for (int j = 0; j < 8; j++) c32[k][j] = E[k][j];
-#pragma unroll
-                    for (int q = 0; q < 4; q++) v16[k][q] = h16[k][q];
+                    for (int j = 0; j < 4; j++) c32[k][j] = E[k][j];
+                    v16[k][0] = h16[k][0]; v16[k][1] = h16[k][1];
                 }
                 continue;
             }
             // ---- half (rows 32*half .. +31): 8x32, 16x32, 32x32, 64x32
             const int half = b >> 2;
+            uint32_t s32[4], s64h[4];
 #pragma unroll
             for (int k = 0; k < 4; k++) {
 #pragma unroll
-                for (int j = 0; j < 8; j++) c32[k][j] += E[k][j];
-#pragma unroll
-                for (int q = 0; q < 4; q++) v16[k][q] += h16[k][q];
-                s32[k][0] = v16[k][0] + v16[k][1]; s32[k][1] = v16[k][2] + v16[k][3];
-                s64h[k] = s32[k][0] + s32[k][1];
+                for (int j = 0; j < 4; j++) c32[k][j] += E[k][j];
+                v16[k][0] += h16[k][0]; v16[k][1] += h16[k][1];
+                s32[k] = v16[k][0] + v16[k][1];
+                s64h[k] = s32[k] + __shfl_xor_sync(0xffffffffu, s32[k], 16);
             }
-            {   // 8x32: column (l16,l8,l4), half l2; bit 1 by shuffle
-                uint32_t k8[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) k8[j] = K(c32[0][j], c32[1][j], c32[2][j], c32[3][j]);
-                const uint32_t a0 = pair_min(k8[0], k8[1], 16, l16), a1 = pair_min(k8[2], k8[3], 16, l16);
-                const uint32_t a2 = pair_min(k8[4], k8[5], 16, l16), a3 = pair_min(k8[6], k8[7], 16, l16);
-                const uint32_t t3 = pair_min(pair_min(a0, a1, 8, l8), pair_min(a2, a3, 8, l8), 4, l4);
-                if (half == 0) c832 = t3;
-                else { const uint32_t f = shfl_min(pair_min(c832, t3, 2, l2), 1); if (!l1) red_min(SLOT(T8x32), f); }
-            }
-            {   // 16x32: column (l16,l8), half l4; bits 2,1 by shuffle
-                uint32_t kq[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) kq[q] = K(v16[0][q], v16[1][q], v16[2][q], v16[3][q]);
-                const uint32_t r2 = pair_min(pair_min(kq[0], kq[1], 16, l16), pair_min(kq[2], kq[3], 16, l16), 8, l8);
-                if (half == 0) c1632 = r2;
-                else { const uint32_t f = shfl_min(shfl_min(pair_min(c1632, r2, 4, l4), 2), 1); if ((lane & 3) == 0) red_min(SLOT(T16x32), f); }
-            }
-            {   // 32x32: column l16, half l8; bits 4,2,1 by shuffle
-                const uint32_t r1 = pair_min(K(s32[0][0], s32[1][0], s32[2][0], s32[3][0]), K(s32[0][1], s32[1][1], s32[2][1], s32[3][1]), 16, l16);
-                if (half == 0) c3232 = r1;
-                else { const uint32_t f = shfl_min(shfl_min(shfl_min(pair_min(c3232, r1, 8, l8), 4), 2), 1); if ((lane & 7) == 0) red_min(SLOT(T32x32), f); }
-            }
-            {   // 64x32: half l16; the rest by shuffle
-                const uint32_t r0 = K(s64h[0], s64h[1], s64h[2], s64h[3]);
-                if (half == 0) c6432 = r0;
-                else {
-                    const uint32_t f = shfl_min(shfl_min(shfl_min(shfl_min(pair_min(c6432, r0, 16, l16), 8), 4), 2), 1);
-                    if ((lane & 15) == 0) red_min(SLOT(T64x32), f);
-                }
-            }
+            if (chain<2, 1>(c832, half, cols4(K, c32, lb), out, lb)) { out = shfl_min(out, 1); if (!lb[3]) red_min(SLOT(T8x32), out); }
+            if (chain<1, 1>(c1632, half, cols2(K, v16, lb), out, lb)) { out = shfl_min(shfl_min(out, 2), 1); if (!(lane & 3)) red_min(SLOT(T16x32), out); }
+            if (chain<0, 1>(c3232, half, K(s32[0], s32[1], s32[2], s32[3]), out, lb)) { out = shfl_min(shfl_min(shfl_min(out, 4), 2), 1); if (!(lane & 7)) red_min(SLOT(T32x32), out); }
+            if (chain<0, 1>(c6432, half, K(s64h[0], s64h[1], s64h[2], s64h[3]), out, lb)) { out = shfl_min(shfl_min(shfl_min(out, 4), 2), 1); if (!(lane & 23)) red_min(SLOT(T64x32), out); }
             if (half == 0) {
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
-#pragma unroll
-                    for (int q = 0; q < 4; q++) w16[k][q] = v16[k][q];
-                    w32[k][0] = s32[k][0]; w32[k][1] = s32[k][1]; s64[k] = s64h[k];
-                }
+                for (int k = 0; k < 4; k++) { w16[k][0] = v16[k][0]; w16[k][1] = v16[k][1]; w32[k] = s32[k]; }
                 continue;
             }
-            // ---- whole SB: 16x64, 32x64, 64x64, and the per-position S / T tables of quirk Q11
+            // ---- whole SB: 16x64, 32x64, 64x64, and the per-position S / T tables of quirk Q11 (S = bottom 64x32, T = the
+            // 32x16 PU at x 0, y 48: the left half's 32x16 sum of the last band pair)
+            uint32_t s64[4];
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-#pragma unroll
-                for (int q = 0; q < 4; q++) w16[k][q] += v16[k][q];
-                w32[k][0] += s32[k][0]; w32[k][1] += s32[k][1]; s64[k] += s64h[k];
-                if (val[k]) { const int pos = ((ty0 + y) << QS) | (tx0 + x0 + 4 * k); q11_s[pos] = s64h[k]; q11_t[pos] = (uint16_t)m32[k][0]; }
+                w16[k][0] += v16[k][0]; w16[k][1] += v16[k][1]; w32[k] += s32[k];
+                s64[k] = w32[k] + __shfl_xor_sync(0xffffffffu, w32[k], 16);
+                if (val[k] && !H) { const int pos = ((ty0 + y) << QS) | (tx0 + x0 + 4 * k); q11_s[pos] = s64h[k]; q11_t[pos] = (uint16_t)m32[k]; }
             }
-            {
-                uint32_t kq[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) kq[q] = K(w16[0][q], w16[1][q], w16[2][q], w16[3][q]);
-                const uint32_t r2 = pair_min(pair_min(kq[0], kq[1], 16, l16), pair_min(kq[2], kq[3], 16, l16), 8, l8);
-                const uint32_t f = shfl_min(shfl_min(shfl_min(r2, 4), 2), 1);
-                if ((lane & 7) == 0) red_min(SLOT(T16x64), f);
-            }
-            {
-                const uint32_t r1 = pair_min(K(w32[0][0], w32[1][0], w32[2][0], w32[3][0]), K(w32[0][1], w32[1][1], w32[2][1], w32[3][1]), 16, l16);
-                const uint32_t f = shfl_min(shfl_min(shfl_min(shfl_min(r1, 8), 4), 2), 1);
-                if ((lane & 15) == 0) red_min(SLOT(T32x64), f);
-            }
+            out = cols2(K, w16, lb);
+            out = shfl_min(shfl_min(shfl_min(out, 4), 2), 1);
+            if (!(lane & 7)) red_min(SLOT(T16x64), out);
+            out = K(w32[0], w32[1], w32[2], w32[3]);
+            out = shfl_min(shfl_min(shfl_min(shfl_min(out, 8), 4), 2), 1);
+            if (!(lane & 15)) red_min(SLOT(T32x64), out);
             {
                 const uint32_t m = __reduce_min_sync(0xffffffffu, K(s64[0], s64[1], s64[2], s64[3]));
                 if (lane == 0) red_min(keys_addr, m);
@@ -423,7 +339,7 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     __syncthreads();
 
     // ---- decode the winning keys into p_sb_best_sad / p_sb_best_mv form (internal index = slot)
-    for (int t = tid; t < kMaxPu; t += kFxThreads) {
+    for (int t = tid; t < kMaxPu; t += NT) {
         if (t == 87 + 5) continue;                                  // quirk Q11: replayed below
         const uint32_t key = keys[t];
         const uint32_t v = key >> 12; const int y = (key >> 6) & 63, x = key & 63;
@@ -445,12 +361,12 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
     // CTA answers one query per step (a handful of steps: S covers four times the area of T, so it rarely drops below an
     // earlier T).
     {
-        constexpr int kPer = QN / kFxThreads;
+        constexpr int kPer = QN / NT;
         auto s_of = [&](int n) { return ((n & ((1 << QS) - 1)) < area_w && (n >> QS) < area_h) ? q11_s[n] : 0xFFFFFFFFu; };
         uint32_t S[Wide ? 1 : kPer];
         if (!Wide) {
 #pragma unroll
-            for (int i = 0; i < kPer; i++) S[i] = s_of(tid + kFxThreads * i);      // raster index (row << QS | col)
+            for (int i = 0; i < kPer; i++) S[i] = s_of(tid + NT * i);      // raster index (row << QS | col)
         }
         uint32_t* red = keys + kMaxPu;                                // three spare words of the key table
         uint32_t best = 0xFFFFFFFFu;
@@ -461,11 +377,11 @@ __global__ void __launch_bounds__(kFxThreads, 1) fullpel_ext_kernel(const DJob* 
             if (!Wide) {
 #pragma unroll
                 for (int i = kPer - 1; i >= 0; i--) {
-                    const int n = tid + kFxThreads * i;
+                    const int n = tid + NT * i;
                     if (n > cur && S[i] < best) cand = (uint32_t)n;
                 }
             } else {
-                for (int n = tid + kFxThreads * max(0, (cur + 1 - tid + kFxThreads - 1) / kFxThreads); n < QN && (n >> QS) < area_h; n += kFxThreads)
+                for (int n = tid + NT * max(0, (cur + 1 - tid + NT - 1) / NT); n < QN && (n >> QS) < area_h; n += NT)
                     if (n > cur && s_of(n) < best) { cand = (uint32_t)n; break; }
             }
             cand = __reduce_min_sync(0xffffffffu, cand);
@@ -492,8 +408,8 @@ cudaError_t configure_fullpel_ext() {
 }
 
 void launch_fullpel_ext(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool wide, cudaStream_t st) {
-    if (wide) fullpel_ext_kernel<true><<<dim3(max_sb, n_jobs), kFxThreads, fx_smem_bytes<true>(), st>>>(d_jobs, list);
-    else      fullpel_ext_kernel<false><<<dim3(max_sb, n_jobs), kFxThreads, fx_smem_bytes<false>(), st>>>(d_jobs, list);
+    if (wide) fullpel_ext_kernel<true><<<dim3(max_sb, n_jobs), FxCfg<true>::kThreads, fx_smem_bytes<true>(), st>>>(d_jobs, list);
+    else      fullpel_ext_kernel<false><<<dim3(max_sb, n_jobs), FxCfg<false>::kThreads, fx_smem_bytes<false>(), st>>>(d_jobs, list);
 }
 
 }  // namespace svtme

@@ -36,3 +36,15 @@ def test_gop_jobs_cover_every_picture_once():
     for poc, tl, r0, r1 in jobs:
         assert 0 <= r0 < bench.N_PICS and 0 <= r1 < bench.N_PICS and r0 != poc and r1 != poc
         assert tl == (0 if poc % 8 == 0 else 1 if poc % 4 == 0 else 2 if poc % 2 == 0 else 3)
+
+
+def test_fullpel_ext_lane_tables():
+    """The transpose-reduction network of fullpel_ext.cu replayed on sets (tools/check_fx_lanes.py): every PU of every
+    class is issued once per tile by a lane that holds all 16 quads' keys of exactly that PU, and lane_pu() names it."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location(
+        "check_fx_lanes", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "check_fx_lanes.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.check()
