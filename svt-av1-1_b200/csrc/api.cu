@@ -8,6 +8,7 @@
 // Batches rotate through a small ring of job tables / scratch / result buffers, so a new batch can be
 // enqueued while the previous one computes and the one before that drains.
 #include "me_common.cuh"
+#include <cuda.h>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -63,6 +64,7 @@ struct Slot {
 struct SvtMeContext {
     int device = 0, width = 0, height = 0, sb_cols = 0, sb_rows = 0, n_sb = 0;
     cudaStream_t stream = nullptr, copy_in = nullptr, copy_out = nullptr;
+    uint8_t* d_tmaps = nullptr;           // SVTME_TMA=1: one 128-byte CUtensorMap per slot (its padded full plane)
     cudaEvent_t join_ev = nullptr;
     // chunked submission: a small batch (one mini-GOP: a handful of waves per kernel) is cut into two chunks of pictures that
     // run their kernel sequences on two streams, so the tail of one chunk's kernel is filled by the other chunk's CTAs.
@@ -223,6 +225,36 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
         CU(cudaEventRecord(s.ready_ipc, ctx->copy_in));
     }
     CU(cudaStreamSynchronize(ctx->copy_in));
+    // The full-pel kernels fetch their raw window as ONE 2-D tensor box per SB (TMA) instead of ~1260 16-byte cp.async granules
+    // (measured: profiles/microbench/tma_window_r02.txt). One descriptor per slot (the planes never move). SVTME_TMA=0 keeps
+    // the cp.async staging; so does a driver without cuTensorMapEncodeTiled unless SVTME_TMA=1 asks for the descriptors.
+    const char* tma_env = getenv("SVTME_TMA");
+    if (!tma_env || atoi(tma_env) > 0) {
+        typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn || q != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            if (tma_env) return fail(ctx, SVTME_ERR_UNDEFINED, "SVTME_TMA=1: cuTensorMapEncodeTiled not available");
+            return SVTME_OK;
+        }
+        std::vector<uint8_t> maps((size_t)num_slots * 128, 0);
+        for (int i = 0; i < num_slots; i++) {
+            const DPlane& pl = ctx->slots[i].pyr.full;
+            const cuuint64_t dims[2] = { (cuuint64_t)pl.stride, (cuuint64_t)(pl.h + 2 * pl.oy) }, strides[1] = { (cuuint64_t)pl.stride };
+            const cuuint32_t box[2] = { kTmaBoxBytes, kTmaBoxRows }, estr[2] = { 1, 1 };
+            CUtensorMap m;
+            memset(&m, 0, sizeof(m));
+            const CUresult r = ((EncodeFn)fn)(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, pl.buf, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return fail(ctx, SVTME_ERR_UNDEFINED, "SVTME_TMA: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+            static_assert(sizeof(CUtensorMap) <= 128, "descriptor slot");
+            memcpy(maps.data() + (size_t)i * 128, &m, sizeof(m));
+        }
+        CU(cudaMalloc(&ctx->d_tmaps, maps.size()));
+        CU(cudaMemcpy(ctx->d_tmaps, maps.data(), maps.size(), cudaMemcpyHostToDevice));
+    }
     return SVTME_OK;
 }
 
@@ -256,6 +288,7 @@ void svtme_destroy(SvtMeContext* ctx) {
     for (auto& t : ctx->timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); if (s.ready_ipc) cudaEventDestroy(s.ready_ipc); }
+    cudaFree(ctx->d_tmaps);
     cudaFree(ctx->d_in16); cudaFree(ctx->d_rem);
     for (auto e : ctx->peer_events) cudaEventDestroy(e);
     for (auto& kv : ctx->ipc_open) { cudaIpcCloseMemHandle(kv.second.first); cudaEventDestroy(kv.second.second); }
@@ -606,6 +639,8 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
         res_rows += (size_t)ctx->n_sb * j.params.num_pus;
         d.debug = j.debug ? b.d_debug + (size_t)i * ctx->n_sb : nullptr;
         d.sb_cols = ctx->sb_cols; d.sb_rows = ctx->sb_rows;
+        d.ref_tmap[0] = ctx->d_tmaps ? (const void*)(ctx->d_tmaps + (size_t)j.ref0_slot * 128) : nullptr;
+        d.ref_tmap[1] = ctx->d_tmaps ? (const void*)(ctx->d_tmaps + (size_t)r1 * 128) : nullptr;
         const bool whole = j.sb_row_begin == 0 && j.sb_row_end == 0;
         const int unit = j.range_in_sbs ? 1 : ctx->sb_cols;
         d.sb_begin = whole ? 0 : j.sb_row_begin * unit;

@@ -54,12 +54,13 @@ __device__ __forceinline__ void red_min(uint32_t slot_addr, uint32_t key) {
 
 template <bool Wide>
 __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __restrict__ jobs, int list) {
-    extern __shared__ __align__(16) uint32_t smem[];
+    extern __shared__ __align__(128) uint32_t smem[];
     __shared__ uint32_t merged_v[Wide ? kNumPu : 1], merged_o[Wide ? kNumPu : 1];   // Wide: running winner per PU (value, order key)
+    __shared__ __align__(8) uint64_t tma_bar;
     uint32_t* win = smem;
     uint32_t* src = smem + 4 * kWinRows * kWinPitch;
     uint32_t* keys = src + 32 * 16;
-    uint32_t* raw = keys + 96;                                   // 16-byte aligned: (4 * 126 * 36 + 512 + 96) * 4 = 16 * 4688
+    uint32_t* raw = keys + 96;                                   // 128-byte aligned (a TMA destination): (4 * 126 * 36 + 512 + 96) * 4 = 128 * 586
     const DJob& job = jobs[blockIdx.y];
     const int sb = job.sb_begin + blockIdx.x;
     if (sb >= job.sb_end) return;
@@ -72,6 +73,10 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const DPlane& rp = job.ref[list].full;
     const int area_x = scr.sa_x[list], area_y = scr.sa_y[list], area_w = scr.sa_w[list], area_h = scr.sa_h[list];
     if (Wide && tid < kNumPu) { merged_v[tid] = 0xFFFFFFFFu; merged_o[tid] = 0xFFFFFFFFu; }
+    const void* tmap = job.ref_tmap[list];                        // CTA-uniform
+    const uint32_t bar_addr = (uint32_t)__cvta_generic_to_shared(&tma_bar);
+    uint32_t tma_phase = 0;
+    if (tmap && tid == 0) mbar_init(bar_addr, 1);
     for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
     // sub-area of this pass: the whole area, or (Wide) one of up to 2 x 2 pieces of at most 64 x 64 positions
     const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
@@ -89,7 +94,16 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
     const uint8_t* g0 = rp.at(ox + sax, oy + say);
     const uint32_t m16 = (uint32_t)(uintptr_t)g0 & 15u;           // the same for every row: the pitch is a multiple of 64
-    {
+    if (tmap) {
+        // one box for the whole window (rows past the window and bytes past the plane's pitch are fetched or zero-filled and
+        // never read). Thread 0 both initialised the mbarrier and issues; every other thread first touches it after the
+        // __syncthreads() below.
+        if (tid == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the previous sub-area's reads of `raw` (generic proxy) come first
+            mbar_expect_tx(bar_addr, kTmaBoxBytes * kTmaBoxRows);
+            tma_load_2d((uint32_t)__cvta_generic_to_shared(raw), tmap, rp.ox + ox + sax - (int)m16, rp.oy + oy + say, bar_addr);
+        }
+    } else {
         const int ngran = ((int)(m16 >> 2) + nfill + 2 + 3) >> 2;     // granules per row that hold the words read below (<= 10)
         const uint8_t* ga = g0 - m16;
         const uint32_t raw_addr = (uint32_t)__cvta_generic_to_shared(raw);
@@ -107,6 +121,7 @@ __global__ void __launch_bounds__(kFpThreads, 2) fullpel_kernel(const DJob* __re
     if (tid < 96) keys[tid] = 0xFFFFFFFFu;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
+    if (tmap) { mbar_wait(bar_addr, tma_phase); tma_phase ^= 1u; }
     {
         // lane = window column (word), warp = every eighth row: three raw words give the four byte-shifted copies of a word
         const int c = tid & 31;

@@ -32,7 +32,7 @@ constexpr int kWinRows = 126;          // 64 search rows + 62
 constexpr int kWinPitch = 36;          // words; = 4 (mod 32): the 8 row-distinct LDS.128 of a warp are conflict-free
 constexpr int kWinWords = 4 * kWinRows * kWinPitch;
 constexpr int kSrcWords = 32 * 16;
-constexpr int kKeyWords = 212;         // 209 PU slots (internal index), padded
+constexpr int kKeyWords = 224;         // 209 PU slots (internal index), padded so that the raw rows behind them start on a 128-byte boundary (TMA)
 constexpr int kRawPitch = 40;          // words per raw window row (ten 16-byte granules), see fullpel.cu
 template <bool Wide> struct FxCfg {    // 256 threads x 2 CTAs per SM; the 128x128 Q11 tables of Wide leave room for one CTA: 512 threads
     static constexpr int kThreads = Wide ? 512 : 256, kCtas = Wide ? 1 : 2;
@@ -123,13 +123,14 @@ __device__ __forceinline__ int lane_pu(int table, int lane) {
 template <bool Wide>
 __global__ void __launch_bounds__(FxCfg<Wide>::kThreads, FxCfg<Wide>::kCtas) fullpel_ext_kernel(const DJob* __restrict__ jobs, int list) {
     constexpr int QS = Q11<Wide>::kShift, QN = Q11<Wide>::kEntries, NT = FxCfg<Wide>::kThreads;
-    extern __shared__ __align__(16) uint32_t smem[];
+    extern __shared__ __align__(128) uint32_t smem[];
+    __shared__ __align__(8) uint64_t tma_bar;
     uint32_t* win = smem;
     uint32_t* src = win + kWinWords;
     uint32_t* keys = src + kSrcWords;
     uint32_t* q11_s = keys + kKeyWords;                                  // bottom 64x32 SAD of every position
     uint16_t* q11_t = reinterpret_cast<uint16_t*>(q11_s + QN);           // 32x16 (x 0, y 48) SAD of every position
-    // raw window rows: over the Q11 tables (byte offset 75472 = 16 * 4717), Wide behind them (173776 = 16 * 10861)
+    // raw window rows: over the Q11 tables (byte offset 75520 = 128 * 590), Wide behind them (173824 = 128 * 1358)
     uint32_t* raw = Wide ? reinterpret_cast<uint32_t*>(q11_t + QN) : q11_s;
     __shared__ uint32_t lane_slot[kNumTables][32];                       // shared ADDRESS of the PU slot a lane owns
     __shared__ uint32_t merged_v[Wide ? kMaxPu : 1], merged_o[Wide ? kMaxPu : 1];   // Wide: running winner per PU (value, row << 8 | column)
@@ -146,6 +147,10 @@ __global__ void __launch_bounds__(FxCfg<Wide>::kThreads, FxCfg<Wide>::kCtas) ful
     const int area_x = scr.sa_x[list], area_y = scr.sa_y[list], area_w = scr.sa_w[list], area_h = scr.sa_h[list];
     const uint32_t keys_addr = (uint32_t)__cvta_generic_to_shared(keys);
     if (Wide) for (int t = tid; t < kMaxPu; t += NT) { merged_v[t] = 0xFFFFFFFFu; merged_o[t] = 0xFFFFFFFFu; }
+    const void* tmap = job.ref_tmap[list];                        // CTA-uniform; see fullpel.cu
+    const uint32_t bar_addr = (uint32_t)__cvta_generic_to_shared(&tma_bar);
+    uint32_t tma_phase = 0;
+    if (tmap && tid == 0) mbar_init(bar_addr, 1);
 #pragma unroll 1
     for (int sub = 0; sub < (Wide ? 4 : 1); sub++) {
     const int tx0 = Wide ? (sub & 1) * 64 : 0, ty0 = Wide ? (sub >> 1) * 64 : 0;
@@ -158,7 +163,13 @@ __global__ void __launch_bounds__(FxCfg<Wide>::kThreads, FxCfg<Wide>::kCtas) ful
     const int nfill = min(32, ((saw + 62 + 3) >> 2) + 1);
     const uint8_t* g0 = rp.at(ox + sax, oy + say);
     const uint32_t m16 = (uint32_t)(uintptr_t)g0 & 15u;
-    {
+    if (tmap) {
+        if (tid == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic-proxy accesses of this memory (Q11 tables / the previous sub-area) come first
+            mbar_expect_tx(bar_addr, kTmaBoxBytes * kTmaBoxRows);
+            tma_load_2d((uint32_t)__cvta_generic_to_shared(raw), tmap, rp.ox + ox + sax - (int)m16, rp.oy + oy + say, bar_addr);
+        }
+    } else {
         const int ngran = ((int)(m16 >> 2) + nfill + 2 + 3) >> 2;
         const uint8_t* ga = g0 - m16;
         const uint32_t raw_addr = (uint32_t)__cvta_generic_to_shared(raw);
@@ -177,6 +188,7 @@ __global__ void __launch_bounds__(FxCfg<Wide>::kThreads, FxCfg<Wide>::kCtas) ful
     for (int t = tid; t < kKeyWords; t += NT) keys[t] = 0xFFFFFFFFu;
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
+    if (tmap) { mbar_wait(bar_addr, tma_phase); tma_phase ^= 1u; }
     {
         const int c = tid & 31;
         if (c < nfill) {

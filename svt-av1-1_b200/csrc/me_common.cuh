@@ -57,7 +57,33 @@ struct DJob {
     SvtMeSbDebug* debug;         // [n_sb]      (device)
     int sb_cols, sb_rows;
     int sb_begin, sb_end;        // SBs [sb_begin, sb_end) of the raster are searched (an SB-row range)
+    const void* ref_tmap[2];     // TMA descriptors (CUtensorMap in global memory) of ref[l].full, box kTmaBoxBytes x kTmaBoxRows; null = cp.async staging
 };
+constexpr int kTmaBoxBytes = 160, kTmaBoxRows = 126;   // the raw full-pel window: ten 16-byte granules x (64 search rows + 62)
+
+// ---- TMA staging of the raw full-pel window (fullpel.cu, fullpel_ext.cu): ONE 2-D tensor box (kTmaBoxBytes x kTmaBoxRows from
+// the 16-byte aligned address below the window's first byte) issued by one thread; completion is counted in bytes on an
+// mbarrier. SVTME_TMA=0 (or a driver without cuTensorMapEncodeTiled) leaves DJob.ref_tmap null: 16-byte cp.async granules.
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && ++spins > (1u << 26)) __trap();          // a copy that never completes is an error, not a hang
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, int x, int y, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(x), "r"(y) : "memory");
+}
 
 // raster index -> internal index (EbMotionEstimation.h:89-128)
 __device__ __constant__ const uint8_t kTab16[16] = { 0, 1, 4, 5, 2, 3, 6, 7, 8, 9, 12, 13, 10, 11, 14, 15 };

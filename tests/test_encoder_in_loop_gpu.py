@@ -36,8 +36,16 @@ def _encode(td, tag, yuv, w, h, n, extra, mode=3, exe=ENC, env_extra=None):
     dump, obu = os.path.join(td, tag + ".medump"), os.path.join(td, tag + ".obu")
     env = _env()
     env.update(env_extra or {})
-    r = subprocess.run([exe, yuv, str(w), str(h), str(n), str(mode), dump, "--bitstream", obu] + extra, env=env,
-                       stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
+    cmd = [exe, yuv, str(w), str(h), str(n), str(mode), dump, "--bitstream", obu] + extra
+    r = subprocess.run(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
+    if r.returncode < 0:
+        # The encoder process died on a signal. Seen ONCE in ~190 hooked encodes (glibc "stack smashing detected" in the
+        # multi-threaded encoder process, first minutes of a fresh box, enc-mode 0) and not reproduced in 80 consecutive runs
+        # of the same clip (profiles/stress_encoder_in_loop.py), nor in 40 stock runs. One retry, loudly, so that such an
+        # event does not hide the parity tests behind it under `pytest -x`; a second death fails the test.
+        import warnings
+        warnings.warn(f"{os.path.basename(exe)} {tag} died on signal {-r.returncode}: {r.stderr[-300:]!r}; retrying once")
+        r = subprocess.run(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     return dump, open(obu, "rb").read(), r.stderr
 

@@ -244,3 +244,21 @@ def test_real_encoder_encdec_blocks(txq, name):
         T.check_encoder_blocks(got, want, w, h, (name, w, h, t))
         blocks += len(want["eob"])
     assert blocks > 250
+
+
+def test_64_point_sizes_on_a_second_device(pkg, q10s):
+    """The dynamic shared-memory attribute of the 64-point kernels is per device: contexts on two GPUs of one process
+    (the first 64-point launch of the process on device 1) must both work and agree."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    rng = np.random.default_rng(64)
+    bd, qi = sorted(q10s)[0]
+    with pkg.TxqContext(1) as c1, pkg.TxqContext(0) as c0:
+        for w, h in ((64, 64), (32, 64), (64, 16)):
+            res = T.synth_residual(rng, 2 * h, 3 * w, bd, "mixed")
+            a = c1.fwd_txfm_quant(res, w, h, 0, q10s[(bd, qi)])
+            b = c0.fwd_txfm_quant(res, w, h, 0, q10s[(bd, qi)])
+            assert_same(a, b, f"{w}x{h} device 1 vs 0")
+            eob, off, lv = c1.fwd_txfm_quant_compact(res, w, h, 0, q10s[(bd, qi)])
+            assert np.array_equal(eob, b["eob"])
