@@ -203,27 +203,35 @@ __global__ void __launch_bounds__(256, TxqGeom<TXW, TXH, ENERGY>::MIN_CTAS) txq_
 #pragma unroll
     for (int j = tid; j < B * ROWS; j += 256) {
         const int slot = j / ROWS, r = j % ROWS;
-        if (slot >= n_here) continue;
-        int32_t* row = smem_txq + j * PITCH;                  // == slot * SLOT + r * PITCH
-        int32_t y[TXW];
+        unsigned long long dropped = 0;
+        if (slot < n_here) {
+            int32_t* row = smem_txq + j * PITCH;                  // == slot * SLOT + r * PITCH
+            int32_t y[TXW];
 #pragma unroll
-        for (int c = 0; c < TXW; c++) y[c] = row[c];
-        txfm1d<TXW, CR>(a.hk == K_FLIPADST ? K_ADST : a.hk, y);
+            for (int c = 0; c < TXW; c++) y[c] = row[c];
+            txfm1d<TXW, CR>(a.hk == K_FLIPADST ? K_ADST : a.hk, y);
 #pragma unroll
-        for (int c = 0; c < (ENERGY ? TXW : PW); c++) {
-            if (shift2(TXW, TXH)) y[c] = rshift_round(y[c], shift2(TXW, TXH));
-            if (RECT) y[c] = mul_sqrt2(y[c]);
+            for (int c = 0; c < (ENERGY ? TXW : PW); c++) {
+                if (shift2(TXW, TXH)) y[c] = rshift_round(y[c], shift2(TXW, TXH));
+                if (RECT) y[c] = mul_sqrt2(y[c]);
+            }
+            if (G::BIG && ENERGY) {                                     // HandleTransform64x64_c & co: energy of what is dropped
+#pragma unroll
+                for (int c = 0; c < TXW; c++)
+                    if (c >= PW || r >= PH) dropped += (unsigned long long)((long long)y[c] * (long long)y[c]);
+            }
+            if (r < PH) {
+#pragma unroll
+                for (int c = 0; c < PW; c++) row[c] = y[c];
+            }
         }
-        if (G::BIG && ENERGY) {                                         // HandleTransform64x64_c & co: energy of what is dropped
-            unsigned long long dropped = 0;
+        if (G::BIG && ENERGY) {
+            // the rows of a block sit on consecutive lanes (B * ROWS is a multiple of 256, so every lane of the warp is here):
+            // one shared 64-bit atomic per warp and block instead of one per row (64 rows contending for the same word)
+            constexpr int RW = ROWS < 32 ? ROWS : 32;
 #pragma unroll
-            for (int c = 0; c < TXW; c++)
-                if (c >= PW || r >= PH) dropped += (unsigned long long)((long long)y[c] * (long long)y[c]);
-            if (dropped) atomicAdd(&s_energy[slot], dropped);
-        }
-        if (r < PH) {
-#pragma unroll
-            for (int c = 0; c < PW; c++) row[c] = y[c];
+            for (int o = RW / 2; o > 0; o >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, o);
+            if ((tid & (RW - 1)) == 0 && dropped) atomicAdd(&s_energy[slot], dropped);
         }
     }
     __syncthreads();
