@@ -839,6 +839,18 @@ def run_gpu_impl(args, rank, world, local_rank):
                           "against": cpu["kind"] + " (whole 40-byte me_results rows of every SB and PU, CRC per picture)",
                           "ok": n_res == n_want and n_e2e == n_want}
     checksum = int(out.view(torch.int32).sum(dtype=torch.int64).item()) if rank == 0 else 0
+    # ---- side product of the ME process (outside the timed regions): zero-motion SADs of the 120 consecutive picture pairs of
+    # the resident pictures (svtme_zz_sad = ComputeDecimatedZzSad), one batched launch + 2 x 510 bytes back per pair
+    zz_sad = None
+    if rank == 0 and not USE_16BIT:
+        pairs = [(i, i - 1) for i in range(1, N_PICS)]
+        ctx.zz_sad(pairs)
+        t0 = time.perf_counter()
+        zz, nm = ctx.zz_sad(pairs)
+        dt = time.perf_counter() - t0
+        zz_sad = {"pairs": len(pairs), "us_per_picture_pair": dt / len(pairs) * 1e6, "launches": 1,
+                  "classes": {str(int(k)): int(v) for k, v in zip(*np.unique(zz, return_counts=True))},
+                  "note": "host wall clock of one synchronous call for all pairs: one launch (512 bytes read per SB) and one copy of 2 bytes per SB"}
     ctx.close()
     del dev
     strong_1080p = strong_4k = peer_parity = None
@@ -916,6 +928,7 @@ def run_gpu_impl(args, rank, world, local_rank):
             "kernel_launches_per_step": {k: v[1] / args.steps for k, v in kt.items()},
             "clocks": clocks, "result_checksum": checksum, "parity_checked": parity_checked,
             "strong_1080p": strong_1080p, "strong_4k": strong_4k, "peer_parity": peer_parity,
+            "zz_sad": zz_sad,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu

@@ -200,6 +200,21 @@ int32_t svtme_join(SvtMeContext *ctx);
 #define SVTME_STATIC_MAX_SBS 256
 int32_t svtme_motion_estimate_static(SvtMeContext *ctx, const SvtMeJob *job);
 
+/* ---- side product of the ME process: zero-motion SADs ---------------------------------------------------------------
+ * Replaces ComputeDecimatedZzSad (EbMotionEstimationProcess.c:219-349, called per ME segment at :585-603 when look-ahead
+ * is on and picture_number > 0): for every complete 64x64 SB the 16x16 SAD between the current picture's sixteenth plane
+ * and the previous picture (display order) sampled every fourth pixel -- both planes are already resident in the slots'
+ * pyramids -- classified into zz_cost (BEA_CLASS_*: 0 / 3 / 10 / 20 / 30, incomplete SBs 255) and non_moving_index
+ * (0 / 10 / 20 / 30). The reference stores both in the PREVIOUS picture's control set (zz_cost_array,
+ * non_moving_index_array); here they are host arrays of one byte per SB in raster order. Either pointer may be NULL.
+ * Synchronous: the arrays are filled when the call returns. */
+typedef struct SvtMeZzJob {
+    int32_t  cur_slot, prev_slot;
+    uint8_t *zz_cost;              /* [num_sb] */
+    uint8_t *non_moving_index;     /* [num_sb] */
+} SvtMeZzJob;
+int32_t svtme_zz_sad(SvtMeContext *ctx, const SvtMeZzJob *jobs, int32_t n_jobs);
+
 /* Introspection for benchmarks: the CUDA stream (cudaStream_t as void*) and the number of kernel
  * launches issued so far. */
 void   *svtme_stream(SvtMeContext *ctx);

@@ -853,3 +853,36 @@ void meo_unpack16(const uint16_t *in, int32_t in_stride, uint8_t *msb, int32_t m
             if (rem) rem[(size_t)y * rem_stride + x] = q9 ? (uint8_t)(v & 3) : (uint8_t)(v << 6);
         }
 }
+
+
+/* ---- ComputeDecimatedZzSad (EbMotionEstimationProcess.c:219-349) ---------------------------------------------------
+ * For every COMPLETE 64x64 SB: the previous picture's SB is decimated on the fly (Decimation2D with step 4: sample
+ * (4x, 4y), EbPictureAnalysisProcess.c:100-125) and compared with the same SB of the current sixteenth picture by the plain
+ * 16x16 SAD (NxMSadKernel_funcPtrArray[asm][2] = Compute16xMSad_AVX2_INTRIN: every row, no quirk). Thresholds:
+ * BEA_CLASS_*_DEC_TH = 256, 512, 1024, 2048 -> zz cost 0, 3, 10, 20, 30 (EbDefinitions.h:2770-2790); the non-moving index
+ * uses (sb_w / 4) * (sb_h / 4) * {2, 4, 8} -> 0, 10, 20, 30. Incomplete SBs: cost 255, SAD = ~0 -> index 30. */
+void meo_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, const MeoPyramid *prev,
+                        uint8_t *zz_cost, uint8_t *non_moving_index) {
+    const int w_sb = (width + 63) / 64, h_sb = (height + 63) / 64;
+    for (int ys = 0; ys < h_sb; ys++)
+        for (int xs = 0; xs < w_sb; xs++) {
+            const int sb = xs + ys * w_sb, ox = xs * 64, oy = ys * 64;
+            const int sb_w = width - ox < 64 ? width - ox : 64, sb_h = height - oy < 64 ? height - oy : 64;
+            uint32_t sad = 0;
+            if (sb_w == 64 && sb_h == 64) {
+                const MeoPlane *c = &cur->sixteenth, *p = &prev->full;
+                for (int y = 0; y < 16; y++)
+                    for (int x = 0; x < 16; x++) {
+                        const int a = c->buf[(size_t)(c->origin_y + (oy >> 2) + y) * c->stride + c->origin_x + (ox >> 2) + x];
+                        const int b = p->buf[(size_t)(p->origin_y + oy + 4 * y) * p->stride + p->origin_x + ox + 4 * x];
+                        sad += (uint32_t)(a > b ? a - b : b - a);
+                    }
+                zz_cost[sb] = sad < 256 ? 0 : sad < 512 ? 3 : sad < 1024 ? 10 : sad < 2048 ? 20 : 30;
+            } else {
+                zz_cost[sb] = 255;
+                sad = ~0u;
+            }
+            const uint32_t area = (uint32_t)((sb_w >> 2) * (sb_h >> 2));
+            non_moving_index[sb] = sad < area * 2 ? 0 : sad < area * 4 ? 10 : sad < area * 8 ? 20 : 30;
+        }
+}

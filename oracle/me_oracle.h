@@ -110,6 +110,15 @@ int ref_motion_estimate_picture(const MeoParams *params, const MeoPyramid *cur,
                                 const MeoPyramid *ref0, const MeoPyramid *ref1,
                                 MeoPuResult *results, MeoSbDebug *debug);
 
+/* Zero-motion SADs of one picture against the previous picture in display order (ComputeDecimatedZzSad,
+ * EbMotionEstimationProcess.c:219-349): per SB the 16x16 SAD between the current sixteenth picture and the previous FULL
+ * picture sampled every fourth pixel, classified into zz_cost[num_sb] and non_moving_index[num_sb] (both belong to the
+ * PREVIOUS picture's control set in the reference). Incomplete SBs get INVALID_ZZ_COST / class 3. */
+void meo_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, const MeoPyramid *prev,
+                        uint8_t *zz_cost, uint8_t *non_moving_index);
+int  ref_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, const MeoPyramid *prev,
+                        uint8_t *zz_cost, uint8_t *non_moving_index);
+
 #ifdef __cplusplus
 }
 #endif

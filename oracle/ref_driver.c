@@ -210,6 +210,47 @@ int ref_motion_estimate_picture(const MeoParams *prm, const MeoPyramid *cur,
     return 0;
 }
 
+/* ComputeDecimatedZzSad of the reference on one picture pair: the minimum of SCS / PCS / context it reads. */
+extern EbErrorType ComputeDecimatedZzSad(MotionEstimationContext_t *, SequenceControlSet_t *, PictureParentControlSet_t *,
+                                         EbPictureBufferDesc_t *, uint32_t, uint32_t, uint32_t, uint32_t);
+int ref_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, const MeoPyramid *prev,
+                       uint8_t *zz_cost, uint8_t *non_moving_index) {
+    ensure_memory_map();
+    const uint32_t w_sb = (width + 63) / 64, h_sb = (height + 63) / 64, n_sb = w_sb * h_sb;
+    SequenceControlSet_t *scs = (SequenceControlSet_t *)calloc(1, sizeof(SequenceControlSet_t));
+    EncodeContext_t *enc = (EncodeContext_t *)calloc(1, sizeof(EncodeContext_t));
+    PictureParentControlSet_t *pcs = (PictureParentControlSet_t *)calloc(1, sizeof(PictureParentControlSet_t));
+    PictureParentControlSet_t *prev_pcs = (PictureParentControlSet_t *)calloc(1, sizeof(PictureParentControlSet_t));
+    MotionEstimationContext_t *mctx = (MotionEstimationContext_t *)calloc(1, sizeof(MotionEstimationContext_t));
+    EbObjectWrapper_t prev_wrapper; memset(&prev_wrapper, 0, sizeof(prev_wrapper));
+    enc->asm_type = ASM_AVX2;
+    scs->encode_context_ptr = enc;
+    scs->luma_width = (uint16_t)width; scs->luma_height = (uint16_t)height; scs->sb_sz = 64;
+    scs->picture_width_in_sb = (uint8_t)w_sb; scs->picture_height_in_sb = (uint8_t)h_sb;
+    scs->sb_params_array = (SbParams_t *)calloc(n_sb, sizeof(SbParams_t));
+    for (uint32_t i = 0; i < n_sb; i++) {                      /* sb_params_init, EbSequenceControlSet.c:395-420 */
+        SbParams_t *sp = &scs->sb_params_array[i];
+        sp->origin_x = (uint16_t)((i % w_sb) * 64); sp->origin_y = (uint16_t)((i / w_sb) * 64);
+        sp->width = (uint8_t)(width - sp->origin_x < 64 ? width - sp->origin_x : 64);
+        sp->height = (uint8_t)(height - sp->origin_y < 64 ? height - sp->origin_y : 64);
+        sp->is_complete_sb = (uint8_t)(sp->width == 64 && sp->height == 64);
+    }
+    static MeContext_t *ctx = NULL;
+    if (!ctx && MeContextCtor(&ctx) != EB_ErrorNone) return -1;
+    mctx->me_context_ptr = ctx;
+    EbPictureBufferDesc_t prev_full, cur16;
+    plane_to_desc(&prev->full, &prev_full);
+    plane_to_desc(&cur->sixteenth, &cur16);
+    prev_pcs->enhanced_picture_ptr = &prev_full;
+    prev_pcs->zz_cost_array = zz_cost;
+    prev_pcs->non_moving_index_array = non_moving_index;
+    prev_wrapper.objectPtr = prev_pcs;
+    pcs->previous_picture_control_set_wrapper_ptr = &prev_wrapper;
+    const EbErrorType rc = ComputeDecimatedZzSad(mctx, scs, pcs, &cur16, 0, w_sb, 0, h_sb);
+    free(scs->sb_params_array); free(mctx); free(prev_pcs); free(pcs); free(enc); free(scs);
+    return rc == EB_ErrorNone ? 0 : -1;
+}
+
 /* Reference values of the search-area parameters (set_me_hme_params_oq + the L0 multiplier tables),
  * used to pin meo_default_params(). */
 void ref_default_params(MeoParams *p, int32_t width, int32_t height, int32_t num_lists,

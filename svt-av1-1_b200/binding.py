@@ -15,6 +15,7 @@ EXPORTED_SYMBOLS = (
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
     "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
     "svtme_pictures_upload_device", "svtme_pictures_upload", "svtme_motion_estimate_static", "svtme_rc_me_distortion",
+    "svtme_zz_sad",
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
                         "svtme_lcu_motion_estimate", "svtme_lcu_session_stats", "svtme_lcu_motion_estimate_segment")
@@ -50,6 +51,10 @@ class SvtMeJob(C.Structure):
     _fields_ = [("cur_slot", C.c_int32), ("ref0_slot", C.c_int32), ("ref1_slot", C.c_int32),
                 ("sb_row_begin", C.c_int32), ("sb_row_end", C.c_int32), ("range_in_sbs", C.c_int32),
                 ("params", SvtMeParams), ("results", C.c_void_p), ("debug", C.c_void_p)]
+
+
+class SvtMeZzJob(C.Structure):
+    _fields_ = [("cur_slot", C.c_int32), ("prev_slot", C.c_int32), ("zz_cost", C.c_void_p), ("non_moving_index", C.c_void_p)]
 
 
 PU_RESULT_DTYPE = np.dtype([("xMvL0", "<i2"), ("yMvL0", "<i2"), ("xMvL1", "<i2"), ("yMvL1", "<i2"),
@@ -112,6 +117,8 @@ def load_library():
     lib.svtme_motion_estimate_static.argtypes = [C.c_void_p, C.POINTER(SvtMeJob)]
     lib.svtme_rc_me_distortion.restype = C.c_uint32
     lib.svtme_rc_me_distortion.argtypes = [C.c_void_p]
+    lib.svtme_zz_sad.restype = C.c_int32
+    lib.svtme_zz_sad.argtypes = [C.c_void_p, C.POINTER(SvtMeZzJob), C.c_int32]
     lib.svtme_synchronize.restype = C.c_int32
     lib.svtme_synchronize.argtypes = [C.c_void_p]
     lib.svtme_synchronize_uploads.restype = C.c_int32
@@ -276,6 +283,17 @@ class MeContext:
         jobs, results, debug = self.make_jobs([spec], want_debug, sb_rows=sb_rows)
         self._check(self.lib.svtme_motion_estimate_static(self._h, C.byref(jobs[0])), "svtme_motion_estimate_static")
         return results, debug
+
+    def zz_sad(self, pairs):
+        """svtme_zz_sad for (cur_slot, prev_slot) pairs: arrays [len(pairs)][num_sb] of zz cost and non-moving index."""
+        n = len(pairs)
+        zz, nm = np.zeros((n, self.n_sb), np.uint8), np.zeros((n, self.n_sb), np.uint8)
+        jobs = (SvtMeZzJob * n)()
+        for i, (c, p) in enumerate(pairs):
+            jobs[i].cur_slot, jobs[i].prev_slot = c, p
+            jobs[i].zz_cost, jobs[i].non_moving_index = zz[i].ctypes.data, nm[i].ctypes.data
+        self._check(self.lib.svtme_zz_sad(self._h, jobs, n), "svtme_zz_sad")
+        return zz, nm
 
     def motion_estimate_async(self, jobs):
         self._check(self.lib.svtme_motion_estimate_async(self._h, jobs, len(jobs)), "svtme_motion_estimate_async")

@@ -65,6 +65,8 @@ struct SvtMeContext {
     int device = 0, width = 0, height = 0, sb_cols = 0, sb_rows = 0, n_sb = 0;
     cudaStream_t stream = nullptr, copy_in = nullptr, copy_out = nullptr;
     uint8_t* d_tmaps = nullptr;           // SVTME_TMA=1: one 128-byte CUtensorMap per slot (its padded full plane)
+    uint8_t* d_zz = nullptr;              // svtme_zz_sad: [cap] ZzJob, then [cap][2][n_sb] output bytes
+    int zz_cap = 0;
     cudaEvent_t join_ev = nullptr;
     // chunked submission: a small batch (one mini-GOP: a handful of waves per kernel) is cut into two chunks of pictures that
     // run their kernel sequences on two streams, so the tail of one chunk's kernel is filled by the other chunk's CTAs.
@@ -289,6 +291,7 @@ void svtme_destroy(SvtMeContext* ctx) {
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); if (s.ready_ipc) cudaEventDestroy(s.ready_ipc); }
     cudaFree(ctx->d_tmaps);
+    cudaFree(ctx->d_zz);
     cudaFree(ctx->d_in16); cudaFree(ctx->d_rem);
     for (auto e : ctx->peer_events) cudaEventDestroy(e);
     for (auto& kv : ctx->ipc_open) { cudaIpcCloseMemHandle(kv.second.first); cudaEventDestroy(kv.second.second); }
@@ -726,6 +729,44 @@ int32_t svtme_join(SvtMeContext* ctx) {
     CU(cudaStreamWaitEvent(ctx->stream, ctx->join_ev, 0));
     CU(cudaEventRecord(ctx->join_ev, ctx->copy_out));
     CU(cudaStreamWaitEvent(ctx->stream, ctx->join_ev, 0));
+    return SVTME_OK;
+}
+
+/* ComputeDecimatedZzSad, EbMotionEstimationProcess.c:219-349 (kernel: zz_sad.cu) */
+int32_t svtme_zz_sad(SvtMeContext* ctx, const SvtMeZzJob* jobs, int32_t n_jobs) {
+    if (!ctx || !jobs || n_jobs <= 0) return ctx ? fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_zz_sad: bad parameter") : SVTME_ERR_BAD_PARAMETER;
+    const int n_slots = (int)ctx->slots.size();
+    for (int i = 0; i < n_jobs; i++)
+        if (jobs[i].cur_slot < 0 || jobs[i].cur_slot >= n_slots || jobs[i].prev_slot < 0 || jobs[i].prev_slot >= n_slots)
+            return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_zz_sad: slot out of range");
+    CU(cudaSetDevice(ctx->device));
+    const size_t jobs_bytes = align_up(sizeof(ZzJob) * (size_t)n_jobs, 256), out_per_job = 2 * (size_t)ctx->n_sb;
+    if (n_jobs > ctx->zz_cap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_zz); ctx->d_zz = nullptr; ctx->zz_cap = 0;
+        CU(cudaMalloc(&ctx->d_zz, jobs_bytes + out_per_job * (size_t)n_jobs));
+        ctx->zz_cap = n_jobs;
+    }
+    uint8_t* d_out = ctx->d_zz + align_up(sizeof(ZzJob) * (size_t)ctx->zz_cap, 256);
+    std::vector<ZzJob> h((size_t)n_jobs);
+    for (int i = 0; i < n_jobs; i++) {
+        h[i].cur16 = ctx->slots[jobs[i].cur_slot].pyr.sixteenth;
+        h[i].prev16 = ctx->slots[jobs[i].prev_slot].pyr.sixteenth;
+        h[i].out = d_out + out_per_job * (size_t)i;
+        for (int sl : { jobs[i].cur_slot, jobs[i].prev_slot }) CU(cudaStreamWaitEvent(ctx->stream, ctx->slots[sl].ready, 0));
+    }
+    CU(cudaMemcpyAsync(ctx->d_zz, h.data(), sizeof(ZzJob) * (size_t)n_jobs, cudaMemcpyHostToDevice, ctx->stream));
+    launch_zz_sad(reinterpret_cast<const ZzJob*>(ctx->d_zz), n_jobs, ctx->width, ctx->height, ctx->sb_cols, ctx->n_sb, ctx->stream);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    // one copy for the whole batch (two bytes per SB), scattered into the callers' arrays on the host
+    std::vector<uint8_t> host(out_per_job * (size_t)n_jobs);
+    CU(cudaMemcpyAsync(host.data(), d_out, host.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));               // synchronous by contract; the slots are free to be rewritten afterwards
+    for (int i = 0; i < n_jobs; i++) {
+        if (jobs[i].zz_cost) memcpy(jobs[i].zz_cost, host.data() + out_per_job * (size_t)i, (size_t)ctx->n_sb);
+        if (jobs[i].non_moving_index) memcpy(jobs[i].non_moving_index, host.data() + out_per_job * (size_t)i + ctx->n_sb, (size_t)ctx->n_sb);
+    }
     return SVTME_OK;
 }
 

@@ -191,6 +191,9 @@ void launch_fullpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool e
 // sequence until it has run (the small-window sub-pel pass defers the SBs whose window does not fit to a second pass)
 void launch_subpel(const DJob* d_jobs, int n_jobs, int max_sb, int list, bool ext, bool wide, uint32_t* worklist, cudaStream_t st);
 void launch_bipred_pack(const DJob* d_jobs, int n_jobs, int max_sb, bool ext, cudaStream_t st);
+// zero-motion SADs (zz_sad.cu): one job = one (current, previous) picture pair
+struct ZzJob { DPlane cur16, prev16; uint8_t* out; };        // out: [2][n_sb] (zz cost, non-moving index), device
+void launch_zz_sad(const ZzJob* d_jobs, int n_jobs, int width, int height, int sb_cols, int n_sb, cudaStream_t st);
 cudaError_t configure_kernels();
 
 }  // namespace svtme

@@ -154,6 +154,18 @@ def motion_estimate(lib, prefix, params, cur, ref0, ref1=None, want_debug=True):
     return res, dbg
 
 
+def zz_sad(lib, prefix, width, height, cur, prev):
+    """ComputeDecimatedZzSad of one picture pair: (zz_cost, non_moving_index), one byte per SB."""
+    n_sb = ((width + 63) // 64) * ((height + 63) // 64)
+    zz, nm = np.full(n_sb, 77, np.uint8), np.full(n_sb, 77, np.uint8)
+    f = getattr(lib, prefix + "_zz_sad_picture")
+    f.restype = C.c_int if prefix == "ref" else None
+    rc = f(width, height, C.byref(cur.c), C.byref(prev.c), zz.ctypes.data, nm.ctypes.data)
+    if prefix == "ref" and rc != 0:
+        raise RuntimeError(f"ref_zz_sad_picture -> {rc}")
+    return zz, nm
+
+
 def synth_video(width, height, n_frames, seed=0, noise=3.0, max_shift=24, contrast=1.0):
     """Deterministic synthetic luma: smooth texture + edges, per-region translation + noise.
 

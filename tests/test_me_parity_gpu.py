@@ -523,3 +523,36 @@ def test_sb_facade_call_shape(pkg, meo):
     for j, (cur, r0, r1, nl) in enumerate(pics):
         want, _ = M.motion_estimate(meo, "meo", M.convert_params(M.MeoParams, prms[j]), pyr[cur], pyr[r0], pyr[r1] if nl == 2 else None)
         assert M.results_diff(got[j], want, nl) == [], j
+
+
+@pytest.mark.parametrize("w,h", [(416, 240), (256, 192), (64, 64), (200, 72), (1920, 1080)])
+def test_zz_sad_matches_oracle(pkg, meo, w, h):
+    """svtme_zz_sad (ComputeDecimatedZzSad): a batch of picture pairs -- still, slow, fast and saturating content -- against
+    the oracle; incomplete SBs carry INVALID_ZZ_COST; a second call (buffers reused) gives the same bytes."""
+    synths = [dict(noise=0.0, max_shift=0), dict(noise=0.6, max_shift=1), dict(noise=1.5, max_shift=3),
+              dict(noise=12.0, contrast=4.0, max_shift=60)]
+    frames = []
+    for seed, synth in enumerate(synths):
+        fr = M.synth_video(w, h, 2, seed=seed + w, **synth)
+        if seed == 0:
+            fr[1] = fr[0].copy()
+        frames += fr
+    ctx = pkg.MeContext(w, h, len(frames))
+    try:
+        for i, f in enumerate(frames):
+            ctx.upload(i, f)
+        pairs = [(2 * k + 1, 2 * k) for k in range(len(synths))]
+        zz, nm = ctx.zz_sad(pairs)
+        zz2, nm2 = ctx.zz_sad(pairs[:2])
+        with pytest.raises(pkg.SvtMeError):
+            ctx.zz_sad([(0, len(frames))])
+    finally:
+        ctx.close()
+    pyr = [M.build_pyramid(meo, "meo", f) for f in frames]
+    for k, (c, p) in enumerate(pairs):
+        wz, wn = M.zz_sad(meo, "meo", w, h, pyr[c], pyr[p])
+        assert np.array_equal(zz[k], wz) and np.array_equal(nm[k], wn), k
+    assert np.array_equal(zz2, zz[:2]) and np.array_equal(nm2, nm[:2])
+    assert not zz[0][zz[0] != 255].any() and not nm[0][zz[0] != 255].any()       # the still pair
+    if w % 64 or h % 64:
+        assert (zz == 255).any() and (nm[zz == 255] == 30).all()

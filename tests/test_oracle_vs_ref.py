@@ -168,3 +168,25 @@ def test_unpack16_matches_reference(libs, w, h):
     assert np.array_equal(a[0], (v >> 2).astype(np.uint8))
     if w not in (32, 64):                                        # quirk Q9 lives in those two special cases only
         assert np.array_equal(a[1], ((v & 3) << 6).astype(np.uint8))
+
+
+@pytest.mark.parametrize("w,h", [(416, 240), (256, 192), (64, 64), (200, 72), (1368, 128), (720, 480)])
+def test_zz_sad_matches_reference(libs, w, h):
+    """ComputeDecimatedZzSad (EbMotionEstimationProcess.c:219-349): zero-motion SAD classes of every SB, complete and
+    incomplete, for still, slowly and quickly moving content (all five cost classes occur)."""
+    meo, ref = libs
+    seen = set()
+    for seed, synth in enumerate([dict(noise=0.0, max_shift=0), dict(noise=0.6, max_shift=1), dict(noise=1.5, max_shift=3),
+                                  dict(noise=3.0, max_shift=24), dict(noise=12.0, contrast=4.0, max_shift=60)]):
+        fr = M.synth_video(w, h, 2, seed=seed + w, **synth)
+        if seed == 0:
+            fr[1] = fr[0].copy()                                   # a still pair: class 0 everywhere
+        po = [M.build_pyramid(meo, "meo", f) for f in fr]
+        zo, no = M.zz_sad(meo, "meo", w, h, po[1], po[0])
+        zr, nr = M.zz_sad(ref, "ref", w, h, po[1], po[0])
+        assert np.array_equal(zo, zr) and np.array_equal(no, nr)
+        seen |= set(zo.tolist())
+    if w >= 256 and w % 64 == 0:
+        assert {0, 30} <= seen
+    if w % 64 or h % 64:
+        assert 255 in seen                                         # INVALID_ZZ_COST of the incomplete SBs
