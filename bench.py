@@ -805,7 +805,7 @@ def run_gpu_impl(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-    ctx.set_profiling(True)
+    ctx.set_profiling(not os.environ.get("SVTME_BENCH_NO_KERNEL_TIMES"))    # per-kernel events keep every batch on one stream
     ctx.kernel_times(reset=True)
     l0 = ctx.kernel_launches
     tl0 = txq["ctx"].kernel_launches() if txq else 0
@@ -869,7 +869,7 @@ def run_gpu_impl(args, rank, world, local_rank):
         total_kernel_ms = sum(v[0] for v in kt.values())
         # algorithmic work of one full-pel launch: every SB of every picture of the batch, one list
         sads_per_launch = fullpel_byte_sads_per_sb_list() * n_sb * len(jobs)
-        achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n else None
+        achieved = sads_per_launch / (fp_ms / fp_n / 1e3) / 1e12 if fp_n and fp_ms else None
         sb_cols_, n_sb_pic, full_rows_sb = (W + 63) // 64, ((W + 63) // 64) * ((H + 63) // 64), (H // 64) * ((W + 63) // 64)
         step_sads = (1 if SHARD_SB_ROWS else world) * sum(
             sp[3].num_lists * (fullpel_byte_sads_per_sb_list() * n_sb_pic + hme_byte_sads_per_sb_list(sp[3]) * full_rows_sb) for sp in specs)
@@ -915,8 +915,8 @@ def run_gpu_impl(args, rank, world, local_rank):
                          "launch_ms": fp_ms / fp_n if fp_n else None, "share_of_kernel_time": fp_ms / total_kernel_ms if total_kernel_ms else None},
             # one launch builds the pyramids of the whole sequence: bytes of all N_PICS pictures over the launches' time
             "roofline_hbm": {"kernel": "pyramid_flat_kernel", "bound": "hbm", "pictures_per_launch": N_PICS * args.steps / py_n if py_n else None,
-                             "achieved": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9) if py_n else None,
-                             "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9 / hbm_peak) if py_n else None,
+                             "achieved": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9) if py_n and py_ms else None,
+                             "peak": hbm_peak, "unit": "GB/s", "frac": (pyr_bytes * N_PICS * args.steps / (py_ms / 1e3) / 1e9 / hbm_peak) if py_n and py_ms else None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
             # the whole step against the same peak: HME + full-pel byte-SADs of every (picture, SB, list) over the step time
             # (the sub-pel / bi-pred arithmetic is not counted, so this under-states the work done)

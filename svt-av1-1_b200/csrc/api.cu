@@ -73,6 +73,7 @@ struct SvtMeContext {
     // SVTME_CHUNKS overrides (1 = never); large batches and profiled runs (per-kernel event times) stay on one stream.
     static constexpr int kChunkStreams = 8;
     int chunks = 0;                       // 0 = automatic
+    int chunk_streams = 2;                // streams the chunks alternate on
     cudaStream_t cstream[kChunkStreams] = {};
     cudaEvent_t fork_ev = nullptr, cjoin_ev[kChunkStreams] = {};
     std::vector<Slot> slots;
@@ -196,7 +197,9 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     if (const char* e = getenv("SVTME_CHUNKS")) ctx->chunks = std::max(0, std::min(atoi(e), 64));
     if (ctx->chunks != 1) {
         CU(cudaEventCreateWithFlags(&ctx->fork_ev, cudaEventDisableTiming));
-        for (int i = 0; i < (ctx->chunks ? std::min(ctx->chunks, (int)SvtMeContext::kChunkStreams) : 2); i++) {
+        ctx->chunk_streams = ctx->chunks ? std::min(ctx->chunks, (int)SvtMeContext::kChunkStreams) : 2;
+        if (const char* e2 = getenv("SVTME_CHUNK_STREAMS")) ctx->chunk_streams = std::max(1, std::min(atoi(e2), ctx->chunk_streams));
+        for (int i = 0; i < ctx->chunk_streams; i++) {
             CU(cudaStreamCreateWithFlags(&ctx->cstream[i], cudaStreamNonBlocking));
             CU(cudaEventCreateWithFlags(&ctx->cjoin_ev[i], cudaEventDisableTiming));
         }
@@ -660,7 +663,7 @@ int32_t svtme_motion_estimate_async(SvtMeContext* ctx, const SvtMeJob* jobs, int
     CU(cudaMemcpyAsync(b.d_jobs, b.h_jobs, sizeof(DJob) * n_jobs, cudaMemcpyHostToDevice, ctx->stream));
     const int n_chunks = ctx->profiling ? 1 : ctx->chunks ? std::min(ctx->chunks, n_jobs) : (n_jobs >= 2 && n_jobs <= 16) ? 2 : 1;
     if (n_chunks > 1) CU(cudaEventRecord(ctx->fork_ev, ctx->stream));
-    const int n_cs = std::min(n_chunks, (int)SvtMeContext::kChunkStreams);
+    const int n_cs = std::min(n_chunks, ctx->chunk_streams);
     for (int i = 0; i < (n_chunks > 1 ? n_cs : 0); i++) CU(cudaStreamWaitEvent(ctx->cstream[i], ctx->fork_ev, 0));
     for (int c = 0; c < n_chunks; c++) {
         const int j0 = (int)((int64_t)n_jobs * c / n_chunks), j1 = (int)((int64_t)n_jobs * (c + 1) / n_chunks), nj = j1 - j0;
