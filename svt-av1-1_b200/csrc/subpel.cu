@@ -15,6 +15,7 @@
 // The wrapping SSD is  dp4a.s8.s8(t,t)  with t = per-byte (a-b) mod 256; the true SSD is dp4a.u8.u8
 // of VABSDIFF4; SAD is VABSDIFF4.ACC.
 #include "me_common.cuh"
+#include "pack.cuh"
 
 namespace svtme {
 
@@ -516,17 +517,29 @@ __device__ __forceinline__ bool subpel_sb(const DJob& job, const int sb, const i
         asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
 
-    // ---- final uni-prediction blocks of this list for every PU level (consumed by bipred_pack_kernel)
+    // ---- final uni-prediction blocks of this list for every PU level. List 0 stores them (one 64x64 byte image per level);
+    // list 1 meets them again right here: bi-prediction SAD(src, (p0 + p1 + 1) >> 1) per 8x8 block while its own blocks are in
+    // registers, then the PU rows are ordered and packed (pack.cuh) -- the list-1 blocks never travel through memory and the
+    // separate bi-prediction kernel only remains for pictures with one list (BiPredictionSearch, ME.c:4933-5342, 6973-7146).
     if (p.num_lists == 2) {
+        uint32_t* part = &sh.sum_ssd[0][0];                     // [NLEV][64] bi-prediction SADs; the candidate sums are dead by now
+        static_assert(9 * NPU >= NLEV * 64, "part[] fits the candidate sums");
+        if (list == 1) __syncthreads();                         // every thread is done with sum_ssd; the source SB has landed for all
         for (int t = tid; t < NLEV * 64; t += kSpThreads) {
             const int blk = t & 63, L = t >> 6, bx = blk & 7, by = blk >> 3;
             const uint32_t mv = sh.pu_mv[block_pu(L, bx, by)];
             const int xm = mv_x(mv), ym = mv_y(mv);
             const int8_t* f = kFrac[(xm & 3) + ((ym & 3) << 2)];
             const int X = kMargin + (xm >> 2) - sax + bx * 8, Y = kMargin + (ym >> 2) - say + by * 8;
-            uint8_t* pred = scr.pred[list][L < kNumLevels ? L : 0];
-            if constexpr (Ext) { if (L >= kNumLevels) pred = job.scratch_ext[sb].pred[list][L - kNumLevels]; }
-            uint32_t* dst = reinterpret_cast<uint32_t*>(pred) + (by * 8) * 16 + bx * 2;
+            uint8_t* pred = scr.pred[0][L < kNumLevels ? L : 0];
+            if constexpr (Ext) { if (L >= kNumLevels) pred = job.scratch_ext[sb].pred[0][L - kNumLevels]; }
+            uint32_t* dst = reinterpret_cast<uint32_t*>(pred) + (by * 8) * 16 + bx * 2;      // list 0: written; list 1: list 0's block, read
+            uint32_t p0[16];
+            if (list == 1) {
+#pragma unroll
+                for (int r = 0; r < 8; r++) { p0[2 * r] = dst[r * 16]; p0[2 * r + 1] = dst[r * 16 + 1]; }
+            }
+            uint32_t sad = 0;
 #pragma unroll
             for (int r = 0; r < 8; r++) {
                 uint2 c = load8(sh.plane[f[0]], sh.rowoff, Y + f[2] + r, X + f[1]);
@@ -534,7 +547,30 @@ __device__ __forceinline__ bool subpel_sb(const DJob& job, const int sb, const i
                     const uint2 d = load8(sh.plane[f[3]], sh.rowoff, Y + f[5] + r, X + f[4]);
                     c.x = __vavgu4(c.x, d.x); c.y = __vavgu4(c.y, d.y);
                 }
-                dst[r * 16] = c.x; dst[r * 16 + 1] = c.y;
+                if (list == 0) { dst[r * 16] = c.x; dst[r * 16 + 1] = c.y; }
+                else {
+                    const uint2 sv = *reinterpret_cast<const uint2*>(&sh.src[(by * 8 + r) * 16 + bx * 2]);
+                    sad = sad4(sv.x, __vavgu4(p0[2 * r], c.x), sad);
+                    sad = sad4(sv.y, __vavgu4(p0[2 * r + 1], c.y), sad);
+                }
+            }
+            if (list == 1) part[t] = sad;
+        }
+        if (list == 1) {
+            __syncthreads();
+            if (tid < NPU) {
+                // list 0 from the scratch the earlier kernels wrote, list 1 from this CTA's shared state (the same values it just stored)
+                auto best_sad = [&](int l, int n) -> uint32_t {
+                    if (l == 1) return sh.pu_sad[n];
+                    if constexpr (Ext) { if (n >= kNumPu) return job.scratch_ext[sb].best_sad[0][n - kNumPu]; }
+                    return scr.best_sad[0][n];
+                };
+                auto best_mv = [&](int l, int n) -> uint32_t {
+                    if (l == 1) return sh.pu_mv[n];
+                    if constexpr (Ext) { if (n >= kNumPu) return job.scratch_ext[sb].best_mv[0][n - kNumPu]; }
+                    return scr.best_mv[0][n];
+                };
+                pack_pu_result<Ext>(job, sb, tid, part, best_sad, best_mv);
             }
         }
     }
