@@ -22,7 +22,6 @@ __global__ void __launch_bounds__(kBpThreads) bipred_pack_kernel(const DJob* __r
     const SvtMeParams& p = job.prm;
     if ((p.num_pus == kMaxPu) != Ext) return;
     const int tid = threadIdx.x;
-    const int ox = (sb % job.sb_cols) * 64, oy = (sb / job.sb_cols) * 64;
     const SbScratch& scr = job.scratch[sb];
 
     // Pictures with two lists were packed by the list-1 pass of the sub-pel kernel (it computes the bi-prediction SADs while the

@@ -160,6 +160,7 @@ def zz_sad(lib, prefix, width, height, cur, prev):
     zz, nm = np.full(n_sb, 77, np.uint8), np.full(n_sb, 77, np.uint8)
     f = getattr(lib, prefix + "_zz_sad_picture")
     f.restype = C.c_int if prefix == "ref" else None
+    f.argtypes = [C.c_int32, C.c_int32, C.POINTER(MeoPyramid), C.POINTER(MeoPyramid), C.c_void_p, C.c_void_p]   # (without them ctypes passes addresses as 32-bit ints)
     rc = f(width, height, C.byref(cur.c), C.byref(prev.c), zz.ctypes.data, nm.ctypes.data)
     if prefix == "ref" and rc != 0:
         raise RuntimeError(f"ref_zz_sad_picture -> {rc}")
