@@ -188,7 +188,7 @@ int32_t svtme_join(SvtMeContext *ctx);
 /* Allocation-free variant of svtme_motion_estimate for ONE picture in the 85-PU mode. It has no counterpart in the
  * reference: it was added for callers that cannot call cudaMalloc (code under
  * CUDA graph capture, tight serving loops, harnesses that forbid it). The job table, the inter-kernel SB scratch, the
- * result rows and the debug rows live in ONE file-scope device array of the library (about 10 MB, resident on every
+ * result rows and the debug rows live in ONE file-scope device array of the library (about 6 MB, resident on every
  * GPU that loads the library until the process exits) instead of the context's cudaMalloc'ed batch ring; the call
  * itself calls no cudaMalloc / cudaFree / cudaMallocHost and creates no stream or event. The caller still passes the
  * inputs (pictures uploaded into the context's slots beforehand) and the outputs (job->results / job->debug, host

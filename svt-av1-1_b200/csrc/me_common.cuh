@@ -38,14 +38,14 @@ struct SbScratch {
     int32_t  hme_x[3][2][2], hme_y[3][2][2];         // per-region HME centres of list 0, inherited by list 1 (quirk Q7)
     uint32_t best_sad[2][kNumPu];                    // internal (z-order) PU index, like p_sb_best_sad
     uint32_t best_mv[2][kNumPu];
-    uint8_t  pred[2][4][64 * 64];                    // final uni-pred blocks per list and PU size level
+    uint8_t  pred[4][64 * 64];                       // final list-0 uni-prediction blocks per PU size level (read by the list-1 sub-pel pass: bi-prediction)
 };
 
 // Extra state of the 209-PU mode: the non-square PUs (internal index 85..208) and their uni-prediction blocks.
 struct SbScratchExt {
     uint32_t best_sad[2][kNumNsq];
     uint32_t best_mv[2][kNumNsq];
-    uint8_t  pred[2][kMaxLevels - kNumLevels][64 * 64];
+    uint8_t  pred[kMaxLevels - kNumLevels][64 * 64];         // list 0 only, as in SbScratch
 };
 
 struct DJob {

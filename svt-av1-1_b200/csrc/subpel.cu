@@ -531,8 +531,8 @@ __device__ __forceinline__ bool subpel_sb(const DJob& job, const int sb, const i
             const int xm = mv_x(mv), ym = mv_y(mv);
             const int8_t* f = kFrac[(xm & 3) + ((ym & 3) << 2)];
             const int X = kMargin + (xm >> 2) - sax + bx * 8, Y = kMargin + (ym >> 2) - say + by * 8;
-            uint8_t* pred = scr.pred[0][L < kNumLevels ? L : 0];
-            if constexpr (Ext) { if (L >= kNumLevels) pred = job.scratch_ext[sb].pred[0][L - kNumLevels]; }
+            uint8_t* pred = scr.pred[L < kNumLevels ? L : 0];
+            if constexpr (Ext) { if (L >= kNumLevels) pred = job.scratch_ext[sb].pred[L - kNumLevels]; }
             uint32_t* dst = reinterpret_cast<uint32_t*>(pred) + (by * 8) * 16 + bx * 2;      // list 0: written; list 1: list 0's block, read
             uint32_t p0[16];
             if (list == 1) {
