@@ -119,6 +119,27 @@ void meo_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, co
 int  ref_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, const MeoPyramid *prev,
                         uint8_t *zz_cost, uint8_t *non_moving_index);
 
+/* ---- open-loop intra search of the ME process (ois_oracle.c; the row that comes next, no CUDA path yet) -------------
+ * OpenLoopIntraSearchLcu (EbMotionEstimation.c:8047-8365) for every SB. Per CU (raster-scan CU index 1..84 = the ME
+ * pu_index of the same square) the candidate array sorted_ois_candidate[cu][] and total_intra_luma_mode[cu]; both start
+ * from zero here and in the reference driver, so whole arrays compare. */
+typedef struct MeoOisCand { uint32_t distortion; uint8_t mode, valid, pad[2]; } MeoOisCand;
+typedef struct MeoOisCu { MeoOisCand cand[18]; uint8_t total, pad[3]; } MeoOisCu;
+typedef struct MeoOisParams {
+    int32_t width, height;
+    int32_t slice_type;            /* 0 = I, 1 = P, 2 = B */
+    int32_t temporal_layer_index, is_used_as_reference;
+    int32_t cu8x8_mode;            /* 1 = no 8x8 CUs */
+    int32_t input_resolution;      /* 0..3, 3 = INPUT_SIZE_4K_RANGE */
+    int32_t limit_ois_to_dc;       /* enc-mode >= 6 only; kept for completeness */
+    int32_t enc_mode;              /* read in ONE place: the valid flag of a stage-1 winner 'vertical' (quirk, see ois_oracle.c) */
+} MeoOisParams;
+void meo_ois_picture(const MeoOisParams *prm, const MeoPlane *pic, const uint32_t *me_sad, MeoOisCu *out);
+int  ref_ois_picture(const MeoOisParams *prm, const MeoPlane *pic, const uint32_t *me_sad, MeoOisCu *out);
+/* one prediction (n x n, mode 0..34) of the CU at (x0, y0) into pred64 (stride 64) + its SAD against the source */
+uint32_t meo_ois_predict_cu(const MeoPlane *pic, int32_t x0, int32_t y0, int32_t n, int32_t mode, uint8_t *pred64);
+uint32_t ref_ois_predict_cu(const MeoPlane *pic, int32_t x0, int32_t y0, int32_t n, int32_t mode, uint8_t *pred64);
+
 #ifdef __cplusplus
 }
 #endif

@@ -251,6 +251,96 @@ int ref_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, con
     return rc == EB_ErrorNone ? 0 : -1;
 }
 
+/* ---- OpenLoopIntraSearchLcu of the reference on one picture: the minimum of SCS / PCS / context it reads ------------- */
+#include "EbIntraPrediction.h"
+extern EbErrorType OpenLoopIntraSearchLcu(PictureParentControlSet_t *, uint32_t, MotionEstimationContext_t *, EbPictureBufferDesc_t *, EbAsm);
+static MotionEstimationContext_t *ois_context(void) {
+    static MotionEstimationContext_t *mctx = NULL;
+    if (!mctx) {
+        ensure_memory_map();
+        mctx = (MotionEstimationContext_t *)calloc(1, sizeof(MotionEstimationContext_t));
+        if (MeContextCtor(&mctx->me_context_ptr) != EB_ErrorNone) return NULL;
+        if (IntraOpenLoopReferenceSamplesCtor(&mctx->intra_ref_ptr) != EB_ErrorNone) return NULL;
+    }
+    return mctx;
+}
+uint32_t ref_ois_predict_cu(const MeoPlane *pic, int32_t x0, int32_t y0, int32_t n, int32_t mode, uint8_t *pred64) {
+    ensure_memory_map();
+    MotionEstimationContext_t *mctx = ois_context();
+    EbPictureBufferDesc_t in;
+    plane_to_desc(pic, &in);
+    UpdateNeighborSamplesArrayOpenLoop(mctx->intra_ref_ptr, &in, in.strideY, (uint32_t)x0, (uint32_t)y0, (uint32_t)n);
+    memset(mctx->me_context_ptr->sb_buffer, 0, 64 * 64);
+    IntraPredictionOpenLoop((uint32_t)n, mctx, (uint32_t)mode, ASM_AVX2);
+    memcpy(pred64, mctx->me_context_ptr->sb_buffer, 64 * 64);
+    return (uint32_t)NxMSadKernel_funcPtrArray[ASM_AVX2][n >> 3](
+        &in.bufferY[(in.origin_y + y0) * in.strideY + in.origin_x + x0], in.strideY, mctx->me_context_ptr->sb_buffer, 64, (uint32_t)n, (uint32_t)n);
+}
+int ref_ois_picture(const MeoOisParams *prm, const MeoPlane *pic, const uint32_t *me_sad, MeoOisCu *out) {
+    ensure_memory_map();
+    MotionEstimationContext_t *mctx = ois_context();
+    if (!mctx) return -1;
+    const uint32_t w_sb = (prm->width + 63) / 64, h_sb = (prm->height + 63) / 64, n_sb = w_sb * h_sb;
+    SequenceControlSet_t *scs = (SequenceControlSet_t *)calloc(1, sizeof(SequenceControlSet_t));
+    EncodeContext_t *enc = (EncodeContext_t *)calloc(1, sizeof(EncodeContext_t));
+    PictureParentControlSet_t *pcs = (PictureParentControlSet_t *)calloc(1, sizeof(PictureParentControlSet_t));
+    EbObjectWrapper_t scs_wrapper; memset(&scs_wrapper, 0, sizeof(scs_wrapper));
+    enc->asm_type = ASM_AVX2;
+    scs->encode_context_ptr = enc;
+    scs->luma_width = (uint16_t)prm->width; scs->luma_height = (uint16_t)prm->height; scs->sb_sz = 64;
+    scs->input_resolution = (EbInputResolution)prm->input_resolution;
+    scs->picture_width_in_sb = (uint8_t)w_sb; scs->picture_height_in_sb = (uint8_t)h_sb;
+    scs->sb_params_array = (SbParams_t *)calloc(n_sb, sizeof(SbParams_t));
+    for (uint32_t i = 0; i < n_sb; i++) {                      /* sb_params_init, EbSequenceControlSet.c:395-440 */
+        SbParams_t *sp = &scs->sb_params_array[i];
+        sp->origin_x = (uint16_t)((i % w_sb) * 64); sp->origin_y = (uint16_t)((i / w_sb) * 64);
+        sp->width = (uint8_t)(prm->width - sp->origin_x < 64 ? prm->width - sp->origin_x : 64);
+        sp->height = (uint8_t)(prm->height - sp->origin_y < 64 ? prm->height - sp->origin_y : 64);
+        sp->is_complete_sb = (uint8_t)(sp->width == 64 && sp->height == 64);
+        for (uint32_t cu = 0; cu < CU_MAX_COUNT; cu++)
+            sp->raster_scan_cu_validity[cu] = (EbBool)(sp->origin_x + RASTER_SCAN_CU_X[cu] + RASTER_SCAN_CU_SIZE[cu] <= (uint32_t)prm->width &&
+                                                       sp->origin_y + RASTER_SCAN_CU_Y[cu] + RASTER_SCAN_CU_SIZE[cu] <= (uint32_t)prm->height);
+    }
+    scs_wrapper.objectPtr = scs;
+    pcs->sequence_control_set_wrapper_ptr = &scs_wrapper;
+    pcs->slice_type = prm->slice_type == 0 ? I_SLICE : prm->slice_type == 1 ? P_SLICE : B_SLICE;
+    pcs->temporal_layer_index = (uint8_t)prm->temporal_layer_index;
+    pcs->is_used_as_reference_flag = (EbBool)prm->is_used_as_reference;
+    pcs->cu8x8_mode = (uint8_t)prm->cu8x8_mode;
+    pcs->limit_ois_to_dc_mode_flag = (EbBool)prm->limit_ois_to_dc;
+    pcs->enc_mode = (EbEncMode)prm->enc_mode;
+    pcs->ois_cu32_cu16_results = (OisCu32Cu16Results_t **)calloc(n_sb, sizeof(void *));
+    pcs->ois_cu8_results = (OisCu8Results_t **)calloc(n_sb, sizeof(void *));
+    pcs->me_results = (MeCuResults_t **)calloc(n_sb, sizeof(MeCuResults_t *));
+    OisCandidate_t *c32 = (OisCandidate_t *)calloc((size_t)n_sb * 21 * 18, sizeof(OisCandidate_t));
+    OisCandidate_t *c8 = (OisCandidate_t *)calloc((size_t)n_sb * 64 * 18, sizeof(OisCandidate_t));
+    for (uint32_t i = 0; i < n_sb; i++) {
+        pcs->ois_cu32_cu16_results[i] = (OisCu32Cu16Results_t *)calloc(1, sizeof(OisCu32Cu16Results_t));
+        pcs->ois_cu8_results[i] = (OisCu8Results_t *)calloc(1, sizeof(OisCu8Results_t));
+        for (int cu = 0; cu < 21; cu++) pcs->ois_cu32_cu16_results[i]->sorted_ois_candidate[cu] = c32 + ((size_t)i * 21 + cu) * 18;
+        for (int cu = 0; cu < 64; cu++) pcs->ois_cu8_results[i]->sorted_ois_candidate[cu] = c8 + ((size_t)i * 64 + cu) * 18;
+        pcs->me_results[i] = (MeCuResults_t *)calloc(85, sizeof(MeCuResults_t));
+        if (me_sad) for (int pu = 0; pu < 85; pu++) pcs->me_results[i][pu].distortionDirection[0].distortion = me_sad[(size_t)i * 85 + pu];
+    }
+    EbPictureBufferDesc_t in;
+    plane_to_desc(pic, &in);
+    for (uint32_t i = 0; i < n_sb; i++) OpenLoopIntraSearchLcu(pcs, i, mctx, &in, ASM_AVX2);
+    for (uint32_t i = 0; i < n_sb; i++) {
+        for (int cu = 1; cu < 85; cu++) {
+            const OisCandidate_t *src = cu < 21 ? pcs->ois_cu32_cu16_results[i]->sorted_ois_candidate[cu] : pcs->ois_cu8_results[i]->sorted_ois_candidate[cu - 21];
+            MeoOisCu *o = &out[(size_t)i * 85 + cu];
+            for (int k = 0; k < 18; k++) {
+                o->cand[k].distortion = src[k].distortion; o->cand[k].mode = (uint8_t)src[k].intra_mode; o->cand[k].valid = (uint8_t)src[k].valid_distortion;
+            }
+            o->total = cu < 21 ? pcs->ois_cu32_cu16_results[i]->total_intra_luma_mode[cu] : pcs->ois_cu8_results[i]->total_intra_luma_mode[cu - 21];
+        }
+        free(pcs->ois_cu32_cu16_results[i]); free(pcs->ois_cu8_results[i]); free(pcs->me_results[i]);
+    }
+    free(c32); free(c8); free(pcs->ois_cu32_cu16_results); free(pcs->ois_cu8_results); free(pcs->me_results);
+    free(scs->sb_params_array); free(pcs); free(enc); free(scs);
+    return 0;
+}
+
 /* Reference values of the search-area parameters (set_me_hme_params_oq + the L0 multiplier tables),
  * used to pin meo_default_params(). */
 void ref_default_params(MeoParams *p, int32_t width, int32_t height, int32_t num_lists,
