@@ -215,6 +215,35 @@ typedef struct SvtMeZzJob {
 } SvtMeZzJob;
 int32_t svtme_zz_sad(SvtMeContext *ctx, const SvtMeZzJob *jobs, int32_t n_jobs);
 
+/* ---- side product of the ME process: open-loop intra search ----------------------------------------------------------
+ * Replaces the OIS loop of MotionEstimationKernel (EbMotionEstimationProcess.c:559-583): OpenLoopIntraSearchLcu
+ * (EbMotionEstimation.c:8047-8365) for every SB of a resident picture. Per SB and raster-scan CU index 1..84 (4 x 32x32,
+ * 16 x 16x16, 64 x 8x8; the index equals the ME pu_index of the same square) the reference leaves
+ * sorted_ois_candidate[cu][0..17] and total_intra_luma_mode[cu]; `cand` receives the byte images of those OisCandidate_t
+ * (bit 0-19 distortion, bit 20 valid_distortion, bit 24-31 intra_mode; EbCodingUnit.h:303-313) and `total` the counts.
+ * Entries the reference does not write for a CU (it leaves the previous picture's values there) are zero; index 0 of every
+ * SB (the 64x64 CU, never searched) is zero. me_sad: the best ME distortion per square PU of the same picture,
+ * me_results[sb][pu].distortionDirection[0].distortion, [num_sb][85]; read for inter pictures above temporal layer 0 (and
+ * for every inter picture at 4K), may be NULL otherwise. Synchronous. */
+typedef struct SvtMeOisParams {
+    int32_t slice_type;                 /* 0 = I, 1 = P, 2 = B */
+    int32_t temporal_layer_index, is_used_as_reference;
+    int32_t cu8x8_mode;                 /* pcs->cu8x8_mode: 1 = no 8x8 CUs on inter pictures */
+    int32_t input_resolution;           /* scs->input_resolution, 3 = INPUT_SIZE_4K_RANGE */
+    int32_t limit_ois_to_dc;            /* pcs->limit_ois_to_dc_mode_flag */
+    int32_t enc_mode;                   /* pcs->enc_mode (one quirk of the reference reads it) */
+} SvtMeOisParams;
+#define SVTME_OIS_CUS        85
+#define SVTME_OIS_CANDIDATES 18
+typedef struct SvtMeOisJob {
+    int32_t         slot;
+    SvtMeOisParams  params;
+    const uint32_t *me_sad;             /* [num_sb][85] or NULL */
+    uint32_t       *cand;               /* [num_sb][85][18] */
+    uint8_t        *total;              /* [num_sb][85] */
+} SvtMeOisJob;
+int32_t svtme_ois(SvtMeContext *ctx, const SvtMeOisJob *jobs, int32_t n_jobs);
+
 /* Introspection for benchmarks: the CUDA stream (cudaStream_t as void*) and the number of kernel
  * launches issued so far. */
 void   *svtme_stream(SvtMeContext *ctx);

@@ -7,7 +7,7 @@ package only carries a thin ctypes binding used by the tests and by ``bench.py``
 fallback: loading fails loudly when the library has not been built, and ``MeContext`` raises when no
 CUDA device is present.
 """
-from .binding import (MeContext, SvtMeError, SvtMeParams, SvtMeJob, SvtMeIpcSlot, PU_RESULT_DTYPE, SB_DEBUG_DTYPE, KERNEL_KINDS,  # noqa: F401
+from .binding import (MeContext, SvtMeError, SvtMeParams, SvtMeJob, SvtMeIpcSlot, SvtMeOisParams, PU_RESULT_DTYPE, SB_DEBUG_DTYPE, KERNEL_KINDS,  # noqa: F401
                       default_params, load_library, library_path, EXPORTED_SYMBOLS, LCU_EXPORTED_SYMBOLS, MeLcuSession,
                       SvtMeLcuPicture)
 from .txq_binding import TxqContext, SvtTxqQuant, TXQ_EXPORTED_SYMBOLS, TX_TYPES, supported as txq_supported, packed_dims  # noqa: F401,E402

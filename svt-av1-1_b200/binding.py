@@ -15,7 +15,7 @@ EXPORTED_SYMBOLS = (
     "svtme_kernel_launches", "svtme_set_profiling", "svtme_kernel_times", "svtme_join", "svtme_picture_upload_16bit",
     "svtme_picture_upload_peer", "svtme_slot_export", "svtme_picture_upload_ipc", "svtme_synchronize_uploads",
     "svtme_pictures_upload_device", "svtme_pictures_upload", "svtme_motion_estimate_static", "svtme_rc_me_distortion",
-    "svtme_zz_sad",
+    "svtme_zz_sad", "svtme_ois",
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
                         "svtme_lcu_motion_estimate", "svtme_lcu_session_stats", "svtme_lcu_motion_estimate_segment")
@@ -51,6 +51,15 @@ class SvtMeJob(C.Structure):
     _fields_ = [("cur_slot", C.c_int32), ("ref0_slot", C.c_int32), ("ref1_slot", C.c_int32),
                 ("sb_row_begin", C.c_int32), ("sb_row_end", C.c_int32), ("range_in_sbs", C.c_int32),
                 ("params", SvtMeParams), ("results", C.c_void_p), ("debug", C.c_void_p)]
+
+
+class SvtMeOisParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("slice_type", "temporal_layer_index", "is_used_as_reference", "cu8x8_mode",
+                                         "input_resolution", "limit_ois_to_dc", "enc_mode")]
+
+
+class SvtMeOisJob(C.Structure):
+    _fields_ = [("slot", C.c_int32), ("params", SvtMeOisParams), ("me_sad", C.c_void_p), ("cand", C.c_void_p), ("total", C.c_void_p)]
 
 
 class SvtMeZzJob(C.Structure):
@@ -117,6 +126,8 @@ def load_library():
     lib.svtme_motion_estimate_static.argtypes = [C.c_void_p, C.POINTER(SvtMeJob)]
     lib.svtme_rc_me_distortion.restype = C.c_uint32
     lib.svtme_rc_me_distortion.argtypes = [C.c_void_p]
+    lib.svtme_ois.restype = C.c_int32
+    lib.svtme_ois.argtypes = [C.c_void_p, C.POINTER(SvtMeOisJob), C.c_int32]
     lib.svtme_zz_sad.restype = C.c_int32
     lib.svtme_zz_sad.argtypes = [C.c_void_p, C.POINTER(SvtMeZzJob), C.c_int32]
     lib.svtme_synchronize.restype = C.c_int32
@@ -294,6 +305,23 @@ class MeContext:
             jobs[i].zz_cost, jobs[i].non_moving_index = zz[i].ctypes.data, nm[i].ctypes.data
         self._check(self.lib.svtme_zz_sad(self._h, jobs, n), "svtme_zz_sad")
         return zz, nm
+
+    def ois(self, specs):
+        """svtme_ois for (slot, SvtMeOisParams, me_sad or None) triples: (cand [n][num_sb][85][18] uint32 byte images of
+        OisCandidate_t, total [n][num_sb][85] uint8)."""
+        n = len(specs)
+        cand, total = np.zeros((n, self.n_sb, 85, 18), np.uint32), np.zeros((n, self.n_sb, 85), np.uint8)
+        jobs, keep = (SvtMeOisJob * n)(), []
+        for i, (slot, prm, me) in enumerate(specs):
+            jobs[i].slot, jobs[i].params = slot, prm
+            if me is not None:
+                me = np.ascontiguousarray(me, dtype=np.uint32)
+                assert me.shape == (self.n_sb, 85)
+                keep.append(me)
+                jobs[i].me_sad = me.ctypes.data
+            jobs[i].cand, jobs[i].total = cand[i].ctypes.data, total[i].ctypes.data
+        self._check(self.lib.svtme_ois(self._h, jobs, n), "svtme_ois")
+        return cand, total
 
     def motion_estimate_async(self, jobs):
         self._check(self.lib.svtme_motion_estimate_async(self._h, jobs, len(jobs)), "svtme_motion_estimate_async")

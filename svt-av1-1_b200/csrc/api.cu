@@ -67,6 +67,8 @@ struct SvtMeContext {
     uint8_t* d_tmaps = nullptr;           // SVTME_TMA=1: one 128-byte CUtensorMap per slot (its padded full plane)
     uint8_t* d_zz = nullptr;              // svtme_zz_sad: [cap] ZzJob, then [cap][2][n_sb] output bytes
     int zz_cap = 0;
+    uint8_t* d_ois = nullptr;             // svtme_ois: [cap] OisJob, then per job me_sad / cand / total
+    int ois_cap = 0;
     cudaEvent_t join_ev = nullptr;
     // chunked submission: a small batch (one mini-GOP: a handful of waves per kernel) is cut into two chunks of pictures that
     // run their kernel sequences on two streams, so the tail of one chunk's kernel is filled by the other chunk's CTAs.
@@ -295,6 +297,7 @@ void svtme_destroy(SvtMeContext* ctx) {
     for (auto& s : ctx->slots) { cudaFree(s.base); if (s.ready) cudaEventDestroy(s.ready); if (s.ready_ipc) cudaEventDestroy(s.ready_ipc); }
     cudaFree(ctx->d_tmaps);
     cudaFree(ctx->d_zz);
+    cudaFree(ctx->d_ois);
     cudaFree(ctx->d_in16); cudaFree(ctx->d_rem);
     for (auto e : ctx->peer_events) cudaEventDestroy(e);
     for (auto& kv : ctx->ipc_open) { cudaIpcCloseMemHandle(kv.second.first); cudaEventDestroy(kv.second.second); }
@@ -770,6 +773,52 @@ int32_t svtme_zz_sad(SvtMeContext* ctx, const SvtMeZzJob* jobs, int32_t n_jobs) 
         if (jobs[i].zz_cost) memcpy(jobs[i].zz_cost, host.data() + out_per_job * (size_t)i, (size_t)ctx->n_sb);
         if (jobs[i].non_moving_index) memcpy(jobs[i].non_moving_index, host.data() + out_per_job * (size_t)i + ctx->n_sb, (size_t)ctx->n_sb);
     }
+    return SVTME_OK;
+}
+
+/* OpenLoopIntraSearchLcu for every SB, EbMotionEstimation.c:8047-8365 (kernel: ois.cu) */
+int32_t svtme_ois(SvtMeContext* ctx, const SvtMeOisJob* jobs, int32_t n_jobs) {
+    if (!ctx || !jobs || n_jobs <= 0) return ctx ? fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_ois: bad parameter") : SVTME_ERR_BAD_PARAMETER;
+    static_assert(sizeof(SvtMeOisParams) == sizeof(ois::Params), "SvtMeOisParams mirrors ois::Params");
+    const int n_slots = (int)ctx->slots.size();
+    for (int i = 0; i < n_jobs; i++) {
+        const SvtMeOisParams& q = jobs[i].params;
+        const bool needs_me = q.slice_type != 0 && !(q.temporal_layer_index == 0 && q.input_resolution != 3) && !q.limit_ois_to_dc;
+        if (jobs[i].slot < 0 || jobs[i].slot >= n_slots || !jobs[i].cand || !jobs[i].total || q.slice_type < 0 || q.slice_type > 2 ||
+            q.temporal_layer_index < 0 || q.temporal_layer_index > 5 || (needs_me && !jobs[i].me_sad))
+            return fail(ctx, SVTME_ERR_BAD_PARAMETER, "svtme_ois: bad slot, parameters or missing buffer");
+    }
+    CU(cudaSetDevice(ctx->device));
+    const size_t cus = (size_t)ctx->n_sb * SVTME_OIS_CUS;
+    const size_t me_bytes = align_up(cus * 4, 256), cand_bytes = align_up(cus * SVTME_OIS_CANDIDATES * 4, 256), total_bytes = align_up(cus, 256);
+    const size_t per_job = me_bytes + cand_bytes + total_bytes;
+    if (n_jobs > ctx->ois_cap) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_ois); ctx->d_ois = nullptr; ctx->ois_cap = 0;
+        CU(cudaMalloc(&ctx->d_ois, align_up(sizeof(OisJob) * (size_t)n_jobs, 256) + per_job * (size_t)n_jobs));
+        ctx->ois_cap = n_jobs;
+    }
+    uint8_t* base = ctx->d_ois + align_up(sizeof(OisJob) * (size_t)ctx->ois_cap, 256);
+    std::vector<OisJob> h((size_t)n_jobs);
+    for (int i = 0; i < n_jobs; i++) {
+        uint8_t* b = base + per_job * (size_t)i;
+        h[i].plane = ctx->slots[jobs[i].slot].pyr.full;
+        memcpy(&h[i].prm, &jobs[i].params, sizeof(ois::Params));
+        h[i].me_sad = jobs[i].me_sad ? reinterpret_cast<const uint32_t*>(b) : nullptr;
+        h[i].out_cand = reinterpret_cast<uint32_t*>(b + me_bytes);
+        h[i].out_total = b + me_bytes + cand_bytes;
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->slots[jobs[i].slot].ready, 0));
+        if (jobs[i].me_sad) CU(cudaMemcpyAsync(b, jobs[i].me_sad, cus * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CU(cudaMemcpyAsync(ctx->d_ois, h.data(), sizeof(OisJob) * (size_t)n_jobs, cudaMemcpyHostToDevice, ctx->stream));
+    launch_ois(reinterpret_cast<const OisJob*>(ctx->d_ois), n_jobs, ctx->sb_cols, ctx->n_sb, ctx->stream);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    for (int i = 0; i < n_jobs; i++) {
+        CU(cudaMemcpyAsync(jobs[i].cand, h[i].out_cand, cus * SVTME_OIS_CANDIDATES * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaMemcpyAsync(jobs[i].total, h[i].out_total, cus, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CU(cudaStreamSynchronize(ctx->stream));               // synchronous by contract
     return SVTME_OK;
 }
 

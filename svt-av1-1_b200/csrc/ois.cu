@@ -1,0 +1,120 @@
+// ois.cu -- open-loop intra search of the ME process for every SB of a picture (OpenLoopIntraSearchLcu, reference
+// Source/Lib/Codec/EbMotionEstimation.c:8047-8365, called per ME segment at EbMotionEstimationProcess.c:559-583).
+//
+// One CTA (8 warps) per SB. Phase 1: the 84 CUs of the SB (4 x 32x32, 16 x 16x16, 64 x 8x8) are dealt to the warps; a warp
+// loads the CU's 4n + 1 neighbours from the source picture into shared memory, and for every mode the path asks for
+// (1, 7, 3..9 or all 35) the lanes predict the CU's pixels (ois_core.cuh: one formula per pixel, no prediction buffer),
+// take |src - pred| and reduce the SAD over the warp. Phase 2: one thread per CU turns the SADs into the reference's
+// candidate list (injected lists per stage-1 winner, best-18 selection + the reference's swap sort on layer-0 pictures) and
+// writes the byte image of OisCandidate_t. The reference's `bestMode` local survives from CU to CU; that only shows when no
+// mode of a CU beats the initial 32 * 32 * 255, which phase 2 resolves by looking back over the earlier CUs.
+// Work: sum of n^2 over the CUs = 12288 pixels per mode and SB; HBM traffic is the source SB + its border once (L2 serves the
+// re-reads), 6.2 KB of results per SB: the kernel is bound by ALU issue at ~35 modes x 12288 pixels x ~12 instructions.
+#include "me_common.cuh"
+#include "ois_core.cuh"
+
+namespace svtme {
+
+using namespace ois;
+
+constexpr int kOisThreads = 256;
+
+__global__ void __launch_bounds__(kOisThreads) ois_kernel(const OisJob* __restrict__ jobs, int sb_cols, int n_sb) {
+    __shared__ uint8_t s_r[8][132];                  // neighbour array of the warp's current CU
+    __shared__ uint8_t s_refbuf[8][104];             // main reference of the current angular mode: index 32 = top-left
+    __shared__ uint32_t s_sad[kCus][kNumModes];      // phase 1 -> phase 2 (inter path: [0..8] stage 1, [9] DC)
+    __shared__ int8_t s_point[kCus];                 // inter path: OIS point; -1 = the CU was not searched
+    __shared__ int8_t s_best[kCus];                  // stage-1 / intra winner of the CU, -1 = none found
+    const OisJob& job = jobs[blockIdx.y];
+    const int sb = blockIdx.x;
+    if (sb >= n_sb) return;
+    const Params q = job.prm;
+    const Picture pic = { job.plane.at(0, 0), job.plane.stride, job.plane.w, job.plane.h };
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ox = (sb % sb_cols) * 64, oy = (sb / sb_cols) * 64;
+    const bool all_modes = all_modes_path(q);
+    if (tid < kCus) { s_point[tid] = -1; s_best[tid] = -1; }
+    __syncthreads();
+
+    uint8_t* r = s_r[warp];
+    uint8_t* ref = s_refbuf[warp] + 32;
+    for (int cu = 1 + warp; cu < kCus; cu += 8) {
+        int cx, cy, n;
+        cu_geometry(cu, cx, cy, n);
+        const int x0 = ox + cx, y0 = oy + cy, lg = n == 8 ? 3 : n == 16 ? 4 : 5;
+        if (x0 + n > pic.w || y0 + n > pic.h) continue;                                  // raster_scan_cu_validity
+        if (q.slice_type != 0 && q.cu8x8_mode == 1 && n == 8) continue;
+        __syncwarp();
+        for (int i = lane; i <= 4 * n; i += 32) r[i] = (uint8_t)neighbour(pic, x0, y0, n, i);
+        __syncwarp();
+        int dc = 0;
+        {
+            int part = 0;
+            for (int i = lane; i < 2 * n; i += 32) part += i < n ? r[2 * n + 1 + i] : r[2 * n - 1 - (i - n)];
+            dc = (__reduce_add_sync(0xffffffffu, part) + n) >> (lg + 1);
+        }
+        const uint8_t* src = pic.pix + (size_t)y0 * pic.stride + x0;
+        auto mode_sad = [&](int mode) -> uint32_t {
+            if (mode >= 2) {
+                __syncwarp();
+                for (int i = ref_first(n, mode) + lane; i <= 2 * n; i += 32) ref[i] = (uint8_t)ref_sample(r, n, mode, i);
+                __syncwarp();
+            }
+            uint32_t part = 0;
+            for (int px = lane; px < n * n; px += 32) {
+                const int x = px & (n - 1), y = px >> lg;
+                const int d = (int)src[(size_t)y * pic.stride + x] - pred_pixel(r, ref, n, lg, mode, x, y, dc);
+                part += (uint32_t)(d < 0 ? -d : d);
+            }
+            return __reduce_add_sync(0xffffffffu, part);
+        };
+        if (q.slice_type == 0) {
+            if (n == 32) { const uint32_t s = mode_sad(kPlanar); if (lane == 0) s_sad[cu][0] = s; }
+            else for (int i = 0; i < 7; i++) { const uint32_t s = mode_sad(islice_mode(i)); if (lane == 0) s_sad[cu][i] = s; }
+            if (lane == 0) s_point[cu] = 0;
+        } else if (all_modes) {
+            for (int m = 0; m < kNumModes; m++) { const uint32_t s = mode_sad(m); if (lane == 0) s_sad[cu][m] = s; }
+            if (lane == 0) s_point[cu] = 0;
+        } else {
+            const uint32_t dcs = mode_sad(kDc);
+            int point = 0;
+            if (!q.limit_ois_to_dc) {
+                point = ois_point(q, job.me_sad[(size_t)sb * kCus + cu], dcs);
+                if (point) for (int i = 0; i < points_modes(point); i++) { const uint32_t s = mode_sad(stage1_mode(i)); if (lane == 0) s_sad[cu][i] = s; }
+            }
+            if (lane == 0) { s_sad[cu][9] = dcs; s_point[cu] = (int8_t)point; }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2a: the winner of every CU that ran a stage-1 / intra-picture search
+    const int cu = tid;
+    const bool searched = cu >= 1 && cu < kCus && s_point[cu] >= 0;
+    int cx = 0, cy = 0, n = 8;
+    if (cu >= 1 && cu < kCus) cu_geometry(cu, cx, cy, n);
+    if (searched) s_best[cu] = (int8_t)cu_winner(q, n, s_sad[cu], s_point[cu]);
+    __syncthreads();
+    if (cu < 1 || cu >= kCus) return;
+    // ---- phase 2b: candidate lists
+    uint32_t c[kMaxCand];
+    int total = 0;
+    if (searched) {
+        int bm = s_best[cu];
+        for (int k = cu - 1; bm < 0 && k >= 1; k--) bm = s_best[k];                      // the reference's local survives from CU to CU
+        if (bm < 0) bm = kPlanar;
+        total = build_lists(q, n, s_sad[cu], s_point[cu], bm, c);
+    } else {
+#pragma unroll
+        for (int i = 0; i < kMaxCand; i++) c[i] = 0;
+    }
+    uint32_t* out = job.out_cand + ((size_t)sb * kCus + cu) * kMaxCand;
+#pragma unroll
+    for (int i = 0; i < kMaxCand; i++) out[i] = c[i];
+    job.out_total[(size_t)sb * kCus + cu] = (uint8_t)total;
+}
+
+void launch_ois(const OisJob* d_jobs, int n_jobs, int sb_cols, int n_sb, cudaStream_t st) {
+    ois_kernel<<<dim3(n_sb, n_jobs), kOisThreads, 0, st>>>(d_jobs, sb_cols, n_sb);
+}
+
+}  // namespace svtme

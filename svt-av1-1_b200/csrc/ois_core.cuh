@@ -1,0 +1,210 @@
+// ois_core.cuh -- the arithmetic of the open-loop intra search (OpenLoopIntraSearchLcu, reference
+// Source/Lib/Codec/EbMotionEstimation.c:7419-8365; predictors EbIntraPrediction.c:3718-3800, 5230-5430 with the leaves of
+// ASM_AVX2/EbIntraPrediction_Intrinsic_AVX2.c) as small host/device functions: one neighbour sample, one sample of the
+// projected main reference, one predicted pixel, and the per-CU candidate-list rules. ois.cu maps them onto warps; the same
+// functions compile for the host (tests/host_emul/ois_emul.cpp), where a serial emulation of the kernel is checked against
+// the oracle without a GPU.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define OIS_HD __host__ __device__ __forceinline__
+#else
+#define OIS_HD static inline
+#endif
+
+namespace svtme {
+namespace ois {
+
+enum { kPlanar = 0, kDc = 1, kHor = 10, kVer = 26, kNumModes = 35, kMaxCand = 18, kCus = 85 };
+
+struct Picture { const uint8_t* pix; int stride, w, h; };          // pix = sample (0, 0) of the (padded) source plane
+
+struct Params {                                                     // what OpenLoopIntraSearchLcu reads from PCS / SCS
+    int32_t slice_type;            // 0 = I, 1 = P, 2 = B
+    int32_t temporal_layer_index, is_used_as_reference;
+    int32_t cu8x8_mode;            // 1: no 8x8 CUs on inter pictures
+    int32_t input_resolution;      // 3 = INPUT_SIZE_4K_RANGE
+    int32_t limit_ois_to_dc;
+    int32_t enc_mode;              // one quirk reads it (valid flag of a vertical stage-1 winner, ME.c:7604-7612)
+};
+
+// raster-scan CU index 1..84 -> position and size inside the SB
+OIS_HD void cu_geometry(int cu, int& x, int& y, int& n) {
+    if (cu < 5) { n = 32; x = ((cu - 1) & 1) * 32; y = ((cu - 1) >> 1) * 32; }
+    else if (cu < 21) { n = 16; x = ((cu - 5) & 3) * 16; y = ((cu - 5) >> 2) * 16; }
+    else { n = 8; x = ((cu - 21) & 7) * 8; y = ((cu - 21) >> 3) * 8; }
+}
+
+// Neighbour array r[0 .. 4n] of the CU at (x0, y0) (UpdateNeighborSamplesArrayOpenLoop, "regular" order):
+// r[0..2n-1] = left column bottom-up, r[2n] = top-left, r[2n+1..4n] = top row. Samples outside the picture are 128; the
+// left column / top row stop at the picture's bottom / right edge.
+OIS_HD int neighbour(const Picture& p, int x0, int y0, int n, int idx) {
+    if (idx < 2 * n) {
+        const int y = 2 * n - 1 - idx;
+        if (x0 == 0 || y0 + y >= p.h) return 128;
+        return p.pix[(long long)(y0 + y) * p.stride + x0 - 1];
+    }
+    if (idx == 2 * n) return (x0 != 0 && y0 != 0) ? p.pix[(long long)(y0 - 1) * p.stride + x0 - 1] : 128;
+    const int x = idx - 2 * n - 1;
+    if (y0 == 0 || x0 + x >= p.w) return 128;
+    return p.pix[(long long)(y0 - 1) * p.stride + x0 + x];
+}
+
+OIS_HD int angle_of(int mode) {
+    const int d = mode < 18 ? mode - 10 : mode - 26;                // distance from pure horizontal / vertical
+    const int m = d < 0 ? -d : d;
+    const int mag = m == 0 ? 0 : m == 1 ? 2 : m == 2 ? 5 : m == 3 ? 9 : m == 4 ? 13 : m == 5 ? 17 : m == 6 ? 21 : m == 7 ? 26 : 32;
+    return (mode < 18 ? -d : d) < 0 ? -mag : mag;                   // horizontal modes: 2 -> +32 ... 17 -> -26; vertical: 18 -> -32 ... 34 -> +32
+}
+OIS_HD int inv_angle_of(int mode) {                                 // only for the negative angles (modes 11..25)
+    const int d = mode < 18 ? mode - 10 : 26 - mode;                // 1..8
+    return d == 1 ? -4096 : d == 2 ? -1638 : d == 3 ? -910 : d == 4 ? -630 : d == 5 ? -482 : d == 6 ? -390 : d == 7 ? -315 : -256;
+}
+
+// Main reference of an angular mode: ref[i], i in [-n, 2n]; i = 0 is the top-left sample, i > 0 runs along the top row
+// (modes >= 18) or down the left column (modes < 18), i < 0 is the side reference projected by the inverse angle.
+OIS_HD int ref_sample(const uint8_t* r, int n, int mode, int i) {
+    const bool vertical = mode >= 18;
+    const uint8_t* left = r + 2 * n - 1;          // left[-y]: sample left of row y
+    const uint8_t* top = r + 2 * n + 1;           // top[x]; top[-1] = top-left
+    if (i >= 0) return vertical ? top[i - 1] : (i == 0 ? top[-1] : left[-(i - 1)]);
+    const int k = (i * inv_angle_of(mode) + 128) >> 8;
+    return vertical ? left[-(k - 1)] : top[k - 1];
+}
+OIS_HD int ref_first(int n, int mode) { const int a = angle_of(mode); return a < 0 ? (n * a) >> 5 : 0; }   // lowest index that is read
+
+OIS_HD int clip8(int v) { return v < 0 ? 0 : v > 255 ? 255 : v; }
+
+// One predicted pixel. r: the neighbour array; ref: the mode's main reference with ref[0] = top-left (angular modes only);
+// dc: (sum of the n top + n left neighbours + n) >> (log2 n + 1) (DC mode only).
+OIS_HD int pred_pixel(const uint8_t* r, const uint8_t* ref, int n, int lg, int mode, int x, int y, int dc) {
+    const uint8_t* left = r + 2 * n - 1;
+    const uint8_t* top = r + 2 * n + 1;
+    if (mode == kPlanar)
+        return ((n - 1 - x) * left[-y] + (x + 1) * top[n] + (n - 1 - y) * top[x] + (y + 1) * left[-n] + n) >> (lg + 1);
+    if (mode == kDc) {
+        if (n < 32) {
+            if (x == 0 && y == 0) return (left[0] + 2 * dc + top[0] + 2) >> 2;
+            if (y == 0) return (top[x] + 3 * dc + 2) >> 2;
+            if (x == 0) return (left[-y] + 3 * dc + 2) >> 2;
+        }
+        return dc;
+    }
+    const bool vertical = mode >= 18;
+    const int a = angle_of(mode);
+    if (a == 0 && n < 32) {                                          // boundary smoothing of the pure vertical / horizontal modes
+        if (vertical && x == 0) return clip8(top[0] + ((left[-y] - top[-1]) >> 1));
+        if (!vertical && y == 0) return clip8(left[0] + ((top[x] - top[-1]) >> 1));
+    }
+    const int j = vertical ? y : x, i = vertical ? x : y;
+    const int pos = (j + 1) * a, idx = pos >> 5, f = pos & 31;
+    return f ? ((32 - f) * ref[i + idx + 1] + f * ref[i + idx + 2] + 16) >> 5 : ref[i + idx + 1];
+}
+
+// ---- candidate lists (per CU, after the SADs) --------------------------------------------------------------------------
+OIS_HD uint32_t pack(uint32_t distortion, int valid, int mode) {     // byte image of OisCandidate_t (EbCodingUnit.h:303-313)
+    return (distortion & 0xFFFFFu) | ((uint32_t)(valid & 1) << 20) | ((uint32_t)mode << 24);
+}
+OIS_HD int islice_mode(int i) { return i == 0 ? kPlanar : i == 1 ? kDc : i == 2 ? kHor : i == 3 ? kVer : i == 4 ? 2 : i == 5 ? 18 : 34; }   // iSliceModesArray[0..6]
+OIS_HD int stage1_mode(int i) { return i == 0 ? kHor : i == 1 ? kVer : i == 2 ? 2 : i == 3 ? 18 : i == 4 ? 34 : i == 5 ? 6 : i == 6 ? 14 : i == 7 ? 22 : 30; }   // stage1ModesArray
+OIS_HD int points_modes(int point) { return 2 * point + 1; }          // numberOfOisModePoints = intraSearchInMd[point][depth 1..3] = 1, 3, 5, 7, 9
+
+// OIS point from the DC SAD and the ME SAD of the same square (GetInterIntraSadDistance + GetOisPoint, ME.c:7747-7826)
+OIS_HD int ois_point(const Params& q, uint32_t me, uint32_t dc_sad) {
+    const bool is_4k = q.input_resolution == 3;
+    const int set = is_4k ? ((q.temporal_layer_index == 0 || q.is_used_as_reference) ? 2 : 1) : 2;
+    const int tl = q.temporal_layer_index;
+    const int32_t diff = (int32_t)(me - dc_sad) * 100;
+    const int32_t dist = dc_sad ? diff / (int32_t)dc_sad : 0;
+    int t0, t1, t2, t3;                                               // OisPointTh[set][layer], ME.c:28-58
+    if (set == 2) { t0 = -400; t1 = -300; t2 = -200; t3 = 0; }
+    else if (set == 1) { t0 = tl < 2 ? -150 : tl == 2 ? -125 : -50; t1 = tl < 3 ? 0 : 50; t2 = tl < 2 ? 150 : tl == 2 ? 100 : 200; t3 = tl < 2 ? 200 : tl == 2 ? 150 : 300; }
+    else { t0 = -20; t1 = 50; t2 = tl < 2 ? 150 : tl == 2 ? 100 : 200; t3 = tl < 2 ? 200 : tl == 2 ? 150 : 300; }
+    if (dc_sad == 0 || me == 0 || dist <= t0) return 0;
+    return dist <= t1 ? 1 : dist <= t2 ? 2 : dist <= t3 ? 3 : 4;
+}
+
+// InjectIntraCandidatesBasedOnBestMode (ME.c:7525-7745): list k of the stage-1 winner `best`; slot = stage-1 index its SAD comes from
+OIS_HD int inject_mode(int best, int k) {
+    if (k == 0) return best;
+    if (k == 1) return kDc;
+    if (k == 2) return kPlanar;
+    const int j = k - 3;                                              // 0..5
+    switch (best) {
+    case 2:    return j < 3 ? 3 + j : 4 + j;                          // 3 4 5 7 8 9
+    case kHor: { const int t[6] = { 9, 11, 8, 12, 7, 13 }; return t[j]; }
+    case 18:   { const int t[6] = { 17, 19, 16, 20, 15, 21 }; return t[j]; }
+    case kVer: { const int t[6] = { 25, 27, 24, 28, 23, 29 }; return t[j]; }
+    case 34:   { const int t[6] = { 33, 32, 29, 31, 27, 28 }; return t[j]; }
+    case 6:    { const int t[6] = { 7, 5, 4, 8, 3, 9 }; return t[j]; }
+    case 14:   { const int t[6] = { 13, 15, 12, 16, 11, 17 }; return t[j]; }
+    case 22:   { const int t[6] = { 21, 23, 20, 24, 19, 25 }; return t[j]; }
+    default:   { const int t[6] = { 29, 31, 28, 32, 27, 33 }; return t[j]; }   // 30
+    }
+}
+OIS_HD int inject_slot(int best) { return best == kHor ? 0 : best == kVer ? 1 : best == 2 ? 2 : best == 18 ? 3 : best == 34 ? 4 : best == 6 ? 5 : best == 14 ? 6 : best == 22 ? 7 : 8; }
+OIS_HD int inject_canonical(int best) {                               // the switch's `default` is the list of mode 30
+    return (best == 2 || best == kHor || best == 18 || best == kVer || best == 34 || best == 6 || best == 14 || best == 22) ? best : 30;
+}
+
+// ---- phase 2 of a CU, shared by the kernel and its host emulation --------------------------------------------------------
+// sad: the CU's SAD row as phase 1 left it -- intra pictures: [i] = islice_mode(i) (32x32: [0] = planar only); layer-0 inter
+// pictures: [m] = mode m, all 35; other inter pictures: [0..8] = stage1_mode(i) for the first points_modes(point) entries,
+// [9] = DC. point: the OIS point (0 when the path has none).
+OIS_HD bool all_modes_path(const Params& q) { return q.slice_type != 0 && q.temporal_layer_index == 0 && q.input_resolution != 3; }
+
+// the stage-1 / intra-picture winner of the CU, -1 when the CU ran no such search or nothing beat the initial 32 * 32 * 255
+OIS_HD int cu_winner(const Params& q, int n, const uint32_t* sad, int point) {
+    int count = 0;
+    if (q.slice_type == 0) count = n == 32 ? 0 : 7;
+    else if (!all_modes_path(q) && !q.limit_ois_to_dc && point > 0) count = points_modes(point);
+    uint32_t best = 32 * 32 * 255;
+    int bm = -1;
+    for (int i = 0; i < count; i++)
+        if (sad[i] < best) { best = sad[i]; bm = q.slice_type == 0 ? islice_mode(i) : stage1_mode(i); }
+    return bm;
+}
+
+// c[18] (byte images of OisCandidate_t, zero where the reference writes nothing) and total_intra_luma_mode of the CU;
+// bm: the winner in force for this CU (its own, else the last earlier one, else planar)
+OIS_HD int build_lists(const Params& q, int n, const uint32_t* sad, int point, int bm, uint32_t* c) {
+    for (int i = 0; i < kMaxCand; i++) c[i] = 0;
+    if (q.slice_type == 0) {
+        if (n == 32) { c[0] = pack(sad[0], 1, kPlanar); return 0; }
+        c[0] = pack(sad[0], 1, kPlanar); c[1] = pack(0, 0, kDc);                       // InjectIntraCandidatesBasedOnBestModeIslice
+        if (bm == kPlanar || bm == kDc) return 2;
+        c[2] = pack(0, 0, bm == 2 ? 2 : bm == kHor ? kHor : bm == 18 ? 18 : bm == kVer ? kVer : 34);
+        c[3] = pack(0, 0, bm == 2 ? 4 : bm == kHor ? 6 : bm == 18 ? 14 : bm == kVer ? 22 : 32);
+        c[4] = pack(0, 0, bm == 2 ? 6 : bm == kHor ? 14 : bm == 18 ? 22 : 30);
+        return 5;
+    }
+    if (all_modes_path(q)) {
+        // SortIntraModesOpenLoop + SortOisCandidateOpenLoop (ME.c:7828-7913): modes 0..17 seed the list, a later mode replaces
+        // the FIRST worst entry when strictly better, then the reference's swap sort (its order among equal SADs is kept)
+        uint32_t d[kMaxCand]; uint8_t m[kMaxCand];
+        for (int i = 0; i < kMaxCand; i++) { d[i] = sad[i]; m[i] = (uint8_t)i; }
+        for (int mode = kMaxCand; mode < kNumModes; mode++) {
+            int worst = 0;
+            for (int i = 1; i < kMaxCand; i++) if (d[i] > d[worst]) worst = i;
+            if (sad[mode] < d[worst]) { d[worst] = sad[mode]; m[worst] = (uint8_t)mode; }
+        }
+        for (int i = 0; i < kMaxCand; i++)
+            for (int j = i; j < kMaxCand; j++)
+                if (d[i] > d[j]) { const uint32_t t = d[i]; d[i] = d[j]; d[j] = t; const uint8_t u = m[i]; m[i] = m[j]; m[j] = u; }
+        for (int i = 0; i < kMaxCand; i++) c[i] = pack(d[i], 0, m[i]);
+        return kMaxCand;
+    }
+    if (q.limit_ois_to_dc) { c[0] = pack(sad[9], 1, kDc); return 1; }              // OpenLoopIntraDC
+    if (point == 0) { c[0] = pack(sad[9], 0, kDc); return 1; }                     // OIS_VERY_FAST_MODE
+    const int b = inject_canonical(bm);
+    // quirk: with ENCODER_MODE_CLEANUP every case of the reference's switch sets valid = (layer > 1) -- except the vertical
+    // winner's, which kept its enc-mode test (ME.c:7604-7612): TRUE above enc-mode 1
+    const int valid = (b == kVer && q.enc_mode > 1) ? 1 : q.temporal_layer_index > 1;
+    c[0] = pack(sad[inject_slot(b)], valid, b);
+    for (int k = 1; k < 9; k++) c[k] = pack(0, 0, inject_mode(b, k));
+    return points_modes(point);
+}
+
+}  // namespace ois
+}  // namespace svtme

@@ -1,0 +1,83 @@
+// ois_emul.cpp -- serial host emulation of ois_kernel (svt-av1-1_b200/csrc/ois.cu): the same ois_core.cuh functions, called in
+// the kernel's order (phase 1: neighbours -> per-mode main reference -> per-pixel prediction and SAD; phase 2a: winners; phase
+// 2b: look-back + candidate lists), so that the arithmetic the kernel shares with this file is checked against the oracle on
+// machines without a GPU. Test infrastructure only: nothing in the product links it.
+#include <string.h>
+#include "../../svt-av1-1_b200/csrc/ois_core.cuh"
+
+using namespace svtme::ois;
+
+extern "C" void ois_emul_picture(const uint8_t* pix, int stride, int w, int h, const Params* prm, const uint32_t* me_sad,
+                                 uint32_t* out_cand, uint8_t* out_total) {
+    const Params q = *prm;
+    const Picture pic = { pix, stride, w, h };
+    const int sb_cols = (w + 63) / 64, sb_rows = (h + 63) / 64;
+    const bool all_modes = all_modes_path(q);
+    for (int sb = 0; sb < sb_cols * sb_rows; sb++) {
+        static uint32_t s_sad[kCus][kNumModes];
+        int8_t s_point[kCus], s_best[kCus];
+        memset(s_sad, 0xAB, sizeof(s_sad));                              // shared memory is not initialised either
+        for (int i = 0; i < kCus; i++) s_point[i] = s_best[i] = -1;
+        const int ox = (sb % sb_cols) * 64, oy = (sb / sb_cols) * 64;
+        for (int cu = 1; cu < kCus; cu++) {
+            int cx, cy, n;
+            cu_geometry(cu, cx, cy, n);
+            const int x0 = ox + cx, y0 = oy + cy, lg = n == 8 ? 3 : n == 16 ? 4 : 5;
+            if (x0 + n > pic.w || y0 + n > pic.h) continue;
+            if (q.slice_type != 0 && q.cu8x8_mode == 1 && n == 8) continue;
+            uint8_t r[132], refbuf[104], *ref = refbuf + 32;
+            memset(r, 0xCD, sizeof(r)); memset(refbuf, 0xEF, sizeof(refbuf));
+            for (int i = 0; i <= 4 * n; i++) r[i] = (uint8_t)neighbour(pic, x0, y0, n, i);
+            int dc = 0;
+            for (int i = 0; i < 2 * n; i++) dc += i < n ? r[2 * n + 1 + i] : r[2 * n - 1 - (i - n)];
+            dc = (dc + n) >> (lg + 1);
+            const uint8_t* src = pic.pix + (long long)y0 * pic.stride + x0;
+            auto mode_sad = [&](int mode) -> uint32_t {
+                if (mode >= 2) for (int i = ref_first(n, mode); i <= 2 * n; i++) ref[i] = (uint8_t)ref_sample(r, n, mode, i);
+                uint32_t sum = 0;
+                for (int px = 0; px < n * n; px++) {
+                    const int x = px & (n - 1), y = px >> lg;
+                    const int d = (int)src[(long long)y * pic.stride + x] - pred_pixel(r, ref, n, lg, mode, x, y, dc);
+                    sum += (uint32_t)(d < 0 ? -d : d);
+                }
+                return sum;
+            };
+            if (q.slice_type == 0) {
+                if (n == 32) s_sad[cu][0] = mode_sad(kPlanar);
+                else for (int i = 0; i < 7; i++) s_sad[cu][i] = mode_sad(islice_mode(i));
+                s_point[cu] = 0;
+            } else if (all_modes) {
+                for (int m = 0; m < kNumModes; m++) s_sad[cu][m] = mode_sad(m);
+                s_point[cu] = 0;
+            } else {
+                const uint32_t dcs = mode_sad(kDc);
+                int point = 0;
+                if (!q.limit_ois_to_dc) {
+                    point = ois_point(q, me_sad[(size_t)sb * kCus + cu], dcs);
+                    if (point) for (int i = 0; i < points_modes(point); i++) s_sad[cu][i] = mode_sad(stage1_mode(i));
+                }
+                s_sad[cu][9] = dcs; s_point[cu] = (int8_t)point;
+            }
+        }
+        for (int cu = 1; cu < kCus; cu++) {
+            int cx, cy, n;
+            cu_geometry(cu, cx, cy, n);
+            if (s_point[cu] >= 0) s_best[cu] = (int8_t)cu_winner(q, n, s_sad[cu], s_point[cu]);
+        }
+        for (int cu = 0; cu < kCus; cu++) {
+            uint32_t* c = out_cand + ((size_t)sb * kCus + cu) * kMaxCand;
+            int total = 0;
+            if (cu >= 1 && s_point[cu] >= 0) {
+                int cx, cy, n;
+                cu_geometry(cu, cx, cy, n);
+                int bm = s_best[cu];
+                for (int k = cu - 1; bm < 0 && k >= 1; k--) bm = s_best[k];
+                if (bm < 0) bm = kPlanar;
+                total = build_lists(q, n, s_sad[cu], s_point[cu], bm, c);
+            } else {
+                for (int i = 0; i < kMaxCand; i++) c[i] = 0;
+            }
+            out_total[(size_t)sb * kCus + cu] = (uint8_t)total;
+        }
+    }
+}

@@ -1,0 +1,97 @@
+"""The arithmetic of the CUDA open-loop intra search (svt-av1-1_b200/csrc/ois_core.cuh, shared by ois.cu) against the oracle
+(oracle/ois_oracle.c, itself pinned to the compiled reference in test_ois_oracle_vs_ref.py) -- through a serial host emulation
+of the kernel (tests/host_emul/ois_emul.cpp) that calls the same functions in the kernel's order. CPU only."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import me_common as M
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class MeoOisParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("width", "height", "slice_type", "temporal_layer_index", "is_used_as_reference",
+                                         "cu8x8_mode", "input_resolution", "limit_ois_to_dc", "enc_mode")]
+
+
+class CoreParams(C.Structure):                                   # svtme::ois::Params == SvtMeOisParams
+    _fields_ = MeoOisParams._fields_[2:]
+
+
+OIS_CU = np.dtype([("cand", [("distortion", "<u4"), ("mode", "u1"), ("valid", "u1"), ("pad", "u1", (2,))], (18,)),
+                   ("total", "u1"), ("pad", "u1", (3,))])
+
+
+def unpack(words):
+    """byte image of OisCandidate_t -> (distortion, valid, mode)"""
+    return words & 0xFFFFF, (words >> 20) & 1, words >> 24
+
+
+def oracle_search(meo, prm, plane, me_sad):
+    n_sb = ((prm.width + 63) // 64) * ((prm.height + 63) // 64)
+    out = np.zeros((n_sb, 85), OIS_CU)
+    meo.meo_ois_picture.restype = None
+    meo.meo_ois_picture.argtypes = [C.POINTER(MeoOisParams), C.POINTER(M.MeoPlane), C.c_void_p, C.c_void_p]
+    meo.meo_ois_picture(C.byref(prm), C.byref(plane), me_sad.ctypes.data if me_sad is not None else None, out.ctypes.data)
+    return out
+
+
+def assert_same(out, cand, total, what=""):
+    d, v, m = unpack(cand)
+    assert np.array_equal(out["total"], total), what
+    for name, got in (("distortion", d), ("valid", v), ("mode", m)):
+        bad = np.argwhere(out["cand"][name] != got)
+        assert len(bad) == 0, (what, name, bad[:5].tolist(), out["cand"][name][tuple(bad[0])], got[tuple(bad[0])])
+
+
+def ois_cases():
+    """(slice_type, layer, is_ref, resolution, dc_only): every path of OpenLoopIntraSearchLcu"""
+    return [(0, 0, 1, 1, 0), (2, 0, 1, 1, 0), (2, 1, 1, 1, 0), (2, 3, 0, 1, 0), (1, 2, 1, 1, 0), (2, 0, 1, 3, 0), (2, 2, 0, 3, 0),
+            (2, 4, 0, 3, 0), (2, 2, 0, 1, 1)]
+
+
+def me_sads(rng, n_sb):
+    """ME SADs small, comparable and huge against the DC SADs, and a few zeros, so that every OIS point occurs"""
+    scale = rng.choice([0.05, 0.5, 1.0, 2.0, 8.0], size=(n_sb, 85))
+    me = (scale * rng.integers(0, 4000, size=(n_sb, 85))).astype(np.uint32)
+    me[rng.random((n_sb, 85)) < 0.05] = 0
+    return me
+
+
+@pytest.fixture(scope="module")
+def emul():
+    so = os.path.join(HERE, "host_emul", "ois_emul.so")
+    src = os.path.join(HERE, "host_emul", "ois_emul.cpp")
+    core = os.path.join(HERE, "..", "svt-av1-1_b200", "csrc", "ois_core.cuh")
+    if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(core)):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-Wall", "-o", so, src])
+    lib = C.CDLL(so)
+    lib.ois_emul_picture.restype = None
+    lib.ois_emul_picture.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(CoreParams), C.c_void_p, C.c_void_p, C.c_void_p]
+    return lib
+
+
+@pytest.mark.parametrize("w,h", [(256, 192), (200, 136), (64, 64), (328, 72)])
+@pytest.mark.parametrize("slice_type,tl,is_ref,res,dc_only", ois_cases())
+def test_kernel_arithmetic_matches_the_oracle(emul, w, h, slice_type, tl, is_ref, res, dc_only):
+    M.build_oracle()
+    meo = M.load_oracle()
+    rng = np.random.default_rng(w * 7 + h + 10 * tl + slice_type)
+    for k, synth in enumerate([dict(), dict(noise=10.0, contrast=3.0), dict(noise=0.0, contrast=0.0)]):
+        f = M.synth_video(w, h, 1, seed=5 * k + tl, **synth)[0]
+        pyr = M.build_pyramid(meo, "meo", f)
+        pl = pyr.c.full
+        n_sb = ((w + 63) // 64) * ((h + 63) // 64)
+        me = me_sads(rng, n_sb)
+        for cu8 in (0, 1):
+            enc = 3 if (tl + cu8) % 2 else 1
+            out = oracle_search(meo, MeoOisParams(w, h, slice_type, tl, is_ref, cu8, res, dc_only, enc), pl, me)
+            cand, total = np.full((n_sb, 85, 18), 0xFFFFFFFF, np.uint32), np.full((n_sb, 85), 0xFF, np.uint8)
+            prm = CoreParams(slice_type, tl, is_ref, cu8, res, dc_only, enc)
+            emul.ois_emul_picture(pl.buf + pl.origin_y * pl.stride + pl.origin_x, pl.stride, w, h, C.byref(prm), me.ctypes.data,
+                                  cand.ctypes.data, total.ctypes.data)
+            assert_same(out, cand, total, (k, cu8))
