@@ -119,7 +119,7 @@ void meo_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, co
 int  ref_zz_sad_picture(int32_t width, int32_t height, const MeoPyramid *cur, const MeoPyramid *prev,
                         uint8_t *zz_cost, uint8_t *non_moving_index);
 
-/* ---- open-loop intra search of the ME process (ois_oracle.c; the row that comes next, no CUDA path yet) -------------
+/* ---- open-loop intra search of the ME process (ois_oracle.c; checker of svtme_ois) -------------
  * OpenLoopIntraSearchLcu (EbMotionEstimation.c:8047-8365) for every SB. Per CU (raster-scan CU index 1..84 = the ME
  * pu_index of the same square) the candidate array sorted_ois_candidate[cu][] and total_intra_luma_mode[cu]; both start
  * from zero here and in the reference driver, so whole arrays compare. */

@@ -25,5 +25,8 @@ for name, prm in (("intra", pkg.SvtMeOisParams(0, 0, 1, 0, 2, 0, 1)), ("layer0_a
         t = time.perf_counter()
         cand, total = ctx.ois([(0, prm, me)])
         dt = (time.perf_counter() - t) * 1e3
-    print(f"{name}: {dt:.3f} ms per picture (synchronous call), total histogram {np.bincount(total.ravel(), minlength=19).tolist()}")
+    t = time.perf_counter()
+    ctx.ois([(0, prm, me)] * 8)                                   # one launch, grid (510, 8)
+    dt8 = (time.perf_counter() - t) * 1e3 / 8
+    print(f"{name}: {dt:.3f} ms per picture (synchronous call), {dt8:.3f} in a batch of 8; total histogram {np.bincount(total.ravel(), minlength=19).tolist()}")
 ctx.close()

@@ -69,6 +69,7 @@ struct SvtMeContext {
     int zz_cap = 0;
     uint8_t* d_ois = nullptr;             // svtme_ois: [cap] OisJob, then per job me_sad / cand / total
     int ois_cap = 0;
+    int ois_variant = 0;                  // SVTME_OIS_KERNEL: 0 = word-wise kernel (default), 1 = pixel-wise kernel, 2 = word-wise at 2 CTAs / SM (both kept for A/B)
     cudaEvent_t join_ev = nullptr;
     // chunked submission: a small batch (one mini-GOP: a handful of waves per kernel) is cut into two chunks of pictures that
     // run their kernel sequences on two streams, so the tail of one chunk's kernel is filled by the other chunk's CTAs.
@@ -196,6 +197,7 @@ int32_t svtme_create(SvtMeContext** out, int32_t device, int32_t width, int32_t 
     }
     CU(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&ctx->join_ev, cudaEventDisableTiming));
+    if (const char* e = getenv("SVTME_OIS_KERNEL")) ctx->ois_variant = std::max(0, std::min(atoi(e), 2));
     if (const char* e = getenv("SVTME_CHUNKS")) ctx->chunks = std::max(0, std::min(atoi(e), 64));
     if (ctx->chunks != 1) {
         CU(cudaEventCreateWithFlags(&ctx->fork_ev, cudaEventDisableTiming));
@@ -811,7 +813,7 @@ int32_t svtme_ois(SvtMeContext* ctx, const SvtMeOisJob* jobs, int32_t n_jobs) {
         if (jobs[i].me_sad) CU(cudaMemcpyAsync(b, jobs[i].me_sad, cus * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
     CU(cudaMemcpyAsync(ctx->d_ois, h.data(), sizeof(OisJob) * (size_t)n_jobs, cudaMemcpyHostToDevice, ctx->stream));
-    launch_ois(reinterpret_cast<const OisJob*>(ctx->d_ois), n_jobs, ctx->sb_cols, ctx->n_sb, ctx->stream);
+    launch_ois(reinterpret_cast<const OisJob*>(ctx->d_ois), n_jobs, ctx->sb_cols, ctx->n_sb, ctx->ois_variant, ctx->stream);
     ctx->launches++;
     CU(cudaGetLastError());
     for (int i = 0; i < n_jobs; i++) {

@@ -113,8 +113,153 @@ __global__ void __launch_bounds__(kOisThreads) ois_kernel(const OisJob* __restri
     job.out_total[(size_t)sb * kCus + cu] = (uint8_t)total;
 }
 
-void launch_ois(const OisJob* d_jobs, int n_jobs, int sb_cols, int n_sb, cudaStream_t st) {
-    ois_kernel<<<dim3(n_sb, n_jobs), kOisThreads, 0, st>>>(d_jobs, sb_cols, n_sb);
+// ---- the word-wise kernel -------------------------------------------------------------------------------------------------
+// Same dealing of CUs to warps and the same phase 2; phase 1 differs: the warp keeps the CU's source pixels in registers (as
+// row words and, for the horizontal modes, as column words), a lane predicts 4 adjacent pixels at a time (ois_core.cuh:
+// angular_word -- two aligned shared-memory words, two pixels per multiply-add) and VABSDIFF4-accumulates them; CUs are handed
+// out largest first from a shared counter, so that the four 32x32 CUs do not make four of the eight warps twice as long.
+template <int LG>
+__device__ __forceinline__ void search_cu_words(const OisJob& job, const Params& q, const Picture& pic, int sb, int cu, int x0, int y0,
+                                                uint8_t* r, uint8_t* vbuf, uint8_t* hbuf, uint32_t* sad_row, int8_t* s_point, int lane, bool all_modes) {
+    constexpr int n = 1 << LG, W = (n * n) / (LG == 3 ? 2 : 4) / 32;
+    __syncwarp();
+    for (int i = lane; i <= 4 * n; i += 32) r[i] = (uint8_t)neighbour(pic, x0, y0, n, i);
+    __syncwarp();
+    int dc;
+    {
+        int part = 0;
+        for (int i = lane; i < 2 * n; i += 32) part += i < n ? r[2 * n + 1 + i] : r[2 * n - 1 - (i - n)];
+        dc = (__reduce_add_sync(0xffffffffu, part) + n) >> (LG + 1);
+    }
+    // main references of the vertical / horizontal modes, [32 + i], i = 0..2n; [32 + i], i < 0, is projected per mode
+    for (int i = lane; i <= 2 * n; i += 32) {
+        vbuf[32 + i] = (uint8_t)straight_sample(r, n, true, i);
+        hbuf[32 + i] = (uint8_t)straight_sample(r, n, false, i);
+    }
+    __syncwarp();
+    const uint8_t* src = pic.pix + (size_t)y0 * pic.stride + x0;
+    uint32_t srow[W], scol[W];
+#pragma unroll
+    for (int k = 0; k < W; k++) {
+        int j, i0;
+        word_pos(LG, lane, k, j, i0);
+        srow[k] = source_word(src, pic.stride, LG, j, i0, false);
+        scol[k] = source_word(src, pic.stride, LG, j, i0, true);
+    }
+    auto mode_sad = [&](int mode) -> uint32_t {
+        uint32_t part = 0;
+        if (mode < 2) {
+#pragma unroll
+            for (int k = 0; k < W; k++) {
+                int j, i0;
+                word_pos(LG, lane, k, j, i0);
+                part += sad_word(flat_word(r, LG, mode, j, i0, dc), srow[k]);
+            }
+        } else {
+            const int a = angle_of(mode);
+            const bool vertical = mode >= 18;
+            uint8_t* refbuf = vertical ? vbuf : hbuf;
+            if (a < 0) {                                                                 // at most n <= 32 projected samples
+                __syncwarp();
+                const int i = ref_first(n, mode) + lane;
+                if (i < 0) refbuf[32 + i] = (uint8_t)ref_sample(r, n, mode, i);
+                __syncwarp();
+            }
+#pragma unroll
+            for (int k = 0; k < W; k++) {
+                int j, i0;
+                word_pos(LG, lane, k, j, i0);
+                part += sad_word(angular_word(refbuf, r, LG, vertical, a, j, i0), vertical ? srow[k] : scol[k]);
+            }
+        }
+        return __reduce_add_sync(0xffffffffu, part);
+    };
+    // one call site for mode_sad (the unrolled word loops are large): the path only decides which mode comes i-th and where its
+    // SAD goes; the inter path starts with DC (slot 9), whose SAD against the ME SAD sets how many stage-1 directions follow
+    const bool intra = q.slice_type == 0;
+    int count = intra ? (n == 32 ? 1 : 7) : all_modes ? kNumModes : 1, point = 0;
+    for (int i = 0; i < count; i++) {
+        int mode, slot;
+        if (intra) { mode = islice_mode(i); slot = i; }
+        else if (all_modes) { mode = i; slot = i; }
+        else if (i == 0) { mode = kDc; slot = 9; }
+        else { mode = stage1_mode(i - 1); slot = i - 1; }
+        const uint32_t s = mode_sad(mode);
+        if (lane == 0) sad_row[slot] = s;
+        if (!intra && !all_modes && i == 0 && !q.limit_ois_to_dc) {
+            point = ois_point(q, job.me_sad[(size_t)sb * kCus + cu], s);
+            if (point) count = 1 + points_modes(point);
+        }
+    }
+    if (lane == 0) s_point[cu] = (int8_t)point;
+}
+
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(kOisThreads, MIN_CTAS) ois_words_kernel(const OisJob* __restrict__ jobs, int sb_cols, int n_sb) {
+    __shared__ uint8_t s_r[8][132];
+    __shared__ uint32_t s_refbuf[8][2][26];          // per warp: vertical / horizontal main reference, 104 bytes, word aligned
+    __shared__ uint32_t s_sad[kCus][kNumModes];
+    __shared__ int8_t s_point[kCus];
+    __shared__ int8_t s_best[kCus];
+    __shared__ int s_next;
+    const OisJob& job = jobs[blockIdx.y];
+    const int sb = blockIdx.x;
+    if (sb >= n_sb) return;
+    const Params q = job.prm;
+    const Picture pic = { job.plane.at(0, 0), job.plane.stride, job.plane.w, job.plane.h };
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ox = (sb % sb_cols) * 64, oy = (sb / sb_cols) * 64;
+    const bool all_modes = all_modes_path(q);
+    if (tid < kCus) { s_point[tid] = -1; s_best[tid] = -1; }
+    if (tid == 0) s_next = 1;
+    __syncthreads();
+
+    for (;;) {
+        int cu = 0;
+        if (lane == 0) cu = atomicAdd(&s_next, 1);
+        cu = __shfl_sync(0xffffffffu, cu, 0);
+        if (cu >= kCus) break;
+        int cx, cy, n;
+        cu_geometry(cu, cx, cy, n);
+        const int x0 = ox + cx, y0 = oy + cy;
+        if (x0 + n > pic.w || y0 + n > pic.h) continue;                                  // raster_scan_cu_validity
+        if (q.slice_type != 0 && q.cu8x8_mode == 1 && n == 8) continue;
+        uint8_t* vbuf = reinterpret_cast<uint8_t*>(s_refbuf[warp][0]);
+        uint8_t* hbuf = reinterpret_cast<uint8_t*>(s_refbuf[warp][1]);
+        if (n == 32) search_cu_words<5>(job, q, pic, sb, cu, x0, y0, s_r[warp], vbuf, hbuf, s_sad[cu], s_point, lane, all_modes);
+        else if (n == 16) search_cu_words<4>(job, q, pic, sb, cu, x0, y0, s_r[warp], vbuf, hbuf, s_sad[cu], s_point, lane, all_modes);
+        else search_cu_words<3>(job, q, pic, sb, cu, x0, y0, s_r[warp], vbuf, hbuf, s_sad[cu], s_point, lane, all_modes);
+    }
+    __syncthreads();
+
+    const int cu = tid;
+    const bool searched = cu >= 1 && cu < kCus && s_point[cu] >= 0;
+    int cx = 0, cy = 0, n = 8;
+    if (cu >= 1 && cu < kCus) cu_geometry(cu, cx, cy, n);
+    if (searched) s_best[cu] = (int8_t)cu_winner(q, n, s_sad[cu], s_point[cu]);
+    __syncthreads();
+    if (cu < 1 || cu >= kCus) return;
+    uint32_t c[kMaxCand];
+    int total = 0;
+    if (searched) {
+        int bm = s_best[cu];
+        for (int k = cu - 1; bm < 0 && k >= 1; k--) bm = s_best[k];
+        if (bm < 0) bm = kPlanar;
+        total = build_lists(q, n, s_sad[cu], s_point[cu], bm, c);
+    } else {
+#pragma unroll
+        for (int i = 0; i < kMaxCand; i++) c[i] = 0;
+    }
+    uint32_t* out = job.out_cand + ((size_t)sb * kCus + cu) * kMaxCand;
+#pragma unroll
+    for (int i = 0; i < kMaxCand; i++) out[i] = c[i];
+    job.out_total[(size_t)sb * kCus + cu] = (uint8_t)total;
+}
+
+void launch_ois(const OisJob* d_jobs, int n_jobs, int sb_cols, int n_sb, int variant, cudaStream_t st) {
+    if (variant == 1) ois_kernel<<<dim3(n_sb, n_jobs), kOisThreads, 0, st>>>(d_jobs, sb_cols, n_sb);
+    else if (variant == 2) ois_words_kernel<2><<<dim3(n_sb, n_jobs), kOisThreads, 0, st>>>(d_jobs, sb_cols, n_sb);
+    else ois_words_kernel<4><<<dim3(n_sb, n_jobs), kOisThreads, 0, st>>>(d_jobs, sb_cols, n_sb);   // 64 registers, 4 CTAs / SM: measured fastest
 }
 
 }  // namespace svtme

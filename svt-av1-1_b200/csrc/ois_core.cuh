@@ -54,12 +54,13 @@ OIS_HD int neighbour(const Picture& p, int x0, int y0, int n, int idx) {
 OIS_HD int angle_of(int mode) {
     const int d = mode < 18 ? mode - 10 : mode - 26;                // distance from pure horizontal / vertical
     const int m = d < 0 ? -d : d;
-    const int mag = m == 0 ? 0 : m == 1 ? 2 : m == 2 ? 5 : m == 3 ? 9 : m == 4 ? 13 : m == 5 ? 17 : m == 6 ? 21 : m == 7 ? 26 : 32;
+    const int mag = (int)((0x2069544D245080ull >> (6 * m)) & 63);    // 0 2 5 9 13 17 21 26 32, six bits each (no jump table on the device)
     return (mode < 18 ? -d : d) < 0 ? -mag : mag;                   // horizontal modes: 2 -> +32 ... 17 -> -26; vertical: 18 -> -32 ... 34 -> +32
 }
 OIS_HD int inv_angle_of(int mode) {                                 // only for the negative angles (modes 11..25)
     const int d = mode < 18 ? mode - 10 : 26 - mode;                // 1..8
-    return d == 1 ? -4096 : d == 2 ? -1638 : d == 3 ? -910 : d == 4 ? -630 : d == 5 ? -482 : d == 6 ? -390 : d == 7 ? -315 : -256;
+    const unsigned long long t = d <= 4 ? 0x13B0E38CCD000ull : 0x8004EC30C1E2ull;   // 4096 1638 910 630 | 482 390 315 256, 13 bits each
+    return -(int)((t >> (13 * ((d - 1) & 3))) & 8191);
 }
 
 // Main reference of an angular mode: ref[i], i in [-n, 2n]; i = 0 is the top-left sample, i > 0 runs along the top row
@@ -72,6 +73,9 @@ OIS_HD int ref_sample(const uint8_t* r, int n, int mode, int i) {
     const int k = (i * inv_angle_of(mode) + 128) >> 8;
     return vertical ? left[-(k - 1)] : top[k - 1];
 }
+// the i >= 0 part does not depend on the angle: the word-wise kernel keeps it per CU (one buffer per direction) and only
+// projects the i < 0 part per mode
+OIS_HD int straight_sample(const uint8_t* r, int n, bool vertical, int i) { return vertical ? r[2 * n + i] : r[2 * n - i]; }
 OIS_HD int ref_first(int n, int mode) { const int a = angle_of(mode); return a < 0 ? (n * a) >> 5 : 0; }   // lowest index that is read
 
 OIS_HD int clip8(int v) { return v < 0 ? 0 : v > 255 ? 255 : v; }
@@ -102,12 +106,75 @@ OIS_HD int pred_pixel(const uint8_t* r, const uint8_t* ref, int n, int lg, int m
     return f ? ((32 - f) * ref[i + idx + 1] + f * ref[i + idx + 2] + 16) >> 5 : ref[i + idx + 1];
 }
 
+// ---- word-wise prediction (the fast kernel): a lane predicts K adjacent pixels at once --------------------------------------
+// A CU of n x n pixels is cut into words of K pixels (K = 4, 8x8 CUs: 2) that run along the MINOR axis i of the mode at a
+// fixed MAJOR coordinate j: vertical modes (>= 18), planar and DC: i = x, j = y (a piece of a row); horizontal modes (2..17):
+// i = y, j = x (a piece of a column, compared with the transposed source word). With that choice every angular mode is the
+// same code: the K pixels interpolate K + 1 consecutive samples of the main reference with one fraction.
+OIS_HD int word_pixels(int lg) { return lg == 3 ? 2 : 4; }
+OIS_HD int words_per_lane(int lg) { return ((1 << lg) << lg) / word_pixels(lg) / 32; }           // 8x8: 1, 16x16: 2, 32x32: 8
+OIS_HD void word_pos(int lg, int lane, int k, int& j, int& i0) {
+    const int wi = lane + 32 * k;
+    j = wi & ((1 << lg) - 1);
+    i0 = (wi >> lg) * word_pixels(lg);
+}
+// K source pixels from (x, y), stepping (dx, dy); byte t of the result = pixel t, unused bytes 0
+OIS_HD uint32_t source_word(const uint8_t* src, int stride, int lg, int j, int i0, bool transposed) {
+    uint32_t w = 0;
+    for (int t = 0; t < word_pixels(lg); t++) {
+        const int x = transposed ? j : i0 + t, y = transposed ? i0 + t : j;
+        w |= (uint32_t)src[(long long)y * stride + x] << (8 * t);
+    }
+    return w;
+}
+OIS_HD uint32_t sad_word(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __vsadu4(a, b);
+#else
+    uint32_t s = 0;
+    for (int t = 0; t < 4; t++) { const int d = (int)((a >> (8 * t)) & 255) - (int)((b >> (8 * t)) & 255); s += (uint32_t)(d < 0 ? -d : d); }
+    return s;
+#endif
+}
+// planar / DC word of row j from column i0
+OIS_HD uint32_t flat_word(const uint8_t* r, int lg, int mode, int j, int i0, int dc) {
+    uint32_t w = 0;
+    for (int t = 0; t < word_pixels(lg); t++) w |= (uint32_t)pred_pixel(r, nullptr, 1 << lg, lg, mode, i0 + t, j, dc) << (8 * t);
+    return w;
+}
+// angular word. refbuf: 4-byte aligned, refbuf[32 + i] = ref[i] of ref_sample(); a = angle_of(mode). Two pixels share one
+// 32-bit multiply-add (16-bit fields: 255 * 32 + 16 fits); a fraction of 0 reproduces the sample itself, so there is no branch.
+OIS_HD uint32_t angular_word(const uint8_t* refbuf, const uint8_t* r, int lg, bool vertical, int a, int j, int i0) {
+    const int n = 1 << lg;
+    const int pos = (j + 1) * a, idx = pos >> 5;
+    const uint32_t f = (uint32_t)(pos & 31);
+    const int b = 32 + i0 + idx + 1;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(refbuf) + (b >> 2);
+    const uint32_t w0 = w[0], w1 = w[1];
+    const int s = (b & 3) * 8;
+#if defined(__CUDA_ARCH__)
+    const uint32_t lo = __funnelshift_r(w0, w1, s);
+#else
+    const uint32_t lo = (uint32_t)((((uint64_t)w1 << 32) | w0) >> s);
+#endif
+    const uint32_t b4 = (w1 >> s) & 0xFFu;
+    const uint32_t e02 = lo & 0x00FF00FFu, e13 = (lo >> 8) & 0x00FF00FFu, e24 = (e02 >> 16) | (b4 << 16);
+    const uint32_t p02 = ((e02 * (32u - f) + e13 * f + 0x00100010u) >> 5) & 0x00FF00FFu;
+    const uint32_t p13 = ((e13 * (32u - f) + e24 * f + 0x00100010u) >> 5) & 0x00FF00FFu;
+    uint32_t p = p02 | (p13 << 8);
+    if (a == 0 && lg < 5 && i0 == 0) {                              // boundary smoothing of the pure modes: first pixel of the line
+        const int side = vertical ? r[2 * n - 1 - j] : r[2 * n + 1 + j];
+        p = (p & ~0xFFu) | (uint32_t)clip8((int)refbuf[33] + ((side - (int)refbuf[32]) >> 1));
+    }
+    return lg == 3 ? (p & 0xFFFFu) : p;
+}
+
 // ---- candidate lists (per CU, after the SADs) --------------------------------------------------------------------------
 OIS_HD uint32_t pack(uint32_t distortion, int valid, int mode) {     // byte image of OisCandidate_t (EbCodingUnit.h:303-313)
     return (distortion & 0xFFFFFu) | ((uint32_t)(valid & 1) << 20) | ((uint32_t)mode << 24);
 }
-OIS_HD int islice_mode(int i) { return i == 0 ? kPlanar : i == 1 ? kDc : i == 2 ? kHor : i == 3 ? kVer : i == 4 ? 2 : i == 5 ? 18 : 34; }   // iSliceModesArray[0..6]
-OIS_HD int stage1_mode(int i) { return i == 0 ? kHor : i == 1 ? kVer : i == 2 ? 2 : i == 3 ? 18 : i == 4 ? 34 : i == 5 ? 6 : i == 6 ? 14 : i == 7 ? 22 : 30; }   // stage1ModesArray
+OIS_HD int islice_mode(int i) { return (int)((0x2248268A040ull >> (6 * i)) & 63); }        // iSliceModesArray[0..6] = 0 1 10 26 2 18 34
+OIS_HD int stage1_mode(int i) { return (int)((0x1E58E1A248268Aull >> (6 * i)) & 63); }     // stage1ModesArray = 10 26 2 18 34 6 14 22 30
 OIS_HD int points_modes(int point) { return 2 * point + 1; }          // numberOfOisModePoints = intraSearchInMd[point][depth 1..3] = 1, 3, 5, 7, 9
 
 // OIS point from the DC SAD and the ME SAD of the same square (GetInterIntraSadDistance + GetOisPoint, ME.c:7747-7826)

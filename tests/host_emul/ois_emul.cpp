@@ -81,3 +81,101 @@ extern "C" void ois_emul_picture(const uint8_t* pix, int stride, int w, int h, c
         }
     }
 }
+
+// The word-wise kernel (ois_words_kernel), lane by lane: source words in "registers" per lane, the main reference in a word
+// aligned buffer whose unwritten bytes hold junk, flat_word / angular_word / sad_word per word, the sum over lanes and words.
+template <int LG>
+static uint32_t words_mode_sad(const Picture& pic, int x0, int y0, const uint8_t* r, uint32_t (*refwords)[26], int mode, int dc) {
+    constexpr int n = 1 << LG, W = (n * n) / (LG == 3 ? 2 : 4) / 32;
+    static_assert(W == (LG == 3 ? 1 : LG == 4 ? 2 : 8), "words per lane");
+    const uint8_t* src = pic.pix + (long long)y0 * pic.stride + x0;
+    // [0] / [1]: the vertical / horizontal main reference; i >= 0 was filled once for the CU, i < 0 is projected per mode and
+    // whatever an earlier mode left below ref_first stays there
+    uint8_t* refbuf = reinterpret_cast<uint8_t*>(refwords[mode >= 18 ? 0 : 1]);
+    if (mode >= 2 && angle_of(mode) < 0)
+        for (int lane = 0; lane < 32; lane++) { const int i = ref_first(n, mode) + lane; if (i < 0) refbuf[32 + i] = (uint8_t)ref_sample(r, n, mode, i); }
+    uint32_t sum = 0;
+    for (int lane = 0; lane < 32; lane++)
+        for (int k = 0; k < W; k++) {
+            int j, i0;
+            word_pos(LG, lane, k, j, i0);
+            if (k >= words_per_lane(LG)) return ~0u;
+            const uint32_t srow = source_word(src, pic.stride, LG, j, i0, false), scol = source_word(src, pic.stride, LG, j, i0, true);
+            if (mode < 2) sum += sad_word(flat_word(r, LG, mode, j, i0, dc), srow);
+            else sum += sad_word(angular_word(refbuf, r, LG, mode >= 18, angle_of(mode), j, i0), mode >= 18 ? srow : scol);
+        }
+    return sum;
+}
+
+extern "C" void ois_emul_picture_words(const uint8_t* pix, int stride, int w, int h, const Params* prm, const uint32_t* me_sad,
+                                       uint32_t* out_cand, uint8_t* out_total) {
+    const Params q = *prm;
+    const Picture pic = { pix, stride, w, h };
+    const int sb_cols = (w + 63) / 64, sb_rows = (h + 63) / 64;
+    const bool all_modes = all_modes_path(q);
+    for (int sb = 0; sb < sb_cols * sb_rows; sb++) {
+        static uint32_t s_sad[kCus][kNumModes];
+        int8_t s_point[kCus], s_best[kCus];
+        memset(s_sad, 0xAB, sizeof(s_sad));
+        for (int i = 0; i < kCus; i++) s_point[i] = s_best[i] = -1;
+        const int ox = (sb % sb_cols) * 64, oy = (sb / sb_cols) * 64;
+        for (int cu = 1; cu < kCus; cu++) {
+            int cx, cy, n;
+            cu_geometry(cu, cx, cy, n);
+            const int x0 = ox + cx, y0 = oy + cy, lg = n == 8 ? 3 : n == 16 ? 4 : 5;
+            if (x0 + n > pic.w || y0 + n > pic.h) continue;
+            if (q.slice_type != 0 && q.cu8x8_mode == 1 && n == 8) continue;
+            uint8_t r[132];
+            uint32_t refwords[2][26];
+            memset(r, 0xCD, sizeof(r)); memset(refwords, 0xEF, sizeof(refwords));
+            for (int i = 0; i <= 4 * n; i++) r[i] = (uint8_t)neighbour(pic, x0, y0, n, i);
+            for (int i = 0; i <= 2 * n; i++) {
+                reinterpret_cast<uint8_t*>(refwords[0])[32 + i] = (uint8_t)straight_sample(r, n, true, i);
+                reinterpret_cast<uint8_t*>(refwords[1])[32 + i] = (uint8_t)straight_sample(r, n, false, i);
+            }
+            int dc = 0;
+            for (int i = 0; i < 2 * n; i++) dc += i < n ? r[2 * n + 1 + i] : r[2 * n - 1 - (i - n)];
+            dc = (dc + n) >> (lg + 1);
+            auto mode_sad = [&](int mode) -> uint32_t {
+                return lg == 5 ? words_mode_sad<5>(pic, x0, y0, r, refwords, mode, dc)
+                     : lg == 4 ? words_mode_sad<4>(pic, x0, y0, r, refwords, mode, dc) : words_mode_sad<3>(pic, x0, y0, r, refwords, mode, dc);
+            };
+            if (q.slice_type == 0) {
+                if (n == 32) s_sad[cu][0] = mode_sad(kPlanar);
+                else for (int i = 0; i < 7; i++) s_sad[cu][i] = mode_sad(islice_mode(i));
+                s_point[cu] = 0;
+            } else if (all_modes) {
+                for (int m = 0; m < kNumModes; m++) s_sad[cu][m] = mode_sad(m);
+                s_point[cu] = 0;
+            } else {
+                const uint32_t dcs = mode_sad(kDc);
+                int point = 0;
+                if (!q.limit_ois_to_dc) {
+                    point = ois_point(q, me_sad[(size_t)sb * kCus + cu], dcs);
+                    if (point) for (int i = 0; i < points_modes(point); i++) s_sad[cu][i] = mode_sad(stage1_mode(i));
+                }
+                s_sad[cu][9] = dcs; s_point[cu] = (int8_t)point;
+            }
+        }
+        for (int cu = 1; cu < kCus; cu++) {
+            int cx, cy, n;
+            cu_geometry(cu, cx, cy, n);
+            if (s_point[cu] >= 0) s_best[cu] = (int8_t)cu_winner(q, n, s_sad[cu], s_point[cu]);
+        }
+        for (int cu = 0; cu < kCus; cu++) {
+            uint32_t* c = out_cand + ((size_t)sb * kCus + cu) * kMaxCand;
+            int total = 0;
+            if (cu >= 1 && s_point[cu] >= 0) {
+                int cx, cy, n;
+                cu_geometry(cu, cx, cy, n);
+                int bm = s_best[cu];
+                for (int k = cu - 1; bm < 0 && k >= 1; k--) bm = s_best[k];
+                if (bm < 0) bm = kPlanar;
+                total = build_lists(q, n, s_sad[cu], s_point[cu], bm, c);
+            } else {
+                for (int i = 0; i < kMaxCand; i++) c[i] = 0;
+            }
+            out_total[(size_t)sb * kCus + cu] = (uint8_t)total;
+        }
+    }
+}

@@ -70,8 +70,9 @@ def emul():
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(core)):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-Wall", "-o", so, src])
     lib = C.CDLL(so)
-    lib.ois_emul_picture.restype = None
-    lib.ois_emul_picture.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(CoreParams), C.c_void_p, C.c_void_p, C.c_void_p]
+    for f in (lib.ois_emul_picture, lib.ois_emul_picture_words):
+        f.restype = None
+        f.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(CoreParams), C.c_void_p, C.c_void_p, C.c_void_p]
     return lib
 
 
@@ -90,8 +91,9 @@ def test_kernel_arithmetic_matches_the_oracle(emul, w, h, slice_type, tl, is_ref
         for cu8 in (0, 1):
             enc = 3 if (tl + cu8) % 2 else 1
             out = oracle_search(meo, MeoOisParams(w, h, slice_type, tl, is_ref, cu8, res, dc_only, enc), pl, me)
-            cand, total = np.full((n_sb, 85, 18), 0xFFFFFFFF, np.uint32), np.full((n_sb, 85), 0xFF, np.uint8)
             prm = CoreParams(slice_type, tl, is_ref, cu8, res, dc_only, enc)
-            emul.ois_emul_picture(pl.buf + pl.origin_y * pl.stride + pl.origin_x, pl.stride, w, h, C.byref(prm), me.ctypes.data,
-                                  cand.ctypes.data, total.ctypes.data)
-            assert_same(out, cand, total, (k, cu8))
+            for kernel in (emul.ois_emul_picture, emul.ois_emul_picture_words):        # the pixel-wise and the word-wise kernel
+                cand, total = np.full((n_sb, 85, 18), 0xFFFFFFFF, np.uint32), np.full((n_sb, 85), 0xFF, np.uint8)
+                kernel(pl.buf + pl.origin_y * pl.stride + pl.origin_x, pl.stride, w, h, C.byref(prm), me.ctypes.data,
+                       cand.ctypes.data, total.ctypes.data)
+                assert_same(out, cand, total, (k, cu8))

@@ -1,6 +1,6 @@
 """Oracle of the row that comes next -- the open-loop intra search of the ME process (oracle/ois_oracle.c) -- pinned against
 the compiled reference (OpenLoopIntraSearchLcu and its intra-prediction leaves in oracle/_ref/libsvtref.so). CPU only; there is
-no CUDA path for this row yet."""
+the CUDA side is checked against this oracle in test_ois_emul.py (host emulation) and test_zzz_ois_parity_gpu.py."""
 import ctypes as C
 
 import numpy as np
