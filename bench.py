@@ -89,6 +89,45 @@ def select_workload(name):
         SB_PER_FRAME = ((W + 63) // 64) * ((H + 63) // 64)
 
 
+def ois_specs(pkg, jobs, rows, first=0, count=None):
+    """svtme_ois specs of the bench's pictures: (slot, parameters, ME SADs of the 85 square PUs) per job. `rows`: the host
+    me_results images [job][sb][pu] (PU_RESULT_DTYPE). All pictures are B pictures of a 4-layer mini-GOP at enc-mode 3."""
+    res = 3 if W >= 3840 else 2 if W >= 1920 else 1 if W >= 1280 else 0
+    specs = []
+    for j in range(first, len(jobs) if count is None else min(len(jobs), first + count)):
+        poc, tl = jobs[j][0], jobs[j][1]
+        me = np.ascontiguousarray(rows[j]["dist0"][:, :85]).astype(np.uint32)
+        specs.append((poc, pkg.SvtMeOisParams(2, tl, 1 if tl < 3 else 0, 0, res, 0, 3), me))
+    return specs
+
+
+def measure_ois(pkg, ctx, jobs, out):
+    rows = out.numpy().view(pkg.PU_RESULT_DTYPE)[..., 0]
+    batches = [ois_specs(pkg, jobs, rows, g, 8) for g in range(0, len(jobs), 8)]
+    import torch
+    n_sb = rows.shape[1]
+    pin = (torch.empty((8, n_sb, 85, 18), dtype=torch.int32).pin_memory().numpy().view(np.uint32),      # results into pinned memory, as e2e does
+           torch.empty((8, n_sb, 85), dtype=torch.uint8).pin_memory().numpy())
+    ctx.ois(batches[0], out=pin)                                 # warm-up (grows the device buffers once)
+    ctx.set_profiling(True)
+    ctx.kernel_times(reset=True)
+    hist = np.zeros(19, np.int64)
+    dt = 0.0
+    for b in batches:
+        t0 = time.perf_counter()
+        _, total = ctx.ois(b, out=pin)
+        dt += time.perf_counter() - t0
+        hist += np.bincount(total.ravel(), minlength=19)
+    ms, n = ctx.kernel_times(reset=True)["ois"]
+    ctx.set_profiling(False)
+    return {"pictures": len(jobs), "launches": int(n), "kernel_us_per_picture": ms / len(jobs) * 1e3,
+            "call_us_per_picture": dt / len(jobs) * 1e6,
+            "total_intra_luma_mode_histogram": {str(k): int(v) for k, v in enumerate(hist) if v},
+            "note": "kernel: CUDA events around the launches (one per mini-GOP of 8 pictures: one layer-0 picture with all 35 modes, "
+                    "seven with DC + 3..9 directions by OIS point); call: host wall clock of the synchronous calls incl. ME SADs up and "
+                    "3.1 MB of candidate words per picture back into pinned memory"}
+
+
 def gop_jobs(n_pics=None):
     """[(poc, temporal_layer, ref0_poc, ref1_poc)] for pictures 1..120 in decode order."""
     jobs = []
@@ -851,6 +890,14 @@ def run_gpu_impl(args, rank, world, local_rank):
         zz_sad = {"pairs": len(pairs), "us_per_picture_pair": dt / len(pairs) * 1e6, "launches": 1,
                   "classes": {str(int(k)): int(v) for k, v in zip(*np.unique(zz, return_counts=True))},
                   "note": "host wall clock of one synchronous call for all pairs: one launch (512 bytes read per SB) and one copy of 2 bytes per SB"}
+    # ---- second side product: the open-loop intra search of the same 120 pictures (svtme_ois = OpenLoopIntraSearchLcu), one
+    # launch per mini-GOP of 8, steered by the ME SADs the e2e steps left in the host rows. Never fatal for the bench line.
+    ois = None
+    if rank == 0 and not USE_16BIT and whole_pictures:
+        try:
+            ois = measure_ois(pkg, ctx, jobs, out)
+        except Exception as e:                                   # noqa: BLE001 -- reported in the line instead
+            ois = {"error": repr(e)}
     ctx.close()
     del dev
     strong_1080p = strong_4k = peer_parity = None
@@ -928,7 +975,7 @@ def run_gpu_impl(args, rank, world, local_rank):
             "kernel_launches_per_step": {k: v[1] / args.steps for k, v in kt.items()},
             "clocks": clocks, "result_checksum": checksum, "parity_checked": parity_checked,
             "strong_1080p": strong_1080p, "strong_4k": strong_4k, "peer_parity": peer_parity,
-            "zz_sad": zz_sad,
+            "zz_sad": zz_sad, "ois": ois,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu

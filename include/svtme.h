@@ -46,7 +46,8 @@ extern "C" {
 #define SVTME_KERNEL_FULLPEL     2
 #define SVTME_KERNEL_SUBPEL      3
 #define SVTME_KERNEL_BIPRED_PACK 4
-#define SVTME_KERNEL_KINDS       5
+#define SVTME_KERNEL_OIS         5
+#define SVTME_KERNEL_KINDS       6
 
 typedef struct SvtMeContext SvtMeContext;          /* opaque: one per GPU / encoder instance */
 

@@ -19,7 +19,7 @@ EXPORTED_SYMBOLS = (
 )
 LCU_EXPORTED_SYMBOLS = ("svtme_lcu_session_create", "svtme_lcu_session_destroy", "svtme_lcu_last_error",
                         "svtme_lcu_motion_estimate", "svtme_lcu_session_stats", "svtme_lcu_motion_estimate_segment")
-KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack")
+KERNEL_KINDS = ("pyramid", "hme", "fullpel", "subpel", "bipred_pack", "ois")
 
 
 class SvtMeError(RuntimeError):
@@ -306,11 +306,16 @@ class MeContext:
         self._check(self.lib.svtme_zz_sad(self._h, jobs, n), "svtme_zz_sad")
         return zz, nm
 
-    def ois(self, specs):
+    def ois(self, specs, out=None):
         """svtme_ois for (slot, SvtMeOisParams, me_sad or None) triples: (cand [n][num_sb][85][18] uint32 byte images of
-        OisCandidate_t, total [n][num_sb][85] uint8)."""
+        OisCandidate_t, total [n][num_sb][85] uint8). out: optional (cand, total) arrays to fill, e.g. views of pinned memory."""
         n = len(specs)
-        cand, total = np.zeros((n, self.n_sb, 85, 18), np.uint32), np.zeros((n, self.n_sb, 85), np.uint8)
+        if out is None:
+            cand, total = np.zeros((n, self.n_sb, 85, 18), np.uint32), np.zeros((n, self.n_sb, 85), np.uint8)
+        else:
+            cand, total = out[0][:n], out[1][:n]
+            assert cand.dtype == np.uint32 and cand.shape == (n, self.n_sb, 85, 18) and cand.flags.c_contiguous
+            assert total.dtype == np.uint8 and total.shape == (n, self.n_sb, 85) and total.flags.c_contiguous
         jobs, keep = (SvtMeOisJob * n)(), []
         for i, (slot, prm, me) in enumerate(specs):
             jobs[i].slot, jobs[i].params = slot, prm

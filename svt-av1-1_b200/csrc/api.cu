@@ -69,7 +69,7 @@ struct SvtMeContext {
     int zz_cap = 0;
     uint8_t* d_ois = nullptr;             // svtme_ois: [cap] OisJob, then per job me_sad / cand / total
     int ois_cap = 0;
-    int ois_variant = 0;                  // SVTME_OIS_KERNEL: 0 = word-wise kernel (default), 1 = pixel-wise kernel, 2 = word-wise at 2 CTAs / SM (both kept for A/B)
+    int ois_variant = 0;                  // SVTME_OIS_KERNEL: 0 = line-per-lane kernel (default), 1 = pixel-wise, 2 = word-wise (earlier generations, kept for A/B)
     cudaEvent_t join_ev = nullptr;
     // chunked submission: a small batch (one mini-GOP: a handful of waves per kernel) is cut into two chunks of pictures that
     // run their kernel sequences on two streams, so the tail of one chunk's kernel is filled by the other chunk's CTAs.
@@ -96,8 +96,8 @@ struct SvtMeContext {
     struct Timed { int kind; cudaEvent_t a, b; };
     std::vector<Timed> timed;
     std::vector<cudaEvent_t> event_pool;
-    double kind_ms[SVTME_KERNEL_KINDS] = { 0, 0, 0, 0, 0 };
-    int64_t kind_launches[SVTME_KERNEL_KINDS] = { 0, 0, 0, 0, 0 };
+    double kind_ms[SVTME_KERNEL_KINDS] = {};
+    int64_t kind_launches[SVTME_KERNEL_KINDS] = {};
 };
 
 // Brackets one kernel launch with events when profiling is on.
@@ -813,8 +813,7 @@ int32_t svtme_ois(SvtMeContext* ctx, const SvtMeOisJob* jobs, int32_t n_jobs) {
         if (jobs[i].me_sad) CU(cudaMemcpyAsync(b, jobs[i].me_sad, cus * 4, cudaMemcpyHostToDevice, ctx->stream));
     }
     CU(cudaMemcpyAsync(ctx->d_ois, h.data(), sizeof(OisJob) * (size_t)n_jobs, cudaMemcpyHostToDevice, ctx->stream));
-    launch_ois(reinterpret_cast<const OisJob*>(ctx->d_ois), n_jobs, ctx->sb_cols, ctx->n_sb, ctx->ois_variant, ctx->stream);
-    ctx->launches++;
+    { LaunchTimer t(ctx, SVTME_KERNEL_OIS, ctx->stream); launch_ois(reinterpret_cast<const OisJob*>(ctx->d_ois), n_jobs, ctx->sb_cols, ctx->n_sb, ctx->ois_variant, ctx->stream); }
     CU(cudaGetLastError());
     for (int i = 0; i < n_jobs; i++) {
         CU(cudaMemcpyAsync(jobs[i].cand, h[i].out_cand, cus * SVTME_OIS_CANDIDATES * 4, cudaMemcpyDeviceToHost, ctx->stream));

@@ -195,7 +195,7 @@ void launch_bipred_pack(const DJob* d_jobs, int n_jobs, int max_sb, bool ext, cu
 // open-loop intra search (ois.cu): one job = one picture; me_sad [n_sb][85] (device, may be null for intra pictures),
 // out_cand [n_sb][85][18] byte images of OisCandidate_t, out_total [n_sb][85]
 struct OisJob { DPlane plane; ois::Params prm; const uint32_t* me_sad; uint32_t* out_cand; uint8_t* out_total; };
-void launch_ois(const OisJob* d_jobs, int n_jobs, int sb_cols, int n_sb, int variant, cudaStream_t st);   // variant 0: word-wise kernel; 1: pixel-wise; 2: word-wise, 2 CTAs / SM
+void launch_ois(const OisJob* d_jobs, int n_jobs, int sb_cols, int n_sb, int variant, cudaStream_t st);   // variant 0: line-per-lane kernel; 1: pixel-wise; 2: word-wise
 // zero-motion SADs (zz_sad.cu): one job = one (current, previous) picture pair
 struct ZzJob { DPlane cur16, prev16; uint8_t* out; };        // out: [2][n_sb] (zz cost, non-moving index), device
 void launch_zz_sad(const ZzJob* d_jobs, int n_jobs, int width, int height, int sb_cols, int n_sb, cudaStream_t st);

@@ -9,8 +9,10 @@
 
 #if defined(__CUDACC__)
 #define OIS_HD __host__ __device__ __forceinline__
+#define OIS_UNROLL _Pragma("unroll")
 #else
 #define OIS_HD static inline
+#define OIS_UNROLL
 #endif
 
 namespace svtme {
@@ -119,13 +121,16 @@ OIS_HD void word_pos(int lg, int lane, int k, int& j, int& i0) {
     i0 = (wi >> lg) * word_pixels(lg);
 }
 // K source pixels from (x, y), stepping (dx, dy); byte t of the result = pixel t, unused bytes 0
-OIS_HD uint32_t source_word(const uint8_t* src, int stride, int lg, int j, int i0, bool transposed) {
+OIS_HD uint32_t source_pixels(const uint8_t* src, int stride, int pixels, int j, int i0, bool transposed) {
     uint32_t w = 0;
-    for (int t = 0; t < word_pixels(lg); t++) {
+    for (int t = 0; t < pixels; t++) {
         const int x = transposed ? j : i0 + t, y = transposed ? i0 + t : j;
         w |= (uint32_t)src[(long long)y * stride + x] << (8 * t);
     }
     return w;
+}
+OIS_HD uint32_t source_word(const uint8_t* src, int stride, int lg, int j, int i0, bool transposed) {
+    return source_pixels(src, stride, word_pixels(lg), j, i0, transposed);
 }
 OIS_HD uint32_t sad_word(uint32_t a, uint32_t b) {
 #if defined(__CUDA_ARCH__)
@@ -144,7 +149,7 @@ OIS_HD uint32_t flat_word(const uint8_t* r, int lg, int mode, int j, int i0, int
 }
 // angular word. refbuf: 4-byte aligned, refbuf[32 + i] = ref[i] of ref_sample(); a = angle_of(mode). Two pixels share one
 // 32-bit multiply-add (16-bit fields: 255 * 32 + 16 fits); a fraction of 0 reproduces the sample itself, so there is no branch.
-OIS_HD uint32_t angular_word(const uint8_t* refbuf, const uint8_t* r, int lg, bool vertical, int a, int j, int i0) {
+OIS_HD uint32_t angular_pixels(const uint8_t* refbuf, const uint8_t* r, int lg, bool vertical, int a, int j, int i0, int pixels) {
     const int n = 1 << lg;
     const int pos = (j + 1) * a, idx = pos >> 5;
     const uint32_t f = (uint32_t)(pos & 31);
@@ -166,7 +171,32 @@ OIS_HD uint32_t angular_word(const uint8_t* refbuf, const uint8_t* r, int lg, bo
         const int side = vertical ? r[2 * n - 1 - j] : r[2 * n + 1 + j];
         p = (p & ~0xFFu) | (uint32_t)clip8((int)refbuf[33] + ((side - (int)refbuf[32]) >> 1));
     }
-    return lg == 3 ? (p & 0xFFFFu) : p;
+    return pixels == 2 ? (p & 0xFFFFu) : p;
+}
+OIS_HD uint32_t angular_word(const uint8_t* refbuf, const uint8_t* r, int lg, bool vertical, int a, int j, int i0) {
+    return angular_pixels(refbuf, r, lg, vertical, a, j, i0, word_pixels(lg));
+}
+
+// ---- line-per-lane prediction (the shipped kernel): lane gl of a group of n lanes owns line j = gl of the CU (a row for the
+// vertical modes, planar and DC, a column for the horizontal ones) as n / 4 words of 4 pixels; 32 / n modes run side by side
+OIS_HD uint32_t dc_line_word(const uint8_t* r, int lg, int j, int i0, int dc) {
+    const int n = 1 << lg;
+    const uint8_t* left = r + 2 * n - 1;
+    const uint8_t* top = r + 2 * n + 1;
+    uint32_t w = (uint32_t)dc * 0x01010101u;
+    if (lg < 5) {                                                    // the filtered first row and first column of 8x8 / 16x16 CUs
+        if (j == 0) {
+            w = 0;
+            for (int t = 0; t < 4; t++) w |= (uint32_t)((top[i0 + t] + 3 * dc + 2) >> 2) << (8 * t);
+        }
+        if (i0 == 0) w = (w & ~0xFFu) | (uint32_t)(j == 0 ? (left[0] + 2 * dc + top[0] + 2) >> 2 : (left[-j] + 3 * dc + 2) >> 2);
+    }
+    return w;
+}
+OIS_HD uint32_t planar_line_word(const uint8_t* r, int lg, int j, int i0) {
+    uint32_t w = 0;
+    for (int t = 0; t < 4; t++) w |= (uint32_t)pred_pixel(r, nullptr, 1 << lg, lg, kPlanar, i0 + t, j, 0) << (8 * t);
+    return w;
 }
 
 // ---- candidate lists (per CU, after the SADs) --------------------------------------------------------------------------
@@ -249,17 +279,29 @@ OIS_HD int build_lists(const Params& q, int n, const uint32_t* sad, int point, i
     if (all_modes_path(q)) {
         // SortIntraModesOpenLoop + SortOisCandidateOpenLoop (ME.c:7828-7913): modes 0..17 seed the list, a later mode replaces
         // the FIRST worst entry when strictly better, then the reference's swap sort (its order among equal SADs is kept)
-        uint32_t d[kMaxCand]; uint8_t m[kMaxCand];
-        for (int i = 0; i < kMaxCand; i++) { d[i] = sad[i]; m[i] = (uint8_t)i; }
+        // (every index into d / m below is a compile-time constant once unrolled, so that both arrays live in registers)
+        uint32_t d[kMaxCand], m[kMaxCand];
+        OIS_UNROLL
+        for (int i = 0; i < kMaxCand; i++) { d[i] = sad[i]; m[i] = (uint32_t)i; }
         for (int mode = kMaxCand; mode < kNumModes; mode++) {
+            uint32_t worst_d = d[0];
             int worst = 0;
-            for (int i = 1; i < kMaxCand; i++) if (d[i] > d[worst]) worst = i;
-            if (sad[mode] < d[worst]) { d[worst] = sad[mode]; m[worst] = (uint8_t)mode; }
+            OIS_UNROLL
+            for (int i = 1; i < kMaxCand; i++) if (d[i] > worst_d) { worst_d = d[i]; worst = i; }
+            const uint32_t s = sad[mode];
+            if (s < worst_d) {
+                OIS_UNROLL
+                for (int i = 0; i < kMaxCand; i++) if (i == worst) { d[i] = s; m[i] = (uint32_t)mode; }
+            }
         }
-        for (int i = 0; i < kMaxCand; i++)
-            for (int j = i; j < kMaxCand; j++)
-                if (d[i] > d[j]) { const uint32_t t = d[i]; d[i] = d[j]; d[j] = t; const uint8_t u = m[i]; m[i] = m[j]; m[j] = u; }
-        for (int i = 0; i < kMaxCand; i++) c[i] = pack(d[i], 0, m[i]);
+        OIS_UNROLL
+        for (int i = 0; i < kMaxCand; i++) {
+            OIS_UNROLL
+            for (int j = i + 1; j < kMaxCand; j++)
+                if (d[i] > d[j]) { const uint32_t t = d[i]; d[i] = d[j]; d[j] = t; const uint32_t u = m[i]; m[i] = m[j]; m[j] = u; }
+        }
+        OIS_UNROLL
+        for (int i = 0; i < kMaxCand; i++) c[i] = pack(d[i], 0, (int)m[i]);
         return kMaxCand;
     }
     if (q.limit_ois_to_dc) { c[0] = pack(sad[9], 1, kDc); return 1; }              // OpenLoopIntraDC

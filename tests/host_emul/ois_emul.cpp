@@ -179,3 +179,109 @@ extern "C" void ois_emul_picture_words(const uint8_t* pix, int stride, int w, in
         }
     }
 }
+
+// The line-per-lane kernel (ois_lines_kernel), pass by pass and lane by lane: n lanes per mode, 32 / n modes side by side, each
+// group of lanes with its own pair of main references; the staged path (DC, then the stage-1 directions the OIS point asks for)
+// runs its DC pass on group 0 alone, exactly like the kernel.
+template <int LG>
+static void lines_search_cu(const Picture& pic, const Params& q, const uint32_t* me_sad, int sb, int cu, int x0, int y0, uint32_t* sad_row,
+                            int8_t* s_point, bool all_modes) {
+    constexpr int n = 1 << LG, M = 32 / n, W = n / 4;
+    uint8_t r[132];
+    uint32_t refs[4][2][26];
+    memset(r, 0xCD, sizeof(r)); memset(refs, 0xEF, sizeof(refs));
+    for (int i = 0; i <= 4 * n; i++) r[i] = (uint8_t)neighbour(pic, x0, y0, n, i);
+    int dc = 0;
+    for (int i = 0; i < 2 * n; i++) dc += i < n ? r[2 * n + 1 + i] : r[2 * n - 1 - (i - n)];
+    dc = (dc + n) >> (LG + 1);
+    for (int g = 0; g < M; g++)
+        for (int i = 0; i <= 2 * n; i++) {
+            reinterpret_cast<uint8_t*>(refs[g][0])[32 + i] = (uint8_t)straight_sample(r, n, true, i);
+            reinterpret_cast<uint8_t*>(refs[g][1])[32 + i] = (uint8_t)straight_sample(r, n, false, i);
+        }
+    const uint8_t* src = pic.pix + (long long)y0 * pic.stride + x0;
+    const bool intra = q.slice_type == 0, staged = !intra && !all_modes;
+    int count = intra ? (n == 32 ? 1 : 7) : all_modes ? kNumModes : 1, point = 0, base = 0;
+    while (base < count) {
+        const bool dc_pass = staged && base == 0;
+        uint32_t group_sum[4] = { 0, 0, 0, 0 };
+        for (int g = 0; g < M; g++) {
+            const int p = base + g;
+            const bool active = dc_pass ? g == 0 : p < count;
+            int mode = kDc, slot = 9;
+            if (active && !dc_pass) {
+                slot = staged ? p - 1 : p;
+                mode = intra ? islice_mode(p) : all_modes ? p : stage1_mode(p - 1);
+            }
+            const bool angular = mode >= 2, vertical = mode >= 18;
+            const int a = angular ? angle_of(mode) : 0;
+            uint8_t* refbuf = reinterpret_cast<uint8_t*>(refs[g][vertical ? 0 : 1]);
+            if (active && a < 0)
+                for (int gl = 0; gl < n; gl++) { const int i = ref_first(n, mode) + gl; if (i < 0) refbuf[32 + i] = (uint8_t)ref_sample(r, n, mode, i); }
+            if (!active) continue;
+            for (int gl = 0; gl < n; gl++)
+                for (int k = 0; k < W; k++) {
+                    const uint32_t srow = source_pixels(src, pic.stride, 4, gl, 4 * k, false), scol = source_pixels(src, pic.stride, 4, gl, 4 * k, true);
+                    if (angular) group_sum[g] += sad_word(angular_pixels(refbuf, r, LG, vertical, a, gl, 4 * k, 4), vertical ? srow : scol);
+                    else if (mode == kDc) group_sum[g] += sad_word(dc_line_word(r, LG, gl, 4 * k, dc), srow);
+                    else group_sum[g] += sad_word(planar_line_word(r, LG, gl, 4 * k), srow);
+                }
+            sad_row[slot] = group_sum[g];
+        }
+        if (dc_pass) {
+            base = 1;
+            if (!q.limit_ois_to_dc) {
+                point = ois_point(q, me_sad[(size_t)sb * kCus + cu], group_sum[0]);
+                if (point) count = 1 + points_modes(point);
+            }
+        } else {
+            base += M;
+        }
+    }
+    s_point[cu] = (int8_t)point;
+}
+
+extern "C" void ois_emul_picture_lines(const uint8_t* pix, int stride, int w, int h, const Params* prm, const uint32_t* me_sad,
+                                       uint32_t* out_cand, uint8_t* out_total) {
+    const Params q = *prm;
+    const Picture pic = { pix, stride, w, h };
+    const int sb_cols = (w + 63) / 64, sb_rows = (h + 63) / 64;
+    const bool all_modes = all_modes_path(q);
+    for (int sb = 0; sb < sb_cols * sb_rows; sb++) {
+        static uint32_t s_sad[kCus][kNumModes];
+        int8_t s_point[kCus], s_best[kCus];
+        memset(s_sad, 0xAB, sizeof(s_sad));
+        for (int i = 0; i < kCus; i++) s_point[i] = s_best[i] = -1;
+        const int ox = (sb % sb_cols) * 64, oy = (sb / sb_cols) * 64;
+        for (int cu = 1; cu < kCus; cu++) {
+            int cx, cy, n;
+            cu_geometry(cu, cx, cy, n);
+            const int x0 = ox + cx, y0 = oy + cy;
+            if (x0 + n > pic.w || y0 + n > pic.h) continue;
+            if (q.slice_type != 0 && q.cu8x8_mode == 1 && n == 8) continue;
+            if (n == 32) lines_search_cu<5>(pic, q, me_sad, sb, cu, x0, y0, s_sad[cu], s_point, all_modes);
+            else if (n == 16) lines_search_cu<4>(pic, q, me_sad, sb, cu, x0, y0, s_sad[cu], s_point, all_modes);
+            else lines_search_cu<3>(pic, q, me_sad, sb, cu, x0, y0, s_sad[cu], s_point, all_modes);
+        }
+        for (int cu = 1; cu < kCus; cu++) {
+            int cx, cy, n;
+            cu_geometry(cu, cx, cy, n);
+            if (s_point[cu] >= 0) s_best[cu] = (int8_t)cu_winner(q, n, s_sad[cu], s_point[cu]);
+        }
+        for (int cu = 0; cu < kCus; cu++) {
+            uint32_t* c = out_cand + ((size_t)sb * kCus + cu) * kMaxCand;
+            int total = 0;
+            if (cu >= 1 && s_point[cu] >= 0) {
+                int cx, cy, n;
+                cu_geometry(cu, cx, cy, n);
+                int bm = s_best[cu];
+                for (int k = cu - 1; bm < 0 && k >= 1; k--) bm = s_best[k];
+                if (bm < 0) bm = kPlanar;
+                total = build_lists(q, n, s_sad[cu], s_point[cu], bm, c);
+            } else {
+                for (int i = 0; i < kMaxCand; i++) c[i] = 0;
+            }
+            out_total[(size_t)sb * kCus + cu] = (uint8_t)total;
+        }
+    }
+}

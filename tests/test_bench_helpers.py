@@ -48,3 +48,20 @@ def test_fullpel_ext_lane_tables():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     mod.check()
+
+
+def test_ois_specs_follow_the_job_list(pkg):
+    """bench.py's `ois` key: one svtme_ois spec per picture of a mini-GOP -- its own slot, its temporal layer (layer 3 is not a
+    reference), the ME SADs of the 85 square PUs taken from the me_results rows (also when the rows hold 209 PUs)."""
+    import numpy as np
+    jobs = bench.gop_jobs()
+    rows = np.zeros((len(jobs), 6, 209), pkg.PU_RESULT_DTYPE)
+    rows["dist0"] = np.arange(len(jobs) * 6 * 209, dtype=np.uint32).reshape(len(jobs), 6, 209)
+    specs = bench.ois_specs(pkg, jobs, rows, 8, 8)
+    assert [s[0] for s in specs] == [j[0] for j in jobs[8:16]]
+    layers = sorted(s[1].temporal_layer_index for s in specs)
+    assert layers == [0, 1, 2, 2, 3, 3, 3, 3]
+    for (slot, prm, me), j in zip(specs, range(8, 16)):
+        assert prm.slice_type == 2 and prm.is_used_as_reference == (1 if prm.temporal_layer_index < 3 else 0) and prm.input_resolution == 2
+        assert me.dtype == np.uint32 and me.shape == (6, 85) and me.flags.c_contiguous and np.array_equal(me, rows[j]["dist0"][:, :85])
+    assert len(bench.ois_specs(pkg, jobs, rows, 112, 8)) == 8 and len(bench.ois_specs(pkg, jobs, rows, 120, 8)) == 0

@@ -70,7 +70,7 @@ def emul():
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(core)):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-Wall", "-o", so, src])
     lib = C.CDLL(so)
-    for f in (lib.ois_emul_picture, lib.ois_emul_picture_words):
+    for f in (lib.ois_emul_picture, lib.ois_emul_picture_words, lib.ois_emul_picture_lines):
         f.restype = None
         f.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(CoreParams), C.c_void_p, C.c_void_p, C.c_void_p]
     return lib
@@ -92,7 +92,7 @@ def test_kernel_arithmetic_matches_the_oracle(emul, w, h, slice_type, tl, is_ref
             enc = 3 if (tl + cu8) % 2 else 1
             out = oracle_search(meo, MeoOisParams(w, h, slice_type, tl, is_ref, cu8, res, dc_only, enc), pl, me)
             prm = CoreParams(slice_type, tl, is_ref, cu8, res, dc_only, enc)
-            for kernel in (emul.ois_emul_picture, emul.ois_emul_picture_words):        # the pixel-wise and the word-wise kernel
+            for kernel in (emul.ois_emul_picture, emul.ois_emul_picture_words, emul.ois_emul_picture_lines):   # the three kernels
                 cand, total = np.full((n_sb, 85, 18), 0xFFFFFFFF, np.uint32), np.full((n_sb, 85), 0xFF, np.uint8)
                 kernel(pl.buf + pl.origin_y * pl.stride + pl.origin_x, pl.stride, w, h, C.byref(prm), me.ctypes.data,
                        cand.ctypes.data, total.ctypes.data)
