@@ -101,7 +101,29 @@ def ois_specs(pkg, jobs, rows, first=0, count=None):
     return specs
 
 
-def measure_ois(pkg, ctx, jobs, out):
+def ois_cpu_ms(frames, jobs, rows):
+    """The CPU side of the `ois` key: the reference's own OpenLoopIntraSearchLcu over one layer-0 and one layer-2 picture of the
+    sequence (oracle/_ref when it was compiled, else the oracle port), one core, ms per picture."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import me_common as M
+    kind = "reference" if cpu_reference_available() else "port"
+    if kind == "port":
+        M.build_oracle(ref=False)
+    lib, pre = (M.load_ref(), "ref") if kind == "reference" else (M.load_oracle(), "meo")
+    res = 3 if W >= 3840 else 2 if W >= 1920 else 1 if W >= 1280 else 0
+    ms = {}
+    for name, want_tl in (("layer0", 0), ("layer2", 2)):
+        j = next(i for i, job in enumerate(jobs) if job[1] == want_tl)
+        poc, tl = jobs[j][0], jobs[j][1]
+        pyr = M.build_pyramid(M.load_oracle(), "meo", np.ascontiguousarray(frames[poc]))
+        me = np.ascontiguousarray(rows[j]["dist0"][:, :85]).astype(np.uint32)
+        t0 = time.perf_counter()
+        M.ois_picture(lib, pre, M.MeoOisParams(W, H, 2, tl, 1 if tl < 3 else 0, 0, res, 0, 3), pyr.c.full, me)
+        ms[name] = (time.perf_counter() - t0) * 1e3
+    return {"kind": kind, "cores": 1, "ms_per_picture": ms}
+
+
+def measure_ois(pkg, ctx, jobs, out, frames=None):
     rows = out.numpy().view(pkg.PU_RESULT_DTYPE)[..., 0]
     batches = [ois_specs(pkg, jobs, rows, g, 8) for g in range(0, len(jobs), 8)]
     import torch
@@ -120,8 +142,14 @@ def measure_ois(pkg, ctx, jobs, out):
         hist += np.bincount(total.ravel(), minlength=19)
     ms, n = ctx.kernel_times(reset=True)["ois"]
     ctx.set_profiling(False)
+    cpu = None
+    if frames is not None:
+        try:
+            cpu = ois_cpu_ms(frames, jobs, rows)
+        except Exception as e:                                   # noqa: BLE001
+            cpu = {"error": repr(e)}
     return {"pictures": len(jobs), "launches": int(n), "kernel_us_per_picture": ms / len(jobs) * 1e3,
-            "call_us_per_picture": dt / len(jobs) * 1e6,
+            "call_us_per_picture": dt / len(jobs) * 1e6, "cpu": cpu,
             "total_intra_luma_mode_histogram": {str(k): int(v) for k, v in enumerate(hist) if v},
             "note": "kernel: CUDA events around the launches (one per mini-GOP of 8 pictures: one layer-0 picture with all 35 modes, "
                     "seven with DC + 3..9 directions by OIS point); call: host wall clock of the synchronous calls incl. ME SADs up and "
@@ -895,7 +923,7 @@ def run_gpu_impl(args, rank, world, local_rank):
     ois = None
     if rank == 0 and not USE_16BIT and whole_pictures:
         try:
-            ois = measure_ois(pkg, ctx, jobs, out)
+            ois = measure_ois(pkg, ctx, jobs, out, None if args.no_cpu_baseline else frames)
         except Exception as e:                                   # noqa: BLE001 -- reported in the line instead
             ois = {"error": repr(e)}
     ctx.close()

@@ -167,6 +167,39 @@ def zz_sad(lib, prefix, width, height, cur, prev):
     return zz, nm
 
 
+class MeoOisParams(C.Structure):                                 # oracle/me_oracle.h
+    _fields_ = [(n, C.c_int32) for n in ("width", "height", "slice_type", "temporal_layer_index", "is_used_as_reference",
+                                         "cu8x8_mode", "input_resolution", "limit_ois_to_dc", "enc_mode")]
+
+
+OIS_CU = np.dtype([("cand", [("distortion", "<u4"), ("mode", "u1"), ("valid", "u1"), ("pad", "u1", (2,))], (18,)),
+                   ("total", "u1"), ("pad", "u1", (3,))])          # MeoOisCu
+
+
+def ois_picture(lib, prefix, prm, plane, me_sad):
+    """OpenLoopIntraSearchLcu for every SB of a picture (meo_ / ref_ois_picture): [num_sb][85] OIS_CU records, zero where the
+    search writes nothing. plane: the MeoPlane of the full-resolution picture; me_sad: [num_sb][85] uint32 or None."""
+    n_sb = ((prm.width + 63) // 64) * ((prm.height + 63) // 64)
+    out = np.zeros((n_sb, 85), OIS_CU)
+    f = getattr(lib, prefix + "_ois_picture")
+    f.restype = C.c_int if prefix == "ref" else None
+    f.argtypes = [C.POINTER(MeoOisParams), C.POINTER(MeoPlane), C.c_void_p, C.c_void_p]
+    rc = f(C.byref(prm), C.byref(plane), me_sad.ctypes.data if me_sad is not None else None, out.ctypes.data)
+    if prefix == "ref" and rc != 0:
+        raise RuntimeError(f"ref_ois_picture -> {rc}")
+    return out
+
+
+def ois_assert_same(out, cand, total, what=""):
+    """OIS_CU records of the oracle against svtme_ois output (byte images of OisCandidate_t: distortion : 20, valid : 1, 3 pad
+    bits, mode : 8, and the candidate counts)."""
+    d, v, m = cand & 0xFFFFF, (cand >> 20) & 1, cand >> 24
+    assert np.array_equal(out["total"], total), what
+    for name, got in (("distortion", d), ("valid", v), ("mode", m)):
+        bad = np.argwhere(out["cand"][name] != got)
+        assert len(bad) == 0, (what, name, bad[:5].tolist(), out["cand"][name][tuple(bad[0])], got[tuple(bad[0])])
+
+
 def synth_video(width, height, n_frames, seed=0, noise=3.0, max_shift=24, contrast=1.0):
     """Deterministic synthetic luma: smooth texture + edges, per-region translation + noise.
 

@@ -65,3 +65,20 @@ def test_ois_specs_follow_the_job_list(pkg):
         assert prm.slice_type == 2 and prm.is_used_as_reference == (1 if prm.temporal_layer_index < 3 else 0) and prm.input_resolution == 2
         assert me.dtype == np.uint32 and me.shape == (6, 85) and me.flags.c_contiguous and np.array_equal(me, rows[j]["dist0"][:, :85])
     assert len(bench.ois_specs(pkg, jobs, rows, 112, 8)) == 8 and len(bench.ois_specs(pkg, jobs, rows, 120, 8)) == 0
+
+
+def test_ois_cpu_side_runs_the_reference_search():
+    """bench.py's ois.cpu: one layer-0 and one layer-2 picture through the reference's OpenLoopIntraSearchLcu (or the oracle port)."""
+    import numpy as np
+    old = bench.W, bench.H
+    bench.W, bench.H = 256, 192
+    try:
+        jobs = bench.gop_jobs(17)
+        frames = bench.synth_sequence(17, seed=2, w=256, h=192)
+        rows = np.zeros((len(jobs), 12, 85), pkg.PU_RESULT_DTYPE)
+        rows["dist0"] = 700
+        cpu = bench.ois_cpu_ms(frames, jobs, rows)
+    finally:
+        bench.W, bench.H = old
+    assert cpu["kind"] in ("reference", "port") and cpu["cores"] == 1
+    assert set(cpu["ms_per_picture"]) == {"layer0", "layer2"} and all(v > 0 for v in cpu["ms_per_picture"].values())

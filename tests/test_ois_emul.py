@@ -9,43 +9,17 @@ import numpy as np
 import pytest
 
 import me_common as M
+from me_common import MeoOisParams, ois_assert_same as assert_same  # noqa: F401  (re-exported for the GPU test)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-
-
-class MeoOisParams(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("width", "height", "slice_type", "temporal_layer_index", "is_used_as_reference",
-                                         "cu8x8_mode", "input_resolution", "limit_ois_to_dc", "enc_mode")]
 
 
 class CoreParams(C.Structure):                                   # svtme::ois::Params == SvtMeOisParams
     _fields_ = MeoOisParams._fields_[2:]
 
 
-OIS_CU = np.dtype([("cand", [("distortion", "<u4"), ("mode", "u1"), ("valid", "u1"), ("pad", "u1", (2,))], (18,)),
-                   ("total", "u1"), ("pad", "u1", (3,))])
-
-
-def unpack(words):
-    """byte image of OisCandidate_t -> (distortion, valid, mode)"""
-    return words & 0xFFFFF, (words >> 20) & 1, words >> 24
-
-
 def oracle_search(meo, prm, plane, me_sad):
-    n_sb = ((prm.width + 63) // 64) * ((prm.height + 63) // 64)
-    out = np.zeros((n_sb, 85), OIS_CU)
-    meo.meo_ois_picture.restype = None
-    meo.meo_ois_picture.argtypes = [C.POINTER(MeoOisParams), C.POINTER(M.MeoPlane), C.c_void_p, C.c_void_p]
-    meo.meo_ois_picture(C.byref(prm), C.byref(plane), me_sad.ctypes.data if me_sad is not None else None, out.ctypes.data)
-    return out
-
-
-def assert_same(out, cand, total, what=""):
-    d, v, m = unpack(cand)
-    assert np.array_equal(out["total"], total), what
-    for name, got in (("distortion", d), ("valid", v), ("mode", m)):
-        bad = np.argwhere(out["cand"][name] != got)
-        assert len(bad) == 0, (what, name, bad[:5].tolist(), out["cand"][name][tuple(bad[0])], got[tuple(bad[0])])
+    return M.ois_picture(meo, "meo", prm, plane, me_sad)
 
 
 def ois_cases():

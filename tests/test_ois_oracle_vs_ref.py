@@ -1,21 +1,13 @@
-"""Oracle of the row that comes next -- the open-loop intra search of the ME process (oracle/ois_oracle.c) -- pinned against
-the compiled reference (OpenLoopIntraSearchLcu and its intra-prediction leaves in oracle/_ref/libsvtref.so). CPU only; there is
-the CUDA side is checked against this oracle in test_ois_emul.py (host emulation) and test_zzz_ois_parity_gpu.py."""
+"""Oracle of the open-loop intra search of the ME process (oracle/ois_oracle.c) pinned against the compiled reference
+(OpenLoopIntraSearchLcu and its intra-prediction leaves in oracle/_ref/libsvtref.so). CPU only; the CUDA side is checked
+against this oracle in test_ois_emul.py (host emulation of the kernels) and test_zzz_ois_parity_gpu.py (through the C-ABI)."""
 import ctypes as C
 
 import numpy as np
 import pytest
 
 import me_common as M
-
-
-class MeoOisParams(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("width", "height", "slice_type", "temporal_layer_index", "is_used_as_reference",
-                                         "cu8x8_mode", "input_resolution", "limit_ois_to_dc", "enc_mode")]
-
-
-OIS_CU = np.dtype([("cand", [("distortion", "<u4"), ("mode", "u1"), ("valid", "u1"), ("pad", "u1", (2,))], (18,)),
-                   ("total", "u1"), ("pad", "u1", (3,))])
+from me_common import MeoOisParams
 
 
 @pytest.fixture(scope="module")
@@ -58,11 +50,7 @@ def test_every_predictor_matches_the_reference_leaves(libs, n):
 
 
 def _search(lib, pre, prm, pyr, me_sad):
-    n_sb = ((prm.width + 63) // 64) * ((prm.height + 63) // 64)
-    out = np.zeros((n_sb, 85), OIS_CU)
-    rc = getattr(lib, pre + "_ois_picture")(C.byref(prm), C.byref(pyr.c.full), me_sad.ctypes.data if me_sad is not None else None, out.ctypes.data)
-    assert not rc
-    return out
+    return M.ois_picture(lib, pre, prm, pyr.c.full, me_sad)
 
 
 @pytest.mark.parametrize("w,h", [(256, 192), (200, 136), (64, 64)])
