@@ -53,7 +53,7 @@ def _search(lib, pre, prm, pyr, me_sad):
     return M.ois_picture(lib, pre, prm, pyr.c.full, me_sad)
 
 
-@pytest.mark.parametrize("w,h", [(256, 192), (200, 136), (64, 64)])
+@pytest.mark.parametrize("w,h", [(256, 192), (200, 136), (64, 64), (328, 72), (136, 264)])
 @pytest.mark.parametrize("slice_type,tl,is_ref,res", [(0, 0, 1, 1), (2, 0, 1, 1), (2, 1, 1, 1), (2, 3, 0, 1), (1, 2, 1, 1),
                                                       (2, 0, 1, 3), (2, 2, 0, 3), (2, 1, 1, 1)])
 def test_open_loop_intra_search_matches_the_reference(libs, w, h, slice_type, tl, is_ref, res):
