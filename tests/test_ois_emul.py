@@ -71,3 +71,24 @@ def test_kernel_arithmetic_matches_the_oracle(emul, w, h, slice_type, tl, is_ref
                 kernel(pl.buf + pl.origin_y * pl.stride + pl.origin_x, pl.stride, w, h, C.byref(prm), me.ctypes.data,
                        cand.ctypes.data, total.ctypes.data)
                 assert_same(out, cand, total, (k, cu8))
+
+
+@pytest.mark.parametrize("slice_type,tl,res", [(0, 0, 1), (2, 0, 1), (2, 2, 1), (2, 3, 3)])
+def test_kernel_arithmetic_on_extreme_content(emul, slice_type, tl, res):
+    """Black, white, checkerboards, stripes and full-range noise (test_ois_oracle_vs_ref.extreme_pictures): the clipping of the
+    boundary smoothing, zero SADs (OIS point 0), ties in the best-18 selection and in the swap sort."""
+    from test_ois_oracle_vs_ref import extreme_pictures
+    M.build_oracle()
+    meo = M.load_oracle()
+    w, h = 200, 136
+    rng = np.random.default_rng(7 + tl)
+    for name, f in extreme_pictures(w, h).items():
+        pyr = M.build_pyramid(meo, "meo", f)
+        pl = pyr.c.full
+        me = rng.integers(0, 20000, size=(12, 85)).astype(np.uint32)
+        out = oracle_search(meo, MeoOisParams(w, h, slice_type, tl, 1 if tl < 3 else 0, 0, res, 0, 2), pl, me)
+        prm = CoreParams(slice_type, tl, 1 if tl < 3 else 0, 0, res, 0, 2)
+        for kernel in (emul.ois_emul_picture, emul.ois_emul_picture_words, emul.ois_emul_picture_lines):
+            cand, total = np.full((12, 85, 18), 0xFFFFFFFF, np.uint32), np.full((12, 85), 0xFF, np.uint8)
+            kernel(pl.buf + pl.origin_y * pl.stride + pl.origin_x, pl.stride, w, h, C.byref(prm), me.ctypes.data, cand.ctypes.data, total.ctypes.data)
+            assert_same(out, cand, total, name)

@@ -89,3 +89,27 @@ def test_dc_only_mode(libs):
     me = np.full((6, 85), 1000, np.uint32)
     a, b = _search(meo, "meo", prm, pyr, me), _search(ref, "ref", prm, pyr, me)
     assert a.tobytes() == b.tobytes()
+
+
+def extreme_pictures(w, h):
+    """Content that drives the predictors into their corners: black, white, a 0 / 255 checkerboard at pixel and at 8-pixel pitch,
+    vertical and horizontal stripes (the boundary smoothing of the pure modes clips both ways), full-range noise."""
+    yy, xx = np.mgrid[0:h, 0:w]
+    rng = np.random.default_rng(w * 3 + h)
+    return {"black": np.zeros((h, w), np.uint8), "white": np.full((h, w), 255, np.uint8),
+            "checker1": (((xx + yy) & 1) * 255).astype(np.uint8), "checker8": ((((xx >> 3) + (yy >> 3)) & 1) * 255).astype(np.uint8),
+            "vstripes": (((xx >> 2) & 1) * 255).astype(np.uint8), "hstripes": (((yy >> 1) & 1) * 255).astype(np.uint8),
+            "noise": rng.integers(0, 256, size=(h, w), dtype=np.uint8)}
+
+
+@pytest.mark.parametrize("slice_type,tl,res", [(0, 0, 1), (2, 0, 1), (2, 2, 1), (2, 3, 3)])
+def test_extreme_content_matches_the_reference(libs, slice_type, tl, res):
+    meo, ref = libs
+    w, h = 200, 136
+    rng = np.random.default_rng(7 + tl)
+    for name, f in extreme_pictures(w, h).items():
+        pyr = M.build_pyramid(meo, "meo", f)
+        me_sad = rng.integers(0, 20000, size=(12, 85)).astype(np.uint32)
+        prm = MeoOisParams(w, h, slice_type, tl, 1 if tl < 3 else 0, 0, res, 0, 2)
+        a, b = _search(meo, "meo", prm, pyr, me_sad), _search(ref, "ref", prm, pyr, me_sad)
+        assert a.tobytes() == b.tobytes(), name
