@@ -52,3 +52,33 @@ def test_open_loop_intra_search_matches_oracle(pkg, w, h):
     assert not cand[:, :, 0].any() and not total[:, :, 0].any()   # the 64x64 CU is never searched
     if w % 64 or h % 64:
         assert (total[0] == 0).sum() > n_sb                         # CUs outside the picture stay empty
+
+
+def test_extreme_content_matches_oracle(pkg):
+    """Black, white, checkerboards, stripes, full-range noise: zero SADs (OIS point 0), ties in the best-18 selection and the swap
+    sort, the boundary smoothing clipping both ways. One batch of 7 pictures x 4 path settings."""
+    from test_ois_oracle_vs_ref import extreme_pictures
+    M.build_oracle(ref=False)
+    meo = M.load_oracle()
+    w, h = 200, 136
+    pics = extreme_pictures(w, h)
+    rng = np.random.default_rng(11)
+    specs, want, names, keep = [], [], [], []
+    for slot, (name, f) in enumerate(pics.items()):
+        pyr = M.build_pyramid(meo, "meo", f)
+        keep.append(pyr)
+        for st, tl, res in ((0, 0, 1), (2, 0, 1), (2, 2, 1), (2, 3, 3)):
+            me = rng.integers(0, 20000, size=(12, 85)).astype(np.uint32)
+            q = (st, tl, 1 if tl < 3 else 0, 0, res, 0, 2)
+            specs.append((slot, pkg.SvtMeOisParams(*q), me))
+            want.append(oracle_search(meo, MeoOisParams(w, h, *q), pyr.c.full, me))
+            names.append((name, st, tl, res))
+    ctx = pkg.MeContext(w, h, len(pics))
+    try:
+        for slot, f in enumerate(pics.values()):
+            ctx.upload(slot, f)
+        cand, total = ctx.ois(specs)
+    finally:
+        ctx.close()
+    for k, out in enumerate(want):
+        assert_same(out, cand[k], total[k], names[k])
