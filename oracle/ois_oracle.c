@@ -1,7 +1,7 @@
 /* oracle/ois_oracle.c -- TEST INFRASTRUCTURE ONLY (never linked into the product).
  *
- * Plain-C restatement of the open-loop intra search of the ME process, the next row of the hot-path scope table
- * (DESIGN.md section 0 / section 8): OpenLoopIntraSearchLcu and what it calls
+ * Plain-C restatement of the open-loop intra search of the ME process, row (k) of the hot-path scope table
+ * (DESIGN.md section 0, section 3.8): OpenLoopIntraSearchLcu and what it calls
  * (reference Source/Lib/Codec/EbMotionEstimation.c:7419-8365, EbIntraPrediction.c:3718-3800, 5230-5430; leaves in
  * ASM_AVX2/EbIntraPrediction_Intrinsic_AVX2.c, ASM_SSE2/EbIntraPrediction_Intrinsic_SSE2.c). For every 32x32 / 16x16 /
  * 8x8 CU of an SB (raster-scan CU index 1..84; index == the ME pu_index of the same square) the reference predicts the CU
@@ -9,7 +9,8 @@
  * or all of the 35 HEVC-style intra modes, and leaves a candidate list per CU that mode decision reads.
  *
  * Pinned by tests/test_ois_oracle_vs_ref.py against the compiled reference function (oracle/_ref/libsvtref.so,
- * ref_ois_picture in ref_driver.c). No CUDA kernel consumes this yet: it is the oracle of the row that comes next.
+ * ref_ois_picture in ref_driver.c). It is the checker of svtme_ois: tests/test_ois_emul.py (host emulation of the kernels'
+ * arithmetic), tests/test_zzz_ois_parity_gpu.py (the kernels through the C-ABI), __graft_entry__.smoke().
  */
 #include "me_oracle.h"
 #include <stddef.h>
